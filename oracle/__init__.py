@@ -1,0 +1,269 @@
+"""ctypes binding of the CPU oracle (oracle/liborb_oracle.so).
+
+TEST INFRASTRUCTURE ONLY: importable from tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs.  The product package never imports this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "liborb_oracle.so")
+
+TAPS_OCV346, TAPS_OCV4 = 0, 1
+SINCOS_LIBM_F32, SINCOS_PORTABLE = 0, 1
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+
+def build(force=False):
+    srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.cc", "match_oracle.cc", "oracle_capi.cc", "orb_oracle.h",
+                                             "match_oracle.h", "Makefile")]
+    if force or not os.path.exists(_LIB) or any(os.path.getmtime(s) > os.path.getmtime(_LIB) for s in srcs):
+        subprocess.check_call(["make", "-C", _HERE, "-B", "liborb_oracle.so"], stdout=subprocess.DEVNULL)
+    return _LIB
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB):
+            build()
+        _lib = C.CDLL(_LIB)
+        _lib.oro_fast_atan2.restype = C.c_float
+        _lib.oro_fast_atan2.argtypes = [C.c_float, C.c_float]
+        _lib.oro_extractor_create.restype = C.c_void_p
+        _lib.oro_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+        _lib.oro_extractor_destroy.argtypes = [C.c_void_p]
+        _lib.oro_time_extract.restype = C.c_double
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _u8(a):
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    return a
+
+
+def resize(src, dw, dh):
+    src = _u8(src)
+    dst = np.empty((dh, dw), np.uint8)
+    lib().oro_resize(_p(src), src.shape[1], src.shape[0], src.strides[0], _p(dst), dw, dh, dw)
+    return dst
+
+
+def blur7(src, taps=TAPS_OCV4):
+    src = _u8(src)
+    dst = np.empty_like(src)
+    lib().oro_blur7(_p(src), src.shape[1], src.shape[0], src.strides[0], _p(dst), dst.strides[0], taps)
+    return dst
+
+
+def fast(img, threshold, nonmax=True):
+    """returns int32 array (n,3): x, y, response in cv::FAST order"""
+    img = np.asarray(img, dtype=np.uint8)
+    assert img.strides[1] == 1
+    cap = img.shape[0] * img.shape[1]
+    out = np.empty((max(cap, 1), 3), np.int32)
+    n = lib().oro_fast(_p(img), img.shape[1], img.shape[0], img.strides[0], threshold, int(nonmax), _p(out), cap)
+    return out[:n].copy()
+
+
+def fast_atan2(y, x):
+    return float(lib().oro_fast_atan2(C.c_float(y), C.c_float(x)))
+
+
+def hamming(a, b):
+    return lib().oro_hamming(_p(_u8(a)), _p(_u8(b)))
+
+
+def knn2(q, t):
+    q, t = _u8(q), _u8(t)
+    idx = np.empty((q.shape[0], 2), np.int32)
+    dist = np.empty((q.shape[0], 2), np.int32)
+    lib().oro_knn2(_p(q), q.shape[0], _p(t), t.shape[0], _p(idx), _p(dist))
+    return idx, dist
+
+
+def knn2_ratio(q, t):
+    q, t = _u8(q), _u8(t)
+    idx = np.empty((q.shape[0], 2), np.int32)
+    dist = np.empty((q.shape[0], 2), np.int32)
+    good = np.empty(q.shape[0], np.uint8)
+    lib().oro_knn2_ratio(_p(q), q.shape[0], _p(t), t.shape[0], _p(idx), _p(dist), _p(good))
+    return idx, dist, good
+
+
+def distribute(cands, minX, maxX, minY, maxY, N):
+    """cands: (n,3) int32 x,y,resp relative to (minX,minY).  Returns kept candidate indices in the reference's order."""
+    cands = np.ascontiguousarray(cands, dtype=np.int32)
+    keep = np.empty(max(N + 16, 64) + 16, np.int32)
+    n = lib().oro_distribute(_p(cands), cands.shape[0], minX, maxX, minY, maxY, N, _p(keep), keep.shape[0])
+    assert n <= keep.shape[0]
+    return keep[:n].copy()
+
+
+def descriptor(blurred, x, y, angle, sincos_mode=SINCOS_PORTABLE):
+    blurred = _u8(blurred)
+    d = np.empty(32, np.uint8)
+    lib().oro_descriptor(_p(blurred), blurred.strides[0], int(x), int(y), C.c_float(angle), sincos_mode, _p(d))
+    return d
+
+
+def three_maxima(hist):
+    hist = np.ascontiguousarray(hist, np.int32)
+    out = np.empty(3, np.int32)
+    lib().oro_three_maxima(_p(hist), hist.shape[0], _p(out))
+    return tuple(int(v) for v in out)
+
+
+class Extractor:
+    """Mirror of ORB_SLAM3::ORBextractor (include/ORBextractor.h:43-109) on numpy arrays."""
+
+    def __init__(self, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFAST=7, blur_taps=TAPS_OCV346,
+                 sincos_mode=SINCOS_PORTABLE):
+        self.args = (nfeatures, float(scaleFactor), nlevels, iniThFAST, minThFAST, blur_taps, sincos_mode)
+        self.nlevels = nlevels
+        self.nfeatures = nfeatures
+        self._h = lib().oro_extractor_create(nfeatures, C.c_float(scaleFactor), nlevels, iniThFAST, minThFAST, blur_taps,
+                                             sincos_mode)
+        self.scale = np.empty(nlevels, np.float32)
+        self.inv_scale = np.empty(nlevels, np.float32)
+        self.sigma2 = np.empty(nlevels, np.float32)
+        self.inv_sigma2 = np.empty(nlevels, np.float32)
+        self.quota = np.empty(nlevels, np.int32)
+        self.umax = np.empty(16, np.int32)
+        lib().oro_extractor_tables(C.c_void_p(self._h), _p(self.scale), _p(self.inv_scale), _p(self.sigma2),
+                                   _p(self.inv_sigma2), _p(self.quota), _p(self.umax))
+
+    def __del__(self):
+        try:
+            lib().oro_extractor_destroy(C.c_void_p(self._h))
+        except Exception:
+            pass
+
+    def __call__(self, img, lapping=(0, 0)):
+        """returns (monoIndex, keypoints[KP_DTYPE], descriptors[n,32])"""
+        if img is None or img.size == 0:
+            return -1, np.empty(0, KP_DTYPE), np.empty((0, 32), np.uint8)
+        img = np.asarray(img, dtype=np.uint8)
+        assert img.ndim == 2 and img.strides[1] == 1
+        cap = 4 * self.nfeatures + 64 * self.nlevels
+        kps = np.empty(cap, KP_DTYPE)
+        desc = np.empty((cap, 32), np.uint8)
+        n = C.c_int(0)
+        mono = lib().oro_extract(C.c_void_p(self._h), _p(img), img.shape[1], img.shape[0], img.strides[0], int(lapping[0]),
+                                 int(lapping[1]), _p(kps), _p(desc), cap, C.byref(n))
+        assert n.value <= cap
+        return mono, kps[:n.value].copy(), desc[:n.value].copy()
+
+    def level(self, l):
+        w, h = C.c_int(), C.c_int()
+        lib().oro_level_size(C.c_void_p(self._h), l, C.byref(w), C.byref(h))
+        out = np.empty((h.value, w.value), np.uint8)
+        lib().oro_level_pixels(C.c_void_p(self._h), l, _p(out))
+        return out
+
+    def level_candidates(self, l):
+        cap = 1 << 18
+        out = np.empty((cap, 3), np.int32)
+        n = lib().oro_level_candidates(C.c_void_p(self._h), l, _p(out), cap)
+        return out[:n].copy()
+
+    def level_keypoints(self, l):
+        cap = 4 * self.nfeatures + 64
+        out = np.empty(cap, KP_DTYPE)
+        n = lib().oro_level_keypoints(C.c_void_p(self._h), l, _p(out), cap)
+        return out[:n].copy()
+
+    def fallback_cells(self, l):
+        return lib().oro_level_fallback_cells(C.c_void_p(self._h), l)
+
+
+def _bounds(w, h):
+    return np.array([0.0, 0.0, float(w), float(h)], np.float32)
+
+
+def features_in_area(kps, w, h, x, y, r, minLevel=-1, maxLevel=-1):
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    out = np.empty(max(kps.shape[0], 1), np.int32)
+    n = lib().oro_features_in_area(kps.shape[0], _p(kps), _p(_bounds(w, h)), C.c_float(x), C.c_float(y), C.c_float(r), minLevel,
+                                   maxLevel, _p(out), out.shape[0])
+    return out[:n].copy()
+
+
+def search_by_projection_mappoints(kps, desc, scale_factors, w, h, in_view, projX, projY, level, viewCos, mpDesc, th, nnratio,
+                                   kp_mp=None, observed=None, uRight=None, projXR=None):
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    desc = _u8(desc)
+    n = kps.shape[0]
+    kp_mp = np.full(n, -1, np.int32) if kp_mp is None else np.ascontiguousarray(kp_mp, np.int32).copy()
+    f32 = lambda a: None if a is None else np.ascontiguousarray(a, np.float32)
+    u8 = lambda a: None if a is None else np.ascontiguousarray(a, np.uint8)
+    sf = f32(scale_factors); in_view = u8(in_view); projX = f32(projX); projY = f32(projY)
+    level = np.ascontiguousarray(level, np.int32); viewCos = f32(viewCos); mpDesc = _u8(mpDesc)
+    observed = u8(observed); uRight = f32(uRight); projXR = f32(projXR)
+    nm = lib().oro_search_by_projection_mappoints(n, _p(kps), _p(desc), _p(uRight), _p(sf), _p(_bounds(w, h)), in_view.shape[0],
+                                                  _p(in_view), _p(projX), _p(projY), _p(level), _p(viewCos), _p(mpDesc),
+                                                  _p(observed), _p(projXR), C.c_float(th), C.c_float(nnratio), _p(kp_mp))
+    return nm, kp_mp
+
+
+def search_by_projection_window(kps, desc, scale_factors, w, h, valid, u, v, lvl, angle, srcDesc, th, mode=0, dist_th=100,
+                                any_mp_blocks=False, check_orientation=True, kp_mp=None, observed=None, uRight=None, ur=None):
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    desc = _u8(desc)
+    n = kps.shape[0]
+    kp_mp = np.full(n, -1, np.int32) if kp_mp is None else np.ascontiguousarray(kp_mp, np.int32).copy()
+    f32 = lambda a: None if a is None else np.ascontiguousarray(a, np.float32)
+    u8 = lambda a: None if a is None else np.ascontiguousarray(a, np.uint8)
+    sf = f32(scale_factors); valid = u8(valid); u = f32(u); v = f32(v); lvl = np.ascontiguousarray(lvl, np.int32)
+    angle = f32(angle); srcDesc = _u8(srcDesc); observed = u8(observed); uRight = f32(uRight); ur = f32(ur)
+    nm = lib().oro_search_by_projection_window(n, _p(kps), _p(desc), _p(uRight), _p(sf), _p(_bounds(w, h)), valid.shape[0],
+                                               _p(valid), _p(u), _p(v), _p(lvl), _p(ur), _p(angle), _p(srcDesc), _p(observed),
+                                               C.c_float(th), mode, dist_th, int(any_mp_blocks), int(check_orientation), _p(kp_mp))
+    return nm, kp_mp
+
+
+def search_for_initialization(kps1, desc1, kps2, desc2, w, h, prev_matched, window, nnratio=0.9, check_orientation=True):
+    kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+    desc1, desc2 = _u8(desc1), _u8(desc2)
+    pm = np.ascontiguousarray(prev_matched, np.float32).copy()
+    m12 = np.empty(kps1.shape[0], np.int32)
+    nm = lib().oro_search_for_initialization(kps1.shape[0], _p(kps1), _p(desc1), kps2.shape[0], _p(kps2), _p(desc2),
+                                             _p(_bounds(w, h)), _p(pm), int(window), C.c_float(nnratio), int(check_orientation),
+                                             _p(m12))
+    return nm, m12, pm
+
+
+def stereo_matches(exL, exR, kpL, descL, kpR, descR, mb, mbf):
+    """exL / exR: oracle Extractor objects that have just extracted the left / right image."""
+    kpL = np.ascontiguousarray(kpL, KP_DTYPE); kpR = np.ascontiguousarray(kpR, KP_DTYPE)
+    descL, descR = _u8(descL), _u8(descR)
+    n = kpL.shape[0]
+    uR = np.empty(n, np.float32); depth = np.empty(n, np.float32)
+    bd = np.empty(n, np.int32); bi = np.empty(n, np.int32)
+    lib().oro_stereo_matches(C.c_void_p(exL._h), C.c_void_p(exR._h), n, _p(kpL), _p(descL), kpR.shape[0], _p(kpR), _p(descR),
+                             C.c_float(mb), C.c_float(mbf), _p(uR), _p(depth), _p(bd), _p(bi))
+    return uR, depth, bd, bi
+
+
+def time_extract(frames, nthreads, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFAST=7,
+                 blur_taps=TAPS_OCV346, sincos_mode=SINCOS_LIBM_F32, lapping=(0, 0)):
+    """frames: (n,h,w) uint8.  Returns (seconds, total keypoints)."""
+    frames = _u8(frames)
+    n, h, w = frames.shape
+    tot = C.c_longlong(0)
+    s = lib().oro_time_extract(nfeatures, C.c_float(scaleFactor), nlevels, iniThFAST, minThFAST, blur_taps, sincos_mode,
+                               _p(frames), n, w, h, int(lapping[0]), int(lapping[1]), int(nthreads), C.byref(tot))
+    return float(s), int(tot.value)

@@ -1,0 +1,325 @@
+// CPU ORACLE (test infrastructure, not product code) -- matcher side; see match_oracle.h.
+#include "match_oracle.h"
+
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstring>
+
+namespace oro {
+
+void FrameView::setBounds(float mnX, float mnY, float mxX, float mxY) {
+  minX = mnX; minY = mnY; maxX = mxX; maxY = mxY;
+  invW = (float)FRAME_GRID_COLS / (maxX - minX);  // Frame.cc:160
+  invH = (float)FRAME_GRID_ROWS / (maxY - minY);
+}
+
+// Frame::AssignFeaturesToGrid + PosInGrid, Frame.cc:434-465, 815-825.
+void FrameView::assignFeaturesToGrid() {
+  for (auto& col : grid) for (auto& c : col) c.clear();
+  for (int i = 0; i < N; i++) {
+    int posX = (int)std::round((kps[i].x - minX) * invW);
+    int posY = (int)std::round((kps[i].y - minY) * invH);
+    if (posX < 0 || posX >= FRAME_GRID_COLS || posY < 0 || posY >= FRAME_GRID_ROWS) continue;
+    grid[posX][posY].push_back(i);
+  }
+}
+
+// Frame::GetFeaturesInArea, Frame.cc:744-813.
+std::vector<int> FrameView::getFeaturesInArea(float x, float y, float r, int minLevel, int maxLevel) const {
+  std::vector<int> vIndices;
+  const float factorX = r, factorY = r;
+  const int nMinCellX = std::max(0, (int)std::floor((x - minX - factorX) * invW));
+  if (nMinCellX >= FRAME_GRID_COLS) return vIndices;
+  const int nMaxCellX = std::min((int)FRAME_GRID_COLS - 1, (int)std::ceil((x - minX + factorX) * invW));
+  if (nMaxCellX < 0) return vIndices;
+  const int nMinCellY = std::max(0, (int)std::floor((y - minY - factorY) * invH));
+  if (nMinCellY >= FRAME_GRID_ROWS) return vIndices;
+  const int nMaxCellY = std::min((int)FRAME_GRID_ROWS - 1, (int)std::ceil((y - minY + factorY) * invH));
+  if (nMaxCellY < 0) return vIndices;
+  const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+  for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+    for (int iy = nMinCellY; iy <= nMaxCellY; iy++)
+      for (int j : grid[ix][iy]) {
+        const KeyPoint& kp = kps[j];
+        if (bCheckLevels) {
+          if (kp.octave < minLevel) continue;
+          if (maxLevel >= 0 && kp.octave > maxLevel) continue;
+        }
+        const float distx = kp.x - x, disty = kp.y - y;
+        if (std::fabs(distx) < factorX && std::fabs(disty) < factorY) vIndices.push_back(j);
+      }
+  return vIndices;
+}
+
+// ORBmatcher::ComputeThreeMaxima, ORBmatcher.cc:2416-2458.
+void compute_three_maxima(const int* hs, int L, int& ind1, int& ind2, int& ind3) {
+  int max1 = 0, max2 = 0, max3 = 0;
+  for (int i = 0; i < L; i++) {
+    const int s = hs[i];
+    if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+    else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+    else if (s > max3) { max3 = s; ind3 = i; }
+  }
+  if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+  else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+}
+
+static inline bool blocks(int slot, const uint8_t* observed) {
+  if (slot == -1 || slot == -3) return false;
+  if (slot == -2) return true;
+  return observed ? observed[slot] != 0 : true;
+}
+
+// ORBmatcher.cc:44-142 (the mbTrackInView / Nleft == -1 branch) + RadiusByViewingCos :216-222.
+int search_by_projection_mappoints(FrameView& F, int nMP, const uint8_t* in_view, const float* projX, const float* projY,
+                                   const int* level, const float* viewCos, const uint8_t* mpDesc, const uint8_t* observed,
+                                   const float* projXR, float th, float nnratio, int* kp_mp) {
+  int nmatches = 0;
+  const bool bFactor = th != 1.0;
+  for (int iMP = 0; iMP < nMP; iMP++) {
+    if (!in_view[iMP]) continue;
+    const int nPredictedLevel = level[iMP];
+    float r = (viewCos[iMP] > 0.998) ? 2.5f : 4.0f;
+    if (bFactor) r *= th;
+    const std::vector<int> vIndices =
+        F.getFeaturesInArea(projX[iMP], projY[iMP], r * F.scaleFactors[nPredictedLevel], nPredictedLevel - 1, nPredictedLevel);
+    if (vIndices.empty()) continue;
+    const uint8_t* MPdescriptor = mpDesc + 32 * (size_t)iMP;
+    int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+    for (int idx : vIndices) {
+      if (blocks(kp_mp[idx], observed)) continue;
+      if (F.uRight && F.uRight[idx] > 0) {
+        const float er = std::fabs(projXR[iMP] - F.uRight[idx]);
+        if (er > r * F.scaleFactors[nPredictedLevel]) continue;
+      }
+      const int dist = hamming256(MPdescriptor, F.desc + 32 * (size_t)idx);
+      if (dist < bestDist) {
+        bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = F.kps[idx].octave; bestIdx = idx;
+      } else if (dist < bestDist2) {
+        bestLevel2 = F.kps[idx].octave; bestDist2 = dist;
+      }
+    }
+    if (bestDist <= TH_HIGH) {
+      if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+      if (bestLevel != bestLevel2 || bestDist <= nnratio * bestDist2) {
+        kp_mp[bestIdx] = iMP;
+        nmatches++;
+      }
+    }
+  }
+  return nmatches;
+}
+
+// ORBmatcher.cc:2027-2289 (Frame/Frame) and :2291-2413 (Frame/KeyFrame), search part.
+int search_by_projection_window(FrameView& F, int n, const uint8_t* valid, const float* u, const float* v, const int* lvl,
+                                const float* ur, const float* angle, const uint8_t* srcDesc, const uint8_t* observed, float th,
+                                int mode, int dist_th, bool any_mp_blocks, bool check_orientation, int* kp_mp) {
+  int nmatches = 0;
+  std::vector<int> rotHist[HISTO_LENGTH];
+  const float factor = 1.0f / HISTO_LENGTH;
+  for (int i = 0; i < n; i++) {
+    if (!valid[i]) continue;
+    const int nLastOctave = lvl[i];
+    const float radius = th * F.scaleFactors[nLastOctave];
+    std::vector<int> vIndices2;
+    if (mode == 1) vIndices2 = F.getFeaturesInArea(u[i], v[i], radius, nLastOctave, -1);
+    else if (mode == 2) vIndices2 = F.getFeaturesInArea(u[i], v[i], radius, 0, nLastOctave);
+    else vIndices2 = F.getFeaturesInArea(u[i], v[i], radius, nLastOctave - 1, nLastOctave + 1);
+    if (vIndices2.empty()) continue;
+    const uint8_t* dMP = srcDesc + 32 * (size_t)i;
+    int bestDist = 256, bestIdx2 = -1;
+    for (int i2 : vIndices2) {
+      if (any_mp_blocks ? kp_mp[i2] != -1 : blocks(kp_mp[i2], observed)) continue;
+      if (ur && F.uRight && F.uRight[i2] > 0) {
+        const float er = std::fabs(ur[i] - F.uRight[i2]);
+        if (er > radius) continue;
+      }
+      const int dist = hamming256(dMP, F.desc + 32 * (size_t)i2);
+      if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+    }
+    if (bestDist <= dist_th) {
+      kp_mp[bestIdx2] = i;
+      nmatches++;
+      if (check_orientation) {
+        float rot = angle[i] - F.kps[bestIdx2].angle;
+        if (rot < 0.0) rot += 360.0f;
+        int bin = (int)std::round(rot * factor);
+        if (bin == HISTO_LENGTH) bin = 0;
+        rotHist[bin].push_back(bestIdx2);
+      }
+    }
+  }
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1, hs[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; i++) hs[i] = (int)rotHist[i].size();
+    compute_three_maxima(hs, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++)
+      if (i != ind1 && i != ind2 && i != ind3)
+        for (int j : rotHist[i]) { kp_mp[j] = -1; nmatches--; }
+  }
+  return nmatches;
+}
+
+// ORBmatcher.cc:722-837.
+int search_for_initialization(const FrameView& F1, FrameView& F2, float* prevMatched, int windowSize, float nnratio,
+                              bool check_orientation, int* vnMatches12) {
+  int nmatches = 0;
+  for (int i = 0; i < F1.N; i++) vnMatches12[i] = -1;
+  std::vector<int> rotHist[HISTO_LENGTH];
+  const float factor = 1.0f / HISTO_LENGTH;
+  std::vector<int> vMatchedDistance(F2.N, INT_MAX), vnMatches21(F2.N, -1);
+  for (int i1 = 0; i1 < F1.N; i1++) {
+    const int level1 = F1.kps[i1].octave;
+    if (level1 > 0) continue;
+    std::vector<int> vIndices2 = F2.getFeaturesInArea(prevMatched[2 * i1], prevMatched[2 * i1 + 1], (float)windowSize, level1, level1);
+    if (vIndices2.empty()) continue;
+    const uint8_t* d1 = F1.desc + 32 * (size_t)i1;
+    int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+    for (int i2 : vIndices2) {
+      int dist = hamming256(d1, F2.desc + 32 * (size_t)i2);
+      if (vMatchedDistance[i2] <= dist) continue;
+      if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+      else if (dist < bestDist2) bestDist2 = dist;
+    }
+    if (bestDist <= TH_LOW) {
+      if (bestDist < (float)bestDist2 * nnratio) {
+        if (vnMatches21[bestIdx2] >= 0) { vnMatches12[vnMatches21[bestIdx2]] = -1; nmatches--; }
+        vnMatches12[i1] = bestIdx2;
+        vnMatches21[bestIdx2] = i1;
+        vMatchedDistance[bestIdx2] = bestDist;
+        nmatches++;
+        if (check_orientation) {
+          float rot = F1.kps[i1].angle - F2.kps[bestIdx2].angle;
+          if (rot < 0.0) rot += 360.0f;
+          int bin = (int)std::round(rot * factor);
+          if (bin == HISTO_LENGTH) bin = 0;
+          rotHist[bin].push_back(i1);
+        }
+      }
+    }
+  }
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1, hs[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; i++) hs[i] = (int)rotHist[i].size();
+    compute_three_maxima(hs, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (int idx1 : rotHist[i])
+        if (vnMatches12[idx1] >= 0) { vnMatches12[idx1] = -1; nmatches--; }
+    }
+  }
+  for (int i1 = 0; i1 < F1.N; i1++)
+    if (vnMatches12[i1] >= 0) {
+      prevMatched[2 * i1] = F2.kps[vnMatches12[i1]].x;
+      prevMatched[2 * i1 + 1] = F2.kps[vnMatches12[i1]].y;
+    }
+  return nmatches;
+}
+
+// Frame.cc:901-1079.
+void compute_stereo_matches(int N, const KeyPoint* kpL, const uint8_t* descL, int Nr, const KeyPoint* kpR, const uint8_t* descR,
+                            const std::vector<Image>& pyrL, const std::vector<Image>& pyrR, const float* mvScaleFactors,
+                            const float* mvInvScaleFactors, StereoParams sp, float* mvuRight, float* mvDepth, int* bestDistOut,
+                            int* bestIdxOut) {
+  for (int i = 0; i < N; i++) { mvuRight[i] = -1.0f; mvDepth[i] = -1.0f; if (bestDistOut) bestDistOut[i] = -1; if (bestIdxOut) bestIdxOut[i] = -1; }
+  const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
+  const int nRows = pyrL[0].h;
+  std::vector<std::vector<int>> vRowIndices(nRows);
+  for (int iR = 0; iR < Nr; iR++) {
+    const float kpY = kpR[iR].y;
+    const float r = 2.0f * mvScaleFactors[kpR[iR].octave];
+    const int maxr = (int)std::ceil(kpY + r);
+    const int minr = (int)std::floor(kpY - r);
+    for (int yi = minr; yi <= maxr; yi++)
+      if (yi >= 0 && yi < nRows) vRowIndices[yi].push_back(iR);  // out-of-range rows are UB in the reference
+  }
+  const float minZ = sp.mb, minD = 0, maxD = sp.mbf / minZ;
+  std::vector<std::pair<int, int>> vDistIdx;
+  for (int iL = 0; iL < N; iL++) {
+    const int levelL = kpL[iL].octave;
+    const float vL = kpL[iL].y, uL = kpL[iL].x;
+    const size_t row = (size_t)vL;
+    if (row >= (size_t)nRows) continue;  // UB in the reference
+    const std::vector<int>& vCandidates = vRowIndices[row];
+    if (vCandidates.empty()) continue;
+    const float minU = uL - maxD, maxU = uL - minD;
+    if (maxU < 0) continue;
+    int bestDist = TH_HIGH;
+    int bestIdxR = 0;
+    const uint8_t* dL = descL + 32 * (size_t)iL;
+    for (int iR : vCandidates) {
+      if (kpR[iR].octave < levelL - 1 || kpR[iR].octave > levelL + 1) continue;
+      const float uR = kpR[iR].x;
+      if (uR >= minU && uR <= maxU) {
+        const int dist = hamming256(dL, descR + 32 * (size_t)iR);
+        if (dist < bestDist) { bestDist = dist; bestIdxR = iR; }
+      }
+    }
+    if (bestDistOut) bestDistOut[iL] = bestDist;
+    if (bestIdxOut) bestIdxOut[iL] = bestDist < TH_HIGH ? bestIdxR : -1;
+    if (bestDist < thOrbDist) {
+      const float uR0 = kpR[bestIdxR].x;
+      const float scaleFactor = mvInvScaleFactors[levelL];
+      const float scaleduL = std::round(uL * scaleFactor);
+      const float scaledvL = std::round(vL * scaleFactor);
+      const float scaleduR0 = std::round(uR0 * scaleFactor);
+      const int w = 5;
+      const Image& imL = pyrL[levelL];
+      const Image& imR = pyrR[levelL];
+      const int y0 = (int)(scaledvL - w), xl0 = (int)(scaleduL - w);
+      if (y0 < 0 || y0 + 2 * w + 1 > imL.h || xl0 < 0 || xl0 + 2 * w + 1 > imL.w) continue;  // cv::Exception in the reference
+      short IL[11][11];
+      const int cL = imL.row(y0 + w)[xl0 + w];
+      for (int yy = 0; yy < 11; yy++) for (int xx = 0; xx < 11; xx++) IL[yy][xx] = (short)(imL.row(y0 + yy)[xl0 + xx] - cL);
+      int bestDistS = INT_MAX, bestincR = 0;
+      const int L = 5;
+      float vDists[2 * 5 + 1];
+      const float iniu = scaleduR0 + L - w;
+      const float endu = scaleduR0 + L + w + 1;
+      if (iniu < 0 || endu >= imR.w) continue;
+      bool oob = false;
+      for (int incR = -L; incR <= +L; incR++) {
+        const int xr0 = (int)(scaleduR0 + incR - w);
+        if (xr0 < 0 || xr0 + 2 * w + 1 > imR.w || y0 + 2 * w + 1 > imR.h) { oob = true; break; }  // cv::Exception in the reference
+        const int cR = imR.row(y0 + w)[xr0 + w];
+        int sum = 0;
+        for (int yy = 0; yy < 11; yy++)
+          for (int xx = 0; xx < 11; xx++) sum += std::abs((int)IL[yy][xx] - (int)(short)(imR.row(y0 + yy)[xr0 + xx] - cR));
+        float dist = (float)(double)sum;
+        if (dist < bestDistS) { bestDistS = (int)dist; bestincR = incR; }
+        vDists[L + incR] = dist;
+      }
+      if (oob) continue;
+      if (bestincR == -L || bestincR == L) continue;
+      const float dist1 = vDists[L + bestincR - 1], dist2 = vDists[L + bestincR], dist3 = vDists[L + bestincR + 1];
+      const float deltaR = (dist1 - dist3) / (2.0f * (dist1 + dist3 - 2.0f * dist2));
+      if (deltaR < -1 || deltaR > 1) continue;
+      float bestuR = mvScaleFactors[levelL] * ((float)scaleduR0 + (float)bestincR + deltaR);
+      float disparity = (uL - bestuR);
+      if (disparity >= minD && disparity < maxD) {
+        if (disparity <= 0) { disparity = 0.01; bestuR = uL - 0.01; }
+        mvDepth[iL] = sp.mbf / disparity;
+        mvuRight[iL] = bestuR;
+        vDistIdx.push_back(std::pair<int, int>(bestDistS, iL));
+      }
+    }
+  }
+  if (vDistIdx.empty()) return;  // the reference reads element 0 of an empty vector here
+  std::sort(vDistIdx.begin(), vDistIdx.end());
+  const float median = vDistIdx[vDistIdx.size() / 2].first;
+  const float thDist = 1.5f * 1.4f * median;
+  for (int i = (int)vDistIdx.size() - 1; i >= 0; i--) {
+    if (vDistIdx[i].first < thDist) break;
+    mvuRight[vDistIdx[i].second] = -1;
+    mvDepth[vDistIdx[i].second] = -1;
+  }
+}
+
+// Frame.cc:1246-1253.
+void knn2_ratio(const uint8_t* q, int nq, const uint8_t* t, int nt, int* idx, int* dist, uint8_t* good) {
+  knn2_hamming(q, nq, t, nt, idx, dist);
+  for (int i = 0; i < nq; i++) good[i] = (idx[2 * i + 1] >= 0) && ((float)dist[2 * i] < (float)dist[2 * i + 1] * 0.7);
+}
+
+}  // namespace oro

@@ -1,0 +1,74 @@
+// CPU ORACLE (test infrastructure, not product code) -- matcher side.
+// Restates, on plain arrays, the Hamming searches of the reference:
+//   Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea   src/Frame.cc:434-465, 815-825, 744-813
+//   Frame::ComputeStereoMatches                                   src/Frame.cc:901-1079
+//   Frame::ComputeStereoFishEyeMatches (kNN + ratio part)         src/Frame.cc:1228-1268
+//   ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&..)  src/ORBmatcher.cc:44-214   (mono / Nleft==-1 branch)
+//   ORBmatcher::SearchByProjection(Frame&, const Frame&, ..)      src/ORBmatcher.cc:2027-2289 (after projection)
+//   ORBmatcher::SearchByProjection(Frame&, KeyFrame*, set, ..)    src/ORBmatcher.cc:2291-2413 (after projection)
+//   ORBmatcher::SearchForInitialization                           src/ORBmatcher.cc:722-837
+//   ORBmatcher::ComputeThreeMaxima                                src/ORBmatcher.cc:2416-2458
+// Pose algebra / camera projection / MapPoint bookkeeping stay with the caller (out of scope); the
+// functions here take the already-projected (u,v), predicted level etc. exactly as the reference computes them
+// before entering the search loop.  Parity status: unpinned by the reference (it has no tests), see orb_oracle.h.
+#pragma once
+#include <cstdint>
+#include <vector>
+
+#include "orb_oracle.h"
+
+namespace oro {
+
+static const int FRAME_GRID_ROWS = 48;  // include/Frame.h:38
+static const int FRAME_GRID_COLS = 64;  // include/Frame.h:39
+static const int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;  // src/ORBmatcher.cc:36-38
+
+struct FrameView {
+  int N = 0;
+  const KeyPoint* kps = nullptr;   // mvKeysUn (pt, octave, angle)
+  const uint8_t* desc = nullptr;   // mDescriptors, N x 32
+  const float* uRight = nullptr;   // mvuRight or null (monocular)
+  const float* scaleFactors = nullptr;
+  float minX = 0, minY = 0, maxX = 0, maxY = 0;  // mnMinX.. (image bounds)
+  float invW = 0, invH = 0;                      // mfGridElementWidthInv / HeightInv
+  std::vector<int> grid[FRAME_GRID_COLS][FRAME_GRID_ROWS];
+  void setBounds(float mnX, float mnY, float mxX, float mxY);
+  void assignFeaturesToGrid();
+  std::vector<int> getFeaturesInArea(float x, float y, float r, int minLevel, int maxLevel) const;
+};
+
+void compute_three_maxima(const int* hist_sizes, int L, int& ind1, int& ind2, int& ind3);
+
+// SearchByProjection(Frame&, vector<MapPoint*>&, th, ...) -- local-map tracking.  Per map point i: in_view[i]
+// (mbTrackInView && !isBad && !far), projX/projY/level/viewCos, 32-byte descriptor, observed[i] (Observations()>0),
+// projXR (mTrackProjXR; used only when F.uRight != null).  kp_mp[] is F.mvpMapPoints as indices: -1 empty,
+// -2 = pre-existing map point with observations (blocks), -3 = pre-existing map point without observations (does not block).
+// Returns nmatches.
+int search_by_projection_mappoints(FrameView& F, int nMP, const uint8_t* in_view, const float* projX, const float* projY,
+                                   const int* level, const float* viewCos, const uint8_t* mpDesc, const uint8_t* observed,
+                                   const float* projXR, float th, float nnratio, int* kp_mp);
+
+// Window argmin used by SearchByProjection(Frame&,Frame&) (mode: 0 = [lvl-1,lvl+1], 1 = forward [lvl,inf), 2 = backward [0,lvl])
+// and SearchByProjection(Frame&,KeyFrame*) (mode 0, any_mp_blocks = true, dist_th = ORBdist, no right check).
+// valid[i]: the point exists, projects inside the image (and invzc >= 0).  ur[i] = uv.x - mbf*invzc (used when F.uRight != null).
+// angle[i]: source keypoint angle for the rotation histogram.  Returns nmatches after the rotation-consistency filter.
+int search_by_projection_window(FrameView& F, int n, const uint8_t* valid, const float* u, const float* v, const int* lvl,
+                                const float* ur, const float* angle, const uint8_t* srcDesc, const uint8_t* observed, float th,
+                                int mode, int dist_th, bool any_mp_blocks, bool check_orientation, int* kp_mp);
+
+// SearchForInitialization.  prevMatched: n1 x 2 floats (in/out).  matches12: n1 ints (out).  Returns nmatches.
+int search_for_initialization(const FrameView& F1, FrameView& F2, float* prevMatched, int windowSize, float nnratio,
+                              bool check_orientation, int* matches12);
+
+struct StereoParams { float mb, mbf; };
+// ComputeStereoMatches.  Pyramids are the un-blurred levels of the left/right extractor.  Outputs uRight/depth (N floats, -1 = none),
+// and for inspection bestDistOut/bestIdxOut (Hamming stage, -1 = skipped).
+void compute_stereo_matches(int N, const KeyPoint* kpL, const uint8_t* descL, int Nr, const KeyPoint* kpR, const uint8_t* descR,
+                            const std::vector<Image>& pyrL, const std::vector<Image>& pyrR, const float* scaleFactors,
+                            const float* invScaleFactors, StereoParams sp, float* uRight, float* depth, int* bestDistOut,
+                            int* bestIdxOut);
+
+// kNN(2) + Lowe ratio of ComputeStereoFishEyeMatches: good[i] = (#neighbours >= 2 && d0 < d1 * 0.7)
+void knn2_ratio(const uint8_t* q, int nq, const uint8_t* t, int nt, int* idx, int* dist, uint8_t* good);
+
+}  // namespace oro

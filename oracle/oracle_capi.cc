@@ -1,0 +1,169 @@
+// CPU ORACLE (test infrastructure, not product code): flat C entry points for ctypes / bench cpu_baseline.
+#include <chrono>
+#include <cstring>
+#include <thread>
+
+#include "match_oracle.h"
+#include "orb_oracle.h"
+
+using namespace oro;
+
+extern "C" {
+
+void oro_resize(const uint8_t* src, int sw, int sh, int sstride, uint8_t* dst, int dw, int dh, int dstride) {
+  resize_linear_u8(src, sw, sh, sstride, dst, dw, dh, dstride);
+}
+void oro_blur7(const uint8_t* src, int w, int h, int sstride, uint8_t* dst, int dstride, int taps) {
+  gaussian_blur7_u8(src, w, h, sstride, dst, dstride, taps);
+}
+// returns the number of keypoints (may exceed cap; only the first cap are written)
+int oro_fast(const uint8_t* img, int w, int h, int stride, int threshold, int nonmax, int* xyr, int cap) {
+  std::vector<Candidate> out;
+  fast9_16(img, w, h, stride, threshold, nonmax != 0, out);
+  for (size_t i = 0; i < out.size() && (int)i < cap; i++) { xyr[3 * i] = out[i].x; xyr[3 * i + 1] = out[i].y; xyr[3 * i + 2] = out[i].resp; }
+  return (int)out.size();
+}
+float oro_fast_atan2(float y, float x) { return fast_atan2(y, x); }
+int oro_hamming(const uint8_t* a, const uint8_t* b) { return hamming256(a, b); }
+void oro_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int* idx, int* dist) { knn2_hamming(q, nq, t, nt, idx, dist); }
+
+int oro_distribute(const int* xyr, int n, int minX, int maxX, int minY, int maxY, int N, int* keep, int cap) {
+  std::vector<Candidate> c(n);
+  for (int i = 0; i < n; i++) c[i] = {xyr[3 * i], xyr[3 * i + 1], xyr[3 * i + 2]};
+  std::vector<int> k = distribute_octtree(c, minX, maxX, minY, maxY, N);
+  for (size_t i = 0; i < k.size() && (int)i < cap; i++) keep[i] = k[i];
+  return (int)k.size();
+}
+
+void* oro_extractor_create(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh, int blur_taps, int sincos_mode) {
+  return new Extractor(nfeatures, scaleFactor, nlevels, iniTh, minTh, blur_taps, sincos_mode);
+}
+void oro_extractor_destroy(void* e) { delete (Extractor*)e; }
+void oro_extractor_tables(void* e, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2, int* quota, int* umax16) {
+  Extractor* x = (Extractor*)e;
+  for (int i = 0; i < x->nlevels; i++) {
+    scale[i] = x->mvScaleFactor[i]; inv_scale[i] = x->mvInvScaleFactor[i];
+    sigma2[i] = x->mvLevelSigma2[i]; inv_sigma2[i] = x->mvInvLevelSigma2[i];
+    quota[i] = x->mnFeaturesPerLevel[i];
+  }
+  for (int i = 0; i < 16; i++) umax16[i] = x->umax[i];
+}
+// returns monoIndex (or -1); *n = number of keypoints; kps (28 B each) / desc (32 B each) hold min(*n, cap) rows.
+int oro_extract(void* e, const uint8_t* img, int w, int h, int stride, int lap0, int lap1, KeyPoint* kps, uint8_t* desc, int cap, int* n) {
+  Extractor* x = (Extractor*)e;
+  std::vector<KeyPoint> k;
+  std::vector<uint8_t> d;
+  int mono = x->extract(img, w, h, stride, lap0, lap1, k, d);
+  *n = (int)k.size();
+  int m = std::min((int)k.size(), cap);
+  if (m > 0) { memcpy(kps, k.data(), sizeof(KeyPoint) * m); memcpy(desc, d.data(), 32 * (size_t)m); }
+  return mono;
+}
+int oro_level_size(void* e, int level, int* w, int* h) {
+  Extractor* x = (Extractor*)e;
+  *w = x->pyramid[level].w; *h = x->pyramid[level].h;
+  return 0;
+}
+void oro_level_pixels(void* e, int level, uint8_t* dst) {
+  Extractor* x = (Extractor*)e;
+  memcpy(dst, x->pyramid[level].px.data(), x->pyramid[level].px.size());
+}
+int oro_level_candidates(void* e, int level, int* xyr, int cap) {
+  Extractor* x = (Extractor*)e;
+  auto& c = x->candidates[level];
+  for (size_t i = 0; i < c.size() && (int)i < cap; i++) { xyr[3 * i] = c[i].x; xyr[3 * i + 1] = c[i].y; xyr[3 * i + 2] = c[i].resp; }
+  return (int)c.size();
+}
+int oro_level_keypoints(void* e, int level, KeyPoint* kps, int cap) {
+  Extractor* x = (Extractor*)e;
+  auto& c = x->levelKeys[level];
+  for (size_t i = 0; i < c.size() && (int)i < cap; i++) kps[i] = c[i];
+  return (int)c.size();
+}
+int oro_level_fallback_cells(void* e, int level) { return ((Extractor*)e)->fallbackCells[level]; }
+void oro_descriptor(const uint8_t* blurred, int stride, int x, int y, float angle, int sincos_mode, uint8_t* desc) {
+  orb_descriptor(blurred, stride, x, y, angle, sincos_mode, desc);
+}
+
+// Timed CPU baseline: extract `nframes` frames (dense w*h each) with `nthreads` threads, one frame per thread at a time
+// exactly as the reference runs it (one extractor object per thread).  Returns wall seconds.
+double oro_time_extract(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh, int blur_taps, int sincos_mode,
+                        const uint8_t* frames, int nframes, int w, int h, int lap0, int lap1, int nthreads, long long* total_kps) {
+  std::vector<std::thread> th;
+  std::vector<long long> counts(nthreads, 0);
+  auto t0 = std::chrono::steady_clock::now();
+  for (int t = 0; t < nthreads; t++)
+    th.emplace_back([&, t]() {
+      Extractor ex(nfeatures, scaleFactor, nlevels, iniTh, minTh, blur_taps, sincos_mode);
+      std::vector<KeyPoint> k;
+      std::vector<uint8_t> d;
+      for (int f = t; f < nframes; f += nthreads) {
+        ex.extract(frames + (size_t)f * w * h, w, h, w, lap0, lap1, k, d);
+        counts[t] += (long long)k.size();
+      }
+    });
+  for (auto& x : th) x.join();
+  auto t1 = std::chrono::steady_clock::now();
+  long long tot = 0;
+  for (auto c : counts) tot += c;
+  if (total_kps) *total_kps = tot;
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+
+// ---- matcher side -----------------------------------------------------------------------------------------------
+static void fill_view(FrameView& F, int N, const KeyPoint* kps, const uint8_t* desc, const float* uRight, const float* scaleFactors,
+                      const float* bounds4) {
+  F.N = N; F.kps = kps; F.desc = desc; F.uRight = uRight; F.scaleFactors = scaleFactors;
+  F.setBounds(bounds4[0], bounds4[1], bounds4[2], bounds4[3]);
+  F.assignFeaturesToGrid();
+}
+int oro_features_in_area(int N, const KeyPoint* kps, const float* bounds4, float x, float y, float r, int minLevel, int maxLevel,
+                         int* out, int cap) {
+  FrameView F;
+  fill_view(F, N, kps, nullptr, nullptr, nullptr, bounds4);
+  std::vector<int> v = F.getFeaturesInArea(x, y, r, minLevel, maxLevel);
+  for (size_t i = 0; i < v.size() && (int)i < cap; i++) out[i] = v[i];
+  return (int)v.size();
+}
+int oro_search_by_projection_mappoints(int N, const KeyPoint* kps, const uint8_t* desc, const float* uRight, const float* scaleFactors,
+                                       const float* bounds4, int nMP, const uint8_t* in_view, const float* projX, const float* projY,
+                                       const int* level, const float* viewCos, const uint8_t* mpDesc, const uint8_t* observed,
+                                       const float* projXR, float th, float nnratio, int* kp_mp) {
+  FrameView F;
+  fill_view(F, N, kps, desc, uRight, scaleFactors, bounds4);
+  return search_by_projection_mappoints(F, nMP, in_view, projX, projY, level, viewCos, mpDesc, observed, projXR, th, nnratio, kp_mp);
+}
+int oro_search_by_projection_window(int N, const KeyPoint* kps, const uint8_t* desc, const float* uRight, const float* scaleFactors,
+                                    const float* bounds4, int n, const uint8_t* valid, const float* u, const float* v, const int* lvl,
+                                    const float* ur, const float* angle, const uint8_t* srcDesc, const uint8_t* observed, float th,
+                                    int mode, int dist_th, int any_mp_blocks, int check_orientation, int* kp_mp) {
+  FrameView F;
+  fill_view(F, N, kps, desc, uRight, scaleFactors, bounds4);
+  return search_by_projection_window(F, n, valid, u, v, lvl, ur, angle, srcDesc, observed, th, mode, dist_th, any_mp_blocks != 0,
+                                     check_orientation != 0, kp_mp);
+}
+int oro_search_for_initialization(int N1, const KeyPoint* kps1, const uint8_t* desc1, int N2, const KeyPoint* kps2, const uint8_t* desc2,
+                                  const float* bounds4, float* prevMatched, int windowSize, float nnratio, int check_orientation,
+                                  int* matches12) {
+  FrameView F1, F2;
+  F1.N = N1; F1.kps = kps1; F1.desc = desc1;
+  fill_view(F2, N2, kps2, desc2, nullptr, nullptr, bounds4);
+  return search_for_initialization(F1, F2, prevMatched, windowSize, nnratio, check_orientation != 0, matches12);
+}
+// Uses the un-blurred pyramids held by the two extractor objects after their last extract() (Frame.cc:908,998,1012).
+void oro_stereo_matches(void* exL, void* exR, int N, const KeyPoint* kpL, const uint8_t* descL, int Nr, const KeyPoint* kpR,
+                        const uint8_t* descR, float mb, float mbf, float* uRight, float* depth, int* bestDist, int* bestIdx) {
+  Extractor* L = (Extractor*)exL; Extractor* R = (Extractor*)exR;
+  compute_stereo_matches(N, kpL, descL, Nr, kpR, descR, L->pyramid, R->pyramid, L->mvScaleFactor.data(), L->mvInvScaleFactor.data(),
+                         StereoParams{mb, mbf}, uRight, depth, bestDist, bestIdx);
+}
+void oro_knn2_ratio(const uint8_t* q, int nq, const uint8_t* t, int nt, int* idx, int* dist, uint8_t* good) {
+  knn2_ratio(q, nq, t, nt, idx, dist, good);
+}
+void oro_three_maxima(const int* hist, int L, int* ind3) {
+  int a = -1, b = -1, c = -1;
+  compute_three_maxima(hist, L, a, b, c);
+  ind3[0] = a; ind3[1] = b; ind3[2] = c;
+}
+
+}  // extern "C"
