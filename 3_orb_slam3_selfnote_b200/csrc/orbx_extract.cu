@@ -1,0 +1,590 @@
+// Host side of the extractor: handle, geometry/tables, workspaces, stream orchestration, and the extern "C" entry points
+// declared in include/orbx.h.  All pixel / keypoint arithmetic happens in the kernels of extract_kernels.cuh; this file
+// only sizes buffers, fills the small lookup tables and enqueues launches.  There is no CPU fallback.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "extract_kernels.cuh"
+#include "orbx_internal.h"
+
+namespace orbx {
+
+static const int8_t kPatternHost[1024] = {
+#include "orb_pattern.inc"
+};
+
+thread_local std::string g_err;
+void set_error(const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+}
+
+#define CK(call)                                                                                         \
+  do {                                                                                                   \
+    cudaError_t e_ = (call);                                                                             \
+    if (e_ != cudaSuccess) {                                                                             \
+      set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));                    \
+      return ORBX_ERR_CUDA;                                                                              \
+    }                                                                                                    \
+  } while (0)
+
+static inline int round_up(int v, int a) { return (v + a - 1) / a * a; }
+static inline int cv_round_f(float v) { return (int)lrintf(v); }
+static inline int cv_floor_d(double v) { int i = (int)v; return i - (i > v); }
+
+struct Slot {
+  cudaStream_t stream = nullptr;
+  uint8_t* in = nullptr;  // staged level-0 frames for the host path [max_batch][h][inPitch]
+  uint8_t* pyr = nullptr;
+  uint8_t* blur = nullptr;
+  PreCand* cand = nullptr;
+  int* zero = nullptr;  // candCount | cellFlags | status  (cleared per batch)
+  size_t zeroBytes = 0;
+  int* candCount = nullptr; int* cellFlags = nullptr; int* status = nullptr;
+  LevelKp* lkp = nullptr; int* lkpCount = nullptr; int* lkpDest = nullptr; int* nCand = nullptr;
+  uint32_t* qXY = nullptr; uint32_t* qOrd = nullptr; uint16_t* qNode = nullptr; uint8_t* qResp = nullptr; uint8_t* qSel = nullptr;
+  orbx_keypoint* kps = nullptr; uint8_t* desc = nullptr; int* counts = nullptr; int* mono = nullptr;
+  int* hStatus = nullptr;  // pinned
+  Batch last{};            // descriptor of the last batch run in this slot
+  int lastFrames = 0;
+};
+
+}  // namespace orbx
+
+using namespace orbx;
+
+struct orbx_extractor {
+  orbx_params p{};
+  double scaleFactorD = 0;
+  std::vector<float> scale, invScale, sigma2, invSigma2;
+  std::vector<int> quota;
+  int umax[16];
+  // geometry-dependent state
+  bool haveGeom = false;
+  Geom g{};
+  int inPitch = 0;  // pitch of the staged input
+  long long pyrFrame = 0, blurFrame = 0;
+  RsX* dRsx = nullptr; RsY* dRsy = nullptr; uint16_t* dInfo = nullptr; int8_t* dPattern = nullptr;
+  size_t qtSmem = 0;
+  Slot slot[2];
+  int lastSlot = 0;
+};
+
+static void free_geom(orbx_extractor* h) {
+  cudaSetDevice(h->p.device);
+  for (Slot& s : h->slot) {
+    if (s.stream) cudaStreamSynchronize(s.stream);
+    void* ptrs[] = {s.in, s.pyr, s.blur, s.cand, s.zero, s.lkp, s.lkpCount, s.lkpDest, s.nCand, s.qXY, s.qOrd, s.qNode, s.qResp, s.qSel,
+                    s.kps, s.desc, s.counts, s.mono};
+    for (void* q : ptrs) if (q) cudaFree(q);
+    if (s.hStatus) cudaFreeHost(s.hStatus);
+    cudaStream_t st = s.stream;
+    s = Slot();
+    s.stream = st;
+  }
+  if (h->dRsx) cudaFree(h->dRsx);
+  if (h->dRsy) cudaFree(h->dRsy);
+  if (h->dInfo) cudaFree(h->dInfo);
+  h->dRsx = nullptr; h->dRsy = nullptr; h->dInfo = nullptr;
+  h->haveGeom = false;
+}
+
+// Build level sizes, cell grids, quadtree roots, tile tables and the lookup tables for one image size.
+static int build_geom(orbx_extractor* h, int width, int height) {
+  if (h->haveGeom && h->g.width == width && h->g.height == height) return ORBX_OK;
+  if (h->haveGeom) free_geom(h);
+  CK(cudaSetDevice(h->p.device));
+  if (width > 8192 || height > 8192) { set_error("image larger than 8192 px is unsupported"); return ORBX_ERR_UNSUPPORTED; }
+  Geom& g = h->g;
+  memset(&g, 0, sizeof g);
+  const int nl = h->p.nlevels;
+  g.nlevels = nl; g.width = width; g.height = height;
+  g.iniTh = h->p.ini_th_fast; g.minTh = h->p.min_th_fast;
+  static const int taps[2][7] = {{18, 34, 49, 55, 49, 34, 18}, {18, 34, 48, 56, 48, 34, 18}};
+  for (int i = 0; i < 7; i++) g.taps[i] = taps[h->p.blur_taps][i];
+  for (int i = 0; i < 16; i++) g.umax[i] = h->umax[i];
+
+  std::vector<RsX> rsx; std::vector<RsY> rsy; std::vector<uint16_t> info;
+  int pyrOff = 0, blurOff = 0, cellBase = 0, candOff = 0, kpOff = 0, tileBase = 0, blurTileBase = 0, maxNodeCap = 0;
+  h->inPitch = round_up(width, 64);
+  for (int l = 0; l < nl; l++) {
+    LevelGeom& L = g.lv[l];
+    // level size, src/ORBextractor.cc:1192-1193
+    L.w = cv_round_f((float)width * h->invScale[l]);
+    L.h = cv_round_f((float)height * h->invScale[l]);
+    if (L.w < 1 || L.h < 1) { set_error("level %d is empty for a %dx%d image", l, width, height); return ORBX_ERR_UNSUPPORTED; }
+    L.pitch = (l == 0) ? h->inPitch : round_up(L.w, 64);
+    L.pyrOff = pyrOff;
+    if (l > 0) pyrOff += L.pitch * L.h;
+    L.blurPitch = round_up(L.w, 64);
+    L.blurOff = blurOff;
+    blurOff += L.blurPitch * L.h;
+    L.scale = h->scale[l];
+    L.kpSize = (float)(int)(kPatch * h->scale[l]);  // src/ORBextractor.cc:862
+    L.quota = h->quota[l];
+    // cell grid, src/ORBextractor.cc:771-785
+    const int minB = kMinBorder, maxBX = L.w - kEdge + 3, maxBY = L.h - kEdge + 3;
+    const float fw = (float)(maxBX - minB), fh = (float)(maxBY - minB);
+    L.nCols = fw > 0 ? (int)(fw / 30.f) : 0;
+    L.nRows = fh > 0 ? (int)(fh / 30.f) : 0;
+    if (L.nCols > 0 && L.nRows > 0) {
+      L.wCell = (int)ceilf(fw / L.nCols);
+      L.hCell = (int)ceilf(fh / L.nRows);
+    } else { L.nCols = L.nRows = 0; L.wCell = L.hCell = 1; }
+    if (L.wCell > 63 || L.hCell > 63) { set_error("cell larger than 63 px"); return ORBX_ERR_UNSUPPORTED; }
+    L.cellBase = cellBase;
+    cellBase += L.nCols * L.nRows;
+    if (L.nCols * L.nRows > 65535) { set_error("too many cells"); return ORBX_ERR_UNSUPPORTED; }
+    // quadtree roots, src/ORBextractor.cc:541-543
+    const int W = maxBX - minB, H = maxBY - minB;
+    if (L.nCols > 0) {
+      L.nIni = (int)roundf((float)W / H);
+      if (L.nIni < 1) { set_error("aspect ratio below 0.5 is unsupported (the reference divides by zero, ORBextractor.cc:541-543)"); return ORBX_ERR_UNSUPPORTED; }
+      if (L.nIni > 16) { set_error("aspect ratio above 16 is unsupported"); return ORBX_ERR_UNSUPPORTED; }
+      L.hX = (float)W / L.nIni;
+    } else { L.nIni = 1; L.hX = 1.f; }
+    L.nodeCap = round_up(std::max(L.quota + 3, 4 * L.nIni) + 4, 8);
+    maxNodeCap = std::max(maxNodeCap, L.nodeCap);
+    L.kpCap = L.nodeCap; L.kpOff = kpOff; kpOff += L.kpCap;
+    L.candCap = round_up(std::max(1024, L.w * L.h / 8), 64);
+    L.candOff = candOff; candOff += L.candCap;
+    // FAST tiles over the region [19, w-19) x [19, h-19)
+    const int rw = L.w - 2 * kEdge, rh = L.h - 2 * kEdge;
+    L.tilesX = (rw > 0 && rh > 0 && L.nCols > 0) ? (rw + kTileW - 1) / kTileW : 0;
+    L.tilesY = (rw > 0 && rh > 0 && L.nCols > 0) ? (rh + kTileH - 1) / kTileH : 0;
+    L.tileBase = tileBase; tileBase += L.tilesX * L.tilesY;
+    L.blurTilesX = (L.w + kBlurW - 1) / kBlurW; L.blurTilesY = (L.h + kBlurH - 1) / kBlurH;
+    L.blurTileBase = blurTileBase; blurTileBase += L.blurTilesX * L.blurTilesY;
+    // column / row cell info: cell index | first<<14 | last<<15
+    L.colInfoOff = (int)info.size();
+    for (int x = 0; x < L.w; x++) {
+      uint16_t v = 0;
+      if (x >= kEdge && x < L.w - kEdge && L.nCols > 0) {
+        const int c = (x - kEdge) / L.wCell, r = (x - kEdge) % L.wCell;
+        v = (uint16_t)c;
+        if (r == 0) v |= 0x4000;
+        if (r == L.wCell - 1 || x == L.w - kEdge - 1) v |= 0x8000;
+      }
+      info.push_back(v);
+    }
+    L.rowInfoOff = (int)info.size();
+    for (int y = 0; y < L.h; y++) {
+      uint16_t v = 0;
+      if (y >= kEdge && y < L.h - kEdge && L.nRows > 0) {
+        const int c = (y - kEdge) / L.hCell, r = (y - kEdge) % L.hCell;
+        v = (uint16_t)c;
+        if (r == 0) v |= 0x4000;
+        if (r == L.hCell - 1 || y == L.h - kEdge - 1) v |= 0x8000;
+      }
+      info.push_back(v);
+    }
+    // resize tables (cv::resize INTER_LINEAR 8U) from level l-1
+    if (l > 0) {
+      const LevelGeom& S = g.lv[l - 1];
+      const double scale_x = 1. / ((double)L.w / S.w), scale_y = 1. / ((double)L.h / S.h);
+      L.rsxOff = (int)rsx.size();
+      const int wpad = round_up(L.w, 4);
+      for (int dx0 = 0; dx0 < wpad; dx0++) {
+        const int dx = std::min(dx0, L.w - 1);
+        float fx = (float)((dx + 0.5) * scale_x - 0.5);
+        int sx = cv_floor_d(fx);
+        fx -= sx;
+        if (sx < 0) { fx = 0; sx = 0; }
+        if (sx >= S.w - 1) { fx = 0; sx = S.w - 1; }
+        RsX e;
+        e.s0 = (int16_t)sx; e.s1 = (int16_t)std::min(sx + 1, S.w - 1);
+        e.a0 = (int16_t)std::min(32767, std::max(-32768, cv_round_f((1.f - fx) * 2048.f)));
+        e.a1 = (int16_t)std::min(32767, std::max(-32768, cv_round_f(fx * 2048.f)));
+        rsx.push_back(e);
+      }
+      L.rsyOff = (int)rsy.size();
+      for (int dy = 0; dy < L.h; dy++) {
+        float fy = (float)((dy + 0.5) * scale_y - 0.5);
+        int sy = cv_floor_d(fy);
+        fy -= sy;
+        RsY e;
+        e.s0 = (int16_t)std::min(std::max(sy, 0), S.h - 1); e.s1 = (int16_t)std::min(std::max(sy + 1, 0), S.h - 1);
+        e.b0 = (int16_t)std::min(32767, std::max(-32768, cv_round_f((1.f - fy) * 2048.f)));
+        e.b1 = (int16_t)std::min(32767, std::max(-32768, cv_round_f(fy * 2048.f)));
+        rsy.push_back(e);
+      }
+    }
+  }
+  g.nCellsTotal = cellBase; g.nTilesTotal = tileBase; g.nBlurTilesTotal = blurTileBase;
+  g.candSlab = candOff; g.kpSlab = kpOff; g.kpStride = kpOff;
+  h->pyrFrame = round_up(std::max(pyrOff, 256), 256);
+  h->blurFrame = round_up(blurOff, 256);
+  h->qtSmem = (size_t)maxNodeCap * 18 * sizeof(int);
+  if (h->qtSmem > 200 * 1024) { set_error("nfeatures too large for the quadtree kernel's shared memory"); return ORBX_ERR_UNSUPPORTED; }
+  CK(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->qtSmem));
+
+  CK(cudaMalloc(&h->dRsx, std::max<size_t>(1, rsx.size()) * sizeof(RsX)));
+  CK(cudaMalloc(&h->dRsy, std::max<size_t>(1, rsy.size()) * sizeof(RsY)));
+  CK(cudaMalloc(&h->dInfo, info.size() * sizeof(uint16_t)));
+  if (!rsx.empty()) CK(cudaMemcpy(h->dRsx, rsx.data(), rsx.size() * sizeof(RsX), cudaMemcpyHostToDevice));
+  if (!rsy.empty()) CK(cudaMemcpy(h->dRsy, rsy.data(), rsy.size() * sizeof(RsY), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(h->dInfo, info.data(), info.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+
+  const size_t B = (size_t)h->p.max_batch;
+  for (Slot& s : h->slot) {
+    CK(cudaMalloc(&s.in, B * h->inPitch * height));
+    CK(cudaMalloc(&s.pyr, B * h->pyrFrame));
+    CK(cudaMalloc(&s.blur, B * h->blurFrame));
+    CK(cudaMalloc(&s.cand, B * g.candSlab * sizeof(PreCand)));
+    s.zeroBytes = (B * ORBX_MAX_LEVELS + B * g.nCellsTotal + 16) * sizeof(int);
+    CK(cudaMalloc(&s.zero, s.zeroBytes));
+    s.candCount = s.zero; s.cellFlags = s.zero + B * ORBX_MAX_LEVELS; s.status = s.cellFlags + B * g.nCellsTotal;
+    CK(cudaMalloc(&s.lkp, B * g.kpSlab * sizeof(LevelKp)));
+    CK(cudaMalloc(&s.lkpCount, B * ORBX_MAX_LEVELS * sizeof(int)));
+    CK(cudaMalloc(&s.nCand, B * ORBX_MAX_LEVELS * sizeof(int)));
+    CK(cudaMalloc(&s.lkpDest, B * g.kpSlab * sizeof(int)));
+    CK(cudaMalloc(&s.qXY, B * g.candSlab * sizeof(uint32_t)));
+    CK(cudaMalloc(&s.qOrd, B * g.candSlab * sizeof(uint32_t)));
+    CK(cudaMalloc(&s.qNode, B * g.candSlab * sizeof(uint16_t)));
+    CK(cudaMalloc(&s.qResp, B * g.candSlab));
+    CK(cudaMalloc(&s.qSel, B * g.candSlab));
+    CK(cudaMalloc(&s.kps, B * g.kpStride * sizeof(orbx_keypoint)));
+    CK(cudaMalloc(&s.desc, B * g.kpStride * 32));
+    CK(cudaMalloc(&s.counts, B * sizeof(int)));
+    CK(cudaMalloc(&s.mono, B * sizeof(int)));
+    CK(cudaMallocHost(&s.hStatus, sizeof(int)));
+    s.lastFrames = 0;
+  }
+  h->haveGeom = true;
+  return ORBX_OK;
+}
+
+// Enqueue one device batch on `st` using the workspaces of slot `si`.
+static int run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int nframes, int pitch, long long frameStride, int lap0, int lap1,
+                     cudaStream_t st) {
+  Slot& s = h->slot[si];
+  const Geom& g = h->g;
+  Geom gg = g;
+  gg.lv[0].pitch = pitch;
+  Batch b{};
+  b.in = dIn; b.inFrameStride = frameStride; b.inPitch = pitch; b.nframes = nframes; b.lap0 = lap0; b.lap1 = lap1;
+  b.pyr = s.pyr; b.pyrFrameStride = h->pyrFrame; b.blur = s.blur; b.blurFrameStride = h->blurFrame;
+  b.cand = s.cand; b.candCount = s.candCount; b.cellFlags = s.cellFlags;
+  b.lkp = s.lkp; b.lkpCount = s.lkpCount; b.lkpDest = s.lkpDest;
+  b.qXY = s.qXY; b.qOrd = s.qOrd; b.qNode = s.qNode; b.qResp = s.qResp; b.qSel = s.qSel;
+  b.kps = s.kps; b.desc = s.desc; b.counts = s.counts; b.mono = s.mono; b.status = s.status;
+  b.rsx = h->dRsx; b.rsy = h->dRsy; b.info = h->dInfo; b.pattern = h->dPattern;
+  s.last = b; s.lastFrames = nframes;
+  h->lastSlot = si;
+
+  CK(cudaMemsetAsync(s.zero, 0, s.zeroBytes, st));
+  for (int l = 1; l < g.nlevels; l++) {
+    const LevelGeom& L = g.lv[l];
+    dim3 grid((L.w + 127) / 128, (L.h + 7) / 8, nframes), block(32, 8);
+    k_pyr_resize<<<grid, block, 0, st>>>(gg, b, l);
+  }
+  if (g.nTilesTotal > 0) k_fast_nms<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
+  k_quadtree<<<dim3(g.nlevels, nframes), 256, h->qtSmem, st>>>(gg, b, s.nCand);
+  k_blur7<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, st>>>(gg, b);
+  k_assemble<<<nframes, 256, 0, st>>>(gg, b);
+  k_orient_desc<<<dim3((g.kpSlab + 7) / 8, nframes), 256, 0, st>>>(gg, b);
+  CK(cudaGetLastError());
+  return ORBX_OK;
+}
+
+extern "C" {
+
+const char* orbx_last_error(void) { return g_err.c_str(); }
+const char* orbx_version(void) { return "orbx 0.1 (sm_100a)"; }
+
+int orbx_create(const orbx_params* p, orbx_extractor** out) {
+  if (!p || !out) return ORBX_ERR_ARG;
+  if (p->nfeatures < 1 || p->nlevels < 1 || p->nlevels > ORBX_MAX_LEVELS || !(p->scale_factor > 1.0f) || p->min_th_fast < 1 ||
+      p->ini_th_fast < p->min_th_fast || p->ini_th_fast > 254 || p->max_batch < 1 || p->max_batch > 65535 ||
+      (p->blur_taps != ORBX_TAPS_OCV346 && p->blur_taps != ORBX_TAPS_OCV4)) {
+    set_error("orbx_create: bad parameters");
+    return ORBX_ERR_ARG;
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= p->device || p->device < 0) {
+    set_error("orbx_create: no usable CUDA device %d (this library has no CPU fallback)", p->device);
+    return ORBX_ERR_CUDA;
+  }
+  CK(cudaSetDevice(p->device));
+  orbx_extractor* h = new orbx_extractor();
+  h->p = *p;
+  const int nl = p->nlevels;
+  // ORBextractor::ORBextractor, src/ORBextractor.cc:408-468
+  h->scaleFactorD = (double)p->scale_factor;  // `double scaleFactor` member initialised from the float argument
+  h->scale.resize(nl); h->invScale.resize(nl); h->sigma2.resize(nl); h->invSigma2.resize(nl); h->quota.resize(nl);
+  h->scale[0] = 1.0f; h->sigma2[0] = 1.0f;
+  for (int i = 1; i < nl; i++) {
+    h->scale[i] = (float)(h->scale[i - 1] * h->scaleFactorD);
+    h->sigma2[i] = h->scale[i] * h->scale[i];
+  }
+  for (int i = 0; i < nl; i++) { h->invScale[i] = 1.0f / h->scale[i]; h->invSigma2[i] = 1.0f / h->sigma2[i]; }
+  float factor = (float)(1.0f / h->scaleFactorD);
+  float nDesired = p->nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)nl));
+  int sum = 0;
+  for (int l = 0; l < nl - 1; l++) {
+    h->quota[l] = cv_round_f(nDesired);
+    sum += h->quota[l];
+    nDesired *= factor;
+  }
+  h->quota[nl - 1] = std::max(p->nfeatures - sum, 0);
+  {  // umax, src/ORBextractor.cc:452-467
+    int v, v0, vmax = cv_floor_d(kHalfPatch * sqrt(2.f) / 2 + 1);
+    int vmin = (int)ceil(kHalfPatch * sqrt(2.f) / 2);
+    const double hp2 = kHalfPatch * kHalfPatch;
+    for (v = 0; v <= vmax; ++v) h->umax[v] = (int)lrint(sqrt(hp2 - v * v));
+    for (v = kHalfPatch, v0 = 0; v >= vmin; --v) {
+      while (h->umax[v0] == h->umax[v0 + 1]) ++v0;
+      h->umax[v] = v0;
+      ++v0;
+    }
+  }
+  for (Slot& s : h->slot)
+    if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; set_error("stream creation failed"); return ORBX_ERR_CUDA; }
+  if (cudaMalloc(&h->dPattern, 1024) != cudaSuccess ||
+      cudaMemcpy(h->dPattern, kPatternHost, 1024, cudaMemcpyHostToDevice) != cudaSuccess) {
+    delete h; set_error("pattern upload failed"); return ORBX_ERR_CUDA;
+  }
+  *out = h;
+  return ORBX_OK;
+}
+
+void orbx_destroy(orbx_extractor* h) {
+  if (!h) return;
+  free_geom(h);
+  for (Slot& s : h->slot) if (s.stream) cudaStreamDestroy(s.stream);
+  if (h->dPattern) cudaFree(h->dPattern);
+  delete h;
+}
+
+int orbx_get_levels(const orbx_extractor* h) { return h ? h->p.nlevels : ORBX_ERR_ARG; }
+float orbx_get_scale_factor(const orbx_extractor* h) { return h ? (float)h->scaleFactorD : 0.f; }
+int orbx_get_scale_tables(const orbx_extractor* h, float* scale, float* inv, float* s2, float* is2) {
+  if (!h) return ORBX_ERR_ARG;
+  for (int i = 0; i < h->p.nlevels; i++) {
+    if (scale) scale[i] = h->scale[i];
+    if (inv) inv[i] = h->invScale[i];
+    if (s2) s2[i] = h->sigma2[i];
+    if (is2) is2[i] = h->invSigma2[i];
+  }
+  return ORBX_OK;
+}
+int orbx_get_features_per_level(const orbx_extractor* h, int* quota) {
+  if (!h || !quota) return ORBX_ERR_ARG;
+  for (int i = 0; i < h->p.nlevels; i++) quota[i] = h->quota[i];
+  return ORBX_OK;
+}
+int orbx_max_keypoints(const orbx_extractor* h, int width, int height) {
+  if (!h || width <= 0 || height <= 0) return ORBX_ERR_ARG;
+  int rc = build_geom(const_cast<orbx_extractor*>(h), width, height);
+  if (rc != ORBX_OK) return rc;
+  return h->g.kpStride;
+}
+int orbx_launches_per_batch(const orbx_extractor* h) {
+  if (!h || !h->haveGeom) return ORBX_ERR_ARG;
+  return (h->g.nlevels - 1) + 5;  // resize per level + fast + quadtree + blur + assemble + orient/desc (memset excluded)
+}
+
+int orbx_extract_batch_device(orbx_extractor* h, const uint8_t* dImages, int nframes, int width, int height, int pitch,
+                              size_t frameStride, int lap0, int lap1, void* stream) {
+  if (!h) return ORBX_ERR_ARG;
+  if (!dImages || width <= 0 || height <= 0 || nframes <= 0) return ORBX_EMPTY_IMAGE;
+  if (nframes > h->p.max_batch) { set_error("nframes %d > max_batch %d", nframes, h->p.max_batch); return ORBX_ERR_ARG; }
+  if (pitch < width || (pitch & 3) || ((uintptr_t)dImages & 3) || (frameStride & 3)) {
+    set_error("device frames must be 4-byte aligned with a pitch that is a multiple of 4");
+    return ORBX_ERR_ARG;
+  }
+  int rc = build_geom(h, width, height);
+  if (rc != ORBX_OK) return rc;
+  cudaStream_t st = stream ? (cudaStream_t)stream : h->slot[0].stream;
+  return run_batch(h, 0, dImages, nframes, pitch, (long long)frameStride, lap0, lap1, st);
+}
+
+int orbx_batch_results_device(orbx_extractor* h, const orbx_keypoint** kps, const uint8_t** desc, const int** counts, const int** mono,
+                              const int** status, int* kpStride) {
+  if (!h || !h->haveGeom) return ORBX_ERR_ARG;
+  Slot& s = h->slot[h->lastSlot];
+  if (kps) *kps = s.kps;
+  if (desc) *desc = s.desc;
+  if (counts) *counts = s.counts;
+  if (mono) *mono = s.mono;
+  if (status) *status = s.status;
+  if (kpStride) *kpStride = h->g.kpStride;
+  return ORBX_OK;
+}
+
+int orbx_extract_batch_host(orbx_extractor* h, const uint8_t* images, int nframes, int width, int height, int stride, size_t frameStride,
+                            int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc, int capPerFrame, int* counts, int* mono) {
+  if (!h) return ORBX_ERR_ARG;
+  if (!images || width <= 0 || height <= 0 || nframes <= 0) return ORBX_EMPTY_IMAGE;
+  if (!kps || !desc || !counts || !mono || capPerFrame <= 0 || stride < width) return ORBX_ERR_ARG;
+  int rc = build_geom(h, width, height);
+  if (rc != ORBX_OK) return rc;
+  const Geom& g = h->g;
+  const int B = h->p.max_batch;
+  const int ncopy = std::min(capPerFrame, g.kpStride);
+  int chunk = 0;
+  for (int f0 = 0; f0 < nframes; f0 += B, chunk++) {
+    const int nb = std::min(B, nframes - f0);
+    const int si = chunk & 1;
+    Slot& s = h->slot[si];
+    cudaStream_t st = s.stream;
+    // (the slot's previous chunk was enqueued on the same stream, so its D2H copies finish before these buffers are reused)
+    const uint8_t* src = images + (size_t)f0 * frameStride;
+    if (frameStride == (size_t)stride * height) {
+      CK(cudaMemcpy2DAsync(s.in, h->inPitch, src, stride, width, (size_t)height * nb, cudaMemcpyHostToDevice, st));
+    } else {
+      for (int f = 0; f < nb; f++)
+        CK(cudaMemcpy2DAsync(s.in + (size_t)f * h->inPitch * height, h->inPitch, src + (size_t)f * frameStride, stride, width, height,
+                             cudaMemcpyHostToDevice, st));
+    }
+    rc = run_batch(h, si, s.in, nb, h->inPitch, (long long)h->inPitch * height, lap0, lap1, st);
+    if (rc != ORBX_OK) return rc;
+    CK(cudaMemcpyAsync(counts + f0, s.counts, nb * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(mono + f0, s.mono, nb * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpy2DAsync(kps + (size_t)f0 * capPerFrame, (size_t)capPerFrame * sizeof(orbx_keypoint), s.kps,
+                         (size_t)g.kpStride * sizeof(orbx_keypoint), (size_t)ncopy * sizeof(orbx_keypoint), nb, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpy2DAsync(desc + (size_t)f0 * capPerFrame * 32, (size_t)capPerFrame * 32, s.desc, (size_t)g.kpStride * 32, (size_t)ncopy * 32, nb,
+                         cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(s.hStatus, s.status, sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (chunk >= 1) {  // keep at most two chunks in flight: wait for the other slot before queueing a third
+      Slot& o = h->slot[si ^ 1];
+      CK(cudaStreamSynchronize(o.stream));
+      if (*o.hStatus != 0) { set_error("device reported status %d (capacity)", *o.hStatus); return *o.hStatus; }
+    }
+  }
+  for (Slot& s : h->slot) {
+    CK(cudaStreamSynchronize(s.stream));
+    if (s.hStatus && s.lastFrames > 0 && *s.hStatus != 0) { set_error("device reported status %d (capacity)", *s.hStatus); return *s.hStatus; }
+  }
+  for (int f = 0; f < nframes; f++)
+    if (counts[f] > capPerFrame) { set_error("frame %d has %d keypoints, capacity %d", f, counts[f], capPerFrame); return ORBX_ERR_CAPACITY; }
+  return ORBX_OK;
+}
+
+int orbx_extract(orbx_extractor* h, const uint8_t* image, int width, int height, int stride, int lap0, int lap1, orbx_keypoint* kps,
+                 uint8_t* desc, int capacity, int* n, int* monoIndex) {
+  if (!h) return ORBX_ERR_ARG;
+  if (!image || width <= 0 || height <= 0) return ORBX_EMPTY_IMAGE;
+  int cnt = 0, mono = 0;
+  int rc = orbx_extract_batch_host(h, image, 1, width, height, stride, (size_t)stride * height, lap0, lap1, kps, desc, capacity, &cnt, &mono);
+  if (n) *n = cnt;
+  if (monoIndex) *monoIndex = mono;
+  return rc;
+}
+
+static int level_view(orbx_extractor* h, int frame, int level, const uint8_t** ptr, int* w, int* hh, int* pitch) {
+  if (!h || !h->haveGeom) return ORBX_ERR_ARG;
+  Slot& s = h->slot[h->lastSlot];
+  if (frame < 0 || frame >= s.lastFrames || level < 0 || level >= h->g.nlevels) return ORBX_ERR_ARG;
+  const LevelGeom& L = h->g.lv[level];
+  if (level == 0) { *ptr = s.last.in + (long long)frame * s.last.inFrameStride; *pitch = s.last.inPitch; }
+  else { *ptr = s.pyr + (long long)frame * h->pyrFrame + L.pyrOff; *pitch = L.pitch; }
+  *w = L.w; *hh = L.h;
+  return ORBX_OK;
+}
+
+int orbx_pyramid_level_device(orbx_extractor* h, int frame, int level, const uint8_t** dPtr, int* w, int* hh, int* pitch) {
+  const uint8_t* p; int ww, hv, pp;
+  int rc = level_view(h, frame, level, &p, &ww, &hv, &pp);
+  if (rc != ORBX_OK) return rc;
+  if (dPtr) *dPtr = p; if (w) *w = ww; if (hh) *hh = hv; if (pitch) *pitch = pp;
+  return ORBX_OK;
+}
+
+int orbx_pyramid_level(orbx_extractor* h, int frame, int level, uint8_t* dst, int dstStride, int* w, int* hh) {
+  const uint8_t* p; int ww, hv, pp;
+  int rc = level_view(h, frame, level, &p, &ww, &hv, &pp);
+  if (rc != ORBX_OK) return rc;
+  if (w) *w = ww; if (hh) *hh = hv;
+  if (dst) {
+    if (dstStride < ww) return ORBX_ERR_ARG;
+    CK(cudaSetDevice(h->p.device));
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy2D(dst, dstStride, p, pp, ww, hv, cudaMemcpyDeviceToHost));
+  }
+  return ORBX_OK;
+}
+
+int orbx_debug_blurred_level(orbx_extractor* h, int frame, int level, uint8_t* dst, int dstStride) {
+  if (!h || !h->haveGeom || !dst) return ORBX_ERR_ARG;
+  Slot& s = h->slot[h->lastSlot];
+  if (frame < 0 || frame >= s.lastFrames || level < 0 || level >= h->g.nlevels) return ORBX_ERR_ARG;
+  const LevelGeom& L = h->g.lv[level];
+  CK(cudaSetDevice(h->p.device));
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpy2D(dst, dstStride, s.blur + (long long)frame * h->blurFrame + L.blurOff, L.blurPitch, L.w, L.h, cudaMemcpyDeviceToHost));
+  return ORBX_OK;
+}
+
+int orbx_debug_candidates(orbx_extractor* h, int frame, int level, int* xyr, int capacity, int* n) {
+  if (!h || !h->haveGeom || !n) return ORBX_ERR_ARG;
+  Slot& s = h->slot[h->lastSlot];
+  if (frame < 0 || frame >= s.lastFrames || level < 0 || level >= h->g.nlevels) return ORBX_ERR_ARG;
+  const LevelGeom& L = h->g.lv[level];
+  CK(cudaSetDevice(h->p.device));
+  CK(cudaDeviceSynchronize());
+  int cnt = 0;
+  CK(cudaMemcpy(&cnt, s.nCand + frame * ORBX_MAX_LEVELS + level, sizeof(int), cudaMemcpyDeviceToHost));
+  *n = cnt;
+  const int m = std::min(cnt, capacity);
+  if (m > 0 && xyr) {
+    std::vector<uint32_t> xy(m);
+    std::vector<uint8_t> r(m);
+    const long long off = (long long)frame * h->g.candSlab + L.candOff;
+    CK(cudaMemcpy(xy.data(), s.qXY + off, m * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(r.data(), s.qResp + off, m, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < m; i++) { xyr[3 * i] = xy[i] & 0xffff; xyr[3 * i + 1] = xy[i] >> 16; xyr[3 * i + 2] = r[i]; }
+  }
+  return ORBX_OK;
+}
+
+int orbx_debug_level_keypoints(orbx_extractor* h, int frame, int level, orbx_keypoint* out, int capacity, int* n) {
+  if (!h || !h->haveGeom || !n) return ORBX_ERR_ARG;
+  Slot& s = h->slot[h->lastSlot];
+  if (frame < 0 || frame >= s.lastFrames || level < 0 || level >= h->g.nlevels) return ORBX_ERR_ARG;
+  const LevelGeom& L = h->g.lv[level];
+  CK(cudaSetDevice(h->p.device));
+  CK(cudaDeviceSynchronize());
+  int cnt = 0;
+  CK(cudaMemcpy(&cnt, s.lkpCount + frame * ORBX_MAX_LEVELS + level, sizeof(int), cudaMemcpyDeviceToHost));
+  *n = cnt;
+  const int m = std::min(cnt, capacity);
+  if (m > 0 && out) {
+    std::vector<LevelKp> lk(m);
+    std::vector<int> dest(m);
+    const long long off = (long long)frame * h->g.kpSlab + L.kpOff;
+    CK(cudaMemcpy(lk.data(), s.lkp + off, m * sizeof(LevelKp), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(dest.data(), s.lkpDest + off, m * sizeof(int), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < m; i++) {
+      orbx_keypoint k;
+      CK(cudaMemcpy(&k, s.kps + (long long)frame * h->g.kpStride + dest[i], sizeof k, cudaMemcpyDeviceToHost));
+      k.x = lk[i].x; k.y = lk[i].y;
+      out[i] = k;
+    }
+  }
+  return ORBX_OK;
+}
+
+int orbx_hamming(const uint8_t* a, const uint8_t* b) {
+  int d = 0;
+  for (int i = 0; i < 4; i++) {
+    uint64_t x, y;
+    memcpy(&x, a + 8 * i, 8);
+    memcpy(&y, b + 8 * i, 8);
+    d += __builtin_popcountll(x ^ y);
+  }
+  return d;
+}
+
+}  // extern "C"

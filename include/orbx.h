@@ -1,0 +1,128 @@
+/* orbx -- C-ABI of the B200-native ORB feature frontend (extract + Hamming searches).
+ *
+ * This is the drop-in boundary under ORB-SLAM3's feature frontend: plain C, plain pointers and sizes, no C++/torch/cv types.
+ * Each entry point names the reference interface it replaces (file:line relative to wangyunpeng139/3_ORB_SLAM3_SelfNote).
+ * The C++ adapters with the reference's own signatures (ORB_SLAM3::ORBextractor / ORBmatcher) live in
+ * 3_orb_slam3_selfnote_b200/host/ and call only the functions declared here; see INTEGRATION.md.
+ *
+ * Conventions
+ *   - every function returns an int status: ORBX_OK (0) or a negative error code; ORBX_EMPTY_IMAGE (-1) mirrors the
+ *     reference's `return -1` on an empty input (src/ORBextractor.cc:1075-1076).  No exceptions cross the boundary.
+ *   - outputs are caller-allocated; "d_" parameters are device pointers on the handle's device, all others host pointers.
+ *   - a handle is not re-entrant (same rule as one ORBextractor object, src/Frame.cc:120-123); different handles may be
+ *     used concurrently from different threads.  Each handle owns its stream(s) and workspaces.
+ *   - there is NO CPU fallback: without a usable CUDA device every compute call fails with ORBX_ERR_CUDA.
+ */
+#ifndef ORBX_H_
+#define ORBX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORBX_OK 0
+#define ORBX_EMPTY_IMAGE (-1)  /* src/ORBextractor.cc:1075 */
+#define ORBX_ERR_ARG (-2)
+#define ORBX_ERR_CUDA (-3)
+#define ORBX_ERR_CAPACITY (-4) /* an output or internal list would overflow; nothing is silently truncated */
+#define ORBX_ERR_UNSUPPORTED (-5)
+
+#define ORBX_TAPS_OCV346 0 /* 7-tap sigma-2 Gaussian of OpenCV 3.4.1-3.4.8: 18 34 49 55 49 34 18 (/256) -- the reference's pin */
+#define ORBX_TAPS_OCV4 1   /* OpenCV >= 3.4.9 / 4.2 bit-exact kernel:        18 34 48 56 48 34 18 (/256) */
+
+#define ORBX_MAX_LEVELS 16
+
+/* Layout-compatible with cv::KeyPoint (pt.x, pt.y, size, angle, response, octave, class_id): 28 bytes. */
+typedef struct orbx_keypoint {
+  float x, y, size, angle, response;
+  int32_t octave, class_id;
+} orbx_keypoint;
+
+/* Constructor arguments of ORB_SLAM3::ORBextractor (include/ORBextractor.h:49-50) plus sizing of the device workspaces. */
+typedef struct orbx_params {
+  int nfeatures;
+  float scale_factor;
+  int nlevels;
+  int ini_th_fast;
+  int min_th_fast;
+  int blur_taps;  /* ORBX_TAPS_* */
+  int max_batch;  /* frames processed per device batch (>= 1); host batches of any size are chunked */
+  int device;     /* CUDA device ordinal */
+} orbx_params;
+
+typedef struct orbx_extractor orbx_extractor;
+
+/* ---- extractor ------------------------------------------------------------------------------------------------- */
+
+/* ORBextractor::ORBextractor, src/ORBextractor.cc:408-468 (scale tables, per-level quotas, pattern, umax). */
+int orbx_create(const orbx_params* params, orbx_extractor** out);
+void orbx_destroy(orbx_extractor* h);
+
+/* GetLevels / GetScaleFactor / GetScaleFactors / GetInverseScaleFactors / GetScaleSigmaSquares /
+ * GetInverseScaleSigmaSquares, include/ORBextractor.h:61-82.  Arrays hold nlevels floats; any pointer may be NULL. */
+int orbx_get_levels(const orbx_extractor* h);
+float orbx_get_scale_factor(const orbx_extractor* h);
+int orbx_get_scale_tables(const orbx_extractor* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2);
+/* mnFeaturesPerLevel (protected in the reference; exposed for tests). */
+int orbx_get_features_per_level(const orbx_extractor* h, int* quota);
+/* Upper bound of keypoints one frame can return (sum over levels of max(quota+3, 4*nIni)); size outputs with it. */
+int orbx_max_keypoints(const orbx_extractor* h, int width, int height);
+
+/* ORBextractor::operator()(image, mask, keypoints, descriptors, vLappingArea), src/ORBextractor.cc:1071-1184.
+ * image: 8-bit single channel, `stride` bytes per row.  lap0/lap1 = vLappingArea[0..1].  The mask is ignored by the
+ * reference (include/ORBextractor.h:56) and has no parameter here.  Writes *n keypoints (28 B each) and *n x 32 descriptor
+ * bytes, *mono_index = the reference's return value.  Returns ORBX_EMPTY_IMAGE when image == NULL or width/height <= 0. */
+int orbx_extract(orbx_extractor* h, const uint8_t* image, int width, int height, int stride, int lap0, int lap1,
+                 orbx_keypoint* keypoints, uint8_t* descriptors, int capacity, int* n, int* mono_index);
+
+/* Throughput form of the same call: `nframes` independent frames of one size, host buffers in and out (H2D and D2H copies
+ * included; chunked by max_batch and double-buffered over two streams).  Frame f starts at image + f*frame_stride.
+ * Per frame f: counts[f] keypoints at keypoints + f*capacity_per_frame (and descriptors + f*capacity_per_frame*32),
+ * mono_index[f] = the reference's return value. */
+int orbx_extract_batch_host(orbx_extractor* h, const uint8_t* images, int nframes, int width, int height, int stride,
+                            size_t frame_stride, int lap0, int lap1, orbx_keypoint* keypoints, uint8_t* descriptors,
+                            int capacity_per_frame, int* counts, int* mono_index);
+
+/* Device-resident form: frames already in HBM (d_images, row pitch `pitch`, frame f at d_images + f*frame_stride), results
+ * stay in handle-owned device buffers (see orbx_batch_results_device).  nframes <= max_batch.  Work is enqueued on
+ * `stream` (a cudaStream_t; NULL = the handle's own stream) and NOT synchronised: the caller owns ordering. */
+int orbx_extract_batch_device(orbx_extractor* h, const uint8_t* d_images, int nframes, int width, int height, int pitch,
+                              size_t frame_stride, int lap0, int lap1, void* stream);
+/* Device views of the last batch: keypoints [nframes][kp_stride] (28 B), descriptors [nframes][kp_stride][32],
+ * counts [nframes], mono_index [nframes], status word (0 = ok, else ORBX_ERR_CAPACITY raised by a kernel). */
+int orbx_batch_results_device(orbx_extractor* h, const orbx_keypoint** d_keypoints, const uint8_t** d_descriptors,
+                              const int** d_counts, const int** d_mono_index, const int** d_status, int* kp_stride);
+/* Number of kernel launches one orbx_extract_batch_device call enqueues for the current geometry (for bench accounting). */
+int orbx_launches_per_batch(const orbx_extractor* h);
+
+/* The public member mvImagePyramid (include/ORBextractor.h:84), read by Frame::ComputeStereoMatches (src/Frame.cc:908,998):
+ * level `level` of frame `frame` of the last batch.  The host form copies the un-blurred level into dst (dst_stride bytes
+ * per row; dst may be NULL to query the size only); the device form returns a pointer into the handle's pyramid slab.
+ * The reference's 19-px replicated frame around each level is not materialised (nothing on the path reads it). */
+int orbx_pyramid_level(orbx_extractor* h, int frame, int level, uint8_t* dst, int dst_stride, int* width, int* height);
+int orbx_pyramid_level_device(orbx_extractor* h, int frame, int level, const uint8_t** d_ptr, int* width, int* height,
+                              int* pitch);
+
+/* Stage taps for parity tests (host copies of intermediate results of frame `frame` of the last batch).
+ * candidates: the list ComputeKeyPointsOctTree hands to DistributeOctTree for `level` (src/ORBextractor.cc:845-859) as
+ * (x, y, response) int triples relative to (minBorderX, minBorderY), in arbitrary order.  level_keypoints: the per-level
+ * result after DistributeOctTree + orientation, in the reference's order, level coordinates. */
+int orbx_debug_candidates(orbx_extractor* h, int frame, int level, int* xyr, int capacity, int* n);
+int orbx_debug_level_keypoints(orbx_extractor* h, int frame, int level, orbx_keypoint* kps, int capacity, int* n);
+int orbx_debug_blurred_level(orbx_extractor* h, int frame, int level, uint8_t* dst, int dst_stride);
+
+/* ---- matcher --------------------------------------------------------------------------------------------------- */
+
+/* ORBmatcher::DescriptorDistance, src/ORBmatcher.cc:2463-2483 (host, 2 x 32 bytes). */
+int orbx_hamming(const uint8_t* a, const uint8_t* b);
+
+const char* orbx_last_error(void);
+const char* orbx_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBX_H_ */
