@@ -163,6 +163,27 @@ class ORBextractor:
         _check(lib().orbx_batch_results_device(self._h, C.byref(k), C.byref(d), C.byref(c), C.byref(m), C.byref(s), C.byref(stride)))
         return dict(keypoints=k.value, descriptors=d.value, counts=c.value, mono=m.value, status=s.value, kp_stride=stride.value)
 
+    def results_host(self, n):
+        """host copy of the last device batch -> (counts[n], mono[n], keypoints[n,cap], descriptors[n,cap,32])"""
+        h, w = self._last_shape
+        cap = self.max_keypoints(w, h)
+        kps = np.empty((n, cap), KP_DTYPE)
+        desc = np.empty((n, cap, 32), np.uint8)
+        counts = np.empty(n, np.int32)
+        mono = np.empty(n, np.int32)
+        _check(lib().orbx_batch_results_host(self._h, _p(kps), _p(desc), cap, _p(counts), _p(mono)))
+        return counts, mono, kps, desc
+
+    def set_profiling(self, enable=True):
+        _check(lib().orbx_set_profiling(self._h, int(enable)))
+
+    def stage_times(self):
+        """-> list of (stage name, ms) of the last profiled batch"""
+        ms = (C.c_float * 8)()
+        names = (C.c_char_p * 8)()
+        n = _check(lib().orbx_stage_times(self._h, ms, names))
+        return [(names[i].decode(), float(ms[i])) for i in range(n)]
+
     def launches_per_batch(self):
         return _check(lib().orbx_launches_per_batch(self._h))
 

@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(256) k_fast_nms(const __grid_constant__ Geom g
       const uint32_t hi = __vminu2(__vmaxu2(r0, r8), __vmaxu2(r4, r12));
       const uint32_t lo = __vmaxu2(__vminu2(r0, r8), __vminu2(r4, r12));
       const uint32_t q = __vmaxu2((hi + kBias) - v, vb - lo);             // biased by 256 per lane
-      const uint32_t pass = __vmaxu2(q, thr2 + kBias + 0x00010001u) ^ (thr2 + kBias + 0x00010001u);  // != 0 iff some lane has Q > minTh
+      const uint32_t pass = __vmaxu2(q, thr2 + kBias) ^ (thr2 + kBias);  // != 0 iff some lane has Q > minTh
       const bool need = (pass != 0) && (in0 || in1);
       if (__any_sync(ORBX_FULL, need)) {
         const uint32_t r1 = ring_ld<1, 3>(sA, sB, sr, p), r2 = ring_ld<2, 2>(sA, sB, sr, p), r3 = ring_ld<3, 1>(sA, sB, sr, p);

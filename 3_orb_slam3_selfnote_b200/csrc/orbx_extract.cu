@@ -58,6 +58,8 @@ struct Slot {
   int* hStatus = nullptr;  // pinned
   Batch last{};            // descriptor of the last batch run in this slot
   int lastFrames = 0;
+  cudaEvent_t ev[8] = {};  // stage boundaries (profiling mode only)
+  bool evValid = false;
 };
 
 }  // namespace orbx
@@ -79,6 +81,7 @@ struct orbx_extractor {
   size_t qtSmem = 0;
   Slot slot[2];
   int lastSlot = 0;
+  bool profile = false;
 };
 
 static void free_geom(orbx_extractor* h) {
@@ -283,17 +286,31 @@ static int run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int nframes,
   s.last = b; s.lastFrames = nframes;
   h->lastSlot = si;
 
+  const bool prof = h->profile;
+  if (prof && !s.ev[0])
+    for (auto& e : s.ev) CK(cudaEventCreate(&e));
+  s.evValid = false;
+  auto mark = [&](int i) { if (prof) cudaEventRecord(s.ev[i], st); };
+  mark(0);
   CK(cudaMemsetAsync(s.zero, 0, s.zeroBytes, st));
+  mark(1);
   for (int l = 1; l < g.nlevels; l++) {
     const LevelGeom& L = g.lv[l];
     dim3 grid((L.w + 127) / 128, (L.h + 7) / 8, nframes), block(32, 8);
     k_pyr_resize<<<grid, block, 0, st>>>(gg, b, l);
   }
+  mark(2);
   if (g.nTilesTotal > 0) k_fast_nms<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
+  mark(3);
   k_quadtree<<<dim3(g.nlevels, nframes), 256, h->qtSmem, st>>>(gg, b, s.nCand);
+  mark(4);
   k_blur7<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, st>>>(gg, b);
+  mark(5);
   k_assemble<<<nframes, 256, 0, st>>>(gg, b);
+  mark(6);
   k_orient_desc<<<dim3((g.kpSlab + 7) / 8, nframes), 256, 0, st>>>(gg, b);
+  mark(7);
+  s.evValid = prof;
   CK(cudaGetLastError());
   return ORBX_OK;
 }
@@ -390,6 +407,23 @@ int orbx_max_keypoints(const orbx_extractor* h, int width, int height) {
   if (rc != ORBX_OK) return rc;
   return h->g.kpStride;
 }
+int orbx_set_profiling(orbx_extractor* h, int enable) {
+  if (!h) return ORBX_ERR_ARG;
+  h->profile = enable != 0;
+  return ORBX_OK;
+}
+int orbx_stage_times(orbx_extractor* h, float* ms, const char** names) {
+  static const char* kNames[7] = {"memset", "k_pyr_resize(x levels-1)", "k_fast_nms", "k_quadtree", "k_blur7", "k_assemble", "k_orient_desc"};
+  if (!h || !h->haveGeom) return ORBX_ERR_ARG;
+  Slot& s = h->slot[h->lastSlot];
+  if (!s.evValid) { set_error("no profiled batch (call orbx_set_profiling(h,1) and run a batch)"); return ORBX_ERR_ARG; }
+  CK(cudaEventSynchronize(s.ev[7]));
+  for (int i = 0; i < 7; i++) {
+    if (ms) CK(cudaEventElapsedTime(&ms[i], s.ev[i], s.ev[i + 1]));
+    if (names) names[i] = kNames[i];
+  }
+  return 7;
+}
 int orbx_launches_per_batch(const orbx_extractor* h) {
   if (!h || !h->haveGeom) return ORBX_ERR_ARG;
   return (h->g.nlevels - 1) + 5;  // resize per level + fast + quadtree + blur + assemble + orient/desc (memset excluded)
@@ -421,6 +455,26 @@ int orbx_batch_results_device(orbx_extractor* h, const orbx_keypoint** kps, cons
   if (status) *status = s.status;
   if (kpStride) *kpStride = h->g.kpStride;
   return ORBX_OK;
+}
+
+int orbx_batch_results_host(orbx_extractor* h, orbx_keypoint* kps, uint8_t* desc, int capPerFrame, int* counts, int* mono) {
+  if (!h || !h->haveGeom) return ORBX_ERR_ARG;
+  Slot& s = h->slot[h->lastSlot];
+  const int nb = s.lastFrames;
+  if (nb <= 0) return ORBX_ERR_ARG;
+  const Geom& g = h->g;
+  CK(cudaSetDevice(h->p.device));
+  CK(cudaDeviceSynchronize());
+  const int ncopy = std::min(capPerFrame, g.kpStride);
+  if (counts) CK(cudaMemcpy(counts, s.counts, nb * sizeof(int), cudaMemcpyDeviceToHost));
+  if (mono) CK(cudaMemcpy(mono, s.mono, nb * sizeof(int), cudaMemcpyDeviceToHost));
+  if (kps) CK(cudaMemcpy2D(kps, (size_t)capPerFrame * sizeof(orbx_keypoint), s.kps, (size_t)g.kpStride * sizeof(orbx_keypoint),
+                           (size_t)ncopy * sizeof(orbx_keypoint), nb, cudaMemcpyDeviceToHost));
+  if (desc) CK(cudaMemcpy2D(desc, (size_t)capPerFrame * 32, s.desc, (size_t)g.kpStride * 32, (size_t)ncopy * 32, nb, cudaMemcpyDeviceToHost));
+  int st = 0;
+  CK(cudaMemcpy(&st, s.status, sizeof(int), cudaMemcpyDeviceToHost));
+  if (st != 0) set_error("device reported status %d (capacity)", st);
+  return st;
 }
 
 int orbx_extract_batch_host(orbx_extractor* h, const uint8_t* images, int nframes, int width, int height, int stride, size_t frameStride,

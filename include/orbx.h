@@ -95,6 +95,15 @@ int orbx_extract_batch_device(orbx_extractor* h, const uint8_t* d_images, int nf
  * counts [nframes], mono_index [nframes], status word (0 = ok, else ORBX_ERR_CAPACITY raised by a kernel). */
 int orbx_batch_results_device(orbx_extractor* h, const orbx_keypoint** d_keypoints, const uint8_t** d_descriptors,
                               const int** d_counts, const int** d_mono_index, const int** d_status, int* kp_stride);
+/* Host copy of the last device batch (synchronises the device first): same layout as orbx_extract_batch_host's outputs.
+ * Returns the status word raised by the kernels (ORBX_OK or ORBX_ERR_CAPACITY). */
+int orbx_batch_results_host(orbx_extractor* h, orbx_keypoint* keypoints, uint8_t* descriptors, int capacity_per_frame,
+                            int* counts, int* mono_index);
+/* Profiling mode: when enabled, every batch records CUDA events between its stages on the launching stream;
+ * orbx_stage_times then returns the per-stage device time (ms) of the last batch and the stage names (7 entries:
+ * memset, pyramid, FAST/NMS, quadtree, blur, assemble, orientation+descriptor).  Returns the number of stages. */
+int orbx_set_profiling(orbx_extractor* h, int enable);
+int orbx_stage_times(orbx_extractor* h, float* ms, const char** names);
 /* Number of kernel launches one orbx_extract_batch_device call enqueues for the current geometry (for bench accounting). */
 int orbx_launches_per_batch(const orbx_extractor* h);
 

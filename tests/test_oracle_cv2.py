@@ -1,0 +1,135 @@
+"""Pins the CPU oracle's OpenCV primitives against the only executable OpenCV in the image (python cv2 4.x).
+
+The reference calls OpenCV 3.4 (CMakeLists.txt:43-48) for resize / FAST / GaussianBlur / fastAtan2 / BFMatcher; those
+sources are not under /root/reference, so the oracle restates them and this file checks the restatement
+bit-for-bit against cv2.  (GaussianBlur is checked with the OCV4 taps; the OCV346 taps differ by construction, F7.)
+"""
+import numpy as np
+import pytest
+
+cv2 = pytest.importorskip("cv2")
+
+
+def _rand_img(rng, h, w, smooth=True):
+    img = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    if smooth:
+        img = cv2.blur(img, (5, 5))
+        img = (img.astype(np.int32) + rng.integers(-12, 13, (h, w))).clip(0, 255).astype(np.uint8)
+    return img
+
+
+@pytest.mark.parametrize("shape", [(480, 752), (512, 512), (720, 1280), (480, 640), (376, 1241), (97, 133)])
+def test_resize_chain_matches_cv2(oracle, shape):
+    rng = np.random.default_rng(1)
+    img = _rand_img(rng, *shape)
+    ex = oracle.Extractor(500)
+    cur = img
+    for l in range(1, 8):
+        w = int(np.rint(np.float32(shape[1]) * ex.inv_scale[l]))
+        h = int(np.rint(np.float32(shape[0]) * ex.inv_scale[l]))
+        nxt = oracle.resize(cur, w, h)
+        ref = cv2.resize(cur, (w, h), interpolation=cv2.INTER_LINEAR)
+        assert np.array_equal(nxt, ref), "level %d" % l
+        cur = nxt
+
+
+def test_resize_on_strided_view(oracle):
+    rng = np.random.default_rng(2)
+    big = _rand_img(rng, 300, 400)
+    view = big[10:210, 20:320]
+    assert np.array_equal(oracle.resize(view, 250, 167), cv2.resize(view, (250, 167), interpolation=cv2.INTER_LINEAR))
+
+
+@pytest.mark.parametrize("shape", [(480, 752), (134, 210), (33, 47), (9, 300)])
+def test_blur_ocv4_taps_match_cv2(oracle, shape):
+    rng = np.random.default_rng(3)
+    for smooth in (True, False):
+        img = _rand_img(rng, *shape, smooth=smooth)
+        ref = cv2.GaussianBlur(img, (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101)
+        assert np.array_equal(oracle.blur7(img, oracle.TAPS_OCV4), ref)
+    white = np.full(shape, 255, np.uint8)
+    assert np.array_equal(oracle.blur7(white, oracle.TAPS_OCV4), cv2.GaussianBlur(white, (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101))
+
+
+def test_blur_ocv346_taps_gain(oracle):
+    # per-tap cvRound(256*g) sums to 257: a constant image c maps to ((c*257)*257 + 32768) >> 16 (saturated)
+    for c in (0, 1, 100, 200, 254, 255):
+        out = oracle.blur7(np.full((20, 30), c, np.uint8), oracle.TAPS_OCV346)
+        assert (out == min(255, (c * 257 * 257 + 32768) >> 16)).all()
+
+
+def _cv_fast(img, t, nonmax=True):
+    f = cv2.FastFeatureDetector_create(t, nonmax, cv2.FAST_FEATURE_DETECTOR_TYPE_9_16)
+    return [(int(k.pt[0]), int(k.pt[1]), int(k.response)) for k in f.detect(img)]
+
+
+def test_fast_matches_cv2_on_cells_and_full_frames(oracle, synth):
+    rng = np.random.default_rng(4)
+    img = synth.frame(752, 480, 11, 0)
+    for t in (20, 7):
+        assert _cv_fast(img, t) == [tuple(r) for r in oracle.fast(img, t).tolist()]
+    # without NMS cv2 leaves response at 0 (not on the reference's path, which always passes nonmax=true): positions only
+    assert [k[:2] for k in _cv_fast(img, 20, False)] == [tuple(r[:2]) for r in oracle.fast(img, 20, False).tolist()]
+    n = 0
+    for _ in range(150):
+        h, w = int(rng.integers(7, 45)), int(rng.integers(7, 45))
+        y, x = int(rng.integers(0, 480 - h)), int(rng.integers(0, 752 - w))
+        cell = img[y:y + h, x:x + w]  # non-contiguous ROI view, as the reference passes to cv::FAST
+        for t in (20, 7):
+            ref = _cv_fast(np.ascontiguousarray(cell), t)
+            assert ref == [tuple(r) for r in oracle.fast(cell, t).tolist()]
+            n += len(ref)
+    assert n > 500
+    noise = rng.integers(0, 256, (64, 64), dtype=np.uint8)
+    assert _cv_fast(noise, 7) == [tuple(r) for r in oracle.fast(noise, 7).tolist()]
+    assert oracle.fast(np.zeros((6, 40), np.uint8), 7).shape[0] == 0
+
+
+def test_fast_atan2_bit_equal(oracle):
+    rng = np.random.default_rng(5)
+    ys = rng.integers(-60000, 60000, 5000)
+    xs = rng.integers(-60000, 60000, 5000)
+    for y, x in list(zip(ys, xs)) + [(0, 0), (0, 5), (5, 0), (0, -5), (-5, 0), (7, 7), (-7, 7), (7, -7), (-7, -7)]:
+        a = np.float32(cv2.fastAtan2(float(y), float(x)))
+        b = np.float32(oracle.fast_atan2(float(y), float(x)))
+        assert a.tobytes() == b.tobytes(), (y, x, a, b)
+
+
+def test_knn2_matches_bfmatcher_including_ties(oracle):
+    rng = np.random.default_rng(6)
+    q = rng.integers(0, 256, (200, 32), dtype=np.uint8)
+    t = rng.integers(0, 256, (300, 32), dtype=np.uint8)
+    t[50] = t[10]; t[120] = t[10]; q[3] = t[10]   # exact ties: lower train index must come first
+    t[:, 8:] = t[0, 8:]; q[:, 8:] = t[0, 8:]       # few distinct distances => many ties
+    m = cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(q, t, k=2)
+    idx, dist = oracle.knn2(q, t)
+    for i, pair in enumerate(m):
+        assert [p.trainIdx for p in pair] == idx[i].tolist()
+        assert [int(p.distance) for p in pair] == dist[i].tolist()
+    idx1, dist1 = oracle.knn2(q[:4], t[:1])
+    assert idx1[:, 1].tolist() == [-1] * 4 and dist1[:, 1].tolist() == [-1] * 4
+
+
+def test_extractor_tables(oracle):
+    # SURVEY.md §8-a1 (probed against the reference's constructor arithmetic)
+    expect = {1000: [217, 181, 151, 126, 105, 87, 73, 60], 1200: [261, 217, 181, 151, 126, 105, 87, 72],
+              1500: [326, 271, 226, 189, 157, 131, 109, 91], 2000: [434, 362, 302, 251, 209, 175, 145, 122],
+              5000: [1086, 905, 754, 628, 524, 436, 364, 303]}
+    for n, q in expect.items():
+        ex = oracle.Extractor(n)
+        assert ex.quota.tolist() == q
+        assert ex.umax.tolist() == [15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3]
+    ex = oracle.Extractor(1000)
+    ex(np.zeros((480, 752), np.uint8))
+    assert [ex.level(l).shape for l in range(8)] == [(480, 752), (400, 627), (333, 522), (278, 435), (231, 363), (193, 302),
+                                                      (161, 252), (134, 210)]
+
+
+def test_hamming_matches_numpy(oracle):
+    rng = np.random.default_rng(7)
+    a = rng.integers(0, 256, (64, 32), dtype=np.uint8)
+    b = rng.integers(0, 256, (64, 32), dtype=np.uint8)
+    for i in range(64):
+        assert oracle.hamming(a[i], b[i]) == int(np.unpackbits(a[i] ^ b[i]).sum())
+    assert oracle.hamming(a[0], a[0]) == 0
+    assert oracle.hamming(np.zeros(32, np.uint8), np.full(32, 255, np.uint8)) == 256

@@ -38,6 +38,8 @@ def diag(w, h, nfeat, seed, fid, taps, lap):
         ang = float(np.abs(ko["angle"] - kg["angle"]).max()) if same_kp and len(ko) else -1
         print("  L%d %s pyr_bad %d blur_bad %d cand o/g %d/%d only_o %d only_g %d  kps o/g %d/%d same %s max|dangle| %g"
               % (l, po.shape, bad, badb, len(so), len(sg), len(so - sg), len(sg - so), len(ko), len(kg), same_kp, ang))
+        if so != sg:
+            print("     only_o", sorted(so - sg)[:8], "only_g", sorted(sg - so)[:8])
         if not same_kp and len(so - sg) == 0 and len(sg - so) == 0:
             n = min(len(ko), len(kg))
             diff = [i for i in range(n) if (ko["x"][i], ko["y"][i]) != (kg["x"][i], kg["y"][i])]
