@@ -226,3 +226,6 @@ def DescriptorDistance(a, b):
     a = np.ascontiguousarray(a, np.uint8)
     b = np.ascontiguousarray(b, np.uint8)
     return lib().orbx_hamming(_p(a), _p(b))
+
+
+from .matcher import FrameView, ORBmatcher  # noqa: E402,F401  (mirror of include/ORBmatcher.h)

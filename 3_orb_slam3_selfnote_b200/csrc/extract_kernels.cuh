@@ -14,20 +14,10 @@
 #include <cuda_runtime.h>
 #include <float.h>
 
+#include "dev_common.cuh"
 #include "geom.h"
 
 namespace orbx {
-
-#define ORBX_FULL 0xffffffffu
-
-__device__ __forceinline__ const uint8_t* level_ptr(const Geom& g, const Batch& b, int level, int frame, int& pitch) {
-  if (level == 0) {
-    pitch = b.inPitch;
-    return b.in + (long long)frame * b.inFrameStride;
-  }
-  pitch = g.lv[level].pitch;
-  return b.pyr + (long long)frame * b.pyrFrameStride + g.lv[level].pyrOff;
-}
 
 // ---------------------------------------------------------------------------------------------------------------
 // Pyramid: level L from level L-1, OpenCV's fixed-point bilinear (Q11 weights).

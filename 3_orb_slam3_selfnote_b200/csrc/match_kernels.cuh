@@ -1,0 +1,674 @@
+// sm_100a kernels of the Hamming searches (ORBmatcher / Frame side of the frontend).
+//   k_hamming_pairs      ORBmatcher::DescriptorDistance                      src/ORBmatcher.cc:2463-2483
+//   k_build_grid         Frame::AssignFeaturesToGrid / PosInGrid             src/Frame.cc:434-465, 815-825
+//   k_window_candidates  Frame::GetFeaturesInArea + the distance loop        src/Frame.cc:744-813, src/ORBmatcher.cc:85-121
+//   k_resolve_*          the sequential claim / ratio / rotation logic       src/ORBmatcher.cc:44-214, 722-837, 2027-2413
+//   k_stereo_*           Frame::ComputeStereoMatches                         src/Frame.cc:901-1079
+//   k_knn2               cv::BFMatcher(NORM_HAMMING).knnMatch(k=2)           src/Frame.cc:1246
+// Distances are 8 x (xor + popc) on 32-bit words, candidates of one query are spread over the lanes of a warp and reduced
+// with shuffles on packed (distance, traversal order, index) keys so that "first minimum wins" ties resolve exactly as the
+// reference's sequential loops do.  The searches whose result depends on earlier queries (keypoints
+// claimed by earlier map points) are split in two: a fully parallel candidate/distance pass, then one warp per frame
+// that replays the reference's order over the precomputed lists.
+#pragma once
+#include <cuda_runtime.h>
+#include <limits.h>
+
+#include "dev_common.cuh"
+#include "geom.h"
+
+namespace orbx {
+
+constexpr int kGridCols = 64, kGridRows = 48, kGridCells = kGridCols * kGridRows;  // include/Frame.h:38-39
+constexpr unsigned long long kKeyNone = 0xffffffffffffffffull;
+
+__device__ __forceinline__ int hamming8(const uint32_t* a, const uint32_t* b) {
+  int d = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) d += __popc(a[i] ^ b[i]);
+  return d;
+}
+__device__ __forceinline__ void load_desc(const uint8_t* p, uint32_t* out) {
+  const uint4 lo = __ldg(reinterpret_cast<const uint4*>(p)), hi = __ldg(reinterpret_cast<const uint4*>(p) + 1);
+  out[0] = lo.x; out[1] = lo.y; out[2] = lo.z; out[3] = lo.w; out[4] = hi.x; out[5] = hi.y; out[6] = hi.z; out[7] = hi.w;
+}
+
+__global__ void k_hamming_pairs(const uint8_t* a, const uint8_t* b, int n, int* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t x[8], y[8];
+  load_desc(a + 32ll * i, x);
+  load_desc(b + 32ll * i, y);
+  out[i] = hamming8(x, y);
+}
+
+// ---- frame grid ---------------------------------------------------------------------------------------------------
+struct GridFrame {
+  const orbx_keypoint* kps;   // mvKeysUn
+  const uint8_t* desc;        // mDescriptors
+  const float* uRight;        // mvuRight or null
+  int n;
+  float minX, minY, invW, invH;
+  int* cellStart;             // [kGridCells + 1]
+  int* cellItems;             // [n] keypoint indices grouped by cell (cell = posX*48 + posY), arbitrary order inside a cell
+};
+
+__device__ int mblock_exscan(int* data, int n, int* warpTmp) {  // same contract as block_exscan (256 threads)
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int chunk = (n + 255) >> 8;
+  const int beg = min(n, tid * chunk), end = min(n, beg + chunk);
+  int sum = 0;
+  for (int i = beg; i < end; i++) sum += data[i];
+  int incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) warpTmp[warp] = incl;
+  __syncthreads();
+  int woff = 0, total = 0;
+#pragma unroll
+  for (int w = 0; w < 8; w++) {
+    const int v = warpTmp[w];
+    if (w < warp) woff += v;
+    total += v;
+  }
+  int run = woff + incl - sum;
+  for (int i = beg; i < end; i++) { const int v = data[i]; data[i] = run; run += v; }
+  __syncthreads();
+  return total;
+}
+
+__device__ __forceinline__ int grid_cell_of(const GridFrame& F, float x, float y) {
+  const int posX = (int)roundf(__fmul_rn(__fsub_rn(x, F.minX), F.invW));
+  const int posY = (int)roundf(__fmul_rn(__fsub_rn(y, F.minY), F.invH));
+  if (posX < 0 || posX >= kGridCols || posY < 0 || posY >= kGridRows) return -1;
+  return posX * kGridRows + posY;
+}
+
+__global__ void __launch_bounds__(256) k_build_grid(const GridFrame* frames) {
+  __shared__ int cnt[kGridCells];
+  __shared__ int warpTmp[8];
+  const GridFrame F = frames[blockIdx.x];
+  const int tid = threadIdx.x;
+  for (int i = tid; i < kGridCells; i += 256) cnt[i] = 0;
+  __syncthreads();
+  for (int i = tid; i < F.n; i += 256) {
+    const int c = grid_cell_of(F, F.kps[i].x, F.kps[i].y);
+    if (c >= 0) atomicAdd(&cnt[c], 1);
+  }
+  __syncthreads();
+  const int total = mblock_exscan(cnt, kGridCells, warpTmp);
+  for (int i = tid; i < kGridCells; i += 256) F.cellStart[i] = cnt[i];
+  if (tid == 0) F.cellStart[kGridCells] = total;
+  __syncthreads();
+  for (int i = tid; i < F.n; i += 256) {
+    const int c = grid_cell_of(F, F.kps[i].x, F.kps[i].y);
+    if (c >= 0) F.cellItems[atomicAdd(&cnt[c], 1)] = i;
+  }
+}
+
+// ---- window candidates ----------------------------------------------------------------------------------------------
+struct QuerySet {            // one per frame
+  int nq;
+  const uint8_t* valid;      // query is searched at all
+  const float* x; const float* y; const float* r;   // window centre / half size
+  const int8_t* minL; const int8_t* maxL;            // GetFeaturesInArea level arguments
+  const float* xr;           // right-image coordinate of the query (used when F.uRight != null and xrCheck)
+  const uint8_t* desc;       // 32-byte descriptor per query
+  int xrCheck;
+  int* qOff; int* qCnt;      // per query: first entry / number of entries
+  unsigned long long* entries; int entryCap; int* entryCursor;
+};
+
+// key layout: dist[52:44] | cell order[43:32] | keypoint index[31:8] | octave[7:0]
+__device__ __forceinline__ unsigned long long make_key(int dist, int cell, int idx, int octave) {
+  return ((unsigned long long)dist << 44) | ((unsigned long long)cell << 32) | ((unsigned long long)idx << 8) | (unsigned)(octave & 0xff);
+}
+
+__global__ void __launch_bounds__(256) k_window_candidates(const GridFrame* frames, const QuerySet* sets, int* status) {
+  const GridFrame F = frames[blockIdx.y];
+  const QuerySet Q = sets[blockIdx.y];
+  const int lane = threadIdx.x & 31;
+  const int i = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (i >= Q.nq) return;
+  int nMinCellX = 0, nMaxCellX = -1, nMinCellY = 0, nMaxCellY = -1;
+  const float x = Q.x[i], y = Q.y[i], r = Q.r[i];
+  const int minLevel = Q.minL[i], maxLevel = Q.maxL[i];
+  bool live = Q.valid[i] != 0;
+  if (live) {  // Frame::GetFeaturesInArea, Frame.cc:755-777
+    nMinCellX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, F.minX), r), F.invW)));
+    nMaxCellX = min(kGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, F.minX), r), F.invW)));
+    nMinCellY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, F.minY), r), F.invH)));
+    nMaxCellY = min(kGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, F.minY), r), F.invH)));
+    if (nMinCellX >= kGridCols || nMaxCellX < 0 || nMinCellY >= kGridRows || nMaxCellY < 0) live = false;
+  }
+  const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+  const float xr = (Q.xrCheck && Q.xr) ? Q.xr[i] : 0.f;
+  const bool rightCheck = Q.xrCheck && F.uRight != nullptr;
+  uint32_t qd[8];
+  if (live) load_desc(Q.desc + 32ll * i, qd);
+  int off = 0, total = 0;
+  for (int pass = 0; pass < 2; pass++) {
+    int written = 0;
+    if (live) {
+      for (int ix = nMinCellX; ix <= nMaxCellX; ix++) {
+        const int c0 = ix * kGridRows + nMinCellY, c1 = ix * kGridRows + nMaxCellY;
+        // cells of one grid column are consecutive in memory: walk their items as one range, tracking the cell id
+        const int jb = F.cellStart[c0], je = F.cellStart[c1 + 1];
+        for (int j0 = jb; j0 < je; j0 += 32) {
+          const int j = j0 + lane;
+          bool ok = false;
+          int idx = 0, oct = 0, cell = 0;
+          if (j < je) {
+            idx = F.cellItems[j];
+            const orbx_keypoint kp = F.kps[idx];
+            oct = kp.octave;
+            ok = true;
+            if (bCheckLevels) {
+              if (oct < minLevel) ok = false;
+              if (maxLevel >= 0 && oct > maxLevel) ok = false;
+            }
+            const float distx = __fsub_rn(kp.x, x), disty = __fsub_rn(kp.y, y);
+            if (!(fabsf(distx) < r && fabsf(disty) < r)) ok = false;
+            if (ok && rightCheck) {
+              const float ur = F.uRight[idx];
+              if (ur > 0) {
+                const float er = fabsf(__fsub_rn(xr, ur));
+                if (er > r) ok = false;
+              }
+            }
+            if (ok && pass == 1) {  // which cell of the column does item j belong to?
+              cell = c0;
+              while (F.cellStart[cell + 1] <= j) cell++;
+            }
+          }
+          const unsigned m = __ballot_sync(0xffffffffu, ok);
+          if (pass == 1 && ok) {
+            uint32_t cd[8];
+            load_desc(F.desc + 32ll * idx, cd);
+            const int dist = hamming8(qd, cd);
+            Q.entries[off + written + __popc(m & ((1u << lane) - 1))] = make_key(dist, cell, idx, oct);
+          }
+          written += __popc(m);
+        }
+      }
+    }
+    if (pass == 0) {
+      total = written;
+      if (lane == 0) {
+        off = total > 0 ? atomicAdd(Q.entryCursor, total) : 0;
+        if (off + total > Q.entryCap) { atomicExch(status, ORBX_ERR_CAPACITY); total = 0; }
+        Q.qOff[i] = off; Q.qCnt[i] = total;
+      }
+      off = __shfl_sync(0xffffffffu, off, 0);
+      total = __shfl_sync(0xffffffffu, total, 0);
+      if (total == 0) break;
+    }
+  }
+}
+
+// ---- warp top-2 on keys ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void top2_insert(unsigned long long k, unsigned long long& k1, unsigned long long& k2) {
+  const unsigned long long lo = min(k, k1), hi = max(k, k1);
+  k1 = lo;
+  k2 = min(k2, hi);
+}
+__device__ __forceinline__ void top2_warp(unsigned long long& k1, unsigned long long& k2) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long o1 = __shfl_xor_sync(0xffffffffu, k1, o), o2 = __shfl_xor_sync(0xffffffffu, k2, o);
+    const unsigned long long lo = min(k1, o1), hi = max(k1, o1);
+    k1 = lo;
+    k2 = min(hi, min(k2, o2));
+  }
+}
+__device__ __forceinline__ int key_dist(unsigned long long k) { return (int)(k >> 44); }
+__device__ __forceinline__ int key_idx(unsigned long long k) { return (int)((k >> 8) & 0xffffffu); }
+__device__ __forceinline__ int key_oct(unsigned long long k) { return (int)(k & 0xffu); }
+
+constexpr int kMaxKpSmem = 16384;
+
+// ORBmatcher::ComputeThreeMaxima, ORBmatcher.cc:2416-2458
+__device__ void three_maxima(const int* hs, int L, int& ind1, int& ind2, int& ind3) {
+  int max1 = 0, max2 = 0, max3 = 0;
+  ind1 = ind2 = ind3 = -1;
+  for (int i = 0; i < L; i++) {
+    const int s = hs[i];
+    if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+    else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+    else if (s > max3) { max3 = s; ind3 = i; }
+  }
+  if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+  else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
+}
+
+__device__ __forceinline__ int rot_bin(float a1, float a2) {  // ORBmatcher.cc:2177-2183
+  float rot = __fsub_rn(a1, a2);
+  if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+  int bin = (int)roundf(__fmul_rn(rot, 1.0f / 30));
+  if (bin == 30) bin = 0;
+  return bin;
+}
+
+struct ResolveArgs {        // one per frame
+  const uint8_t* observed;  // per query: MapPoint::Observations() > 0 (null = all observed)
+  const float* angle;       // per query: source keypoint angle (rotation histogram)
+  int* kpMp;                // in/out, F.mvpMapPoints as indices (-1 empty, -2 blocking, -3 non-blocking pre-existing)
+  int* assigned;            // scratch [nq]
+  int* nmatches;            // out
+  float nnratio;
+  int distTh;
+  int anyMpBlocks;
+  int checkOrientation;
+};
+
+// SearchByProjection(Frame&, vector<MapPoint*>&, ...), ORBmatcher.cc:44-142: one warp per frame replays the map points in order.
+__global__ void __launch_bounds__(32) k_resolve_mappoints(const GridFrame* frames, const QuerySet* sets, const ResolveArgs* args) {
+  __shared__ uint8_t blocked[kMaxKpSmem];
+  const GridFrame F = frames[blockIdx.x];
+  const QuerySet Q = sets[blockIdx.x];
+  const ResolveArgs A = args[blockIdx.x];
+  const int lane = threadIdx.x;
+  for (int k = lane; k < F.n; k += 32) {
+    const int s = A.kpMp[k];
+    blocked[k] = (s == -2) || (s >= 0 && (A.observed ? A.observed[s] != 0 : true));
+  }
+  __syncwarp();
+  int nmatches = 0;
+  for (int i = 0; i < Q.nq; i++) {
+    const int c = Q.qCnt[i];
+    if (c == 0) continue;
+    const unsigned long long* e = Q.entries + Q.qOff[i];
+    unsigned long long k1 = kKeyNone, k2 = kKeyNone;
+    for (int j = lane; j < c; j += 32) {
+      const unsigned long long k = e[j];
+      if (!blocked[key_idx(k)]) top2_insert(k, k1, k2);
+    }
+    top2_warp(k1, k2);
+    if (k1 == kKeyNone) continue;
+    const int bestDist = key_dist(k1), bestLevel = key_oct(k1), bestIdx = key_idx(k1);
+    const int bestDist2 = (k2 == kKeyNone) ? 256 : key_dist(k2), bestLevel2 = (k2 == kKeyNone) ? -1 : key_oct(k2);
+    if (bestDist <= 100) {  // TH_HIGH
+      const float lim = __fmul_rn(A.nnratio, (float)bestDist2);
+      if (bestLevel == bestLevel2 && (float)bestDist > lim) continue;
+      if (bestLevel != bestLevel2 || (float)bestDist <= lim) {
+        if (lane == 0) {
+          A.kpMp[bestIdx] = i;
+          blocked[bestIdx] = A.observed ? (A.observed[i] != 0) : 1;
+        }
+        nmatches++;
+        __syncwarp();
+      }
+    }
+  }
+  if (lane == 0) *A.nmatches = nmatches;
+}
+
+// SearchByProjection(Frame&, const Frame&, ...) / (Frame&, KeyFrame*, ...): best-1 window search with the rotation histogram.
+__global__ void __launch_bounds__(32) k_resolve_window(const GridFrame* frames, const QuerySet* sets, const ResolveArgs* args) {
+  __shared__ uint8_t blocked[kMaxKpSmem];
+  __shared__ int hist[30];
+  const GridFrame F = frames[blockIdx.x];
+  const QuerySet Q = sets[blockIdx.x];
+  const ResolveArgs A = args[blockIdx.x];
+  const int lane = threadIdx.x;
+  for (int k = lane; k < F.n; k += 32) {
+    const int s = A.kpMp[k];
+    blocked[k] = A.anyMpBlocks ? (s != -1) : ((s == -2) || (s >= 0 && (A.observed ? A.observed[s] != 0 : true)));
+  }
+  if (lane < 30) hist[lane] = 0;
+  __syncwarp();
+  int nmatches = 0;
+  for (int i = 0; i < Q.nq; i++) {
+    const int c = Q.qCnt[i];
+    if (lane == 0) A.assigned[i] = -1;
+    if (c == 0) continue;
+    const unsigned long long* e = Q.entries + Q.qOff[i];
+    unsigned long long k1 = kKeyNone;
+    for (int j = lane; j < c; j += 32) {
+      const unsigned long long k = e[j];
+      if (!blocked[key_idx(k)]) k1 = min(k1, k);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) k1 = min(k1, __shfl_xor_sync(0xffffffffu, k1, o));
+    if (k1 == kKeyNone) continue;
+    const int bestDist = key_dist(k1), bestIdx = key_idx(k1);
+    if (bestDist <= A.distTh) {
+      if (lane == 0) {
+        A.kpMp[bestIdx] = i;
+        blocked[bestIdx] = A.anyMpBlocks ? 1 : (A.observed ? (A.observed[i] != 0) : 1);
+        int bin = 0;
+        if (A.checkOrientation) { bin = rot_bin(A.angle[i], F.kps[bestIdx].angle); hist[bin]++; }
+        A.assigned[i] = bestIdx | (bin << 24);
+      }
+      nmatches++;
+      __syncwarp();
+    }
+  }
+  __syncwarp();
+  if (A.checkOrientation) {
+    int i1, i2, i3;
+    three_maxima(hist, 30, i1, i2, i3);
+    int removed = 0;
+    for (int i = lane; i < Q.nq; i += 32) {
+      const int a = ((volatile int*)A.assigned)[i];
+      if (a >= 0) {
+        const int bin = a >> 24;
+        if (bin != i1 && bin != i2 && bin != i3) { A.kpMp[a & 0xffffff] = -1; removed++; }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) removed += __shfl_xor_sync(0xffffffffu, removed, o);
+    nmatches -= removed;
+  }
+  if (lane == 0) *A.nmatches = nmatches;
+}
+
+struct InitArgs {  // SearchForInitialization state, one per frame pair
+  const orbx_keypoint* kps1;   // F1.mvKeysUn
+  float* prevMatched;          // [n1][2] in/out
+  int* matches12;              // [n1] out
+  int* matches21;              // [n2] scratch
+  int* matchedDist;            // [n2] scratch
+  int* bins;                   // [n1] scratch
+  int* nmatches;
+  float nnratio;
+  int checkOrientation;
+};
+
+// ORBmatcher::SearchForInitialization, ORBmatcher.cc:722-837.
+__global__ void __launch_bounds__(32) k_resolve_init(const GridFrame* frames, const QuerySet* sets, const InitArgs* args) {
+  __shared__ int hist[30];
+  const GridFrame F2 = frames[blockIdx.x];
+  const QuerySet Q = sets[blockIdx.x];
+  const InitArgs A = args[blockIdx.x];
+  const int lane = threadIdx.x;
+  volatile int* matchedDist = A.matchedDist;
+  volatile int* matches21 = A.matches21;
+  volatile int* matches12 = A.matches12;
+  for (int k = lane; k < F2.n; k += 32) { matchedDist[k] = INT_MAX; matches21[k] = -1; }
+  for (int k = lane; k < Q.nq; k += 32) { matches12[k] = -1; A.bins[k] = -1; }
+  if (lane < 30) hist[lane] = 0;
+  __syncwarp();
+  int nmatches = 0;
+  for (int i1 = 0; i1 < Q.nq; i1++) {
+    const int c = Q.qCnt[i1];
+    if (c == 0) continue;
+    const unsigned long long* e = Q.entries + Q.qOff[i1];
+    unsigned long long k1 = kKeyNone, k2 = kKeyNone;
+    for (int j = lane; j < c; j += 32) {
+      const unsigned long long k = e[j];
+      if (matchedDist[key_idx(k)] <= key_dist(k)) continue;
+      top2_insert(k, k1, k2);
+    }
+    top2_warp(k1, k2);
+    if (k1 == kKeyNone) continue;
+    const int bestDist = key_dist(k1), bestIdx2 = key_idx(k1);
+    const float bestDist2 = (k2 == kKeyNone) ? (float)INT_MAX : (float)key_dist(k2);
+    if (bestDist <= 50 && (float)bestDist < __fmul_rn(bestDist2, A.nnratio)) {  // TH_LOW
+      const int prev = matches21[bestIdx2];
+      if (lane == 0) {
+        if (prev >= 0) matches12[prev] = -1;
+        matches12[i1] = bestIdx2;
+        matches21[bestIdx2] = i1;
+        matchedDist[bestIdx2] = bestDist;
+        if (A.checkOrientation) {
+          const int bin = rot_bin(A.kps1[i1].angle, F2.kps[bestIdx2].angle);
+          hist[bin]++;
+          A.bins[i1] = bin;
+        }
+      }
+      if (prev >= 0) nmatches--;
+      nmatches++;
+      __syncwarp();
+    }
+  }
+  __syncwarp();
+  if (A.checkOrientation) {
+    int i1, i2, i3;
+    three_maxima(hist, 30, i1, i2, i3);
+    int removed = 0;
+    for (int i = lane; i < Q.nq; i += 32) {
+      const int bin = ((volatile int*)A.bins)[i];
+      if (bin >= 0 && bin != i1 && bin != i2 && bin != i3 && matches12[i] >= 0) { matches12[i] = -1; removed++; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) removed += __shfl_xor_sync(0xffffffffu, removed, o);
+    nmatches -= removed;
+  }
+  __syncwarp();
+  for (int i = lane; i < Q.nq; i += 32) {
+    const int m = matches12[i];
+    if (m >= 0) { A.prevMatched[2 * i] = F2.kps[m].x; A.prevMatched[2 * i + 1] = F2.kps[m].y; }
+  }
+  if (lane == 0) *A.nmatches = nmatches;
+}
+
+// ---- brute-force 2-NN ----------------------------------------------------------------------------------------------------
+// thread = one query (descriptor in 8 registers); train descriptors stream through shared memory in tiles of 128 and are
+// read as broadcast LDS.128; best/second inside one launch are packed 32-bit keys (dist << 23 | local train index) so the
+// update is three integer min/max; lower index wins ties exactly like cv::BFMatcher.  The running state across launches
+// (successive train chunks of the all-pairs sweep arriving over NCCL) is a pair of 64-bit keys (dist << 32 | global index).
+// `exclude` (optional, per query) removes one contiguous global train range (a keyframe is not matched against itself);
+// only the few tiles that overlap the block's exclusion ranges take the checked path.
+__global__ void __launch_bounds__(128) k_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, long long trainBase, const int2* exclude,
+                                              unsigned long long* key0, unsigned long long* key1, int init) {
+  __shared__ uint4 tile[128 * 2];
+  __shared__ int sExMin, sExMax;
+  const int i = blockIdx.x * 128 + threadIdx.x;
+  uint32_t qd[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  uint32_t k0 = 0xffffffffu, k1 = 0xffffffffu;
+  int ex0 = 0, ex1 = 0;  // local (chunk-relative) exclusion range
+  if (threadIdx.x == 0) { sExMin = INT_MAX; sExMax = INT_MIN; }
+  __syncthreads();
+  if (i < nq) {
+    load_desc(q + 32ll * i, qd);
+    if (exclude) {
+      const int2 ex = exclude[i];
+      ex0 = (int)max(0ll, min((long long)nt, (long long)ex.x - trainBase));
+      ex1 = (int)max(0ll, min((long long)nt, (long long)ex.y - trainBase));
+      if (ex1 > ex0) { atomicMin(&sExMin, ex0); atomicMax(&sExMax, ex1); }
+    }
+  }
+  __syncthreads();
+  const int bExMin = sExMin, bExMax = sExMax;
+  for (int base = 0; base < nt; base += 128) {
+    const int m = min(128, nt - base);
+    __syncthreads();
+    for (int w = threadIdx.x; w < 2 * m; w += 128) tile[w] = __ldg(reinterpret_cast<const uint4*>(t + 32ll * base) + w);
+    __syncthreads();
+    if (i >= nq) continue;
+    const bool checked = (base < bExMax) && (base + m > bExMin);
+    if (!checked) {
+#pragma unroll 4
+      for (int j = 0; j < m; j++) {
+        const uint4 a = tile[2 * j], b = tile[2 * j + 1];
+        const int d = __popc(qd[0] ^ a.x) + __popc(qd[1] ^ a.y) + __popc(qd[2] ^ a.z) + __popc(qd[3] ^ a.w) + __popc(qd[4] ^ b.x) +
+                      __popc(qd[5] ^ b.y) + __popc(qd[6] ^ b.z) + __popc(qd[7] ^ b.w);
+        const uint32_t k = ((uint32_t)d << 23) | (uint32_t)(base + j);
+        const uint32_t lo = min(k, k0), hi = max(k, k0);
+        k0 = lo;
+        k1 = min(k1, hi);
+      }
+    } else {
+      for (int j = 0; j < m; j++) {
+        const int lj = base + j;
+        if (lj >= ex0 && lj < ex1) continue;
+        const uint4 a = tile[2 * j], b = tile[2 * j + 1];
+        const int d = __popc(qd[0] ^ a.x) + __popc(qd[1] ^ a.y) + __popc(qd[2] ^ a.z) + __popc(qd[3] ^ a.w) + __popc(qd[4] ^ b.x) +
+                      __popc(qd[5] ^ b.y) + __popc(qd[6] ^ b.z) + __popc(qd[7] ^ b.w);
+        const uint32_t k = ((uint32_t)d << 23) | (uint32_t)lj;
+        const uint32_t lo = min(k, k0), hi = max(k, k0);
+        k0 = lo;
+        k1 = min(k1, hi);
+      }
+    }
+  }
+  if (i < nq) {
+    unsigned long long g0 = kKeyNone, g1 = kKeyNone;
+    if (!init) { g0 = key0[i]; g1 = key1[i]; }
+    if (k0 != 0xffffffffu) top2_insert(((unsigned long long)(k0 >> 23) << 32) | (unsigned long long)(trainBase + (k0 & 0x7fffffu)), g0, g1);
+    if (k1 != 0xffffffffu) top2_insert(((unsigned long long)(k1 >> 23) << 32) | (unsigned long long)(trainBase + (k1 & 0x7fffffu)), g0, g1);
+    key0[i] = g0; key1[i] = g1;
+  }
+}
+
+// ---- stereo -----------------------------------------------------------------------------------------------------------------
+struct ScaleTab { float scale[ORBX_MAX_LEVELS]; float invScale[ORBX_MAX_LEVELS]; };
+
+struct StereoOut {   // [nframes][kpStride]
+  float* uRight; float* depth; int* bestDist; int* bestIdx; int* sad;
+};
+
+// Hamming stage of Frame::ComputeStereoMatches (Frame.cc:911-984): one warp per left keypoint scans every right keypoint of
+// the pair; "iR is listed in row vL" (the reference's vRowIndices table) is evaluated as floor(yR - r) <= (int)vL <= ceil(yR + r).
+__global__ void __launch_bounds__(256) k_stereo_hamming(const __grid_constant__ Geom g, const __grid_constant__ Batch bL,
+                                                        const __grid_constant__ Batch bR, const __grid_constant__ ScaleTab tab,
+                                                        float maxD, StereoOut out) {
+  const int f = blockIdx.y, lane = threadIdx.x & 31;
+  const int iL = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int nL = bL.counts[f], nR = bR.counts[f];
+  if (iL >= nL) return;
+  const long long o = (long long)f * g.kpStride;
+  const orbx_keypoint kl = bL.kps[o + iL];
+  const int levelL = kl.octave;
+  const float vL = kl.y, uL = kl.x;
+  const int row = (int)vL;
+  const float minU = __fsub_rn(uL, maxD), maxU = uL;
+  uint32_t key = 100u << 16;  // TH_HIGH: only dist < 100 replaces it
+  if (!(maxU < 0)) {
+    uint32_t dl[8];
+    load_desc(bL.desc + (o + iL) * 32, dl);
+    for (int iR = lane; iR < nR; iR += 32) {
+      const orbx_keypoint kr = bR.kps[o + iR];
+      const float r = __fmul_rn(2.0f, tab.scale[kr.octave]);
+      const int maxr = (int)ceilf(__fadd_rn(kr.y, r)), minr = (int)floorf(__fsub_rn(kr.y, r));
+      if (row < minr || row > maxr) continue;
+      if (kr.octave < levelL - 1 || kr.octave > levelL + 1) continue;
+      if (kr.x >= minU && kr.x <= maxU) {
+        uint32_t dr[8];
+        load_desc(bR.desc + (o + iR) * 32, dr);
+        key = min(key, ((uint32_t)hamming8(dl, dr) << 16) | (uint32_t)iR);
+      }
+    }
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, s));
+  if (lane == 0) {
+    const int d = key >> 16;
+    out.bestDist[o + iL] = d;
+    out.bestIdx[o + iL] = d < 100 ? (int)(key & 0xffffu) : -1;
+    out.uRight[o + iL] = -1.0f; out.depth[o + iL] = -1.0f; out.sad[o + iL] = -1;
+  }
+}
+
+// Sub-pixel refinement (Frame.cc:987-1062): 11x11 centre-subtracted SAD over 11 shifts on the keypoint's pyramid level, parabola fit.
+__global__ void __launch_bounds__(256) k_stereo_sad(const __grid_constant__ Geom g, const __grid_constant__ Batch bL,
+                                                    const __grid_constant__ Batch bR, const __grid_constant__ ScaleTab tab,
+                                                    float maxD, float mbf, StereoOut out) {
+  const int f = blockIdx.y, lane = threadIdx.x & 31;
+  const int iL = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (iL >= bL.counts[f]) return;
+  const long long o = (long long)f * g.kpStride;
+  if (out.bestDist[o + iL] >= 75) return;  // thOrbDist = (TH_HIGH+TH_LOW)/2
+  const int bestIdxR = out.bestIdx[o + iL];
+  const orbx_keypoint kl = bL.kps[o + iL];
+  const int levelL = kl.octave;
+  const float uL = kl.x, vL = kl.y;
+  const float uR0 = bR.kps[o + bestIdxR].x;
+  const float sf = tab.invScale[levelL];
+  const float scaleduL = roundf(__fmul_rn(uL, sf)), scaledvL = roundf(__fmul_rn(vL, sf)), scaleduR0 = roundf(__fmul_rn(uR0, sf));
+  const int w = 5, L = 5;
+  const LevelGeom& G = g.lv[levelL];
+  int spL, spR;
+  const uint8_t* imL = level_ptr(g, bL, levelL, f, spL);
+  const uint8_t* imR = level_ptr(g, bR, levelL, f, spR);
+  const int y0 = (int)(scaledvL - w), xl0 = (int)(scaleduL - w);
+  if (y0 < 0 || y0 + 2 * w + 1 > G.h || xl0 < 0 || xl0 + 2 * w + 1 > G.w) return;  // the reference throws cv::Exception here
+  const float iniu = __fsub_rn(__fadd_rn(scaleduR0, (float)L), (float)w);
+  const float endu = __fadd_rn(__fadd_rn(__fadd_rn(scaleduR0, (float)L), (float)w), 1.0f);
+  if (iniu < 0 || endu >= (float)G.w) return;
+  const int xrBase = (int)scaleduR0 - w;  // leftmost column of the incR = 0 window
+  if (xrBase - L < 0 || xrBase + L + 2 * w + 1 > G.w) return;  // cv::Exception in the reference
+  const int cL = imL[(long long)(y0 + w) * spL + xl0 + w];
+  int il[4], py[4], px[4];
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const int p = lane + 32 * k;
+    py[k] = p / 11; px[k] = p - py[k] * 11;
+    il[k] = (p < 121) ? (int)imL[(long long)(y0 + py[k]) * spL + xl0 + px[k]] - cL : 0;
+  }
+  int bestDistS = INT_MAX, bestincR = 0;
+  float vDists[11];
+#pragma unroll
+  for (int incR = -5; incR <= 5; incR++) {
+    const int xr0 = xrBase + incR;
+    const int cR = imR[(long long)(y0 + w) * spR + xr0 + w];
+    int sum = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int p = lane + 32 * k;
+      if (p < 121) sum += abs(il[k] - ((int)imR[(long long)(y0 + py[k]) * spR + xr0 + px[k]] - cR));
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, s);
+    const float dist = (float)sum;
+    if (dist < (float)bestDistS) { bestDistS = (int)dist; bestincR = incR; }
+    vDists[incR + 5] = dist;
+  }
+  if (bestincR == -L || bestincR == L) return;
+  float dist1 = 0, dist2 = 0, dist3 = 0;
+#pragma unroll
+  for (int k = 1; k < 10; k++)
+    if (k == bestincR + 5) { dist1 = vDists[k - 1]; dist2 = vDists[k]; dist3 = vDists[k + 1]; }
+  const float deltaR = __fdiv_rn(__fsub_rn(dist1, dist3), __fmul_rn(2.0f, __fsub_rn(__fadd_rn(dist1, dist3), __fmul_rn(2.0f, dist2))));
+  if (deltaR < -1 || deltaR > 1) return;
+  float bestuR = __fmul_rn(tab.scale[levelL], __fadd_rn(__fadd_rn(scaleduR0, (float)bestincR), deltaR));
+  float disparity = __fsub_rn(uL, bestuR);
+  if (disparity >= 0 && disparity < maxD) {
+    if (disparity <= 0) { disparity = 0.01f; bestuR = (float)((double)uL - 0.01); }
+    if (lane == 0) {
+      out.depth[o + iL] = __fdiv_rn(mbf, disparity);
+      out.uRight[o + iL] = bestuR;
+      out.sad[o + iL] = bestDistS;
+    }
+  }
+}
+
+// Outlier cut (Frame.cc:1065-1078): median of the accepted SAD values by (sad, iL) order, drop everything >= 1.5*1.4*median.
+__global__ void __launch_bounds__(256) k_stereo_median(const __grid_constant__ Geom g, const __grid_constant__ Batch bL, StereoOut out) {
+  extern __shared__ int ssad[];
+  __shared__ int sN, sMedian;
+  const int f = blockIdx.x, tid = threadIdx.x;
+  const int nL = bL.counts[f];
+  const long long o = (long long)f * g.kpStride;
+  if (tid == 0) { sN = 0; sMedian = -1; }
+  __syncthreads();
+  int local = 0;
+  for (int i = tid; i < nL; i += 256) { const int v = out.sad[o + i]; ssad[i] = v; local += v >= 0; }
+  if (local) atomicAdd(&sN, local);
+  __syncthreads();
+  const int n = sN;
+  if (n == 0) return;
+  const int target = n / 2;
+  for (int i = tid; i < nL; i += 256) {
+    const int v = ssad[i];
+    if (v < 0) continue;
+    int rank = 0;
+    for (int j = 0; j < nL; j++) {
+      const int u = ssad[j];
+      rank += (u >= 0) && (u < v || (u == v && j < i));
+    }
+    if (rank == target) sMedian = v;
+  }
+  __syncthreads();
+  const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)sMedian);
+  for (int i = tid; i < nL; i += 256) {
+    const int v = ssad[i];
+    if (v >= 0 && !((float)v < thDist)) { out.uRight[o + i] = -1.0f; out.depth[o + i] = -1.0f; }
+  }
+}
+
+}  // namespace orbx

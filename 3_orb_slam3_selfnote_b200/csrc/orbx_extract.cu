@@ -30,59 +30,13 @@ void set_error(const char* fmt, ...) {
   g_err = buf;
 }
 
-#define CK(call)                                                                                         \
-  do {                                                                                                   \
-    cudaError_t e_ = (call);                                                                             \
-    if (e_ != cudaSuccess) {                                                                             \
-      set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));                    \
-      return ORBX_ERR_CUDA;                                                                              \
-    }                                                                                                    \
-  } while (0)
-
 static inline int round_up(int v, int a) { return (v + a - 1) / a * a; }
 static inline int cv_round_f(float v) { return (int)lrintf(v); }
 static inline int cv_floor_d(double v) { int i = (int)v; return i - (i > v); }
 
-struct Slot {
-  cudaStream_t stream = nullptr;
-  uint8_t* in = nullptr;  // staged level-0 frames for the host path [max_batch][h][inPitch]
-  uint8_t* pyr = nullptr;
-  uint8_t* blur = nullptr;
-  PreCand* cand = nullptr;
-  int* zero = nullptr;  // candCount | cellFlags | status  (cleared per batch)
-  size_t zeroBytes = 0;
-  int* candCount = nullptr; int* cellFlags = nullptr; int* status = nullptr;
-  LevelKp* lkp = nullptr; int* lkpCount = nullptr; int* lkpDest = nullptr; int* nCand = nullptr;
-  uint32_t* qXY = nullptr; uint32_t* qOrd = nullptr; uint16_t* qNode = nullptr; uint8_t* qResp = nullptr; uint8_t* qSel = nullptr;
-  orbx_keypoint* kps = nullptr; uint8_t* desc = nullptr; int* counts = nullptr; int* mono = nullptr;
-  int* hStatus = nullptr;  // pinned
-  Batch last{};            // descriptor of the last batch run in this slot
-  int lastFrames = 0;
-  cudaEvent_t ev[8] = {};  // stage boundaries (profiling mode only)
-  bool evValid = false;
-};
-
 }  // namespace orbx
 
 using namespace orbx;
-
-struct orbx_extractor {
-  orbx_params p{};
-  double scaleFactorD = 0;
-  std::vector<float> scale, invScale, sigma2, invSigma2;
-  std::vector<int> quota;
-  int umax[16];
-  // geometry-dependent state
-  bool haveGeom = false;
-  Geom g{};
-  int inPitch = 0;  // pitch of the staged input
-  long long pyrFrame = 0, blurFrame = 0;
-  RsX* dRsx = nullptr; RsY* dRsy = nullptr; uint16_t* dInfo = nullptr; int8_t* dPattern = nullptr;
-  size_t qtSmem = 0;
-  Slot slot[2];
-  int lastSlot = 0;
-  bool profile = false;
-};
 
 static void free_geom(orbx_extractor* h) {
   cudaSetDevice(h->p.device);
@@ -104,7 +58,7 @@ static void free_geom(orbx_extractor* h) {
 }
 
 // Build level sizes, cell grids, quadtree roots, tile tables and the lookup tables for one image size.
-static int build_geom(orbx_extractor* h, int width, int height) {
+int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
   if (h->haveGeom && h->g.width == width && h->g.height == height) return ORBX_OK;
   if (h->haveGeom) free_geom(h);
   CK(cudaSetDevice(h->p.device));
@@ -269,7 +223,7 @@ static int build_geom(orbx_extractor* h, int width, int height) {
 }
 
 // Enqueue one device batch on `st` using the workspaces of slot `si`.
-static int run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int nframes, int pitch, long long frameStride, int lap0, int lap1,
+int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int nframes, int pitch, long long frameStride, int lap0, int lap1,
                      cudaStream_t st) {
   Slot& s = h->slot[si];
   const Geom& g = h->g;
@@ -403,7 +357,7 @@ int orbx_get_features_per_level(const orbx_extractor* h, int* quota) {
 }
 int orbx_max_keypoints(const orbx_extractor* h, int width, int height) {
   if (!h || width <= 0 || height <= 0) return ORBX_ERR_ARG;
-  int rc = build_geom(const_cast<orbx_extractor*>(h), width, height);
+  int rc = extractor_build_geom(const_cast<orbx_extractor*>(h), width, height);
   if (rc != ORBX_OK) return rc;
   return h->g.kpStride;
 }
@@ -438,10 +392,10 @@ int orbx_extract_batch_device(orbx_extractor* h, const uint8_t* dImages, int nfr
     set_error("device frames must be 4-byte aligned with a pitch that is a multiple of 4");
     return ORBX_ERR_ARG;
   }
-  int rc = build_geom(h, width, height);
+  int rc = extractor_build_geom(h, width, height);
   if (rc != ORBX_OK) return rc;
   cudaStream_t st = stream ? (cudaStream_t)stream : h->slot[0].stream;
-  return run_batch(h, 0, dImages, nframes, pitch, (long long)frameStride, lap0, lap1, st);
+  return extractor_run_batch(h, 0, dImages, nframes, pitch, (long long)frameStride, lap0, lap1, st);
 }
 
 int orbx_batch_results_device(orbx_extractor* h, const orbx_keypoint** kps, const uint8_t** desc, const int** counts, const int** mono,
@@ -482,7 +436,7 @@ int orbx_extract_batch_host(orbx_extractor* h, const uint8_t* images, int nframe
   if (!h) return ORBX_ERR_ARG;
   if (!images || width <= 0 || height <= 0 || nframes <= 0) return ORBX_EMPTY_IMAGE;
   if (!kps || !desc || !counts || !mono || capPerFrame <= 0 || stride < width) return ORBX_ERR_ARG;
-  int rc = build_geom(h, width, height);
+  int rc = extractor_build_geom(h, width, height);
   if (rc != ORBX_OK) return rc;
   const Geom& g = h->g;
   const int B = h->p.max_batch;
@@ -502,7 +456,7 @@ int orbx_extract_batch_host(orbx_extractor* h, const uint8_t* images, int nframe
         CK(cudaMemcpy2DAsync(s.in + (size_t)f * h->inPitch * height, h->inPitch, src + (size_t)f * frameStride, stride, width, height,
                              cudaMemcpyHostToDevice, st));
     }
-    rc = run_batch(h, si, s.in, nb, h->inPitch, (long long)h->inPitch * height, lap0, lap1, st);
+    rc = extractor_run_batch(h, si, s.in, nb, h->inPitch, (long long)h->inPitch * height, lap0, lap1, st);
     if (rc != ORBX_OK) return rc;
     CK(cudaMemcpyAsync(counts + f0, s.counts, nb * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(mono + f0, s.mono, nb * sizeof(int), cudaMemcpyDeviceToHost, st));

@@ -1,7 +1,68 @@
-// Internal helpers shared by the translation units of liborbx.so.
+// Internal definitions shared by the translation units of liborbx.so (not part of the C-ABI).
 #pragma once
+#include <cuda_runtime.h>
 #include <stdarg.h>
+
+#include <vector>
+
+#include "geom.h"
 
 namespace orbx {
 void set_error(const char* fmt, ...);
-}
+
+#define CK(call)                                                                                         \
+  do {                                                                                                   \
+    cudaError_t e_ = (call);                                                                             \
+    if (e_ != cudaSuccess) {                                                                             \
+      set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));                    \
+      return ORBX_ERR_CUDA;                                                                              \
+    }                                                                                                    \
+  } while (0)
+
+struct Slot {
+  cudaStream_t stream = nullptr;
+  uint8_t* in = nullptr;  // staged level-0 frames for the host path [max_batch][h][inPitch]
+  uint8_t* pyr = nullptr;
+  uint8_t* blur = nullptr;
+  PreCand* cand = nullptr;
+  int* zero = nullptr;  // candCount | cellFlags | status  (cleared per batch)
+  size_t zeroBytes = 0;
+  int* candCount = nullptr; int* cellFlags = nullptr; int* status = nullptr;
+  LevelKp* lkp = nullptr; int* lkpCount = nullptr; int* lkpDest = nullptr; int* nCand = nullptr;
+  uint32_t* qXY = nullptr; uint32_t* qOrd = nullptr; uint16_t* qNode = nullptr; uint8_t* qResp = nullptr; uint8_t* qSel = nullptr;
+  orbx_keypoint* kps = nullptr; uint8_t* desc = nullptr; int* counts = nullptr; int* mono = nullptr;
+  int* hStatus = nullptr;  // pinned
+  Batch last{};            // descriptor of the last batch run in this slot
+  int lastFrames = 0;
+  cudaEvent_t ev[8] = {};  // stage boundaries (profiling mode only)
+  bool evValid = false;
+};
+
+}  // namespace orbx
+
+struct orbx_extractor {
+  typedef orbx::Geom Geom; typedef orbx::RsX RsX; typedef orbx::RsY RsY; typedef orbx::Slot Slot;
+  orbx_params p{};
+  double scaleFactorD = 0;
+  std::vector<float> scale, invScale, sigma2, invSigma2;
+  std::vector<int> quota;
+  int umax[16];
+  // geometry-dependent state
+  bool haveGeom = false;
+  Geom g{};
+  int inPitch = 0;  // pitch of the staged input
+  long long pyrFrame = 0, blurFrame = 0;
+  RsX* dRsx = nullptr; RsY* dRsy = nullptr; uint16_t* dInfo = nullptr; int8_t* dPattern = nullptr;
+  size_t qtSmem = 0;
+  Slot slot[2];
+  int lastSlot = 0;
+  bool profile = false;
+};
+
+
+namespace orbx {
+// enqueue one extractor batch (defined in orbx_extract.cu)
+int extractor_run_batch(orbx_extractor* h, int slot, const uint8_t* dIn, int nframes, int pitch, long long frameStride, int lap0, int lap1,
+                        cudaStream_t st);
+int extractor_build_geom(orbx_extractor* h, int width, int height);
+}  // namespace orbx

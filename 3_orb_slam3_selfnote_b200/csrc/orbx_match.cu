@@ -1,0 +1,520 @@
+// Host side of the matcher: handle, device arena, query preparation (the scalar per-query arithmetic the reference does in
+// its loop prologues) and the extern "C" entry points of include/orbx.h.  All distance / search work is in match_kernels.cuh.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "match_kernels.cuh"
+#include "orbx_internal.h"
+
+using namespace orbx;
+
+struct orbx_matcher {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  uint8_t* arena = nullptr;
+  size_t arenaCap = 0, arenaUsed = 0;
+  int* dStatus = nullptr;
+  // stereo results of the last orbx_stereo_match_batch
+  float* sURight = nullptr; float* sDepth = nullptr; int* sBestDist = nullptr; int* sBestIdx = nullptr; int* sSad = nullptr;
+  size_t sCap = 0;
+  int sFrames = 0, sStride = 0;
+};
+
+namespace {
+
+struct ArenaPlan {  // two-phase bump allocation: plan sizes, ensure capacity, then carve
+  size_t total = 0;
+  size_t add(size_t bytes) { size_t off = total; total += (bytes + 255) & ~(size_t)255; return off; }
+};
+
+int arena_ensure(orbx_matcher* m, size_t bytes) {
+  if (bytes <= m->arenaCap) return ORBX_OK;
+  CK(cudaStreamSynchronize(m->stream));
+  if (m->arena) CK(cudaFree(m->arena));
+  m->arena = nullptr;
+  m->arenaCap = 0;
+  size_t cap = std::max(bytes + bytes / 4, (size_t)1 << 20);
+  CK(cudaMalloc(&m->arena, cap));
+  m->arenaCap = cap;
+  return ORBX_OK;
+}
+
+template <class T>
+T* at(orbx_matcher* m, size_t off) { return reinterpret_cast<T*>(m->arena + off); }
+
+int check_view(const orbx_frame_view* F, bool needScale) {
+  if (!F || F->n < 0 || (F->n > 0 && (!F->keypoints || !F->descriptors))) { set_error("bad frame view"); return ORBX_ERR_ARG; }
+  if (needScale && (!F->scale_factors || F->nlevels < 1)) { set_error("frame view without scale factors"); return ORBX_ERR_ARG; }
+  if (!(F->max_x > F->min_x) || !(F->max_y > F->min_y)) { set_error("frame view with empty bounds"); return ORBX_ERR_ARG; }
+  if (F->n > kMaxKpSmem) { set_error("more than %d keypoints per frame is unsupported by the resolve kernels", kMaxKpSmem); return ORBX_ERR_UNSUPPORTED; }
+  return ORBX_OK;
+}
+
+// One window-search problem: the frame, its queries (already reduced to x / y / r / level range by the caller) and where
+// results go.  Everything is a host pointer; run_window_search stages it, builds the grid, lists candidates and resolves.
+struct HostQueries {
+  int nq = 0;
+  std::vector<uint8_t> valid;
+  std::vector<float> x, y, r, xr;
+  std::vector<int8_t> minL, maxL;
+  const uint8_t* desc = nullptr;  // nq x 32
+  bool xrCheck = false;
+};
+
+enum ResolveKind { RESOLVE_NONE, RESOLVE_MAPPOINTS, RESOLVE_WINDOW, RESOLVE_INIT };
+
+struct WindowJob {
+  // frame (host, or device when devKps != null)
+  const orbx_frame_view* F = nullptr;
+  const orbx_keypoint* devKps = nullptr; const uint8_t* devDesc = nullptr; const int* devCount = nullptr; int devN = 0;
+  float minX = 0, minY = 0, maxX = 0, maxY = 0;
+  HostQueries q;
+  // resolve inputs
+  const uint8_t* observed = nullptr; const float* angle = nullptr;
+  int* kpMp = nullptr; int kpMpLen = 0;  // host in/out
+  float nnratio = 0; int distTh = 100; int anyMpBlocks = 0; int checkOrientation = 0;
+  // init search
+  const orbx_frame_view* F1 = nullptr; float* prevMatched = nullptr; int* matches12 = nullptr;
+  int* nmatches = nullptr;
+  // features_in_area
+  std::vector<unsigned long long>* entriesOut = nullptr;
+};
+
+int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind kind) {
+  const int nj = (int)jobs.size();
+  if (nj == 0) return ORBX_OK;
+  CK(cudaSetDevice(m->device));
+  // ---- plan the arena
+  ArenaPlan plan;
+  struct Off { size_t kps, desc, uRight, cellStart, cellItems, valid, x, y, r, xr, minL, maxL, qdesc, qOff, qCnt, entries, cursor,
+               observed, angle, kpMp, assigned, nmatches, kps1, prevMatched, m12, m21, mdist, bins; };
+  std::vector<Off> off(nj);
+  std::vector<int> entryCap(nj);
+  for (int j = 0; j < nj; j++) {
+    WindowJob& J = jobs[j];
+    const int n = J.devKps ? J.devN : J.F->n;
+    const int nq = J.q.nq;
+    Off& o = off[j];
+    o.kps = J.devKps ? 0 : plan.add((size_t)std::max(n, 1) * sizeof(orbx_keypoint));
+    o.desc = J.devKps ? 0 : plan.add((size_t)std::max(n, 1) * 32);
+    o.uRight = (!J.devKps && J.F->u_right) ? plan.add((size_t)std::max(n, 1) * 4) : (size_t)-1;
+    o.cellStart = plan.add((kGridCells + 1) * sizeof(int));
+    o.cellItems = plan.add((size_t)std::max(n, 1) * sizeof(int));
+    o.valid = plan.add(std::max(nq, 1));
+    o.x = plan.add((size_t)std::max(nq, 1) * 4); o.y = plan.add((size_t)std::max(nq, 1) * 4); o.r = plan.add((size_t)std::max(nq, 1) * 4);
+    o.xr = J.q.xrCheck ? plan.add((size_t)std::max(nq, 1) * 4) : (size_t)-1;
+    o.minL = plan.add(std::max(nq, 1)); o.maxL = plan.add(std::max(nq, 1));
+    o.qdesc = plan.add((size_t)std::max(nq, 1) * 32);
+    o.qOff = plan.add((size_t)std::max(nq, 1) * 4); o.qCnt = plan.add((size_t)std::max(nq, 1) * 4);
+    // candidate capacity: windows hold a few dozen keypoints; size generously and report overflow instead of truncating
+    entryCap[j] = (int)std::min<long long>((long long)nq * std::max(n, 1), std::max<long long>(1 << 16, (long long)nq * 256));
+    o.entries = plan.add((size_t)std::max(entryCap[j], 1) * 8);
+    o.cursor = plan.add(4);
+    o.observed = J.observed ? plan.add(std::max(nq, 1)) : (size_t)-1;
+    o.angle = J.angle ? plan.add((size_t)std::max(nq, 1) * 4) : (size_t)-1;
+    o.kpMp = J.kpMp ? plan.add((size_t)std::max(n, 1) * 4) : (size_t)-1;
+    o.assigned = plan.add((size_t)std::max(nq, 1) * 4);
+    o.nmatches = plan.add(4);
+    if (kind == RESOLVE_INIT) {
+      o.kps1 = plan.add((size_t)std::max(nq, 1) * sizeof(orbx_keypoint));
+      o.prevMatched = plan.add((size_t)std::max(nq, 1) * 8);
+      o.m12 = plan.add((size_t)std::max(nq, 1) * 4);
+      o.m21 = plan.add((size_t)std::max(n, 1) * 4);
+      o.mdist = plan.add((size_t)std::max(n, 1) * 4);
+      o.bins = plan.add((size_t)std::max(nq, 1) * 4);
+    }
+  }
+  const size_t oFrames = plan.add(nj * sizeof(GridFrame)), oSets = plan.add(nj * sizeof(QuerySet));
+  const size_t oArgs = plan.add(nj * std::max(sizeof(ResolveArgs), sizeof(InitArgs)));
+  int rc = arena_ensure(m, plan.total);
+  if (rc != ORBX_OK) return rc;
+  cudaStream_t st = m->stream;
+  auto up = [&](size_t o, const void* src, size_t bytes) -> cudaError_t {
+    if (bytes == 0 || !src) return cudaSuccess;
+    return cudaMemcpyAsync(m->arena + o, src, bytes, cudaMemcpyHostToDevice, st);
+  };
+  std::vector<GridFrame> frames(nj);
+  std::vector<QuerySet> sets(nj);
+  std::vector<ResolveArgs> rargs(nj);
+  std::vector<InitArgs> iargs(nj);
+  int maxQ = 0, maxN = 0;
+  for (int j = 0; j < nj; j++) {
+    WindowJob& J = jobs[j];
+    const Off& o = off[j];
+    const int nq = J.q.nq;
+    GridFrame& G = frames[j];
+    if (J.devKps) {
+      G.kps = J.devKps; G.desc = J.devDesc; G.uRight = nullptr; G.n = J.devN;
+    } else {
+      CK(up(o.kps, J.F->keypoints, (size_t)J.F->n * sizeof(orbx_keypoint)));
+      CK(up(o.desc, J.F->descriptors, (size_t)J.F->n * 32));
+      if (J.F->u_right) CK(up(o.uRight, J.F->u_right, (size_t)J.F->n * 4));
+      G.kps = at<orbx_keypoint>(m, o.kps); G.desc = at<uint8_t>(m, o.desc);
+      G.uRight = J.F->u_right ? at<float>(m, o.uRight) : nullptr;
+      G.n = J.F->n;
+    }
+    G.minX = J.minX; G.minY = J.minY;
+    G.invW = (float)kGridCols / (J.maxX - J.minX);  // Frame.cc:160-161
+    G.invH = (float)kGridRows / (J.maxY - J.minY);
+    G.cellStart = at<int>(m, o.cellStart); G.cellItems = at<int>(m, o.cellItems);
+    maxN = std::max(maxN, G.n);
+    QuerySet& Q = sets[j];
+    Q.nq = nq;
+    CK(up(o.valid, J.q.valid.data(), nq)); CK(up(o.x, J.q.x.data(), (size_t)nq * 4)); CK(up(o.y, J.q.y.data(), (size_t)nq * 4));
+    CK(up(o.r, J.q.r.data(), (size_t)nq * 4)); CK(up(o.minL, J.q.minL.data(), nq)); CK(up(o.maxL, J.q.maxL.data(), nq));
+    CK(up(o.qdesc, J.q.desc, (size_t)nq * 32));
+    if (J.q.xrCheck) CK(up(o.xr, J.q.xr.data(), (size_t)nq * 4));
+    Q.valid = at<uint8_t>(m, o.valid); Q.x = at<float>(m, o.x); Q.y = at<float>(m, o.y); Q.r = at<float>(m, o.r);
+    Q.minL = at<int8_t>(m, o.minL); Q.maxL = at<int8_t>(m, o.maxL); Q.desc = at<uint8_t>(m, o.qdesc);
+    Q.xr = J.q.xrCheck ? at<float>(m, o.xr) : nullptr; Q.xrCheck = J.q.xrCheck ? 1 : 0;
+    Q.qOff = at<int>(m, o.qOff); Q.qCnt = at<int>(m, o.qCnt);
+    Q.entries = at<unsigned long long>(m, o.entries); Q.entryCap = entryCap[j]; Q.entryCursor = at<int>(m, o.cursor);
+    CK(cudaMemsetAsync(m->arena + o.cursor, 0, 4, st));
+    maxQ = std::max(maxQ, nq);
+    if (kind == RESOLVE_MAPPOINTS || kind == RESOLVE_WINDOW) {
+      ResolveArgs& A = rargs[j];
+      if (J.observed) CK(up(o.observed, J.observed, nq));
+      if (J.angle) CK(up(o.angle, J.angle, (size_t)nq * 4));
+      CK(up(o.kpMp, J.kpMp, (size_t)G.n * 4));
+      A.observed = J.observed ? at<uint8_t>(m, o.observed) : nullptr;
+      A.angle = J.angle ? at<float>(m, o.angle) : nullptr;
+      A.kpMp = at<int>(m, o.kpMp); A.assigned = at<int>(m, o.assigned); A.nmatches = at<int>(m, o.nmatches);
+      A.nnratio = J.nnratio; A.distTh = J.distTh; A.anyMpBlocks = J.anyMpBlocks; A.checkOrientation = J.checkOrientation;
+    } else if (kind == RESOLVE_INIT) {
+      InitArgs& A = iargs[j];
+      CK(up(o.kps1, J.F1->keypoints, (size_t)nq * sizeof(orbx_keypoint)));
+      CK(up(o.prevMatched, J.prevMatched, (size_t)nq * 8));
+      A.kps1 = at<orbx_keypoint>(m, o.kps1); A.prevMatched = at<float>(m, o.prevMatched); A.matches12 = at<int>(m, o.m12);
+      A.matches21 = at<int>(m, o.m21); A.matchedDist = at<int>(m, o.mdist); A.bins = at<int>(m, o.bins);
+      A.nmatches = at<int>(m, o.nmatches); A.nnratio = J.nnratio; A.checkOrientation = J.checkOrientation;
+    }
+  }
+  CK(cudaMemcpyAsync(m->arena + oFrames, frames.data(), nj * sizeof(GridFrame), cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(m->arena + oSets, sets.data(), nj * sizeof(QuerySet), cudaMemcpyHostToDevice, st));
+  if (kind == RESOLVE_INIT) CK(cudaMemcpyAsync(m->arena + oArgs, iargs.data(), nj * sizeof(InitArgs), cudaMemcpyHostToDevice, st));
+  else CK(cudaMemcpyAsync(m->arena + oArgs, rargs.data(), nj * sizeof(ResolveArgs), cudaMemcpyHostToDevice, st));
+  CK(cudaMemsetAsync(m->dStatus, 0, sizeof(int), st));
+  const GridFrame* dFrames = at<GridFrame>(m, oFrames);
+  const QuerySet* dSets = at<QuerySet>(m, oSets);
+  k_build_grid<<<nj, 256, 0, st>>>(dFrames);
+  if (maxQ > 0) k_window_candidates<<<dim3((maxQ + 7) / 8, nj), 256, 0, st>>>(dFrames, dSets, m->dStatus);
+  if (kind == RESOLVE_MAPPOINTS) k_resolve_mappoints<<<nj, 32, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs));
+  else if (kind == RESOLVE_WINDOW) k_resolve_window<<<nj, 32, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs));
+  else if (kind == RESOLVE_INIT) k_resolve_init<<<nj, 32, 0, st>>>(dFrames, dSets, at<InitArgs>(m, oArgs));
+  CK(cudaGetLastError());
+  // ---- results
+  int status = 0;
+  CK(cudaMemcpyAsync(&status, m->dStatus, sizeof(int), cudaMemcpyDeviceToHost, st));
+  for (int j = 0; j < nj; j++) {
+    WindowJob& J = jobs[j];
+    const Off& o = off[j];
+    if (kind == RESOLVE_MAPPOINTS || kind == RESOLVE_WINDOW) {
+      CK(cudaMemcpyAsync(J.kpMp, m->arena + o.kpMp, (size_t)std::min(frames[j].n, J.kpMpLen) * 4, cudaMemcpyDeviceToHost, st));
+      CK(cudaMemcpyAsync(J.nmatches, m->arena + o.nmatches, 4, cudaMemcpyDeviceToHost, st));
+    } else if (kind == RESOLVE_INIT) {
+      CK(cudaMemcpyAsync(J.matches12, m->arena + o.m12, (size_t)J.q.nq * 4, cudaMemcpyDeviceToHost, st));
+      CK(cudaMemcpyAsync(J.prevMatched, m->arena + o.prevMatched, (size_t)J.q.nq * 8, cudaMemcpyDeviceToHost, st));
+      CK(cudaMemcpyAsync(J.nmatches, m->arena + o.nmatches, 4, cudaMemcpyDeviceToHost, st));
+    } else if (J.entriesOut) {
+      int cnt = 0;
+      CK(cudaMemcpyAsync(&cnt, m->arena + o.qCnt, 4, cudaMemcpyDeviceToHost, st));
+      CK(cudaStreamSynchronize(st));
+      J.entriesOut->resize(cnt);
+      if (cnt) CK(cudaMemcpyAsync(J.entriesOut->data(), m->arena + o.entries, (size_t)cnt * 8, cudaMemcpyDeviceToHost, st));
+    }
+  }
+  CK(cudaStreamSynchronize(st));
+  if (status != 0) { set_error("candidate list capacity exceeded"); return status; }
+  return ORBX_OK;
+}
+
+void set_bounds(WindowJob& J, const orbx_frame_view* F) { J.minX = F->min_x; J.minY = F->min_y; J.maxX = F->max_x; J.maxY = F->max_y; }
+
+// ORBmatcher.cc:52-73 + RadiusByViewingCos :216-222
+void prep_mappoint_queries(HostQueries& q, int nmp, const uint8_t* inView, const float* projX, const float* projY, const int* level,
+                           const float* viewCos, const uint8_t* mpDesc, const float* projXR, float th, const float* scaleFactors,
+                           int nlevels, bool haveRight) {
+  q.nq = nmp; q.valid.resize(nmp); q.x.resize(nmp); q.y.resize(nmp); q.r.resize(nmp); q.minL.resize(nmp); q.maxL.resize(nmp);
+  q.desc = mpDesc;
+  q.xrCheck = haveRight && projXR;
+  if (q.xrCheck) q.xr.assign(projXR, projXR + nmp);
+  const bool bFactor = th != 1.0;
+  for (int i = 0; i < nmp; i++) {
+    const int lvl = level[i];
+    const bool ok = inView[i] != 0 && lvl >= 0 && lvl < nlevels;
+    q.valid[i] = ok;
+    float r = (viewCos[i] > 0.998) ? 2.5f : 4.0f;
+    if (bFactor) r *= th;
+    q.x[i] = projX[i]; q.y[i] = projY[i];
+    q.r[i] = ok ? r * scaleFactors[lvl] : 0.f;
+    q.minL[i] = (int8_t)(lvl - 1); q.maxL[i] = (int8_t)lvl;
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbx_matcher_create(int device, orbx_matcher** out) {
+  if (!out) return ORBX_ERR_ARG;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+    set_error("orbx_matcher_create: no usable CUDA device %d (this library has no CPU fallback)", device);
+    return ORBX_ERR_CUDA;
+  }
+  CK(cudaSetDevice(device));
+  orbx_matcher* m = new orbx_matcher();
+  m->device = device;
+  if (cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess || cudaMalloc(&m->dStatus, sizeof(int)) != cudaSuccess) {
+    delete m; set_error("matcher resources"); return ORBX_ERR_CUDA;
+  }
+  *out = m;
+  return ORBX_OK;
+}
+
+void orbx_matcher_destroy(orbx_matcher* m) {
+  if (!m) return;
+  cudaSetDevice(m->device);
+  cudaStreamSynchronize(m->stream);
+  void* ptrs[] = {m->arena, m->dStatus, m->sURight, m->sDepth, m->sBestDist, m->sBestIdx, m->sSad};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  cudaStreamDestroy(m->stream);
+  delete m;
+}
+
+int orbx_hamming_batch(orbx_matcher* m, const uint8_t* a, const uint8_t* b, int n, int* dist) {
+  if (!m || n < 0 || (n > 0 && (!a || !b || !dist))) return ORBX_ERR_ARG;
+  if (n == 0) return ORBX_OK;
+  CK(cudaSetDevice(m->device));
+  ArenaPlan plan;
+  const size_t oa = plan.add((size_t)n * 32), ob = plan.add((size_t)n * 32), od = plan.add((size_t)n * 4);
+  int rc = arena_ensure(m, plan.total);
+  if (rc != ORBX_OK) return rc;
+  CK(cudaMemcpyAsync(m->arena + oa, a, (size_t)n * 32, cudaMemcpyHostToDevice, m->stream));
+  CK(cudaMemcpyAsync(m->arena + ob, b, (size_t)n * 32, cudaMemcpyHostToDevice, m->stream));
+  k_hamming_pairs<<<(n + 255) / 256, 256, 0, m->stream>>>(m->arena + oa, m->arena + ob, n, at<int>(m, od));
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(dist, m->arena + od, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
+  CK(cudaStreamSynchronize(m->stream));
+  return ORBX_OK;
+}
+
+int orbx_features_in_area(orbx_matcher* m, const orbx_frame_view* F, float x, float y, float r, int minLevel, int maxLevel, int* indices,
+                          int capacity, int* n) {
+  if (!m || !n) return ORBX_ERR_ARG;
+  int rc = check_view(F, false);
+  if (rc != ORBX_OK) return rc;
+  std::vector<WindowJob> jobs(1);
+  WindowJob& J = jobs[0];
+  J.F = F; set_bounds(J, F);
+  static const uint8_t zeros[32] = {0};
+  J.q.nq = 1; J.q.valid = {1}; J.q.x = {x}; J.q.y = {y}; J.q.r = {r};
+  J.q.minL = {(int8_t)std::max(-128, std::min(127, minLevel))}; J.q.maxL = {(int8_t)std::max(-128, std::min(127, maxLevel))};
+  J.q.desc = zeros;
+  std::vector<unsigned long long> entries;
+  J.entriesOut = &entries;
+  rc = run_window_jobs(m, jobs, RESOLVE_NONE);
+  if (rc != ORBX_OK) return rc;
+  // order of the reference's vIndices: grid column, grid row, insertion (= keypoint index)
+  std::sort(entries.begin(), entries.end(), [](unsigned long long a, unsigned long long b) { return (a & 0xfffffffffffull) < (b & 0xfffffffffffull); });
+  *n = (int)entries.size();
+  for (int i = 0; i < (int)entries.size() && i < capacity; i++) indices[i] = (int)((entries[i] >> 8) & 0xffffff);
+  return ORBX_OK;
+}
+
+int orbx_search_by_projection_mappoints(orbx_matcher* m, const orbx_frame_view* F, int nmp, const uint8_t* inView, const float* projX,
+                                        const float* projY, const int* level, const float* viewCos, const uint8_t* mpDesc,
+                                        const uint8_t* observed, const float* projXR, float th, float nnratio, int* kpMp, int* nmatches) {
+  if (!m || nmp < 0 || !kpMp || !nmatches || (nmp > 0 && (!inView || !projX || !projY || !level || !viewCos || !mpDesc))) return ORBX_ERR_ARG;
+  int rc = check_view(F, true);
+  if (rc != ORBX_OK) return rc;
+  std::vector<WindowJob> jobs(1);
+  WindowJob& J = jobs[0];
+  J.F = F; set_bounds(J, F);
+  prep_mappoint_queries(J.q, nmp, inView, projX, projY, level, viewCos, mpDesc, projXR, th, F->scale_factors, F->nlevels, F->u_right != nullptr);
+  J.observed = observed; J.kpMp = kpMp; J.kpMpLen = F->n; J.nnratio = nnratio; J.nmatches = nmatches;
+  return run_window_jobs(m, jobs, RESOLVE_MAPPOINTS);
+}
+
+int orbx_search_by_projection_mappoints_batch(orbx_matcher* m, orbx_extractor* ex, int nframes, int nmp, const uint8_t* inView,
+                                              const float* projX, const float* projY, const int* level, const float* viewCos,
+                                              const uint8_t* mpDesc, const uint8_t* observed, float th, float nnratio, int* kpMp,
+                                              int capPerFrame, int* nmatches) {
+  if (!m || !ex || !ex->haveGeom || nframes < 1 || nmp < 0 || !kpMp || !nmatches) return ORBX_ERR_ARG;
+  Slot& s = ex->slot[ex->lastSlot];
+  if (nframes > s.lastFrames) { set_error("extractor holds %d frames", s.lastFrames); return ORBX_ERR_ARG; }
+  CK(cudaSetDevice(m->device));
+  CK(cudaDeviceSynchronize());  // the extractor batch may still be in flight on another stream
+  std::vector<int> counts(nframes);
+  CK(cudaMemcpy(counts.data(), s.counts, nframes * sizeof(int), cudaMemcpyDeviceToHost));
+  std::vector<WindowJob> jobs(nframes);
+  for (int f = 0; f < nframes; f++) {
+    WindowJob& J = jobs[f];
+    if (counts[f] > capPerFrame || counts[f] > kMaxKpSmem) { set_error("frame %d: %d keypoints exceed the capacity", f, counts[f]); return ORBX_ERR_CAPACITY; }
+    J.devKps = s.kps + (size_t)f * ex->g.kpStride; J.devDesc = s.desc + (size_t)f * ex->g.kpStride * 32; J.devN = counts[f];
+    J.minX = 0.f; J.minY = 0.f; J.maxX = (float)ex->g.width; J.maxY = (float)ex->g.height;  // Frame.cc:894-897 (no distortion)
+    const size_t o = (size_t)f * nmp;
+    prep_mappoint_queries(J.q, nmp, inView + o, projX + o, projY + o, level + o, viewCos + o, mpDesc + o * 32, nullptr, th, ex->scale.data(),
+                          ex->p.nlevels, false);
+    J.observed = observed ? observed + o : nullptr;
+    J.kpMp = kpMp + (size_t)f * capPerFrame; J.kpMpLen = counts[f]; J.nnratio = nnratio; J.nmatches = nmatches + f;
+  }
+  return run_window_jobs(m, jobs, RESOLVE_MAPPOINTS);
+}
+
+int orbx_search_by_projection_window(orbx_matcher* m, const orbx_frame_view* F, int n, const uint8_t* valid, const float* u, const float* v,
+                                     const int* level, const float* ur, const float* angle, const uint8_t* srcDesc, const uint8_t* observed,
+                                     float th, int mode, int distTh, int anyMpBlocks, int checkOrientation, int* kpMp, int* nmatches) {
+  if (!m || n < 0 || !kpMp || !nmatches || (n > 0 && (!valid || !u || !v || !level || !srcDesc)) || (checkOrientation && n > 0 && !angle)) return ORBX_ERR_ARG;
+  int rc = check_view(F, true);
+  if (rc != ORBX_OK) return rc;
+  std::vector<WindowJob> jobs(1);
+  WindowJob& J = jobs[0];
+  J.F = F; set_bounds(J, F);
+  HostQueries& q = J.q;
+  q.nq = n; q.valid.resize(n); q.x.assign(u, u + n); q.y.assign(v, v + n); q.r.resize(n); q.minL.resize(n); q.maxL.resize(n);
+  q.desc = srcDesc;
+  q.xrCheck = ur != nullptr && F->u_right != nullptr;
+  if (q.xrCheck) q.xr.assign(ur, ur + n);
+  for (int i = 0; i < n; i++) {  // ORBmatcher.cc:2105-2118 / :2340-2342
+    const int l = level[i];
+    const bool ok = valid[i] != 0 && l >= 0 && l < F->nlevels;
+    q.valid[i] = ok;
+    q.r[i] = ok ? th * F->scale_factors[l] : 0.f;
+    if (mode == 1) { q.minL[i] = (int8_t)l; q.maxL[i] = -1; }
+    else if (mode == 2) { q.minL[i] = 0; q.maxL[i] = (int8_t)l; }
+    else { q.minL[i] = (int8_t)(l - 1); q.maxL[i] = (int8_t)(l + 1); }
+  }
+  J.observed = observed; J.angle = angle; J.kpMp = kpMp; J.kpMpLen = F->n; J.distTh = distTh; J.anyMpBlocks = anyMpBlocks;
+  J.checkOrientation = checkOrientation; J.nmatches = nmatches;
+  return run_window_jobs(m, jobs, RESOLVE_WINDOW);
+}
+
+int orbx_search_for_initialization(orbx_matcher* m, const orbx_frame_view* F1, const orbx_frame_view* F2, float* prevMatched, int windowSize,
+                                   float nnratio, int checkOrientation, int* matches12, int* nmatches) {
+  if (!m || !F1 || !prevMatched || !matches12 || !nmatches) return ORBX_ERR_ARG;
+  int rc = check_view(F2, false);
+  if (rc != ORBX_OK) return rc;
+  if (F1->n < 0 || (F1->n > 0 && (!F1->keypoints || !F1->descriptors))) return ORBX_ERR_ARG;
+  std::vector<WindowJob> jobs(1);
+  WindowJob& J = jobs[0];
+  J.F = F2; set_bounds(J, F2);
+  HostQueries& q = J.q;
+  const int n = F1->n;
+  q.nq = n; q.valid.resize(n); q.x.resize(n); q.y.resize(n); q.r.assign(n, (float)windowSize); q.minL.resize(n); q.maxL.resize(n);
+  q.desc = F1->descriptors;
+  for (int i = 0; i < n; i++) {  // ORBmatcher.cc:736-742
+    const int level1 = F1->keypoints[i].octave;
+    q.valid[i] = !(level1 > 0);
+    q.x[i] = prevMatched[2 * i]; q.y[i] = prevMatched[2 * i + 1];
+    q.minL[i] = (int8_t)level1; q.maxL[i] = (int8_t)level1;
+  }
+  J.F1 = F1; J.prevMatched = prevMatched; J.matches12 = matches12; J.nnratio = nnratio; J.checkOrientation = checkOrientation;
+  J.nmatches = nmatches;
+  return run_window_jobs(m, jobs, RESOLVE_INIT);
+}
+
+int orbx_knn2_chunk_device(orbx_matcher* m, const uint8_t* dQ, int nq, const uint8_t* dT, int nt, long long trainBase, const int* dExclude,
+                           unsigned long long* dKey0, unsigned long long* dKey1, int init, void* stream) {
+  if (!m || nq < 0 || nt < 0 || !dKey0 || !dKey1) return ORBX_ERR_ARG;
+  if (nq == 0) return ORBX_OK;
+  if (nt > (1 << 23)) { set_error("train chunk larger than 2^23 rows"); return ORBX_ERR_ARG; }
+  CK(cudaSetDevice(m->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : m->stream;
+  k_knn2<<<(nq + 127) / 128, 128, 0, st>>>(dQ, nq, dT, nt, trainBase, reinterpret_cast<const int2*>(dExclude), dKey0, dKey1, init);
+  CK(cudaGetLastError());
+  return ORBX_OK;
+}
+
+int orbx_knn2(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, int* idx, int* dist, uint8_t* good) {
+  if (!m || nq < 0 || nt < 0 || (nq > 0 && (!q || !idx || !dist)) || (nt > 0 && !t)) return ORBX_ERR_ARG;
+  if (nq == 0) return ORBX_OK;
+  CK(cudaSetDevice(m->device));
+  ArenaPlan plan;
+  const size_t oq = plan.add((size_t)nq * 32), ot = plan.add((size_t)std::max(nt, 1) * 32), k0 = plan.add((size_t)nq * 8), k1 = plan.add((size_t)nq * 8);
+  int rc = arena_ensure(m, plan.total);
+  if (rc != ORBX_OK) return rc;
+  cudaStream_t st = m->stream;
+  CK(cudaMemcpyAsync(m->arena + oq, q, (size_t)nq * 32, cudaMemcpyHostToDevice, st));
+  if (nt > 0) CK(cudaMemcpyAsync(m->arena + ot, t, (size_t)nt * 32, cudaMemcpyHostToDevice, st));
+  int init = 1;
+  if (nt == 0) CK(cudaMemsetAsync(m->arena + k0, 0xff, (size_t)nq * 16 + 256, st));
+  for (int base = 0; base < nt; base += (1 << 23)) {
+    const int n = std::min(1 << 23, nt - base);
+    rc = orbx_knn2_chunk_device(m, m->arena + oq, nq, m->arena + ot + (size_t)base * 32, n, base, nullptr, at<unsigned long long>(m, k0),
+                                at<unsigned long long>(m, k1), init, st);
+    if (rc != ORBX_OK) return rc;
+    init = 0;
+  }
+  std::vector<unsigned long long> h0(nq), h1(nq);
+  CK(cudaMemcpyAsync(h0.data(), m->arena + k0, (size_t)nq * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(h1.data(), m->arena + k1, (size_t)nq * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  for (int i = 0; i < nq; i++) {
+    const bool a = h0[i] != kKeyNone, b = h1[i] != kKeyNone;
+    idx[2 * i] = a ? (int)(h0[i] & 0xffffffffu) : -1; dist[2 * i] = a ? (int)(h0[i] >> 32) : -1;
+    idx[2 * i + 1] = b ? (int)(h1[i] & 0xffffffffu) : -1; dist[2 * i + 1] = b ? (int)(h1[i] >> 32) : -1;
+    if (good) good[i] = b && ((float)dist[2 * i] < (float)dist[2 * i + 1] * 0.7);  // Frame.cc:1253
+  }
+  return ORBX_OK;
+}
+
+int orbx_stereo_match_batch(orbx_matcher* m, orbx_extractor* exL, orbx_extractor* exR, float mb, float mbf, void* stream) {
+  if (!m || !exL || !exR || !exL->haveGeom || !exR->haveGeom) return ORBX_ERR_ARG;
+  Slot& sL = exL->slot[exL->lastSlot];
+  Slot& sR = exR->slot[exR->lastSlot];
+  const Geom& g = exL->g;
+  if (exR->g.width != g.width || exR->g.height != g.height || exR->g.nlevels != g.nlevels || exR->g.kpStride != g.kpStride ||
+      sL.lastFrames != sR.lastFrames || sL.lastFrames < 1 || exL->p.scale_factor != exR->p.scale_factor) {
+    set_error("left / right extractors must hold batches of the same geometry and size");
+    return ORBX_ERR_ARG;
+  }
+  if (g.kpStride > 65535) { set_error("more than 65535 keypoints per frame"); return ORBX_ERR_UNSUPPORTED; }
+  CK(cudaSetDevice(m->device));
+  const int nf = sL.lastFrames;
+  const size_t need = (size_t)nf * g.kpStride;
+  if (need > m->sCap) {
+    CK(cudaDeviceSynchronize());
+    void** ptrs[] = {(void**)&m->sURight, (void**)&m->sDepth, (void**)&m->sBestDist, (void**)&m->sBestIdx, (void**)&m->sSad};
+    for (void** p : ptrs) { if (*p) CK(cudaFree(*p)); *p = nullptr; CK(cudaMalloc(p, need * 4)); }
+    m->sCap = need;
+  }
+  m->sFrames = nf; m->sStride = g.kpStride;
+  cudaStream_t st = stream ? (cudaStream_t)stream : m->stream;
+  ScaleTab tab{};
+  for (int l = 0; l < g.nlevels; l++) { tab.scale[l] = exL->scale[l]; tab.invScale[l] = exL->invScale[l]; }
+  Geom gg = g;
+  const float maxD = mbf / mb;  // Frame.cc:931-933 (minZ = mb, minD = 0)
+  StereoOut out{m->sURight, m->sDepth, m->sBestDist, m->sBestIdx, m->sSad};
+  dim3 grid((g.kpStride + 7) / 8, nf);
+  k_stereo_hamming<<<grid, 256, 0, st>>>(gg, sL.last, sR.last, tab, maxD, out);
+  k_stereo_sad<<<grid, 256, 0, st>>>(gg, sL.last, sR.last, tab, maxD, mbf, out);
+  k_stereo_median<<<nf, 256, (size_t)g.kpStride * sizeof(int), st>>>(gg, sL.last, out);
+  CK(cudaGetLastError());
+  return ORBX_OK;
+}
+
+int orbx_stereo_results_device(orbx_matcher* m, const float** uRight, const float** depth, int* stride) {
+  if (!m || m->sFrames < 1) return ORBX_ERR_ARG;
+  if (uRight) *uRight = m->sURight;
+  if (depth) *depth = m->sDepth;
+  if (stride) *stride = m->sStride;
+  return ORBX_OK;
+}
+
+int orbx_stereo_results_host(orbx_matcher* m, float* uRight, float* depth, int* bestDist, int* bestIdx, int capPerFrame) {
+  if (!m || m->sFrames < 1 || capPerFrame < 1) return ORBX_ERR_ARG;
+  CK(cudaSetDevice(m->device));
+  CK(cudaDeviceSynchronize());
+  const size_t w = (size_t)std::min(capPerFrame, m->sStride) * 4;
+  struct { void* dst; const void* src; } c[] = {{uRight, m->sURight}, {depth, m->sDepth}, {bestDist, m->sBestDist}, {bestIdx, m->sBestIdx}};
+  for (auto& e : c)
+    if (e.dst) CK(cudaMemcpy2D(e.dst, (size_t)capPerFrame * 4, e.src, (size_t)m->sStride * 4, w, m->sFrames, cudaMemcpyDeviceToHost));
+  return ORBX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,162 @@
+"""ctypes mirror of the reference's ORBmatcher / Frame Hamming searches over the C-ABI (include/orbx.h, matcher section).
+
+    ORBmatcher(nnratio=0.6, checkOri=True)                    include/ORBmatcher.h:44
+    ORBmatcher.DescriptorDistance(a, b)                       src/ORBmatcher.cc:2463
+    ORBmatcher.SearchByProjection(F, mappoints, th)           src/ORBmatcher.cc:44     (map-point arrays instead of MapPoint*)
+    ORBmatcher.SearchByProjectionWindow(...)                  src/ORBmatcher.cc:2027 / :2291 (after the caller's projection)
+    ORBmatcher.SearchForInitialization(F1, F2, prev, win)     src/ORBmatcher.cc:722
+    FrameView.GetFeaturesInArea(x, y, r, minLevel, maxLevel)  src/Frame.cc:744
+    knn2 / stereo_match_batch                                 src/Frame.cc:1246 / :901
+
+A FrameView holds the members of Frame the searches read.  Everything runs in the CUDA kernels of csrc/match_kernels.cuh.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import KP_DTYPE, _check, _p, lib
+
+TH_HIGH, TH_LOW, HISTO_LENGTH = 100, 50, 30  # src/ORBmatcher.cc:36-38
+
+
+class _FrameViewC(C.Structure):
+    _fields_ = [("n", C.c_int), ("keypoints", C.c_void_p), ("descriptors", C.c_void_p), ("u_right", C.c_void_p),
+                ("scale_factors", C.c_void_p), ("nlevels", C.c_int), ("min_x", C.c_float), ("min_y", C.c_float),
+                ("max_x", C.c_float), ("max_y", C.c_float)]
+
+
+class FrameView:
+    """N, mvKeysUn, mDescriptors, mvuRight, mvScaleFactors, mnMinX.. of a Frame (include/Frame.h)."""
+
+    def __init__(self, keypoints, descriptors, scale_factors, width, height, u_right=None, bounds=None):
+        self.kps = np.ascontiguousarray(keypoints, KP_DTYPE)
+        self.desc = np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 32)
+        self.sf = np.ascontiguousarray(scale_factors, np.float32)
+        self.u_right = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+        b = bounds if bounds is not None else (0.0, 0.0, float(width), float(height))
+        self.c = _FrameViewC(len(self.kps), self.kps.ctypes.data, self.desc.ctypes.data,
+                             None if self.u_right is None else self.u_right.ctypes.data, self.sf.ctypes.data, len(self.sf),
+                             b[0], b[1], b[2], b[3])
+
+    @property
+    def N(self):
+        return len(self.kps)
+
+
+def _f32(a):
+    return None if a is None else np.ascontiguousarray(a, np.float32)
+
+
+def _u8(a):
+    return None if a is None else np.ascontiguousarray(a, np.uint8)
+
+
+def _i32(a):
+    return None if a is None else np.ascontiguousarray(a, np.int32)
+
+
+class ORBmatcher:
+    def __init__(self, nnratio=0.6, checkOri=True, device=0):
+        self.mfNNratio = float(nnratio)
+        self.mbCheckOrientation = bool(checkOri)
+        self._m = C.c_void_p()
+        _check(lib().orbx_matcher_create(device, C.byref(self._m)))
+
+    def close(self):
+        if getattr(self, "_m", None) and self._m.value:
+            lib().orbx_matcher_destroy(self._m)
+            self._m = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @staticmethod
+    def DescriptorDistance(a, b):
+        return lib().orbx_hamming(_p(_u8(a)), _p(_u8(b)))
+
+    def hamming_batch(self, a, b):
+        a, b = _u8(a).reshape(-1, 32), _u8(b).reshape(-1, 32)
+        out = np.empty(len(a), np.int32)
+        _check(lib().orbx_hamming_batch(self._m, _p(a), _p(b), len(a), _p(out)))
+        return out
+
+    def GetFeaturesInArea(self, F, x, y, r, minLevel=-1, maxLevel=-1):
+        out = np.empty(max(F.N, 1), np.int32)
+        n = C.c_int(0)
+        _check(lib().orbx_features_in_area(self._m, C.byref(F.c), C.c_float(x), C.c_float(y), C.c_float(r), minLevel, maxLevel,
+                                           _p(out), len(out), C.byref(n)))
+        return out[:n.value].copy()
+
+    def SearchByProjection(self, F, in_view, projX, projY, level, viewCos, mpDesc, th=1.0, kp_mp=None, observed=None, projXR=None):
+        """local-map search; returns (nmatches, kp_mp) with kp_mp[k] = index of the map point matched to keypoint k (or -1)"""
+        in_view, projX, projY, level, viewCos = _u8(in_view), _f32(projX), _f32(projY), _i32(level), _f32(viewCos)
+        mpDesc, observed, projXR = _u8(mpDesc), _u8(observed), _f32(projXR)
+        kp_mp = np.full(F.N, -1, np.int32) if kp_mp is None else _i32(kp_mp).copy()
+        nm = C.c_int(0)
+        _check(lib().orbx_search_by_projection_mappoints(self._m, C.byref(F.c), len(in_view), _p(in_view), _p(projX), _p(projY),
+                                                         _p(level), _p(viewCos), _p(mpDesc), _p(observed), _p(projXR),
+                                                         C.c_float(th), C.c_float(self.mfNNratio), _p(kp_mp), C.byref(nm)))
+        return nm.value, kp_mp
+
+    def SearchByProjectionBatch(self, extractor, nframes, in_view, projX, projY, level, viewCos, mpDesc, th=1.0, observed=None):
+        """map-point arrays are [nframes, nmp]; keypoints are the device-resident results of `extractor`'s last batch"""
+        in_view, projX, projY, level, viewCos = _u8(in_view), _f32(projX), _f32(projY), _i32(level), _f32(viewCos)
+        mpDesc, observed = _u8(mpDesc), _u8(observed)
+        nmp = in_view.shape[1]
+        h, w = extractor._last_shape
+        cap = extractor.max_keypoints(w, h)
+        kp_mp = np.full((nframes, cap), -1, np.int32)
+        nm = np.zeros(nframes, np.int32)
+        _check(lib().orbx_search_by_projection_mappoints_batch(self._m, extractor._h, nframes, nmp, _p(in_view), _p(projX), _p(projY),
+                                                               _p(level), _p(viewCos), _p(mpDesc), _p(observed), C.c_float(th),
+                                                               C.c_float(self.mfNNratio), _p(kp_mp), cap, _p(nm)))
+        return nm, kp_mp
+
+    def SearchByProjectionWindow(self, F, valid, u, v, level, angle, srcDesc, th, mode=0, dist_th=TH_HIGH, any_mp_blocks=False,
+                                 kp_mp=None, observed=None, ur=None):
+        valid, u, v, level, angle = _u8(valid), _f32(u), _f32(v), _i32(level), _f32(angle)
+        srcDesc, observed, ur = _u8(srcDesc), _u8(observed), _f32(ur)
+        kp_mp = np.full(F.N, -1, np.int32) if kp_mp is None else _i32(kp_mp).copy()
+        nm = C.c_int(0)
+        _check(lib().orbx_search_by_projection_window(self._m, C.byref(F.c), len(valid), _p(valid), _p(u), _p(v), _p(level), _p(ur),
+                                                      _p(angle), _p(srcDesc), _p(observed), C.c_float(th), int(mode), int(dist_th),
+                                                      int(any_mp_blocks), int(self.mbCheckOrientation), _p(kp_mp), C.byref(nm)))
+        return nm.value, kp_mp
+
+    def SearchForInitialization(self, F1, F2, vbPrevMatched, windowSize=10):
+        pm = _f32(vbPrevMatched).reshape(-1, 2).copy()
+        m12 = np.empty(F1.N, np.int32)
+        nm = C.c_int(0)
+        _check(lib().orbx_search_for_initialization(self._m, C.byref(F1.c), C.byref(F2.c), _p(pm), int(windowSize),
+                                                    C.c_float(self.mfNNratio), int(self.mbCheckOrientation), _p(m12), C.byref(nm)))
+        return nm.value, m12, pm
+
+    def knn2(self, q, t):
+        """BFMatcher(NORM_HAMMING).knnMatch(k=2) + the 0.7 ratio flag of Frame.cc:1253 -> (idx[nq,2], dist[nq,2], good[nq])"""
+        q, t = _u8(q).reshape(-1, 32), _u8(t).reshape(-1, 32)
+        idx = np.empty((len(q), 2), np.int32)
+        dist = np.empty((len(q), 2), np.int32)
+        good = np.empty(len(q), np.uint8)
+        _check(lib().orbx_knn2(self._m, _p(q), len(q), _p(t), len(t), _p(idx), _p(dist), _p(good)))
+        return idx, dist, good
+
+    def knn2_chunk_device(self, d_q, nq, d_t, nt, train_base, d_exclude, d_key0, d_key1, init, stream=0):
+        _check(lib().orbx_knn2_chunk_device(self._m, C.c_void_p(d_q), nq, C.c_void_p(d_t), nt, C.c_longlong(train_base),
+                                            C.c_void_p(d_exclude), C.c_void_p(d_key0), C.c_void_p(d_key1), int(init),
+                                            C.c_void_p(stream)))
+
+    def stereo_match_batch(self, exL, exR, mb, mbf, stream=0):
+        """Frame::ComputeStereoMatches for every pair of the two extractors' last batches (asynchronous)"""
+        _check(lib().orbx_stereo_match_batch(self._m, exL._h, exR._h, C.c_float(mb), C.c_float(mbf), C.c_void_p(stream)))
+        self._stereo_shape = exL._last_shape
+        self._stereo_cap = exL.max_keypoints(exL._last_shape[1], exL._last_shape[0])
+
+    def stereo_results(self, nframes):
+        cap = self._stereo_cap
+        uR = np.empty((nframes, cap), np.float32); depth = np.empty((nframes, cap), np.float32)
+        bd = np.empty((nframes, cap), np.int32); bi = np.empty((nframes, cap), np.int32)
+        _check(lib().orbx_stereo_results_host(self._m, _p(uR), _p(depth), _p(bd), _p(bi), cap))
+        return uR, depth, bd, bi

@@ -128,6 +128,89 @@ int orbx_debug_blurred_level(orbx_extractor* h, int frame, int level, uint8_t* d
 /* ORBmatcher::DescriptorDistance, src/ORBmatcher.cc:2463-2483 (host, 2 x 32 bytes). */
 int orbx_hamming(const uint8_t* a, const uint8_t* b);
 
+/* A matcher handle owns a stream and growable device workspaces.  Like ORBmatcher objects (stack objects at every call
+ * site, used concurrently from Tracking / LocalMapping / LoopClosing) handles are independent; one handle is not re-entrant. */
+typedef struct orbx_matcher orbx_matcher;
+int orbx_matcher_create(int device, orbx_matcher** out);
+void orbx_matcher_destroy(orbx_matcher* m);
+
+/* The members of Frame the searches read (src/Frame.cc, include/Frame.h): N, mvKeysUn, mDescriptors, mvuRight (NULL for
+ * monocular), mvScaleFactors, mnMinX/mnMinY/mnMaxX/mnMaxY.  The 64x48 grid (Frame::AssignFeaturesToGrid, Frame.cc:434-465)
+ * is rebuilt on the device from these on every call. */
+typedef struct orbx_frame_view {
+  int n;
+  const orbx_keypoint* keypoints;
+  const uint8_t* descriptors;
+  const float* u_right;
+  const float* scale_factors;
+  int nlevels;
+  float min_x, min_y, max_x, max_y;
+} orbx_frame_view;
+
+/* n x DescriptorDistance(a[i], b[i]) on the device (host arrays in/out). */
+int orbx_hamming_batch(orbx_matcher* m, const uint8_t* a, const uint8_t* b, int n, int* dist);
+
+/* Frame::GetFeaturesInArea(x, y, r, minLevel, maxLevel), src/Frame.cc:744-813: indices in the reference's order
+ * (grid column, grid row, insertion order).  *n = number found (may exceed capacity; only capacity are written). */
+int orbx_features_in_area(orbx_matcher* m, const orbx_frame_view* F, float x, float y, float r, int min_level, int max_level,
+                          int* indices, int capacity, int* n);
+
+/* ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th, ...), src/ORBmatcher.cc:44-142 (the mbTrackInView /
+ * Nleft == -1 branch).  Per map point i: in_view[i] = mbTrackInView && !isBad() && !(bFarPoints && far); proj_x/proj_y =
+ * mTrackProjX/Y; level = mnTrackScaleLevel; view_cos = mTrackViewCos; mp_desc = GetDescriptor() (32 B); observed[i] =
+ * Observations() > 0 (NULL: all observed); proj_xr = mTrackProjXR (read only when F->u_right != NULL).  kp_mp is
+ * F.mvpMapPoints as indices, in/out: -1 none, -2 pre-existing map point with observations (blocks), -3 pre-existing
+ * without observations; matched keypoints receive the map-point index.  *nmatches = the reference's return value. */
+int orbx_search_by_projection_mappoints(orbx_matcher* m, const orbx_frame_view* F, int nmp, const uint8_t* in_view,
+                                        const float* proj_x, const float* proj_y, const int* level, const float* view_cos,
+                                        const uint8_t* mp_desc, const uint8_t* observed, const float* proj_xr, float th,
+                                        float nnratio, int* kp_mp, int* nmatches);
+/* The same search for `nframes` frames whose keypoints/descriptors are the device-resident results of the last batch of
+ * extractor `ex` (mvKeysUn == mvKeys, bounds = the image): per-frame map-point arrays are [nframes][nmp] host arrays,
+ * kp_mp is [nframes][capacity_per_frame] (in/out), nmatches [nframes]. */
+int orbx_search_by_projection_mappoints_batch(orbx_matcher* m, orbx_extractor* ex, int nframes, int nmp, const uint8_t* in_view,
+                                              const float* proj_x, const float* proj_y, const int* level, const float* view_cos,
+                                              const uint8_t* mp_desc, const uint8_t* observed, float th, float nnratio,
+                                              int* kp_mp, int capacity_per_frame, int* nmatches);
+
+/* Window best-match search shared by ORBmatcher::SearchByProjection(Frame& Cur, const Frame& Last, th, bMono)
+ * (src/ORBmatcher.cc:2027-2289; mode 0 = levels [l-1,l+1], 1 = forward [l,inf), 2 = backward [0,l]; dist_th = TH_HIGH) and
+ * SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:2291-2413; mode 0, any_mp_blocks = 1,
+ * dist_th = ORBdist).  The caller projects the points (pose algebra and camera model stay on the host, as in the
+ * reference's loop prologue): valid[i] = point exists, is not an outlier / not already found, invzc >= 0 and projects
+ * inside the image bounds; u,v = projection; level = nLastOctave / predicted level; ur = uv.x - mbf*invzc (read only when
+ * F->u_right != NULL, may be NULL); angle = source keypoint angle.  Rotation-consistency filtering (30-bin histogram, three
+ * maxima, src/ORBmatcher.cc:2416-2458) is applied when check_orientation != 0. */
+int orbx_search_by_projection_window(orbx_matcher* m, const orbx_frame_view* F, int n, const uint8_t* valid, const float* u,
+                                     const float* v, const int* level, const float* ur, const float* angle,
+                                     const uint8_t* src_desc, const uint8_t* observed, float th, int mode, int dist_th,
+                                     int any_mp_blocks, int check_orientation, int* kp_mp, int* nmatches);
+
+/* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize), src/ORBmatcher.cc:722-837.
+ * prev_matched: F1->n x 2 floats (in/out), matches12: F1->n ints (out). */
+int orbx_search_for_initialization(orbx_matcher* m, const orbx_frame_view* F1, const orbx_frame_view* F2, float* prev_matched,
+                                   int window_size, float nnratio, int check_orientation, int* matches12, int* nmatches);
+
+/* cv::BFMatcher(NORM_HAMMING).knnMatch(query, train, k = 2) as used by Frame::ComputeStereoFishEyeMatches
+ * (src/Frame.cc:1246): idx/dist are nq x 2 (-1 where fewer than two train rows exist), ascending distance, lower train
+ * index first on ties.  good (optional, nq bytes) = Lowe test of src/Frame.cc:1253 (two neighbours and d0 < 0.7*d1). */
+int orbx_knn2(orbx_matcher* m, const uint8_t* query, int nq, const uint8_t* train, int nt, int* idx, int* dist, uint8_t* good);
+/* Device building block of the all-pairs keyframe sweep: folds one train chunk (global index of its first row =
+ * train_base) into the running best / second-best keys (dist << 32 | global index; init != 0 resets them).  d_exclude
+ * (optional, nq x int2) = global train range to skip per query (its own keyframe).  Asynchronous on `stream`. */
+int orbx_knn2_chunk_device(orbx_matcher* m, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt, long long train_base,
+                           const int* d_exclude, unsigned long long* d_key0, unsigned long long* d_key1, int init, void* stream);
+
+/* Frame::ComputeStereoMatches, src/Frame.cc:901-1079, for every frame of the last batches of two extractor handles
+ * (left / right image of each pair; same geometry and frame count; keypoints, descriptors and un-blurred pyramids are read
+ * where they lie in HBM, exactly the members the reference reads at Frame.cc:908,998,1012).  mb / mbf as in Frame.
+ * Asynchronous on `stream` (NULL = the matcher's stream).  Results: per left keypoint mvuRight / mvDepth (-1 = no match). */
+int orbx_stereo_match_batch(orbx_matcher* m, orbx_extractor* left, orbx_extractor* right, float mb, float mbf, void* stream);
+int orbx_stereo_results_device(orbx_matcher* m, const float** d_u_right, const float** d_depth, int* stride);
+/* Host copy (synchronises): [nframes][capacity_per_frame]; best_dist / best_idx expose the Hamming stage (may be NULL). */
+int orbx_stereo_results_host(orbx_matcher* m, float* u_right, float* depth, int* best_dist, int* best_idx,
+                             int capacity_per_frame);
+
 const char* orbx_last_error(void);
 const char* orbx_version(void);
 
