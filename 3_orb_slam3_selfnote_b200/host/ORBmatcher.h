@@ -1,0 +1,149 @@
+// Drop-in counterpart of the reference's include/ORBmatcher.h (class ORB_SLAM3::ORBmatcher, lines 39-107): constructor,
+// the three constants, static DescriptorDistance and the data-parallel search entry points, computed on the GPU through
+// the C-ABI of include/orbx.h.  The search methods are templates over the frame / map-point types and read exactly the
+// members the reference's bodies read (F.N, F.mvKeysUn, F.mDescriptors, F.mvuRight, F.mvScaleFactors, F.mnMinX.., F.Nleft,
+// F.mvpMapPoints, pMP->mbTrackInView, ...), so they bind to the reference's own Frame / MapPoint classes unchanged and to
+// the small mocks of tests/cpp/shim_test.cc alike.  Pose algebra / camera projection (the loop prologues of the
+// Frame-Frame and Frame-KeyFrame overloads) stay on the host: see SearchByProjectionProjected and INTEGRATION.md.
+#pragma once
+#include <climits>
+#include <stdexcept>
+#include <vector>
+
+#include "../../include/orbx.h"
+#include "ORBextractor.h"
+#include "cvlite.h"
+
+namespace ORB_SLAM3 {
+
+class ORBmatcher {
+ public:
+  static const int TH_LOW = 50;        // src/ORBmatcher.cc:37
+  static const int TH_HIGH = 100;      // src/ORBmatcher.cc:36
+  static const int HISTO_LENGTH = 30;  // src/ORBmatcher.cc:38
+
+  ORBmatcher(float nnratio = 0.6, bool checkOri = true, int device = 0) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {
+    orbx_shim::check(orbx_matcher_create(device, &m_), "orbx_matcher_create");
+  }
+  ~ORBmatcher() { orbx_matcher_destroy(m_); }
+  ORBmatcher(const ORBmatcher&) = delete;
+  ORBmatcher& operator=(const ORBmatcher&) = delete;
+
+  // Computes the Hamming distance between two ORB descriptors (src/ORBmatcher.cc:2463-2483)
+  static int DescriptorDistance(const cvx::Mat& a, const cvx::Mat& b) { return orbx_hamming(a.ptr(0), b.ptr(0)); }
+
+  // Search matches between Frame keypoints and projected MapPoints (local-map tracking), src/ORBmatcher.cc:44-142.
+  // Monocular / rectified-stereo frames (F.Nleft == -1); the fisheye-stereo right-camera pass (:144-211) is not offloaded.
+  template <class FrameT, class MapPointT>
+  int SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, const float th = 3, const bool bFarPoints = false,
+                         const float thFarPoints = 50.0f) {
+    if (F.Nleft != -1) throw std::runtime_error("ORBmatcher::SearchByProjection: fisheye stereo (Nleft != -1) is not offloaded");
+    const int nmp = (int)vpMapPoints.size();
+    std::vector<uint8_t> inView(nmp), observed(nmp), desc((size_t)nmp * 32);
+    std::vector<float> px(nmp), py(nmp), vc(nmp), pxr(nmp);
+    std::vector<int> lvl(nmp);
+    for (int i = 0; i < nmp; i++) {  // the gating of src/ORBmatcher.cc:52-62
+      MapPointT* pMP = vpMapPoints[i];
+      bool ok = pMP->mbTrackInView;
+      if (ok && bFarPoints && pMP->mTrackDepth > thFarPoints) ok = false;
+      if (ok && pMP->isBad()) ok = false;
+      inView[i] = ok;
+      if (!ok) continue;
+      px[i] = pMP->mTrackProjX; py[i] = pMP->mTrackProjY; pxr[i] = pMP->mTrackProjXR;
+      lvl[i] = pMP->mnTrackScaleLevel; vc[i] = pMP->mTrackViewCos;
+      observed[i] = pMP->Observations() > 0;
+      const cvx::Mat d = pMP->GetDescriptor();
+      memcpy(&desc[(size_t)i * 32], d.ptr(0), 32);
+    }
+    FrameViewHolder fv(F);
+    std::vector<int> kpMp(F.N);
+    std::vector<MapPointT*> pre(F.mvpMapPoints.begin(), F.mvpMapPoints.end());
+    for (int k = 0; k < F.N; k++) kpMp[k] = !pre[k] ? -1 : (pre[k]->Observations() > 0 ? -2 : -3);
+    int nmatches = 0;
+    orbx_shim::check(orbx_search_by_projection_mappoints(m_, &fv.v, nmp, inView.data(), px.data(), py.data(), lvl.data(), vc.data(), desc.data(),
+                                                         observed.data(), pxr.data(), th, mfNNratio, kpMp.data(), &nmatches),
+                     "orbx_search_by_projection_mappoints");
+    for (int k = 0; k < F.N; k++)
+      if (kpMp[k] >= 0) F.mvpMapPoints[k] = vpMapPoints[kpMp[k]];
+    return nmatches;
+  }
+
+  // Matching for the Map Initialization (only used in the monocular case), src/ORBmatcher.cc:722-837.
+  template <class FrameT>
+  int SearchForInitialization(FrameT& F1, FrameT& F2, std::vector<cvx::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12,
+                              int windowSize = 10) {
+    FrameViewHolder a(F1), b(F2);
+    vnMatches12.assign(F1.mvKeysUn.size(), -1);
+    int nmatches = 0;
+    static_assert(sizeof(cvx::Point2f) == 8, "Point2f layout");
+    orbx_shim::check(orbx_search_for_initialization(m_, &a.v, &b.v, reinterpret_cast<float*>(vbPrevMatched.data()), windowSize, mfNNratio,
+                                                    mbCheckOrientation ? 1 : 0, vnMatches12.data(), &nmatches),
+                     "orbx_search_for_initialization");
+    return nmatches;
+  }
+
+  // The search loop shared by SearchByProjection(Frame& Cur, const Frame& Last, th, bMono) (src/ORBmatcher.cc:2027-2289) and
+  // SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) (:2291-2413) once the caller has projected the points
+  // (valid / u / v / level / ur / angle / descriptors per source point; see include/orbx.h).  kpMp: -1 none, -2 blocking, -3 not.
+  template <class FrameT>
+  int SearchByProjectionProjected(FrameT& F, const std::vector<uint8_t>& valid, const std::vector<float>& u, const std::vector<float>& v,
+                                  const std::vector<int>& level, const std::vector<float>* ur, const std::vector<float>& angle,
+                                  const std::vector<uint8_t>& srcDesc, const std::vector<uint8_t>* observed, float th, int mode, int distTh,
+                                  bool anyMpBlocks, std::vector<int>& kpMp) {
+    FrameViewHolder fv(F);
+    int nmatches = 0;
+    orbx_shim::check(orbx_search_by_projection_window(m_, &fv.v, (int)valid.size(), valid.data(), u.data(), v.data(), level.data(),
+                                                      ur ? ur->data() : nullptr, angle.data(), srcDesc.data(), observed ? observed->data() : nullptr,
+                                                      th, mode, distTh, anyMpBlocks ? 1 : 0, mbCheckOrientation ? 1 : 0, kpMp.data(), &nmatches),
+                     "orbx_search_by_projection_window");
+    return nmatches;
+  }
+
+  // Frame::ComputeStereoMatches (src/Frame.cc:901-1079) for a frame whose two extractors have just run: fills F.mvuRight / F.mvDepth.
+  template <class FrameT>
+  void ComputeStereoMatches(FrameT& F, ORBextractor& left, ORBextractor& right) {
+    orbx_shim::check(orbx_stereo_match_batch(m_, left.handle(), right.handle(), F.mb, F.mbf, nullptr), "orbx_stereo_match_batch");
+    const int cap = std::max(F.N, 1);
+    F.mvuRight.assign(F.N, -1.0f);
+    F.mvDepth.assign(F.N, -1.0f);
+    orbx_shim::check(orbx_stereo_results_host(m_, F.mvuRight.data(), F.mvDepth.data(), nullptr, nullptr, cap), "orbx_stereo_results_host");
+  }
+
+  // The brute-force 2-NN + Lowe ratio of Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1246-1253); triangulation stays on the host.
+  void KnnMatch2(const cvx::Mat& query, const cvx::Mat& train, std::vector<int>& idx, std::vector<int>& dist, std::vector<uint8_t>& good) {
+    idx.assign((size_t)query.rows * 2, -1); dist.assign((size_t)query.rows * 2, -1); good.assign(query.rows, 0);
+    std::vector<uint8_t> q((size_t)query.rows * 32), t((size_t)train.rows * 32);
+    for (int i = 0; i < query.rows; i++) memcpy(&q[(size_t)i * 32], query.ptr(i), 32);
+    for (int i = 0; i < train.rows; i++) memcpy(&t[(size_t)i * 32], train.ptr(i), 32);
+    orbx_shim::check(orbx_knn2(m_, q.data(), query.rows, t.data(), train.rows, idx.data(), dist.data(), good.data()), "orbx_knn2");
+  }
+
+ protected:
+  float mfNNratio;
+  bool mbCheckOrientation;
+
+ private:
+  // gathers the Frame members of include/orbx.h's orbx_frame_view (descriptors are copied only if the Mat is not dense)
+  struct FrameViewHolder {
+    orbx_frame_view v;
+    std::vector<uint8_t> dense;
+    template <class FrameT>
+    explicit FrameViewHolder(FrameT& F) {
+      v.n = (int)F.mvKeysUn.size();
+      v.keypoints = reinterpret_cast<const orbx_keypoint*>(F.mvKeysUn.data());
+      if (F.mDescriptors.step == 32 || v.n == 0) v.descriptors = F.mDescriptors.ptr(0);
+      else {
+        dense.resize((size_t)v.n * 32);
+        for (int i = 0; i < v.n; i++) memcpy(&dense[(size_t)i * 32], F.mDescriptors.ptr(i), 32);
+        v.descriptors = dense.data();
+      }
+      v.u_right = (F.mvuRight.size() == (size_t)v.n && v.n > 0) ? F.mvuRight.data() : nullptr;
+      v.scale_factors = F.mvScaleFactors.data();
+      v.nlevels = (int)F.mvScaleFactors.size();
+      v.min_x = F.mnMinX; v.min_y = F.mnMinY; v.max_x = F.mnMaxX; v.max_y = F.mnMaxY;
+    }
+  };
+  orbx_matcher* m_ = nullptr;
+};
+
+}  // namespace ORB_SLAM3
