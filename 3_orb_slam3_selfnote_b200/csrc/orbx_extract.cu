@@ -74,7 +74,7 @@ int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
 
   std::vector<RsX> rsx; std::vector<RsY> rsy; std::vector<uint16_t> info;
   int pyrOff = 0, blurOff = 0, cellBase = 0, candOff = 0, kpOff = 0, tileBase = 0, blurTileBase = 0, maxNodeCap = 0;
-  h->inPitch = round_up(width, 64);
+  h->inPitch = round_up(width, 4);  // dense when width % 4 == 0: host frames then upload as one linear copy
   for (int l = 0; l < nl; l++) {
     LevelGeom& L = g.lv[l];
     // level size, src/ORBextractor.cc:1192-1193
@@ -449,7 +449,9 @@ int orbx_extract_batch_host(orbx_extractor* h, const uint8_t* images, int nframe
     cudaStream_t st = s.stream;
     // (the slot's previous chunk was enqueued on the same stream, so its D2H copies finish before these buffers are reused)
     const uint8_t* src = images + (size_t)f0 * frameStride;
-    if (frameStride == (size_t)stride * height) {
+    if (frameStride == (size_t)stride * height && stride == h->inPitch) {
+      CK(cudaMemcpyAsync(s.in, src, (size_t)stride * height * nb, cudaMemcpyHostToDevice, st));
+    } else if (frameStride == (size_t)stride * height) {
       CK(cudaMemcpy2DAsync(s.in, h->inPitch, src, stride, width, (size_t)height * nb, cudaMemcpyHostToDevice, st));
     } else {
       for (int f = 0; f < nb; f++)

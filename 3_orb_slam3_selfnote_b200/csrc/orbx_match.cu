@@ -20,8 +20,8 @@ struct orbx_matcher {
   int* dStatus = nullptr;
   // stereo results of the last orbx_stereo_match_batch
   float* sURight = nullptr; float* sDepth = nullptr; int* sBestDist = nullptr; int* sBestIdx = nullptr; int* sSad = nullptr;
-  size_t sCap = 0;
-  int sFrames = 0, sStride = 0;
+  size_t sCap = 0, sHalf = 0;
+  int sFrames = 0, sStride = 0, sLast = 0;
 };
 
 namespace {
@@ -463,10 +463,10 @@ int orbx_knn2(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int n
   return ORBX_OK;
 }
 
-int orbx_stereo_match_batch(orbx_matcher* m, orbx_extractor* exL, orbx_extractor* exR, float mb, float mbf, void* stream) {
-  if (!m || !exL || !exR || !exL->haveGeom || !exR->haveGeom) return ORBX_ERR_ARG;
-  Slot& sL = exL->slot[exL->lastSlot];
-  Slot& sR = exR->slot[exR->lastSlot];
+// Enqueue ComputeStereoMatches for the batches held by slot `si` of both extractors; results go to half `si` of the matcher's buffers.
+static int stereo_launch(orbx_matcher* m, orbx_extractor* exL, orbx_extractor* exR, int si, float mb, float mbf, cudaStream_t st) {
+  Slot& sL = exL->slot[si];
+  Slot& sR = exR->slot[si];
   const Geom& g = exL->g;
   if (exR->g.width != g.width || exR->g.height != g.height || exR->g.nlevels != g.nlevels || exR->g.kpStride != g.kpStride ||
       sL.lastFrames != sR.lastFrames || sL.lastFrames < 1 || exL->p.scale_factor != exR->p.scale_factor) {
@@ -474,22 +474,21 @@ int orbx_stereo_match_batch(orbx_matcher* m, orbx_extractor* exL, orbx_extractor
     return ORBX_ERR_ARG;
   }
   if (g.kpStride > 65535) { set_error("more than 65535 keypoints per frame"); return ORBX_ERR_UNSUPPORTED; }
-  CK(cudaSetDevice(m->device));
   const int nf = sL.lastFrames;
-  const size_t need = (size_t)nf * g.kpStride;
-  if (need > m->sCap) {
+  const size_t half = (size_t)std::max(exL->p.max_batch, exR->p.max_batch) * g.kpStride;
+  if (2 * half > m->sCap) {
     CK(cudaDeviceSynchronize());
     void** ptrs[] = {(void**)&m->sURight, (void**)&m->sDepth, (void**)&m->sBestDist, (void**)&m->sBestIdx, (void**)&m->sSad};
-    for (void** p : ptrs) { if (*p) CK(cudaFree(*p)); *p = nullptr; CK(cudaMalloc(p, need * 4)); }
-    m->sCap = need;
+    for (void** p : ptrs) { if (*p) CK(cudaFree(*p)); *p = nullptr; CK(cudaMalloc(p, 2 * half * 4)); }
+    m->sCap = 2 * half;
   }
-  m->sFrames = nf; m->sStride = g.kpStride;
-  cudaStream_t st = stream ? (cudaStream_t)stream : m->stream;
+  m->sFrames = nf; m->sStride = g.kpStride; m->sHalf = half; m->sLast = si;
   ScaleTab tab{};
   for (int l = 0; l < g.nlevels; l++) { tab.scale[l] = exL->scale[l]; tab.invScale[l] = exL->invScale[l]; }
   Geom gg = g;
   const float maxD = mbf / mb;  // Frame.cc:931-933 (minZ = mb, minD = 0)
-  StereoOut out{m->sURight, m->sDepth, m->sBestDist, m->sBestIdx, m->sSad};
+  const size_t o = (size_t)si * half;
+  StereoOut out{m->sURight + o, m->sDepth + o, m->sBestDist + o, m->sBestIdx + o, m->sSad + o};
   dim3 grid((g.kpStride + 7) / 8, nf);
   k_stereo_hamming<<<grid, 256, 0, st>>>(gg, sL.last, sR.last, tab, maxD, out);
   k_stereo_sad<<<grid, 256, 0, st>>>(gg, sL.last, sR.last, tab, maxD, mbf, out);
@@ -498,10 +497,82 @@ int orbx_stereo_match_batch(orbx_matcher* m, orbx_extractor* exL, orbx_extractor
   return ORBX_OK;
 }
 
+int orbx_stereo_match_batch(orbx_matcher* m, orbx_extractor* exL, orbx_extractor* exR, float mb, float mbf, void* stream) {
+  if (!m || !exL || !exR || !exL->haveGeom || !exR->haveGeom) return ORBX_ERR_ARG;
+  if (exL->lastSlot != exR->lastSlot) { set_error("left / right extractors last ran in different slots"); return ORBX_ERR_ARG; }
+  CK(cudaSetDevice(m->device));
+  return stereo_launch(m, exL, exR, exL->lastSlot, mb, mbf, stream ? (cudaStream_t)stream : m->stream);
+}
+
+// Whole stereo frames from host buffers: per chunk H2D(left,right) -> both extractions -> stereo matching -> D2H, double-buffered
+// over the two slots of the extractor handles so copies overlap kernels (the e2e form of Frame::Frame(stereo), src/Frame.cc:89-187).
+int orbx_stereo_frames_host(orbx_matcher* m, orbx_extractor* exL, orbx_extractor* exR, const uint8_t* imagesL, const uint8_t* imagesR,
+                            int nframes, int width, int height, int stride, size_t frameStride, float mb, float mbf, orbx_keypoint* kpsL,
+                            uint8_t* descL, int* countsL, orbx_keypoint* kpsR, uint8_t* descR, int* countsR, float* uRight, float* depth,
+                            int capPerFrame) {
+  if (!m || !exL || !exR) return ORBX_ERR_ARG;
+  if (!imagesL || !imagesR || width <= 0 || height <= 0 || nframes <= 0) return ORBX_EMPTY_IMAGE;
+  if (!kpsL || !descL || !countsL || !kpsR || !descR || !countsR || !uRight || !depth || capPerFrame <= 0 || stride < width) return ORBX_ERR_ARG;
+  int rc = extractor_build_geom(exL, width, height);
+  if (rc != ORBX_OK) return rc;
+  rc = extractor_build_geom(exR, width, height);
+  if (rc != ORBX_OK) return rc;
+  CK(cudaSetDevice(m->device));
+  const Geom& g = exL->g;
+  const int B = std::min(exL->p.max_batch, exR->p.max_batch);
+  const int ncopy = std::min(capPerFrame, g.kpStride);
+  const size_t kpRow = (size_t)g.kpStride * sizeof(orbx_keypoint), kpDst = (size_t)capPerFrame * sizeof(orbx_keypoint);
+  int chunk = 0;
+  for (int f0 = 0; f0 < nframes; f0 += B, chunk++) {
+    const int nb = std::min(B, nframes - f0), si = chunk & 1;
+    cudaStream_t st = exL->slot[si].stream;
+    orbx_extractor* ex[2] = {exL, exR};
+    const uint8_t* img[2] = {imagesL, imagesR};
+    for (int e = 0; e < 2; e++) {
+      Slot& s = ex[e]->slot[si];
+      const uint8_t* src = img[e] + (size_t)f0 * frameStride;
+      if (frameStride == (size_t)stride * height && stride == ex[e]->inPitch)
+        CK(cudaMemcpyAsync(s.in, src, (size_t)stride * height * nb, cudaMemcpyHostToDevice, st));
+      else if (frameStride == (size_t)stride * height)
+        CK(cudaMemcpy2DAsync(s.in, ex[e]->inPitch, src, stride, width, (size_t)height * nb, cudaMemcpyHostToDevice, st));
+      else
+        for (int f = 0; f < nb; f++)
+          CK(cudaMemcpy2DAsync(s.in + (size_t)f * ex[e]->inPitch * height, ex[e]->inPitch, src + (size_t)f * frameStride, stride, width,
+                               height, cudaMemcpyHostToDevice, st));
+      rc = extractor_run_batch(ex[e], si, s.in, nb, ex[e]->inPitch, (long long)ex[e]->inPitch * height, 0, 0, st);
+      if (rc != ORBX_OK) return rc;
+    }
+    rc = stereo_launch(m, exL, exR, si, mb, mbf, st);
+    if (rc != ORBX_OK) return rc;
+    orbx_keypoint* kd[2] = {kpsL, kpsR}; uint8_t* dd[2] = {descL, descR}; int* cd[2] = {countsL, countsR};
+    for (int e = 0; e < 2; e++) {
+      Slot& s = ex[e]->slot[si];
+      CK(cudaMemcpyAsync(cd[e] + f0, s.counts, nb * sizeof(int), cudaMemcpyDeviceToHost, st));
+      CK(cudaMemcpy2DAsync(kd[e] + (size_t)f0 * capPerFrame, kpDst, s.kps, kpRow, (size_t)ncopy * sizeof(orbx_keypoint), nb, cudaMemcpyDeviceToHost, st));
+      CK(cudaMemcpy2DAsync(dd[e] + (size_t)f0 * capPerFrame * 32, (size_t)capPerFrame * 32, s.desc, (size_t)g.kpStride * 32, (size_t)ncopy * 32, nb,
+                           cudaMemcpyDeviceToHost, st));
+      CK(cudaMemcpyAsync(s.hStatus, s.status, sizeof(int), cudaMemcpyDeviceToHost, st));
+    }
+    const size_t o = (size_t)si * m->sHalf;
+    CK(cudaMemcpy2DAsync(uRight + (size_t)f0 * capPerFrame, (size_t)capPerFrame * 4, m->sURight + o, (size_t)g.kpStride * 4, (size_t)ncopy * 4, nb,
+                         cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpy2DAsync(depth + (size_t)f0 * capPerFrame, (size_t)capPerFrame * 4, m->sDepth + o, (size_t)g.kpStride * 4, (size_t)ncopy * 4, nb,
+                         cudaMemcpyDeviceToHost, st));
+    if (chunk >= 1) CK(cudaStreamSynchronize(exL->slot[si ^ 1].stream));  // at most two chunks in flight
+  }
+  for (int si = 0; si < 2; si++) CK(cudaStreamSynchronize(exL->slot[si].stream));
+  for (int si = 0; si < 2; si++)
+    for (orbx_extractor* e : {exL, exR})
+      if (e->slot[si].lastFrames > 0 && *e->slot[si].hStatus != 0) { set_error("device reported status %d (capacity)", *e->slot[si].hStatus); return *e->slot[si].hStatus; }
+  for (int f = 0; f < nframes; f++)
+    if (countsL[f] > capPerFrame || countsR[f] > capPerFrame) { set_error("frame %d exceeds the output capacity", f); return ORBX_ERR_CAPACITY; }
+  return ORBX_OK;
+}
+
 int orbx_stereo_results_device(orbx_matcher* m, const float** uRight, const float** depth, int* stride) {
   if (!m || m->sFrames < 1) return ORBX_ERR_ARG;
-  if (uRight) *uRight = m->sURight;
-  if (depth) *depth = m->sDepth;
+  if (uRight) *uRight = m->sURight + (size_t)m->sLast * m->sHalf;
+  if (depth) *depth = m->sDepth + (size_t)m->sLast * m->sHalf;
   if (stride) *stride = m->sStride;
   return ORBX_OK;
 }
@@ -511,7 +582,8 @@ int orbx_stereo_results_host(orbx_matcher* m, float* uRight, float* depth, int* 
   CK(cudaSetDevice(m->device));
   CK(cudaDeviceSynchronize());
   const size_t w = (size_t)std::min(capPerFrame, m->sStride) * 4;
-  struct { void* dst; const void* src; } c[] = {{uRight, m->sURight}, {depth, m->sDepth}, {bestDist, m->sBestDist}, {bestIdx, m->sBestIdx}};
+  const size_t o = (size_t)m->sLast * m->sHalf;
+  struct { void* dst; const void* src; } c[] = {{uRight, m->sURight + o}, {depth, m->sDepth + o}, {bestDist, m->sBestDist + o}, {bestIdx, m->sBestIdx + o}};
   for (auto& e : c)
     if (e.dst) CK(cudaMemcpy2D(e.dst, (size_t)capPerFrame * 4, e.src, (size_t)m->sStride * 4, w, m->sFrames, cudaMemcpyDeviceToHost));
   return ORBX_OK;

@@ -207,6 +207,14 @@ int orbx_knn2_chunk_device(orbx_matcher* m, const uint8_t* d_query, int nq, cons
  * Asynchronous on `stream` (NULL = the matcher's stream).  Results: per left keypoint mvuRight / mvDepth (-1 = no match). */
 int orbx_stereo_match_batch(orbx_matcher* m, orbx_extractor* left, orbx_extractor* right, float mb, float mbf, void* stream);
 int orbx_stereo_results_device(orbx_matcher* m, const float** d_u_right, const float** d_depth, int* stride);
+/* Whole stereo frames from HOST buffers (the data-parallel part of Frame::Frame(stereo), src/Frame.cc:89-187): for each of
+ * `nframes` rectified pairs, both extractions (vLappingArea {0,0}, Frame.cc:120-121) and ComputeStereoMatches; uploads,
+ * kernels and downloads are chunked by max_batch and double-buffered.  Outputs per frame f at index f*capacity_per_frame. */
+int orbx_stereo_frames_host(orbx_matcher* m, orbx_extractor* left, orbx_extractor* right, const uint8_t* images_left,
+                            const uint8_t* images_right, int nframes, int width, int height, int stride, size_t frame_stride,
+                            float mb, float mbf, orbx_keypoint* keypoints_left, uint8_t* descriptors_left, int* counts_left,
+                            orbx_keypoint* keypoints_right, uint8_t* descriptors_right, int* counts_right, float* u_right,
+                            float* depth, int capacity_per_frame);
 /* Host copy (synchronises): [nframes][capacity_per_frame]; best_dist / best_idx expose the Hamming stage (may be NULL). */
 int orbx_stereo_results_host(orbx_matcher* m, float* u_right, float* depth, int* best_dist, int* best_idx,
                              int capacity_per_frame);

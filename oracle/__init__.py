@@ -43,6 +43,7 @@ def lib():
         _lib.oro_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
         _lib.oro_extractor_destroy.argtypes = [C.c_void_p]
         _lib.oro_time_extract.restype = C.c_double
+        _lib.oro_time_stereo.restype = C.c_double
     return _lib
 
 
@@ -256,6 +257,17 @@ def stereo_matches(exL, exR, kpL, descL, kpR, descR, mb, mbf):
     lib().oro_stereo_matches(C.c_void_p(exL._h), C.c_void_p(exR._h), n, _p(kpL), _p(descL), kpR.shape[0], _p(kpR), _p(descR),
                              C.c_float(mb), C.c_float(mbf), _p(uR), _p(depth), _p(bd), _p(bi))
     return uR, depth, bd, bi
+
+
+def time_stereo(left, right, nthreads, nfeatures, mb, mbf, scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFAST=7,
+                blur_taps=TAPS_OCV346, sincos_mode=SINCOS_LIBM_F32):
+    """whole stereo frames (extract L+R on two threads per frame + ComputeStereoMatches).  Returns (seconds, matched keypoints)."""
+    left, right = _u8(left), _u8(right)
+    n, h, w = left.shape
+    tot = C.c_longlong(0)
+    s = lib().oro_time_stereo(nfeatures, C.c_float(scaleFactor), nlevels, iniThFAST, minThFAST, blur_taps, sincos_mode, _p(left),
+                              _p(right), n, w, h, C.c_float(mb), C.c_float(mbf), int(nthreads), C.byref(tot))
+    return float(s), int(tot.value)
 
 
 def time_extract(frames, nthreads, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFAST=7,

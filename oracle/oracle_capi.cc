@@ -166,4 +166,37 @@ void oro_three_maxima(const int* hist, int L, int* ind3) {
   ind3[0] = a; ind3[1] = b; ind3[2] = c;
 }
 
+// Timed CPU baseline for whole stereo frames: frame-parallel workers; each worker extracts left and right on two threads
+// exactly as Frame::Frame(stereo) does (src/Frame.cc:120-123), then runs ComputeStereoMatches.  nthreads = total threads used.
+double oro_time_stereo(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh, int blur_taps, int sincos_mode,
+                       const uint8_t* left, const uint8_t* right, int nframes, int w, int h, float mb, float mbf, int nthreads,
+                       long long* total_matched) {
+  const int workers = std::max(1, nthreads / 2);
+  std::vector<std::thread> th;
+  std::vector<long long> counts(workers, 0);
+  auto t0 = std::chrono::steady_clock::now();
+  for (int t = 0; t < workers; t++)
+    th.emplace_back([&, t]() {
+      Extractor exL(nfeatures, scaleFactor, nlevels, iniTh, minTh, blur_taps, sincos_mode), exR(nfeatures, scaleFactor, nlevels, iniTh, minTh, blur_taps, sincos_mode);
+      std::vector<KeyPoint> kl, kr;
+      std::vector<uint8_t> dl, dr;
+      std::vector<float> uR, depth;
+      for (int f = t; f < nframes; f += workers) {
+        std::thread tr([&]() { exR.extract(right + (size_t)f * w * h, w, h, w, 0, 0, kr, dr); });
+        exL.extract(left + (size_t)f * w * h, w, h, w, 0, 0, kl, dl);
+        tr.join();
+        uR.resize(kl.size() + 1); depth.resize(kl.size() + 1);
+        compute_stereo_matches((int)kl.size(), kl.data(), dl.data(), (int)kr.size(), kr.data(), dr.data(), exL.pyramid, exR.pyramid,
+                               exL.mvScaleFactor.data(), exL.mvInvScaleFactor.data(), StereoParams{mb, mbf}, uR.data(), depth.data(), nullptr, nullptr);
+        for (size_t i = 0; i < kl.size(); i++) counts[t] += uR[i] >= 0;
+      }
+    });
+  for (auto& x : th) x.join();
+  auto t1 = std::chrono::steady_clock::now();
+  long long tot = 0;
+  for (auto c : counts) tot += c;
+  if (total_matched) *total_matched = tot;
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+
 }  // extern "C"

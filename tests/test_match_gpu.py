@@ -216,3 +216,24 @@ def test_search_by_projection_batch_on_device_results(orbx, oracle, synth):
         assert nm[f] == nm_o and np.array_equal(kp_mp[f, :c], kp_o)
         assert nm_o > 300
     gx.close(); m.close()
+
+
+def test_stereo_frames_host_pipeline(orbx, oracle, synth):
+    """orbx_stereo_frames_host: chunked (4,4,3), double-buffered; every frame must equal the oracle's stereo frame"""
+    n = 11
+    left = synth.frames(W, H, 52, range(n), False)
+    right = synth.frames(W, H, 52, range(n), True)
+    gl = orbx.ORBextractor(1200, max_batch=4); gr = orbx.ORBextractor(1200, max_batch=4)
+    m = orbx.ORBmatcher()
+    mbf = np.float32(47.90639384423901); mb = np.float32(mbf / np.float32(435.2046959714599))
+    o = m.stereo_frames_host(gl, gr, left, right, mb, mbf)
+    exL = oracle.Extractor(1200, sincos_mode=oracle.SINCOS_PORTABLE); exR = oracle.Extractor(1200, sincos_mode=oracle.SINCOS_PORTABLE)
+    for f in range(n):
+        _, kl, dl = exL(left[f], (0, 0)); _, kr, dr = exR(right[f], (0, 0))
+        uo, do, _, _ = oracle.stereo_matches(exL, exR, kl, dl, kr, dr, mb, mbf)
+        cl, cr = int(o["countsL"][f]), int(o["countsR"][f])
+        assert cl == len(kl) and cr == len(kr)
+        assert o["kpsL"][f, :cl].tobytes() == kl.tobytes() and o["kpsR"][f, :cr].tobytes() == kr.tobytes()
+        assert np.array_equal(o["descL"][f, :cl], dl) and np.array_equal(o["descR"][f, :cr], dr)
+        assert o["uRight"][f, :cl].tobytes() == uo.tobytes() and o["depth"][f, :cl].tobytes() == do.tobytes()
+    gl.close(); gr.close(); m.close()
