@@ -71,7 +71,8 @@ __device__ __forceinline__ uint32_t ring_ld(const uint32_t* sA, const uint32_t* 
   return sB[row * kPairWords + p + 1 + DX / 2];
 }
 
-__global__ void __launch_bounds__(256) k_fast_nms(const __grid_constant__ Geom g, const __grid_constant__ Batch b) {
+// (first version, kept for A/B comparison through ORBX_FAST_V1=1; the tuned kernel is k_fast_nms in fast_nms.cuh)
+__global__ void __launch_bounds__(256) k_fast_nms_v1(const __grid_constant__ Geom g, const __grid_constant__ Batch b) {
   __shared__ uint32_t sRaw[kWinH * kRawWords];
   __shared__ uint32_t sA[kWinH * kPairWords];
   __shared__ uint32_t sB[kWinH * kPairWords];

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -12,6 +13,7 @@
 #include <vector>
 
 #include "extract_kernels.cuh"
+#include "fast_nms.cuh"
 #include "orbx_internal.h"
 
 namespace orbx {
@@ -254,7 +256,10 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
     k_pyr_resize<<<grid, block, 0, st>>>(gg, b, l);
   }
   mark(2);
-  if (g.nTilesTotal > 0) k_fast_nms<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
+  if (g.nTilesTotal > 0) {
+    if (h->fastV1) k_fast_nms_v1<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
+    else k_fast_nms<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
+  }
   mark(3);
   k_quadtree<<<dim3(g.nlevels, nframes), 256, h->qtSmem, st>>>(gg, b, s.nCand);
   mark(4);
@@ -290,6 +295,7 @@ int orbx_create(const orbx_params* p, orbx_extractor** out) {
   CK(cudaSetDevice(p->device));
   orbx_extractor* h = new orbx_extractor();
   h->p = *p;
+  { const char* e = getenv("ORBX_FAST_V1"); h->fastV1 = e && e[0] == '1'; }  // A/B switch for the first FAST kernel
   const int nl = p->nlevels;
   // ORBextractor::ORBextractor, src/ORBextractor.cc:408-468
   h->scaleFactorD = (double)p->scale_factor;  // `double scaleFactor` member initialised from the float argument
