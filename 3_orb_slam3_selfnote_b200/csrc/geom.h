@@ -41,6 +41,7 @@ struct Geom {
   int candSlab;    // records per frame
   int kpSlab;      // level keypoints per frame (sum kpCap)
   int kpStride;    // final keypoints per frame (capacity of the output arrays)
+  int rsWinWords, rsWinRows;  // k_pyr_resize2: staged source window, maxima over all tiles of all levels (words per row, rows)
   int taps[7];     // blur taps (Q8.8)
   int umax[16];
   LevelGeom lv[ORBX_MAX_LEVELS];

@@ -14,6 +14,8 @@
 
 #include "extract_kernels.cuh"
 #include "fast_nms.cuh"
+#include "pyr_resize.cuh"
+#include "blur7.cuh"
 #include "orbx_internal.h"
 
 namespace orbx {
@@ -123,7 +125,8 @@ int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
     L.tilesX = (rw > 0 && rh > 0 && L.nCols > 0) ? (rw + kTileW - 1) / kTileW : 0;
     L.tilesY = (rw > 0 && rh > 0 && L.nCols > 0) ? (rh + kTileH - 1) / kTileH : 0;
     L.tileBase = tileBase; tileBase += L.tilesX * L.tilesY;
-    L.blurTilesX = (L.w + kBlurW - 1) / kBlurW; L.blurTilesY = (L.h + kBlurH - 1) / kBlurH;
+    const int btw = h->blurV1 ? kBlurW : kBvW, bth = h->blurV1 ? kBlurH : kBvH;
+    L.blurTilesX = (L.w + btw - 1) / btw; L.blurTilesY = (L.h + bth - 1) / bth;
     L.blurTileBase = blurTileBase; blurTileBase += L.blurTilesX * L.blurTilesY;
     // column / row cell info: cell index | first<<14 | last<<15
     L.colInfoOff = (int)info.size();
@@ -178,8 +181,25 @@ int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
         e.b1 = (int16_t)std::min(32767, std::max(-32768, cv_round_f(fy * 2048.f)));
         rsy.push_back(e);
       }
+      // staged source window of k_pyr_resize2: maxima over the level's tiles
+      const RsX* tx = rsx.data() + L.rsxOff;
+      const RsY* ty = rsy.data() + L.rsyOff;
+      for (int x0 = 0; x0 < L.w; x0 += kRsTileW) {
+        const int xl = std::min(x0 + kRsTileW, wpad) - 1;
+        const int gx0 = tx[x0].s0 & ~3;
+        g.rsWinWords = std::max(g.rsWinWords, ((tx[xl].s1 - gx0) >> 2) + 1);
+      }
+      for (int y0 = 0; y0 < L.h; y0 += kRsTileH) {
+        const int yl = std::min(y0 + kRsTileH, L.h) - 1;
+        g.rsWinRows = std::max(g.rsWinRows, ty[yl].s1 - ty[y0].s0 + 1);
+      }
     }
   }
+  g.rsWinWords = round_up(std::max(g.rsWinWords, 4), 4);
+  g.rsWinRows = std::max(g.rsWinRows, 1);
+  h->rsSmem = (size_t)g.rsWinRows * (g.rsWinWords + kRsTileW) * 4;
+  if (h->rsSmem > 200 * 1024) { set_error("scale factor too large for the resize kernel's shared memory"); return ORBX_ERR_UNSUPPORTED; }
+  CK(cudaFuncSetAttribute(k_pyr_resize2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->rsSmem));
   g.nCellsTotal = cellBase; g.nTilesTotal = tileBase; g.nBlurTilesTotal = blurTileBase;
   g.candSlab = candOff; g.kpSlab = kpOff; g.kpStride = kpOff;
   h->pyrFrame = round_up(std::max(pyrOff, 256), 256);
@@ -252,8 +272,13 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
   mark(1);
   for (int l = 1; l < g.nlevels; l++) {
     const LevelGeom& L = g.lv[l];
-    dim3 grid((L.w + 127) / 128, (L.h + 7) / 8, nframes), block(32, 8);
-    k_pyr_resize<<<grid, block, 0, st>>>(gg, b, l);
+    if (h->resizeV1) {
+      dim3 grid((L.w + 127) / 128, (L.h + 7) / 8, nframes), block(32, 8);
+      k_pyr_resize<<<grid, block, 0, st>>>(gg, b, l);
+    } else {
+      dim3 grid((L.w + kRsTileW - 1) / kRsTileW, (L.h + kRsTileH - 1) / kRsTileH, nframes);
+      k_pyr_resize2<<<grid, 256, h->rsSmem, st>>>(gg, b, l);
+    }
   }
   mark(2);
   if (g.nTilesTotal > 0) {
@@ -263,7 +288,8 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
   mark(3);
   k_quadtree<<<dim3(g.nlevels, nframes), 256, h->qtSmem, st>>>(gg, b, s.nCand);
   mark(4);
-  k_blur7<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, st>>>(gg, b);
+  if (h->blurV1) k_blur7<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, st>>>(gg, b);
+  else k_blur7v<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, st>>>(gg, b);
   mark(5);
   k_assemble<<<nframes, 256, 0, st>>>(gg, b);
   mark(6);
@@ -295,7 +321,9 @@ int orbx_create(const orbx_params* p, orbx_extractor** out) {
   CK(cudaSetDevice(p->device));
   orbx_extractor* h = new orbx_extractor();
   h->p = *p;
-  { const char* e = getenv("ORBX_FAST_V1"); h->fastV1 = e && e[0] == '1'; }  // A/B switch for the first FAST kernel
+  { const char* e = getenv("ORBX_FAST_V1"); h->fastV1 = e && e[0] == '1'; }  // A/B switches for the first versions of kernels
+  { const char* e = getenv("ORBX_RESIZE_V1"); h->resizeV1 = e && e[0] == '1'; }
+  { const char* e = getenv("ORBX_BLUR_V1"); h->blurV1 = e && e[0] == '1'; }
   const int nl = p->nlevels;
   // ORBextractor::ORBextractor, src/ORBextractor.cc:408-468
   h->scaleFactorD = (double)p->scale_factor;  // `double scaleFactor` member initialised from the float argument

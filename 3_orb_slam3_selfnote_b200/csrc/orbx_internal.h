@@ -57,6 +57,8 @@ struct orbx_extractor {
   Slot slot[2];
   int lastSlot = 0;
   bool profile = false;
+  bool resizeV1 = false, blurV1 = false;
+  size_t rsSmem = 0;
   bool fastV1 = false;  // ORBX_FAST_V1=1: run the first FAST kernel instead of the tuned one (A/B only)
 };
 

@@ -1,0 +1,83 @@
+// k_pyr_resize2 -- one pyramid level from the previous one, cv::resize(INTER_LINEAR) on 8U in OpenCV's fixed point
+// (reference call site src/ORBextractor.cc:1201).  Tuned replacement of k_pyr_resize (extract_kernels.cuh),
+// which issued 16 byte-wide LDGs per thread and was LSU/latency bound (profiles/r01: issue 30 %, DRAM 5 %).
+//   CTA = 128x16 destination pixels of one frame.
+//   1. the source window (<= ~156x21 px at scale 1.2) is staged with aligned 32-bit loads, coalesced along rows;
+//   2. horizontal pass ONCE per source row (OpenCV's order: rows are interpolated horizontally first):
+//      h = S[sx]*a0 + S[sx+1]*a1, kept as (h >> 4) in shared memory; a thread owns one destination column, so its
+//      table entry (source columns + Q11 weights) lives in registers for all window rows;
+//   3. vertical pass: thread = 4 destination pixels of one row, two LDS.128 (rows sy, sy+1), one 32-bit store:
+//      v = ((b0*(h0>>4))>>16) + ((b1*(h1>>4))>>16) + 2 >> 2.
+// Algorithmic bytes per launch: read level l-1 + write level l.
+#pragma once
+#include "dev_common.cuh"
+#include "geom.h"
+
+namespace orbx {
+
+constexpr int kRsTileW = 128, kRsTileH = 16;
+
+__global__ void __launch_bounds__(256) k_pyr_resize2(const __grid_constant__ Geom g, const __grid_constant__ Batch b, int level) {
+  extern __shared__ __align__(16) uint32_t rs_smem[];
+  const LevelGeom& L = g.lv[level];
+  const int winWords = g.rsWinWords, winRows = g.rsWinRows;
+  uint32_t* sRaw = rs_smem;                                               // [winRows][winWords]  source bytes
+  int* sH = reinterpret_cast<int*>(rs_smem + winRows * winWords);          // [winRows][128]       (h >> 4)
+  const int tid = threadIdx.x, f = blockIdx.z;
+  const int x0 = blockIdx.x * kRsTileW, y0 = blockIdx.y * kRsTileH;
+  int sp;
+  const uint8_t* src = level_ptr(g, b, level - 1, f, sp);
+  const RsX* tx = b.rsx + L.rsxOff;
+  const RsY* ty = b.rsy + L.rsyOff;
+  const int wpad = (L.w + 3) & ~3;                                         // the column table is padded to a multiple of 4
+  const int xl = min(x0 + kRsTileW, wpad) - 1, yl = min(y0 + kRsTileH, L.h) - 1;
+  const int gx0 = (int)tx[x0].s0 & ~3;                                     // first staged source column (word aligned)
+  const int nW = (((int)tx[xl].s1 - gx0) >> 2) + 1;                        // words per window row   (<= winWords)
+  const int wy0 = ty[y0].s0;
+  const int nR = (int)ty[yl].s1 - wy0 + 1;                                 // window rows            (<= winRows)
+
+  // ---- 1. stage the window
+  for (int r = tid >> 5; r < nR; r += 8) {
+    const uint32_t* row = reinterpret_cast<const uint32_t*>(src + (long long)(wy0 + r) * sp + gx0);
+    for (int k = tid & 31; k < nW; k += 32) sRaw[r * winWords + k] = __ldg(row + k);
+  }
+  __syncthreads();
+
+  // ---- 2. horizontal pass: thread = destination column c, row group rg
+  {
+    const int c = tid & (kRsTileW - 1), rg = tid >> 7;
+    if (x0 + c < wpad) {
+      const RsX e = tx[x0 + c];
+      const int o0 = e.s0 - gx0, o1 = e.s1 - gx0, a0 = e.a0, a1 = e.a1;
+      const uint8_t* rawb = reinterpret_cast<const uint8_t*>(sRaw);
+#pragma unroll 4
+      for (int r = rg; r < nR; r += 2) {
+        const uint8_t* rb = rawb + r * (winWords * 4);
+        const int h = (int)rb[o0] * a0 + (int)rb[o1] * a1;
+        sH[r * kRsTileW + c] = h >> 4;
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- 3. vertical pass: task = 4 destination pixels
+  uint8_t* dstBase = b.pyr + (long long)f * b.pyrFrameStride + L.pyrOff;
+#pragma unroll
+  for (int it = 0; it < (kRsTileW / 4) * kRsTileH / 256; it++) {
+    const int task = tid + it * 256;
+    const int q = task & 31, r = task >> 5;
+    const int x = x0 + 4 * q, y = y0 + r;
+    if (x >= L.w || y >= L.h) continue;
+    const RsY e = ty[y];
+    const int b0 = e.b0, b1 = e.b1;
+    const int4 h0 = *reinterpret_cast<const int4*>(sH + (e.s0 - wy0) * kRsTileW + 4 * q);
+    const int4 h1 = *reinterpret_cast<const int4*>(sH + (e.s1 - wy0) * kRsTileW + 4 * q);
+    const int v0 = min(255, max(0, (((b0 * h0.x) >> 16) + ((b1 * h1.x) >> 16) + 2) >> 2));
+    const int v1 = min(255, max(0, (((b0 * h0.y) >> 16) + ((b1 * h1.y) >> 16) + 2) >> 2));
+    const int v2 = min(255, max(0, (((b0 * h0.z) >> 16) + ((b1 * h1.z) >> 16) + 2) >> 2));
+    const int v3 = min(255, max(0, (((b0 * h0.w) >> 16) + ((b1 * h1.w) >> 16) + 2) >> 2));
+    *reinterpret_cast<uint32_t*>(dstBase + (long long)y * L.pitch + x) = (uint32_t)v0 | ((uint32_t)v1 << 8) | ((uint32_t)v2 << 16) | ((uint32_t)v3 << 24);
+  }
+}
+
+}  // namespace orbx
