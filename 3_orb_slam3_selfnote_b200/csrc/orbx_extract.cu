@@ -14,6 +14,7 @@
 
 #include "extract_kernels.cuh"
 #include "fast_nms.cuh"
+#include "fast_nms3.cuh"
 #include "pyr_resize.cuh"
 #include "blur7.cuh"
 #include "orbx_internal.h"
@@ -122,8 +123,9 @@ int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
     L.candOff = candOff; candOff += L.candCap;
     // FAST tiles over the region [19, w-19) x [19, h-19)
     const int rw = L.w - 2 * kEdge, rh = L.h - 2 * kEdge;
-    L.tilesX = (rw > 0 && rh > 0 && L.nCols > 0) ? (rw + kTileW - 1) / kTileW : 0;
-    L.tilesY = (rw > 0 && rh > 0 && L.nCols > 0) ? (rh + kTileH - 1) / kTileH : 0;
+    const int ftw = h->fastVer == 3 ? kF3TileW : kTileW, fth = h->fastVer == 3 ? kF3TileH : kTileH;
+    L.tilesX = (rw > 0 && rh > 0 && L.nCols > 0) ? (rw + ftw - 1) / ftw : 0;
+    L.tilesY = (rw > 0 && rh > 0 && L.nCols > 0) ? (rh + fth - 1) / fth : 0;
     L.tileBase = tileBase; tileBase += L.tilesX * L.tilesY;
     const int btw = h->blurV1 ? kBlurW : kBvW, bth = h->blurV1 ? kBlurH : kBvH;
     L.blurTilesX = (L.w + btw - 1) / btw; L.blurTilesY = (L.h + bth - 1) / bth;
@@ -282,8 +284,9 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
   }
   mark(2);
   if (g.nTilesTotal > 0) {
-    if (h->fastV1) k_fast_nms_v1<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
-    else k_fast_nms<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
+    if (h->fastVer == 1) k_fast_nms_v1<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
+    else if (h->fastVer == 2) k_fast_nms<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
+    else k_fast_nms3<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
   }
   mark(3);
   k_quadtree<<<dim3(g.nlevels, nframes), 256, h->qtSmem, st>>>(gg, b, s.nCand);
@@ -321,7 +324,9 @@ int orbx_create(const orbx_params* p, orbx_extractor** out) {
   CK(cudaSetDevice(p->device));
   orbx_extractor* h = new orbx_extractor();
   h->p = *p;
-  { const char* e = getenv("ORBX_FAST_V1"); h->fastV1 = e && e[0] == '1'; }  // A/B switches for the first versions of kernels
+  // A/B switches for the earlier versions of kernels
+  { const char* e = getenv("ORBX_FAST_V1"); if (e && e[0] == '1') h->fastVer = 1; }
+  { const char* e = getenv("ORBX_FAST_V2"); if (e && e[0] == '1') h->fastVer = 2; }
   { const char* e = getenv("ORBX_RESIZE_V1"); h->resizeV1 = e && e[0] == '1'; }
   { const char* e = getenv("ORBX_BLUR_V1"); h->blurV1 = e && e[0] == '1'; }
   const int nl = p->nlevels;

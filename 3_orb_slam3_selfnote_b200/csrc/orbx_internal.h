@@ -59,7 +59,7 @@ struct orbx_extractor {
   bool profile = false;
   bool resizeV1 = false, blurV1 = false;
   size_t rsSmem = 0;
-  bool fastV1 = false;  // ORBX_FAST_V1=1: run the first FAST kernel instead of the tuned one (A/B only)
+  int fastVer = 3;      // ORBX_FAST_V1=1 / ORBX_FAST_V2=1: run an earlier FAST kernel instead of k_fast_nms3 (A/B only)
 };
 
 
