@@ -1,6 +1,7 @@
 // Geometry / batch descriptors shared by host code and kernels (passed BY VALUE as __grid_constant__ kernel parameters,
 // so several handles with different geometry can run concurrently -- no __constant__ globals).
 #pragma once
+#include <cuda_runtime.h>
 #include <stdint.h>
 
 #include "../../include/orbx.h"
@@ -83,6 +84,7 @@ struct Batch {
   const RsX* rsx; const RsY* rsy;                    // indexed by LevelGeom::rsxOff + x / rsyOff + y
   const uint16_t* info;                              // cell index | first<<14 | last<<15, indexed by colInfoOff + x / rowInfoOff + y
   const int8_t* pattern;                             // 256 x (x0,y0,x1,y1)
+  const float4* patternF;                            // the same as floats (k_orient_desc2)
 };
 
 }  // namespace orbx

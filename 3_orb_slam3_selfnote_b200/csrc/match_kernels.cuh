@@ -564,6 +564,114 @@ __global__ void __launch_bounds__(256) k_stereo_hamming(const __grid_constant__ 
   }
 }
 
+// ---- row table (Frame.cc:911-928) -------------------------------------------------------------------------------------------
+// The reference lists every right keypoint iR in the rows floor(y - r) .. ceil(y + r), r = 2 * scale[octave], and a left
+// keypoint only looks at the list of its own row.  k_stereo_rowtable builds that table per frame in CSR form (one CTA per
+// frame: shared-memory histogram over the image rows, exclusive scan, fill); an item carries everything the gates need
+// (index, octave, x) so k_stereo_hamming2 touches a right keypoint's record only for its 32-byte descriptor.  ~27 items per
+// row instead of a scan over all ~1200 right keypoints per left keypoint (k_stereo_hamming, kept for A/B: ORBX_STEREO_V1=1).
+struct RowTable {
+  int* rowStart;   // [nframes][rows + 1]
+  uint2* items;    // [nframes][itemCap]   x = iR | octave << 16, y = float bits of kp.x
+  int rows, itemCap;
+};
+
+__global__ void __launch_bounds__(256) k_stereo_rowtable(const __grid_constant__ Geom g, const __grid_constant__ Batch bR,
+                                                         const __grid_constant__ ScaleTab tab, RowTable rt) {
+  extern __shared__ int srow[];   // [rows] counts -> starts, [rows] fill cursors
+  __shared__ int warpTmp[8];
+  const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int rows = rt.rows;
+  int* cnt = srow;
+  int* cur = srow + rows;
+  const int nR = bR.counts[f];
+  const long long o = (long long)f * g.kpStride;
+  for (int i = tid; i < rows; i += 256) { cnt[i] = 0; cur[i] = 0; }
+  __syncthreads();
+  for (int iR = tid; iR < nR; iR += 256) {
+    const orbx_keypoint kr = bR.kps[o + iR];
+    const float r = __fmul_rn(2.0f, tab.scale[kr.octave]);
+    const int maxr = min((int)ceilf(__fadd_rn(kr.y, r)), rows - 1), minr = max((int)floorf(__fsub_rn(kr.y, r)), 0);
+    for (int y = minr; y <= maxr; y++) atomicAdd(&cnt[y], 1);
+  }
+  __syncthreads();
+  // exclusive scan of cnt[0..rows): thread = contiguous chunk
+  const int chunk = (rows + 255) >> 8;
+  const int beg = min(rows, tid * chunk), end = min(rows, beg + chunk);
+  int sum = 0;
+  for (int i = beg; i < end; i++) sum += cnt[i];
+  int incl = sum;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += v;
+  }
+  if (lane == 31) warpTmp[warp] = incl;
+  __syncthreads();
+  int woff = 0;
+#pragma unroll
+  for (int w = 0; w < 8; w++) if (w < warp) woff += warpTmp[w];
+  int run = woff + incl - sum;
+  int* rowStart = rt.rowStart + (long long)f * (rows + 1);
+  for (int i = beg; i < end; i++) { const int v = cnt[i]; cnt[i] = run; rowStart[i] = min(run, rt.itemCap); run += v; }
+  if (tid == 255) rowStart[rows] = min(run, rt.itemCap);
+  __syncthreads();
+  uint2* items = rt.items + (long long)f * rt.itemCap;
+  for (int iR = tid; iR < nR; iR += 256) {
+    const orbx_keypoint kr = bR.kps[o + iR];
+    const float r = __fmul_rn(2.0f, tab.scale[kr.octave]);
+    const int maxr = min((int)ceilf(__fadd_rn(kr.y, r)), rows - 1), minr = max((int)floorf(__fsub_rn(kr.y, r)), 0);
+    const uint2 it = make_uint2((uint32_t)iR | ((uint32_t)kr.octave << 16), __float_as_uint(kr.x));
+    for (int y = minr; y <= maxr; y++) {
+      const int pos = cnt[y] + atomicAdd(&cur[y], 1);
+      if (pos < rt.itemCap) items[pos] = it;
+    }
+  }
+}
+
+// Hamming stage of Frame::ComputeStereoMatches (Frame.cc:936-984) over the row table: one warp per left keypoint, lanes = items of
+// its row.  Ties in distance go to the lower iR, as the reference's strict `dist < bestDist` over an iR-ascending list does.
+__global__ void __launch_bounds__(256) k_stereo_hamming2(const __grid_constant__ Geom g, const __grid_constant__ Batch bL,
+                                                         const __grid_constant__ Batch bR, float maxD, RowTable rt, StereoOut out) {
+  const int f = blockIdx.y, lane = threadIdx.x & 31;
+  const int iL = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int nL = bL.counts[f];
+  if (iL >= nL) return;
+  const long long o = (long long)f * g.kpStride;
+  const orbx_keypoint kl = bL.kps[o + iL];
+  const int levelL = kl.octave;
+  const float vL = kl.y, uL = kl.x;
+  const int row = (int)vL;
+  const float minU = __fsub_rn(uL, maxD), maxU = uL;
+  uint32_t key = 100u << 16;  // TH_HIGH: only dist < 100 replaces it
+  if (!(maxU < 0) && row >= 0 && row < rt.rows) {
+    const int* rowStart = rt.rowStart + (long long)f * (rt.rows + 1);
+    const int beg = rowStart[row], end = rowStart[row + 1];
+    const uint2* items = rt.items + (long long)f * rt.itemCap;
+    uint32_t dl[8];
+    load_desc(bL.desc + (o + iL) * 32, dl);
+    for (int j = beg + lane; j < end; j += 32) {
+      const uint2 it = items[j];
+      const int oct = (int)(it.x >> 16), iR = (int)(it.x & 0xffffu);
+      const float uR = __uint_as_float(it.y);
+      if (oct < levelL - 1 || oct > levelL + 1) continue;
+      if (uR >= minU && uR <= maxU) {
+        uint32_t dr[8];
+        load_desc(bR.desc + (o + iR) * 32, dr);
+        key = min(key, ((uint32_t)hamming8(dl, dr) << 16) | (uint32_t)iR);
+      }
+    }
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, s));
+  if (lane == 0) {
+    const int d = key >> 16;
+    out.bestDist[o + iL] = d;
+    out.bestIdx[o + iL] = d < 100 ? (int)(key & 0xffffu) : -1;
+    out.uRight[o + iL] = -1.0f; out.depth[o + iL] = -1.0f; out.sad[o + iL] = -1;
+  }
+}
+
 // Sub-pixel refinement (Frame.cc:987-1062): 11x11 centre-subtracted SAD over 11 shifts on the keypoint's pyramid level, parabola fit.
 __global__ void __launch_bounds__(256) k_stereo_sad(const __grid_constant__ Geom g, const __grid_constant__ Batch bL,
                                                     const __grid_constant__ Batch bR, const __grid_constant__ ScaleTab tab,
@@ -639,35 +747,37 @@ __global__ void __launch_bounds__(256) k_stereo_sad(const __grid_constant__ Geom
 
 // Outlier cut (Frame.cc:1065-1078): median of the accepted SAD values by (sad, iL) order, drop everything >= 1.5*1.4*median.
 __global__ void __launch_bounds__(256) k_stereo_median(const __grid_constant__ Geom g, const __grid_constant__ Batch bL, StereoOut out) {
-  extern __shared__ int ssad[];
+  extern __shared__ uint32_t skey[];   // accepted matches as (sad << 16 | iL) keys: distinct, ordered like the reference's sorted (dist, iL) pairs
   __shared__ int sN, sMedian;
-  const int f = blockIdx.x, tid = threadIdx.x;
+  const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
   const int nL = bL.counts[f];
   const long long o = (long long)f * g.kpStride;
   if (tid == 0) { sN = 0; sMedian = -1; }
   __syncthreads();
-  int local = 0;
-  for (int i = tid; i < nL; i += 256) { const int v = out.sad[o + i]; ssad[i] = v; local += v >= 0; }
-  if (local) atomicAdd(&sN, local);
+  for (int base = 0; base < nL; base += 256) {
+    const int i = base + tid;
+    const int v = (i < nL) ? out.sad[o + i] : -1;     // 11x11 SAD <= 121 * 510 < 65536
+    const uint32_t m = __ballot_sync(0xffffffffu, v >= 0);
+    int wbase = 0;
+    if (lane == 0 && m) wbase = atomicAdd(&sN, __popc(m));
+    wbase = __shfl_sync(0xffffffffu, wbase, 0);
+    if (v >= 0) skey[wbase + __popc(m & ((1u << lane) - 1))] = ((uint32_t)v << 16) | (uint32_t)i;
+  }
   __syncthreads();
   const int n = sN;
   if (n == 0) return;
   const int target = n / 2;
-  for (int i = tid; i < nL; i += 256) {
-    const int v = ssad[i];
-    if (v < 0) continue;
+  for (int i = tid; i < n; i += 256) {
+    const uint32_t k = skey[i];
     int rank = 0;
-    for (int j = 0; j < nL; j++) {
-      const int u = ssad[j];
-      rank += (u >= 0) && (u < v || (u == v && j < i));
-    }
-    if (rank == target) sMedian = v;
+    for (int j = 0; j < n; j++) rank += skey[j] < k;
+    if (rank == target) sMedian = (int)(k >> 16);
   }
   __syncthreads();
   const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)sMedian);
-  for (int i = tid; i < nL; i += 256) {
-    const int v = ssad[i];
-    if (v >= 0 && !((float)v < thDist)) { out.uRight[o + i] = -1.0f; out.depth[o + i] = -1.0f; }
+  for (int i = tid; i < n; i += 256) {
+    const uint32_t k = skey[i];
+    if (!((float)(k >> 16) < thDist)) { out.uRight[o + (k & 0xffffu)] = -1.0f; out.depth[o + (k & 0xffffu)] = -1.0f; }
   }
 }
 

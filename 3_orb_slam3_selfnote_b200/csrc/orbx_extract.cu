@@ -17,6 +17,7 @@
 #include "fast_nms3.cuh"
 #include "pyr_resize.cuh"
 #include "blur7.cuh"
+#include "orient_desc.cuh"
 #include "orbx_internal.h"
 
 namespace orbx {
@@ -66,6 +67,7 @@ static void free_geom(orbx_extractor* h) {
 int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
   if (h->haveGeom && h->g.width == width && h->g.height == height) return ORBX_OK;
   if (h->haveGeom) free_geom(h);
+  h->geomEpoch++;
   CK(cudaSetDevice(h->p.device));
   if (width > 8192 || height > 8192) { set_error("image larger than 8192 px is unsupported"); return ORBX_ERR_UNSUPPORTED; }
   Geom& g = h->g;
@@ -260,7 +262,7 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
   b.lkp = s.lkp; b.lkpCount = s.lkpCount; b.lkpDest = s.lkpDest;
   b.qXY = s.qXY; b.qOrd = s.qOrd; b.qNode = s.qNode; b.qResp = s.qResp; b.qSel = s.qSel;
   b.kps = s.kps; b.desc = s.desc; b.counts = s.counts; b.mono = s.mono; b.status = s.status;
-  b.rsx = h->dRsx; b.rsy = h->dRsy; b.info = h->dInfo; b.pattern = h->dPattern;
+  b.rsx = h->dRsx; b.rsy = h->dRsy; b.info = h->dInfo; b.pattern = h->dPattern; b.patternF = reinterpret_cast<const float4*>(h->dPattern + 1024);
   s.last = b; s.lastFrames = nframes;
   h->lastSlot = si;
 
@@ -296,7 +298,8 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
   mark(5);
   k_assemble<<<nframes, 256, 0, st>>>(gg, b);
   mark(6);
-  k_orient_desc<<<dim3((g.kpSlab + 7) / 8, nframes), 256, 0, st>>>(gg, b);
+  if (h->orientV1) k_orient_desc<<<dim3((g.kpSlab + 7) / 8, nframes), 256, 0, st>>>(gg, b);
+  else k_orient_desc2<<<dim3((g.kpSlab + 7) / 8, nframes), 256, 0, st>>>(gg, b);
   mark(7);
   s.evValid = prof;
   CK(cudaGetLastError());
@@ -361,8 +364,15 @@ int orbx_create(const orbx_params* p, orbx_extractor** out) {
   }
   for (Slot& s : h->slot)
     if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; set_error("stream creation failed"); return ORBX_ERR_CUDA; }
-  if (cudaMalloc(&h->dPattern, 1024) != cudaSuccess ||
-      cudaMemcpy(h->dPattern, kPatternHost, 1024, cudaMemcpyHostToDevice) != cudaSuccess) {
+  float patF[1024];   // pair 8 * lane + j  ->  record j * 32 + lane (k_orient_desc2 reads [j][lane])
+  for (int pr = 0; pr < 256; pr++)
+    for (int k = 0; k < 4; k++) patF[((pr & 7) * 32 + (pr >> 3)) * 4 + k] = (float)kPatternHost[pr * 4 + k];
+  for (int v = 0; v <= kHalfPatch; v++)
+    if (h->umax[v] != od_umax(v)) { delete h; set_error("umax table differs from the compiled-in one"); return ORBX_ERR_UNSUPPORTED; }
+  { const char* e = getenv("ORBX_ORIENT_V1"); h->orientV1 = e && e[0] == '1'; }
+  if (cudaMalloc(&h->dPattern, 1024 + sizeof(patF)) != cudaSuccess ||
+      cudaMemcpy(h->dPattern, kPatternHost, 1024, cudaMemcpyHostToDevice) != cudaSuccess ||
+      cudaMemcpy(h->dPattern + 1024, patF, sizeof(patF), cudaMemcpyHostToDevice) != cudaSuccess) {
     delete h; set_error("pattern upload failed"); return ORBX_ERR_CUDA;
   }
   *out = h;

@@ -49,6 +49,7 @@ struct orbx_extractor {
   int umax[16];
   // geometry-dependent state
   bool haveGeom = false;
+  unsigned long long geomEpoch = 0;  // bumped whenever the geometry (and with it every workspace pointer) is rebuilt
   Geom g{};
   int inPitch = 0;  // pitch of the staged input
   long long pyrFrame = 0, blurFrame = 0;
@@ -57,7 +58,7 @@ struct orbx_extractor {
   Slot slot[2];
   int lastSlot = 0;
   bool profile = false;
-  bool resizeV1 = false, blurV1 = false;
+  bool resizeV1 = false, blurV1 = false, orientV1 = false;
   size_t rsSmem = 0;
   int fastVer = 3;      // ORBX_FAST_V1=1 / ORBX_FAST_V2=1: run an earlier FAST kernel instead of k_fast_nms3 (A/B only)
 };

@@ -2,6 +2,7 @@
 // its loop prologues) and the extern "C" entry points of include/orbx.h.  All distance / search work is in match_kernels.cuh.
 #include <cuda_runtime.h>
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -21,7 +22,21 @@ struct orbx_matcher {
   // stereo results of the last orbx_stereo_match_batch
   float* sURight = nullptr; float* sDepth = nullptr; int* sBestDist = nullptr; int* sBestIdx = nullptr; int* sSad = nullptr;
   size_t sCap = 0, sHalf = 0;
+  unsigned long long sEpoch = 0;   // bumped whenever a stereo buffer is reallocated (invalidates cached graphs)
   int sFrames = 0, sStride = 0, sLast = 0;
+  // row table of the right keypoints (Frame.cc:911-928), two halves like the results
+  int* sRowStart = nullptr; uint2* sRowItems = nullptr;
+  size_t sRowStartCap = 0, sRowItemsCap = 0;
+  bool stereoV1 = false;   // ORBX_STEREO_V1=1: brute-force scan instead of the row table (A/B only)
+  // CUDA graph of one chunk of orbx_stereo_frames_host (extract L + extract R + stereo kernels), one per slot: the call is
+  // bound by the host's launch rate otherwise (~30 launches with 2 KB of parameters each per chunk)
+  struct ChunkGraph {
+    cudaGraphExec_t exec = nullptr;
+    int nb = 0; float mb = 0, mbf = 0;
+    const orbx_extractor* exL = nullptr; const orbx_extractor* exR = nullptr;
+    unsigned long long epochL = 0, epochR = 0, epochM = 0;
+  } chunkGraph[2];
+  bool noGraph = false;    // ORBX_NO_GRAPH=1
 };
 
 namespace {
@@ -269,6 +284,8 @@ int orbx_matcher_create(int device, orbx_matcher** out) {
   CK(cudaSetDevice(device));
   orbx_matcher* m = new orbx_matcher();
   m->device = device;
+  { const char* e = getenv("ORBX_STEREO_V1"); m->stereoV1 = e && e[0] == '1'; }
+  { const char* e = getenv("ORBX_NO_GRAPH"); m->noGraph = e && e[0] == '1'; }
   if (cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess || cudaMalloc(&m->dStatus, sizeof(int)) != cudaSuccess) {
     delete m; set_error("matcher resources"); return ORBX_ERR_CUDA;
   }
@@ -280,8 +297,9 @@ void orbx_matcher_destroy(orbx_matcher* m) {
   if (!m) return;
   cudaSetDevice(m->device);
   cudaStreamSynchronize(m->stream);
-  void* ptrs[] = {m->arena, m->dStatus, m->sURight, m->sDepth, m->sBestDist, m->sBestIdx, m->sSad};
+  void* ptrs[] = {m->arena, m->dStatus, m->sURight, m->sDepth, m->sBestDist, m->sBestIdx, m->sSad, m->sRowStart, m->sRowItems};
   for (void* p : ptrs) if (p) cudaFree(p);
+  for (auto& cg : m->chunkGraph) if (cg.exec) cudaGraphExecDestroy(cg.exec);
   cudaStreamDestroy(m->stream);
   delete m;
 }
@@ -463,8 +481,40 @@ int orbx_knn2(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int n
   return ORBX_OK;
 }
 
+// Allocations of the stereo stage for the two extractors' geometry (never called while a stream is capturing).
+static int stereo_prepare(orbx_matcher* m, orbx_extractor* exL, orbx_extractor* exR) {
+  const Geom& g = exL->g;
+  const int nfCap = std::max(exL->p.max_batch, exR->p.max_batch);
+  const size_t half = (size_t)nfCap * g.kpStride;
+  if (2 * half > m->sCap) {
+    CK(cudaDeviceSynchronize());
+    void** ptrs[] = {(void**)&m->sURight, (void**)&m->sDepth, (void**)&m->sBestDist, (void**)&m->sBestIdx, (void**)&m->sSad};
+    for (void** p : ptrs) { if (*p) CK(cudaFree(*p)); *p = nullptr; CK(cudaMalloc(p, 2 * half * 4)); }
+    m->sCap = 2 * half;
+    m->sEpoch++;
+  }
+  if (!m->stereoV1) {
+    // a right keypoint is listed in at most 2 * ceil(r) + 2 rows, r = 2 * scale[octave]
+    const int maxRows = 2 * (int)std::ceil(2.0f * exL->scale[g.nlevels - 1]) + 2;
+    const size_t itemCap = (size_t)g.kpStride * maxRows, needStart = 2 * (size_t)nfCap * (g.height + 1), needItems = 2 * (size_t)nfCap * itemCap;
+    if (needStart > m->sRowStartCap || needItems > m->sRowItemsCap) {
+      CK(cudaDeviceSynchronize());
+      if (m->sRowStart) CK(cudaFree(m->sRowStart));
+      if (m->sRowItems) CK(cudaFree(m->sRowItems));
+      m->sRowStart = nullptr; m->sRowItems = nullptr;
+      CK(cudaMalloc(&m->sRowStart, needStart * sizeof(int)));
+      CK(cudaMalloc(&m->sRowItems, needItems * sizeof(uint2)));
+      m->sRowStartCap = needStart; m->sRowItemsCap = needItems;
+      m->sEpoch++;
+    }
+    const size_t rtSmem = 2 * (size_t)g.height * sizeof(int);
+    if (rtSmem > 48 * 1024) CK(cudaFuncSetAttribute(k_stereo_rowtable, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rtSmem));
+  }
+  return ORBX_OK;
+}
+
 // Enqueue ComputeStereoMatches for the batches held by slot `si` of both extractors; results go to half `si` of the matcher's buffers.
-static int stereo_launch(orbx_matcher* m, orbx_extractor* exL, orbx_extractor* exR, int si, float mb, float mbf, cudaStream_t st) {
+static int stereo_launch(orbx_matcher* m, orbx_extractor* exL, orbx_extractor* exR, int si, float mb, float mbf, cudaStream_t st, bool prepared = false) {
   Slot& sL = exL->slot[si];
   Slot& sR = exR->slot[si];
   const Geom& g = exL->g;
@@ -474,14 +524,10 @@ static int stereo_launch(orbx_matcher* m, orbx_extractor* exL, orbx_extractor* e
     return ORBX_ERR_ARG;
   }
   if (g.kpStride > 65535) { set_error("more than 65535 keypoints per frame"); return ORBX_ERR_UNSUPPORTED; }
+  if (!prepared) { const int rc = stereo_prepare(m, exL, exR); if (rc != ORBX_OK) return rc; }
   const int nf = sL.lastFrames;
-  const size_t half = (size_t)std::max(exL->p.max_batch, exR->p.max_batch) * g.kpStride;
-  if (2 * half > m->sCap) {
-    CK(cudaDeviceSynchronize());
-    void** ptrs[] = {(void**)&m->sURight, (void**)&m->sDepth, (void**)&m->sBestDist, (void**)&m->sBestIdx, (void**)&m->sSad};
-    for (void** p : ptrs) { if (*p) CK(cudaFree(*p)); *p = nullptr; CK(cudaMalloc(p, 2 * half * 4)); }
-    m->sCap = 2 * half;
-  }
+  const int nfCap = std::max(exL->p.max_batch, exR->p.max_batch);
+  const size_t half = (size_t)nfCap * g.kpStride;
   m->sFrames = nf; m->sStride = g.kpStride; m->sHalf = half; m->sLast = si;
   ScaleTab tab{};
   for (int l = 0; l < g.nlevels; l++) { tab.scale[l] = exL->scale[l]; tab.invScale[l] = exL->invScale[l]; }
@@ -490,7 +536,15 @@ static int stereo_launch(orbx_matcher* m, orbx_extractor* exL, orbx_extractor* e
   const size_t o = (size_t)si * half;
   StereoOut out{m->sURight + o, m->sDepth + o, m->sBestDist + o, m->sBestIdx + o, m->sSad + o};
   dim3 grid((g.kpStride + 7) / 8, nf);
-  k_stereo_hamming<<<grid, 256, 0, st>>>(gg, sL.last, sR.last, tab, maxD, out);
+  if (m->stereoV1) {
+    k_stereo_hamming<<<grid, 256, 0, st>>>(gg, sL.last, sR.last, tab, maxD, out);
+  } else {
+    const int maxRows = 2 * (int)std::ceil(2.0f * exL->scale[g.nlevels - 1]) + 2;
+    const size_t itemCap = (size_t)g.kpStride * maxRows;
+    RowTable rt{m->sRowStart + (size_t)si * nfCap * (g.height + 1), m->sRowItems + (size_t)si * nfCap * itemCap, g.height, (int)itemCap};
+    k_stereo_rowtable<<<nf, 256, 2 * (size_t)g.height * sizeof(int), st>>>(gg, sR.last, tab, rt);
+    k_stereo_hamming2<<<grid, 256, 0, st>>>(gg, sL.last, sR.last, maxD, rt, out);
+  }
   k_stereo_sad<<<grid, 256, 0, st>>>(gg, sL.last, sR.last, tab, maxD, mbf, out);
   k_stereo_median<<<nf, 256, (size_t)g.kpStride * sizeof(int), st>>>(gg, sL.last, out);
   CK(cudaGetLastError());
@@ -522,6 +576,9 @@ int orbx_stereo_frames_host(orbx_matcher* m, orbx_extractor* exL, orbx_extractor
   const int B = std::min(exL->p.max_batch, exR->p.max_batch);
   const int ncopy = std::min(capPerFrame, g.kpStride);
   const size_t kpRow = (size_t)g.kpStride * sizeof(orbx_keypoint), kpDst = (size_t)capPerFrame * sizeof(orbx_keypoint);
+  rc = stereo_prepare(m, exL, exR);
+  if (rc != ORBX_OK) return rc;
+  const bool useGraph = !m->noGraph && !exL->profile && !exR->profile;
   int chunk = 0;
   for (int f0 = 0; f0 < nframes; f0 += B, chunk++) {
     const int nb = std::min(B, nframes - f0), si = chunk & 1;
@@ -539,11 +596,39 @@ int orbx_stereo_frames_host(orbx_matcher* m, orbx_extractor* exL, orbx_extractor
         for (int f = 0; f < nb; f++)
           CK(cudaMemcpy2DAsync(s.in + (size_t)f * ex[e]->inPitch * height, ex[e]->inPitch, src + (size_t)f * frameStride, stride, width,
                                height, cudaMemcpyHostToDevice, st));
-      rc = extractor_run_batch(ex[e], si, s.in, nb, ex[e]->inPitch, (long long)ex[e]->inPitch * height, 0, 0, st);
-      if (rc != ORBX_OK) return rc;
+      if (!useGraph) {   // direct launches: the left extraction overlaps the right upload
+        rc = extractor_run_batch(ex[e], si, s.in, nb, ex[e]->inPitch, (long long)ex[e]->inPitch * height, 0, 0, st);
+        if (rc != ORBX_OK) return rc;
+      }
     }
-    rc = stereo_launch(m, exL, exR, si, mb, mbf, st);
-    if (rc != ORBX_OK) return rc;
+    if (!useGraph) {
+      rc = stereo_launch(m, exL, exR, si, mb, mbf, st, true);
+      if (rc != ORBX_OK) return rc;
+    } else {
+      orbx_matcher::ChunkGraph& cg = m->chunkGraph[si];
+      const bool hit = cg.exec && cg.nb == nb && cg.mb == mb && cg.mbf == mbf && cg.exL == exL && cg.exR == exR &&
+                       cg.epochL == exL->geomEpoch && cg.epochR == exR->geomEpoch && cg.epochM == m->sEpoch;
+      if (!hit) {
+        if (cg.exec) { CK(cudaGraphExecDestroy(cg.exec)); cg.exec = nullptr; }
+        cudaGraph_t graph = nullptr;
+        CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        for (int e = 0; e < 2 && rc == ORBX_OK; e++)
+          rc = extractor_run_batch(ex[e], si, ex[e]->slot[si].in, nb, ex[e]->inPitch, (long long)ex[e]->inPitch * height, 0, 0, st);
+        if (rc == ORBX_OK) rc = stereo_launch(m, exL, exR, si, mb, mbf, st, true);
+        const cudaError_t ce = cudaStreamEndCapture(st, &graph);
+        if (rc != ORBX_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+        CK(ce);
+        CK(cudaGraphInstantiate(&cg.exec, graph, 0));
+        CK(cudaGraphDestroy(graph));
+        cg.nb = nb; cg.mb = mb; cg.mbf = mbf; cg.exL = exL; cg.exR = exR;
+        cg.epochL = exL->geomEpoch; cg.epochR = exR->geomEpoch; cg.epochM = m->sEpoch;
+      } else {
+        // same bookkeeping as the captured calls made (the batch descriptors kept in the slots are unchanged)
+        for (int e = 0; e < 2; e++) { ex[e]->slot[si].lastFrames = nb; ex[e]->lastSlot = si; ex[e]->slot[si].evValid = false; }
+        m->sFrames = nb; m->sStride = g.kpStride; m->sHalf = (size_t)std::max(exL->p.max_batch, exR->p.max_batch) * g.kpStride; m->sLast = si;
+      }
+      CK(cudaGraphLaunch(cg.exec, st));
+    }
     orbx_keypoint* kd[2] = {kpsL, kpsR}; uint8_t* dd[2] = {descL, descR}; int* cd[2] = {countsL, countsR};
     for (int e = 0; e < 2; e++) {
       Slot& s = ex[e]->slot[si];

@@ -140,7 +140,7 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-STEREO_KERNELS = 3   # k_stereo_hamming, k_stereo_sad, k_stereo_median
+STEREO_KERNELS = 4   # k_stereo_rowtable, k_stereo_hamming2, k_stereo_sad, k_stereo_median
 
 
 def run_orbx(args):
@@ -238,7 +238,7 @@ def run_orbx(args):
 
     # end to end through the host-buffer C-ABI call: pinned images in; keypoints, descriptors, uRight, depth out
     cap = exL.max_keypoints(W, H)
-    nb = max(1, B // 4)   # 4 chunks per call -> copies overlap kernels
+    nb = max(1, B // args.e2e_chunks)   # chunks per call -> copies overlap kernels
     eL = orbx.ORBextractor(NFEAT, max_batch=nb, device=local)
     eR = orbx.ORBextractor(NFEAT, max_batch=nb, device=local)
     em = orbx.ORBmatcher(device=local)
@@ -269,10 +269,27 @@ def run_orbx(args):
         t = torch.tensor([e2e_s], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
+    # host<->device link speed on this box (the e2e ceiling: h2d bytes per step / link rate), pinned buffers, device timer
+    probe_d = torch.empty(64 << 20, dtype=torch.uint8, device="cuda")
+    probe_h = torch.empty(64 << 20, dtype=torch.uint8).pin_memory()
+    link = {}
+    for name, (dst, src) in {"h2d": (probe_d, probe_h), "d2h": (probe_h, probe_d)}.items():
+        dst.copy_(src, non_blocking=True)
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        p0.record(stream)
+        for _ in range(4):
+            dst.copy_(src, non_blocking=True)
+        p1.record(stream)
+        torch.cuda.synchronize()
+        link[name] = 4 * (64 << 20) / (p0.elapsed_time(p1) / 1e3) / 1e9
+    del probe_d, probe_h
     assert np.array_equal(ocL.numpy(), countsL) and np.array_equal(ouR.numpy()[:, :8], uR[:, :8]), "e2e and device-resident paths disagree"
     e2e = {"value": world * B * args.steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": 2 * B * W * H,
            "d2h_bytes_per_step": int(B * (2 * cap * 60 + cap * 8 + 8)), "timer": "host wall clock around the synchronous C-ABI call",
-           "api": "orbx_stereo_frames_host"}
+           "api": "orbx_stereo_frames_host", "chunks_per_call": args.e2e_chunks,
+           "link_gbs_measured": {k: round(v, 2) for k, v in link.items()},
+           "link_bound_frames_per_s": world * B / (2 * B * W * H / (link["h2d"] * 1e9))}
 
     # informational: mono extraction only at the shape the north-star target is quoted on (752x480, nFeatures 1000)
     gm = orbx.ORBextractor(1000, max_batch=B, device=local)
@@ -292,12 +309,12 @@ def run_orbx(args):
         ncpu = max(cores, min(2 * cores, 128))
         fps1, _, _ = cpu_stereo_sample(synth, 4, 2)
         secN, passes = 0.0, 0
-        while secN < 10.0 and passes < 40:   # bounded sample: ~10 s of CPU work on all host threads
+        while secN < (0.0 if args.skip_cpu else 10.0) and passes < 40:   # bounded sample: ~10 s of CPU work on all host threads
             _, s_, _ = cpu_stereo_sample(synth, ncpu, cores, seed=2000 + passes)
             secN += s_
             passes += 1
         ncpu *= passes
-        fpsN = ncpu / secN
+        fpsN = ncpu / secN if secN > 0 else 0.0
         cpu = {"value": fpsN, "unit": "frames/s", "cores": cores, "kind": "port",
                "sample": "%d stereo frames of the workload, frame-parallel with 2 threads per frame, %d threads (%.1f s); one frame at a time "
                          "(2 threads): %.1f frames/s" % (ncpu, cores, secN, fps1), "two_thread_value": fps1}
@@ -327,6 +344,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="orbx", choices=["orbx", "reference"])
     ap.add_argument("--batch", type=int, default=128)
+    ap.add_argument("--e2e-chunks", type=int, default=4, help="chunks per orbx_stereo_frames_host call (copy/compute overlap)")
+    ap.add_argument("--skip-cpu", action="store_true", help="development only: skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
