@@ -54,6 +54,34 @@ def lib():
     return _lib
 
 
+class HostBuffer:
+    """Page-locked host array from orbx_host_alloc (full-rate uploads / downloads); `.array` is a numpy view, freed on close()."""
+
+    def __init__(self, shape, dtype=np.uint8):
+        self.shape, self.dtype = tuple(int(x) for x in np.atleast_1d(shape)), np.dtype(dtype)
+        self.nbytes = int(np.prod(self.shape)) * self.dtype.itemsize
+        self._p = C.c_void_p()
+        _check(lib().orbx_host_alloc(C.c_size_t(max(self.nbytes, 1)), C.byref(self._p)))
+        buf = (C.c_uint8 * max(self.nbytes, 1)).from_address(self._p.value)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=int(np.prod(self.shape))).reshape(self.shape)
+
+    @property
+    def ptr(self):
+        return C.c_void_p(self._p.value)
+
+    def close(self):
+        if self._p is not None and self._p.value:
+            self.array = None
+            lib().orbx_host_free(self._p)
+            self._p = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def _check(rc):
     if rc < 0:
         raise OrbxError(rc, lib().orbx_last_error().decode())

@@ -52,9 +52,11 @@ static void free_geom(orbx_extractor* h) {
                     s.kps, s.desc, s.counts, s.mono};
     for (void* q : ptrs) if (q) cudaFree(q);
     if (s.hStatus) cudaFreeHost(s.hStatus);
-    cudaStream_t st = s.stream;
+    cudaStream_t st = s.stream, sd = s.side;
+    cudaEvent_t ef = s.evFork, ej = s.evJoin;
+    if (sd) cudaStreamSynchronize(sd);
     s = Slot();
-    s.stream = st;
+    s.stream = st; s.side = sd; s.evFork = ef; s.evJoin = ej;
   }
   if (h->dRsx) cudaFree(h->dRsx);
   if (h->dRsy) cudaFree(h->dRsy);
@@ -285,6 +287,16 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
     }
   }
   mark(2);
+  // The blur needs only the pyramid: it runs on the slot's side stream beside FAST -> quadtree -> assemble, whose last two
+  // kernels are short dependent chains (one CTA per level / frame) that leave most SMs idle.  Profiling mode keeps one stream.
+  const bool fork = !prof && !h->noFork;
+  cudaStream_t sb = fork ? s.side : st;
+  if (fork) { CK(cudaEventRecord(s.evFork, st)); CK(cudaStreamWaitEvent(sb, s.evFork, 0)); }
+  if (fork) {
+    if (h->blurV1) k_blur7<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, sb>>>(gg, b);
+    else k_blur7v<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, sb>>>(gg, b);
+    CK(cudaEventRecord(s.evJoin, sb));
+  }
   if (g.nTilesTotal > 0) {
     if (h->fastVer == 1) k_fast_nms_v1<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
     else if (h->fastVer == 2) k_fast_nms<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
@@ -293,10 +305,13 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
   mark(3);
   k_quadtree<<<dim3(g.nlevels, nframes), 256, h->qtSmem, st>>>(gg, b, s.nCand);
   mark(4);
-  if (h->blurV1) k_blur7<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, st>>>(gg, b);
-  else k_blur7v<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, st>>>(gg, b);
+  if (!fork) {
+    if (h->blurV1) k_blur7<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, st>>>(gg, b);
+    else k_blur7v<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, st>>>(gg, b);
+  }
   mark(5);
   k_assemble<<<nframes, 256, 0, st>>>(gg, b);
+  if (fork) CK(cudaStreamWaitEvent(st, s.evJoin, 0));
   mark(6);
   if (h->orientV1) k_orient_desc<<<dim3((g.kpSlab + 7) / 8, nframes), 256, 0, st>>>(gg, b);
   else k_orient_desc2<<<dim3((g.kpSlab + 7) / 8, nframes), 256, 0, st>>>(gg, b);
@@ -309,6 +324,18 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
 extern "C" {
 
 const char* orbx_last_error(void) { return g_err.c_str(); }
+
+int orbx_host_alloc(size_t bytes, void** ptr) {
+  if (!ptr || bytes == 0) return ORBX_ERR_ARG;
+  *ptr = nullptr;
+  CK(cudaHostAlloc(ptr, bytes, cudaHostAllocPortable));
+  return ORBX_OK;
+}
+int orbx_host_free(void* ptr) {
+  if (!ptr) return ORBX_OK;
+  CK(cudaFreeHost(ptr));
+  return ORBX_OK;
+}
 const char* orbx_version(void) { return "orbx 0.1 (sm_100a)"; }
 
 int orbx_create(const orbx_params* p, orbx_extractor** out) {
@@ -363,7 +390,12 @@ int orbx_create(const orbx_params* p, orbx_extractor** out) {
     }
   }
   for (Slot& s : h->slot)
-    if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; set_error("stream creation failed"); return ORBX_ERR_CUDA; }
+    if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess || cudaStreamCreateWithFlags(&s.side, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s.evFork, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&s.evJoin, cudaEventDisableTiming) != cudaSuccess) {
+      delete h; set_error("stream creation failed"); return ORBX_ERR_CUDA;
+    }
+  // measured: beside a concurrently running second extractor the fork gains nothing on the device path and costs 9 % end to end
+  { const char* e = getenv("ORBX_FORK"); h->noFork = !(e && e[0] == '1'); }
   float patF[1024];   // pair 8 * lane + j  ->  record j * 32 + lane (k_orient_desc2 reads [j][lane])
   for (int pr = 0; pr < 256; pr++)
     for (int k = 0; k < 4; k++) patF[((pr & 7) * 32 + (pr >> 3)) * 4 + k] = (float)kPatternHost[pr * 4 + k];
@@ -382,7 +414,12 @@ int orbx_create(const orbx_params* p, orbx_extractor** out) {
 void orbx_destroy(orbx_extractor* h) {
   if (!h) return;
   free_geom(h);
-  for (Slot& s : h->slot) if (s.stream) cudaStreamDestroy(s.stream);
+  for (Slot& s : h->slot) {
+    if (s.stream) cudaStreamDestroy(s.stream);
+    if (s.side) cudaStreamDestroy(s.side);
+    if (s.evFork) cudaEventDestroy(s.evFork);
+    if (s.evJoin) cudaEventDestroy(s.evJoin);
+  }
   if (h->dPattern) cudaFree(h->dPattern);
   delete h;
 }

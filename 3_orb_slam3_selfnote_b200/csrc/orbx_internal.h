@@ -21,6 +21,8 @@ void set_error(const char* fmt, ...);
 
 struct Slot {
   cudaStream_t stream = nullptr;
+  cudaStream_t side = nullptr;            // blur branch of a batch (runs beside FAST -> quadtree -> assemble)
+  cudaEvent_t evFork = nullptr, evJoin = nullptr;
   uint8_t* in = nullptr;  // staged level-0 frames for the host path [max_batch][h][inPitch]
   uint8_t* pyr = nullptr;
   uint8_t* blur = nullptr;
@@ -59,6 +61,7 @@ struct orbx_extractor {
   int lastSlot = 0;
   bool profile = false;
   bool resizeV1 = false, blurV1 = false, orientV1 = false;
+  bool noFork = true;    // ORBX_FORK=1: run the blur on the slot's side stream beside FAST -> quadtree -> assemble (A/B only)
   size_t rsSmem = 0;
   int fastVer = 3;      // ORBX_FAST_V1=1 / ORBX_FAST_V2=1: run an earlier FAST kernel instead of k_fast_nms3 (A/B only)
 };

@@ -2,6 +2,7 @@
 // its loop prologues) and the extern "C" entry points of include/orbx.h.  All distance / search work is in match_kernels.cuh.
 #include <cuda_runtime.h>
 #include <math.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -31,12 +32,22 @@ struct orbx_matcher {
   // CUDA graph of one chunk of orbx_stereo_frames_host (extract L + extract R + stereo kernels), one per slot: the call is
   // bound by the host's launch rate otherwise (~30 launches with 2 KB of parameters each per chunk)
   struct ChunkGraph {
-    cudaGraphExec_t exec = nullptr;
+    cudaGraphExec_t execL = nullptr, execR = nullptr, execS = nullptr;   // extract left / extract right / stereo kernels
     int nb = 0; float mb = 0, mbf = 0;
     const orbx_extractor* exL = nullptr; const orbx_extractor* exR = nullptr;
     unsigned long long epochL = 0, epochR = 0, epochM = 0;
-  } chunkGraph[2];
+    void reset() {
+      for (cudaGraphExec_t* e : {&execL, &execR, &execS}) { if (*e) cudaGraphExecDestroy(*e); *e = nullptr; }
+    }
+  } chunkGraph[2][4];    // [slot][entry]: a call's chunks come in up to three sizes (ramped first, full, tail)
+  int chunkGraphNext[2] = {0, 0};
   bool noGraph = false;    // ORBX_NO_GRAPH=1
+  // orbx_stereo_frames_host pipeline: one upload stream feeds both slots in issue order; per slot: images uploaded (left, right),
+  // right branch joined, input buffers free again (both extractions done), slot's downloads done
+  cudaStream_t upStream = nullptr;
+  cudaEvent_t evUpL[2] = {}, evUpR[2] = {}, evJoin[2] = {}, evInFree[2] = {}, evSlotDone[2] = {};
+  int* hStat = nullptr;    // pinned: device status words of every chunk of a call (2 per chunk)
+  static constexpr int kStatChunks = 256;
 };
 
 namespace {
@@ -286,7 +297,13 @@ int orbx_matcher_create(int device, orbx_matcher** out) {
   m->device = device;
   { const char* e = getenv("ORBX_STEREO_V1"); m->stereoV1 = e && e[0] == '1'; }
   { const char* e = getenv("ORBX_NO_GRAPH"); m->noGraph = e && e[0] == '1'; }
-  if (cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess || cudaMalloc(&m->dStatus, sizeof(int)) != cudaSuccess) {
+  bool evOk = true;
+  for (int i = 0; i < 2; i++)
+    for (cudaEvent_t* e : {&m->evUpL[i], &m->evUpR[i], &m->evJoin[i], &m->evInFree[i], &m->evSlotDone[i]})
+      evOk = evOk && cudaEventCreateWithFlags(e, cudaEventDisableTiming) == cudaSuccess;
+  evOk = evOk && cudaStreamCreateWithFlags(&m->upStream, cudaStreamNonBlocking) == cudaSuccess &&
+         cudaHostAlloc(&m->hStat, 2 * orbx_matcher::kStatChunks * sizeof(int), cudaHostAllocDefault) == cudaSuccess;
+  if (!evOk || cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking) != cudaSuccess || cudaMalloc(&m->dStatus, sizeof(int)) != cudaSuccess) {
     delete m; set_error("matcher resources"); return ORBX_ERR_CUDA;
   }
   *out = m;
@@ -299,7 +316,11 @@ void orbx_matcher_destroy(orbx_matcher* m) {
   cudaStreamSynchronize(m->stream);
   void* ptrs[] = {m->arena, m->dStatus, m->sURight, m->sDepth, m->sBestDist, m->sBestIdx, m->sSad, m->sRowStart, m->sRowItems};
   for (void* p : ptrs) if (p) cudaFree(p);
-  for (auto& cg : m->chunkGraph) if (cg.exec) cudaGraphExecDestroy(cg.exec);
+  for (auto& slot : m->chunkGraph) for (auto& cg : slot) cg.reset();
+  for (int i = 0; i < 2; i++)
+    for (cudaEvent_t e : {m->evUpL[i], m->evUpR[i], m->evJoin[i], m->evInFree[i], m->evSlotDone[i]}) if (e) cudaEventDestroy(e);
+  if (m->upStream) cudaStreamDestroy(m->upStream);
+  if (m->hStat) cudaFreeHost(m->hStat);
   cudaStreamDestroy(m->stream);
   delete m;
 }
@@ -575,51 +596,75 @@ int orbx_stereo_frames_host(orbx_matcher* m, orbx_extractor* exL, orbx_extractor
   const Geom& g = exL->g;
   const int B = std::min(exL->p.max_batch, exR->p.max_batch);
   const int ncopy = std::min(capPerFrame, g.kpStride);
-  const size_t kpRow = (size_t)g.kpStride * sizeof(orbx_keypoint), kpDst = (size_t)capPerFrame * sizeof(orbx_keypoint);
   rc = stereo_prepare(m, exL, exR);
   if (rc != ORBX_OK) return rc;
   const bool useGraph = !m->noGraph && !exL->profile && !exR->profile;
+  // ORBX_TRACE=1 (development): device timeline of the call, one line per chunk on stderr
+  static const bool trace = [] { const char* e = getenv("ORBX_TRACE"); return e && e[0] == '1'; }();
+  std::vector<cudaEvent_t> tev;
+  auto tmark = [&](cudaStream_t cs) { if (trace) { cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, cs); tev.push_back(e); } };
+  tmark(exL->slot[0].stream);
+  // Chunk schedule: the call's latency is upload(first chunk, left) + kernels + download(last chunk), and a chunk's kernel time
+  // has a fixed part (~0.1 ms of short dependent kernels), so the first chunk is a quarter of the others.
+  const int first = (nframes > B / 4 && B >= 8) ? B / 4 : B;
   int chunk = 0;
-  for (int f0 = 0; f0 < nframes; f0 += B, chunk++) {
-    const int nb = std::min(B, nframes - f0), si = chunk & 1;
-    cudaStream_t st = exL->slot[si].stream;
+  for (int f0 = 0; f0 < nframes; chunk++) {
+    const int nb = std::min(chunk == 0 ? first : B, nframes - f0), si = chunk & 1;
+    cudaStream_t st = exL->slot[si].stream, stR = exR->slot[si].stream;
     orbx_extractor* ex[2] = {exL, exR};
     const uint8_t* img[2] = {imagesL, imagesR};
-    for (int e = 0; e < 2; e++) {
+    auto upload = [&](int e, cudaStream_t cs) -> int {
       Slot& s = ex[e]->slot[si];
       const uint8_t* src = img[e] + (size_t)f0 * frameStride;
       if (frameStride == (size_t)stride * height && stride == ex[e]->inPitch)
-        CK(cudaMemcpyAsync(s.in, src, (size_t)stride * height * nb, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(s.in, src, (size_t)stride * height * nb, cudaMemcpyHostToDevice, cs));
       else if (frameStride == (size_t)stride * height)
-        CK(cudaMemcpy2DAsync(s.in, ex[e]->inPitch, src, stride, width, (size_t)height * nb, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpy2DAsync(s.in, ex[e]->inPitch, src, stride, width, (size_t)height * nb, cudaMemcpyHostToDevice, cs));
       else
         for (int f = 0; f < nb; f++)
           CK(cudaMemcpy2DAsync(s.in + (size_t)f * ex[e]->inPitch * height, ex[e]->inPitch, src + (size_t)f * frameStride, stride, width,
-                               height, cudaMemcpyHostToDevice, st));
-      if (!useGraph) {   // direct launches: the left extraction overlaps the right upload
-        rc = extractor_run_batch(ex[e], si, s.in, nb, ex[e]->inPitch, (long long)ex[e]->inPitch * height, 0, 0, st);
-        if (rc != ORBX_OK) return rc;
+                               height, cudaMemcpyHostToDevice, cs));
+      return ORBX_OK;
+    };
+    auto extract = [&](int e, cudaStream_t cs) -> int {
+      return extractor_run_batch(ex[e], si, ex[e]->slot[si].in, nb, ex[e]->inPitch, (long long)ex[e]->inPitch * height, 0, 0, cs);
+    };
+    if (!useGraph) {   // direct launches on one stream: the left extraction overlaps the right upload
+      for (int e = 0; e < 2; e++) {
+        if ((rc = upload(e, st)) != ORBX_OK) return rc;
+        if ((rc = extract(e, st)) != ORBX_OK) return rc;
       }
-    }
-    if (!useGraph) {
-      rc = stereo_launch(m, exL, exR, si, mb, mbf, st, true);
-      if (rc != ORBX_OK) return rc;
+      if ((rc = stereo_launch(m, exL, exR, si, mb, mbf, st, true)) != ORBX_OK) return rc;
     } else {
-      orbx_matcher::ChunkGraph& cg = m->chunkGraph[si];
-      const bool hit = cg.exec && cg.nb == nb && cg.mb == mb && cg.mbf == mbf && cg.exL == exL && cg.exR == exR &&
-                       cg.epochL == exL->geomEpoch && cg.epochR == exR->geomEpoch && cg.epochM == m->sEpoch;
+      // Three graphs per chunk.  The two extractions are independent branches, like the reference's two threads
+      // (src/Frame.cc:120-123): left on the slot stream of exL, right on the slot stream of exR; the right upload is ordered
+      // behind the left one so the left extraction starts as soon as its own images have arrived.  Everything that used this
+      // slot before has completed (the host waits for a slot's previous chunk before reusing it).
+      auto matches = [&](const orbx_matcher::ChunkGraph& c) {
+        return c.execL && c.nb == nb && c.mb == mb && c.mbf == mbf && c.exL == exL && c.exR == exR && c.epochL == exL->geomEpoch &&
+               c.epochR == exR->geomEpoch && c.epochM == m->sEpoch;
+      };
+      int ci = -1;
+      for (int k = 0; k < 4; k++) if (matches(m->chunkGraph[si][k])) ci = k;
+      const bool hit = ci >= 0;
+      if (!hit) { ci = m->chunkGraphNext[si]; m->chunkGraphNext[si] = (ci + 1) & 3; }
+      orbx_matcher::ChunkGraph& cg = m->chunkGraph[si][ci];
       if (!hit) {
-        if (cg.exec) { CK(cudaGraphExecDestroy(cg.exec)); cg.exec = nullptr; }
-        cudaGraph_t graph = nullptr;
-        CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-        for (int e = 0; e < 2 && rc == ORBX_OK; e++)
-          rc = extractor_run_batch(ex[e], si, ex[e]->slot[si].in, nb, ex[e]->inPitch, (long long)ex[e]->inPitch * height, 0, 0, st);
-        if (rc == ORBX_OK) rc = stereo_launch(m, exL, exR, si, mb, mbf, st, true);
-        const cudaError_t ce = cudaStreamEndCapture(st, &graph);
-        if (rc != ORBX_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
-        CK(ce);
-        CK(cudaGraphInstantiate(&cg.exec, graph, 0));
-        CK(cudaGraphDestroy(graph));
+        cg.reset();
+        auto capture = [&](cudaStream_t cs, cudaGraphExec_t* out, auto&& body) -> int {
+          cudaGraph_t graph = nullptr;
+          CK(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+          const int brc = body(cs);
+          const cudaError_t ce = cudaStreamEndCapture(cs, &graph);
+          if (brc != ORBX_OK) { if (graph) cudaGraphDestroy(graph); return brc; }
+          CK(ce);
+          CK(cudaGraphInstantiate(out, graph, 0));
+          CK(cudaGraphDestroy(graph));
+          return ORBX_OK;
+        };
+        if ((rc = capture(st, &cg.execL, [&](cudaStream_t cs) { return extract(0, cs); })) != ORBX_OK) return rc;
+        if ((rc = capture(stR, &cg.execR, [&](cudaStream_t cs) { return extract(1, cs); })) != ORBX_OK) return rc;
+        if ((rc = capture(st, &cg.execS, [&](cudaStream_t cs) { return stereo_launch(m, exL, exR, si, mb, mbf, cs, true); })) != ORBX_OK) return rc;
         cg.nb = nb; cg.mb = mb; cg.mbf = mbf; cg.exL = exL; cg.exR = exR;
         cg.epochL = exL->geomEpoch; cg.epochR = exR->geomEpoch; cg.epochM = m->sEpoch;
       } else {
@@ -627,25 +672,72 @@ int orbx_stereo_frames_host(orbx_matcher* m, orbx_extractor* exL, orbx_extractor
         for (int e = 0; e < 2; e++) { ex[e]->slot[si].lastFrames = nb; ex[e]->lastSlot = si; ex[e]->slot[si].evValid = false; }
         m->sFrames = nb; m->sStride = g.kpStride; m->sHalf = (size_t)std::max(exL->p.max_batch, exR->p.max_batch) * g.kpStride; m->sLast = si;
       }
-      CK(cudaGraphLaunch(cg.exec, st));
+      // uploads: one stream for the whole call, so the link carries L0 R0 L1 R1 ... in that order without waiting for kernels
+      tmark(m->upStream);
+      CK(cudaStreamWaitEvent(m->upStream, m->evInFree[si], 0));    // the slot's previous extractions have consumed their inputs
+      if ((rc = upload(0, m->upStream)) != ORBX_OK) return rc;
+      CK(cudaEventRecord(m->evUpL[si], m->upStream));
+      tmark(m->upStream);
+      if ((rc = upload(1, m->upStream)) != ORBX_OK) return rc;
+      CK(cudaEventRecord(m->evUpR[si], m->upStream));
+      tmark(m->upStream);
+      // right branch (behind the slot's previous downloads, which ran on the left stream)
+      CK(cudaStreamWaitEvent(stR, m->evSlotDone[si], 0));
+      CK(cudaStreamWaitEvent(stR, m->evUpR[si], 0));
+      CK(cudaGraphLaunch(cg.execR, stR));
+      CK(cudaEventRecord(m->evJoin[si], stR));
+      tmark(stR);
+      // left branch, join, stereo
+      CK(cudaStreamWaitEvent(st, m->evUpL[si], 0));
+      CK(cudaGraphLaunch(cg.execL, st));
+      tmark(st);
+      CK(cudaStreamWaitEvent(st, m->evJoin[si], 0));
+      CK(cudaEventRecord(m->evInFree[si], st));
+      CK(cudaGraphLaunch(cg.execS, st));
+      tmark(st);
     }
     orbx_keypoint* kd[2] = {kpsL, kpsR}; uint8_t* dd[2] = {descL, descR}; int* cd[2] = {countsL, countsR};
+    // downloads: rows of `ncopy` records per frame; one linear copy when the caller's capacity equals the device stride
+    auto download = [&](void* dst, const void* src, size_t rec) -> int {
+      if (capPerFrame == g.kpStride) CK(cudaMemcpyAsync(dst, src, rec * g.kpStride * nb, cudaMemcpyDeviceToHost, st));
+      else CK(cudaMemcpy2DAsync(dst, rec * capPerFrame, src, rec * g.kpStride, rec * ncopy, nb, cudaMemcpyDeviceToHost, st));
+      return ORBX_OK;
+    };
     for (int e = 0; e < 2; e++) {
       Slot& s = ex[e]->slot[si];
       CK(cudaMemcpyAsync(cd[e] + f0, s.counts, nb * sizeof(int), cudaMemcpyDeviceToHost, st));
-      CK(cudaMemcpy2DAsync(kd[e] + (size_t)f0 * capPerFrame, kpDst, s.kps, kpRow, (size_t)ncopy * sizeof(orbx_keypoint), nb, cudaMemcpyDeviceToHost, st));
-      CK(cudaMemcpy2DAsync(dd[e] + (size_t)f0 * capPerFrame * 32, (size_t)capPerFrame * 32, s.desc, (size_t)g.kpStride * 32, (size_t)ncopy * 32, nb,
-                           cudaMemcpyDeviceToHost, st));
+      if ((rc = download(kd[e] + (size_t)f0 * capPerFrame, s.kps, sizeof(orbx_keypoint))) != ORBX_OK) return rc;
+      if ((rc = download(dd[e] + (size_t)f0 * capPerFrame * 32, s.desc, 32)) != ORBX_OK) return rc;
       CK(cudaMemcpyAsync(s.hStatus, s.status, sizeof(int), cudaMemcpyDeviceToHost, st));
+      CK(cudaMemcpyAsync(m->hStat + 2 * (chunk % orbx_matcher::kStatChunks) + e, s.status, sizeof(int), cudaMemcpyDeviceToHost, st));
     }
     const size_t o = (size_t)si * m->sHalf;
-    CK(cudaMemcpy2DAsync(uRight + (size_t)f0 * capPerFrame, (size_t)capPerFrame * 4, m->sURight + o, (size_t)g.kpStride * 4, (size_t)ncopy * 4, nb,
-                         cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpy2DAsync(depth + (size_t)f0 * capPerFrame, (size_t)capPerFrame * 4, m->sDepth + o, (size_t)g.kpStride * 4, (size_t)ncopy * 4, nb,
-                         cudaMemcpyDeviceToHost, st));
-    if (chunk >= 1) CK(cudaStreamSynchronize(exL->slot[si ^ 1].stream));  // at most two chunks in flight
+    if ((rc = download(uRight + (size_t)f0 * capPerFrame, m->sURight + o, 4)) != ORBX_OK) return rc;
+    if ((rc = download(depth + (size_t)f0 * capPerFrame, m->sDepth + o, 4)) != ORBX_OK) return rc;
+    tmark(st);
+    CK(cudaEventRecord(m->evSlotDone[si], st));
+    f0 += nb;
+    const bool wrap = (chunk + 1) % orbx_matcher::kStatChunks == 0;
+    if (!useGraph) {
+      if (chunk >= 1) CK(cudaStreamSynchronize(exL->slot[si ^ 1].stream));  // one stream per slot: at most two chunks in flight
+    } else if (wrap || f0 >= nframes) {
+      // graph pipeline: slot reuse is ordered by events on the device, the host only waits at the end (or when the status ring wraps)
+      for (int k = 0; k < 2; k++) CK(cudaStreamSynchronize(exL->slot[k].stream));
+      const int used = wrap ? orbx_matcher::kStatChunks : (chunk % orbx_matcher::kStatChunks) + 1;
+      for (int k = 0; k < 2 * used; k++)
+        if (m->hStat[k] != 0) { set_error("device reported status %d (capacity)", m->hStat[k]); return m->hStat[k]; }
+    }
   }
   for (int si = 0; si < 2; si++) CK(cudaStreamSynchronize(exL->slot[si].stream));
+  if (trace && useGraph) {
+    static const char* kName[7] = {"begin", "upL", "upR", "extR", "extL", "stereo", "d2h"};
+    for (size_t c = 0; 1 + 7 * (c + 1) <= tev.size(); c++) {
+      fprintf(stderr, "[orbx trace] chunk %zu:", c);
+      for (int k = 0; k < 7; k++) { float ms = 0; cudaEventElapsedTime(&ms, tev[0], tev[1 + 7 * c + k]); fprintf(stderr, " %s %.3f", kName[k], ms); }
+      fprintf(stderr, "\n");
+    }
+  }
+  for (cudaEvent_t e : tev) cudaEventDestroy(e);
   for (int si = 0; si < 2; si++)
     for (orbx_extractor* e : {exL, exR})
       if (e->slot[si].lastFrames > 0 && *e->slot[si].hStatus != 0) { set_error("device reported status %d (capacity)", *e->slot[si].hStatus); return *e->slot[si].hStatus; }

@@ -161,8 +161,7 @@ def run_orbx(args):
     reps = (B + distinct - 1) // distinct
     hostL = np.concatenate([synth.frames(W, H, 1000 + rank, range(distinct), False)] * reps)[:B]
     hostR = np.concatenate([synth.frames(W, H, 1000 + rank, range(distinct), True)] * reps)[:B]
-    pinL, pinR = torch.from_numpy(hostL).pin_memory(), torch.from_numpy(hostR).pin_memory()
-    devL, devR = pinL.cuda(), pinR.cuda()
+    devL, devR = torch.from_numpy(hostL).cuda(), torch.from_numpy(hostR).cuda()
     exL = orbx.ORBextractor(NFEAT, max_batch=B, device=local)
     exR = orbx.ORBextractor(NFEAT, max_batch=B, device=local)
     mt = orbx.ORBmatcher(device=local)
@@ -170,9 +169,19 @@ def run_orbx(args):
     torch.cuda.set_stream(stream)
     sh = stream.cuda_stream
 
+    # the two extractor objects run concurrently, as the reference's two threads do (src/Frame.cc:120-123): the right image goes
+    # on a second stream; the stereo matcher joins them.  Timing events sit on `stream`, which waits for the right branch.
+    streamR = torch.cuda.Stream()
+    shR = streamR.cuda_stream
+    evFork, evJoin = torch.cuda.Event(), torch.cuda.Event()
+
     def step():
+        evFork.record(stream)
+        streamR.wait_event(evFork)
+        exR.extract_batch_device(devR.data_ptr(), B, W, H, W, W * H, (0, 0), shR)
+        evJoin.record(streamR)
         exL.extract_batch_device(devL.data_ptr(), B, W, H, W, W * H, (0, 0), sh)
-        exR.extract_batch_device(devR.data_ptr(), B, W, H, W, W * H, (0, 0), sh)
+        stream.wait_event(evJoin)
         mt.stereo_match_batch(exL, exR, MB, MBF, sh)
 
     nwarm = max(args.warmup, 3)
@@ -242,15 +251,20 @@ def run_orbx(args):
     eL = orbx.ORBextractor(NFEAT, max_batch=nb, device=local)
     eR = orbx.ORBextractor(NFEAT, max_batch=nb, device=local)
     em = orbx.ORBmatcher(device=local)
-    pin = lambda shape, dt: torch.empty(shape, dtype=dt).pin_memory()
-    okL, okR = pin((B, cap, 28), torch.uint8), pin((B, cap, 28), torch.uint8)
-    odL, odR = pin((B, cap, 32), torch.uint8), pin((B, cap, 32), torch.uint8)
-    ocL, ocR = pin((B,), torch.int32), pin((B,), torch.int32)
-    ouR, odp = pin((B, cap), torch.float32), pin((B, cap), torch.float32)
-    vp = lambda t: C.c_void_p(t.data_ptr())
+    # host buffers of the e2e call come from orbx_host_alloc (cudaHostAlloc): torch's pin_memory() buffers upload at half the link rate here
+    hb = lambda shape, dt: orbx.HostBuffer(shape, dt)
+    hinL, hinR = hb((B, H, W), np.uint8), hb((B, H, W), np.uint8)
+    hinL.array[...] = hostL
+    hinR.array[...] = hostR
+    okL, okR = hb((B, cap, 28), np.uint8), hb((B, cap, 28), np.uint8)
+    odL, odR = hb((B, cap, 32), np.uint8), hb((B, cap, 32), np.uint8)
+    ocL, ocR = hb((B,), np.int32), hb((B,), np.int32)
+    ouR, odp = hb((B, cap), np.float32), hb((B, cap), np.float32)
+    hbufs = [hinL, hinR, okL, okR, odL, odR, ocL, ocR, ouR, odp]
+    vp = lambda t: t.ptr
 
     def e2e_step():
-        rc = orbx.lib().orbx_stereo_frames_host(em._m, eL._h, eR._h, vp(pinL), vp(pinR), B, W, H, W, C.c_size_t(W * H), C.c_float(MB),
+        rc = orbx.lib().orbx_stereo_frames_host(em._m, eL._h, eR._h, vp(hinL), vp(hinR), B, W, H, W, C.c_size_t(W * H), C.c_float(MB),
                                                 C.c_float(MBF), vp(okL), vp(odL), vp(ocL), vp(okR), vp(odR), vp(ocR), vp(ouR), vp(odp), cap)
         if rc != 0:
             raise RuntimeError("orbx_stereo_frames_host failed: %d %s" % (rc, orbx.lib().orbx_last_error()))
@@ -271,20 +285,23 @@ def run_orbx(args):
         e2e_s = float(t.item())
     # host<->device link speed on this box (the e2e ceiling: h2d bytes per step / link rate), pinned buffers, device timer
     probe_d = torch.empty(64 << 20, dtype=torch.uint8, device="cuda")
-    probe_h = torch.empty(64 << 20, dtype=torch.uint8).pin_memory()
+    probe_h = orbx.HostBuffer((64 << 20,), np.uint8)
+    probe_h.array[...] = 1
+    rt = C.CDLL("libcudart.so.12")
     link = {}
-    for name, (dst, src) in {"h2d": (probe_d, probe_h), "d2h": (probe_h, probe_d)}.items():
-        dst.copy_(src, non_blocking=True)
+    for name, (dst, src, kind) in {"h2d": (C.c_void_p(probe_d.data_ptr()), probe_h.ptr, 1), "d2h": (probe_h.ptr, C.c_void_p(probe_d.data_ptr()), 2)}.items():
         p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        rt.cudaMemcpyAsync(dst, src, C.c_size_t(64 << 20), C.c_int(kind), C.c_void_p(sh))
         torch.cuda.synchronize()
         p0.record(stream)
         for _ in range(4):
-            dst.copy_(src, non_blocking=True)
+            rt.cudaMemcpyAsync(dst, src, C.c_size_t(64 << 20), C.c_int(kind), C.c_void_p(sh))
         p1.record(stream)
         torch.cuda.synchronize()
         link[name] = 4 * (64 << 20) / (p0.elapsed_time(p1) / 1e3) / 1e9
-    del probe_d, probe_h
-    assert np.array_equal(ocL.numpy(), countsL) and np.array_equal(ouR.numpy()[:, :8], uR[:, :8]), "e2e and device-resident paths disagree"
+    del probe_d
+    probe_h.close()
+    assert np.array_equal(ocL.array, countsL) and np.array_equal(ouR.array[:, :8], uR[:, :8]), "e2e and device-resident paths disagree"
     e2e = {"value": world * B * args.steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": 2 * B * W * H,
            "d2h_bytes_per_step": int(B * (2 * cap * 60 + cap * 8 + 8)), "timer": "host wall clock around the synchronous C-ABI call",
            "api": "orbx_stereo_frames_host", "chunks_per_call": args.e2e_chunks,
@@ -331,7 +348,7 @@ def run_orbx(args):
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
                 "extra": {"mono_extract_752x480_nfeat1000_frames_per_s_per_gpu": mono_fps}}
         print(json.dumps(line), flush=True)
-    for o in (exL, exR, mt, eL, eR, em, gm):
+    for o in [exL, exR, mt, eL, eR, em, gm] + hbufs:
         o.close()
     if world > 1:
         dist.destroy_process_group()

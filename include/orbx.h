@@ -219,6 +219,13 @@ int orbx_stereo_frames_host(orbx_matcher* m, orbx_extractor* left, orbx_extracto
 int orbx_stereo_results_host(orbx_matcher* m, float* u_right, float* depth, int* best_dist, int* best_idx,
                              int capacity_per_frame);
 
+/* Page-locked host staging buffers for the *_host entry points (cudaHostAlloc).  Frames handed over in such a buffer upload at
+ * the full link rate; memory pinned after the fact (cudaHostRegister of pageable pages, which is what e.g. torch's
+ * pin_memory() produced on the test box) was measured at half of it (27 vs 55 GB/s host-to-device on PCIe 5 x16).  The
+ * reference has no counterpart: its cv::Mat frames live in pageable memory (Examples/Stereo/stereo_euroc.cc:166-167). */
+int orbx_host_alloc(size_t bytes, void** ptr);
+int orbx_host_free(void* ptr);
+
 const char* orbx_last_error(void);
 const char* orbx_version(void);
 
