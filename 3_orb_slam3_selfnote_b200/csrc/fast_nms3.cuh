@@ -9,10 +9,13 @@
 //   0. stages a 70x70 window for a 62x62 output tile (halo overhead 27 % instead of 43 %), all loads of a warp issued
 //      before the first use; words are stored at their natural 4-byte alignment (no funnel shift), the two u16-pair copies
 //      (even / odd first column) swap roles with the parity of the window origin instead;
-//   1. evaluates the 4-point compass bound for every pixel pair and appends the survivors to a shared-memory list
-//      (ballot + one shared atomic per warp row);
+//   1. evaluates the 4-point compass bound for every pixel pair and appends the survivors to a per-warp shared-memory list
+//      (ballot + popc, no atomics, no CTA barrier before step 2: a warp scores the pairs of its own rows);
 //   2. computes the full 16-arc score only for list entries (dense warps again: VIMNMX3.U16x2, 82 per pair);
-//   3. runs the NMS / emission only for list entries whose score is non-zero.
+//   3. runs the NMS only for list entries whose score is non-zero; kept pixels are gathered in shared memory and written
+//      with one global atomic per CTA and coalesced 8-byte records.
+// (profiles/r01c, first cut of this kernel: 38 % of the instructions were step 1 -- 63 per warp row, half of them the per-row
+// shared atomic + shuffle and generic-pointer address arithmetic -- and 26 % step 3's divergent per-warp emission.)
 // Output: pre-candidate records (x, y, cell, S) with S > minTh in arbitrary order + per-cell "has S > iniTh" flags; the
 // quadtree kernel orders them and applies the per-cell threshold fallback (src/ORBextractor.cc:825-828).
 // Algorithmic bytes per launch: read every level once.
@@ -27,23 +30,26 @@ constexpr int kF3SW = 64, kF3SH = 64;         // score tile (one halo pixel each
 constexpr int kF3WinH = kF3SH + 6;            // 70 window rows
 constexpr int kF3Pitch = 38;                  // u16-pair words per window row (76 columns >= 3 + 70 + 1)
 constexpr int kF3RowsPerWarp = (kF3WinH + 7) / 8;
+constexpr int kF3Copy = kF3WinH * kF3Pitch;   // words per pair copy
+constexpr int kF3SPitch = 32, kF3SSlack = 34; // score rows: 32 pair words (33 = one pad word: fewer conflicts in step 3, measured 3 % slower); slack before / after the tile
+constexpr int kF3OutCap = 1024;               // kept pixels per tile: 3x3 local maxima, at most one per 2x2 block (961)
 
-struct F3Bases { const uint32_t* e; const uint32_t* o; };   // pair copies for even / odd dx, offsets folded in
-
+// ring pixel pair (DX, DY) of the pair whose centre word is at eIdx (even dx) / oIdx (odd dx); both are word indices into sW
 template <int DX, int DY>
-__device__ __forceinline__ uint32_t f3ring(const F3Bases& s, int idx) {   // idx = (sr + 3) * pitch + p
+__device__ __forceinline__ uint32_t f3ring(const uint32_t* sW, int eIdx, int oIdx) {
   constexpr bool odd = (DX & 1) != 0;
-  if (odd) return s.o[idx + DY * kF3Pitch + (DX + 1) / 2];
-  return s.e[idx + DY * kF3Pitch + DX / 2];
+  if (odd) return sW[oIdx + DY * kF3Pitch + (DX + 1) / 2];
+  return sW[eIdx + DY * kF3Pitch + DX / 2];
 }
 
 __global__ void __launch_bounds__(256) k_fast_nms3(const __grid_constant__ Geom g, const __grid_constant__ Batch b) {
-  __shared__ __align__(16) uint32_t sA[kF3WinH * kF3Pitch];   // (col 2j, 2j+1) relative to the aligned window origin
-  __shared__ __align__(16) uint32_t sB[kF3WinH * kF3Pitch];   // (col 2j+1, 2j+2)
-  __shared__ uint32_t sS[kF3SH * 32 + 64];                    // 64x64 scores as u16 pairs, 32 words of slack each side
-  __shared__ uint16_t sList[kF3SH * 32];                      // surviving pairs: sr * 32 + p
+  // pair copy A = (col 2j, 2j+1) at [0, kF3Copy), copy B = (col 2j+1, 2j+2) at [kF3Copy, 2 kF3Copy), columns relative to the
+  // aligned window origin; after step 2 the same memory holds the kept pixels of the tile
+  __shared__ __align__(16) uint32_t sW[2 * kF3Copy];
+  __shared__ uint32_t sS[kF3SH * kF3SPitch + 2 * kF3SSlack];  // 64x64 scores as u16 pairs (+1 pad word per row), slack words each side
+  __shared__ uint16_t sList[8][kF3SH * 32 / 8];               // per warp: surviving pairs of its rows, sr * 32 + p
   __shared__ uint16_t sCol[kF3SW], sRow[kF3SH];               // cell info of the tile's columns / rows
-  __shared__ int sN;
+  __shared__ int sNOut, sBase;
 
   const int tid = threadIdx.x, warp = tid >> 5, p = tid & 31;
   const int f = blockIdx.y;
@@ -58,10 +64,11 @@ __global__ void __launch_bounds__(256) k_fast_nms3(const __grid_constant__ Geom 
   const int maxX = L.w - kEdge, maxY = L.h - kEdge;                  // region = [kEdge, max)
   int sp;
   const uint8_t* src = level_ptr(g, b, level, f, sp);
-  uint32_t* const S = sS + 32;
+  uint32_t* const S = sS + kF3SSlack;   // score pair (sr, q) at S[sr * kF3SPitch + q]
 
-  if (tid == 0) sN = 0;
-  if (tid >= 192) { sS[tid - 192 >= 32 ? kF3SH * 32 + tid - 192 : tid - 192] = 0; }   // slack words are read as (masked) neighbours: keep them <= 255 per half
+  if (tid == 0) sNOut = 0;
+  // slack and pad words are read as (masked) neighbours: they must stay <= 255 per half or the packed compare borrows
+  if (tid < kF3SSlack) { sS[tid] = 0; sS[kF3SSlack + kF3SH * kF3SPitch + tid] = 0; }
   if (tid < kF3SW) {
     const int x = ox - 1 + tid;
     sCol[tid] = (x >= kEdge && x < maxX) ? b.info[L.colInfoOff + x] : (uint16_t)0;
@@ -91,59 +98,61 @@ __global__ void __launch_bounds__(256) k_fast_nms3(const __grid_constant__ Geom 
         uint2 va, vb;
         va.x = __byte_perm(u, 0u, 0x4140); va.y = __byte_perm(u, 0u, 0x4342);
         vb.x = __byte_perm(u, 0u, 0x4241); vb.y = __byte_perm(u, un, 0x5453);
-        *reinterpret_cast<uint2*>(&sA[r * kF3Pitch + 2 * p]) = va;
-        *reinterpret_cast<uint2*>(&sB[r * kF3Pitch + 2 * p]) = vb;
+        *reinterpret_cast<uint2*>(&sW[r * kF3Pitch + 2 * p]) = va;
+        *reinterpret_cast<uint2*>(&sW[kF3Copy + r * kF3Pitch + 2 * p]) = vb;
       }
     }
   }
   // the pair of lane p starts at window column 2p+3, i.e. column c0 = 2p + 3 + a of the staged row:
-  //   a odd  -> c0 even: centre / even dx from sA at p + (3+a)/2 + dx/2,   odd dx from sB at p + (a+1)/2 + (dx+1)/2
-  //   a even -> c0 odd:  centre / even dx from sB at p + 1 + a/2 + dx/2,   odd dx from sA at p + a/2 + 1 + (dx+1)/2
-  F3Bases sb;
-  if (a & 1) { sb.e = sA + (3 + a) / 2; sb.o = sB + (a + 1) / 2; }
-  else { sb.e = sB + 1 + a / 2; sb.o = sA + a / 2 + 1; }
+  //   a odd  -> c0 even: centre / even dx from copy A at p + (3+a)/2 + dx/2,   odd dx from copy B at p + (a+1)/2 + (dx+1)/2
+  //   a even -> c0 odd:  centre / even dx from copy B at p + 1 + a/2 + dx/2,   odd dx from copy A at p + a/2 + 1 + (dx+1)/2
+  const int eBase = (a & 1) ? (3 + a) / 2 : kF3Copy + 1 + a / 2;
+  const int oBase = (a & 1) ? kF3Copy + (a + 1) / 2 : a / 2 + 1;
   __syncthreads();
 
   // ---- 1. compass bound for every pair: every 9-arc holds one of (r0|r8) and one of (r4|r12)  =>  S <= Q
   const uint32_t kBias = 0x01000100u;
   const uint32_t thrB = (uint32_t)g.minTh * 0x00010001u + kBias;
+  uint16_t* const myList = sList[warp];
+  int cnt = 0;   // warp-uniform
   {
     const bool colNeeded = (ox - 1 + 2 * p) < maxX;
-#pragma unroll 2
+    const uint32_t lt = (1u << p) - 1;
+    // rows are dealt to the warps round-robin: 8 consecutive rows per warp would avoid some bank conflicts of the gathers in
+    // steps 2 and 3, but was measured 8 % slower (busy rows cluster, the warps of a CTA finish unevenly)
+#pragma unroll 4
     for (int sr = warp; sr < kF3SH; sr += 8) {
-      S[sr * 32 + p] = 0;
+      S[sr * kF3SPitch + p] = 0;
+      if (kF3SPitch > 32 && p == 0) S[sr * kF3SPitch + 32] = 0;
       if (oy - 1 + sr >= maxY) continue;   // warp-uniform: rows below the region are never read as neighbours of a kept pixel
       const int idx = (sr + 3) * kF3Pitch + p;
-      const uint32_t v = f3ring<0, 0>(sb, idx);
-      const uint32_t r0 = f3ring<0, 3>(sb, idx), r8 = f3ring<0, -3>(sb, idx);
-      const uint32_t r4 = f3ring<3, 0>(sb, idx), r12 = f3ring<-3, 0>(sb, idx);
+      const int eI = eBase + idx, oI = oBase + idx;
+      const uint32_t v = f3ring<0, 0>(sW, eI, oI);
+      const uint32_t r0 = f3ring<0, 3>(sW, eI, oI), r8 = f3ring<0, -3>(sW, eI, oI);
+      const uint32_t r4 = f3ring<3, 0>(sW, eI, oI), r12 = f3ring<-3, 0>(sW, eI, oI);
       const uint32_t hi = __vminu2(__vmaxu2(r0, r8), __vmaxu2(r4, r12));
       const uint32_t lo = __vmaxu2(__vminu2(r0, r8), __vminu2(r4, r12));
       const uint32_t q = __vmaxu2((hi + kBias) - v, (v + kBias) - lo);  // Q + 256 per half
       const bool pass = colNeeded && (__vmaxu2(q, thrB) != thrB);
       const uint32_t m = __ballot_sync(ORBX_FULL, pass);
-      if (m) {
-        int base = 0;
-        if (p == 0) base = atomicAdd(&sN, __popc(m));
-        base = __shfl_sync(ORBX_FULL, base, 0);
-        if (pass) sList[base + __popc(m & ((1u << p) - 1))] = (uint16_t)(sr * 32 + p);
-      }
+      if (pass) myList[cnt + __popc(m & lt)] = (uint16_t)(sr * 32 + p);
+      cnt += __popc(m);
     }
   }
-  __syncthreads();
-  const int n = sN;
+  __syncwarp();
 
-  // ---- 2. full score of the surviving pairs
+  // ---- 2. full score of the surviving pairs of this warp's rows
 #pragma unroll 1
-  for (int i = tid; i < n; i += 256) {
-    const int e = sList[i];
+  for (int i = p; i < cnt; i += 32) {
+    const int e = myList[i];
     const int idx = ((e >> 5) + 3) * kF3Pitch + (e & 31);
-    const uint32_t v = f3ring<0, 0>(sb, idx);
+    const int eI = eBase + idx, oI = oBase + idx;
+    const uint32_t v = f3ring<0, 0>(sW, eI, oI);
     uint32_t r[16];
-    r[0] = f3ring<0, 3>(sb, idx);   r[1] = f3ring<1, 3>(sb, idx);    r[2] = f3ring<2, 2>(sb, idx);    r[3] = f3ring<3, 1>(sb, idx);
-    r[4] = f3ring<3, 0>(sb, idx);   r[5] = f3ring<3, -1>(sb, idx);   r[6] = f3ring<2, -2>(sb, idx);   r[7] = f3ring<1, -3>(sb, idx);
-    r[8] = f3ring<0, -3>(sb, idx);  r[9] = f3ring<-1, -3>(sb, idx);  r[10] = f3ring<-2, -2>(sb, idx); r[11] = f3ring<-3, -1>(sb, idx);
-    r[12] = f3ring<-3, 0>(sb, idx); r[13] = f3ring<-3, 1>(sb, idx);  r[14] = f3ring<-2, 2>(sb, idx);  r[15] = f3ring<-1, 3>(sb, idx);
+    r[0] = f3ring<0, 3>(sW, eI, oI);   r[1] = f3ring<1, 3>(sW, eI, oI);    r[2] = f3ring<2, 2>(sW, eI, oI);    r[3] = f3ring<3, 1>(sW, eI, oI);
+    r[4] = f3ring<3, 0>(sW, eI, oI);   r[5] = f3ring<3, -1>(sW, eI, oI);   r[6] = f3ring<2, -2>(sW, eI, oI);   r[7] = f3ring<1, -3>(sW, eI, oI);
+    r[8] = f3ring<0, -3>(sW, eI, oI);  r[9] = f3ring<-1, -3>(sW, eI, oI);  r[10] = f3ring<-2, -2>(sW, eI, oI); r[11] = f3ring<-3, -1>(sW, eI, oI);
+    r[12] = f3ring<-3, 0>(sW, eI, oI); r[13] = f3ring<-3, 1>(sW, eI, oI);  r[14] = f3ring<-2, 2>(sW, eI, oI);  r[15] = f3ring<-1, 3>(sW, eI, oI);
     uint32_t n3[16], x3[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) {
@@ -160,25 +169,24 @@ __global__ void __launch_bounds__(256) k_fast_nms3(const __grid_constant__ Geom 
       mxn = __vimax3_u16x2(mxn, na, nb);
       mnx = __vimin3_u16x2(mnx, xa, xb);
     }
-    S[e] = __vmaxu2(__vmaxu2((mxn + kBias) - v, (v + kBias) - mnx), kBias) - kBias;  // max(S, 0) per half
+    S[e + (e >> 5) * (kF3SPitch - 32)] = __vmaxu2(__vmaxu2((mxn + kBias) - v, (v + kBias) - mnx), kBias) - kBias;  // max(S, 0) per half
   }
-  __syncthreads();
+  __syncthreads();   // all scores written; the window copies are dead from here on
 
-  // ---- 3. NMS inside the owning cell + emission of pre-candidates (S > minTh), list entries only
+  // ---- 3. NMS inside the owning cell for list entries with a non-zero score; kept pixels go to the tile's output list
+  uint2* const sOut = reinterpret_cast<uint2*>(sW);   // x | y << 16,  cell | S << 16   (= PreCand)
   const uint32_t thr2 = (uint32_t)g.minTh * 0x00010001u;
-  PreCand* cand = b.cand + (long long)f * g.candSlab + L.candOff;
-  int* candCount = b.candCount + f * ORBX_MAX_LEVELS + level;
-  int* cellFlags = b.cellFlags + (long long)f * g.nCellsTotal + L.cellBase;
 #pragma unroll 1
-  for (int base0 = 0; base0 < n; base0 += 256) {
-    const int i = base0 + tid;
+  for (int i0 = 0; i0 < cnt; i0 += 32) {
+    const int i = i0 + p;
     bool keepA = false, keepB = false;
     uint32_t cc = 0, ciA = 0, ciB = 0, ri = 0;
     int xa = 0, y = 0;
-    if (i < n) {
-      const int e = sList[i];
+    if (i < cnt) {
+      const int e = myList[i];
       const int sr = e >> 5, q = e & 31;
-      cc = S[e];
+      const uint32_t* Se = S + e + sr * (kF3SPitch - 32);
+      cc = Se[0];
       y = oy - 1 + sr; xa = ox - 1 + 2 * q;
       if (cc != 0 && sr >= 1 && sr <= kF3TileH && y < maxY) {
         const bool okA = (q >= 1) && (xa < maxX), okB = (q <= 30) && (xa + 1 < maxX);
@@ -187,14 +195,14 @@ __global__ void __launch_bounds__(256) k_fast_nms3(const __grid_constant__ Geom 
         const uint32_t maskL = ((ciA & 0x4000u) ? 0u : 0x0000ffffu) | ((ciB & 0x4000u) ? 0u : 0xffff0000u);
         const uint32_t maskR = ((ciA & 0x8000u) ? 0u : 0x0000ffffu) | ((ciB & 0x8000u) ? 0u : 0xffff0000u);
         const uint32_t valid = (okA ? 0x0000ffffu : 0u) | (okB ? 0xffff0000u : 0u);
-        const uint32_t pc = S[e - 1], nc = S[e + 1];
+        const uint32_t pc = Se[-1], nc = Se[1];
         uint32_t nb = __vmaxu2(__funnelshift_r(pc, cc, 16) & maskL, __funnelshift_r(cc, nc, 16) & maskR);
         if (!(ri & 0x4000u)) {
-          const uint32_t pu = S[e - 33], cu = S[e - 32], nu = S[e - 31];
+          const uint32_t pu = Se[-kF3SPitch - 1], cu = Se[-kF3SPitch], nu = Se[-kF3SPitch + 1];
           nb = __vimax3_u16x2(nb, cu, __vmaxu2(__funnelshift_r(pu, cu, 16) & maskL, __funnelshift_r(cu, nu, 16) & maskR));
         }
         if (!(ri & 0x8000u)) {
-          const uint32_t pd = S[e + 31], cd = S[e + 32], nd = S[e + 33];
+          const uint32_t pd = Se[kF3SPitch - 1], cd = Se[kF3SPitch], nd = Se[kF3SPitch + 1];
           nb = __vimax3_u16x2(nb, cd, __vmaxu2(__funnelshift_r(pd, cd, 16) & maskL, __funnelshift_r(cd, nd, 16) & maskR));
         }
         nb = __vmaxu2(nb, thr2);
@@ -206,25 +214,33 @@ __global__ void __launch_bounds__(256) k_fast_nms3(const __grid_constant__ Geom 
     if ((mA | mB) == 0) continue;
     const int nA = __popc(mA), total = nA + __popc(mB);
     int base = 0;
-    if (p == 0) base = atomicAdd(candCount, total);
+    if (p == 0) base = atomicAdd(&sNOut, total);
     base = __shfl_sync(ORBX_FULL, base, 0);
-    const int rowCell = (int)(ri & 0x3fffu) * L.nCols;
+    const uint32_t rowCell = (ri & 0x3fffu) * (uint32_t)L.nCols, lt = (1u << p) - 1;
     if (keepA) {
-      const int idx = base + __popc(mA & ((1u << p) - 1)), s = cc & 0xffffu, cell = rowCell + (int)(ciA & 0x3fffu);
-      if (idx < L.candCap) {
-        PreCand pc2; pc2.x = (uint16_t)xa; pc2.y = (uint16_t)y; pc2.cell = (uint16_t)cell; pc2.S = (uint8_t)s; pc2.pad = 0;
-        cand[idx] = pc2;
-      } else atomicExch(b.status, ORBX_ERR_CAPACITY);
-      if (s > g.iniTh) atomicOr(cellFlags + cell, 1);
+      const int o = base + __popc(mA & lt);
+      if (o < kF3OutCap) sOut[o] = make_uint2((uint32_t)xa | ((uint32_t)y << 16), (rowCell + (ciA & 0x3fffu)) | ((cc & 0xffu) << 16));
     }
     if (keepB) {
-      const int idx = base + nA + __popc(mB & ((1u << p) - 1)), s = cc >> 16, cell = rowCell + (int)(ciB & 0x3fffu);
-      if (idx < L.candCap) {
-        PreCand pc2; pc2.x = (uint16_t)(xa + 1); pc2.y = (uint16_t)y; pc2.cell = (uint16_t)cell; pc2.S = (uint8_t)s; pc2.pad = 0;
-        cand[idx] = pc2;
-      } else atomicExch(b.status, ORBX_ERR_CAPACITY);
-      if (s > g.iniTh) atomicOr(cellFlags + cell, 1);
+      const int o = base + nA + __popc(mB & lt);
+      if (o < kF3OutCap) sOut[o] = make_uint2((uint32_t)(xa + 1) | ((uint32_t)y << 16), (rowCell + (ciB & 0x3fffu)) | (((cc >> 16) & 0xffu) << 16));
     }
+  }
+  __syncthreads();
+
+  // ---- emission: one global reservation per tile, coalesced records, per-cell "has S > iniTh" flags
+  const int nOut = min(sNOut, kF3OutCap);
+  if (nOut == 0) return;
+  if (tid == 0) sBase = atomicAdd(b.candCount + f * ORBX_MAX_LEVELS + level, nOut);
+  __syncthreads();
+  const int gbase = sBase;
+  uint2* cand = reinterpret_cast<uint2*>(b.cand + (long long)f * g.candSlab + L.candOff);
+  int* cellFlags = b.cellFlags + (long long)f * g.nCellsTotal + L.cellBase;
+  for (int i = tid; i < nOut; i += 256) {
+    const uint2 rec = sOut[i];
+    if (gbase + i < L.candCap) cand[gbase + i] = rec;
+    else atomicExch(b.status, ORBX_ERR_CAPACITY);
+    if ((int)(rec.y >> 16) > g.iniTh) atomicOr(cellFlags + (rec.y & 0xffffu), 1);
   }
 }
 
