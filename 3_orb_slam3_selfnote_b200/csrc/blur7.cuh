@@ -11,6 +11,9 @@
 //   B. row pass on the u16 sums with IDP.2A (two 16-bit x 8-bit products per instruction) on aligned word pairs -- the tap
 //      bytes are pre-arranged per output parity so no funnel shifts are needed; rounding rides in the accumulator init.
 // CTA = 120 x 8R output pixels: the 32 word columns of a strip cover x0-4 .. x0+123 (3-pixel halo each side).
+// Second cut (profiles/r01c: 71 % of the instructions were in pass A -- 4-row strips re-read 10 rows for 4, the byte-wise
+// reflect path of edge lanes ran in 41 % of the warps at 200 instructions, per-row reflect selects in every warp): strips of
+// R = 8 rows, edge lanes load two aligned words + one PRMT, the row-reflect form only runs in the top / bottom strips.
 // Algorithmic bytes per launch: read + write every level.
 #pragma once
 #include "dev_common.cuh"
@@ -19,13 +22,49 @@
 namespace orbx {
 
 constexpr int kBvW = 120;          // output pixels per tile row
-constexpr int kBvR = 4;            // output rows per warp
+constexpr int kBvR = 8;            // output rows per warp (14 source rows: 1.75 loads per output row)
 constexpr int kBvH = 8 * kBvR;     // output rows per tile
 
 __device__ __forceinline__ int bv_refl(int i, int n) {
   if (i < 0) i = -i;
   if (i >= n) i = 2 * (n - 1) - i;
   return max(0, min(n - 1, i));  // (twice-reflected only on degenerate tiny levels)
+}
+
+// one source row of the column pass: the lane's 4 pixels (columns gx .. gx+3, reflected at the level's left / right edge)
+template <bool EDGE>
+__device__ __forceinline__ uint32_t bv_load(const uint8_t* row, int gx, int wb, int wb2, uint32_t sel) {
+  if (!EDGE) return __ldg(reinterpret_cast<const uint32_t*>(row + gx));
+  // reflected columns are 4 consecutive ones in reverse order: they lie in two adjacent aligned words, picked apart by PRMT
+  return __byte_perm(__ldg(reinterpret_cast<const uint32_t*>(row + wb)), __ldg(reinterpret_cast<const uint32_t*>(row + wb2)), sel);
+}
+
+template <bool EDGE>
+__device__ __forceinline__ void bv_column_pass(const Geom& g, const uint8_t* src, int sp, int h, int ys, int gx, int wb, int wb2, uint32_t sel,
+                                               uint32_t* dst /* &sV[(warp * kBvR) * 64 + 2 * lane] */) {
+  uint32_t w[kBvR + 6];
+  if (ys >= 3 && ys + kBvR + 2 < h) {   // warp-uniform: no row reflection needed
+    const uint8_t* row = src + (long long)(ys - 3) * sp;
+#pragma unroll
+    for (int i = 0; i < kBvR + 6; i++) { w[i] = bv_load<EDGE>(row, gx, wb, wb2, sel); row += sp; }
+  } else {
+#pragma unroll
+    for (int i = 0; i < kBvR + 6; i++) w[i] = bv_load<EDGE>(src + (long long)bv_refl(ys - 3 + i, h) * sp, gx, wb, wb2, sel);
+  }
+  const uint32_t t[7] = {(uint32_t)g.taps[0], (uint32_t)g.taps[1], (uint32_t)g.taps[2], (uint32_t)g.taps[3], (uint32_t)g.taps[4],
+                         (uint32_t)g.taps[5], (uint32_t)g.taps[6]};
+  uint32_t alo[kBvR], ahi[kBvR];
+#pragma unroll
+  for (int j = 0; j < kBvR; j++) { alo[j] = 0; ahi[j] = 0; }
+#pragma unroll
+  for (int i = 0; i < kBvR + 6; i++) {
+    const uint32_t lo = __byte_perm(w[i], 0u, 0x4140), hi = __byte_perm(w[i], 0u, 0x4342);   // bytes -> u16 pairs
+#pragma unroll
+    for (int j = 0; j < kBvR; j++)
+      if (i - j >= 0 && i - j < 7) { alo[j] += t[i - j] * lo; ahi[j] += t[i - j] * hi; }   // one IMAD = two pixels (sums <= 65535)
+  }
+#pragma unroll
+  for (int j = 0; j < kBvR; j++) *reinterpret_cast<uint2*>(dst + j * 64) = make_uint2(alo[j], ahi[j]);
 }
 
 __global__ void __launch_bounds__(256) k_blur7v(const __grid_constant__ Geom g, const __grid_constant__ Batch b) {
@@ -40,34 +79,25 @@ __global__ void __launch_bounds__(256) k_blur7v(const __grid_constant__ Geom g, 
   int sp;
   const uint8_t* src = level_ptr(g, b, level, f, sp);
 
-  // ---- A. column pass
+  // ---- A. column pass: warp = strip of kBvR output rows, lane = one word column
   {
     const int ys = y0 + warp * kBvR;      // first output row of the strip
     if (ys < L.h) {
       const int gx = x0 - 4 + 4 * lane;   // first pixel column of this lane's word
       const bool edge = (gx < 0) || (gx + 3 >= L.w);
-      int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
-      if (edge) { c0 = bv_refl(gx, L.w); c1 = bv_refl(gx + 1, L.w); c2 = bv_refl(gx + 2, L.w); c3 = bv_refl(gx + 3, L.w); }
-      uint32_t lo[kBvR + 6], hi[kBvR + 6];
-      const bool inner = (ys >= 3) && (ys + kBvR + 2 < L.h);   // warp-uniform: no row reflection needed
-      const uint8_t* rowIn = src + (long long)(ys - 3) * sp;
-#pragma unroll
-      for (int i = 0; i < kBvR + 6; i++) {
-        const uint8_t* row = inner ? rowIn + i * sp : src + (long long)bv_refl(ys - 3 + i, L.h) * sp;
-        uint32_t w;
-        if (!edge) w = __ldg(reinterpret_cast<const uint32_t*>(row + gx));
-        else w = (uint32_t)__ldg(row + c0) | ((uint32_t)__ldg(row + c1) << 8) | ((uint32_t)__ldg(row + c2) << 16) | ((uint32_t)__ldg(row + c3) << 24);
-        lo[i] = __byte_perm(w, 0u, 0x4140);
-        hi[i] = __byte_perm(w, 0u, 0x4342);
+      int wb = 0, wb2 = 0;
+      uint32_t sel = 0x3210u;
+      if (edge) {
+        const int c0 = bv_refl(gx, L.w), c1 = bv_refl(gx + 1, L.w), c2 = bv_refl(gx + 2, L.w), c3 = bv_refl(gx + 3, L.w);
+        wb = min(min(c0, c1), min(c2, c3)) & ~3;
+        wb2 = min(wb + 4, sp - 4);          // never selected when it had to be clamped: all four columns are then inside word wb
+        sel = (uint32_t)min(c0 - wb, 7) | ((uint32_t)min(c1 - wb, 7) << 4) | ((uint32_t)min(c2 - wb, 7) << 8) | ((uint32_t)min(c3 - wb, 7) << 12);
+      } else {
+        wb = gx; wb2 = gx;
       }
-      const uint32_t t0 = g.taps[0], t1 = g.taps[1], t2 = g.taps[2], t3 = g.taps[3], t4 = g.taps[4], t5 = g.taps[5], t6 = g.taps[6];
-#pragma unroll
-      for (int j = 0; j < kBvR; j++) {
-        uint2 v;
-        v.x = t0 * lo[j] + t1 * lo[j + 1] + t2 * lo[j + 2] + t3 * lo[j + 3] + t4 * lo[j + 4] + t5 * lo[j + 5] + t6 * lo[j + 6];
-        v.y = t0 * hi[j] + t1 * hi[j + 1] + t2 * hi[j + 2] + t3 * hi[j + 3] + t4 * hi[j + 4] + t5 * hi[j + 5] + t6 * hi[j + 6];
-        *reinterpret_cast<uint2*>(&sV[(warp * kBvR + j) * 64 + 2 * lane]) = v;
-      }
+      uint32_t* dst = &sV[(warp * kBvR) * 64 + 2 * lane];
+      if (__any_sync(0xffffffffu, edge)) bv_column_pass<true>(g, src, sp, L.h, ys, gx, wb, wb2, sel, dst);
+      else bv_column_pass<false>(g, src, sp, L.h, ys, gx, wb, wb2, sel, dst);
     }
   }
   __syncthreads();
