@@ -70,6 +70,7 @@ int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
   if (h->haveGeom && h->g.width == width && h->g.height == height) return ORBX_OK;
   if (h->haveGeom) free_geom(h);
   h->geomEpoch++;
+  h->rs3ok = true;
   CK(cudaSetDevice(h->p.device));
   if (width > 8192 || height > 8192) { set_error("image larger than 8192 px is unsupported"); return ORBX_ERR_UNSUPPORTED; }
   Geom& g = h->g;
@@ -187,6 +188,9 @@ int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
         e.b1 = (int16_t)std::min(32767, std::max(-32768, cv_round_f(fy * 2048.f)));
         rsy.push_back(e);
       }
+      // k_pyr_resize3 covers the taps of 4 adjacent destination columns with 8 source bytes
+      for (int x0 = 0; x0 < wpad; x0 += 4)
+        if (rsx[L.rsxOff + x0 + 3].s1 - rsx[L.rsxOff + x0].s0 > 7 || (L.rsxOff & 1)) h->rs3ok = false;
       // staged source window of k_pyr_resize2: maxima over the level's tiles
       const RsX* tx = rsx.data() + L.rsxOff;
       const RsY* ty = rsy.data() + L.rsyOff;
@@ -278,9 +282,12 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
   mark(1);
   for (int l = 1; l < g.nlevels; l++) {
     const LevelGeom& L = g.lv[l];
-    if (h->resizeV1) {
+    if (h->resizeVer == 1) {
       dim3 grid((L.w + 127) / 128, (L.h + 7) / 8, nframes), block(32, 8);
       k_pyr_resize<<<grid, block, 0, st>>>(gg, b, l);
+    } else if (h->resizeVer == 3 && h->rs3ok) {
+      dim3 grid((L.w + kRs3TileW - 1) / kRs3TileW, (L.h + kRs3TileH - 1) / kRs3TileH, nframes);
+      k_pyr_resize3<<<grid, 256, 0, st>>>(gg, b, l);
     } else {
       dim3 grid((L.w + kRsTileW - 1) / kRsTileW, (L.h + kRsTileH - 1) / kRsTileH, nframes);
       k_pyr_resize2<<<grid, 256, h->rsSmem, st>>>(gg, b, l);
@@ -357,7 +364,8 @@ int orbx_create(const orbx_params* p, orbx_extractor** out) {
   // A/B switches for the earlier versions of kernels
   { const char* e = getenv("ORBX_FAST_V1"); if (e && e[0] == '1') h->fastVer = 1; }
   { const char* e = getenv("ORBX_FAST_V2"); if (e && e[0] == '1') h->fastVer = 2; }
-  { const char* e = getenv("ORBX_RESIZE_V1"); h->resizeV1 = e && e[0] == '1'; }
+  { const char* e = getenv("ORBX_RESIZE_V1"); if (e && e[0] == '1') h->resizeVer = 1; }
+  { const char* e = getenv("ORBX_RESIZE_V2"); if (e && e[0] == '1') h->resizeVer = 2; }
   { const char* e = getenv("ORBX_BLUR_V1"); h->blurV1 = e && e[0] == '1'; }
   const int nl = p->nlevels;
   // ORBextractor::ORBextractor, src/ORBextractor.cc:408-468

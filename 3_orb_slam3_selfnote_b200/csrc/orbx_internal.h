@@ -60,7 +60,9 @@ struct orbx_extractor {
   Slot slot[2];
   int lastSlot = 0;
   bool profile = false;
-  bool resizeV1 = false, blurV1 = false, orientV1 = false;
+  bool blurV1 = false, orientV1 = false;
+  int resizeVer = 3;     // ORBX_RESIZE_V1=1 / ORBX_RESIZE_V2=1: earlier resize kernels (A/B only)
+  bool rs3ok = true;     // k_pyr_resize3 applies to this geometry (scale factor <= 2)
   bool noFork = true;    // ORBX_FORK=1: run the blur on the slot's side stream beside FAST -> quadtree -> assemble (A/B only)
   size_t rsSmem = 0;
   int fastVer = 3;      // ORBX_FAST_V1=1 / ORBX_FAST_V2=1: run an earlier FAST kernel instead of k_fast_nms3 (A/B only)

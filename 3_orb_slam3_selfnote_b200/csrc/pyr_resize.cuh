@@ -80,4 +80,88 @@ __global__ void __launch_bounds__(256) k_pyr_resize2(const __grid_constant__ Geo
   }
 }
 
+
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// k_pyr_resize3 -- register-resident version (profiles/r01c: k_pyr_resize2 executed ~70 thread-instructions per destination
+// pixel, issue-bound at 82 %: partially filled staging loops, one shared-memory round trip for the horizontal pass, scalar
+// vertical arithmetic with clamps).
+//   thread = 4 destination columns (one 32-bit store) walking down a strip of kRs3Rows destination rows;
+//   per source row: three aligned 32-bit loads cover the <= 8 source bytes the 4 columns touch (scale <= 2), two funnel shifts
+//   line them up at the first source column, and per column one PRMT picks its two taps and one IDP.2A computes
+//   S[sx]*a0 + S[sx+1]*a1 (the Q11 weights as a u16 pair); source rows are interpolated horizontally once and carried in
+//   registers from one destination row to the next (the row tables are warp-uniform, so the reuse test does not diverge);
+//   vertical: ((b0*(h0>>4))>>16) + ((b1*(h1>>4))>>16) as two IMAD.HI with the weights pre-shifted by 16, then (+2)>>2.
+//   No clamp: h>>4 <= 32655 and b0+b1 <= 2049 bound the result by 255.
+// Levels whose 4-column groups span more than 8 source bytes (scale factor > 2) use k_pyr_resize2.
+// ---------------------------------------------------------------------------------------------------------------------------
+constexpr int kRs3Rows = 8;                    // destination rows per warp
+constexpr int kRs3TileW = 128, kRs3TileH = 8 * kRs3Rows;
+
+struct Rs3Col { uint32_t sel[4]; uint32_t wt[4]; int base; uint32_t sh; };
+
+__device__ __forceinline__ void rs3_hrow(const uint8_t* row, int sp, const Rs3Col& c, uint32_t (&h)[4]) {
+  const int o1 = min(c.base + 4, sp - 4), o2 = min(c.base + 8, sp - 4);   // words past the row end hold no tap (s1 <= w-1 < sp)
+  const uint32_t w0 = __ldg(reinterpret_cast<const uint32_t*>(row + c.base));
+  const uint32_t w1 = __ldg(reinterpret_cast<const uint32_t*>(row + o1));
+  const uint32_t w2 = __ldg(reinterpret_cast<const uint32_t*>(row + o2));
+  const uint32_t u0 = __funnelshift_r(w0, w1, c.sh), u1 = __funnelshift_r(w1, w2, c.sh);   // 8 bytes from the first source column on
+#pragma unroll
+  for (int k = 0; k < 4; k++) h[k] = __dp2a_lo(c.wt[k], __byte_perm(u0, u1, c.sel[k]), 0u) >> 4;
+}
+
+__global__ void __launch_bounds__(256) k_pyr_resize3(const __grid_constant__ Geom g, const __grid_constant__ Batch b, int level) {
+  const LevelGeom& L = g.lv[level];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, f = blockIdx.z;
+  const int x = blockIdx.x * kRs3TileW + 4 * lane;
+  const int ys = blockIdx.y * kRs3TileH + warp * kRs3Rows;
+  const int wpad = (L.w + 3) & ~3;   // the column table is padded to a multiple of 4
+  if (x >= wpad || ys >= L.h) return;
+  int sp;
+  const uint8_t* src = level_ptr(g, b, level - 1, f, sp);
+  const RsY* ty = b.rsy + L.rsyOff;
+  Rs3Col c;
+  {
+    const uint4* tx = reinterpret_cast<const uint4*>(b.rsx + L.rsxOff + x);   // 4 entries of 8 bytes
+    const uint4 p0 = __ldg(tx), p1 = __ldg(tx + 1);
+    const uint32_t e[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};   // (s0 | s1 << 16), (a0 | a1 << 16) per column
+    const int sx0 = (int)(e[0] & 0xffffu);
+    c.base = sx0 & ~3; c.sh = (uint32_t)(sx0 & 3) * 8;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int s0 = (int)(e[2 * k] & 0xffffu), s1 = (int)(e[2 * k] >> 16);
+      c.sel[k] = (uint32_t)min(s0 - sx0, 7) | ((uint32_t)min(s1 - sx0, 7) << 4);   // upper two bytes: don't care (byte 0)
+      c.wt[k] = e[2 * k + 1];
+    }
+  }
+  uint8_t* dst = b.pyr + (long long)f * b.pyrFrameStride + L.pyrOff + x;
+  int r0 = -1, r1 = -1;
+  uint32_t hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0};
+#pragma unroll
+  for (int j = 0; j < kRs3Rows; j++) {
+    const int y = ys + j;
+    if (y >= L.h) break;
+    const RsY e = ty[y];
+    const int s0 = e.s0, s1 = e.s1;
+    if (s0 != r0) {
+      if (s0 == r1) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) hA[k] = hB[k];
+      } else rs3_hrow(src + (long long)s0 * sp, sp, c, hA);
+      r0 = s0;
+    }
+    if (s1 != r1) {
+      if (s1 == r0) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) hB[k] = hA[k];
+      } else rs3_hrow(src + (long long)s1 * sp, sp, c, hB);
+      r1 = s1;
+    }
+    const uint32_t B0 = (uint32_t)(uint16_t)e.b0 << 16, B1 = (uint32_t)(uint16_t)e.b1 << 16;
+    uint32_t v[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) v[k] = (__umulhi(B0, hA[k]) + __umulhi(B1, hB[k]) + 2u) >> 2;
+    *reinterpret_cast<uint32_t*>(dst + (long long)y * L.pitch) = v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24);
+  }
+}
 }  // namespace orbx
