@@ -56,6 +56,26 @@ def test_extract_matches_oracle(orbx, oracle, synth, w, h, nfeat, lap, taps):
     gx.close()
 
 
+@pytest.mark.parametrize("w,h,nfeat,scale,nlevels,ini,mn", [
+    (1920, 1080, 2000, 1.2, 8, 20, 7),    # BASELINE config 4 (HD)
+    (752, 480, 1000, 1.5, 6, 20, 7),      # other scale factor / level count (4-column groups span up to 7 source bytes)
+    (640, 480, 800, 2.4, 4, 20, 7),       # scale factor > 2: the resize falls back to the staged-window kernel
+    (752, 480, 1000, 1.2, 8, 40, 12),     # other FAST thresholds (more cells take the minThFAST fallback)
+    (752, 480, 300, 1.1, 12, 20, 7),      # many shallow levels
+])
+def test_extract_other_geometries(orbx, oracle, synth, w, h, nfeat, scale, nlevels, ini, mn):
+    img = synth.frame(w, h, 300 + nfeat, 1)
+    ex = oracle.Extractor(nfeat, scaleFactor=scale, nlevels=nlevels, iniThFAST=ini, minThFAST=mn, sincos_mode=oracle.SINCOS_PORTABLE)
+    mono_o, ko, do = ex(img, (0, 0))
+    gx = orbx.ORBextractor(nfeat, scaleFactor=scale, nlevels=nlevels, iniThFAST=ini, minThFAST=mn)
+    mono_g, kg, dg = gx(img, None, (0, 0))
+    assert mono_g == mono_o
+    _assert_same(kg, dg, ko, do, "%dx%d scale %.1f" % (w, h, scale))
+    for l in range(nlevels):
+        assert np.array_equal(gx.pyramid_level(l), ex.level(l)), "pyramid level %d" % l
+    gx.close()
+
+
 def test_reference_literal_sincos_mode_difference_is_reported(orbx, oracle, synth):
     """the reference's cos(float) is libm cosf; the CUDA path implements (float)cos((double)x).
     The descriptor difference between the two definitions is measured (not hidden); on these frames it is zero rows."""

@@ -237,3 +237,34 @@ def test_stereo_frames_host_pipeline(orbx, oracle, synth):
         assert np.array_equal(o["descL"][f, :cl], dl) and np.array_equal(o["descR"][f, :cr], dr)
         assert o["uRight"][f, :cl].tobytes() == uo.tobytes() and o["depth"][f, :cl].tobytes() == do.tobytes()
     gl.close(); gr.close(); m.close()
+
+
+def test_host_buffers_and_chunked_pipeline(orbx, oracle, synth):
+    """orbx_host_alloc staging buffers + orbx_stereo_frames_host over several ramped / tail chunks (graph cache hit on the
+    second call) against the per-frame oracle."""
+    W, H, n = 752, 480, 11
+    left = np.stack([synth.frame(W, H, 55, i % 3, False) for i in range(n)])
+    right = np.stack([synth.frame(W, H, 55, i % 3, True) for i in range(n)])
+    hl, hr = orbx.HostBuffer((n, H, W)), orbx.HostBuffer((n, H, W))
+    hl.array[...] = left
+    hr.array[...] = right
+    mbf = np.float32(47.90639384423901); mb = np.float32(mbf / np.float32(435.2046959714599))
+    exL, exR, mt = orbx.ORBextractor(1200, max_batch=8), orbx.ORBextractor(1200, max_batch=8), orbx.ORBmatcher()   # chunks 2, 8, 1
+    ref = []
+    for i in range(3):
+        oL = oracle.Extractor(1200, sincos_mode=oracle.SINCOS_PORTABLE); oR = oracle.Extractor(1200, sincos_mode=oracle.SINCOS_PORTABLE)
+        _, kl, dl = oL(left[i], (0, 0)); _, kr, dr = oR(right[i], (0, 0))
+        uo, dpo, _, _ = oracle.stereo_matches(oL, oR, kl, dl, kr, dr, mb, mbf)
+        ref.append((kl, dl, kr, dr, uo, dpo))
+    for rep in range(2):
+        o = mt.stereo_frames_host(exL, exR, hl.array, hr.array, mb, mbf)
+        for i in range(n):
+            kl, dl, kr, dr, uo, dpo = ref[i % 3]
+            c = int(o["countsL"][i])
+            assert c == len(kl) and int(o["countsR"][i]) == len(kr)
+            assert o["kpsL"][i, :c].tobytes() == kl.tobytes() and np.array_equal(o["descL"][i, :c], dl)
+            assert o["kpsR"][i, :len(kr)].tobytes() == kr.tobytes() and np.array_equal(o["descR"][i, :len(kr)], dr)
+            assert o["uRight"][i, :c].tobytes() == uo.tobytes() and o["depth"][i, :c].tobytes() == dpo.tobytes()
+    for b in (hl, hr):
+        b.close()
+    exL.close(); exR.close(); mt.close()
