@@ -59,6 +59,28 @@ def _peaks():
         return 6650.0, "fallback"
 
 
+NCU_SUMMARY = os.path.join(ROOT, "profiles", "r01d_ncu_full_summary.csv")   # tools/ncu_summary.py of one --set full capture (128 images per launch)
+NCU_NAME = {"k_fast_nms": "k_fast_nms3", "k_blur7": "k_blur7v", "k_orient_desc": "k_orient_desc2", "k_quadtree": "k_quadtree"}
+
+
+def _ncu_traffic(stage, images_per_launch):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's kernel from the committed ncu capture, or None.
+    The capture ran 128 images per launch; the bench launch is scaled linearly when its batch differs."""
+    import csv
+    try:
+        rows = list(csv.reader(open(NCU_SUMMARY)))
+        hdr, units = rows[0], rows[1]
+        ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        name = NCU_NAME.get(stage)
+        for r in rows[2:]:
+            if name and r[0].startswith(name + "("):
+                return (float(r[ir]) * mult[units[ir]] + float(r[iw]) * mult[units[iw]]) * images_per_launch / 128.0
+    except Exception:
+        pass
+    return None
+
+
 class ClockSampler:
     """samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)"""
 
@@ -240,7 +262,7 @@ def run_orbx(args):
     step_ms = 2 * sum(t for _, t in stages) + stereo_ms
     abf = algo_bytes_per_stereo_frame(kp_per_image)
     roof = {"bound": "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
-            "frac": achieved / peak, "traffic": None, "kernel_ms_per_launch": dom_ms, "launches_per_step": 2,
+            "frac": achieved / peak, "traffic": _ncu_traffic(dom_name, B), "traffic_source": os.path.relpath(NCU_SUMMARY, ROOT), "kernel_ms_per_launch": dom_ms, "launches_per_step": 2,
             "kernel_share_of_step": 2 * dom_ms / step_ms, "algorithmic_bytes_per_launch": dom_bytes,
             "whole_path": {"achieved": value / world * abf / 1e9, "frac": value / world * abf / 1e9 / peak, "bytes_per_frame": abf},
             "stage_ms_per_image_batch": {n: round(t, 4) for n, t in stages}, "stereo_match_ms": round(stereo_ms, 4)}
