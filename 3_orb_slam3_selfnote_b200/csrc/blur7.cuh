@@ -70,11 +70,9 @@ __device__ __forceinline__ void bv_column_pass(const Geom& g, const uint8_t* src
 __global__ void __launch_bounds__(256) k_blur7v(const __grid_constant__ Geom g, const __grid_constant__ Batch b) {
   __shared__ __align__(16) uint32_t sV[kBvH * 64];  // column-pass sums, u16 pairs: [row][64 words = 128 columns]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, f = blockIdx.y;
-  int level = 0;
-  while (level + 1 < g.nlevels && (int)blockIdx.x >= g.lv[level + 1].blurTileBase) level++;
+  const uint32_t tinfo = __ldg(b.blurTiles + blockIdx.x);
+  const int level = tinfo & 15, tx = (tinfo >> 4) & 0x3fff, ty = tinfo >> 18;
   const LevelGeom& L = g.lv[level];
-  const int t = blockIdx.x - L.blurTileBase;
-  const int ty = t / L.blurTilesX, tx = t - ty * L.blurTilesX;
   const int x0 = tx * kBvW, y0 = ty * kBvH;
   int sp;
   const uint8_t* src = level_ptr(g, b, level, f, sp);

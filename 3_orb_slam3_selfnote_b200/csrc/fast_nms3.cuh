@@ -42,22 +42,21 @@ __device__ __forceinline__ uint32_t f3ring(const uint32_t* sW, int eIdx, int oId
   return sW[eIdx + DY * kF3Pitch + DX / 2];
 }
 
-__global__ void __launch_bounds__(256) k_fast_nms3(const __grid_constant__ Geom g, const __grid_constant__ Batch b) {
+__global__ void __launch_bounds__(256, 5) k_fast_nms3(const __grid_constant__ Geom g, const __grid_constant__ Batch b) {
   // pair copy A = (col 2j, 2j+1) at [0, kF3Copy), copy B = (col 2j+1, 2j+2) at [kF3Copy, 2 kF3Copy), columns relative to the
   // aligned window origin; after step 2 the same memory holds the kept pixels of the tile
   __shared__ __align__(16) uint32_t sW[2 * kF3Copy];
   __shared__ uint32_t sS[kF3SH * kF3SPitch + 2 * kF3SSlack];  // 64x64 scores as u16 pairs (+1 pad word per row), slack words each side
   __shared__ uint16_t sList[8][kF3SH * 32 / 8];               // per warp: surviving pairs of its rows, sr * 32 + p
   __shared__ uint16_t sCol[kF3SW], sRow[kF3SH];               // cell info of the tile's columns / rows
+  __shared__ uint32_t sMask[3][32];                           // per pair column: left / right neighbour masks, valid halves
   __shared__ int sNOut, sBase;
 
   const int tid = threadIdx.x, warp = tid >> 5, p = tid & 31;
   const int f = blockIdx.y;
-  int level = 0;
-  while (level + 1 < g.nlevels && (int)blockIdx.x >= g.lv[level + 1].tileBase) level++;
+  const uint32_t tinfo = __ldg(b.fastTiles + blockIdx.x);
+  const int level = tinfo & 15, tx = (tinfo >> 4) & 0x3fff, ty = tinfo >> 18;
   const LevelGeom& L = g.lv[level];
-  const int t = blockIdx.x - L.tileBase;
-  const int ty = t / L.tilesX, tx = t - ty * L.tilesX;
   const int ox = kEdge + kF3TileW * tx, oy = kEdge + kF3TileH * ty;  // first output pixel of the tile
   const int wx0 = ox - 4, wy0 = oy - 4;                              // window origin (>= 15)
   const int a = wx0 & 3, gx0 = wx0 & ~3;
@@ -109,6 +108,16 @@ __global__ void __launch_bounds__(256) k_fast_nms3(const __grid_constant__ Geom 
   const int eBase = (a & 1) ? (3 + a) / 2 : kF3Copy + 1 + a / 2;
   const int oBase = (a & 1) ? kF3Copy + (a + 1) / 2 : a / 2 + 1;
   __syncthreads();
+  if (tid < 32) {
+    // the left neighbour of a first-column pixel and the right neighbour of a last-column pixel belong to another cell;
+    // halves outside the tile's 62 output columns or outside the region are never kept
+    const uint32_t ciA = sCol[2 * tid], ciB = sCol[2 * tid + 1];
+    const int xa = ox - 1 + 2 * tid;
+    const bool okA = (tid >= 1) && (xa < maxX), okB = (tid <= 30) && (xa + 1 < maxX);
+    sMask[0][tid] = ((ciA & 0x4000u) ? 0u : 0x0000ffffu) | ((ciB & 0x4000u) ? 0u : 0xffff0000u);
+    sMask[1][tid] = ((ciA & 0x8000u) ? 0u : 0x0000ffffu) | ((ciB & 0x8000u) ? 0u : 0xffff0000u);
+    sMask[2][tid] = (okA ? 0x0000ffffu : 0u) | (okB ? 0xffff0000u : 0u);
+  }
 
   // ---- 1. compass bound for every pair: every 9-arc holds one of (r0|r8) and one of (r4|r12)  =>  S <= Q
   const uint32_t kBias = 0x01000100u;
@@ -142,9 +151,14 @@ __global__ void __launch_bounds__(256) k_fast_nms3(const __grid_constant__ Geom 
   __syncwarp();
 
   // ---- 2. full score of the surviving pairs of this warp's rows
+  // Entries whose two scores are both <= minTh can neither be kept nor beat a kept pixel: the list is compacted in place
+  // (about half of the compass survivors go) so that step 3 runs over dense warps too.
+  const uint32_t thr2 = (uint32_t)g.minTh * 0x00010001u;
+  int cnt2 = 0;   // warp-uniform
 #pragma unroll 1
-  for (int i = p; i < cnt; i += 32) {
-    const int e = myList[i];
+  for (int i0 = 0; i0 < cnt; i0 += 32) {
+    const int i = i0 + p;
+    const int e = myList[min(i, cnt - 1)];
     const int idx = ((e >> 5) + 3) * kF3Pitch + (e & 31);
     const int eI = eBase + idx, oI = oBase + idx;
     const uint32_t v = f3ring<0, 0>(sW, eI, oI);
@@ -169,13 +183,19 @@ __global__ void __launch_bounds__(256) k_fast_nms3(const __grid_constant__ Geom 
       mxn = __vimax3_u16x2(mxn, na, nb);
       mnx = __vimin3_u16x2(mnx, xa, xb);
     }
-    S[e + (e >> 5) * (kF3SPitch - 32)] = __vmaxu2(__vmaxu2((mxn + kBias) - v, (v + kBias) - mnx), kBias) - kBias;  // max(S, 0) per half
+    const uint32_t s2 = __vmaxu2(__vmaxu2((mxn + kBias) - v, (v + kBias) - mnx), kBias) - kBias;  // max(S, 0) per half
+    const bool live = (i < cnt) && (__vmaxu2(s2, thr2) != thr2);
+    if (i < cnt) S[e + (e >> 5) * (kF3SPitch - 32)] = s2;
+    const uint32_t m = __ballot_sync(ORBX_FULL, live);
+    __syncwarp();   // every lane has read its entry of this round before the slots are reused
+    if (live) myList[cnt2 + __popc(m & ((1u << p) - 1))] = (uint16_t)e;
+    cnt2 += __popc(m);
   }
+  cnt = cnt2;
   __syncthreads();   // all scores written; the window copies are dead from here on
 
   // ---- 3. NMS inside the owning cell for list entries with a non-zero score; kept pixels go to the tile's output list
   uint2* const sOut = reinterpret_cast<uint2*>(sW);   // x | y << 16,  cell | S << 16   (= PreCand)
-  const uint32_t thr2 = (uint32_t)g.minTh * 0x00010001u;
 #pragma unroll 1
   for (int i0 = 0; i0 < cnt; i0 += 32) {
     const int i = i0 + p;
@@ -189,12 +209,8 @@ __global__ void __launch_bounds__(256) k_fast_nms3(const __grid_constant__ Geom 
       cc = Se[0];
       y = oy - 1 + sr; xa = ox - 1 + 2 * q;
       if (cc != 0 && sr >= 1 && sr <= kF3TileH && y < maxY) {
-        const bool okA = (q >= 1) && (xa < maxX), okB = (q <= 30) && (xa + 1 < maxX);
         ciA = sCol[2 * q]; ciB = sCol[2 * q + 1]; ri = sRow[sr];
-        // the left neighbour of a first-column pixel and the right neighbour of a last-column pixel belong to another cell
-        const uint32_t maskL = ((ciA & 0x4000u) ? 0u : 0x0000ffffu) | ((ciB & 0x4000u) ? 0u : 0xffff0000u);
-        const uint32_t maskR = ((ciA & 0x8000u) ? 0u : 0x0000ffffu) | ((ciB & 0x8000u) ? 0u : 0xffff0000u);
-        const uint32_t valid = (okA ? 0x0000ffffu : 0u) | (okB ? 0xffff0000u : 0u);
+        const uint32_t maskL = sMask[0][q], maskR = sMask[1][q], valid = sMask[2][q];
         const uint32_t pc = Se[-1], nc = Se[1];
         uint32_t nb = __vmaxu2(__funnelshift_r(pc, cc, 16) & maskL, __funnelshift_r(cc, nc, 16) & maskR);
         if (!(ri & 0x4000u)) {

@@ -83,6 +83,7 @@ struct Batch {
   // tables
   const RsX* rsx; const RsY* rsy;                    // indexed by LevelGeom::rsxOff + x / rsyOff + y
   const uint16_t* info;                              // cell index | first<<14 | last<<15, indexed by colInfoOff + x / rowInfoOff + y
+  const uint32_t* fastTiles; const uint32_t* blurTiles;  // per CTA of the all-level launches: level | tile x << 4 | tile y << 18
   const int8_t* pattern;                             // 256 x (x0,y0,x1,y1)
   const float4* patternF;                            // the same as floats (k_orient_desc2)
 };

@@ -61,7 +61,8 @@ static void free_geom(orbx_extractor* h) {
   if (h->dRsx) cudaFree(h->dRsx);
   if (h->dRsy) cudaFree(h->dRsy);
   if (h->dInfo) cudaFree(h->dInfo);
-  h->dRsx = nullptr; h->dRsy = nullptr; h->dInfo = nullptr;
+  if (h->dTiles) cudaFree(h->dTiles);
+  h->dRsx = nullptr; h->dRsy = nullptr; h->dInfo = nullptr; h->dTiles = nullptr;
   h->haveGeom = false;
 }
 
@@ -218,6 +219,18 @@ int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
   if (h->qtSmem > 200 * 1024) { set_error("nfeatures too large for the quadtree kernel's shared memory"); return ORBX_ERR_UNSUPPORTED; }
   CK(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->qtSmem));
 
+  // per-CTA tile tables (level | tile x << 4 | tile y << 18): the kernels that cover all levels in one launch look their tile up
+  // instead of searching the level list and dividing (~50 instructions per warp in profiles/r01d)
+  std::vector<uint32_t> tiles;
+  for (int l = 0; l < nl; l++)
+    for (int t = 0; t < g.lv[l].tilesX * g.lv[l].tilesY; t++)
+      tiles.push_back((uint32_t)l | ((uint32_t)(t % g.lv[l].tilesX) << 4) | ((uint32_t)(t / g.lv[l].tilesX) << 18));
+  h->blurTilesOff = (int)tiles.size();
+  for (int l = 0; l < nl; l++)
+    for (int t = 0; t < g.lv[l].blurTilesX * g.lv[l].blurTilesY; t++)
+      tiles.push_back((uint32_t)l | ((uint32_t)(t % g.lv[l].blurTilesX) << 4) | ((uint32_t)(t / g.lv[l].blurTilesX) << 18));
+  CK(cudaMalloc(&h->dTiles, std::max<size_t>(1, tiles.size()) * sizeof(uint32_t)));
+  if (!tiles.empty()) CK(cudaMemcpy(h->dTiles, tiles.data(), tiles.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
   CK(cudaMalloc(&h->dRsx, std::max<size_t>(1, rsx.size()) * sizeof(RsX)));
   CK(cudaMalloc(&h->dRsy, std::max<size_t>(1, rsy.size()) * sizeof(RsY)));
   CK(cudaMalloc(&h->dInfo, info.size() * sizeof(uint16_t)));
@@ -268,7 +281,7 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
   b.lkp = s.lkp; b.lkpCount = s.lkpCount; b.lkpDest = s.lkpDest;
   b.qXY = s.qXY; b.qOrd = s.qOrd; b.qNode = s.qNode; b.qResp = s.qResp; b.qSel = s.qSel;
   b.kps = s.kps; b.desc = s.desc; b.counts = s.counts; b.mono = s.mono; b.status = s.status;
-  b.rsx = h->dRsx; b.rsy = h->dRsy; b.info = h->dInfo; b.pattern = h->dPattern; b.patternF = reinterpret_cast<const float4*>(h->dPattern + 1024);
+  b.rsx = h->dRsx; b.rsy = h->dRsy; b.info = h->dInfo; b.fastTiles = h->dTiles; b.blurTiles = h->dTiles + h->blurTilesOff; b.pattern = h->dPattern; b.patternF = reinterpret_cast<const float4*>(h->dPattern + 1024);
   s.last = b; s.lastFrames = nframes;
   h->lastSlot = si;
 

@@ -55,7 +55,7 @@ struct orbx_extractor {
   Geom g{};
   int inPitch = 0;  // pitch of the staged input
   long long pyrFrame = 0, blurFrame = 0;
-  RsX* dRsx = nullptr; RsY* dRsy = nullptr; uint16_t* dInfo = nullptr; int8_t* dPattern = nullptr;
+  RsX* dRsx = nullptr; RsY* dRsy = nullptr; uint16_t* dInfo = nullptr; uint32_t* dTiles = nullptr; int blurTilesOff = 0; int8_t* dPattern = nullptr;
   size_t qtSmem = 0;
   Slot slot[2];
   int lastSlot = 0;
