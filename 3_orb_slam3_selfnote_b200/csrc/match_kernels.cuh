@@ -118,6 +118,8 @@ struct QuerySet {            // one per frame
   const float* xr;           // right-image coordinate of the query (used when F.uRight != null and xrCheck)
   const uint8_t* desc;       // 32-byte descriptor per query
   int xrCheck;
+  int gate;                  // Fuse chi-square gate (ORBmatcher.cc:1547-1575): uses xr as the projected right coordinate
+  const float* invSigma2;    // mvInvLevelSigma2 (gate only)
   int* qOff; int* qCnt;      // per query: first entry / number of entries
   unsigned long long* entries; int entryCap; int* entryCursor;
 };
@@ -178,6 +180,18 @@ __global__ void __launch_bounds__(256) k_window_candidates(const GridFrame* fram
                 const float er = fabsf(__fsub_rn(xr, ur));
                 if (er > r) ok = false;
               }
+            }
+            if (ok && Q.gate) {  // ORBmatcher.cc:1547-1575
+              const float ex = __fsub_rn(x, kp.x), ey = __fsub_rn(y, kp.y);
+              float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+              const float kpr = F.uRight ? F.uRight[idx] : -1.0f;
+              double lim = 5.99;
+              if (kpr >= 0) {
+                const float er = __fsub_rn(Q.xr[i], kpr);
+                e2 = __fadd_rn(e2, __fmul_rn(er, er));
+                lim = 7.8;
+              }
+              if ((double)__fmul_rn(e2, Q.invSigma2[oct]) > lim) ok = false;
             }
             if (ok && pass == 1) {  // which cell of the column does item j belong to?
               cell = c0;
@@ -256,7 +270,8 @@ struct ResolveArgs {        // one per frame
   const uint8_t* observed;  // per query: MapPoint::Observations() > 0 (null = all observed)
   const float* angle;       // per query: source keypoint angle (rotation histogram)
   int* kpMp;                // in/out, F.mvpMapPoints as indices (-1 empty, -2 blocking, -3 non-blocking pre-existing)
-  int* assigned;            // scratch [nq]
+  int* assigned;            // scratch [nq] (k_resolve_best: best index per query)
+  int* bestDist;            // k_resolve_best only: best distance per query
   int* nmatches;            // out
   float nnratio;
   int distTh;
@@ -779,6 +794,179 @@ __global__ void __launch_bounds__(256) k_stereo_median(const __grid_constant__ G
     const uint32_t k = skey[i];
     if (!((float)(k >> 16) < thDist)) { out.uRight[o + (k & 0xffffu)] = -1.0f; out.depth[o + (k & 0xffffu)] = -1.0f; }
   }
+}
+
+// ---- Fuse / SearchBySim3 search loops, SearchByBoW, SearchForTriangulation ------------------------------
+// Independent window argmin (ORBmatcher.cc:1524-1590, 1728-1756, 1866-1895, 1946-1975): warp = query over its candidate list;
+// the key order (distance, grid traversal order) reproduces "first strict minimum wins".
+__global__ void __launch_bounds__(256) k_resolve_best(const QuerySet* sets, const ResolveArgs* args) {
+  const QuerySet Q = sets[blockIdx.y];
+  const ResolveArgs A = args[blockIdx.y];
+  const int lane = threadIdx.x & 31;
+  const int i = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (i >= Q.nq) return;
+  const int c = Q.qCnt[i];
+  unsigned long long k1 = kKeyNone;
+  const unsigned long long* e = Q.entries + Q.qOff[i];
+  for (int j = lane; j < c; j += 32) k1 = min(k1, e[j]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) k1 = min(k1, __shfl_xor_sync(0xffffffffu, k1, o));
+  if (lane == 0) {
+    A.assigned[i] = (k1 == kKeyNone) ? -1 : key_idx(k1);
+    A.bestDist[i] = (k1 == kKeyNone) ? 256 : key_dist(k1);
+  }
+}
+
+// One side of a bag-of-words bucketed search: the features of a keyframe / frame and its DBoW2::FeatureVector as CSR.
+struct BowSide {
+  const orbx_keypoint* kps; const uint8_t* desc; int n;
+  const unsigned* indices;      // concatenated per-node feature index lists
+  const uint8_t* elig;          // static eligibility per feature (may be null = all)
+  const uint8_t* stereo;        // mvuRight >= 0 (triangulation only, may be null)
+};
+struct BowWork { int p1; int b0; int b1; int off; };   // position in side 1's index list; [b0,b1) = matching node's range in side 2; entry offset
+struct BowArgs {
+  BowSide s1, s2;
+  const BowWork* work; int nwork;
+  unsigned long long* entries;  // [sum (b1 - b0)]
+  int* matches12;               // [n1]
+  int* nmatches;
+  int maxDist; float nnratio; int checkOrientation;
+  // triangulation gates (ORBmatcher.cc:1087-1146, Pinhole.cpp:150-164)
+  float F12[9]; float epx, epy; const float* scaleFactors2; const float* levelSigma2; int coarse;
+};
+// bow key: dist[63:40] | position in the node list [39:20] | feature index [19:0]
+__device__ __forceinline__ unsigned long long bow_key(int dist, int pos, int idx) {
+  return ((unsigned long long)dist << 40) | ((unsigned long long)pos << 20) | (unsigned)idx;
+}
+
+// distance pass of both SearchByBoW overloads: warp = one side-1 feature of a common node, lanes = the node's side-2 features
+__global__ void __launch_bounds__(256) k_bow_distances(const __grid_constant__ BowArgs A) {
+  const int lane = threadIdx.x & 31;
+  const int w = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (w >= A.nwork) return;
+  const BowWork W = A.work[w];
+  const int idx1 = (int)A.s1.indices[W.p1];
+  const bool live = (unsigned)idx1 < (unsigned)A.s1.n && (!A.s1.elig || A.s1.elig[idx1]);
+  uint32_t d1[8];
+  if (live) load_desc(A.s1.desc + 32ll * idx1, d1);
+  for (int p = W.b0 + lane; p < W.b1; p += 32) {
+    unsigned long long key = kKeyNone;
+    const int idx2 = (int)A.s2.indices[p];
+    if (live && (unsigned)idx2 < (unsigned)A.s2.n && (!A.s2.elig || A.s2.elig[idx2])) {
+      uint32_t d2[8];
+      load_desc(A.s2.desc + 32ll * idx2, d2);
+      key = bow_key(hamming8(d1, d2), p - W.b0, idx2);
+    }
+    A.entries[W.off + (p - W.b0)] = key;
+  }
+}
+
+// replay of the reference's order (node by node, then the node's list) with claiming of side-2 features: one warp
+__global__ void __launch_bounds__(32) k_bow_resolve(const __grid_constant__ BowArgs A) {
+  __shared__ uint8_t claimed[kMaxKpSmem];
+  const int lane = threadIdx.x;
+  for (int k = lane; k < A.s2.n; k += 32) claimed[k] = 0;
+  for (int k = lane; k < A.s1.n; k += 32) A.matches12[k] = -1;
+  __syncwarp();
+  for (int w = 0; w < A.nwork; w++) {
+    const BowWork W = A.work[w];
+    const int idx1 = (int)A.s1.indices[W.p1];
+    if ((unsigned)idx1 >= (unsigned)A.s1.n || (A.s1.elig && !A.s1.elig[idx1])) continue;
+    unsigned long long k1 = kKeyNone, k2 = kKeyNone;
+    const int c = W.b1 - W.b0;
+    for (int j = lane; j < c; j += 32) {
+      const unsigned long long k = A.entries[W.off + j];
+      if (k != kKeyNone && !claimed[(int)(k & 0xfffffu)]) top2_insert(k, k1, k2);
+    }
+    top2_warp(k1, k2);
+    if (k1 == kKeyNone) continue;
+    const int bestDist1 = (int)(k1 >> 40), bestIdx2 = (int)(k1 & 0xfffffu);
+    const int bestDist2 = (k2 == kKeyNone) ? 256 : (int)(k2 >> 40);
+    if (bestDist1 <= A.maxDist && (float)bestDist1 < __fmul_rn(A.nnratio, (float)bestDist2)) {
+      if (lane == 0) { A.matches12[idx1] = bestIdx2; claimed[bestIdx2] = 1; }
+      __syncwarp();
+    }
+  }
+}
+
+// SearchForTriangulation (ORBmatcher.cc:1046-1175): no claiming in the reference (vbMatched2 is never set), so every side-1
+// feature is independent: last minimum within dist <= TH_LOW among the gated candidates (":dist>bestDist -> continue").
+__global__ void __launch_bounds__(256) k_bow_triangulate(const __grid_constant__ BowArgs A) {
+  const int lane = threadIdx.x & 31;
+  const int w = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (w >= A.nwork) return;
+  const BowWork W = A.work[w];
+  const int idx1 = (int)A.s1.indices[W.p1];
+  if ((unsigned)idx1 >= (unsigned)A.s1.n || !A.s1.elig[idx1]) return;
+  const bool bStereo1 = A.s1.stereo && A.s1.stereo[idx1];
+  const orbx_keypoint kp1 = A.s1.kps[idx1];
+  uint32_t d1[8];
+  load_desc(A.s1.desc + 32ll * idx1, d1);
+  // epipolar line of kp1 in the second image
+  const float a = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, A.F12[0]), __fmul_rn(kp1.y, A.F12[3])), A.F12[6]);
+  const float b = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, A.F12[1]), __fmul_rn(kp1.y, A.F12[4])), A.F12[7]);
+  const float c = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, A.F12[2]), __fmul_rn(kp1.y, A.F12[5])), A.F12[8]);
+  const float den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
+  unsigned long long best = kKeyNone;
+  for (int p = W.b0 + lane; p < W.b1; p += 32) {
+    const int idx2 = (int)A.s2.indices[p];
+    if ((unsigned)idx2 >= (unsigned)A.s2.n || !A.s2.elig[idx2]) continue;
+    uint32_t d2[8];
+    load_desc(A.s2.desc + 32ll * idx2, d2);
+    const int dist = hamming8(d1, d2);
+    if (dist > 50) continue;  // TH_LOW
+    const orbx_keypoint kp2 = A.s2.kps[idx2];
+    const bool bStereo2 = A.s2.stereo && A.s2.stereo[idx2];
+    if (!bStereo1 && !bStereo2) {
+      const float distex = __fsub_rn(A.epx, kp2.x), distey = __fsub_rn(A.epy, kp2.y);
+      if (__fadd_rn(__fmul_rn(distex, distex), __fmul_rn(distey, distey)) < __fmul_rn(100.0f, A.scaleFactors2[kp2.octave])) continue;
+    }
+    bool ok = A.coarse != 0;
+    if (den != 0.0f) {
+      const float num = __fadd_rn(__fadd_rn(__fmul_rn(a, kp2.x), __fmul_rn(b, kp2.y)), c);
+      const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+      if ((double)dsqr < 3.84 * (double)A.levelSigma2[kp2.octave]) ok = true;
+    }
+    if (!ok) continue;
+    best = min(best, bow_key(dist, 0xfffff - (p - W.b0), idx2));   // later list position wins ties
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+  if (lane == 0 && best != kKeyNone) A.matches12[idx1] = (int)(best & 0xfffffu);
+}
+
+// rotation-consistency filter over matches12 (ORBmatcher.cc:453-470, 957-975, 1190-1209) + final count: one CTA
+__global__ void __launch_bounds__(256) k_bow_rotfilter(const __grid_constant__ BowArgs A) {
+  __shared__ int hist[30];
+  __shared__ int keep[3];
+  __shared__ int total;
+  const int tid = threadIdx.x;
+  if (tid < 30) hist[tid] = 0;
+  if (tid == 0) total = 0;
+  __syncthreads();
+  int mine = 0;
+  if (A.checkOrientation) {
+    for (int i = tid; i < A.s1.n; i += 256) {
+      const int m = A.matches12[i];
+      if (m >= 0) atomicAdd(&hist[rot_bin(A.s1.kps[i].angle, A.s2.kps[m].angle)], 1);
+    }
+    __syncthreads();
+    if (tid == 0) { int i1, i2, i3; three_maxima(hist, 30, i1, i2, i3); keep[0] = i1; keep[1] = i2; keep[2] = i3; }
+    __syncthreads();
+  }
+  for (int i = tid; i < A.s1.n; i += 256) {
+    const int m = A.matches12[i];
+    if (m < 0) continue;
+    if (A.checkOrientation) {
+      const int bin = rot_bin(A.s1.kps[i].angle, A.s2.kps[m].angle);
+      if (bin != keep[0] && bin != keep[1] && bin != keep[2]) { A.matches12[i] = -1; continue; }
+    }
+    mine++;
+  }
+  atomicAdd(&total, mine);
+  __syncthreads();
+  if (tid == 0) *A.nmatches = total;
 }
 
 }  // namespace orbx

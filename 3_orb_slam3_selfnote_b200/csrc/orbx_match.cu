@@ -89,9 +89,10 @@ struct HostQueries {
   std::vector<int8_t> minL, maxL;
   const uint8_t* desc = nullptr;  // nq x 32
   bool xrCheck = false;
+  bool gate = false; const float* invSigma2 = nullptr; int nSigma = 0;   // Fuse chi-square gate (xr = projected right coordinate)
 };
 
-enum ResolveKind { RESOLVE_NONE, RESOLVE_MAPPOINTS, RESOLVE_WINDOW, RESOLVE_INIT };
+enum ResolveKind { RESOLVE_NONE, RESOLVE_MAPPOINTS, RESOLVE_WINDOW, RESOLVE_INIT, RESOLVE_BEST };
 
 struct WindowJob {
   // frame (host, or device when devKps != null)
@@ -106,6 +107,8 @@ struct WindowJob {
   // init search
   const orbx_frame_view* F1 = nullptr; float* prevMatched = nullptr; int* matches12 = nullptr;
   int* nmatches = nullptr;
+  // independent argmin (Fuse / SearchBySim3)
+  int* bestIdx = nullptr; int* bestDist = nullptr;
   // features_in_area
   std::vector<unsigned long long>* entriesOut = nullptr;
 };
@@ -117,7 +120,7 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
   // ---- plan the arena
   ArenaPlan plan;
   struct Off { size_t kps, desc, uRight, cellStart, cellItems, valid, x, y, r, xr, minL, maxL, qdesc, qOff, qCnt, entries, cursor,
-               observed, angle, kpMp, assigned, nmatches, kps1, prevMatched, m12, m21, mdist, bins; };
+               observed, angle, kpMp, assigned, nmatches, kps1, prevMatched, m12, m21, mdist, bins, sigma; };
   std::vector<Off> off(nj);
   std::vector<int> entryCap(nj);
   for (int j = 0; j < nj; j++) {
@@ -132,7 +135,9 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
     o.cellItems = plan.add((size_t)std::max(n, 1) * sizeof(int));
     o.valid = plan.add(std::max(nq, 1));
     o.x = plan.add((size_t)std::max(nq, 1) * 4); o.y = plan.add((size_t)std::max(nq, 1) * 4); o.r = plan.add((size_t)std::max(nq, 1) * 4);
-    o.xr = J.q.xrCheck ? plan.add((size_t)std::max(nq, 1) * 4) : (size_t)-1;
+    o.xr = (J.q.xrCheck || (J.q.gate && !J.q.xr.empty())) ? plan.add((size_t)std::max(nq, 1) * 4) : (size_t)-1;
+    o.sigma = J.q.gate ? plan.add((size_t)std::max(J.q.nSigma, 1) * 4) : (size_t)-1;
+    if (kind == RESOLVE_BEST) o.m12 = plan.add((size_t)std::max(nq, 1) * 4);
     o.minL = plan.add(std::max(nq, 1)); o.maxL = plan.add(std::max(nq, 1));
     o.qdesc = plan.add((size_t)std::max(nq, 1) * 32);
     o.qOff = plan.add((size_t)std::max(nq, 1) * 4); o.qCnt = plan.add((size_t)std::max(nq, 1) * 4);
@@ -193,10 +198,12 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
     CK(up(o.valid, J.q.valid.data(), nq)); CK(up(o.x, J.q.x.data(), (size_t)nq * 4)); CK(up(o.y, J.q.y.data(), (size_t)nq * 4));
     CK(up(o.r, J.q.r.data(), (size_t)nq * 4)); CK(up(o.minL, J.q.minL.data(), nq)); CK(up(o.maxL, J.q.maxL.data(), nq));
     CK(up(o.qdesc, J.q.desc, (size_t)nq * 32));
-    if (J.q.xrCheck) CK(up(o.xr, J.q.xr.data(), (size_t)nq * 4));
+    if (o.xr != (size_t)-1) CK(up(o.xr, J.q.xr.data(), (size_t)nq * 4));
+    if (J.q.gate) CK(up(o.sigma, J.q.invSigma2, (size_t)J.q.nSigma * 4));
     Q.valid = at<uint8_t>(m, o.valid); Q.x = at<float>(m, o.x); Q.y = at<float>(m, o.y); Q.r = at<float>(m, o.r);
     Q.minL = at<int8_t>(m, o.minL); Q.maxL = at<int8_t>(m, o.maxL); Q.desc = at<uint8_t>(m, o.qdesc);
-    Q.xr = J.q.xrCheck ? at<float>(m, o.xr) : nullptr; Q.xrCheck = J.q.xrCheck ? 1 : 0;
+    Q.xr = o.xr != (size_t)-1 ? at<float>(m, o.xr) : nullptr; Q.xrCheck = J.q.xrCheck ? 1 : 0;
+    Q.gate = J.q.gate ? 1 : 0; Q.invSigma2 = J.q.gate ? at<float>(m, o.sigma) : nullptr;
     Q.qOff = at<int>(m, o.qOff); Q.qCnt = at<int>(m, o.qCnt);
     Q.entries = at<unsigned long long>(m, o.entries); Q.entryCap = entryCap[j]; Q.entryCursor = at<int>(m, o.cursor);
     CK(cudaMemsetAsync(m->arena + o.cursor, 0, 4, st));
@@ -210,6 +217,10 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
       A.angle = J.angle ? at<float>(m, o.angle) : nullptr;
       A.kpMp = at<int>(m, o.kpMp); A.assigned = at<int>(m, o.assigned); A.nmatches = at<int>(m, o.nmatches);
       A.nnratio = J.nnratio; A.distTh = J.distTh; A.anyMpBlocks = J.anyMpBlocks; A.checkOrientation = J.checkOrientation;
+    } else if (kind == RESOLVE_BEST) {
+      ResolveArgs& A = rargs[j];
+      A = ResolveArgs{};
+      A.assigned = at<int>(m, o.assigned); A.bestDist = at<int>(m, o.m12);
     } else if (kind == RESOLVE_INIT) {
       InitArgs& A = iargs[j];
       CK(up(o.kps1, J.F1->keypoints, (size_t)nq * sizeof(orbx_keypoint)));
@@ -231,6 +242,7 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
   if (kind == RESOLVE_MAPPOINTS) k_resolve_mappoints<<<nj, 32, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs));
   else if (kind == RESOLVE_WINDOW) k_resolve_window<<<nj, 32, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs));
   else if (kind == RESOLVE_INIT) k_resolve_init<<<nj, 32, 0, st>>>(dFrames, dSets, at<InitArgs>(m, oArgs));
+  else if (kind == RESOLVE_BEST && maxQ > 0) k_resolve_best<<<dim3((maxQ + 7) / 8, nj), 256, 0, st>>>(dSets, at<ResolveArgs>(m, oArgs));
   CK(cudaGetLastError());
   // ---- results
   int status = 0;
@@ -245,6 +257,9 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
       CK(cudaMemcpyAsync(J.matches12, m->arena + o.m12, (size_t)J.q.nq * 4, cudaMemcpyDeviceToHost, st));
       CK(cudaMemcpyAsync(J.prevMatched, m->arena + o.prevMatched, (size_t)J.q.nq * 8, cudaMemcpyDeviceToHost, st));
       CK(cudaMemcpyAsync(J.nmatches, m->arena + o.nmatches, 4, cudaMemcpyDeviceToHost, st));
+    } else if (kind == RESOLVE_BEST) {
+      CK(cudaMemcpyAsync(J.bestIdx, m->arena + o.assigned, (size_t)J.q.nq * 4, cudaMemcpyDeviceToHost, st));
+      CK(cudaMemcpyAsync(J.bestDist, m->arena + o.m12, (size_t)J.q.nq * 4, cudaMemcpyDeviceToHost, st));
     } else if (J.entriesOut) {
       int cnt = 0;
       CK(cudaMemcpyAsync(&cnt, m->arena + o.qCnt, 4, cudaMemcpyDeviceToHost, st));
@@ -426,11 +441,165 @@ int orbx_search_by_projection_window(orbx_matcher* m, const orbx_frame_view* F, 
     q.r[i] = ok ? th * F->scale_factors[l] : 0.f;
     if (mode == 1) { q.minL[i] = (int8_t)l; q.maxL[i] = -1; }
     else if (mode == 2) { q.minL[i] = 0; q.maxL[i] = (int8_t)l; }
+    else if (mode == 3) { q.minL[i] = (int8_t)(l - 1); q.maxL[i] = (int8_t)l; }   // ORBmatcher.cc:573-576, 689-692
     else { q.minL[i] = (int8_t)(l - 1); q.maxL[i] = (int8_t)(l + 1); }
   }
   J.observed = observed; J.angle = angle; J.kpMp = kpMp; J.kpMpLen = F->n; J.distTh = distTh; J.anyMpBlocks = anyMpBlocks;
   J.checkOrientation = checkOrientation; J.nmatches = nmatches;
   return run_window_jobs(m, jobs, RESOLVE_WINDOW);
+}
+
+int orbx_search_window_best(orbx_matcher* m, const orbx_frame_view* F, int n, const uint8_t* valid, const float* u, const float* v,
+                            const float* radius, const int* level, const float* ur, const uint8_t* desc, int gate,
+                            const float* invLevelSigma2, int* bestIdx, int* bestDist) {
+  if (!m || n < 0 || (n > 0 && (!valid || !u || !v || !radius || !level || !desc || !bestIdx || !bestDist))) return ORBX_ERR_ARG;
+  int rc = check_view(F, false);
+  if (rc != ORBX_OK) return rc;
+  if (gate && (!invLevelSigma2 || F->nlevels < 1 || (F->u_right && !ur))) { set_error("chi-square gate needs inv_level_sigma2 (and ur for stereo keyframes)"); return ORBX_ERR_ARG; }
+  if (n == 0) return ORBX_OK;
+  std::vector<WindowJob> jobs(1);
+  WindowJob& J = jobs[0];
+  J.F = F; set_bounds(J, F);
+  HostQueries& q = J.q;
+  q.nq = n; q.valid.assign(valid, valid + n); q.x.assign(u, u + n); q.y.assign(v, v + n); q.r.assign(radius, radius + n);
+  q.minL.resize(n); q.maxL.resize(n);
+  q.desc = desc;
+  q.gate = gate != 0; q.invSigma2 = invLevelSigma2; q.nSigma = gate ? F->nlevels : 0;
+  if (q.gate && ur) q.xr.assign(ur, ur + n);
+  for (int i = 0; i < n; i++) {  // ORBmatcher.cc:1535-1537: kpLevel in [nPredictedLevel-1, nPredictedLevel]
+    const int l = level[i];
+    if (l < 0 || l > 127) q.valid[i] = 0;
+    q.minL[i] = (int8_t)(l - 1); q.maxL[i] = (int8_t)l;
+  }
+  J.bestIdx = bestIdx; J.bestDist = bestDist;
+  return run_window_jobs(m, jobs, RESOLVE_BEST);
+}
+
+namespace {
+// Common node ids of two FeatureVectors in ascending order, as the reference's merge loop visits them (ORBmatcher.cc:289-299,
+// 440-451): one work item per (side-1 list position, side-2 node range).
+int bow_check(const orbx_featvec* fv, int n) {
+  if (!fv || fv->nnodes < 0 || (fv->nnodes > 0 && (!fv->node_ids || !fv->node_start || !fv->indices))) return ORBX_ERR_ARG;
+  for (int i = 0; i < fv->nnodes; i++) {
+    if (fv->node_start[i + 1] < fv->node_start[i]) return ORBX_ERR_ARG;
+    if (i > 0 && fv->node_ids[i] <= fv->node_ids[i - 1]) return ORBX_ERR_ARG;
+  }
+  (void)n;
+  return ORBX_OK;
+}
+
+struct BowProblem {
+  int n1, n2;
+  const orbx_keypoint* kps1; const uint8_t* desc1; const orbx_featvec* fv1; const uint8_t* elig1; const uint8_t* stereo1;
+  const orbx_keypoint* kps2; const uint8_t* desc2; const orbx_featvec* fv2; const uint8_t* elig2; const uint8_t* stereo2;
+  int maxDist; float nnratio; int checkOrientation;
+  bool triangulate; const float* F12; float epx, epy; const float* scaleFactors2; const float* levelSigma2; int nlevels; int coarse;
+};
+
+int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches) {
+  if (!m || !matches12 || !nmatches || P.n1 < 0 || P.n2 < 0) return ORBX_ERR_ARG;
+  if ((P.n1 > 0 && (!P.kps1 || !P.desc1)) || (P.n2 > 0 && (!P.kps2 || !P.desc2))) return ORBX_ERR_ARG;
+  if (bow_check(P.fv1, P.n1) != ORBX_OK || bow_check(P.fv2, P.n2) != ORBX_OK) { set_error("bad feature vector (node ids must ascend)"); return ORBX_ERR_ARG; }
+  if (P.n1 >= (1 << 20) || P.n2 >= (1 << 20)) { set_error("more than 2^20 features per keyframe is unsupported"); return ORBX_ERR_UNSUPPORTED; }
+  if (!P.triangulate && P.n2 > kMaxKpSmem) { set_error("more than %d features per frame is unsupported by the resolve kernel", kMaxKpSmem); return ORBX_ERR_UNSUPPORTED; }
+  *nmatches = 0;
+  for (int i = 0; i < P.n1; i++) matches12[i] = -1;
+  if (P.n1 == 0 || P.n2 == 0) return ORBX_OK;
+  CK(cudaSetDevice(m->device));
+  std::vector<BowWork> work;
+  long long nEntries = 0;
+  {
+    const orbx_featvec &a = *P.fv1, &b = *P.fv2;
+    int ia = 0, ib = 0;
+    while (ia < a.nnodes && ib < b.nnodes) {
+      if (a.node_ids[ia] == b.node_ids[ib]) {
+        const int b0 = b.node_start[ib], b1 = b.node_start[ib + 1];
+        if (b1 - b0 >= (1 << 20)) { set_error("vocabulary node with 2^20 features"); return ORBX_ERR_UNSUPPORTED; }
+        for (int p1 = a.node_start[ia]; p1 < a.node_start[ia + 1]; p1++) {
+          work.push_back(BowWork{p1, b0, b1, (int)nEntries});
+          nEntries += b1 - b0;
+          if (nEntries > (1ll << 30)) { set_error("candidate list capacity exceeded"); return ORBX_ERR_CAPACITY; }
+        }
+        ia++; ib++;
+      } else if (a.node_ids[ia] < b.node_ids[ib]) ia++;
+      else ib++;
+    }
+  }
+  const int nw = (int)work.size();
+  if (nw == 0) return ORBX_OK;
+  const int ni1 = P.fv1->node_start[P.fv1->nnodes], ni2 = P.fv2->node_start[P.fv2->nnodes];
+  ArenaPlan plan;
+  const size_t oK1 = plan.add((size_t)P.n1 * sizeof(orbx_keypoint)), oD1 = plan.add((size_t)P.n1 * 32), oI1 = plan.add((size_t)std::max(ni1, 1) * 4);
+  const size_t oK2 = plan.add((size_t)P.n2 * sizeof(orbx_keypoint)), oD2 = plan.add((size_t)P.n2 * 32), oI2 = plan.add((size_t)std::max(ni2, 1) * 4);
+  const size_t oE1 = P.elig1 ? plan.add(P.n1) : (size_t)-1, oE2 = P.elig2 ? plan.add(P.n2) : (size_t)-1;
+  const size_t oS1 = P.stereo1 ? plan.add(P.n1) : (size_t)-1, oS2 = P.stereo2 ? plan.add(P.n2) : (size_t)-1;
+  const size_t oW = plan.add((size_t)nw * sizeof(BowWork));
+  const size_t oEnt = P.triangulate ? (size_t)-1 : plan.add((size_t)std::max<long long>(nEntries, 1) * 8);
+  const size_t oM = plan.add((size_t)P.n1 * 4), oN = plan.add(4);
+  const size_t oSF = P.triangulate ? plan.add((size_t)P.nlevels * 4) : (size_t)-1, oLS = P.triangulate ? plan.add((size_t)P.nlevels * 4) : (size_t)-1;
+  int rc = arena_ensure(m, plan.total);
+  if (rc != ORBX_OK) return rc;
+  cudaStream_t st = m->stream;
+  auto up = [&](size_t o, const void* src, size_t bytes) -> cudaError_t {
+    if (bytes == 0 || !src || o == (size_t)-1) return cudaSuccess;
+    return cudaMemcpyAsync(m->arena + o, src, bytes, cudaMemcpyHostToDevice, st);
+  };
+  CK(up(oK1, P.kps1, (size_t)P.n1 * sizeof(orbx_keypoint))); CK(up(oD1, P.desc1, (size_t)P.n1 * 32)); CK(up(oI1, P.fv1->indices, (size_t)ni1 * 4));
+  CK(up(oK2, P.kps2, (size_t)P.n2 * sizeof(orbx_keypoint))); CK(up(oD2, P.desc2, (size_t)P.n2 * 32)); CK(up(oI2, P.fv2->indices, (size_t)ni2 * 4));
+  CK(up(oE1, P.elig1, P.n1)); CK(up(oE2, P.elig2, P.n2)); CK(up(oS1, P.stereo1, P.n1)); CK(up(oS2, P.stereo2, P.n2));
+  CK(up(oW, work.data(), (size_t)nw * sizeof(BowWork)));
+  CK(up(oSF, P.scaleFactors2, (size_t)P.nlevels * 4)); CK(up(oLS, P.levelSigma2, (size_t)P.nlevels * 4));
+  BowArgs A{};
+  A.s1 = BowSide{at<orbx_keypoint>(m, oK1), at<uint8_t>(m, oD1), P.n1, at<unsigned>(m, oI1), P.elig1 ? at<uint8_t>(m, oE1) : nullptr,
+                 P.stereo1 ? at<uint8_t>(m, oS1) : nullptr};
+  A.s2 = BowSide{at<orbx_keypoint>(m, oK2), at<uint8_t>(m, oD2), P.n2, at<unsigned>(m, oI2), P.elig2 ? at<uint8_t>(m, oE2) : nullptr,
+                 P.stereo2 ? at<uint8_t>(m, oS2) : nullptr};
+  A.work = at<BowWork>(m, oW); A.nwork = nw;
+  A.entries = P.triangulate ? nullptr : at<unsigned long long>(m, oEnt);
+  A.matches12 = at<int>(m, oM); A.nmatches = at<int>(m, oN);
+  A.maxDist = P.maxDist; A.nnratio = P.nnratio; A.checkOrientation = P.checkOrientation;
+  if (P.triangulate) {
+    memcpy(A.F12, P.F12, sizeof(A.F12));
+    A.epx = P.epx; A.epy = P.epy; A.scaleFactors2 = at<float>(m, oSF); A.levelSigma2 = at<float>(m, oLS); A.coarse = P.coarse;
+    CK(cudaMemsetAsync(m->arena + oM, 0xff, (size_t)P.n1 * 4, st));
+    k_bow_triangulate<<<(nw + 7) / 8, 256, 0, st>>>(A);
+  } else {
+    k_bow_distances<<<(nw + 7) / 8, 256, 0, st>>>(A);
+    k_bow_resolve<<<1, 32, 0, st>>>(A);
+  }
+  k_bow_rotfilter<<<1, 256, 0, st>>>(A);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(matches12, m->arena + oM, (size_t)P.n1 * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(nmatches, m->arena + oN, 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return ORBX_OK;
+}
+}  // namespace
+
+int orbx_search_by_bow(orbx_matcher* m, int n1, const orbx_keypoint* kps1, const uint8_t* desc1, const orbx_featvec* fv1, const uint8_t* elig1,
+                       int n2, const orbx_keypoint* kps2, const uint8_t* desc2, const orbx_featvec* fv2, const uint8_t* elig2, int maxDist,
+                       float nnratio, int checkOrientation, int* matches12, int* nmatches) {
+  BowProblem P{};
+  P.n1 = n1; P.kps1 = kps1; P.desc1 = desc1; P.fv1 = fv1; P.elig1 = elig1;
+  P.n2 = n2; P.kps2 = kps2; P.desc2 = desc2; P.fv2 = fv2; P.elig2 = elig2;
+  P.maxDist = maxDist; P.nnratio = nnratio; P.checkOrientation = checkOrientation; P.triangulate = false;
+  return run_bow(m, P, matches12, nmatches);
+}
+
+int orbx_search_for_triangulation(orbx_matcher* m, int n1, const orbx_keypoint* kps1, const uint8_t* desc1, const orbx_featvec* fv1,
+                                  const uint8_t* elig1, const uint8_t* stereo1, int n2, const orbx_keypoint* kps2, const uint8_t* desc2,
+                                  const orbx_featvec* fv2, const uint8_t* elig2, const uint8_t* stereo2, const float* F12, float epx,
+                                  float epy, const float* scaleFactors2, const float* levelSigma2_2, int nlevels, int coarse,
+                                  int checkOrientation, int* matches12, int* nmatches) {
+  if (!F12 || !scaleFactors2 || !levelSigma2_2 || nlevels < 1 || !elig1 || !elig2) return ORBX_ERR_ARG;
+  for (int i = 0; i < n2 && kps2; i++)
+    if (kps2[i].octave < 0 || kps2[i].octave >= nlevels) { set_error("keypoint octave outside the level tables"); return ORBX_ERR_ARG; }
+  BowProblem P{};
+  P.n1 = n1; P.kps1 = kps1; P.desc1 = desc1; P.fv1 = fv1; P.elig1 = elig1; P.stereo1 = stereo1;
+  P.n2 = n2; P.kps2 = kps2; P.desc2 = desc2; P.fv2 = fv2; P.elig2 = elig2; P.stereo2 = stereo2;
+  P.checkOrientation = checkOrientation; P.triangulate = true;
+  P.F12 = F12; P.epx = epx; P.epy = epy; P.scaleFactors2 = scaleFactors2; P.levelSigma2 = levelSigma2_2; P.nlevels = nlevels; P.coarse = coarse;
+  return run_bow(m, P, matches12, nmatches);
 }
 
 int orbx_search_for_initialization(orbx_matcher* m, const orbx_frame_view* F1, const orbx_frame_view* F2, float* prevMatched, int windowSize,

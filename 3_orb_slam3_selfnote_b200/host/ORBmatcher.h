@@ -5,9 +5,13 @@
 // F.mvpMapPoints, pMP->mbTrackInView, ...), so they bind to the reference's own Frame / MapPoint classes unchanged and to
 // the small mocks of tests/cpp/shim_test.cc alike.  Pose algebra / camera projection (the loop prologues of the
 // Frame-Frame and Frame-KeyFrame overloads) stay on the host: see SearchByProjectionProjected and INTEGRATION.md.
+// SearchByProjectionProjected with mode 3 is the search loop of both SearchByProjection(KeyFrame*, Scw, ...) overloads
+// (src/ORBmatcher.cc:489-720: anyMpBlocks = true, distTh = floor(TH_LOW*ratioHamming), kpMp = vpMatched as -1 / -2).
 #pragma once
 #include <climits>
+#include <cstring>
 #include <stdexcept>
+#include <utility>
 #include <vector>
 
 #include "../../include/orbx.h"
@@ -99,6 +103,95 @@ class ORBmatcher {
     return nmatches;
   }
 
+  // ---- SURVEY.md section 8(f) rank 1 ---------------------------------------------------------------------------------------
+  // Search matches between MapPoints in a KeyFrame and ORB in a Frame, brute force constrained to ORB that belong to the same
+  // vocabulary node (relocalisation / reference-keyframe tracking), src/ORBmatcher.cc:273-475.  Nleft == -1 frames.
+  template <class KeyFrameT, class FrameT, class MapPointT>
+  int SearchByBoW(KeyFrameT* pKF, FrameT& F, std::vector<MapPointT*>& vpMapPointMatches) {
+    if (F.Nleft != -1) throw std::runtime_error("ORBmatcher::SearchByBoW: fisheye stereo (Nleft != -1) is not offloaded");
+    const std::vector<MapPointT*> vpMapPointsKF = pKF->GetMapPointMatches();
+    vpMapPointMatches.assign(F.N, static_cast<MapPointT*>(nullptr));
+    const int n1 = (int)vpMapPointsKF.size();
+    std::vector<uint8_t> elig1(std::max(n1, 1));
+    for (int i = 0; i < n1; i++) elig1[i] = vpMapPointsKF[i] && !vpMapPointsKF[i]->isBad();
+    FeatVecHolder fv1(pKF->mFeatVec), fv2(F.mFeatVec);
+    DescHolder d1(pKF->mDescriptors, n1), d2(F.mDescriptors, F.N);
+    std::vector<int> m12(std::max(n1, 1), -1);
+    int nmatches = 0;
+    orbx_shim::check(orbx_search_by_bow(m_, n1, reinterpret_cast<const orbx_keypoint*>(pKF->mvKeysUn.data()), d1.p, &fv1.v, elig1.data(), F.N,
+                                        reinterpret_cast<const orbx_keypoint*>(F.mvKeys.data()), d2.p, &fv2.v, nullptr, TH_LOW, mfNNratio,
+                                        mbCheckOrientation ? 1 : 0, m12.data(), &nmatches),
+                     "orbx_search_by_bow");
+    for (int i = 0; i < n1; i++)
+      if (m12[i] >= 0) vpMapPointMatches[m12[i]] = vpMapPointsKF[i];
+    return nmatches;
+  }
+
+  // Matches between the map points of two keyframes (loop detection / merging), src/ORBmatcher.cc:839-979.
+  template <class KeyFrameT, class MapPointT>
+  int SearchByBoW(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12) {
+    const std::vector<MapPointT*> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
+    const int n1 = (int)std::min(vpMapPoints1.size(), pKF1->mvKeysUn.size()), n2 = (int)std::min(vpMapPoints2.size(), pKF2->mvKeysUn.size());
+    vpMatches12.assign(vpMapPoints1.size(), static_cast<MapPointT*>(nullptr));
+    std::vector<uint8_t> elig1(std::max(n1, 1)), elig2(std::max(n2, 1));
+    for (int i = 0; i < n1; i++) elig1[i] = vpMapPoints1[i] && !vpMapPoints1[i]->isBad();
+    for (int i = 0; i < n2; i++) elig2[i] = vpMapPoints2[i] && !vpMapPoints2[i]->isBad();
+    FeatVecHolder fv1(pKF1->mFeatVec), fv2(pKF2->mFeatVec);
+    DescHolder d1(pKF1->mDescriptors, n1), d2(pKF2->mDescriptors, n2);
+    std::vector<int> m12(std::max(n1, 1), -1);
+    int nmatches = 0;
+    orbx_shim::check(orbx_search_by_bow(m_, n1, reinterpret_cast<const orbx_keypoint*>(pKF1->mvKeysUn.data()), d1.p, &fv1.v, elig1.data(), n2,
+                                        reinterpret_cast<const orbx_keypoint*>(pKF2->mvKeysUn.data()), d2.p, &fv2.v, elig2.data(), TH_LOW - 1,
+                                        mfNNratio, mbCheckOrientation ? 1 : 0, m12.data(), &nmatches),
+                     "orbx_search_by_bow");
+    for (int i = 0; i < n1; i++)
+      if (m12[i] >= 0) vpMatches12[i] = vpMapPoints2[m12[i]];
+    return nmatches;
+  }
+
+  // Matching to triangulate new MapPoints, src/ORBmatcher.cc:981-1222, for pinhole keyframes without a second camera.  The
+  // reference ignores its F12 argument and lets Pinhole::epipolarConstrain rebuild the matrix per pair
+  // (src/CameraModels/Pinhole.cpp:145-148); here the caller forms it once (row-major 3x3) together with the epipole
+  // ep = pKF2->mpCamera->project(R2w*Cw + t2w) (src/ORBmatcher.cc:988-994).
+  template <class KeyFrameT>
+  int SearchForTriangulation(KeyFrameT* pKF1, KeyFrameT* pKF2, const float* F12, const cvx::Point2f& ep,
+                             std::vector<std::pair<size_t, size_t> >& vMatchedPairs, const bool bOnlyStereo, const bool bCoarse = false) {
+    const int n1 = pKF1->N, n2 = pKF2->N;
+    std::vector<uint8_t> e1(std::max(n1, 1)), e2(std::max(n2, 1)), s1(std::max(n1, 1)), s2(std::max(n2, 1));
+    for (int i = 0; i < n1; i++) { s1[i] = pKF1->mvuRight[i] >= 0; e1[i] = !pKF1->GetMapPoint(i) && (!bOnlyStereo || s1[i]); }
+    for (int i = 0; i < n2; i++) { s2[i] = pKF2->mvuRight[i] >= 0; e2[i] = !pKF2->GetMapPoint(i) && (!bOnlyStereo || s2[i]); }
+    FeatVecHolder fv1(pKF1->mFeatVec), fv2(pKF2->mFeatVec);
+    DescHolder d1(pKF1->mDescriptors, n1), d2(pKF2->mDescriptors, n2);
+    std::vector<int> m12(std::max(n1, 1), -1);
+    int nmatches = 0;
+    orbx_shim::check(orbx_search_for_triangulation(m_, n1, reinterpret_cast<const orbx_keypoint*>(pKF1->mvKeysUn.data()), d1.p, &fv1.v, e1.data(),
+                                                   s1.data(), n2, reinterpret_cast<const orbx_keypoint*>(pKF2->mvKeysUn.data()), d2.p, &fv2.v,
+                                                   e2.data(), s2.data(), F12, ep.x, ep.y, pKF2->mvScaleFactors.data(), pKF2->mvLevelSigma2.data(),
+                                                   (int)pKF2->mvScaleFactors.size(), bCoarse ? 1 : 0, mbCheckOrientation ? 1 : 0, m12.data(),
+                                                   &nmatches),
+                     "orbx_search_for_triangulation");
+    vMatchedPairs.clear();
+    vMatchedPairs.reserve(nmatches);
+    for (int i = 0; i < n1; i++)
+      if (m12[i] >= 0) vMatchedPairs.push_back(std::make_pair((size_t)i, (size_t)m12[i]));
+    return nmatches;
+  }
+
+  // The search loop of Fuse (src/ORBmatcher.cc:1524-1590, :1728-1756; gate = true for the first overload) and of both passes of
+  // SearchBySim3 (:1866-1895, :1946-1975) once the caller has projected the points: best keypoint index / distance per point.
+  // Replace / AddObservation / the Sim3 agreement check stay with the caller, in the reference's order.
+  template <class KeyFrameT>
+  void SearchWindowBest(KeyFrameT* pKF, const std::vector<uint8_t>& valid, const std::vector<float>& u, const std::vector<float>& v,
+                        const std::vector<float>& radius, const std::vector<int>& level, const std::vector<float>* ur,
+                        const std::vector<uint8_t>& desc, bool gate, std::vector<int>& bestIdx, std::vector<int>& bestDist) {
+    FrameViewHolder fv(*pKF);
+    bestIdx.assign(valid.size(), -1); bestDist.assign(valid.size(), 256);
+    orbx_shim::check(orbx_search_window_best(m_, &fv.v, (int)valid.size(), valid.data(), u.data(), v.data(), radius.data(), level.data(),
+                                             ur ? ur->data() : nullptr, desc.data(), gate ? 1 : 0, gate ? pKF->mvInvLevelSigma2.data() : nullptr,
+                                             bestIdx.data(), bestDist.data()),
+                     "orbx_search_window_best");
+  }
+
   // Frame::ComputeStereoMatches (src/Frame.cc:901-1079) for a frame whose two extractors have just run: fills F.mvuRight / F.mvDepth.
   template <class FrameT>
   void ComputeStereoMatches(FrameT& F, ORBextractor& left, ORBextractor& right) {
@@ -141,6 +234,35 @@ class ORBmatcher {
       v.scale_factors = F.mvScaleFactors.data();
       v.nlevels = (int)F.mvScaleFactors.size();
       v.min_x = F.mnMinX; v.min_y = F.mnMinY; v.max_x = F.mnMaxX; v.max_y = F.mnMaxY;
+    }
+  };
+  // DBoW2::FeatureVector (an ordered map NodeId -> vector<unsigned>) flattened for the C-ABI
+  struct FeatVecHolder {
+    orbx_featvec v;
+    std::vector<uint32_t> ids, indices;
+    std::vector<int> start;
+    template <class FeatVecT>
+    explicit FeatVecHolder(const FeatVecT& fv) {
+      start.push_back(0);
+      for (typename FeatVecT::const_iterator it = fv.begin(); it != fv.end(); ++it) {
+        ids.push_back((uint32_t)it->first);
+        for (size_t k = 0; k < it->second.size(); k++) indices.push_back((uint32_t)it->second[k]);
+        start.push_back((int)indices.size());
+      }
+      v.nnodes = (int)ids.size(); v.node_ids = ids.data(); v.node_start = start.data(); v.indices = indices.data();
+    }
+  };
+  struct DescHolder {  // dense n x 32 view of a descriptor matrix
+    const uint8_t* p = nullptr;
+    std::vector<uint8_t> dense;
+    DescHolder(const cvx::Mat& m, int n) {
+      if (n == 0) { dense.resize(32); p = dense.data(); }
+      else if (m.step == 32) p = m.ptr(0);
+      else {
+        dense.resize((size_t)n * 32);
+        for (int i = 0; i < n; i++) memcpy(&dense[(size_t)i * 32], m.ptr(i), 32);
+        p = dense.data();
+      }
     }
   };
   orbx_matcher* m_ = nullptr;

@@ -6,6 +6,10 @@
     ORBmatcher.SearchByProjectionWindow(...)                  src/ORBmatcher.cc:2027 / :2291 (after the caller's projection)
     ORBmatcher.SearchForInitialization(F1, F2, prev, win)     src/ORBmatcher.cc:722
     FrameView.GetFeaturesInArea(x, y, r, minLevel, maxLevel)  src/Frame.cc:744
+    ORBmatcher.SearchByBoW(...)                               src/ORBmatcher.cc:273 / :839 (FeatureVectors as CSR triples)
+    ORBmatcher.SearchForTriangulation(...)                    src/ORBmatcher.cc:981    (pinhole; F12 / epipole from the caller)
+    ORBmatcher.SearchWindowBest(...)                          src/ORBmatcher.cc:1524 / :1728 / :1866 (Fuse x2, SearchBySim3 loops)
+    ORBmatcher.SearchBySim3Projected(...)                     src/ORBmatcher.cc:1788   (both passes + the agreement check)
     knn2 / stereo_match_batch                                 src/Frame.cc:1246 / :901
 
 A FrameView holds the members of Frame the searches read.  Everything runs in the CUDA kernels of csrc/match_kernels.cuh.
@@ -23,6 +27,10 @@ class _FrameViewC(C.Structure):
     _fields_ = [("n", C.c_int), ("keypoints", C.c_void_p), ("descriptors", C.c_void_p), ("u_right", C.c_void_p),
                 ("scale_factors", C.c_void_p), ("nlevels", C.c_int), ("min_x", C.c_float), ("min_y", C.c_float),
                 ("max_x", C.c_float), ("max_y", C.c_float)]
+
+
+class _FeatVecC(C.Structure):
+    _fields_ = [("nnodes", C.c_int), ("node_ids", C.c_void_p), ("node_start", C.c_void_p), ("indices", C.c_void_p)]
 
 
 class FrameView:
@@ -125,6 +133,64 @@ class ORBmatcher:
                                                       _p(angle), _p(srcDesc), _p(observed), C.c_float(th), int(mode), int(dist_th),
                                                       int(any_mp_blocks), int(self.mbCheckOrientation), _p(kp_mp), C.byref(nm)))
         return nm.value, kp_mp
+
+    def SearchWindowBest(self, F, valid, u, v, radius, level, desc, gate=False, inv_level_sigma2=None, ur=None):
+        """independent window argmin of Fuse / SearchBySim3: -> (best_idx[n], best_dist[n])"""
+        valid, u, v, radius, level, desc = _u8(valid), _f32(u), _f32(v), _f32(radius), _i32(level), _u8(desc)
+        ils, ur = _f32(inv_level_sigma2), _f32(ur)
+        n = len(valid)
+        bi = np.full(max(n, 1), -1, np.int32); bd = np.full(max(n, 1), 256, np.int32)
+        _check(lib().orbx_search_window_best(self._m, C.byref(F.c), n, _p(valid), _p(u), _p(v), _p(radius), _p(level), _p(ur),
+                                             _p(desc), int(gate), _p(ils), _p(bi), _p(bd)))
+        return bi[:n], bd[:n]
+
+    def SearchBySim3Projected(self, F1, F2, valid1, u1, v1, radius1, level1, desc1, valid2, u2, v2, radius2, level2, desc2):
+        """SearchBySim3 after the caller's Sim3 projections: pass 1 = map points of KF1 (one per keypoint of F1) projected
+        into KF2 (u1.. in F2's image), pass 2 the other way; returns match12[i1] = i2 where both passes agree (-1 otherwise),
+        src/ORBmatcher.cc:1896-1900, 1976-1980, 1983-1999 (bestDist <= TH_HIGH)."""
+        b1, d1 = self.SearchWindowBest(F2, valid1, u1, v1, radius1, level1, desc1)
+        b2, d2 = self.SearchWindowBest(F1, valid2, u2, v2, radius2, level2, desc2)
+        m1 = np.where(d1 <= TH_HIGH, b1, -1)
+        m2 = np.where(d2 <= TH_HIGH, b2, -1)
+        out = np.full(len(m1), -1, np.int32)
+        ok = m1 >= 0
+        i1 = np.nonzero(ok)[0]
+        agree = m2[m1[i1]] == i1
+        out[i1[agree]] = m1[i1[agree]]
+        return int(agree.sum()), out
+
+    @staticmethod
+    def _fv(fv):
+        ids = np.ascontiguousarray(fv[0], np.uint32); start = np.ascontiguousarray(fv[1], np.int32)
+        ind = np.ascontiguousarray(fv[2], np.uint32)
+        return _FeatVecC(len(ids), ids.ctypes.data, start.ctypes.data, ind.ctypes.data), (ids, start, ind)
+
+    def SearchByBoW(self, kps1, desc1, fv1, elig1, kps2, desc2, fv2, elig2=None, max_dist=TH_LOW):
+        """fv = (node_ids ascending, node_start[nnodes+1], indices).  KF-Frame: max_dist=TH_LOW, elig2=None; KF-KF: TH_LOW-1.
+        -> (nmatches, matches12)"""
+        kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+        desc1, desc2, elig1, elig2 = _u8(desc1), _u8(desc2), _u8(elig1), _u8(elig2)
+        c1, keep1 = self._fv(fv1); c2, keep2 = self._fv(fv2)
+        m12 = np.full(max(len(kps1), 1), -1, np.int32)
+        nm = C.c_int(0)
+        _check(lib().orbx_search_by_bow(self._m, len(kps1), _p(kps1), _p(desc1), C.byref(c1), _p(elig1), len(kps2), _p(kps2),
+                                        _p(desc2), C.byref(c2), _p(elig2), int(max_dist), C.c_float(self.mfNNratio),
+                                        int(self.mbCheckOrientation), _p(m12), C.byref(nm)))
+        return nm.value, m12[:len(kps1)]
+
+    def SearchForTriangulation(self, kps1, desc1, fv1, elig1, stereo1, kps2, desc2, fv2, elig2, stereo2, F12, ep, scale_factors2,
+                               level_sigma2_2, coarse=False):
+        kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+        desc1, desc2, elig1, elig2, stereo1, stereo2 = _u8(desc1), _u8(desc2), _u8(elig1), _u8(elig2), _u8(stereo1), _u8(stereo2)
+        c1, keep1 = self._fv(fv1); c2, keep2 = self._fv(fv2)
+        F12 = _f32(F12).reshape(9); sf = _f32(scale_factors2); ls = _f32(level_sigma2_2)
+        m12 = np.full(max(len(kps1), 1), -1, np.int32)
+        nm = C.c_int(0)
+        _check(lib().orbx_search_for_triangulation(self._m, len(kps1), _p(kps1), _p(desc1), C.byref(c1), _p(elig1), _p(stereo1),
+                                                   len(kps2), _p(kps2), _p(desc2), C.byref(c2), _p(elig2), _p(stereo2), _p(F12),
+                                                   C.c_float(ep[0]), C.c_float(ep[1]), _p(sf), _p(ls), len(sf), int(coarse),
+                                                   int(self.mbCheckOrientation), _p(m12), C.byref(nm)))
+        return nm.value, m12[:len(kps1)]
 
     def SearchForInitialization(self, F1, F2, vbPrevMatched, windowSize=10):
         pm = _f32(vbPrevMatched).reshape(-1, 2).copy()

@@ -174,7 +174,9 @@ int orbx_search_by_projection_mappoints_batch(orbx_matcher* m, orbx_extractor* e
                                               int* kp_mp, int capacity_per_frame, int* nmatches);
 
 /* Window best-match search shared by ORBmatcher::SearchByProjection(Frame& Cur, const Frame& Last, th, bMono)
- * (src/ORBmatcher.cc:2027-2289; mode 0 = levels [l-1,l+1], 1 = forward [l,inf), 2 = backward [0,l]; dist_th = TH_HIGH) and
+ * (src/ORBmatcher.cc:2027-2289; mode 0 = levels [l-1,l+1], 1 = forward [l,inf), 2 = backward [0,l]; dist_th = TH_HIGH),
+ * both SearchByProjection(KeyFrame*, Scw, vpPoints, [vpPointsKFs,] vpMatched, ...) overloads (:489-602, :604-720; mode 3 =
+ * levels [l-1,l], any_mp_blocks = 1, dist_th = floor(TH_LOW*ratioHamming), check_orientation = 0, kp_mp = vpMatched) and
  * SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:2291-2413; mode 0, any_mp_blocks = 1,
  * dist_th = ORBdist).  The caller projects the points (pose algebra and camera model stay on the host, as in the
  * reference's loop prologue): valid[i] = point exists, is not an outlier / not already found, invzc >= 0 and projects
@@ -185,6 +187,49 @@ int orbx_search_by_projection_window(orbx_matcher* m, const orbx_frame_view* F, 
                                      const float* v, const int* level, const float* ur, const float* angle,
                                      const uint8_t* src_desc, const uint8_t* observed, float th, int mode, int dist_th,
                                      int any_mp_blocks, int check_orientation, int* kp_mp, int* nmatches);
+
+/* ---- the remaining ORBmatcher entry points ------------------------------------------------ */
+
+/* The per-point search loop shared by ORBmatcher::Fuse(KeyFrame*, const vector<MapPoint*>&, th, bRight)
+ * (src/ORBmatcher.cc:1524-1590), Fuse(KeyFrame*, Scw, ...) (:1728-1756) and both passes of SearchBySim3 (:1866-1895,
+ * :1946-1975): KeyFrame::GetFeaturesInArea(u, v, radius) (src/KeyFrame.cc:796-838), octave in [level-1, level], optional
+ * chi-square gate (gate != 0, Fuse only: e2 * inv_level_sigma2[octave] > 7.8 with a right coordinate, > 5.99 without; needs
+ * F->u_right for stereo keyframes and ur = uv.x - bf*invz), strict argmin Hamming in the reference's traversal order.
+ * Queries are independent.  best_idx[i] = -1 and best_dist[i] = 256 when nothing qualifies; the caller applies
+ * bestDist <= TH_LOW / TH_HIGH and the MapPoint bookkeeping (Replace / AddObservation / the Sim3 agreement check). */
+int orbx_search_window_best(orbx_matcher* m, const orbx_frame_view* F, int n, const uint8_t* valid, const float* u, const float* v,
+                            const float* radius, const int* level, const float* ur, const uint8_t* desc, int gate,
+                            const float* inv_level_sigma2, int* best_idx, int* best_dist);
+
+/* DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned int>>, Thirdparty/DBoW2/DBoW2/FeatureVector.h) flattened:
+ * node ids strictly ascending, node_start[nnodes + 1] offsets into indices. */
+typedef struct orbx_featvec {
+  int nnodes;
+  const uint32_t* node_ids;
+  const int* node_start;
+  const uint32_t* indices;
+} orbx_featvec;
+
+/* Both ORBmatcher::SearchByBoW overloads: (KeyFrame*, Frame&, vpMapPointMatches) src/ORBmatcher.cc:273-475 (Nleft == -1
+ * branch; max_dist = TH_LOW) and (KeyFrame*, KeyFrame*, vpMatches12) :839-979 (max_dist = TH_LOW - 1, the reference tests
+ * "< TH_LOW").  Side 1 is walked node by node in the order of its lists, side 2 is claimed.  elig1[i] = feature i of side 1
+ * has a good map point; elig2 (may be NULL) = static eligibility of side-2 features (KF-KF: has a good map point).
+ * matches12[i] = claimed side-2 feature or -1, after the rotation filter; *nmatches = the reference's return value. */
+int orbx_search_by_bow(orbx_matcher* m, int n1, const orbx_keypoint* kps1, const uint8_t* desc1, const orbx_featvec* fv1,
+                       const uint8_t* elig1, int n2, const orbx_keypoint* kps2, const uint8_t* desc2, const orbx_featvec* fv2,
+                       const uint8_t* elig2, int max_dist, float nnratio, int check_orientation, int* matches12, int* nmatches);
+
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo, bCoarse), src/ORBmatcher.cc:981-1222, for
+ * pinhole keyframes without a second camera.  elig1[i] = !pKF1->GetMapPoint(i) && (!bOnlyStereo || stereo1[i]), elig2
+ * likewise; stereo = mvuRight >= 0 (NULL = monocular).  F12 (row-major 3x3) is the matrix Pinhole::epipolarConstrain forms
+ * (src/CameraModels/Pinhole.cpp:145-148: K1^-T [t12]x R12 K2^-1); ep = pKF2->mpCamera->project(R2w*Cw + t2w);
+ * scale_factors2 / level_sigma2_2 = pKF2->mvScaleFactors / mvLevelSigma2.  matches12[i] = index in pKF2 or -1. */
+int orbx_search_for_triangulation(orbx_matcher* m, int n1, const orbx_keypoint* kps1, const uint8_t* desc1, const orbx_featvec* fv1,
+                                  const uint8_t* elig1, const uint8_t* stereo1, int n2, const orbx_keypoint* kps2,
+                                  const uint8_t* desc2, const orbx_featvec* fv2, const uint8_t* elig2, const uint8_t* stereo2,
+                                  const float* F12, float epx, float epy, const float* scale_factors2,
+                                  const float* level_sigma2_2, int nlevels, int coarse, int check_orientation, int* matches12,
+                                  int* nmatches);
 
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize), src/ORBmatcher.cc:722-837.
  * prev_matched: F1->n x 2 floats (in/out), matches12: F1->n ints (out). */

@@ -247,6 +247,54 @@ def search_for_initialization(kps1, desc1, kps2, desc2, w, h, prev_matched, wind
     return nm, m12, pm
 
 
+def _fv(fv):
+    """fv = (node_ids uint32 ascending, node_start int32 [nnodes+1], indices uint32)"""
+    ids = np.ascontiguousarray(fv[0], np.uint32); start = np.ascontiguousarray(fv[1], np.int32)
+    ind = np.ascontiguousarray(fv[2], np.uint32)
+    return ids, start, ind
+
+
+def search_by_bow(kps1, desc1, fv1, elig1, kps2, desc2, fv2, elig2, max_dist, nnratio, check_orientation=True):
+    kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+    desc1, desc2 = _u8(desc1), _u8(desc2)
+    i1, s1, x1 = _fv(fv1); i2, s2, x2 = _fv(fv2)
+    elig1 = _u8(elig1); elig2 = None if elig2 is None else _u8(elig2)
+    m12 = np.empty(max(kps1.shape[0], 1), np.int32)
+    nm = lib().oro_search_by_bow(kps1.shape[0], _p(kps1), _p(desc1), i1.shape[0], _p(i1), _p(s1), _p(x1), _p(elig1), kps2.shape[0],
+                                 _p(kps2), _p(desc2), i2.shape[0], _p(i2), _p(s2), _p(x2), _p(elig2), int(max_dist),
+                                 C.c_float(nnratio), int(check_orientation), _p(m12))
+    return nm, m12[:kps1.shape[0]]
+
+
+def search_for_triangulation(kps1, desc1, fv1, elig1, stereo1, kps2, desc2, fv2, elig2, stereo2, F12, ep, scale_factors2,
+                             level_sigma2_2, coarse=False, check_orientation=True):
+    kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+    desc1, desc2 = _u8(desc1), _u8(desc2)
+    i1, s1, x1 = _fv(fv1); i2, s2, x2 = _fv(fv2)
+    u8 = lambda a: None if a is None else np.ascontiguousarray(a, np.uint8)
+    elig1, elig2, stereo1, stereo2 = u8(elig1), u8(elig2), u8(stereo1), u8(stereo2)
+    F12 = np.ascontiguousarray(F12, np.float32).reshape(9)
+    sf = np.ascontiguousarray(scale_factors2, np.float32); ls = np.ascontiguousarray(level_sigma2_2, np.float32)
+    m12 = np.empty(max(kps1.shape[0], 1), np.int32)
+    nm = lib().oro_search_for_triangulation(kps1.shape[0], _p(kps1), _p(desc1), i1.shape[0], _p(i1), _p(s1), _p(x1), _p(elig1),
+                                            _p(stereo1), kps2.shape[0], _p(kps2), _p(desc2), i2.shape[0], _p(i2), _p(s2), _p(x2),
+                                            _p(elig2), _p(stereo2), _p(F12), C.c_float(ep[0]), C.c_float(ep[1]), _p(sf), _p(ls),
+                                            int(coarse), int(check_orientation), _p(m12))
+    return nm, m12[:kps1.shape[0]]
+
+
+def search_window_best(kps, desc, w, h, valid, u, v, radius, level, qdesc, gate=0, inv_level_sigma2=None, uRight=None, ur=None):
+    kps = np.ascontiguousarray(kps, KP_DTYPE); desc = _u8(desc)
+    f32 = lambda a: None if a is None else np.ascontiguousarray(a, np.float32)
+    valid = _u8(valid); u = f32(u); v = f32(v); radius = f32(radius); level = np.ascontiguousarray(level, np.int32)
+    qdesc = _u8(qdesc); ils = f32(inv_level_sigma2); uRight = f32(uRight); ur = f32(ur)
+    n = valid.shape[0]
+    bi = np.empty(max(n, 1), np.int32); bd = np.empty(max(n, 1), np.int32)
+    lib().oro_search_window_best(kps.shape[0], _p(kps), _p(desc), _p(uRight), _p(_bounds(w, h)), n, _p(valid), _p(u), _p(v),
+                                 _p(radius), _p(level), _p(ur), _p(qdesc), int(gate), _p(ils), _p(bi), _p(bd))
+    return bi[:n], bd[:n]
+
+
 def stereo_matches(exL, exR, kpL, descL, kpR, descR, mb, mbf):
     """exL / exR: oracle Extractor objects that have just extracted the left / right image."""
     kpL = np.ascontiguousarray(kpL, KP_DTYPE); kpR = np.ascontiguousarray(kpR, KP_DTYPE)

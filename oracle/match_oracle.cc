@@ -111,7 +111,7 @@ int search_by_projection_mappoints(FrameView& F, int nMP, const uint8_t* in_view
   return nmatches;
 }
 
-// ORBmatcher.cc:2027-2289 (Frame/Frame) and :2291-2413 (Frame/KeyFrame), search part.
+// ORBmatcher.cc:2027-2289 (Frame/Frame), :2291-2413 (Frame/KeyFrame) and :489-720 (KeyFrame/Scw, mode 3), search part.
 int search_by_projection_window(FrameView& F, int n, const uint8_t* valid, const float* u, const float* v, const int* lvl,
                                 const float* ur, const float* angle, const uint8_t* srcDesc, const uint8_t* observed, float th,
                                 int mode, int dist_th, bool any_mp_blocks, bool check_orientation, int* kp_mp) {
@@ -125,6 +125,10 @@ int search_by_projection_window(FrameView& F, int n, const uint8_t* valid, const
     std::vector<int> vIndices2;
     if (mode == 1) vIndices2 = F.getFeaturesInArea(u[i], v[i], radius, nLastOctave, -1);
     else if (mode == 2) vIndices2 = F.getFeaturesInArea(u[i], v[i], radius, 0, nLastOctave);
+    else if (mode == 3) {  // SearchByProjection(KeyFrame*, Scw, ...), ORBmatcher.cc:557-576 / :672-692: octave in [l-1, l]
+      for (int i2 : F.getFeaturesInArea(u[i], v[i], radius, -1, -1))
+        if (!(F.kps[i2].octave < nLastOctave - 1 || F.kps[i2].octave > nLastOctave)) vIndices2.push_back(i2);
+    }
     else vIndices2 = F.getFeaturesInArea(u[i], v[i], radius, nLastOctave - 1, nLastOctave + 1);
     if (vIndices2.empty()) continue;
     const uint8_t* dMP = srcDesc + 32 * (size_t)i;
@@ -321,5 +325,165 @@ void knn2_ratio(const uint8_t* q, int nq, const uint8_t* t, int nt, int* idx, in
   knn2_hamming(q, nq, t, nt, idx, dist);
   for (int i = 0; i < nq; i++) good[i] = (idx[2 * i + 1] >= 0) && ((float)dist[2 * i] < (float)dist[2 * i + 1] * 0.7);
 }
+
+// ---- SURVEY.md §8(f) rank 1 ----------------------------------------------------------------------------------------------------
+
+// Walks two FeatureVectors the way the reference's while-loop does (ORBmatcher.cc:289-299, 440-451): matching node ids in
+// ascending order; lower_bound on a sorted map == advance until >=.
+template <class Fn>
+static void for_common_nodes(const FeatVec& a, const FeatVec& b, Fn fn) {
+  int ia = 0, ib = 0;
+  while (ia < a.nnodes && ib < b.nnodes) {
+    if (a.nodeIds[ia] == b.nodeIds[ib]) { fn(ia, ib); ia++; ib++; }
+    else if (a.nodeIds[ia] < b.nodeIds[ib]) { while (ia < a.nnodes && a.nodeIds[ia] < b.nodeIds[ib]) ia++; }
+    else { while (ib < b.nnodes && b.nodeIds[ib] < a.nodeIds[ia]) ib++; }
+  }
+}
+
+static inline int rot_bin_of(float a1, float a2) {  // ORBmatcher.cc:395-401
+  const float factor = 1.0f / HISTO_LENGTH;
+  float rot = a1 - a2;
+  if (rot < 0.0) rot += 360.0f;
+  int bin = (int)std::round(rot * factor);
+  if (bin == HISTO_LENGTH) bin = 0;
+  return bin;
+}
+
+// ORBmatcher.cc:273-475 (KF-Frame, Nleft == -1) and :839-979 (KF-KF).
+int search_by_bow(int n1, const KeyPoint* kps1, const uint8_t* desc1, const FeatVec& fv1, const uint8_t* elig1, int n2,
+                  const KeyPoint* kps2, const uint8_t* desc2, const FeatVec& fv2, const uint8_t* elig2, int maxDist, float nnratio,
+                  bool check_orientation, int* matches12) {
+  for (int i = 0; i < n1; i++) matches12[i] = -1;
+  std::vector<uint8_t> claimed2(n2, 0);
+  std::vector<int> rotHist[HISTO_LENGTH];
+  int nmatches = 0;
+  for_common_nodes(fv1, fv2, [&](int a, int b) {
+    for (int p1 = fv1.nodeStart[a]; p1 < fv1.nodeStart[a + 1]; p1++) {
+      const int idx1 = (int)fv1.indices[p1];
+      if (idx1 >= n1 || !elig1[idx1]) continue;
+      const uint8_t* d1 = desc1 + 32 * (size_t)idx1;
+      int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+      for (int p2 = fv2.nodeStart[b]; p2 < fv2.nodeStart[b + 1]; p2++) {
+        const int idx2 = (int)fv2.indices[p2];
+        if (idx2 >= n2) continue;
+        if (claimed2[idx2] || (elig2 && !elig2[idx2])) continue;
+        const int dist = hamming256(d1, desc2 + 32 * (size_t)idx2);
+        if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = idx2; }
+        else if (dist < bestDist2) bestDist2 = dist;
+      }
+      if (bestDist1 <= maxDist) {
+        if ((float)bestDist1 < nnratio * (float)bestDist2) {
+          matches12[idx1] = bestIdx2;
+          claimed2[bestIdx2] = 1;
+          if (check_orientation) rotHist[rot_bin_of(kps1[idx1].angle, kps2[bestIdx2].angle)].push_back(idx1);
+          nmatches++;
+        }
+      }
+    }
+  });
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1, hs[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; i++) hs[i] = (int)rotHist[i].size();
+    compute_three_maxima(hs, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++)
+      if (i != ind1 && i != ind2 && i != ind3)
+        for (int j : rotHist[i]) { matches12[j] = -1; nmatches--; }
+  }
+  return nmatches;
+}
+
+// Pinhole.cpp:150-164.
+bool epipolar_constrain_pinhole(const KeyPoint& kp1, const KeyPoint& kp2, const float* F, float unc) {
+  const float a = kp1.x * F[0] + kp1.y * F[3] + F[6];
+  const float b = kp1.x * F[1] + kp1.y * F[4] + F[7];
+  const float c = kp1.x * F[2] + kp1.y * F[5] + F[8];
+  const float num = a * kp2.x + b * kp2.y + c;
+  const float den = a * a + b * b;
+  if (den == 0) return false;
+  const float dsqr = num * num / den;
+  return dsqr < 3.84 * unc;
+}
+
+// ORBmatcher.cc:981-1222.
+int search_for_triangulation(int n1, const KeyPoint* kps1, const uint8_t* desc1, const FeatVec& fv1, const uint8_t* elig1,
+                             const uint8_t* stereo1, int n2, const KeyPoint* kps2, const uint8_t* desc2, const FeatVec& fv2,
+                             const uint8_t* elig2, const uint8_t* stereo2, const float* F12, float epx, float epy,
+                             const float* scaleFactors2, const float* levelSigma2_2, bool coarse, bool check_orientation,
+                             int* matches12) {
+  for (int i = 0; i < n1; i++) matches12[i] = -1;
+  std::vector<int> rotHist[HISTO_LENGTH];
+  int nmatches = 0;
+  for_common_nodes(fv1, fv2, [&](int a, int b) {
+    for (int p1 = fv1.nodeStart[a]; p1 < fv1.nodeStart[a + 1]; p1++) {
+      const int idx1 = (int)fv1.indices[p1];
+      if (!elig1[idx1]) continue;
+      const bool bStereo1 = stereo1 && stereo1[idx1];
+      const KeyPoint& kp1 = kps1[idx1];
+      const uint8_t* d1 = desc1 + 32 * (size_t)idx1;
+      int bestDist = TH_LOW, bestIdx2 = -1;
+      for (int p2 = fv2.nodeStart[b]; p2 < fv2.nodeStart[b + 1]; p2++) {
+        const int idx2 = (int)fv2.indices[p2];
+        if (!elig2[idx2]) continue;   // vbMatched2 is never set by the reference (:1026), so only the static gates remain
+        const bool bStereo2 = stereo2 && stereo2[idx2];
+        const int dist = hamming256(d1, desc2 + 32 * (size_t)idx2);
+        if (dist > TH_LOW || dist > bestDist) continue;
+        const KeyPoint& kp2 = kps2[idx2];
+        if (!bStereo1 && !bStereo2) {
+          const float distex = epx - kp2.x, distey = epy - kp2.y;
+          if (distex * distex + distey * distey < 100 * scaleFactors2[kp2.octave]) continue;
+        }
+        if (epipolar_constrain_pinhole(kp1, kp2, F12, levelSigma2_2[kp2.octave]) || coarse) { bestIdx2 = idx2; bestDist = dist; }
+      }
+      if (bestIdx2 >= 0) {
+        matches12[idx1] = bestIdx2;
+        nmatches++;
+        if (check_orientation) rotHist[rot_bin_of(kp1.angle, kps2[bestIdx2].angle)].push_back(idx1);
+      }
+    }
+  });
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1, hs[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; i++) hs[i] = (int)rotHist[i].size();
+    compute_three_maxima(hs, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++)
+      if (i != ind1 && i != ind2 && i != ind3)
+        for (int j : rotHist[i]) { matches12[j] = -1; nmatches--; }
+  }
+  return nmatches;
+}
+
+// ORBmatcher.cc:1524-1590 (Fuse), :1728-1756 (Fuse/Scw), :1866-1895 and :1946-1975 (SearchBySim3).
+void search_window_best(const FrameView& F, int n, const uint8_t* valid, const float* u, const float* v, const float* radius,
+                        const int* level, const float* ur, const uint8_t* desc, int gate, const float* invLevelSigma2,
+                        int* bestIdxOut, int* bestDistOut) {
+  for (int i = 0; i < n; i++) {
+    bestIdxOut[i] = -1; bestDistOut[i] = 256;
+    if (!valid[i]) continue;
+    const int nPredictedLevel = level[i];
+    const std::vector<int> vIndices = F.getFeaturesInArea(u[i], v[i], radius[i], -1, -1);
+    const uint8_t* dMP = desc + 32 * (size_t)i;
+    int bestDist = 256, bestIdx = -1;
+    for (int idx : vIndices) {
+      const KeyPoint& kp = F.kps[idx];
+      const int kpLevel = kp.octave;
+      if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+      if (gate) {
+        if (F.uRight && F.uRight[idx] >= 0) {
+          const float ex = u[i] - kp.x, ey = v[i] - kp.y, er = ur[i] - F.uRight[idx];
+          const float e2 = ex * ex + ey * ey + er * er;
+          if (e2 * invLevelSigma2[kpLevel] > 7.8) continue;
+        } else {
+          const float ex = u[i] - kp.x, ey = v[i] - kp.y;
+          const float e2 = ex * ex + ey * ey;
+          if (e2 * invLevelSigma2[kpLevel] > 5.99) continue;
+        }
+      }
+      const int dist = hamming256(dMP, F.desc + 32 * (size_t)idx);
+      if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+    }
+    bestIdxOut[i] = bestIdx; bestDistOut[i] = bestDist;
+  }
+}
+
 
 }  // namespace oro

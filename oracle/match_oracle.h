@@ -8,6 +8,14 @@
 //   ORBmatcher::SearchByProjection(Frame&, KeyFrame*, set, ..)    src/ORBmatcher.cc:2291-2413 (after projection)
 //   ORBmatcher::SearchForInitialization                           src/ORBmatcher.cc:722-837
 //   ORBmatcher::ComputeThreeMaxima                                src/ORBmatcher.cc:2416-2458
+//   ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ..)                src/ORBmatcher.cc:273-475   (Nleft == -1 branch)
+//   ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, ..)             src/ORBmatcher.cc:839-979
+//   ORBmatcher::SearchForTriangulation(.., bOnlyStereo, bCoarse)  src/ORBmatcher.cc:981-1222  (pinhole, no second camera)
+//   Pinhole::epipolarConstrain                                    src/CameraModels/Pinhole.cpp:143-165 (F12 given)
+//   ORBmatcher::SearchByProjection(KeyFrame*, Scw, ..) x2         src/ORBmatcher.cc:489-602, 604-720 (after projection)
+//   ORBmatcher::Fuse(KeyFrame*, vector<MapPoint*>, th, bRight)    src/ORBmatcher.cc:1425-1662 (search loop, after projection)
+//   ORBmatcher::Fuse(KeyFrame*, Scw, ..)                          src/ORBmatcher.cc:1664-1786 (search loop, after projection)
+//   ORBmatcher::SearchBySim3                                      src/ORBmatcher.cc:1788-2018 (search loops + agreement)
 // Pose algebra / camera projection / MapPoint bookkeeping stay with the caller (out of scope); the
 // functions here take the already-projected (u,v), predicted level etc. exactly as the reference computes them
 // before entering the search loop.  Parity status: unpinned by the reference (it has no tests), see orb_oracle.h.
@@ -70,5 +78,44 @@ void compute_stereo_matches(int N, const KeyPoint* kpL, const uint8_t* descL, in
 
 // kNN(2) + Lowe ratio of ComputeStereoFishEyeMatches: good[i] = (#neighbours >= 2 && d0 < d1 * 0.7)
 void knn2_ratio(const uint8_t* q, int nq, const uint8_t* t, int nt, int* idx, int* dist, uint8_t* good);
+
+// ---- the remaining ORBmatcher entry points ------------------------------------------------------
+// DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>) flattened: node ids ascending, CSR offsets, feature indices.
+struct FeatVec {
+  int nnodes = 0;
+  const uint32_t* nodeIds = nullptr;
+  const int* nodeStart = nullptr;   // [nnodes + 1]
+  const uint32_t* indices = nullptr;
+};
+
+// The bucketed best/second search shared by both SearchByBoW overloads.  Side 1 is walked (node order, then position in the
+// node's list), side 2 is claimed.  elig1[i]: the feature takes part (has a good map point; idx < mvKeysUn.size());
+// elig2[j]: static eligibility of a side-2 feature (KF-KF: has a good map point; KF-Frame: always).  A claimed side-2
+// feature is skipped by later side-1 features.  Accept when best <= maxDist and (float)best < nnratio * (float)second.
+// maxDist = TH_LOW for KF-Frame (":<=TH_LOW"), TH_LOW - 1 for KF-KF ("<TH_LOW").  matches12[i] = j or -1; returns nmatches
+// after the rotation filter (angle1 - angle2 histogram).
+int search_by_bow(int n1, const KeyPoint* kps1, const uint8_t* desc1, const FeatVec& fv1, const uint8_t* elig1, int n2,
+                  const KeyPoint* kps2, const uint8_t* desc2, const FeatVec& fv2, const uint8_t* elig2, int maxDist, float nnratio,
+                  bool check_orientation, int* matches12);
+
+// Pinhole::epipolarConstrain with the fundamental matrix already formed (F12 row-major 3x3), unc = mvLevelSigma2[kp2.octave].
+bool epipolar_constrain_pinhole(const KeyPoint& kp1, const KeyPoint& kp2, const float* F12, float unc);
+
+// SearchForTriangulation (pinhole, mpCamera2 == null).  elig1[i] = !GetMapPoint(i) && (!bOnlyStereo || stereo1[i]);
+// elig2[j] likewise for pKF2.  stereo1/2 = mvuRight[.] >= 0.  ep = projection of KF1's centre in KF2; levelSigma2 /
+// scaleFactors are pKF2's tables.  matches12[i] = j or -1.
+int search_for_triangulation(int n1, const KeyPoint* kps1, const uint8_t* desc1, const FeatVec& fv1, const uint8_t* elig1,
+                             const uint8_t* stereo1, int n2, const KeyPoint* kps2, const uint8_t* desc2, const FeatVec& fv2,
+                             const uint8_t* elig2, const uint8_t* stereo2, const float* F12, float epx, float epy,
+                             const float* scaleFactors2, const float* levelSigma2_2, bool coarse, bool check_orientation,
+                             int* matches12);
+
+// The per-point search loop shared by Fuse (both overloads), SearchBySim3 and (without blocking) SearchByProjection(KF,Scw):
+// KeyFrame::GetFeaturesInArea(u, v, radius) -> octave in [level-1, level] -> optional Fuse chi-square gate
+// (gate != 0: uses F.uRight / ur / invLevelSigma2; 7.8 with a right coordinate, 5.99 without) -> strict argmin Hamming.
+// bestIdx[i] = -1 / bestDist[i] = 256 when nothing qualifies.  The queries are independent of each other.
+void search_window_best(const FrameView& F, int n, const uint8_t* valid, const float* u, const float* v, const float* radius,
+                        const int* level, const float* ur, const uint8_t* desc, int gate, const float* invLevelSigma2,
+                        int* bestIdx, int* bestDist);
 
 }  // namespace oro

@@ -160,6 +160,34 @@ void oro_stereo_matches(void* exL, void* exR, int N, const KeyPoint* kpL, const 
 void oro_knn2_ratio(const uint8_t* q, int nq, const uint8_t* t, int nt, int* idx, int* dist, uint8_t* good) {
   knn2_ratio(q, nq, t, nt, idx, dist, good);
 }
+// ---- SURVEY.md §8(f) rank 1 ----
+static FeatVec fv_of(int nnodes, const uint32_t* ids, const int* start, const uint32_t* indices) {
+  FeatVec f; f.nnodes = nnodes; f.nodeIds = ids; f.nodeStart = start; f.indices = indices; return f;
+}
+int oro_search_by_bow(int n1, const KeyPoint* kps1, const uint8_t* desc1, int nn1, const uint32_t* ids1, const int* start1,
+                      const uint32_t* ind1, const uint8_t* elig1, int n2, const KeyPoint* kps2, const uint8_t* desc2, int nn2,
+                      const uint32_t* ids2, const int* start2, const uint32_t* ind2, const uint8_t* elig2, int maxDist, float nnratio,
+                      int check_orientation, int* matches12) {
+  return search_by_bow(n1, kps1, desc1, fv_of(nn1, ids1, start1, ind1), elig1, n2, kps2, desc2, fv_of(nn2, ids2, start2, ind2), elig2,
+                       maxDist, nnratio, check_orientation != 0, matches12);
+}
+int oro_search_for_triangulation(int n1, const KeyPoint* kps1, const uint8_t* desc1, int nn1, const uint32_t* ids1, const int* start1,
+                                 const uint32_t* ind1, const uint8_t* elig1, const uint8_t* stereo1, int n2, const KeyPoint* kps2,
+                                 const uint8_t* desc2, int nn2, const uint32_t* ids2, const int* start2, const uint32_t* ind2,
+                                 const uint8_t* elig2, const uint8_t* stereo2, const float* F12, float epx, float epy,
+                                 const float* scaleFactors2, const float* levelSigma2_2, int coarse, int check_orientation,
+                                 int* matches12) {
+  return search_for_triangulation(n1, kps1, desc1, fv_of(nn1, ids1, start1, ind1), elig1, stereo1, n2, kps2, desc2,
+                                  fv_of(nn2, ids2, start2, ind2), elig2, stereo2, F12, epx, epy, scaleFactors2, levelSigma2_2,
+                                  coarse != 0, check_orientation != 0, matches12);
+}
+void oro_search_window_best(int N, const KeyPoint* kps, const uint8_t* desc, const float* uRight, const float* bounds4, int n,
+                            const uint8_t* valid, const float* u, const float* v, const float* radius, const int* level,
+                            const float* ur, const uint8_t* qdesc, int gate, const float* invLevelSigma2, int* bestIdx, int* bestDist) {
+  FrameView F;
+  fill_view(F, N, kps, desc, uRight, nullptr, bounds4);
+  search_window_best(F, n, valid, u, v, radius, level, ur, qdesc, gate, invLevelSigma2, bestIdx, bestDist);
+}
 void oro_three_maxima(const int* hist, int L, int* ind3) {
   int a = -1, b = -1, c = -1;
   compute_three_maxima(hist, L, a, b, c);

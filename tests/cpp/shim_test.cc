@@ -5,6 +5,7 @@
 // then SearchByProjection of the left frame against map points made of the right frame's keypoints: nmatches, kp->mp index.
 #include <cstdio>
 #include <cstdlib>
+#include <map>
 #include <vector>
 
 #include "../../3_orb_slam3_selfnote_b200/host/ORBmatcher.h"
@@ -30,6 +31,23 @@ struct MockFrame {
   float mnMinX = 0, mnMinY = 0, mnMaxX = 0, mnMaxY = 0, mb = 0, mbf = 0;
   std::vector<MockMapPoint*> mvpMapPoints;
 };
+
+// the members of KeyFrame the bag-of-words searches read (include/KeyFrame.h)
+struct MockKeyFrame {
+  int N = 0, NLeft = -1;
+  std::vector<cvx::KeyPoint> mvKeysUn;
+  cvx::Mat mDescriptors;
+  std::vector<float> mvuRight, mvScaleFactors, mvLevelSigma2, mvInvLevelSigma2;
+  float mnMinX = 0, mnMinY = 0, mnMaxX = 0, mnMaxY = 0;
+  std::map<unsigned, std::vector<unsigned> > mFeatVec;   // DBoW2::FeatureVector
+  std::vector<MockMapPoint*> mps;
+  std::vector<MockMapPoint*> GetMapPointMatches() const { return mps; }
+  MockMapPoint* GetMapPoint(size_t i) const { return mps[i]; }
+};
+// test vocabulary: node = low 5 bits of the first descriptor byte (the Python side builds the same lists)
+static void fill_featvec(std::map<unsigned, std::vector<unsigned> >& fv, const cvx::Mat& desc, int n) {
+  for (int i = 0; i < n; i++) fv[(unsigned)(desc.ptr(i)[0] & 31)].push_back((unsigned)i);
+}
 
 static std::vector<uint8_t> read_raw(const char* fn, size_t n) {
   std::vector<uint8_t> v(n);
@@ -92,6 +110,31 @@ int main(int argc, char** argv) {
     for (int k = 0; k < F.N; k++) { int id = F.mvpMapPoints[k] ? F.mvpMapPoints[k]->id : -1; fwrite(&id, 4, 1, out); }
     int dd = ORBmatcher::DescriptorDistance(F.mDescriptors.row(0), descR.row(0));
     fwrite(&dd, 4, 1, out);
+
+    // --- SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) and (KeyFrame*, KeyFrame*, vpMatches12): keyframes = the two images
+    MockKeyFrame kfL, kfR;
+    kfL.N = F.N; kfL.mvKeysUn = F.mvKeys; kfL.mDescriptors = F.mDescriptors;
+    kfR.N = (int)FR.mvKeys.size(); kfR.mvKeysUn = FR.mvKeys; kfR.mDescriptors = descR;
+    fill_featvec(kfL.mFeatVec, kfL.mDescriptors, kfL.N); fill_featvec(kfR.mFeatVec, kfR.mDescriptors, kfR.N);
+    std::vector<MockMapPoint> mpsL(kfL.N);
+    kfL.mps.assign(kfL.N, nullptr);
+    for (int i = 0; i < kfL.N; i++) { mpsL[i].id = i; if (i % 5 != 0) kfL.mps[i] = &mpsL[i]; }
+    kfR.mps.assign(kfR.N, nullptr);
+    for (int i = 0; i < kfR.N; i++) if (i % 7 != 0) kfR.mps[i] = &mps[i];
+    MockFrame FB;
+    FB.N = kfR.N; FB.mvKeys = FR.mvKeys; FB.mvKeysUn = FR.mvKeys; FB.mDescriptors = descR;
+    std::map<unsigned, std::vector<unsigned> >& fvB = kfR.mFeatVec;
+    struct FrameWithBow : MockFrame { std::map<unsigned, std::vector<unsigned> > mFeatVec; } FBB;
+    static_cast<MockFrame&>(FBB) = FB; FBB.mFeatVec = fvB;
+    std::vector<MockMapPoint*> vpMatches;
+    ORBmatcher bow(0.75f, true);
+    int nb = bow.SearchByBoW(&kfL, FBB, vpMatches);
+    fwrite(&nb, 4, 1, out);
+    for (int k = 0; k < FBB.N; k++) { int id = vpMatches[k] ? vpMatches[k]->id : -1; fwrite(&id, 4, 1, out); }
+    std::vector<MockMapPoint*> vpMatches12;
+    int nb2 = bow.SearchByBoW(&kfL, &kfR, vpMatches12);
+    fwrite(&nb2, 4, 1, out);
+    for (int k = 0; k < kfL.N; k++) { int id = vpMatches12[k] ? vpMatches12[k]->id : -1; fwrite(&id, 4, 1, out); }
   } catch (const std::exception& e) {
     fprintf(stderr, "exception: %s\n", e.what());
     return 4;

@@ -1,6 +1,6 @@
 """Builds tests/cpp/shim_test.cc (the reference-signature C++ shims over the C-ABI) with g++, runs it on the GPU and checks
 its outputs against the CPU oracle: ORBextractor::operator(), Frame::ComputeStereoMatches and
-ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th) through the same class / member names the reference uses."""
+ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th), both ORBmatcher::SearchByBoW overloads through the same class / member names the reference uses."""
 import os
 import shutil
 import subprocess
@@ -56,3 +56,21 @@ def test_cpp_shim_end_to_end(orbx, oracle, synth, tmp_path):
                                                        3.0, 0.8, uRight=uo, projXR=kr["x"])
     assert nm == nm_o and np.array_equal(kp_mp, kp_o) and nm_o > 50
     assert int(take(np.int32, 1)[0]) == oracle.hamming(dl[0], dr[0])
+    # SearchByBoW through the reference signatures: keyframe = left image (map point on every keypoint with i % 5 != 0)
+    def fv(d):
+        node = d[:, 0] & 31
+        ids = np.unique(node)
+        start = [0]; ind = []
+        for w in ids:
+            ind.extend(np.nonzero(node == w)[0].tolist()); start.append(len(ind))
+        return ids.astype(np.uint32), np.array(start, np.int32), np.array(ind, np.uint32)
+    e1 = (np.arange(len(kl)) % 5 != 0).astype(np.uint8)
+    nb = int(take(np.int32, 1)[0]); got = take(np.int32, len(kr))
+    nb_o, m12 = oracle.search_by_bow(kl, dl, fv(dl), e1, kr, dr, fv(dr), None, 50, 0.75, True)
+    ref = np.full(len(kr), -1, np.int32)
+    ref[m12[m12 >= 0]] = np.nonzero(m12 >= 0)[0]
+    assert nb == nb_o and np.array_equal(got, ref) and nb_o > 10
+    e2 = (np.arange(len(kr)) % 7 != 0).astype(np.uint8)
+    nb2 = int(take(np.int32, 1)[0]); got2 = take(np.int32, len(kl))
+    nb2_o, m12 = oracle.search_by_bow(kl, dl, fv(dl), e1, kr, dr, fv(dr), e2, 49, 0.75, True)
+    assert nb2 == nb2_o and np.array_equal(got2, m12) and nb2_o > 10

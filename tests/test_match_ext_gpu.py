@@ -1,0 +1,183 @@
+"""GPU parity tests of the SURVEY.md §8(f) rank-1 entry points (SearchByBoW x2, SearchForTriangulation, the Fuse /
+SearchBySim3 search loops, SearchByProjection(KeyFrame*, Scw, ...)) against the CPU oracle: bit-exact indices / counts."""
+import numpy as np
+import pytest
+
+from bowsynth import feature_vector, triangulation_geometry
+
+pytestmark = pytest.mark.gpu
+
+W, H = 752, 480
+
+
+@pytest.fixture(scope="module")
+def frames(oracle, synth):
+    out = {}
+    ex = oracle.Extractor(1200, sincos_mode=oracle.SINCOS_PORTABLE)
+    for name, fid, right, jitter in (("a", 0, False, False), ("a_right", 0, True, False), ("a_jit", 0, False, True), ("b", 1, False, False)):
+        img = synth.frame(W, H, 31, fid, right, jitter)
+        _, k, d = ex(img, (0, 0))
+        out[name] = (k, d)
+    out["scale"] = ex.scale.copy()
+    out["sigma2"] = (ex.scale * ex.scale).astype(np.float32)
+    out["inv_sigma2"] = (np.float32(1.0) / out["sigma2"]).astype(np.float32)
+    return out
+
+
+@pytest.mark.parametrize("pair,kfkf,ratio,ori", [(("a", "a_jit"), False, 0.7, True), (("a", "a_jit"), True, 0.75, True),
+                                                 (("a", "a_right"), False, 0.9, False), (("a", "b"), True, 0.9, True)])
+def test_search_by_bow(orbx, oracle, frames, pair, kfkf, ratio, ori):
+    (k1, d1), (k2, d2) = frames[pair[0]], frames[pair[1]]
+    rng = np.random.default_rng(3)
+    fv1, fv2 = feature_vector(d1, 96, 11), feature_vector(d2, 96, 11)
+    elig1 = (rng.uniform(size=len(k1)) < 0.8).astype(np.uint8)          # KF features holding a good map point
+    elig2 = (rng.uniform(size=len(k2)) < 0.85).astype(np.uint8) if kfkf else None
+    max_dist = 49 if kfkf else 50
+    ref_n, ref = oracle.search_by_bow(k1, d1, fv1, elig1, k2, d2, fv2, elig2, max_dist, ratio, ori)
+    m = orbx.ORBmatcher(ratio, ori)
+    n, got = m.SearchByBoW(k1, d1, fv1, elig1, k2, d2, fv2, elig2, max_dist)
+    assert n == ref_n and np.array_equal(got, ref)
+    if pair[1] != "b":
+        assert ref_n > 20
+    # claimed side-2 features are unique and share the vocabulary node of their side-1 feature
+    mm = got[got >= 0]
+    assert len(np.unique(mm)) == len(mm)
+    m.close()
+
+
+def test_search_by_bow_edge_cases(orbx, oracle, frames):
+    (k1, d1), (k2, d2) = frames["a"], frames["a_jit"]
+    m = orbx.ORBmatcher(0.7, True)
+    fv1, fv2 = feature_vector(d1, 8, 1), feature_vector(d2, 8, 1)   # few, very long node lists (> 32 entries per warp pass)
+    e1 = np.ones(len(k1), np.uint8)
+    ref = oracle.search_by_bow(k1, d1, fv1, e1, k2, d2, fv2, None, 50, 0.7, True)
+    got = m.SearchByBoW(k1, d1, fv1, e1, k2, d2, fv2, None, 50)
+    assert got[0] == ref[0] and np.array_equal(got[1], ref[1])
+    # disjoint vocabularies -> nothing; empty sides -> nothing
+    fv2d = (fv2[0] + 100000, fv2[1], fv2[2])
+    assert m.SearchByBoW(k1, d1, fv1, e1, k2, d2, fv2d, None, 50)[0] == 0
+    empty = (np.zeros(0, np.uint32), np.zeros(1, np.int32), np.zeros(0, np.uint32))
+    n, mm = m.SearchByBoW(k1, d1, fv1, e1, k2[:0], d2[:0], empty, None, 50)
+    assert n == 0 and (mm == -1).all()
+    # duplicated descriptors: ties keep the first entry of the node list, second-best equals best -> the ratio test rejects
+    k2d = np.concatenate([k2, k2]); d2d = np.concatenate([d2, d2])
+    fvd = feature_vector(d2d, 8, 1)
+    ref = oracle.search_by_bow(k1, d1, fv1, e1, k2d, d2d, fvd, None, 50, 0.7, False)
+    mo = orbx.ORBmatcher(0.7, False)
+    got = mo.SearchByBoW(k1, d1, fv1, e1, k2d, d2d, fvd, None, 50)
+    assert got[0] == ref[0] and np.array_equal(got[1], ref[1])
+    m.close(); mo.close()
+
+
+@pytest.mark.parametrize("only_stereo,coarse,ori", [(False, False, True), (True, False, True), (False, True, False)])
+def test_search_for_triangulation(orbx, oracle, frames, only_stereo, coarse, ori):
+    (k1, d1), (k2, d2) = frames["a"], frames["a_right"]
+    rng = np.random.default_rng(4)
+    fv1, fv2 = feature_vector(d1, 64, 5), feature_vector(d2, 64, 5)
+    F12, ep = triangulation_geometry(W, H, 7)
+    stereo1 = (rng.uniform(size=len(k1)) < 0.5).astype(np.uint8)
+    stereo2 = (rng.uniform(size=len(k2)) < 0.5).astype(np.uint8)
+    nomp1 = rng.uniform(size=len(k1)) < 0.7
+    nomp2 = rng.uniform(size=len(k2)) < 0.7
+    elig1 = (nomp1 & ((stereo1 > 0) | (not only_stereo))).astype(np.uint8)
+    elig2 = (nomp2 & ((stereo2 > 0) | (not only_stereo))).astype(np.uint8)
+    ref_n, ref = oracle.search_for_triangulation(k1, d1, fv1, elig1, stereo1, k2, d2, fv2, elig2, stereo2, F12, ep, frames["scale"],
+                                                 frames["sigma2"], coarse, ori)
+    m = orbx.ORBmatcher(0.6, ori)
+    n, got = m.SearchForTriangulation(k1, d1, fv1, elig1, stereo1, k2, d2, fv2, elig2, stereo2, F12, ep, frames["scale"],
+                                      frames["sigma2"], coarse)
+    assert n == ref_n and np.array_equal(got, ref)
+    assert ref_n > 3
+    # monocular keyframes (no stereo flags at all)
+    ref_n, ref = oracle.search_for_triangulation(k1, d1, fv1, nomp1.astype(np.uint8), None, k2, d2, fv2, nomp2.astype(np.uint8), None,
+                                                 F12, ep, frames["scale"], frames["sigma2"], coarse, ori)
+    n, got = m.SearchForTriangulation(k1, d1, fv1, nomp1.astype(np.uint8), None, k2, d2, fv2, nomp2.astype(np.uint8), None, F12, ep,
+                                      frames["scale"], frames["sigma2"], coarse)
+    assert n == ref_n and np.array_equal(got, ref)
+    m.close()
+
+
+def _projected_points(frames, synth, name, n, seed):
+    """map points 'seen' from another keyframe: keypoints of `name` with sub-pixel noise + random padding"""
+    k, d = frames[name]
+    rng = np.random.default_rng(seed)
+    pad = n - len(k)
+    u = np.concatenate([k["x"] + rng.normal(0, 0.7, len(k)), rng.uniform(-20, W + 20, pad)]).astype(np.float32)
+    v = np.concatenate([k["y"] + rng.normal(0, 0.7, len(k)), rng.uniform(-20, H + 20, pad)]).astype(np.float32)
+    level = np.concatenate([np.clip(k["octave"] + rng.integers(0, 2, len(k)), 0, 7), rng.integers(0, 8, pad)]).astype(np.int32)
+    desc = np.concatenate([d, synth.random_descriptors(pad, seed)])
+    valid = (rng.uniform(size=n) < 0.93).astype(np.uint8)
+    return valid, u, v, level, desc
+
+
+@pytest.mark.parametrize("gate,stereo,th", [(False, False, 3.0), (True, False, 3.0), (True, True, 4.0), (False, True, 7.5)])
+def test_search_window_best_fuse_loops(orbx, oracle, synth, frames, gate, stereo, th):
+    k, d = frames["a"]
+    rng = np.random.default_rng(6)
+    n = len(frames["a_jit"][0]) + 800
+    valid, u, v, level, desc = _projected_points(frames, synth, "a_jit", n, 8)
+    radius = (np.float32(th) * frames["scale"][level]).astype(np.float32)
+    uR = None; ur = None
+    if stereo:
+        uR = np.where(rng.uniform(size=len(k)) < 0.6, k["x"] - rng.uniform(0, 30, len(k)), -1).astype(np.float32)
+        ur = (u - rng.uniform(0, 30, n)).astype(np.float32)
+    ref_i, ref_d = oracle.search_window_best(k, d, W, H, valid, u, v, radius, level, desc, int(gate), frames["inv_sigma2"], uR, ur)
+    F = orbx.FrameView(k, d, frames["scale"], W, H, u_right=uR)
+    m = orbx.ORBmatcher()
+    bi, bd = m.SearchWindowBest(F, valid, u, v, radius, level, desc, gate, frames["inv_sigma2"], ur)
+    assert np.array_equal(bi, ref_i) and np.array_equal(bd, ref_d)
+    assert (ref_d <= 50).sum() > 200
+    if gate:  # the chi-square gate must actually remove candidates that the ungated search accepts
+        ui, ud = oracle.search_window_best(k, d, W, H, valid, u, v, radius, level, desc, 0, None, uR, ur)
+        assert (ui != ref_i).any()
+    m.close()
+
+
+def test_search_by_sim3(orbx, oracle, synth, frames):
+    (k1, d1), (k2, d2) = frames["a"], frames["a_jit"]
+    n1, n2 = len(k1), len(k2)
+    rng = np.random.default_rng(9)
+    # pass 1: map point of keypoint i1 of KF1 projected into KF2 (near its true match when there is one); pass 2 likewise
+    def proj(ksrc, seed):
+        r = np.random.default_rng(seed)
+        u = (ksrc["x"] + r.normal(0, 1.0, len(ksrc))).astype(np.float32)
+        v = (ksrc["y"] + r.normal(0, 1.0, len(ksrc))).astype(np.float32)
+        lvl = np.clip(ksrc["octave"] + r.integers(0, 2, len(ksrc)), 0, 7).astype(np.int32)
+        valid = (r.uniform(size=len(ksrc)) < 0.8).astype(np.uint8)   # has a good map point, not already matched, in image
+        return valid, u, v, lvl
+    va1, u1, v1, l1 = proj(k1, 1); va2, u2, v2, l2 = proj(k2, 2)
+    r1 = (np.float32(7.5) * frames["scale"][l1]).astype(np.float32); r2 = (np.float32(7.5) * frames["scale"][l2]).astype(np.float32)
+    F1 = orbx.FrameView(k1, d1, frames["scale"], W, H); F2 = orbx.FrameView(k2, d2, frames["scale"], W, H)
+    m = orbx.ORBmatcher()
+    nfound, m12 = m.SearchBySim3Projected(F1, F2, va1, u1, v1, r1, l1, d1, va2, u2, v2, r2, l2, d2)
+    # oracle: the reference's two loops + agreement (ORBmatcher.cc:1866-1999)
+    b1, dd1 = oracle.search_window_best(k2, d2, W, H, va1, u1, v1, r1, l1, d1)
+    b2, dd2 = oracle.search_window_best(k1, d1, W, H, va2, u2, v2, r2, l2, d2)
+    vn1 = np.where(dd1 <= 100, b1, -1); vn2 = np.where(dd2 <= 100, b2, -1)
+    ref = np.full(n1, -1, np.int32)
+    for i1 in range(n1):
+        if vn1[i1] >= 0 and vn2[vn1[i1]] == i1:
+            ref[i1] = vn1[i1]
+    assert np.array_equal(m12, ref) and nfound == int((ref >= 0).sum())
+    assert nfound > 300
+    m.close()
+
+
+@pytest.mark.parametrize("ratio_hamming,th", [(1.0, 3), (0.8, 5)])
+def test_search_by_projection_keyframe_scw(orbx, oracle, synth, frames, ratio_hamming, th):
+    """SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th, ratioHamming), ORBmatcher.cc:489-602, after projection"""
+    k, d = frames["a"]
+    n = len(frames["a_jit"][0]) + 500
+    valid, u, v, level, desc = _projected_points(frames, synth, "a_jit", n, 12)
+    rng = np.random.default_rng(13)
+    kp0 = np.full(len(k), -1, np.int32)
+    kp0[rng.integers(0, len(k), 150)] = -2          # vpMatched[idx] already set
+    dist_th = int(np.floor(np.float32(50) * np.float32(ratio_hamming)))
+    ref_n, ref = oracle.search_by_projection_window(k, d, frames["scale"], W, H, valid, u, v, level, np.zeros(n, np.float32), desc,
+                                                    float(th), 3, dist_th, True, False, kp0)
+    F = orbx.FrameView(k, d, frames["scale"], W, H)
+    m = orbx.ORBmatcher(0.6, False)
+    got_n, got = m.SearchByProjectionWindow(F, valid, u, v, level, np.zeros(n, np.float32), desc, float(th), 3, dist_th, True, kp0)
+    assert got_n == ref_n and np.array_equal(got, ref)
+    assert ref_n > 200
+    m.close()
