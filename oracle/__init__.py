@@ -295,6 +295,28 @@ def search_window_best(kps, desc, w, h, valid, u, v, radius, level, qdesc, gate=
     return bi[:n], bd[:n]
 
 
+def distinctive_descriptors(desc, start):
+    """MapPoint::ComputeDistinctiveDescriptors for a batch: -> (best_idx[npoints], best_median[npoints])"""
+    desc = _u8(desc); start = np.ascontiguousarray(start, np.int32)
+    npts = start.shape[0] - 1
+    bi = np.empty(max(npts, 1), np.int32); bm = np.empty(max(npts, 1), np.int32)
+    lib().oro_distinctive_descriptors(_p(desc), _p(start), npts, _p(bi), _p(bm))
+    return bi[:npts], bm[:npts]
+
+
+def vocab_transform(vocab, desc, levelsup):
+    """vocab = dict(L, child_start, child_ids, node_desc, node_weight, node_word_id) -> (word_id, node_id, weight) per feature"""
+    desc = _u8(desc).reshape(-1, 32)
+    cs = np.ascontiguousarray(vocab["child_start"], np.int32); ci = np.ascontiguousarray(vocab["child_ids"], np.int32)
+    nd = _u8(vocab["node_desc"]); nw = np.ascontiguousarray(vocab["node_weight"], np.float64)
+    wi = np.ascontiguousarray(vocab["node_word_id"], np.int32)
+    n = desc.shape[0]
+    w = np.empty(max(n, 1), np.int32); nid = np.empty(max(n, 1), np.int32); wt = np.empty(max(n, 1), np.float64)
+    lib().oro_vocab_transform(cs.shape[0] - 1, int(vocab["L"]), _p(cs), _p(ci), _p(nd), _p(nw), _p(wi), _p(desc), n, int(levelsup),
+                              _p(w), _p(nid), _p(wt))
+    return w[:n], nid[:n], wt[:n]
+
+
 def stereo_matches(exL, exR, kpL, descL, kpR, descR, mb, mbf):
     """exL / exR: oracle Extractor objects that have just extracted the left / right image."""
     kpL = np.ascontiguousarray(kpL, KP_DTYPE); kpR = np.ascontiguousarray(kpR, KP_DTYPE)

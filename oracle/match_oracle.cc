@@ -486,4 +486,49 @@ void search_window_best(const FrameView& F, int n, const uint8_t* valid, const f
 }
 
 
+// ---- SURVEY.md §8(f) rank 4 ----------------------------------------------------------------------------------------------------
+// MapPoint.cc:385-428.
+void distinctive_descriptors(const uint8_t* desc, const int* start, int npoints, int* bestIdxOut, int* bestMedianOut) {
+  std::vector<int> vDists;
+  for (int p = 0; p < npoints; p++) {
+    const int N = start[p + 1] - start[p];
+    const uint8_t* d = desc + 32 * (size_t)start[p];
+    int BestMedian = INT_MAX, BestIdx = 0;
+    if (N <= 0) { bestIdxOut[p] = -1; bestMedianOut[p] = INT_MAX; continue; }
+    for (int i = 0; i < N; i++) {
+      vDists.resize(N);
+      for (int j = 0; j < N; j++) vDists[j] = (i == j) ? 0 : hamming256(d + 32 * (size_t)i, d + 32 * (size_t)j);
+      std::sort(vDists.begin(), vDists.end());
+      const int median = vDists[(size_t)(0.5 * (N - 1))];
+      if (median < BestMedian) { BestMedian = median; BestIdx = i; }
+    }
+    bestIdxOut[p] = BestIdx; bestMedianOut[p] = BestMedian;
+  }
+}
+
+// TemplatedVocabulary.h:1218-1259 (FORB::distance = the same bit-count, FORB.cpp:81-101).
+void vocab_transform(const VocabTree& V, const uint8_t* desc, int n, int levelsup, int* wordId, int* nodeId, double* weight) {
+  const int nid_level = V.L - levelsup;
+  for (int f = 0; f < n; f++) {
+    const uint8_t* feature = desc + 32 * (size_t)f;
+    int nid = 0;   // "if(nid_level <= 0 && nid != NULL) *nid = 0"; otherwise set on the way down
+    int final_id = 0, current_level = 0;
+    do {
+      ++current_level;
+      const int c0 = V.childStart[final_id], c1 = V.childStart[final_id + 1];
+      final_id = V.childIds[c0];
+      double best_d = hamming256(feature, V.nodeDesc + 32 * (size_t)final_id);
+      for (int c = c0 + 1; c < c1; c++) {
+        const int id = V.childIds[c];
+        const double d = hamming256(feature, V.nodeDesc + 32 * (size_t)id);
+        if (d < best_d) { best_d = d; final_id = id; }
+      }
+      if (current_level == nid_level) nid = final_id;
+    } while (V.childStart[final_id + 1] > V.childStart[final_id]);   // !isLeaf()
+    wordId[f] = V.nodeWordId[final_id];
+    nodeId[f] = nid;
+    weight[f] = V.nodeWeight[final_id];
+  }
+}
+
 }  // namespace oro

@@ -118,4 +118,23 @@ void search_window_best(const FrameView& F, int n, const uint8_t* valid, const f
                         const int* level, const float* ur, const uint8_t* desc, int gate, const float* invLevelSigma2,
                         int* bestIdx, int* bestDist);
 
+// ---- pure Hamming workloads next to the path ------------------------------------------------------------
+// MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:350-436, for a batch of map points: descriptors of point p are
+// rows start[p] .. start[p+1]-1 of desc.  bestIdx[p] = row (relative to start[p]) with the least median distance to the others
+// (median = sorted row [0.5*(N-1)], first minimum wins), bestMedian[p] that median; -1 / INT_MAX for a point without rows.
+void distinctive_descriptors(const uint8_t* desc, const int* start, int npoints, int* bestIdx, int* bestMedian);
+
+// DBoW2 vocabulary tree flattened (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h: m_nodes[id].children / descriptor / weight /
+// word_id).  Node 0 is the root; children of node i are childIds[childStart[i] .. childStart[i+1]) in their stored order.
+struct VocabTree {
+  int nnodes = 0, L = 0;
+  const int* childStart = nullptr;
+  const int* childIds = nullptr;
+  const uint8_t* nodeDesc = nullptr;   // nnodes x 32
+  const double* nodeWeight = nullptr;
+  const int* nodeWordId = nullptr;     // -1 for inner nodes
+};
+// TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup), TemplatedVocabulary.h:1218-1259, for n features.
+void vocab_transform(const VocabTree& V, const uint8_t* desc, int n, int levelsup, int* wordId, int* nodeId, double* weight);
+
 }  // namespace oro

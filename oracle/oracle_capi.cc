@@ -188,6 +188,16 @@ void oro_search_window_best(int N, const KeyPoint* kps, const uint8_t* desc, con
   fill_view(F, N, kps, desc, uRight, nullptr, bounds4);
   search_window_best(F, n, valid, u, v, radius, level, ur, qdesc, gate, invLevelSigma2, bestIdx, bestDist);
 }
+// ---- SURVEY.md §8(f) rank 4 ----
+void oro_distinctive_descriptors(const uint8_t* desc, const int* start, int npoints, int* bestIdx, int* bestMedian) {
+  distinctive_descriptors(desc, start, npoints, bestIdx, bestMedian);
+}
+void oro_vocab_transform(int nnodes, int L, const int* childStart, const int* childIds, const uint8_t* nodeDesc, const double* nodeWeight,
+                         const int* nodeWordId, const uint8_t* desc, int n, int levelsup, int* wordId, int* nodeId, double* weight) {
+  VocabTree V; V.nnodes = nnodes; V.L = L; V.childStart = childStart; V.childIds = childIds; V.nodeDesc = nodeDesc;
+  V.nodeWeight = nodeWeight; V.nodeWordId = nodeWordId;
+  vocab_transform(V, desc, n, levelsup, wordId, nodeId, weight);
+}
 void oro_three_maxima(const int* hist, int L, int* ind3) {
   int a = -1, b = -1, c = -1;
   compute_three_maxima(hist, L, a, b, c);
