@@ -969,4 +969,88 @@ __global__ void __launch_bounds__(256) k_bow_rotfilter(const __grid_constant__ B
   if (tid == 0) *A.nmatches = total;
 }
 
+// ---- MapPoint::ComputeDistinctiveDescriptors, DBoW2 tree descent ------------------------------------------
+// MapPoint.cc:385-428 for a batch of map points: warp = map point.  For every row i the lanes spread over the other
+// observations, distances go into a per-warp 257-bin histogram in shared memory, the median (sorted row [0.5*(N-1)]) is the
+// first bin whose running count exceeds that rank; the row with the least median wins, first row on ties.
+__global__ void __launch_bounds__(256) k_distinctive(const uint8_t* desc, const int* start, int npoints, int* bestIdx, int* bestMedian) {
+  __shared__ int hist[8][288];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int p = blockIdx.x * 8 + warp;
+  if (p >= npoints) return;
+  const int s0 = start[p], N = start[p + 1] - s0;
+  if (N <= 0) { if (lane == 0) { bestIdx[p] = -1; bestMedian[p] = INT_MAX; } return; }
+  const uint8_t* d = desc + 32ll * s0;
+  const int rank = (int)(0.5 * (double)(N - 1));
+  int* h = hist[warp];
+  int best = INT_MAX, bestI = 0;
+  for (int i = 0; i < N; i++) {
+#pragma unroll
+    for (int b = 0; b < 9; b++) h[lane * 9 + b] = 0;
+    __syncwarp();
+    uint32_t di[8];
+    load_desc(d + 32ll * i, di);
+    for (int j = lane; j < N; j += 32) {
+      uint32_t dj[8];
+      load_desc(d + 32ll * j, dj);
+      atomicAdd(&h[(i == j) ? 0 : hamming8(di, dj)], 1);
+    }
+    __syncwarp();
+    // lane owns bins [9*lane, 9*lane+9): exclusive prefix of the lane sums, then walk the own bins
+    int c[9], sum = 0;
+#pragma unroll
+    for (int b = 0; b < 9; b++) { c[b] = h[lane * 9 + b]; sum += c[b]; }
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    int run = incl - sum, median = INT_MAX;
+#pragma unroll
+    for (int b = 0; b < 9; b++) {
+      if (median == INT_MAX && run <= rank && rank < run + c[b]) median = lane * 9 + b;
+      run += c[b];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) median = min(median, __shfl_xor_sync(0xffffffffu, median, o));
+    if (median < best) { best = median; bestI = i; }
+    __syncwarp();
+  }
+  if (lane == 0) { bestIdx[p] = bestI; bestMedian[p] = best; }
+}
+
+// TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup), TemplatedVocabulary.h:1218-1259: warp = feature, lanes =
+// the children of the current node (k = 10 for ORBvoc), first strict minimum wins (key = distance | child position).
+struct VocabDev {
+  const int* childStart; const int* childIds; const uint8_t* nodeDesc; const double* nodeWeight; const int* nodeWordId;
+  int nnodes, L;
+};
+__global__ void __launch_bounds__(256) k_vocab_transform(const __grid_constant__ VocabDev V, const uint8_t* desc, int n, int levelsup,
+                                                         int* wordId, int* nodeId, double* weight) {
+  const int lane = threadIdx.x & 31;
+  const int f = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (f >= n) return;
+  uint32_t d[8];
+  load_desc(desc + 32ll * f, d);
+  const int nidLevel = V.L - levelsup;
+  int nid = 0, finalId = 0, level = 0;
+  for (;;) {
+    const int c0 = V.childStart[finalId], c1 = V.childStart[finalId + 1];
+    if (c1 <= c0 || level >= 64) break;   // leaf (the host validated the depth)
+    ++level;
+    unsigned best = 0xffffffffu;
+    for (int c = c0 + lane; c < c1; c += 32) {
+      uint32_t cd[8];
+      load_desc(V.nodeDesc + 32ll * V.childIds[c], cd);
+      best = min(best, ((unsigned)hamming8(d, cd) << 20) | (unsigned)(c - c0));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    finalId = V.childIds[c0 + (int)(best & 0xfffffu)];
+    if (level == nidLevel) nid = finalId;
+  }
+  if (lane == 0) { wordId[f] = V.nodeWordId[finalId]; nodeId[f] = nid; weight[f] = V.nodeWeight[finalId]; }
+}
+
 }  // namespace orbx

@@ -602,6 +602,114 @@ int orbx_search_for_triangulation(orbx_matcher* m, int n1, const orbx_keypoint* 
   return run_bow(m, P, matches12, nmatches);
 }
 
+int orbx_distinctive_descriptors(orbx_matcher* m, const uint8_t* desc, const int* start, int npoints, int* bestIdx, int* bestMedian) {
+  if (!m || npoints < 0 || (npoints > 0 && (!start || !bestIdx || !bestMedian))) return ORBX_ERR_ARG;
+  if (npoints == 0) return ORBX_OK;
+  for (int p = 0; p < npoints; p++)
+    if (start[p + 1] < start[p] || start[p] < 0) { set_error("descriptor ranges must ascend"); return ORBX_ERR_ARG; }
+  const int total = start[npoints];
+  if (total > 0 && !desc) return ORBX_ERR_ARG;
+  CK(cudaSetDevice(m->device));
+  ArenaPlan plan;
+  const size_t oD = plan.add((size_t)std::max(total, 1) * 32), oS = plan.add((size_t)(npoints + 1) * 4);
+  const size_t oI = plan.add((size_t)npoints * 4), oM = plan.add((size_t)npoints * 4);
+  int rc = arena_ensure(m, plan.total);
+  if (rc != ORBX_OK) return rc;
+  cudaStream_t st = m->stream;
+  if (total > 0) CK(cudaMemcpyAsync(m->arena + oD, desc, (size_t)total * 32, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(m->arena + oS, start, (size_t)(npoints + 1) * 4, cudaMemcpyHostToDevice, st));
+  k_distinctive<<<(npoints + 7) / 8, 256, 0, st>>>(at<uint8_t>(m, oD), at<int>(m, oS), npoints, at<int>(m, oI), at<int>(m, oM));
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(bestIdx, m->arena + oI, (size_t)npoints * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(bestMedian, m->arena + oM, (size_t)npoints * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return ORBX_OK;
+}
+
+struct orbx_vocabulary {
+  int device = 0;
+  uint8_t* mem = nullptr;
+  VocabDev dev{};
+};
+
+int orbx_vocabulary_create(int device, int nnodes, int L, const int* childStart, const int* childIds, const uint8_t* nodeDesc,
+                           const double* nodeWeight, const int* nodeWordId, orbx_vocabulary** out) {
+  if (!out || nnodes < 2 || L < 1 || L > 63 || !childStart || !childIds || !nodeDesc || !nodeWeight || !nodeWordId) return ORBX_ERR_ARG;
+  *out = nullptr;
+  // structure checks: child ranges ascend, ids are in range and point "down" (every non-root node has exactly one parent), root not a leaf,
+  // depth <= L so the descent terminates
+  if (childStart[0] != 0 || childStart[1] <= 0) { set_error("vocabulary root has no children"); return ORBX_ERR_ARG; }
+  const int nchild = childStart[nnodes];
+  if (nchild != nnodes - 1) { set_error("vocabulary is not a tree (%d child links for %d nodes)", nchild, nnodes); return ORBX_ERR_ARG; }
+  std::vector<int> depth(nnodes, -1);
+  depth[0] = 0;
+  std::vector<int> stack(1, 0);
+  int visited = 0;
+  while (!stack.empty()) {
+    const int id = stack.back(); stack.pop_back();
+    visited++;
+    if (childStart[id + 1] < childStart[id]) { set_error("vocabulary child ranges must ascend"); return ORBX_ERR_ARG; }
+    for (int c = childStart[id]; c < childStart[id + 1]; c++) {
+      const int ch = childIds[c];
+      if (ch <= 0 || ch >= nnodes || depth[ch] != -1) { set_error("vocabulary child id %d invalid or shared", ch); return ORBX_ERR_ARG; }
+      depth[ch] = depth[id] + 1;
+      if (depth[ch] > L) { set_error("vocabulary deeper than L = %d", L); return ORBX_ERR_ARG; }
+      stack.push_back(ch);
+    }
+  }
+  if (visited != nnodes) { set_error("vocabulary has unreachable nodes"); return ORBX_ERR_ARG; }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) { set_error("no usable CUDA device %d", device); return ORBX_ERR_CUDA; }
+  CK(cudaSetDevice(device));
+  orbx_vocabulary* v = new orbx_vocabulary();
+  v->device = device;
+  ArenaPlan plan;
+  const size_t oCS = plan.add((size_t)(nnodes + 1) * 4), oCI = plan.add((size_t)nchild * 4), oND = plan.add((size_t)nnodes * 32);
+  const size_t oNW = plan.add((size_t)nnodes * 8), oWI = plan.add((size_t)nnodes * 4);
+  if (cudaMalloc(&v->mem, plan.total) != cudaSuccess) { delete v; set_error("cudaMalloc of the vocabulary failed"); return ORBX_ERR_CUDA; }
+  cudaMemcpy(v->mem + oCS, childStart, (size_t)(nnodes + 1) * 4, cudaMemcpyHostToDevice);
+  cudaMemcpy(v->mem + oCI, childIds, (size_t)nchild * 4, cudaMemcpyHostToDevice);
+  cudaMemcpy(v->mem + oND, nodeDesc, (size_t)nnodes * 32, cudaMemcpyHostToDevice);
+  cudaMemcpy(v->mem + oNW, nodeWeight, (size_t)nnodes * 8, cudaMemcpyHostToDevice);
+  if (cudaMemcpy(v->mem + oWI, nodeWordId, (size_t)nnodes * 4, cudaMemcpyHostToDevice) != cudaSuccess) {
+    cudaFree(v->mem); delete v; set_error("vocabulary upload failed"); return ORBX_ERR_CUDA;
+  }
+  v->dev.childStart = reinterpret_cast<int*>(v->mem + oCS); v->dev.childIds = reinterpret_cast<int*>(v->mem + oCI);
+  v->dev.nodeDesc = v->mem + oND; v->dev.nodeWeight = reinterpret_cast<double*>(v->mem + oNW);
+  v->dev.nodeWordId = reinterpret_cast<int*>(v->mem + oWI);
+  v->dev.nnodes = nnodes; v->dev.L = L;
+  *out = v;
+  return ORBX_OK;
+}
+
+void orbx_vocabulary_destroy(orbx_vocabulary* v) {
+  if (!v) return;
+  cudaSetDevice(v->device);
+  if (v->mem) cudaFree(v->mem);
+  delete v;
+}
+
+int orbx_vocabulary_transform(orbx_matcher* m, const orbx_vocabulary* v, const uint8_t* desc, int n, int levelsup, int* wordId, int* nodeId,
+                              double* weight) {
+  if (!m || !v || n < 0 || (n > 0 && (!desc || !wordId || !nodeId || !weight))) return ORBX_ERR_ARG;
+  if (v->device != m->device) { set_error("vocabulary and matcher live on different devices"); return ORBX_ERR_ARG; }
+  if (n == 0) return ORBX_OK;
+  CK(cudaSetDevice(m->device));
+  ArenaPlan plan;
+  const size_t oD = plan.add((size_t)n * 32), oW = plan.add((size_t)n * 4), oN = plan.add((size_t)n * 4), oWt = plan.add((size_t)n * 8);
+  int rc = arena_ensure(m, plan.total);
+  if (rc != ORBX_OK) return rc;
+  cudaStream_t st = m->stream;
+  CK(cudaMemcpyAsync(m->arena + oD, desc, (size_t)n * 32, cudaMemcpyHostToDevice, st));
+  k_vocab_transform<<<(n + 7) / 8, 256, 0, st>>>(v->dev, at<uint8_t>(m, oD), n, levelsup, at<int>(m, oW), at<int>(m, oN), at<double>(m, oWt));
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(wordId, m->arena + oW, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(nodeId, m->arena + oN, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(weight, m->arena + oWt, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return ORBX_OK;
+}
+
 int orbx_search_for_initialization(orbx_matcher* m, const orbx_frame_view* F1, const orbx_frame_view* F2, float* prevMatched, int windowSize,
                                    float nnratio, int checkOrientation, int* matches12, int* nmatches) {
   if (!m || !F1 || !prevMatched || !matches12 || !nmatches) return ORBX_ERR_ARG;

@@ -211,6 +211,23 @@ class ORBmatcher {
     orbx_shim::check(orbx_knn2(m_, q.data(), query.rows, t.data(), train.rows, idx.data(), dist.data(), good.data()), "orbx_knn2");
   }
 
+  // MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:385-428) for a batch of map points: vDescriptors[p] is the list
+  // the reference gathers per point (:366-382); returns the index of the descriptor to keep per point (-1 for an empty list).
+  std::vector<int> DistinctiveDescriptors(const std::vector<std::vector<cvx::Mat> >& vDescriptors) {
+    std::vector<int> start(1, 0), best(vDescriptors.size(), -1), median(vDescriptors.size(), 0);
+    std::vector<uint8_t> rows;
+    for (size_t p = 0; p < vDescriptors.size(); p++) {
+      for (size_t k = 0; k < vDescriptors[p].size(); k++) rows.insert(rows.end(), vDescriptors[p][k].ptr(0), vDescriptors[p][k].ptr(0) + 32);
+      start.push_back((int)(rows.size() / 32));
+    }
+    if (rows.empty()) rows.resize(32);
+    orbx_shim::check(orbx_distinctive_descriptors(m_, rows.data(), start.data(), (int)vDescriptors.size(), best.data(), median.data()),
+                     "orbx_distinctive_descriptors");
+    return best;
+  }
+
+  orbx_matcher* handle() const { return m_; }
+
  protected:
   float mfNNratio;
   bool mbCheckOrientation;
@@ -266,6 +283,42 @@ class ORBmatcher {
     }
   };
   orbx_matcher* m_ = nullptr;
+};
+
+// The tree descent of ORBVocabulary::transform (DBoW2 TemplatedVocabulary<FORB>, Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1130-1195,
+// 1218-1259) on the GPU, for Frame::ComputeBoW / KeyFrame::ComputeBoW (src/Frame.cc:828-835).  Built from the flattened m_nodes
+// (a subclass of the reference's vocabulary can export them: m_nodes is protected); BowVectorT / FeatureVectorT are the
+// reference's DBoW2::BowVector / DBoW2::FeatureVector (addWeight / normalize / addFeature are called in the reference's order).
+class ORBVocabularyDevice {
+ public:
+  ORBVocabularyDevice(int L, const std::vector<int>& childStart, const std::vector<int>& childIds, const std::vector<uint8_t>& nodeDesc,
+                      const std::vector<double>& nodeWeight, const std::vector<int>& nodeWordId, int device = 0) {
+    orbx_shim::check(orbx_vocabulary_create(device, (int)nodeWordId.size(), L, childStart.data(), childIds.data(), nodeDesc.data(),
+                                            nodeWeight.data(), nodeWordId.data(), &v_),
+                     "orbx_vocabulary_create");
+  }
+  ~ORBVocabularyDevice() { orbx_vocabulary_destroy(v_); }
+  ORBVocabularyDevice(const ORBVocabularyDevice&) = delete;
+  ORBVocabularyDevice& operator=(const ORBVocabularyDevice&) = delete;
+
+  template <class BowVectorT, class FeatureVectorT, class NormT>
+  void transform(ORBmatcher& matcher, const std::vector<cvx::Mat>& features, BowVectorT& v, FeatureVectorT& fv, int levelsup, NormT l1) const {
+    v.clear(); fv.clear();
+    const int n = (int)features.size();
+    if (n == 0) return;
+    std::vector<uint8_t> rows((size_t)n * 32);
+    for (int i = 0; i < n; i++) memcpy(&rows[(size_t)i * 32], features[i].ptr(0), 32);
+    std::vector<int> word(n), node(n);
+    std::vector<double> weight(n);
+    orbx_shim::check(orbx_vocabulary_transform(matcher.handle(), v_, rows.data(), n, levelsup, word.data(), node.data(), weight.data()),
+                     "orbx_vocabulary_transform");
+    for (int i = 0; i < n; i++)
+      if (weight[i] > 0) { v.addWeight(word[i], weight[i]); fv.addFeature(node[i], (unsigned)i); }   // TemplatedVocabulary.h:1160-1168
+    v.normalize(l1);                                                                                   // :1194 (L1 for ORBvoc)
+  }
+
+ private:
+  orbx_vocabulary* v_ = nullptr;
 };
 
 }  // namespace ORB_SLAM3

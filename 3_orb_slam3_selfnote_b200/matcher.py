@@ -192,6 +192,15 @@ class ORBmatcher:
                                                    int(self.mbCheckOrientation), _p(m12), C.byref(nm)))
         return nm.value, m12[:len(kps1)]
 
+    def DistinctiveDescriptors(self, desc, start):
+        """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:350) for a batch of map points: descriptors of point p
+        are rows start[p]:start[p+1].  -> (best_idx[npoints] relative to start[p], best_median[npoints])"""
+        desc = _u8(desc).reshape(-1, 32); start = _i32(start)
+        npts = len(start) - 1
+        bi = np.empty(max(npts, 1), np.int32); bm = np.empty(max(npts, 1), np.int32)
+        _check(lib().orbx_distinctive_descriptors(self._m, _p(desc), _p(start), npts, _p(bi), _p(bm)))
+        return bi[:npts], bm[:npts]
+
     def SearchForInitialization(self, F1, F2, vbPrevMatched, windowSize=10):
         pm = _f32(vbPrevMatched).reshape(-1, 2).copy()
         m12 = np.empty(F1.N, np.int32)
@@ -240,3 +249,55 @@ class ORBmatcher:
         bd = np.empty((nframes, cap), np.int32); bi = np.empty((nframes, cap), np.int32)
         _check(lib().orbx_stereo_results_host(self._m, _p(uR), _p(depth), _p(bd), _p(bi), cap))
         return uR, depth, bd, bi
+
+
+class ORBVocabulary:
+    """The tree descent of DBoW2's TemplatedVocabulary<FORB> (the reference's ORBVocabulary, include/ORBVocabulary.h) on the GPU.
+
+    vocab = dict(L, child_start, child_ids, node_desc, node_weight, node_word_id): the flattened m_nodes."""
+
+    def __init__(self, vocab, device=0):
+        self._keep = (_i32(vocab["child_start"]), _i32(vocab["child_ids"]), _u8(vocab["node_desc"]),
+                      np.ascontiguousarray(vocab["node_weight"], np.float64), _i32(vocab["node_word_id"]))
+        cs, ci, nd, nw, wi = self._keep
+        self._v = C.c_void_p()
+        _check(lib().orbx_vocabulary_create(device, len(cs) - 1, int(vocab["L"]), _p(cs), _p(ci), _p(nd), _p(nw), _p(wi),
+                                            C.byref(self._v)))
+
+    def close(self):
+        if getattr(self, "_v", None) and self._v.value:
+            lib().orbx_vocabulary_destroy(self._v)
+            self._v = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def transform_features(self, matcher, desc, levelsup=4):
+        """-> (word_id, node_id, weight) per feature, TemplatedVocabulary.h:1218-1259"""
+        desc = _u8(desc).reshape(-1, 32)
+        n = len(desc)
+        w = np.empty(max(n, 1), np.int32); nid = np.empty(max(n, 1), np.int32); wt = np.empty(max(n, 1), np.float64)
+        _check(lib().orbx_vocabulary_transform(matcher._m, self._v, _p(desc), n, int(levelsup), _p(w), _p(nid), _p(wt)))
+        return w[:n], nid[:n], wt[:n]
+
+    def transform(self, matcher, desc, levelsup=4):
+        """Frame::ComputeBoW (src/Frame.cc:828-835): -> (bow_ids, bow_values, (fv_node_ids, fv_start, fv_indices)) for the
+        TF_IDF / L1 settings of ORBvoc.  The fold is the reference's std::map insertion order restated on arrays: weights of
+        one word are added in feature order, the L1 norm runs over ascending word ids (TemplatedVocabulary.h:1145-1195)."""
+        w, nid, wt = self.transform_features(matcher, desc, levelsup)
+        keep = wt > 0
+        idx = np.nonzero(keep)[0]
+        ids, inv = np.unique(w[idx], return_inverse=True)
+        vals = np.zeros(len(ids), np.float64)
+        np.add.at(vals, inv, wt[idx])                 # unbuffered: sequential in feature order, like addWeight
+        norm = float(np.cumsum(np.abs(vals))[-1]) if len(vals) else 0.0   # sequential sum in ascending word order
+        if norm > 0.0:
+            vals = vals / norm
+        nodes = np.unique(nid[idx])
+        start = [0]; ind = []
+        for nd in nodes:
+            ind.extend(idx[nid[idx] == nd].tolist()); start.append(len(ind))
+        return ids.astype(np.uint32), vals, (nodes.astype(np.uint32), np.array(start, np.int32), np.array(ind, np.uint32))

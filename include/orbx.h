@@ -231,6 +231,30 @@ int orbx_search_for_triangulation(orbx_matcher* m, int n1, const orbx_keypoint* 
                                   const float* level_sigma2_2, int nlevels, int coarse, int check_orientation, int* matches12,
                                   int* nmatches);
 
+/* ---- pure Hamming workloads on descriptors next to the path ---------------------------------- */
+
+/* MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:350-436, for a batch of map points (LocalMapping calls it per
+ * point in loops, src/LocalMapping.cc:539, :1011): the observations' descriptors of point p are rows start[p] .. start[p+1]-1
+ * of desc (the vDescriptors the reference gathers at MapPoint.cc:366-382).  best_idx[p] = row (relative to start[p]) whose
+ * median Hamming distance to the others is least, first row on ties; best_median[p] that median; -1 / INT_MAX when empty. */
+int orbx_distinctive_descriptors(orbx_matcher* m, const uint8_t* desc, const int* start, int npoints, int* best_idx,
+                                 int* best_median);
+
+/* The DBoW2 vocabulary tree (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h, m_nodes) resident in HBM.  Node 0 is the root;
+ * the children of node i are child_ids[child_start[i] .. child_start[i+1]) in stored order; node_desc is nnodes x 32 bytes
+ * (FORB descriptors), node_weight the idf weights, node_word_id the word id of leaves (-1 otherwise).  ORBvoc (k = 10, L = 6,
+ * 1 082 073 nodes) takes 52 MB. */
+typedef struct orbx_vocabulary orbx_vocabulary;
+int orbx_vocabulary_create(int device, int nnodes, int L, const int* child_start, const int* child_ids, const uint8_t* node_desc,
+                           const double* node_weight, const int* node_word_id, orbx_vocabulary** out);
+void orbx_vocabulary_destroy(orbx_vocabulary* v);
+/* TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup), TemplatedVocabulary.h:1218-1259, for n features: the
+ * tree descent of Frame::ComputeBoW / KeyFrame::ComputeBoW (src/Frame.cc:828-835, levelsup = 4).  The caller folds the three
+ * arrays into BowVector / FeatureVector in feature order (addWeight / addFeature / normalize, TemplatedVocabulary.h:1145-1195):
+ * that part is a std::map insertion in a fixed order and stays on the host. */
+int orbx_vocabulary_transform(orbx_matcher* m, const orbx_vocabulary* v, const uint8_t* desc, int n, int levelsup, int* word_id,
+                              int* node_id, double* weight);
+
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize), src/ORBmatcher.cc:722-837.
  * prev_matched: F1->n x 2 floats (in/out), matches12: F1->n ints (out). */
 int orbx_search_for_initialization(orbx_matcher* m, const orbx_frame_view* F1, const orbx_frame_view* F2, float* prev_matched,

@@ -317,6 +317,18 @@ def vocab_transform(vocab, desc, levelsup):
     return w[:n], nid[:n], wt[:n]
 
 
+def vocab_fold(word_id, node_id, weight):
+    """per-feature (word, node, weight) -> (bow_ids, bow_values, (fv_node_ids, fv_start, fv_indices)); TF_IDF + L1"""
+    word_id = np.ascontiguousarray(word_id, np.int32); node_id = np.ascontiguousarray(node_id, np.int32)
+    weight = np.ascontiguousarray(weight, np.float64)
+    n = word_id.shape[0]
+    bi = np.empty(max(n, 1), np.uint32); bv = np.empty(max(n, 1), np.float64)
+    fi = np.empty(max(n, 1), np.uint32); fs = np.empty(n + 1, np.int32); fx = np.empty(max(n, 1), np.uint32)
+    nn = C.c_int(0)
+    k = lib().oro_vocab_fold(_p(word_id), _p(node_id), _p(weight), n, _p(bi), _p(bv), _p(fi), _p(fs), _p(fx), C.byref(nn))
+    return bi[:k].copy(), bv[:k].copy(), (fi[:nn.value].copy(), fs[:nn.value + 1].copy(), fx[:fs[nn.value]].copy())
+
+
 def stereo_matches(exL, exR, kpL, descL, kpR, descR, mb, mbf):
     """exL / exR: oracle Extractor objects that have just extracted the left / right image."""
     kpL = np.ascontiguousarray(kpL, KP_DTYPE); kpR = np.ascontiguousarray(kpR, KP_DTYPE)

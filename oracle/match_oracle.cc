@@ -531,4 +531,33 @@ void vocab_transform(const VocabTree& V, const uint8_t* desc, int n, int levelsu
   }
 }
 
+int vocab_fold(const int* wordId, const int* nodeId, const double* weight, int n, uint32_t* bowIds, double* bowValues,
+               uint32_t* fvNodeIds, int* fvStart, uint32_t* fvIndices, int* nnodesOut) {
+  std::map<unsigned, double> v;                       // BowVector
+  std::map<unsigned, std::vector<unsigned>> fv;       // FeatureVector
+  for (int i = 0; i < n; i++) {
+    const double w = weight[i];
+    if (w > 0) {  // not stopped
+      auto vit = v.lower_bound((unsigned)wordId[i]);  // BowVector::addWeight
+      if (vit != v.end() && !(v.key_comp()((unsigned)wordId[i], vit->first))) vit->second += w;
+      else v.insert(vit, std::make_pair((unsigned)wordId[i], w));
+      fv[(unsigned)nodeId[i]].push_back((unsigned)i); // FeatureVector::addFeature
+    }
+  }
+  double norm = 0.0;                                   // BowVector::normalize(L1)
+  for (auto& kv : v) norm += std::fabs(kv.second);
+  if (norm > 0.0) for (auto& kv : v) kv.second /= norm;
+  int k = 0;
+  for (auto& kv : v) { bowIds[k] = kv.first; bowValues[k] = kv.second; k++; }
+  int nn = 0, pos = 0;
+  fvStart[0] = 0;
+  for (auto& kv : fv) {
+    fvNodeIds[nn] = kv.first;
+    for (unsigned f : kv.second) fvIndices[pos++] = f;
+    fvStart[++nn] = pos;
+  }
+  *nnodesOut = nn;
+  return k;
+}
+
 }  // namespace oro

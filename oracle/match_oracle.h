@@ -21,6 +21,7 @@
 // before entering the search loop.  Parity status: unpinned by the reference (it has no tests), see orb_oracle.h.
 #pragma once
 #include <cstdint>
+#include <map>
 #include <vector>
 
 #include "orb_oracle.h"
@@ -135,6 +136,11 @@ struct VocabTree {
   const int* nodeWordId = nullptr;     // -1 for inner nodes
 };
 // TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup), TemplatedVocabulary.h:1218-1259, for n features.
+// The folding of per-feature (word, weight, node) into BowVector / FeatureVector for TF_IDF weighting + L1 norm (ORBvoc's
+// settings), TemplatedVocabulary.h:1145-1195, BowVector.cpp:34-84, FeatureVector.cpp:28-42.  Outputs: sorted word ids + values,
+// and the FeatureVector as CSR.  Returns the number of words; nnodesOut = number of FeatureVector nodes.
+int vocab_fold(const int* wordId, const int* nodeId, const double* weight, int n, uint32_t* bowIds, double* bowValues,
+               uint32_t* fvNodeIds, int* fvStart, uint32_t* fvIndices, int* nnodesOut);
 void vocab_transform(const VocabTree& V, const uint8_t* desc, int n, int levelsup, int* wordId, int* nodeId, double* weight);
 
 }  // namespace oro

@@ -198,6 +198,10 @@ void oro_vocab_transform(int nnodes, int L, const int* childStart, const int* ch
   V.nodeWeight = nodeWeight; V.nodeWordId = nodeWordId;
   vocab_transform(V, desc, n, levelsup, wordId, nodeId, weight);
 }
+int oro_vocab_fold(const int* wordId, const int* nodeId, const double* weight, int n, uint32_t* bowIds, double* bowValues,
+                   uint32_t* fvNodeIds, int* fvStart, uint32_t* fvIndices, int* nnodesOut) {
+  return vocab_fold(wordId, nodeId, weight, n, bowIds, bowValues, fvNodeIds, fvStart, fvIndices, nnodesOut);
+}
 void oro_three_maxima(const int* hist, int L, int* ind3) {
   int a = -1, b = -1, c = -1;
   compute_three_maxima(hist, L, a, b, c);

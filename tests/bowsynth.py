@@ -36,3 +36,44 @@ def triangulation_geometry(w, h, seed):
     F += rng.normal(0, 2e-4, (3, 3)) * np.array([[1e-3, 1e-3, 1], [1e-3, 1e-3, 1], [1, 1, 1]])
     ep = (float(w) * 0.3 + float(rng.uniform(-5, 5)), float(h) * 0.5 + float(rng.uniform(-5, 5)))
     return F.astype(np.float32), ep
+
+
+def vocabulary(k, L, seed, ragged=True):
+    """A seeded random k-ary vocabulary tree of depth L, flattened like DBoW2's m_nodes (TemplatedVocabulary.h): node 0 = root;
+    children get their ids in breadth-first creation order but are *stored* in a shuffled order per node (ids need not be
+    contiguous or sorted in DBoW2 files); with ragged=True some inner nodes have fewer children and some branches stop early
+    (leaves above level L), as k-means on few descriptors produces.  Child descriptors are bit-flipped copies of the parent's so
+    that the descent is discriminative; a few words get weight 0 (stopped words)."""
+    rng = np.random.default_rng(3000 + seed)
+    desc = [rng.integers(0, 256, 32, dtype=np.uint8)]
+    children = [[]]
+    level = [0]
+    frontier = [0]
+    for l in range(1, L + 1):
+        nxt = []
+        for p in frontier:
+            if ragged and l > 1 and rng.uniform() < 0.05:
+                continue                      # early leaf
+            kk = k if not ragged else int(rng.integers(max(2, k - 3), k + 1))
+            for _ in range(kk):
+                d = np.unpackbits(desc[p]).copy()
+                flip = rng.choice(256, size=max(4, 96 >> l), replace=False)
+                d[flip] ^= 1
+                desc.append(np.packbits(d)); children.append([]); level.append(l)
+                children[p].append(len(desc) - 1)
+                nxt.append(len(desc) - 1)
+            rng.shuffle(children[p])
+        frontier = nxt
+    n = len(desc)
+    child_start = np.zeros(n + 1, np.int32)
+    child_ids = []
+    for i in range(n):
+        child_ids.extend(children[i]); child_start[i + 1] = len(child_ids)
+    word_id = np.full(n, -1, np.int32)
+    leaves = [i for i in range(n) if not children[i]]
+    word_id[leaves] = np.arange(len(leaves))
+    weight = np.zeros(n, np.float64)
+    weight[leaves] = rng.uniform(0.5, 9.0, len(leaves))
+    weight[rng.choice(leaves, size=max(1, len(leaves) // 50), replace=False)] = 0.0
+    return dict(L=L, child_start=child_start, child_ids=np.array(child_ids, np.int32), node_desc=np.stack(desc),
+                node_weight=weight, node_word_id=word_id, level=np.array(level, np.int32))

@@ -160,3 +160,53 @@ def test_search_window_best_is_gated_argmin(oracle, synth):
                 if dist < best:
                     best, bidx = dist, j
             assert (bidx, best) == (int(bi[i]), int(bd[i]))
+
+
+def test_distinctive_descriptors_matches_numpy(oracle):
+    """src/MapPoint.cc:385-428 restated with numpy sorting"""
+    rng = np.random.default_rng(3)
+    counts = np.array([0, 1, 2, 3, 8, 33, 64, 5], np.int32)
+    start = np.concatenate([[0], np.cumsum(counts)]).astype(np.int32)
+    desc = rng.integers(0, 256, (start[-1], 32), dtype=np.uint8)
+    desc[20:30] = desc[20]   # ties
+    bi, bm = oracle.distinctive_descriptors(desc, start)
+    for p, n in enumerate(counts):
+        if n == 0:
+            assert bi[p] == -1
+            continue
+        d = desc[start[p]:start[p + 1]]
+        D = np.unpackbits(d[:, None, :] ^ d[None, :, :], axis=2).sum(axis=2)
+        med = np.sort(D, axis=1)[:, int(0.5 * (n - 1))]
+        assert bi[p] == int(np.argmin(med)) and bm[p] == int(med.min())
+
+
+def test_vocab_transform_matches_python_descent(oracle):
+    """Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1218-1259 restated as a Python loop"""
+    from bowsynth import vocabulary
+    voc = vocabulary(5, 3, 2, True)
+    rng = np.random.default_rng(4)
+    desc = np.concatenate([rng.integers(0, 256, (60, 32), dtype=np.uint8), voc["node_desc"][5:25]])
+    for levelsup in (0, 1, 2, 5):
+        w, nid, wt = oracle.vocab_transform(voc, desc, levelsup)
+        for f in range(len(desc)):
+            node, lvl, n_at = 0, 0, 0
+            while voc["child_start"][node + 1] > voc["child_start"][node]:
+                lvl += 1
+                ch = voc["child_ids"][voc["child_start"][node]:voc["child_start"][node + 1]]
+                dist = [_ham(desc[f], voc["node_desc"][c]) for c in ch]
+                node = int(ch[int(np.argmin(dist))])      # argmin = first minimum, like the strict '<' of the reference
+                if lvl == voc["L"] - levelsup:
+                    n_at = node
+            assert (w[f], nid[f], wt[f]) == (voc["node_word_id"][node], n_at, voc["node_weight"][node])
+    # fold: TF-IDF sums in feature order, L1 over ascending word ids
+    w, nid, wt = oracle.vocab_transform(voc, desc, 1)
+    ids, vals, fv = oracle.vocab_fold(w, nid, wt)
+    acc = {}
+    for f in range(len(desc)):
+        if wt[f] > 0:
+            acc[int(w[f])] = acc.get(int(w[f]), 0.0) + float(wt[f])
+    norm = 0.0
+    for k in sorted(acc):
+        norm += abs(acc[k])
+    assert list(ids) == sorted(acc) and [acc[k] / norm for k in sorted(acc)] == list(vals)
+    assert sorted(fv[2].tolist()) == [f for f in range(len(desc)) if wt[f] > 0]
