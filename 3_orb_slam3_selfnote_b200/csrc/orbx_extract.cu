@@ -67,7 +67,11 @@ static void free_geom(orbx_extractor* h) {
 }
 
 // Build level sizes, cell grids, quadtree roots, tile tables and the lookup tables for one image size.
+std::recursive_mutex& orbx::setup_mutex() { static std::recursive_mutex m; return m; }
+
 int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
+  if (h->haveGeom && h->g.width == width && h->g.height == height) return ORBX_OK;   // steady state: no lock
+  std::lock_guard<std::recursive_mutex> setupLock(setup_mutex());
   if (h->haveGeom && h->g.width == width && h->g.height == height) return ORBX_OK;
   if (h->haveGeom) free_geom(h);
   h->geomEpoch++;

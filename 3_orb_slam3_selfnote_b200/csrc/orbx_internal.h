@@ -3,12 +3,17 @@
 #include <cuda_runtime.h>
 #include <stdarg.h>
 
+#include <mutex>
 #include <vector>
 
 #include "geom.h"
 
 namespace orbx {
 void set_error(const char* fmt, ...);
+// Process-wide lock around the rare host-side set-up sections of every handle (allocation / free, function attributes,
+// lookup-table uploads on the NULL stream, CUDA graph capture): several host threads may drive their own handles concurrently
+// (include/orbx.h), and a capture must not overlap another handle's allocation phase.  The steady state never takes it.
+std::recursive_mutex& setup_mutex();
 
 #define CK(call)                                                                                         \
   do {                                                                                                   \

@@ -59,6 +59,7 @@ struct ArenaPlan {  // two-phase bump allocation: plan sizes, ensure capacity, t
 
 int arena_ensure(orbx_matcher* m, size_t bytes) {
   if (bytes <= m->arenaCap) return ORBX_OK;
+  std::lock_guard<std::recursive_mutex> setupLock(setup_mutex());
   CK(cudaStreamSynchronize(m->stream));
   if (m->arena) CK(cudaFree(m->arena));
   m->arena = nullptr;
@@ -781,6 +782,7 @@ int orbx_knn2(orbx_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int n
 
 // Allocations of the stereo stage for the two extractors' geometry (never called while a stream is capturing).
 static int stereo_prepare(orbx_matcher* m, orbx_extractor* exL, orbx_extractor* exR) {
+  std::lock_guard<std::recursive_mutex> setupLock(setup_mutex());
   const Geom& g = exL->g;
   const int nfCap = std::max(exL->p.max_batch, exR->p.max_batch);
   const size_t half = (size_t)nfCap * g.kpStride;
@@ -927,6 +929,7 @@ int orbx_stereo_frames_host(orbx_matcher* m, orbx_extractor* exL, orbx_extractor
       if (!hit) { ci = m->chunkGraphNext[si]; m->chunkGraphNext[si] = (ci + 1) & 3; }
       orbx_matcher::ChunkGraph& cg = m->chunkGraph[si][ci];
       if (!hit) {
+        std::lock_guard<std::recursive_mutex> setupLock(setup_mutex());
         cg.reset();
         auto capture = [&](cudaStream_t cs, cudaGraphExec_t* out, auto&& body) -> int {
           cudaGraph_t graph = nullptr;
@@ -969,8 +972,10 @@ int orbx_stereo_frames_host(orbx_matcher* m, orbx_extractor* exL, orbx_extractor
       CK(cudaGraphLaunch(cg.execL, st));
       tmark(st);
       CK(cudaStreamWaitEvent(st, m->evJoin[si], 0));
-      CK(cudaEventRecord(m->evInFree[si], st));
       CK(cudaGraphLaunch(cg.execS, st));
+      // the staged images are level 0 of both pyramids, which the SAD refinement still reads (Frame.cc:998-1017): the slot's
+      // input buffers are free only after the stereo kernels
+      CK(cudaEventRecord(m->evInFree[si], st));
       tmark(st);
     }
     orbx_keypoint* kd[2] = {kpsL, kpsR}; uint8_t* dd[2] = {descL, descR}; int* cd[2] = {countsL, countsR};

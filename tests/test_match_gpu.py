@@ -268,3 +268,41 @@ def test_host_buffers_and_chunked_pipeline(orbx, oracle, synth):
     for b in (hl, hr):
         b.close()
     exL.close(); exR.close(); mt.close()
+
+
+def test_concurrent_host_threads_on_independent_handles(orbx, synth):
+    """Handles are independent (include/orbx.h): several host threads, each with its own extractor / matcher handles, run the
+    host-buffer pipeline at once -- including their first calls (geometry set-up, allocation, graph capture) -- and every call
+    returns exactly what a single thread gets."""
+    import threading
+    W, H, n = 752, 480, 12
+    left = np.stack([synth.frame(W, H, 77, i % 4, False) for i in range(n)])
+    right = np.stack([synth.frame(W, H, 77, i % 4, True) for i in range(n)])
+    mbf = np.float32(47.90639384423901); mb = np.float32(mbf / np.float32(435.2046959714599))
+    exL, exR, mt = orbx.ORBextractor(1200, max_batch=4), orbx.ORBextractor(1200, max_batch=4), orbx.ORBmatcher()
+    ref = mt.stereo_frames_host(exL, exR, left, right, mb, mbf)
+    exL.close(); exR.close(); mt.close()
+    errs = []
+
+    def worker(k):
+        try:
+            a, b, m = orbx.ORBextractor(1200, max_batch=4), orbx.ORBextractor(1200, max_batch=4), orbx.ORBmatcher()
+            for rep in range(4):
+                o = m.stereo_frames_host(a, b, left, right, mb, mbf)
+                for key in ("countsL", "countsR"):
+                    assert np.array_equal(o[key], ref[key]), (k, rep, key)
+                for i in range(n):
+                    c = int(ref["countsL"][i])
+                    assert o["kpsL"][i, :c].tobytes() == ref["kpsL"][i, :c].tobytes()
+                    assert np.array_equal(o["descL"][i, :c], ref["descL"][i, :c])
+                    assert o["uRight"][i, :c].tobytes() == ref["uRight"][i, :c].tobytes()
+            a.close(); b.close(); m.close()
+        except Exception as e:   # noqa: BLE001
+            errs.append(repr(e))
+
+    ths = [threading.Thread(target=worker, args=(k,)) for k in range(4)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    assert not errs, errs
