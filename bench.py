@@ -19,7 +19,9 @@ JSON keys beyond the base contract:
                 duration vs the measured HBM peak (MEASURED_PEAKS.json); DESIGN.md states the per-kernel byte model
   cpu_baseline  the CPU oracle (port of the reference's ORBextractor + ComputeStereoMatches; the reference itself needs
                 OpenCV 3.4 C++ and cannot be compiled in this image) on the box's host cores, bounded sample
-  extra         mono extraction-only throughput (752x480, nFeatures 1000: the shape the north-star target is quoted on)
+  extra         mono extraction-only throughput (752x480, nFeatures 1000: the shape the north-star target is quoted on) and
+                informational device-resident runs of the other BASELINE.json configs (HD shapes, TUM-VI shape with
+                SearchByProjection, the all-pairs 2-NN tile kernel against the popc roofline); --no-extras skips them
   --impl reference  runs only the CPU arm, one bounded sample per step, same line with impl=reference
 """
 import argparse
@@ -160,6 +162,89 @@ def run_reference(args):
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+def extra_configs(orbx, synth, torch, stream, local, steps):
+    """Informational device-resident runs of the other BASELINE.json configs on one GPU (the parity of each is covered by tests/):
+    config 2 (TUM-VI shaped 512x512 mono, 1500 features, extraction + SearchByProjection against 5000 projected map points per
+    frame), config 3 (1280x720 and 1920x1080, 2000 features, 256 frames per batch) and the tile kernel of config 4's all-pairs
+    keyframe 2-NN sweep (descriptor pairs/s against the popc roofline of SURVEY.md section 8-d)."""
+    sh = stream.cuda_stream
+    out = {}
+
+    def timed(fn, reps):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(reps):
+            fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / 1e3 / reps
+
+    def tiled(w, h, n, distinct, seed):
+        fr = synth.frames(w, h, seed, range(distinct), False)
+        return torch.from_numpy(np.concatenate([fr] * ((n + distinct - 1) // distinct))[:n]).cuda()
+
+    # HD shapes, 2000 features, 256 frames per batch
+    for (w, h, name) in ((1280, 720, "hd720"), (1920, 1080, "hd1080")):
+        n = 256
+        dev = tiled(w, h, n, 4, 3000)
+        ex = orbx.ORBextractor(2000, max_batch=n, device=local)
+        sec = timed(lambda: ex.extract_batch_device(dev.data_ptr(), n, w, h, w, w * h, (0, 0), sh), steps)
+        counts = ex.results_host(n)[0]
+        out["%s_extract_nfeat2000_batch256_frames_per_s_per_gpu" % name] = n / sec
+        out["%s_keypoints_per_frame" % name] = float(counts.mean())
+        ex.close()
+        del dev
+    # TUM-VI shape: extraction + windowed matching against 5000 projected map points per frame (host map-point arrays in, matches out)
+    w = h = 512
+    n, nmp = 64, 5000
+    dev = tiled(w, h, n, 8, 4000)
+    ex = orbx.ORBextractor(1500, max_batch=n, device=local)
+    mt = orbx.ORBmatcher(0.8, device=local)
+    ex.extract_batch_device(dev.data_ptr(), n, w, h, w, w * h, (0, 0), sh)
+    torch.cuda.synchronize()
+    counts, _, kps, desc = ex.results_host(n)
+    rng = np.random.default_rng(7)
+    px = np.empty((n, nmp), np.float32); py = np.empty((n, nmp), np.float32); lv = np.empty((n, nmp), np.int32)
+    md = rng.integers(0, 256, (n, nmp, 32), dtype=np.uint8)
+    for f in range(n):   # map points = this frame's own keypoints shifted by a pixel + uniformly random padding (SURVEY.md section 8-d)
+        c = int(counts[f])
+        px[f, :c] = kps[f, :c]["x"] + 1.0; py[f, :c] = kps[f, :c]["y"] - 1.0; lv[f, :c] = kps[f, :c]["octave"]; md[f, :c] = desc[f, :c]
+        px[f, c:] = rng.uniform(0, w, nmp - c); py[f, c:] = rng.uniform(0, h, nmp - c); lv[f, c:] = rng.integers(0, 8, nmp - c)
+    inv = np.ones((n, nmp), np.uint8)
+    vc = np.where(np.arange(nmp) % 2 == 0, 1.0, 0.9).astype(np.float32)[None].repeat(n, 0)
+    nm_holder = {}
+
+    def tum_step():
+        ex.extract_batch_device(dev.data_ptr(), n, w, h, w, w * h, (0, 0), sh)
+        nm_holder["nm"] = mt.SearchByProjectionBatch(ex, n, inv, px, py, lv, vc, md, 1.0)[0]
+
+    ex._last_shape = (h, w)
+    sec = timed(tum_step, max(2, steps // 2))
+    out["tumvi512_extract_nfeat1500+SearchByProjection_5000mp_frames_per_s_per_gpu"] = n / sec
+    out["tumvi512_matches_per_frame"] = float(np.mean(nm_holder["nm"]))
+    ex.close(); mt.close()
+    # all-pairs tile kernel: 16384 queries against 262144 train descriptors, running (best, second) keys
+    nq, nt = 16384, 262144
+    q = torch.randint(0, 256, (nq, 32), dtype=torch.uint8, device="cuda"); t = torch.randint(0, 256, (nt, 32), dtype=torch.uint8, device="cuda")
+    k0 = torch.empty(nq, dtype=torch.int64, device="cuda"); k1 = torch.empty(nq, dtype=torch.int64, device="cuda")
+    mk = orbx.ORBmatcher(device=local)
+    sec = timed(lambda: mk.knn2_chunk_device(q.data_ptr(), nq, t.data_ptr(), nt, 0, 0, k0.data_ptr(), k1.data_ptr(), 1, sh), steps)
+    pairs = nq * nt / sec
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fjs:
+            smhz = float(json.load(fjs).get("sm_max_mhz", 1965.0))
+    except Exception:
+        smhz = 1965.0
+    popc_roof = 16 * 148 * smhz * 1e6 / 8      # 16 popc/clk/SM, 8 popc per 256-bit pair (SURVEY.md section 8-d)
+    out["allpairs_knn2_tile_pairs_per_s_per_gpu"] = pairs
+    out["allpairs_knn2_frac_of_popc_roofline"] = pairs / popc_roof
+    mk.close()
+    return out
 
 
 STEREO_KERNELS = 4   # k_stereo_rowtable, k_stereo_hamming2, k_stereo_sad, k_stereo_median
@@ -380,6 +465,9 @@ def run_orbx(args):
     torch.cuda.synchronize()
     mono_fps = B * args.steps / (m0.elapsed_time(m1) / 1e3)
 
+    extras = {"mono_extract_752x480_nfeat1000_frames_per_s_per_gpu": mono_fps}
+    if rank == 0 and not args.no_extras:
+        extras.update(extra_configs(orbx, synth, torch, stream, local, max(3, min(args.steps, 10))))
     if rank == 0:
         cores = os.cpu_count() or 1
         ncpu = max(cores, min(2 * cores, 128))
@@ -405,7 +493,7 @@ def run_orbx(args):
                                  % (2 * B * (W * H + 2 * LEVEL_PIXELS) / 1e6),
                            "sharding": "stereo frames partitioned by rank, no collective on the data path"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
-                "extra": {"mono_extract_752x480_nfeat1000_frames_per_s_per_gpu": mono_fps}}
+                "extra": extras}
         print(json.dumps(line), flush=True)
     for w in workers:
         for o in (w.eL, w.eR, w.em, w.okL, w.okR, w.odL, w.odR, w.ocL, w.ocR, w.ouR, w.odp):
@@ -425,6 +513,7 @@ def main():
     ap.add_argument("--batch", type=int, default=256, help="stereo frames per step per GPU")
     ap.add_argument("--e2e-chunks", type=int, default=4, help="chunks per orbx_stereo_frames_host call (copy/compute overlap)")
     ap.add_argument("--e2e-workers", type=int, default=2, help="host threads issuing the blocking e2e call on their own handles")
+    ap.add_argument("--no-extras", action="store_true", help="skip the informational runs of BASELINE.json configs 2-4")
     ap.add_argument("--skip-cpu", action="store_true", help="development only: skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":
