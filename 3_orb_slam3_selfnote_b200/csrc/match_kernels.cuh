@@ -9,8 +9,10 @@
 // with shuffles on packed (distance, traversal order, index) keys so that "first minimum wins" ties resolve exactly as the
 // reference's sequential loops do.  The searches whose result depends on earlier queries (keypoints
 // claimed by earlier map points) are split in two: a fully parallel candidate/distance pass, then one warp per frame
-// that replays the reference's order over the precomputed lists.
+// that replays the reference's order over the precomputed lists (k_resolve_mappoints / _window / _init, k_bow_resolve) or --
+// the default -- a parallel fixed-point iteration that reaches the same result (k_resolve_par, k_bow_resolve_par).
 #pragma once
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <limits.h>
 
@@ -272,6 +274,8 @@ struct ResolveArgs {        // one per frame
   int* kpMp;                // in/out, F.mvpMapPoints as indices (-1 empty, -2 blocking, -3 non-blocking pre-existing)
   int* assigned;            // scratch [nq] (k_resolve_best: best index per query)
   int* bestDist;            // k_resolve_best only: best distance per query
+  int* blk[2];              // parallel resolve: per keypoint, smallest query index whose (blocking) claim holds it ([n] each)
+  int* chg;                 // parallel resolve: [2] "a choice changed" flags
   int* nmatches;            // out
   float nnratio;
   int distTh;
@@ -319,6 +323,123 @@ __global__ void __launch_bounds__(32) k_resolve_mappoints(const GridFrame* frame
     }
   }
   if (lane == 0) *A.nmatches = nmatches;
+}
+
+// The same search as a parallel fixed point (default path).  The reference's loop is sequential only through the claims: map
+// point i cannot take a keypoint that an earlier map point j < i with observations already took.  Let choice[i] be the keypoint
+// map point i ends up with; choice[i] is a function of {choice[j] : j < i} alone, so the sequential result is the unique fixed
+// point of  choice <- F(choice), and iterating F from "no claims" reaches it after at most (longest dependency chain) + 1
+// rounds -- a handful in practice, because most windows do not compete.  One round is fully parallel: warp = map point, the
+// per-keypoint state is blk[k] = smallest index of an observed map point currently choosing k (atomicMin), and k is blocked for
+// i iff blk[k] < i.  A cluster of 8 CTAs works on one frame (128 warps), two cluster barriers per round.  Afterwards
+// kpMp[k] = the largest index that chose k (later map points overwrite earlier ones without observations, ORBmatcher.cc:89-91).
+constexpr int kParCluster = 8, kParThreads = 512;
+// mode 0: SearchByProjection(Frame&, vector<MapPoint*>&) (best / second with the level rule, TH_HIGH, ratio)
+// mode 1: the best-1 window searches (k_resolve_window's rule: distTh, anyMpBlocks, rotation histogram afterwards)
+__global__ void __cluster_dims__(kParCluster, 1, 1) __launch_bounds__(kParThreads)
+k_resolve_par(const GridFrame* frames, const QuerySet* sets, const ResolveArgs* args, int mode) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  const GridFrame F = frames[blockIdx.y];
+  const QuerySet Q = sets[blockIdx.y];
+  const ResolveArgs A = args[blockIdx.y];
+  const int lane = threadIdx.x & 31;
+  const int gthread = blockIdx.x * kParThreads + threadIdx.x, nthreads = kParCluster * kParThreads;
+  const int gwarp = gthread >> 5, nwarps = nthreads >> 5;
+  const bool anyBlocks = mode == 1 && A.anyMpBlocks;
+  auto obs = [&](int i) { return A.observed ? A.observed[i] != 0 : true; };
+  auto pre = [&](int k) {   // keypoints that block everybody before the call
+    const int s = A.kpMp[k];
+    const bool bl = anyBlocks ? (s != -1) : ((s == -2) || (s >= 0 && obs(s)));
+    return bl ? -1 : INT_MAX;
+  };
+  for (int k = gthread; k < F.n; k += nthreads) { A.blk[0][k] = pre(k); A.blk[1][k] = pre(k); }
+  for (int i = gthread; i < Q.nq; i += nthreads) A.assigned[i] = -1;
+  if (gthread < 2) A.chg[gthread] = 0;
+  if (gthread == 0) *A.nmatches = 0;
+  cluster.sync();
+  for (int it = 0; it <= Q.nq; it++) {
+    const int* cur = A.blk[it & 1];
+    int* nxt = A.blk[(it & 1) ^ 1];
+    bool changed = false;
+    for (int i = gwarp; i < Q.nq; i += nwarps) {
+      const int c = Q.qCnt[i];
+      int choice = -1;
+      if (c > 0) {
+        const unsigned long long* e = Q.entries + Q.qOff[i];
+        unsigned long long k1 = kKeyNone, k2 = kKeyNone;
+        for (int j = lane; j < c; j += 32) {
+          const unsigned long long k = e[j];
+          if (!(__ldcg(cur + key_idx(k)) < i)) top2_insert(k, k1, k2);
+        }
+        top2_warp(k1, k2);
+        if (k1 != kKeyNone) {
+          const int bestDist = key_dist(k1);
+          if (mode == 0) {
+            const int bestLevel = key_oct(k1);
+            const int bestDist2 = (k2 == kKeyNone) ? 256 : key_dist(k2), bestLevel2 = (k2 == kKeyNone) ? -1 : key_oct(k2);
+            if (bestDist <= 100) {  // TH_HIGH
+              const float lim = __fmul_rn(A.nnratio, (float)bestDist2);
+              if (!(bestLevel == bestLevel2 && (float)bestDist > lim)) choice = key_idx(k1);
+            }
+          } else if (bestDist <= A.distTh) choice = key_idx(k1);
+        }
+      }
+      if (lane == 0) {
+        if (choice != A.assigned[i]) { A.assigned[i] = choice; changed = true; }
+        if (choice >= 0 && (anyBlocks || obs(i))) atomicMin(nxt + choice, i);
+      }
+    }
+    if (changed) atomicExch(A.chg + (it & 1), 1);
+    cluster.sync();
+    const int any = __ldcg(A.chg + (it & 1));
+    // nobody reads `cur` any more: it becomes the target of the next round
+    for (int k = gthread; k < F.n; k += nthreads) A.blk[it & 1][k] = pre(k);
+    if (gthread == 0) A.chg[(it & 1) ^ 1] = 0;
+    cluster.sync();
+    if (!any) break;
+  }
+  // the fixed point is reached.  blk[0] becomes "largest index that chose k", blk[1][0..29] the rotation histogram
+  for (int k = gthread; k < F.n; k += nthreads) A.blk[0][k] = -1;
+  if (gthread < 32) A.blk[1][gthread] = 0;
+  cluster.sync();
+  const bool ori = mode == 1 && A.checkOrientation;
+  int mine = 0;
+  for (int i = gthread; i < Q.nq; i += nthreads) {
+    const int ch = __ldcg(A.assigned + i);
+    if (ch >= 0) {
+      atomicMax(A.blk[0] + ch, i);
+      mine++;
+      if (ori) {
+        const int bin = rot_bin(A.angle[i], F.kps[ch].angle);
+        atomicAdd(A.blk[1] + bin, 1);
+        A.assigned[i] = ch | (bin << 24);
+      }
+    }
+  }
+  cluster.sync();
+  for (int k = gthread; k < F.n; k += nthreads) {
+    const int w = __ldcg(A.blk[0] + k);
+    if (w >= 0) A.kpMp[k] = w;
+  }
+  if (ori) {
+    cluster.sync();   // winners are in place before the histogram filter clears some of them
+    int hist[30];
+#pragma unroll
+    for (int bI = 0; bI < 30; bI++) hist[bI] = __ldcg(A.blk[1] + bI);
+    int i1, i2, i3;
+    three_maxima(hist, 30, i1, i2, i3);
+    for (int i = gthread; i < Q.nq; i += nthreads) {
+      const int a = A.assigned[i];   // written by this thread above
+      if (a >= 0) {
+        const int bin = a >> 24;
+        if (bin != i1 && bin != i2 && bin != i3) { A.kpMp[a & 0xffffff] = -1; mine--; }
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+  if (lane == 0 && mine) atomicAdd(A.nmatches, mine);
 }
 
 // SearchByProjection(Frame&, const Frame&, ...) / (Frame&, KeyFrame*, ...): best-1 window search with the rotation histogram.
@@ -832,6 +953,7 @@ struct BowArgs {
   int* matches12;               // [n1]
   int* nmatches;
   int maxDist; float nnratio; int checkOrientation;
+  int* blk[2]; int* chg; int* choice;   // parallel resolve scratch: [n2] x 2, [2], [nwork]
   // triangulation gates (ORBmatcher.cc:1087-1146, Pinhole.cpp:150-164)
   float F12[9]; float epx, epy; const float* scaleFactors2; const float* levelSigma2; int coarse;
 };
@@ -887,6 +1009,61 @@ __global__ void __launch_bounds__(32) k_bow_resolve(const __grid_constant__ BowA
       if (lane == 0) { A.matches12[idx1] = bestIdx2; claimed[bestIdx2] = 1; }
       __syncwarp();
     }
+  }
+}
+
+// The same replay as a parallel fixed point (see k_resolve_par): a side-2 feature claimed by work item w blocks every later
+// work item; choice[w] depends only on the choices of earlier work items, so iterating from "nothing claimed" converges to
+// the sequential result.  Cluster of 8 CTAs per problem, warp = work item.
+__global__ void __cluster_dims__(kParCluster, 1, 1) __launch_bounds__(kParThreads) k_bow_resolve_par(const __grid_constant__ BowArgs A) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  const int lane = threadIdx.x & 31;
+  const int gthread = blockIdx.x * kParThreads + threadIdx.x, nthreads = kParCluster * kParThreads;
+  const int gwarp = gthread >> 5, nwarps = nthreads >> 5;
+  for (int k = gthread; k < A.s2.n; k += nthreads) { A.blk[0][k] = INT_MAX; A.blk[1][k] = INT_MAX; }
+  for (int k = gthread; k < A.s1.n; k += nthreads) A.matches12[k] = -1;
+  for (int w = gthread; w < A.nwork; w += nthreads) A.choice[w] = -1;
+  if (gthread < 2) A.chg[gthread] = 0;
+  cluster.sync();
+  for (int it = 0; it <= A.nwork; it++) {
+    const int* cur = A.blk[it & 1];
+    int* nxt = A.blk[(it & 1) ^ 1];
+    bool changed = false;
+    for (int w = gwarp; w < A.nwork; w += nwarps) {
+      const BowWork W = A.work[w];
+      const int idx1 = (int)A.s1.indices[W.p1];
+      int choice = -1;
+      if ((unsigned)idx1 < (unsigned)A.s1.n && (!A.s1.elig || A.s1.elig[idx1])) {
+        unsigned long long k1 = kKeyNone, k2 = kKeyNone;
+        const int c = W.b1 - W.b0;
+        for (int j = lane; j < c; j += 32) {
+          const unsigned long long k = A.entries[W.off + j];
+          if (k != kKeyNone && !(__ldcg(cur + (int)(k & 0xfffffu)) < w)) top2_insert(k, k1, k2);
+        }
+        top2_warp(k1, k2);
+        if (k1 != kKeyNone) {
+          const int bestDist1 = (int)(k1 >> 40);
+          const int bestDist2 = (k2 == kKeyNone) ? 256 : (int)(k2 >> 40);
+          if (bestDist1 <= A.maxDist && (float)bestDist1 < __fmul_rn(A.nnratio, (float)bestDist2)) choice = (int)(k1 & 0xfffffu);
+        }
+      }
+      if (lane == 0) {
+        if (choice != A.choice[w]) { A.choice[w] = choice; changed = true; }
+        if (choice >= 0) atomicMin(nxt + choice, w);
+      }
+    }
+    if (changed) atomicExch(A.chg + (it & 1), 1);
+    cluster.sync();
+    const int any = __ldcg(A.chg + (it & 1));
+    for (int k = gthread; k < A.s2.n; k += nthreads) A.blk[it & 1][k] = INT_MAX;
+    if (gthread == 0) A.chg[(it & 1) ^ 1] = 0;
+    cluster.sync();
+    if (!any) break;
+  }
+  for (int w = gthread; w < A.nwork; w += nthreads) {
+    const int ch = __ldcg(A.choice + w);
+    if (ch >= 0) A.matches12[(int)A.s1.indices[A.work[w].p1]] = ch;   // a feature sits in one node: one work item per idx1
   }
 }
 

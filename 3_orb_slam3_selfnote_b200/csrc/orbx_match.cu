@@ -42,6 +42,7 @@ struct orbx_matcher {
   } chunkGraph[2][4];    // [slot][entry]: a call's chunks come in up to three sizes (ramped first, full, tail)
   int chunkGraphNext[2] = {0, 0};
   bool noGraph = false;    // ORBX_NO_GRAPH=1
+  bool resolveSeq = false; // ORBX_RESOLVE_SEQ=1: one-warp sequential replay instead of the parallel fixed point (A/B only)
   // orbx_stereo_frames_host pipeline: one upload stream feeds both slots in issue order; per slot: images uploaded (left, right),
   // right branch joined, input buffers free again (both extractions done), slot's downloads done
   cudaStream_t upStream = nullptr;
@@ -121,7 +122,7 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
   // ---- plan the arena
   ArenaPlan plan;
   struct Off { size_t kps, desc, uRight, cellStart, cellItems, valid, x, y, r, xr, minL, maxL, qdesc, qOff, qCnt, entries, cursor,
-               observed, angle, kpMp, assigned, nmatches, kps1, prevMatched, m12, m21, mdist, bins, sigma; };
+               observed, angle, kpMp, assigned, nmatches, kps1, prevMatched, m12, m21, mdist, bins, sigma, blk0, blk1, chg; };
   std::vector<Off> off(nj);
   std::vector<int> entryCap(nj);
   for (int j = 0; j < nj; j++) {
@@ -151,6 +152,7 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
     o.kpMp = J.kpMp ? plan.add((size_t)std::max(n, 1) * 4) : (size_t)-1;
     o.assigned = plan.add((size_t)std::max(nq, 1) * 4);
     o.nmatches = plan.add(4);
+    o.blk0 = plan.add((size_t)std::max(n, 32) * 4); o.blk1 = plan.add((size_t)std::max(n, 32) * 4); o.chg = plan.add(8);
     if (kind == RESOLVE_INIT) {
       o.kps1 = plan.add((size_t)std::max(nq, 1) * sizeof(orbx_keypoint));
       o.prevMatched = plan.add((size_t)std::max(nq, 1) * 8);
@@ -218,6 +220,7 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
       A.angle = J.angle ? at<float>(m, o.angle) : nullptr;
       A.kpMp = at<int>(m, o.kpMp); A.assigned = at<int>(m, o.assigned); A.nmatches = at<int>(m, o.nmatches);
       A.nnratio = J.nnratio; A.distTh = J.distTh; A.anyMpBlocks = J.anyMpBlocks; A.checkOrientation = J.checkOrientation;
+      A.blk[0] = at<int>(m, o.blk0); A.blk[1] = at<int>(m, o.blk1); A.chg = at<int>(m, o.chg);
     } else if (kind == RESOLVE_BEST) {
       ResolveArgs& A = rargs[j];
       A = ResolveArgs{};
@@ -240,8 +243,13 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
   const QuerySet* dSets = at<QuerySet>(m, oSets);
   k_build_grid<<<nj, 256, 0, st>>>(dFrames);
   if (maxQ > 0) k_window_candidates<<<dim3((maxQ + 7) / 8, nj), 256, 0, st>>>(dFrames, dSets, m->dStatus);
-  if (kind == RESOLVE_MAPPOINTS) k_resolve_mappoints<<<nj, 32, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs));
-  else if (kind == RESOLVE_WINDOW) k_resolve_window<<<nj, 32, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs));
+  if (kind == RESOLVE_MAPPOINTS) {
+    if (m->resolveSeq) k_resolve_mappoints<<<nj, 32, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs));
+    else k_resolve_par<<<dim3(kParCluster, nj), kParThreads, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs), 0);
+  } else if (kind == RESOLVE_WINDOW) {
+    if (m->resolveSeq) k_resolve_window<<<nj, 32, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs));
+    else k_resolve_par<<<dim3(kParCluster, nj), kParThreads, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs), 1);
+  }
   else if (kind == RESOLVE_INIT) k_resolve_init<<<nj, 32, 0, st>>>(dFrames, dSets, at<InitArgs>(m, oArgs));
   else if (kind == RESOLVE_BEST && maxQ > 0) k_resolve_best<<<dim3((maxQ + 7) / 8, nj), 256, 0, st>>>(dSets, at<ResolveArgs>(m, oArgs));
   CK(cudaGetLastError());
@@ -313,6 +321,7 @@ int orbx_matcher_create(int device, orbx_matcher** out) {
   m->device = device;
   { const char* e = getenv("ORBX_STEREO_V1"); m->stereoV1 = e && e[0] == '1'; }
   { const char* e = getenv("ORBX_NO_GRAPH"); m->noGraph = e && e[0] == '1'; }
+  { const char* e = getenv("ORBX_RESOLVE_SEQ"); m->resolveSeq = e && e[0] == '1'; }
   bool evOk = true;
   for (int i = 0; i < 2; i++)
     for (cudaEvent_t* e : {&m->evUpL[i], &m->evUpR[i], &m->evJoin[i], &m->evInFree[i], &m->evSlotDone[i]})
@@ -502,7 +511,7 @@ int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches)
   if ((P.n1 > 0 && (!P.kps1 || !P.desc1)) || (P.n2 > 0 && (!P.kps2 || !P.desc2))) return ORBX_ERR_ARG;
   if (bow_check(P.fv1, P.n1) != ORBX_OK || bow_check(P.fv2, P.n2) != ORBX_OK) { set_error("bad feature vector (node ids must ascend)"); return ORBX_ERR_ARG; }
   if (P.n1 >= (1 << 20) || P.n2 >= (1 << 20)) { set_error("more than 2^20 features per keyframe is unsupported"); return ORBX_ERR_UNSUPPORTED; }
-  if (!P.triangulate && P.n2 > kMaxKpSmem) { set_error("more than %d features per frame is unsupported by the resolve kernel", kMaxKpSmem); return ORBX_ERR_UNSUPPORTED; }
+  if (!P.triangulate && m->resolveSeq && P.n2 > kMaxKpSmem) { set_error("more than %d features per frame is unsupported by the resolve kernel", kMaxKpSmem); return ORBX_ERR_UNSUPPORTED; }
   *nmatches = 0;
   for (int i = 0; i < P.n1; i++) matches12[i] = -1;
   if (P.n1 == 0 || P.n2 == 0) return ORBX_OK;
@@ -537,6 +546,7 @@ int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches)
   const size_t oW = plan.add((size_t)nw * sizeof(BowWork));
   const size_t oEnt = P.triangulate ? (size_t)-1 : plan.add((size_t)std::max<long long>(nEntries, 1) * 8);
   const size_t oM = plan.add((size_t)P.n1 * 4), oN = plan.add(4);
+  const size_t oB0 = plan.add((size_t)P.n2 * 4), oB1 = plan.add((size_t)P.n2 * 4), oChg = plan.add(8), oCh = plan.add((size_t)nw * 4);
   const size_t oSF = P.triangulate ? plan.add((size_t)P.nlevels * 4) : (size_t)-1, oLS = P.triangulate ? plan.add((size_t)P.nlevels * 4) : (size_t)-1;
   int rc = arena_ensure(m, plan.total);
   if (rc != ORBX_OK) return rc;
@@ -559,6 +569,7 @@ int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches)
   A.entries = P.triangulate ? nullptr : at<unsigned long long>(m, oEnt);
   A.matches12 = at<int>(m, oM); A.nmatches = at<int>(m, oN);
   A.maxDist = P.maxDist; A.nnratio = P.nnratio; A.checkOrientation = P.checkOrientation;
+  A.blk[0] = at<int>(m, oB0); A.blk[1] = at<int>(m, oB1); A.chg = at<int>(m, oChg); A.choice = at<int>(m, oCh);
   if (P.triangulate) {
     memcpy(A.F12, P.F12, sizeof(A.F12));
     A.epx = P.epx; A.epy = P.epy; A.scaleFactors2 = at<float>(m, oSF); A.levelSigma2 = at<float>(m, oLS); A.coarse = P.coarse;
@@ -566,7 +577,8 @@ int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches)
     k_bow_triangulate<<<(nw + 7) / 8, 256, 0, st>>>(A);
   } else {
     k_bow_distances<<<(nw + 7) / 8, 256, 0, st>>>(A);
-    k_bow_resolve<<<1, 32, 0, st>>>(A);
+    if (m->resolveSeq) k_bow_resolve<<<1, 32, 0, st>>>(A);
+    else k_bow_resolve_par<<<kParCluster, kParThreads, 0, st>>>(A);
   }
   k_bow_rotfilter<<<1, 256, 0, st>>>(A);
   CK(cudaGetLastError());

@@ -181,3 +181,40 @@ def test_search_by_projection_keyframe_scw(orbx, oracle, synth, frames, ratio_ha
     assert got_n == ref_n and np.array_equal(got, ref)
     assert ref_n > 200
     m.close()
+
+
+def test_parallel_resolve_on_long_claim_chains(orbx, oracle, synth, frames):
+    """The resolve kernels iterate a parallel fixed point instead of replaying the reference's loop (match_kernels.cuh,
+    k_resolve_par / k_bow_resolve_par).  Worst case for that scheme: many queries that compete for the same keypoints, so that
+    every claim depends on the one before (map points / source points / keyframe features repeated up to 12 times)."""
+    k, d = frames["a"]
+    kj, dj = frames["a_jit"]
+    rng = np.random.default_rng(21)
+    rep = rng.integers(1, 13, len(kj))
+    idx = np.repeat(np.arange(len(kj)), rep)
+    rng.shuffle(idx)
+    n = len(idx)
+    u = (kj["x"][idx] + rng.normal(0, 0.3, n)).astype(np.float32); v = (kj["y"][idx] + rng.normal(0, 0.3, n)).astype(np.float32)
+    lvl = kj["octave"][idx].astype(np.int32); desc = dj[idx]
+    observed = (rng.uniform(size=n) < 0.7).astype(np.uint8)
+    F = orbx.FrameView(k, d, frames["scale"], W, H)
+    # SearchByProjection(F, map points): ratio 1.0 so that most repeated points pass the ratio test and claim in turn
+    m = orbx.ORBmatcher(1.0, True)
+    ref = oracle.search_by_projection_mappoints(k, d, frames["scale"], W, H, np.ones(n, np.uint8), u, v, lvl, np.ones(n, np.float32), desc,
+                                                3.0, 1.0, observed=observed)
+    got = m.SearchByProjection(F, np.ones(n, np.uint8), u, v, lvl, np.ones(n, np.float32), desc, 3.0, observed=observed)
+    assert got[0] == ref[0] and np.array_equal(got[1], ref[1]) and ref[0] > 800
+    # window search (Frame / Frame rule and the any-map-point-blocks rule of Frame / KeyFrame)
+    ang = kj["angle"][idx]
+    for any_blocks in (False, True):
+        ref = oracle.search_by_projection_window(k, d, frames["scale"], W, H, np.ones(n, np.uint8), u, v, lvl, ang, desc, 7.0, 0, 100,
+                                                 any_blocks, True, observed=observed)
+        got = m.SearchByProjectionWindow(F, np.ones(n, np.uint8), u, v, lvl, ang, desc, 7.0, 0, 100, any_blocks, observed=observed)
+        assert got[0] == ref[0] and np.array_equal(got[1], ref[1]) and ref[0] > 300
+    # SearchByBoW: the keyframe side holds every feature several times, all in the same few nodes
+    k1, d1 = kj[idx], dj[idx]
+    fv1, fv2 = feature_vector(d1, 6, 2), feature_vector(d, 6, 2)
+    ref = oracle.search_by_bow(k1, d1, fv1, np.ones(n, np.uint8), k, d, fv2, None, 50, 1.0, True)
+    got = m.SearchByBoW(k1, d1, fv1, np.ones(n, np.uint8), k, d, fv2, None, 50)
+    assert got[0] == ref[0] and np.array_equal(got[1], ref[1]) and ref[0] > 100
+    m.close()
