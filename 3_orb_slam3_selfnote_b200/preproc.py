@@ -1,0 +1,120 @@
+"""ctypes mirror of the pre-processing entry points of include/orbx.h, named after the OpenCV calls
+the reference makes before ORBextractor::operator():
+
+    cvtColor(im, CV_{RGB,BGR,RGBA,BGRA}2GRAY)         src/Tracking.cc:989-1014, 1059-1073, 1121-1135
+    remap(im, M1, M2, INTER_LINEAR)                   Examples/Stereo/stereo_euroc.cc:117-118, 166-167
+    createCLAHE(3.0, (8, 8)).apply(im)                Examples/Monocular/mono_tum_vi.cc:101, 109
+
+Host arrays (numpy) in / out through ORBX_MEM_HOST; the *_device methods take raw device pointers and enqueue on a stream.
+No CPU fallback: everything runs in liborbx.so's kernels.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _check, _p, lib
+
+MEM_HOST, MEM_DEVICE = 0, 1
+GRAY_OCV346, GRAY_OCV4 = 0, 1
+COLOR_BGR2GRAY, COLOR_RGB2GRAY, COLOR_BGRA2GRAY, COLOR_RGBA2GRAY = "bgr", "rgb", "bgra", "rgba"
+_LL = C.c_longlong
+
+
+def _frames(a, ndim):
+    """(frames?, h, w[, c]) uint8 array -> contiguous batch + whether a batch axis was given."""
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    if a.ndim == ndim:
+        return a[None], False
+    if a.ndim != ndim + 1:
+        raise ValueError("expected %d or %d dimensions" % (ndim, ndim + 1))
+    return a, True
+
+
+class RemapTable:
+    def __init__(self, owner, mapx, mapy, src_size):
+        mapx = np.ascontiguousarray(mapx, np.float32)
+        mapy = np.ascontiguousarray(mapy, np.float32)
+        assert mapx.shape == mapy.shape and mapx.ndim == 2
+        self.dh, self.dw = mapx.shape
+        self.sw, self.sh = int(src_size[0]), int(src_size[1])
+        self._t = C.c_void_p()
+        _check(lib().orbx_remap_create(owner._h, _p(mapx), _p(mapy), self.dw, self.dh, self.dw, self.sw, self.sh, C.byref(self._t)))
+
+    def close(self):
+        if getattr(self, "_t", None) and self._t.value:
+            lib().orbx_remap_destroy(self._t)
+            self._t = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Preprocessor:
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        _check(lib().orbx_preproc_create(int(device), C.byref(self._h)))
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().orbx_preproc_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- cvtColor ---------------------------------------------------------------------------------------------------------
+    def cvtColor(self, src, code, coeffs=GRAY_OCV4):
+        src, batched = _frames(src, 3)
+        n, h, w, c = src.shape
+        if {"bgr": 3, "rgb": 3, "bgra": 4, "rgba": 4}[code] != c:
+            raise ValueError("channel count does not match the conversion code")
+        dst = np.empty((n, h, w), np.uint8)
+        _check(lib().orbx_cvt_gray(self._h, _p(src), n, w, h, w * c, _LL(h * w * c), c, int(code[0] == "r"), int(coeffs), _p(dst), w,
+                                   _LL(h * w), MEM_HOST, None))
+        return dst if batched else dst[0]
+
+    def cvt_gray_device(self, d_src, n, w, h, src_stride, src_frame_stride, channels, rgb_order, d_dst, dst_stride, dst_frame_stride,
+                        stream=None, coeffs=GRAY_OCV4):
+        _check(lib().orbx_cvt_gray(self._h, C.c_void_p(d_src), n, w, h, src_stride, _LL(src_frame_stride), channels, int(rgb_order),
+                                   int(coeffs), C.c_void_p(d_dst), dst_stride, _LL(dst_frame_stride), MEM_DEVICE,
+                                   C.c_void_p(stream or 0)))
+
+    # -- remap ------------------------------------------------------------------------------------------------------------
+    def remap_table(self, mapx, mapy, src_size):
+        """src_size = (width, height) of the images that will be remapped."""
+        return RemapTable(self, mapx, mapy, src_size)
+
+    def remap(self, src, table):
+        src, batched = _frames(src, 2)
+        n, h, w = src.shape
+        if (w, h) != (table.sw, table.sh):
+            raise ValueError("image size differs from the table's source size")
+        dst = np.empty((n, table.dh, table.dw), np.uint8)
+        _check(lib().orbx_remap(self._h, table._t, _p(src), n, w, _LL(h * w), _p(dst), table.dw, _LL(table.dh * table.dw), MEM_HOST, None))
+        return dst if batched else dst[0]
+
+    def remap_device(self, table, d_src, n, src_stride, src_frame_stride, d_dst, dst_stride, dst_frame_stride, stream=None):
+        _check(lib().orbx_remap(self._h, table._t, C.c_void_p(d_src), n, src_stride, _LL(src_frame_stride), C.c_void_p(d_dst), dst_stride,
+                                _LL(dst_frame_stride), MEM_DEVICE, C.c_void_p(stream or 0)))
+
+    # -- CLAHE ------------------------------------------------------------------------------------------------------------
+    def clahe(self, src, clip_limit=3.0, tiles=(8, 8)):
+        src, batched = _frames(src, 2)
+        n, h, w = src.shape
+        dst = np.empty((n, h, w), np.uint8)
+        _check(lib().orbx_clahe(self._h, _p(src), n, w, h, w, _LL(h * w), C.c_double(clip_limit), int(tiles[0]), int(tiles[1]), _p(dst), w,
+                                _LL(h * w), MEM_HOST, None))
+        return dst if batched else dst[0]
+
+    def clahe_device(self, d_src, n, w, h, src_stride, src_frame_stride, d_dst, dst_stride, dst_frame_stride, clip_limit=3.0, tiles=(8, 8),
+                     stream=None):
+        _check(lib().orbx_clahe(self._h, C.c_void_p(d_src), n, w, h, src_stride, _LL(src_frame_stride), C.c_double(clip_limit),
+                                int(tiles[0]), int(tiles[1]), C.c_void_p(d_dst), dst_stride, _LL(dst_frame_stride), MEM_DEVICE,
+                                C.c_void_p(stream or 0)))

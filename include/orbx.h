@@ -288,6 +288,41 @@ int orbx_stereo_frames_host(orbx_matcher* m, orbx_extractor* left, orbx_extracto
 int orbx_stereo_results_host(orbx_matcher* m, float* u_right, float* depth, int* best_dist, int* best_idx,
                              int capacity_per_frame);
 
+/* ---- pre-processing in front of the extractor ---------------------------------------------------
+ * The 8-bit image operations the reference applies to a frame before ORBextractor::operator() sees it, bit-exact with the
+ * OpenCV calls they replace.  Batched: nframes images, frame f at base + f * frame_stride, rows `stride` bytes apart.
+ * mem = ORBX_MEM_HOST: host pointers, the call stages through the handle's device buffers and blocks until dst is written.
+ * mem = ORBX_MEM_DEVICE: device pointers, the kernels are enqueued on `stream` (NULL = the handle's own stream) and the
+ * call returns at once -- the form that feeds orbx_extract_batch_device without leaving HBM.
+ * A handle is not re-entrant; handles are independent. */
+#define ORBX_MEM_HOST 0
+#define ORBX_MEM_DEVICE 1
+#define ORBX_GRAY_OCV346 0 /* 14-bit weights R 4899 G 9617 B 1868 (OpenCV 3.4's table path; unverifiable here) */
+#define ORBX_GRAY_OCV4 1   /* 15-bit weights R 9798 G 19235 B 3735 (verified bit-exact against cv2 4.13) */
+typedef struct orbx_preproc orbx_preproc;
+int orbx_preproc_create(int device, orbx_preproc** out);
+void orbx_preproc_destroy(orbx_preproc* p);
+
+/* cvtColor(im, im, CV_{RGB,BGR,RGBA,BGRA}2GRAY): src/Tracking.cc:989-1014 (GrabImageStereo), :1059-1073 (GrabImageRGBD), :1121-1135
+ * (GrabImageMonocular).  channels 3 or 4; rgb_order != 0 when channel 0 is red (mbRGB).  src and dst must not overlap. */
+int orbx_cvt_gray(orbx_preproc* p, const uint8_t* src, int nframes, int width, int height, int src_stride, long long src_frame_stride,
+                  int channels, int rgb_order, int coeffs, uint8_t* dst, int dst_stride, long long dst_frame_stride, int mem, void* stream);
+
+/* cv::remap(im, imRect, M1, M2, cv::INTER_LINEAR): Examples/Stereo/stereo_euroc.cc:166-167, maps (CV_32F, host) from
+ * cv::initUndistortRectifyMap at :117-118.  The table is built once per camera: OpenCV's 1/32-px fixed-point form of the two
+ * maps, 4 bytes per destination pixel.  BORDER_CONSTANT 0 like the reference's call.  Source images up to 2046 px. */
+typedef struct orbx_remap_table orbx_remap_table;
+int orbx_remap_create(orbx_preproc* p, const float* mapx, const float* mapy, int dst_width, int dst_height, int map_stride_floats,
+                      int src_width, int src_height, orbx_remap_table** out);
+void orbx_remap_destroy(orbx_remap_table* t);
+int orbx_remap(orbx_preproc* p, const orbx_remap_table* t, const uint8_t* src, int nframes, int src_stride, long long src_frame_stride,
+               uint8_t* dst, int dst_stride, long long dst_frame_stride, int mem, void* stream);
+
+/* cv::createCLAHE(clip_limit, Size(tiles_x, tiles_y))->apply(im, im): Examples/Monocular/mono_tum_vi.cc:101,109 (3.0, 8x8).
+ * dst may be src (same strides). */
+int orbx_clahe(orbx_preproc* p, const uint8_t* src, int nframes, int width, int height, int src_stride, long long src_frame_stride,
+               double clip_limit, int tiles_x, int tiles_y, uint8_t* dst, int dst_stride, long long dst_frame_stride, int mem, void* stream);
+
 /* Page-locked host staging buffers for the *_host entry points (cudaHostAlloc).  Frames handed over in such a buffer upload at
  * the full link rate; memory pinned after the fact (cudaHostRegister of pageable pages, which is what e.g. torch's
  * pin_memory() produced on the test box) was measured at half of it (27 vs 55 GB/s host-to-device on PCIe 5 x16).  The

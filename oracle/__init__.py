@@ -21,7 +21,7 @@ assert KP_DTYPE.itemsize == 28
 
 
 def build(force=False):
-    srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.cc", "match_oracle.cc", "oracle_capi.cc", "orb_oracle.h",
+    srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.cc", "match_oracle.cc", "oracle_capi.cc", "preproc_oracle.cc", "orb_oracle.h",
                                              "match_oracle.h", "Makefile")]
     if force or not os.path.exists(_LIB) or any(os.path.getmtime(s) > os.path.getmtime(_LIB) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-B", "liborb_oracle.so"], stdout=subprocess.DEVNULL)
@@ -361,3 +361,36 @@ def time_extract(frames, nthreads, nfeatures=1000, scaleFactor=1.2, nlevels=8, i
     s = lib().oro_time_extract(nfeatures, C.c_float(scaleFactor), nlevels, iniThFAST, minThFAST, blur_taps, sincos_mode,
                                _p(frames), n, w, h, int(lapping[0]), int(lapping[1]), int(nthreads), C.byref(tot))
     return float(s), int(tot.value)
+
+
+# ---- pre-processing before the extractor (oracle/preproc_oracle.cc) -------------------------------
+GRAY_OCV346, GRAY_OCV4 = 0, 1
+
+
+def cvt_gray(src, rgb_order=False, coeffs=GRAY_OCV4):
+    """cvtColor(src, CV_{RGB,BGR,RGBA,BGRA}2GRAY) -- src/Tracking.cc:989-1014."""
+    src = _u8(src)
+    h, w, c = src.shape
+    dst = np.empty((h, w), np.uint8)
+    lib().oro_cvt_gray(_p(src), w, h, w * c, c, int(bool(rgb_order)), int(coeffs), _p(dst), w)
+    return dst
+
+
+def remap_linear(src, mapx, mapy):
+    """cv::remap(src, dst, M1, M2, INTER_LINEAR) -- Examples/Stereo/stereo_euroc.cc:166-167."""
+    src = _u8(src)
+    mapx = np.ascontiguousarray(mapx, np.float32)
+    mapy = np.ascontiguousarray(mapy, np.float32)
+    dh, dw = mapx.shape
+    dst = np.empty((dh, dw), np.uint8)
+    lib().oro_remap_linear(_p(src), src.shape[1], src.shape[0], src.shape[1], _p(mapx), _p(mapy), dw, _p(dst), dw, dh, dw)
+    return dst
+
+
+def clahe(src, clip_limit=3.0, tiles=(8, 8)):
+    """cv::createCLAHE(clip_limit, tiles)->apply(src, dst) -- Examples/Monocular/mono_tum_vi.cc:101,109."""
+    src = _u8(src)
+    h, w = src.shape
+    dst = np.empty((h, w), np.uint8)
+    lib().oro_clahe(_p(src), w, h, w, C.c_double(clip_limit), int(tiles[0]), int(tiles[1]), _p(dst), w)
+    return dst

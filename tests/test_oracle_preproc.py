@@ -1,0 +1,61 @@
+"""Pins oracle/preproc_oracle.cc (cvtColor -> gray, remap, CLAHE) against the real OpenCV:
+live against python cv2 when it is importable, and against tests/golden/preproc/preproc_cv2.npz (cv2 outputs committed by
+tools/gen_golden_preproc.py) always.  Bit-exact in every case."""
+import os
+import zlib
+
+import numpy as np
+import pytest
+
+import preproc_cases as pc
+
+GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "preproc", "preproc_cv2.npz"))
+CODES = ("bgr", "rgb", "bgra", "rgba")
+
+
+def _same(gold_key, img):
+    assert np.array_equal(GOLD[gold_key + "_corner"], img[:64, :64])
+    assert int(GOLD[gold_key + "_crc"]) == zlib.crc32(img.tobytes())
+
+
+@pytest.mark.parametrize("name", list(pc.SHAPES))
+def test_oracle_gray_matches_cv2_golden(oracle, name):
+    col = pc.colour_image(name, 4)
+    for code in CODES:
+        g = oracle.cvt_gray(np.ascontiguousarray(col[:, :, :len(code)]), rgb_order=code[0] == "r", coeffs=oracle.GRAY_OCV4)
+        _same("gray_%s_%s" % (name, code), g)
+
+
+def test_oracle_gray_coefficient_sets_differ_by_at_most_one(oracle):
+    col = pc.colour_image("euroc", 3)
+    a = oracle.cvt_gray(col, False, oracle.GRAY_OCV346).astype(int)
+    b = oracle.cvt_gray(col, False, oracle.GRAY_OCV4).astype(int)
+    assert np.abs(a - b).max() <= 1 and (a != b).any()
+
+
+@pytest.mark.parametrize("name", list(pc.SHAPES))
+def test_oracle_remap_matches_cv2_golden(oracle, name):
+    mx, my = pc.rectify_maps(name)
+    _same("remap_%s" % name, oracle.remap_linear(pc.gray_image(name), mx, my))
+
+
+@pytest.mark.parametrize("name", list(pc.SHAPES))
+def test_oracle_clahe_matches_cv2_golden(oracle, name):
+    img = pc.gray_image(name)
+    for clip, tiles in pc.CLAHE_PARAMS:
+        _same("clahe_%s_%g_%dx%d" % (name, clip, tiles[0], tiles[1]), oracle.clahe(img, clip, tiles))
+
+
+def test_oracle_matches_live_cv2_on_random_inputs(oracle):
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(7)
+    for h, w in [(64, 64), (75, 203), (240, 320)]:
+        col = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+        assert np.array_equal(cv2.cvtColor(col, cv2.COLOR_RGBA2GRAY), oracle.cvt_gray(col, True))
+        assert np.array_equal(cv2.cvtColor(col[:, :, :3].copy(), cv2.COLOR_BGR2GRAY), oracle.cvt_gray(col[:, :, :3], False))
+        g = rng.integers(0, 256, (h, w), dtype=np.uint8)
+        mx = (rng.random((h, w)) * (w + 8) - 4).astype(np.float32)
+        my = (rng.random((h, w)) * (h + 8) - 4).astype(np.float32)
+        assert np.array_equal(cv2.remap(g, mx, my, cv2.INTER_LINEAR), oracle.remap_linear(g, mx, my))
+        for clip, tiles in [(3.0, (8, 8)), (1.0, (2, 7)), (0.0, (8, 8))]:
+            assert np.array_equal(cv2.createCLAHE(clip, tiles).apply(g), oracle.clahe(g, clip, tiles))
