@@ -92,6 +92,20 @@ int check_image(const void* src, const void* dst, int n, int w, int h, int mem) 
 }
 }  // namespace
 
+namespace orbx {
+// used by orbx_frame.cu (the Frame-side helpers share the handle's stream and staging buffers)
+int preproc_device(const orbx_preproc* p) { return p->device; }
+cudaStream_t preproc_stream(const orbx_preproc* p) { return p->stream; }
+int preproc_scratch(orbx_preproc* p, size_t inBytes, size_t outBytes, uint8_t** dIn, uint8_t** dOut) {
+  int rc = grow(&p->dIn, &p->inBytes, inBytes);
+  if (rc) return rc;
+  rc = grow(&p->dOut, &p->outBytes, outBytes);
+  if (rc) return rc;
+  *dIn = p->dIn; *dOut = p->dOut;
+  return ORBX_OK;
+}
+}  // namespace orbx
+
 extern "C" {
 
 int orbx_preproc_create(int device, orbx_preproc** out) {
@@ -141,7 +155,7 @@ int orbx_cvt_gray(orbx_preproc* p, const uint8_t* src, int nframes, int width, i
   A.half = 1u << (A.shift - 1);
   A.c0 = rgb_order ? cr : cb; A.c1 = cg; A.c2 = rgb_order ? cb : cr;
   A.vec = aligned(S.dSrc, src_stride, src_frame_stride, channels == 3 ? 4 : 16) && aligned(S.dDst, dst_stride, dst_frame_stride, 4);
-  dim3 grid((width + 1023) / 1024, height, nframes);
+  dim3 grid((width + 1023) / 1024, (height + ORBX_GRAY_ROWS - 1) / ORBX_GRAY_ROWS, nframes);
   if (channels == 3) k_cvt_gray<3><<<grid, 256, 0, S.st>>>(A);
   else k_cvt_gray<4><<<grid, 256, 0, S.st>>>(A);
   return S.finish();
@@ -199,6 +213,7 @@ int orbx_remap(orbx_preproc* p, const orbx_remap_table* t, const uint8_t* src, i
   int rc = check_image(src, dst, nframes, t->dw, t->dh, mem);
   if (rc) return rc;
   if (src_stride < t->sw || dst_stride < t->dw) { set_error("stride shorter than a row"); return ORBX_ERR_ARG; }
+  if ((long long)src_stride * t->sh > 0x7fffffffLL) { set_error("remap: source frame larger than 2 GB"); return ORBX_ERR_UNSUPPORTED; }
   if (nframes == 0) return ORBX_OK;
   Staging S;
   rc = S.begin(p, mem, stream, src, nframes, t->sw, t->sh, src_stride, src_frame_stride, dst, t->dw, t->dh, dst_stride, dst_frame_stride);
@@ -208,7 +223,7 @@ int orbx_remap(orbx_preproc* p, const orbx_remap_table* t, const uint8_t* src, i
   A.sw = t->sw; A.sh = t->sh; A.dw = t->dw; A.dh = t->dh; A.sstride = src_stride; A.dstride = dst_stride;
   A.sfs = src_frame_stride; A.dfs = dst_frame_stride;
   A.vecDst = aligned(S.dDst, dst_stride, dst_frame_stride, 4);
-  dim3 grid((t->dw + 1023) / 1024, t->dh, nframes);
+  dim3 grid((t->dw + 1023) / 1024, (t->dh + ORBX_REMAP_ROWS - 1) / ORBX_REMAP_ROWS, nframes);
   k_remap<<<grid, 256, 0, S.st>>>(A);
   return S.finish();
 }
@@ -239,14 +254,14 @@ int orbx_clahe(orbx_preproc* p, const uint8_t* src, int nframes, int width, int 
   if (clip_limit > 0.0) { A.clip = (int)(clip_limit * total / 256); if (A.clip < 1) A.clip = 1; }
   A.invTw = 1.0f / A.tw; A.invTh = 1.0f / A.th;
   A.vec = aligned(S.dSrc, src_stride, src_frame_stride, 4) && aligned(S.dDst, dst_stride, dst_frame_stride, 4);
-  A.rows = 16;
   if (!p->claheAttr) {
     std::lock_guard<std::recursive_mutex> lock(setup_mutex());
     CK(cudaFuncSetAttribute(k_clahe_apply, cudaFuncAttributeMaxDynamicSharedMemorySize, 512 * 256));
     p->claheAttr = true;
   }
   k_clahe_lut<<<dim3(tiles_x * tiles_y, nframes), 256, 0, S.st>>>(A);
-  k_clahe_apply<<<dim3((height + A.rows - 1) / A.rows, nframes), 256, nlut, S.st>>>(A);
+  const int wq = (width + 3) / 4, threads = wq >= 256 ? 256 : ((wq + 31) & ~31);
+  k_clahe_apply<<<dim3((height + ORBX_CLAHE_ROWS - 1) / ORBX_CLAHE_ROWS, nframes), threads, nlut, S.st>>>(A);
   return S.finish();
 }
 

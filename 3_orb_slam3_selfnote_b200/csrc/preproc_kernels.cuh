@@ -22,32 +22,55 @@ __device__ __forceinline__ unsigned gray_px(unsigned a, unsigned b, unsigned c, 
   return (a * A.c0 + b * A.c1 + c * A.c2 + A.half) >> A.shift;
 }
 
+// Thread = 4 adjacent pixels of GRAY_ROWS consecutive rows; every row's loads are issued before the first multiply so one
+// thread keeps GRAY_ROWS x 12 (16) bytes in flight (one row per thread measured 56-67 % of the HBM peak: latency-bound).
+#define ORBX_GRAY_ROWS 4
 template <int CH>
 __global__ void __launch_bounds__(256) k_cvt_gray(const __grid_constant__ GrayArgs A) {
-  const int x4 = (blockIdx.x * 256 + threadIdx.x) * 4, y = blockIdx.y;
+  const int x4 = (blockIdx.x * 256 + threadIdx.x) * 4, y0 = blockIdx.y * ORBX_GRAY_ROWS;
   if (x4 >= A.w) return;
-  const uint8_t* s = A.src + (long long)blockIdx.z * A.sfs + (long long)y * A.sstride + (long long)x4 * CH;
-  uint8_t* d = A.dst + (long long)blockIdx.z * A.dfs + (long long)y * A.dstride + x4;
+  const uint8_t* s = A.src + (long long)blockIdx.z * A.sfs + (long long)y0 * A.sstride + (long long)x4 * CH;
+  uint8_t* d = A.dst + (long long)blockIdx.z * A.dfs + (long long)y0 * A.dstride + x4;
+  const int nr = min(ORBX_GRAY_ROWS, A.h - y0);
   if (A.vec && x4 + 4 <= A.w) {
-    unsigned g0, g1, g2, g3;
-    if (CH == 3) {
-      const unsigned* p = reinterpret_cast<const unsigned*>(s);
-      unsigned w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
-      g0 = gray_px(w0 & 255u, (w0 >> 8) & 255u, (w0 >> 16) & 255u, A);
-      g1 = gray_px(w0 >> 24, w1 & 255u, (w1 >> 8) & 255u, A);
-      g2 = gray_px((w1 >> 16) & 255u, w1 >> 24, w2 & 255u, A);
-      g3 = gray_px((w2 >> 8) & 255u, (w2 >> 16) & 255u, w2 >> 24, A);
-    } else {
-      uint4 q = __ldg(reinterpret_cast<const uint4*>(s));
-      g0 = gray_px(q.x & 255u, (q.x >> 8) & 255u, (q.x >> 16) & 255u, A);
-      g1 = gray_px(q.y & 255u, (q.y >> 8) & 255u, (q.y >> 16) & 255u, A);
-      g2 = gray_px(q.z & 255u, (q.z >> 8) & 255u, (q.z >> 16) & 255u, A);
-      g3 = gray_px(q.w & 255u, (q.w >> 8) & 255u, (q.w >> 16) & 255u, A);
+    unsigned q[ORBX_GRAY_ROWS][4];
+#pragma unroll
+    for (int r = 0; r < ORBX_GRAY_ROWS; ++r) {
+      if (r < nr) {
+        if (CH == 3) {
+          const unsigned* p = reinterpret_cast<const unsigned*>(s + (long long)r * A.sstride);
+          q[r][0] = __ldg(p); q[r][1] = __ldg(p + 1); q[r][2] = __ldg(p + 2); q[r][3] = 0;
+        } else {
+          const uint4 v = __ldg(reinterpret_cast<const uint4*>(s + (long long)r * A.sstride));
+          q[r][0] = v.x; q[r][1] = v.y; q[r][2] = v.z; q[r][3] = v.w;
+        }
+      }
     }
-    *reinterpret_cast<unsigned*>(d) = g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
+#pragma unroll
+    for (int r = 0; r < ORBX_GRAY_ROWS; ++r) {
+      if (r < nr) {
+        unsigned g0, g1, g2, g3;
+        if (CH == 3) {
+          const unsigned w0 = q[r][0], w1 = q[r][1], w2 = q[r][2];
+          g0 = gray_px(w0 & 255u, (w0 >> 8) & 255u, (w0 >> 16) & 255u, A);
+          g1 = gray_px(w0 >> 24, w1 & 255u, (w1 >> 8) & 255u, A);
+          g2 = gray_px((w1 >> 16) & 255u, w1 >> 24, w2 & 255u, A);
+          g3 = gray_px((w2 >> 8) & 255u, (w2 >> 16) & 255u, w2 >> 24, A);
+        } else {
+          g0 = gray_px(q[r][0] & 255u, (q[r][0] >> 8) & 255u, (q[r][0] >> 16) & 255u, A);
+          g1 = gray_px(q[r][1] & 255u, (q[r][1] >> 8) & 255u, (q[r][1] >> 16) & 255u, A);
+          g2 = gray_px(q[r][2] & 255u, (q[r][2] >> 8) & 255u, (q[r][2] >> 16) & 255u, A);
+          g3 = gray_px(q[r][3] & 255u, (q[r][3] >> 8) & 255u, (q[r][3] >> 16) & 255u, A);
+        }
+        *reinterpret_cast<unsigned*>(d + (long long)r * A.dstride) = g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
+      }
+    }
   } else {
     const int n = min(4, A.w - x4);
-    for (int i = 0; i < n; ++i) d[i] = (uint8_t)gray_px(s[i * CH], s[i * CH + 1], s[i * CH + 2], A);
+    for (int r = 0; r < nr; ++r)
+      for (int i = 0; i < n; ++i)
+        d[(long long)r * A.dstride + i] = (uint8_t)gray_px(s[(long long)r * A.sstride + i * CH], s[(long long)r * A.sstride + i * CH + 1],
+                                                          s[(long long)r * A.sstride + i * CH + 2], A);
   }
 }
 
@@ -63,38 +86,79 @@ struct RemapArgs {
   int vecDst;
 };
 
-__device__ __forceinline__ unsigned remap_px(const uint8_t* __restrict__ S, uint32_t t, const RemapArgs& A) {
-  const int sx = (int)(t & 0xffffu) - 32, sy = (int)(t >> 16) - 32;
-  const int ix = sx >> 5, iy = sy >> 5, fx = sx & 31, fy = sy & 31;
-  unsigned p00, p01, p10, p11;
-  if ((unsigned)ix < (unsigned)(A.sw - 1) && (unsigned)iy < (unsigned)(A.sh - 1)) {
-    const uint8_t* r = S + (long long)iy * A.sstride + ix;
-    p00 = __ldg(r); p01 = __ldg(r + 1); p10 = __ldg(r + A.sstride); p11 = __ldg(r + A.sstride + 1);
-  } else {
-    const bool x0 = (unsigned)ix < (unsigned)A.sw, x1 = (unsigned)(ix + 1) < (unsigned)A.sw;
-    const bool y0 = (unsigned)iy < (unsigned)A.sh, y1 = (unsigned)(iy + 1) < (unsigned)A.sh;
-    const uint8_t* r = S + (long long)iy * A.sstride + ix;
-    p00 = (x0 && y0) ? __ldg(r) : 0u; p01 = (x1 && y0) ? __ldg(r + 1) : 0u;
-    p10 = (x0 && y1) ? __ldg(r + A.sstride) : 0u; p11 = (x1 && y1) ? __ldg(r + A.sstride + 1) : 0u;
-  }
-  // weights (32-fx)(32-fy)*32 ... scaled by 2^15 in OpenCV's table: factor the common 32 out, (sum*32 + 2^14) >> 15 == (sum + 512) >> 10
-  const unsigned top = p00 * (32 - fx) + p01 * fx, bot = p10 * (32 - fx) + p11 * fx;
-  return (top * (32 - fy) + bot * fy + 512u) >> 10;
+// OpenCV's table weights are (32-fx)(32-fy)*32 ... (2^15 scale): factor the common 32 out, (32*T + 2^14) >> 15 == (T + 512) >> 10
+__device__ __forceinline__ unsigned remap_blend(unsigned p00, unsigned p01, unsigned p10, unsigned p11, uint32_t t) {
+  const unsigned fx = t & 31u, fy = (t >> 16) & 31u;  // the +32 bias of the packed form leaves the low 5 bits alone
+  const unsigned top = p00 * (32u - fx) + p01 * fx, bot = p10 * (32u - fx) + p11 * fx;
+  return (top * (32u - fy) + bot * fy + 512u) >> 10;
 }
 
+// Thread = 4 adjacent destination pixels (x REMAP_ROWS rows): the table word(s), then all 16 tap loads, are issued before the
+// first blend.  Warps whose 2x2 footprints all lie inside the image (all but those on the rectified image's rim) take a path
+// without clamps or masks: one 32-bit offset per entry, four byte loads.  The kernel is bound by the L1 (ncu: l1tex 74 %, 8
+// sectors per request, LSU queue stalls): 16 one-byte gathers per thread.  More rows per thread (2, 4) only deepened the LSU
+// queue and lost occupancy (0.19 -> 0.27 / 0.32 ms per 256 frames), so ROWS stays 1; the next step is a shared-memory staged
+// source tile per CTA.
+#define ORBX_REMAP_ROWS 1
 __global__ void __launch_bounds__(256) k_remap(const __grid_constant__ RemapArgs A) {
-  const int x4 = (blockIdx.x * 256 + threadIdx.x) * 4, y = blockIdx.y;
-  if (x4 >= A.dw) return;
-  const uint8_t* S = A.src + (long long)blockIdx.z * A.sfs;
-  uint8_t* d = A.dst + (long long)blockIdx.z * A.dfs + (long long)y * A.dstride + x4;
-  const uint4 t = __ldg(reinterpret_cast<const uint4*>(A.table + (long long)y * A.tpitch + x4));
-  if (A.vecDst && x4 + 4 <= A.dw) {
-    unsigned v = remap_px(S, t.x, A) | (remap_px(S, t.y, A) << 8) | (remap_px(S, t.z, A) << 16) | (remap_px(S, t.w, A) << 24);
-    *reinterpret_cast<unsigned*>(d) = v;
+  const int x4 = (blockIdx.x * 256 + threadIdx.x) * 4, y0 = blockIdx.y * ORBX_REMAP_ROWS;
+  const bool live = x4 < A.dw;
+  const uint8_t* __restrict__ S = A.src + (long long)blockIdx.z * A.sfs;
+  const int nr = min(ORBX_REMAP_ROWS, A.dh - y0);
+  uint32_t t[ORBX_REMAP_ROWS][4];
+  bool interior = true;
+#pragma unroll
+  for (int r = 0; r < ORBX_REMAP_ROWS; ++r) {
+    // rows / columns past the end carry an interior dummy entry (pixel 0,0) that is never stored
+    const uint4 q = (live && r < nr) ? __ldg(reinterpret_cast<const uint4*>(A.table + (long long)(y0 + r) * A.tpitch + x4))
+                                     : make_uint4(0x00200020u, 0x00200020u, 0x00200020u, 0x00200020u);
+    t[r][0] = q.x; t[r][1] = q.y; t[r][2] = q.z; t[r][3] = q.w;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int ix = (int)((t[r][i] & 0xffffu) >> 5) - 1, iy = (int)(t[r][i] >> 21) - 1;
+      interior = interior && (unsigned)ix < (unsigned)(A.sw - 1) && (unsigned)iy < (unsigned)(A.sh - 1);
+    }
+  }
+  unsigned p[ORBX_REMAP_ROWS][4][4];
+  if (__all_sync(0xffffffffu, interior)) {
+#pragma unroll
+    for (int r = 0; r < ORBX_REMAP_ROWS; ++r)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int ix = (int)((t[r][i] & 0xffffu) >> 5) - 1, iy = (int)(t[r][i] >> 21) - 1;
+        const uint8_t* a = S + (unsigned)(iy * A.sstride + ix);
+        const uint8_t* b = a + A.sstride;
+        p[r][i][0] = __ldg(a); p[r][i][1] = __ldg(a + 1); p[r][i][2] = __ldg(b); p[r][i][3] = __ldg(b + 1);
+      }
   } else {
-    const uint32_t tt[4] = {t.x, t.y, t.z, t.w};
-    const int n = min(4, A.dw - x4);
-    for (int i = 0; i < n; ++i) d[i] = (uint8_t)remap_px(S, tt[i], A);
+#pragma unroll
+    for (int r = 0; r < ORBX_REMAP_ROWS; ++r)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int ix = (int)((t[r][i] & 0xffffu) >> 5) - 1, iy = (int)(t[r][i] >> 21) - 1;
+        const bool x0 = (unsigned)ix < (unsigned)A.sw, x1 = (unsigned)(ix + 1) < (unsigned)A.sw;
+        const bool v0 = (unsigned)iy < (unsigned)A.sh, v1 = (unsigned)(iy + 1) < (unsigned)A.sh;
+        const uint8_t* a = S + (long long)iy * A.sstride + ix;
+        p[r][i][0] = (x0 && v0) ? __ldg(a) : 0u; p[r][i][1] = (x1 && v0) ? __ldg(a + 1) : 0u;
+        p[r][i][2] = (x0 && v1) ? __ldg(a + A.sstride) : 0u; p[r][i][3] = (x1 && v1) ? __ldg(a + A.sstride + 1) : 0u;
+      }
+  }
+  if (!live) return;
+  uint8_t* d = A.dst + (long long)blockIdx.z * A.dfs + (long long)y0 * A.dstride + x4;
+#pragma unroll
+  for (int r = 0; r < ORBX_REMAP_ROWS; ++r) {
+    if (r < nr) {
+      uint8_t* dr = d + (long long)r * A.dstride;
+      unsigned o[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) o[i] = remap_blend(p[r][i][0], p[r][i][1], p[r][i][2], p[r][i][3], t[r][i]);
+      if (A.vecDst && x4 + 4 <= A.dw) {
+        *reinterpret_cast<unsigned*>(dr) = o[0] | (o[1] << 8) | (o[2] << 16) | (o[3] << 24);
+      } else {
+        const int n = min(4, A.dw - x4);
+        for (int i = 0; i < n; ++i) dr[i] = (uint8_t)o[i];
+      }
+    }
   }
 }
 
@@ -105,7 +169,7 @@ struct ClaheArgs {
   long long sfs, dfs;
   int tilesX, tilesY, tw, th, clip;
   float lutScale, invTw, invTh;
-  int vec, rows;
+  int vec;
 };
 
 __device__ __forceinline__ int reflect101_dev(int p, int len) {
@@ -116,6 +180,9 @@ __device__ __forceinline__ int reflect101_dev(int p, int len) {
 
 // CTA = one tile of one frame: per-warp shared histograms, clip + redistribute, 256-wide inclusive scan, LUT.
 __global__ void __launch_bounds__(256) k_clahe_lut(const __grid_constant__ ClaheArgs A) {
+  // one sub-histogram per warp.  (32 sub-histograms -- one per (warp, lane & 3), so that the correlated pixels of adjacent lanes
+  // never share a counter -- removed the atomic serialisation but cost more in clearing and folding 32 KB than it saved: a
+  // tile is only ~22 pixels per thread.  Measured 0.27 -> 0.30 ms per 256 frames, reverted.)
   __shared__ int wh[8][256];
   __shared__ int wsum[8];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -123,12 +190,29 @@ __global__ void __launch_bounds__(256) k_clahe_lut(const __grid_constant__ Clahe
   const uint8_t* S = A.src + (long long)blockIdx.y * A.sfs;
   for (int i = tid; i < 8 * 256; i += 256) (&wh[0][0])[i] = 0;
   __syncthreads();
-  const int total = A.tw * A.th;
   const bool inside = (tx + 1) * A.tw <= A.w && (ty + 1) * A.th <= A.h;
-  for (int i = tid; i < total; i += 256) {
-    int yy = ty * A.th + i / A.tw, xx = tx * A.tw + i % A.tw;
-    if (!inside) { yy = reflect101_dev(yy, A.h); xx = reflect101_dev(xx, A.w); }
-    atomicAdd(&wh[warp][__ldg(S + (long long)yy * A.sstride + xx)], 1);
+  if (inside && A.vec) {
+    // warp = tile row, lane = aligned 32-bit word of it (bytes outside [x0, x0 + tw) are skipped)
+    const int x0 = tx * A.tw, a0 = x0 & ~3, nw = (x0 + A.tw - a0 + 3) >> 2;
+    for (int r = warp; r < A.th; r += 8) {
+      const uint8_t* row = S + (long long)(ty * A.th + r) * A.sstride + a0;
+      for (int wi = lane; wi < nw; wi += 32) {
+        const int xb = a0 + wi * 4;
+        unsigned q;
+        if (xb + 4 <= A.w) q = __ldg(reinterpret_cast<const unsigned*>(row + wi * 4));
+        else { q = 0; for (int b = 0; b < A.w - xb; ++b) q |= (unsigned)__ldg(row + wi * 4 + b) << (8 * b); }
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+          if (xb + b >= x0 && xb + b < x0 + A.tw) atomicAdd(&wh[warp][(q >> (8 * b)) & 255u], 1);
+      }
+    }
+  } else {
+    const int total = A.tw * A.th;
+    for (int i = tid; i < total; i += 256) {
+      int yy = ty * A.th + i / A.tw, xx = tx * A.tw + i % A.tw;
+      if (!inside) { yy = reflect101_dev(yy, A.h); xx = reflect101_dev(xx, A.w); }
+      atomicAdd(&wh[warp][__ldg(S + (long long)yy * A.sstride + xx)], 1);
+    }
   }
   __syncthreads();
   int hv = 0;
@@ -161,46 +245,72 @@ __global__ void __launch_bounds__(256) k_clahe_lut(const __grid_constant__ Clahe
   A.lut[((long long)blockIdx.y * A.tilesX * A.tilesY + tile) * 256 + tid] = (uint8_t)min(max(v, 0), 255);
 }
 
-__device__ __forceinline__ unsigned clahe_px(const uint8_t* L1, const uint8_t* L2, int x, unsigned v, float ya, float ya1, const ClaheArgs& A) {
+struct ClaheCol { float xa, xa1; int i1, i2; };  // per-column constants of the blend (clahe.cpp's ind1_p / ind2_p / xa_p / xa1_p)
+
+__device__ __forceinline__ ClaheCol clahe_col(int x, const ClaheArgs& A) {
   const float txf = __fsub_rn(__fmul_rn((float)x, A.invTw), 0.5f);
   int tx1 = __float2int_rd(txf), tx2 = tx1 + 1;
-  const float xa = __fsub_rn(txf, (float)tx1), xa1 = __fsub_rn(1.0f, xa);
-  tx1 = max(tx1, 0); tx2 = min(tx2, A.tilesX - 1);
-  const int i1 = tx1 * 256 + v, i2 = tx2 * 256 + v;
-  const float a = __fadd_rn(__fmul_rn((float)L1[i1], xa1), __fmul_rn((float)L1[i2], xa));
-  const float b = __fadd_rn(__fmul_rn((float)L2[i1], xa1), __fmul_rn((float)L2[i2], xa));
-  const int r = __float2int_rn(__fadd_rn(__fmul_rn(a, ya1), __fmul_rn(b, ya)));
+  ClaheCol c;
+  c.xa = __fsub_rn(txf, (float)tx1); c.xa1 = __fsub_rn(1.0f, c.xa);
+  c.i1 = max(tx1, 0) * 256; c.i2 = min(tx2, A.tilesX - 1) * 256;
+  return c;
+}
+
+// u8 -> float and cvRound(float) -> int through the 2^23 magic numbers (exact for these ranges): the conversion
+// instructions (I2F / F2I) run at a quarter of the FP32 rate and there are five of them per pixel otherwise.
+__device__ __forceinline__ float u8_to_float(unsigned v) { return __fsub_rn(__uint_as_float(0x4B000000u | v), 8388608.0f); }
+
+__device__ __forceinline__ unsigned clahe_px(const uint8_t* L1, const uint8_t* L2, const ClaheCol& c, unsigned v, float ya, float ya1) {
+  const float a = __fadd_rn(__fmul_rn(u8_to_float(L1[c.i1 + v]), c.xa1), __fmul_rn(u8_to_float(L1[c.i2 + v]), c.xa));
+  const float b = __fadd_rn(__fmul_rn(u8_to_float(L2[c.i1 + v]), c.xa1), __fmul_rn(u8_to_float(L2[c.i2 + v]), c.xa));
+  const float res = __fadd_rn(__fmul_rn(a, ya1), __fmul_rn(b, ya));  // in [0, 255.001]: a blend of LUT bytes
+  const int r = __float_as_int(__fadd_rn(res, 12582912.0f)) - 0x4B400000;  // round-half-even, = cvRound(res)
   return (unsigned)min(max(r, 0), 255);
 }
 
-// CTA = A.rows image rows of one frame; the frame's tile LUTs are staged in shared memory once per CTA.
+#define ORBX_CLAHE_ROWS 16
+// CTA = ORBX_CLAHE_ROWS image rows of one frame; the frame's tile LUTs are staged in shared memory once per CTA.  Thread = a
+// group of 4 adjacent columns walking down the rows: the column constants stay in registers, the row constants come from
+// a small shared table, the next row's word is loaded while the current one is blended.
 __global__ void __launch_bounds__(256) k_clahe_apply(const __grid_constant__ ClaheArgs A) {
   extern __shared__ __align__(16) uint8_t sl[];
+  __shared__ float sYa[ORBX_CLAHE_ROWS], sYa1[ORBX_CLAHE_ROWS];
+  __shared__ int sT1[ORBX_CLAHE_ROWS], sT2[ORBX_CLAHE_ROWS];
   const int nlut = A.tilesX * A.tilesY * 256;
   const uint8_t* G = A.lut + (long long)blockIdx.y * nlut;
-  for (int i = threadIdx.x * 16; i < nlut; i += 256 * 16) *reinterpret_cast<uint4*>(sl + i) = __ldg(reinterpret_cast<const uint4*>(G + i));
+  for (int i = threadIdx.x * 16; i < nlut; i += blockDim.x * 16) *reinterpret_cast<uint4*>(sl + i) = __ldg(reinterpret_cast<const uint4*>(G + i));
+  const int wq = (A.w + 3) >> 2, y0 = blockIdx.x * ORBX_CLAHE_ROWS, nrows = min(ORBX_CLAHE_ROWS, A.h - y0);
+  if (threadIdx.x < nrows) {
+    const float tyf = __fsub_rn(__fmul_rn((float)(y0 + threadIdx.x), A.invTh), 0.5f);
+    const int ty1 = __float2int_rd(tyf), ty2 = ty1 + 1;
+    const float ya = __fsub_rn(tyf, (float)ty1);
+    sYa[threadIdx.x] = ya; sYa1[threadIdx.x] = __fsub_rn(1.0f, ya);
+    sT1[threadIdx.x] = max(ty1, 0) * A.tilesX * 256; sT2[threadIdx.x] = min(ty2, A.tilesY - 1) * A.tilesX * 256;
+  }
   __syncthreads();
-  const int wq = (A.w + 3) >> 2, y0 = blockIdx.x * A.rows, nrows = min(A.rows, A.h - y0);
-  const uint8_t* S = A.src + (long long)blockIdx.y * A.sfs;
-  uint8_t* D = A.dst + (long long)blockIdx.y * A.dfs;
-  for (int g = threadIdx.x; g < nrows * wq; g += 256) {
-    const int y = y0 + g / wq, x4 = (g % wq) * 4;
-    const float tyf = __fsub_rn(__fmul_rn((float)y, A.invTh), 0.5f);
-    int ty1 = __float2int_rd(tyf), ty2 = ty1 + 1;
-    const float ya = __fsub_rn(tyf, (float)ty1), ya1 = __fsub_rn(1.0f, ya);
-    ty1 = max(ty1, 0); ty2 = min(ty2, A.tilesY - 1);
-    const uint8_t* L1 = sl + ty1 * A.tilesX * 256;
-    const uint8_t* L2 = sl + ty2 * A.tilesX * 256;
-    const uint8_t* s = S + (long long)y * A.sstride + x4;
-    uint8_t* d = D + (long long)y * A.dstride + x4;
+  const uint8_t* S = A.src + (long long)blockIdx.y * A.sfs + (long long)y0 * A.sstride;
+  uint8_t* D = A.dst + (long long)blockIdx.y * A.dfs + (long long)y0 * A.dstride;
+  for (int c = threadIdx.x; c < wq; c += blockDim.x) {
+    const int x4 = c * 4;
+    const ClaheCol c0 = clahe_col(x4, A), c1 = clahe_col(x4 + 1, A), c2 = clahe_col(x4 + 2, A), c3 = clahe_col(x4 + 3, A);
     if (A.vec && x4 + 4 <= A.w) {
-      const unsigned q = __ldg(reinterpret_cast<const unsigned*>(s));
-      unsigned o = clahe_px(L1, L2, x4, q & 255u, ya, ya1, A) | (clahe_px(L1, L2, x4 + 1, (q >> 8) & 255u, ya, ya1, A) << 8) |
-                   (clahe_px(L1, L2, x4 + 2, (q >> 16) & 255u, ya, ya1, A) << 16) | (clahe_px(L1, L2, x4 + 3, q >> 24, ya, ya1, A) << 24);
-      *reinterpret_cast<unsigned*>(d) = o;
+      unsigned q = __ldg(reinterpret_cast<const unsigned*>(S + x4));
+      for (int r = 0; r < nrows; ++r) {
+        const unsigned cur = q;
+        if (r + 1 < nrows) q = __ldg(reinterpret_cast<const unsigned*>(S + (long long)(r + 1) * A.sstride + x4));
+        const uint8_t* L1 = sl + sT1[r];
+        const uint8_t* L2 = sl + sT2[r];
+        const float ya = sYa[r], ya1 = sYa1[r];
+        *reinterpret_cast<unsigned*>(D + (long long)r * A.dstride + x4) =
+            clahe_px(L1, L2, c0, cur & 255u, ya, ya1) | (clahe_px(L1, L2, c1, (cur >> 8) & 255u, ya, ya1) << 8) |
+            (clahe_px(L1, L2, c2, (cur >> 16) & 255u, ya, ya1) << 16) | (clahe_px(L1, L2, c3, cur >> 24, ya, ya1) << 24);
+      }
     } else {
+      const ClaheCol cc[4] = {c0, c1, c2, c3};
       const int n = min(4, A.w - x4);
-      for (int i = 0; i < n; ++i) d[i] = (uint8_t)clahe_px(L1, L2, x4 + i, s[i], ya, ya1, A);
+      for (int r = 0; r < nrows; ++r)
+        for (int i = 0; i < n; ++i)
+          D[(long long)r * A.dstride + x4 + i] = (uint8_t)clahe_px(sl + sT1[r], sl + sT2[r], cc[i], S[(long long)r * A.sstride + x4 + i], sYa[r], sYa1[r]);
     }
   }
 }

@@ -118,3 +118,60 @@ class Preprocessor:
         _check(lib().orbx_clahe(self._h, C.c_void_p(d_src), n, w, h, src_stride, _LL(src_frame_stride), C.c_double(clip_limit),
                                 int(tiles[0]), int(tiles[1]), C.c_void_p(d_dst), dst_stride, _LL(dst_frame_stride), MEM_DEVICE,
                                 C.c_void_p(stream or 0)))
+
+
+# ---- Frame glue ---------------------------------------------------------------------------------
+class _Frustum(C.Structure):
+    _fields_ = [("Rcw", C.c_float * 9), ("tcw", C.c_float * 3), ("Ow", C.c_float * 3), ("fx", C.c_float), ("fy", C.c_float),
+                ("cx", C.c_float), ("cy", C.c_float), ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float),
+                ("max_y", C.c_float), ("bf", C.c_float), ("log_scale_factor", C.c_float), ("viewing_cos_limit", C.c_float),
+                ("n_scale_levels", C.c_int)]
+
+
+def frustum(Rcw, tcw, fx, fy, cx, cy, bounds, bf, scale_factor, nlevels, viewing_cos_limit=0.5):
+    """The members of Frame that isInFrustum reads.  Ow = -Rcw^T tcw and mfLogScaleFactor = log(mfScaleFactor) are computed
+    here in float32 like Frame::UpdatePoseMatrices (src/Frame.cc:561-566) and the constructor (:110)."""
+    Rcw = np.asarray(Rcw, np.float32).reshape(3, 3)
+    tcw = np.asarray(tcw, np.float32).reshape(3)
+    Ow = -(Rcw.T @ tcw).astype(np.float32)
+    f = _Frustum()
+    f.Rcw[:] = Rcw.reshape(-1).tolist(); f.tcw[:] = tcw.tolist(); f.Ow[:] = Ow.tolist()
+    f.fx, f.fy, f.cx, f.cy = float(fx), float(fy), float(cx), float(cy)
+    f.min_x, f.max_x, f.min_y, f.max_y = [float(b) for b in bounds]
+    f.bf = float(bf)
+    f.log_scale_factor = float(np.log(np.float32(scale_factor)))
+    f.viewing_cos_limit = float(viewing_cos_limit)
+    f.n_scale_levels = int(nlevels)
+    return f
+
+
+def _undistort(self, kps, fx, fy, cx, cy, dist):
+    """Frame::UndistortKeyPoints (src/Frame.cc:837-870): mvKeys -> mvKeysUn."""
+    from . import KP_DTYPE
+    kps = np.ascontiguousarray(kps, dtype=KP_DTYPE)
+    d = np.zeros(5, np.float32)
+    d[:len(dist)] = dist
+    out = np.empty_like(kps)
+    _check(lib().orbx_undistort_keypoints(self._h, _p(kps), len(kps), C.c_float(fx), C.c_float(fy), C.c_float(cx), C.c_float(cy), _p(d),
+                                          _p(out), MEM_HOST, None))
+    return out
+
+
+def _is_in_frustum(self, cam, P, normal, max_dist, min_dist):
+    """Frame::isInFrustum (src/Frame.cc:572-642) over n map points -> dict of the MapPoint tracking fields."""
+    P = np.ascontiguousarray(P, np.float32).reshape(-1, 3)
+    normal = np.ascontiguousarray(normal, np.float32).reshape(-1, 3)
+    max_dist = np.ascontiguousarray(max_dist, np.float32)
+    min_dist = np.ascontiguousarray(min_dist, np.float32)
+    n = len(P)
+    o = dict(in_view=np.empty(n, np.uint8), proj_x=np.empty(n, np.float32), proj_y=np.empty(n, np.float32),
+             proj_xr=np.empty(n, np.float32), depth=np.empty(n, np.float32), level=np.empty(n, np.int32),
+             view_cos=np.empty(n, np.float32))
+    _check(lib().orbx_is_in_frustum(self._h, C.byref(cam), n, _p(P), _p(normal), _p(max_dist), _p(min_dist), _p(o["in_view"]),
+                                    _p(o["proj_x"]), _p(o["proj_y"]), _p(o["proj_xr"]), _p(o["depth"]), _p(o["level"]), _p(o["view_cos"]),
+                                    MEM_HOST, None))
+    return o
+
+
+Preprocessor.UndistortKeyPoints = _undistort
+Preprocessor.isInFrustum = _is_in_frustum

@@ -323,6 +323,33 @@ int orbx_remap(orbx_preproc* p, const orbx_remap_table* t, const uint8_t* src, i
 int orbx_clahe(orbx_preproc* p, const uint8_t* src, int nframes, int width, int height, int src_stride, long long src_frame_stride,
                double clip_limit, int tiles_x, int tiles_y, uint8_t* dst, int dst_stride, long long dst_frame_stride, int mem, void* stream);
 
+/* ---- Frame glue on either side of the path -----------------------------------------------------------
+ * Same handle, same mem / stream convention as the pre-processing calls above. */
+
+/* Frame::UndistortKeyPoints, src/Frame.cc:837-870 (and the four corners of ComputeImageBounds, :872-899):
+ * cv::undistortPoints(mat, mat, K, mDistCoef, cv::Mat(), mK) -- 5 fixed-point iterations in double, then re-projection with
+ * K.  dist5 = k1 k2 p1 p2 k3 (k3 = 0 for the 4-coefficient YAMLs).  Every other keypoint field is copied; when dist5[0] == 0
+ * the keypoints are copied unchanged as the reference does (:839-843).  kps_un may be kps. */
+int orbx_undistort_keypoints(orbx_preproc* p, const orbx_keypoint* kps, int n, float fx, float fy, float cx, float cy, const float* dist5,
+                             orbx_keypoint* kps_un, int mem, void* stream);
+
+/* Frame::isInFrustum (monocular / rectified-stereo branch, src/Frame.cc:572-642) with MapPoint::PredictScale
+ * (src/MapPoint.cc:587-602) and Pinhole::project (src/CameraModels/Pinhole.cpp:46-49) over n map points.  The outputs are the
+ * MapPoint fields the reference fills -- mbTrackInView, mTrackProjX, mTrackProjY, mTrackProjXR, mTrackDepth,
+ * mnTrackScaleLevel, mTrackViewCos -- and are exactly the inputs of orbx_search_by_projection_mappoints
+ * (Tracking::SearchLocalPoints, src/Tracking.cc:3490-3520).  Points that fail get in_view 0, level -1 and proj_x / proj_y -1
+ * unless they passed the image-bounds test (:577-578, :604-605). */
+typedef struct orbx_frustum {
+  float Rcw[9], tcw[3], Ow[3];          /* mRcw (row-major), mtcw, mOw */
+  float fx, fy, cx, cy;                 /* Pinhole parameters */
+  float min_x, max_x, min_y, max_y;     /* mnMinX .. mnMaxY */
+  float bf, log_scale_factor, viewing_cos_limit; /* mbf, mfLogScaleFactor, 0.5 at the call site */
+  int n_scale_levels;                   /* mnScaleLevels */
+} orbx_frustum;
+int orbx_is_in_frustum(orbx_preproc* p, const orbx_frustum* cam, int n, const float* world_pos, const float* normal, const float* max_dist,
+                       const float* min_dist, uint8_t* in_view, float* proj_x, float* proj_y, float* proj_xr, float* depth, int* level,
+                       float* view_cos, int mem, void* stream);
+
 /* Page-locked host staging buffers for the *_host entry points (cudaHostAlloc).  Frames handed over in such a buffer upload at
  * the full link rate; memory pinned after the fact (cudaHostRegister of pageable pages, which is what e.g. torch's
  * pin_memory() produced on the test box) was measured at half of it (27 vs 55 GB/s host-to-device on PCIe 5 x16).  The

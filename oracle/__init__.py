@@ -21,7 +21,7 @@ assert KP_DTYPE.itemsize == 28
 
 
 def build(force=False):
-    srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.cc", "match_oracle.cc", "oracle_capi.cc", "preproc_oracle.cc", "orb_oracle.h",
+    srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.cc", "match_oracle.cc", "oracle_capi.cc", "preproc_oracle.cc", "frame_oracle.cc", "orb_oracle.h",
                                              "match_oracle.h", "Makefile")]
     if force or not os.path.exists(_LIB) or any(os.path.getmtime(s) > os.path.getmtime(_LIB) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-B", "liborb_oracle.so"], stdout=subprocess.DEVNULL)
@@ -394,3 +394,39 @@ def clahe(src, clip_limit=3.0, tiles=(8, 8)):
     dst = np.empty((h, w), np.uint8)
     lib().oro_clahe(_p(src), w, h, w, C.c_double(clip_limit), int(tiles[0]), int(tiles[1]), _p(dst), w)
     return dst
+
+
+# ---- Frame glue (oracle/frame_oracle.cc) -----------------------------------------------------------
+LOG_LIBM_F32, LOG_PORTABLE = 0, 1
+
+
+class FrustumCam(C.Structure):
+    _fields_ = [("Rcw", C.c_float * 9), ("tcw", C.c_float * 3), ("Ow", C.c_float * 3), ("fx", C.c_float), ("fy", C.c_float),
+                ("cx", C.c_float), ("cy", C.c_float), ("minX", C.c_float), ("maxX", C.c_float), ("minY", C.c_float),
+                ("maxY", C.c_float), ("bf", C.c_float), ("logScaleFactor", C.c_float), ("viewingCosLimit", C.c_float),
+                ("nScaleLevels", C.c_int), ("logMode", C.c_int)]
+
+
+def undistort_points(pts, fx, fy, cx, cy, dist):
+    """cv::undistortPoints(mat, mat, K, D, Mat(), K) -- src/Frame.cc:856, 884."""
+    pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 2)
+    d = np.zeros(5, np.float32)
+    d[:len(dist)] = dist
+    out = np.empty_like(pts)
+    lib().oro_undistort_points(_p(pts), len(pts), C.c_float(fx), C.c_float(fy), C.c_float(cx), C.c_float(cy), _p(d), _p(out))
+    return out
+
+
+def is_in_frustum(cam, P, normal, max_dist, min_dist):
+    """Frame::isInFrustum (src/Frame.cc:572-642) over n map points; cam is a FrustumCam."""
+    P = np.ascontiguousarray(P, np.float32).reshape(-1, 3)
+    normal = np.ascontiguousarray(normal, np.float32).reshape(-1, 3)
+    max_dist = np.ascontiguousarray(max_dist, np.float32)
+    min_dist = np.ascontiguousarray(min_dist, np.float32)
+    n = len(P)
+    out = dict(in_view=np.empty(n, np.uint8), proj_x=np.empty(n, np.float32), proj_y=np.empty(n, np.float32),
+               proj_xr=np.empty(n, np.float32), depth=np.empty(n, np.float32), level=np.empty(n, np.int32),
+               view_cos=np.empty(n, np.float32))
+    lib().oro_is_in_frustum(C.byref(cam), n, _p(P), _p(normal), _p(max_dist), _p(min_dist), _p(out["in_view"]), _p(out["proj_x"]),
+                            _p(out["proj_y"]), _p(out["proj_xr"]), _p(out["depth"]), _p(out["level"]), _p(out["view_cos"]))
+    return out
