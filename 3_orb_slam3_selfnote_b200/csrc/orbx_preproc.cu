@@ -223,7 +223,7 @@ int orbx_remap(orbx_preproc* p, const orbx_remap_table* t, const uint8_t* src, i
   A.sw = t->sw; A.sh = t->sh; A.dw = t->dw; A.dh = t->dh; A.sstride = src_stride; A.dstride = dst_stride;
   A.sfs = src_frame_stride; A.dfs = dst_frame_stride;
   A.vecDst = aligned(S.dDst, dst_stride, dst_frame_stride, 4);
-  dim3 grid((t->dw + 1023) / 1024, (t->dh + ORBX_REMAP_ROWS - 1) / ORBX_REMAP_ROWS, nframes);
+  dim3 grid((t->dw + 1023) / 1024, t->dh, nframes);
   k_remap<<<grid, 256, 0, S.st>>>(A);
   return S.finish();
 }

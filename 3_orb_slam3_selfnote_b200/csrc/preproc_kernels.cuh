@@ -86,79 +86,44 @@ struct RemapArgs {
   int vecDst;
 };
 
-// OpenCV's table weights are (32-fx)(32-fy)*32 ... (2^15 scale): factor the common 32 out, (32*T + 2^14) >> 15 == (T + 512) >> 10
-__device__ __forceinline__ unsigned remap_blend(unsigned p00, unsigned p01, unsigned p10, unsigned p11, uint32_t t) {
-  const unsigned fx = t & 31u, fy = (t >> 16) & 31u;  // the +32 bias of the packed form leaves the low 5 bits alone
-  const unsigned top = p00 * (32u - fx) + p01 * fx, bot = p10 * (32u - fx) + p11 * fx;
-  return (top * (32u - fy) + bot * fy + 512u) >> 10;
+// Thread = 4 adjacent destination pixels of one row, one table word (uint4) and 16 one-byte gathers.  ncu (profiles/
+// r01f_preproc_ncu_summary.csv): bound by the L1 -- l1tex 74 %, 8 sectors per request, LSU-queue (lg_throttle) stalls -- not by
+// HBM (DRAM 7 %).  Variants measured on the B200 per 256 frames of 752x480 and dropped: 4 rows per thread with branch-free
+// clamped addresses 0.32 ms, 2 rows + warp-uniform interior fast path 0.27 ms, 1 row + fast path 0.25 ms, this one 0.19 ms:
+// deeper per-thread load queues only lengthen the LSU queue.  The step that would change the bound is a shared-memory
+// staged source tile per CTA (bounding box of the tile's table entries), left for the next round.
+__device__ __forceinline__ unsigned remap_px(const uint8_t* __restrict__ S, uint32_t t, const RemapArgs& A) {
+  const int sx = (int)(t & 0xffffu) - 32, sy = (int)(t >> 16) - 32;
+  const int ix = sx >> 5, iy = sy >> 5, fx = sx & 31, fy = sy & 31;
+  unsigned p00, p01, p10, p11;
+  if ((unsigned)ix < (unsigned)(A.sw - 1) && (unsigned)iy < (unsigned)(A.sh - 1)) {
+    const uint8_t* r = S + (long long)iy * A.sstride + ix;
+    p00 = __ldg(r); p01 = __ldg(r + 1); p10 = __ldg(r + A.sstride); p11 = __ldg(r + A.sstride + 1);
+  } else {
+    const bool x0 = (unsigned)ix < (unsigned)A.sw, x1 = (unsigned)(ix + 1) < (unsigned)A.sw;
+    const bool y0 = (unsigned)iy < (unsigned)A.sh, y1 = (unsigned)(iy + 1) < (unsigned)A.sh;
+    const uint8_t* r = S + (long long)iy * A.sstride + ix;
+    p00 = (x0 && y0) ? __ldg(r) : 0u; p01 = (x1 && y0) ? __ldg(r + 1) : 0u;
+    p10 = (x0 && y1) ? __ldg(r + A.sstride) : 0u; p11 = (x1 && y1) ? __ldg(r + A.sstride + 1) : 0u;
+  }
+  // weights (32-fx)(32-fy)*32 ... scaled by 2^15 in OpenCV's table: factor the common 32 out, (sum*32 + 2^14) >> 15 == (sum + 512) >> 10
+  const unsigned top = p00 * (32 - fx) + p01 * fx, bot = p10 * (32 - fx) + p11 * fx;
+  return (top * (32 - fy) + bot * fy + 512u) >> 10;
 }
 
-// Thread = 4 adjacent destination pixels (x REMAP_ROWS rows): the table word(s), then all 16 tap loads, are issued before the
-// first blend.  Warps whose 2x2 footprints all lie inside the image (all but those on the rectified image's rim) take a path
-// without clamps or masks: one 32-bit offset per entry, four byte loads.  The kernel is bound by the L1 (ncu: l1tex 74 %, 8
-// sectors per request, LSU queue stalls): 16 one-byte gathers per thread.  More rows per thread (2, 4) only deepened the LSU
-// queue and lost occupancy (0.19 -> 0.27 / 0.32 ms per 256 frames), so ROWS stays 1; the next step is a shared-memory staged
-// source tile per CTA.
-#define ORBX_REMAP_ROWS 1
 __global__ void __launch_bounds__(256) k_remap(const __grid_constant__ RemapArgs A) {
-  const int x4 = (blockIdx.x * 256 + threadIdx.x) * 4, y0 = blockIdx.y * ORBX_REMAP_ROWS;
-  const bool live = x4 < A.dw;
-  const uint8_t* __restrict__ S = A.src + (long long)blockIdx.z * A.sfs;
-  const int nr = min(ORBX_REMAP_ROWS, A.dh - y0);
-  uint32_t t[ORBX_REMAP_ROWS][4];
-  bool interior = true;
-#pragma unroll
-  for (int r = 0; r < ORBX_REMAP_ROWS; ++r) {
-    // rows / columns past the end carry an interior dummy entry (pixel 0,0) that is never stored
-    const uint4 q = (live && r < nr) ? __ldg(reinterpret_cast<const uint4*>(A.table + (long long)(y0 + r) * A.tpitch + x4))
-                                     : make_uint4(0x00200020u, 0x00200020u, 0x00200020u, 0x00200020u);
-    t[r][0] = q.x; t[r][1] = q.y; t[r][2] = q.z; t[r][3] = q.w;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int ix = (int)((t[r][i] & 0xffffu) >> 5) - 1, iy = (int)(t[r][i] >> 21) - 1;
-      interior = interior && (unsigned)ix < (unsigned)(A.sw - 1) && (unsigned)iy < (unsigned)(A.sh - 1);
-    }
-  }
-  unsigned p[ORBX_REMAP_ROWS][4][4];
-  if (__all_sync(0xffffffffu, interior)) {
-#pragma unroll
-    for (int r = 0; r < ORBX_REMAP_ROWS; ++r)
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int ix = (int)((t[r][i] & 0xffffu) >> 5) - 1, iy = (int)(t[r][i] >> 21) - 1;
-        const uint8_t* a = S + (unsigned)(iy * A.sstride + ix);
-        const uint8_t* b = a + A.sstride;
-        p[r][i][0] = __ldg(a); p[r][i][1] = __ldg(a + 1); p[r][i][2] = __ldg(b); p[r][i][3] = __ldg(b + 1);
-      }
+  const int x4 = (blockIdx.x * 256 + threadIdx.x) * 4, y = blockIdx.y;
+  if (x4 >= A.dw) return;
+  const uint8_t* S = A.src + (long long)blockIdx.z * A.sfs;
+  uint8_t* d = A.dst + (long long)blockIdx.z * A.dfs + (long long)y * A.dstride + x4;
+  const uint4 t = __ldg(reinterpret_cast<const uint4*>(A.table + (long long)y * A.tpitch + x4));
+  if (A.vecDst && x4 + 4 <= A.dw) {
+    unsigned v = remap_px(S, t.x, A) | (remap_px(S, t.y, A) << 8) | (remap_px(S, t.z, A) << 16) | (remap_px(S, t.w, A) << 24);
+    *reinterpret_cast<unsigned*>(d) = v;
   } else {
-#pragma unroll
-    for (int r = 0; r < ORBX_REMAP_ROWS; ++r)
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int ix = (int)((t[r][i] & 0xffffu) >> 5) - 1, iy = (int)(t[r][i] >> 21) - 1;
-        const bool x0 = (unsigned)ix < (unsigned)A.sw, x1 = (unsigned)(ix + 1) < (unsigned)A.sw;
-        const bool v0 = (unsigned)iy < (unsigned)A.sh, v1 = (unsigned)(iy + 1) < (unsigned)A.sh;
-        const uint8_t* a = S + (long long)iy * A.sstride + ix;
-        p[r][i][0] = (x0 && v0) ? __ldg(a) : 0u; p[r][i][1] = (x1 && v0) ? __ldg(a + 1) : 0u;
-        p[r][i][2] = (x0 && v1) ? __ldg(a + A.sstride) : 0u; p[r][i][3] = (x1 && v1) ? __ldg(a + A.sstride + 1) : 0u;
-      }
-  }
-  if (!live) return;
-  uint8_t* d = A.dst + (long long)blockIdx.z * A.dfs + (long long)y0 * A.dstride + x4;
-#pragma unroll
-  for (int r = 0; r < ORBX_REMAP_ROWS; ++r) {
-    if (r < nr) {
-      uint8_t* dr = d + (long long)r * A.dstride;
-      unsigned o[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) o[i] = remap_blend(p[r][i][0], p[r][i][1], p[r][i][2], p[r][i][3], t[r][i]);
-      if (A.vecDst && x4 + 4 <= A.dw) {
-        *reinterpret_cast<unsigned*>(dr) = o[0] | (o[1] << 8) | (o[2] << 16) | (o[3] << 24);
-      } else {
-        const int n = min(4, A.dw - x4);
-        for (int i = 0; i < n; ++i) dr[i] = (uint8_t)o[i];
-      }
-    }
+    const uint32_t tt[4] = {t.x, t.y, t.z, t.w};
+    const int n = min(4, A.dw - x4);
+    for (int i = 0; i < n; ++i) d[i] = (uint8_t)remap_px(S, tt[i], A);
   }
 }
 
