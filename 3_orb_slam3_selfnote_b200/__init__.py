@@ -256,4 +256,4 @@ def DescriptorDistance(a, b):
     return lib().orbx_hamming(_p(a), _p(b))
 
 
-from .matcher import FrameView, ORBmatcher, ORBVocabulary  # noqa: E402,F401  (mirror of include/ORBmatcher.h)
+from .matcher import FrameView, LocalMap, ORBmatcher, ORBVocabulary  # noqa: E402,F401  (mirror of include/ORBmatcher.h)

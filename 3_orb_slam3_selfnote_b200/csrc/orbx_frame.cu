@@ -13,6 +13,7 @@
 #include <math.h>
 
 #include "../../include/orbx.h"
+#include "frustum.cuh"
 #include "orbx_internal.h"
 
 using namespace orbx;
@@ -65,39 +66,10 @@ struct FrustumArgs {
 __global__ void __launch_bounds__(256) k_frustum(const __grid_constant__ FrustumArgs A) {
   const int i = blockIdx.x * 256 + threadIdx.x;
   if (i >= A.n) return;
-  const orbx_frustum& C = A.cam;
-  uint8_t in = 0; float px = -1.f, py = -1.f, pxr = 0.f, dep = 0.f, vc = 0.f; int lvl = -1;
-  const float p0 = A.P[3 * i], p1 = A.P[3 * i + 1], p2 = A.P[3 * i + 2];
-  float Pc[3];
-#pragma unroll
-  for (int r = 0; r < 3; ++r) {
-    const float t = __fadd_rn(__fadd_rn(__fmul_rn(C.Rcw[3 * r], p0), __fmul_rn(C.Rcw[3 * r + 1], p1)), __fmul_rn(C.Rcw[3 * r + 2], p2));
-    Pc[r] = __fadd_rn(t, C.tcw[r]);
-  }
-  const float PcDist = (float)sqrt((double)Pc[0] * Pc[0] + (double)Pc[1] * Pc[1] + (double)Pc[2] * Pc[2]);
-  const float invz = __fdiv_rn(1.0f, Pc[2]);
-  do {
-    if (Pc[2] < 0.0f) break;
-    const float ux = __fadd_rn(__fdiv_rn(__fmul_rn(C.fx, Pc[0]), Pc[2]), C.cx);
-    const float uy = __fadd_rn(__fdiv_rn(__fmul_rn(C.fy, Pc[1]), Pc[2]), C.cy);
-    if (ux < C.min_x || ux > C.max_x) break;
-    if (uy < C.min_y || uy > C.max_y) break;
-    px = ux; py = uy;
-    const float o0 = __fsub_rn(p0, C.Ow[0]), o1 = __fsub_rn(p1, C.Ow[1]), o2 = __fsub_rn(p2, C.Ow[2]);
-    const float dist = (float)sqrt((double)o0 * o0 + (double)o1 * o1 + (double)o2 * o2);
-    const float mx = A.maxDist[i], mn = A.minDist[i];
-    if (dist < mn || dist > mx) break;
-    const double dot = (double)o0 * A.normal[3 * i] + (double)o1 * A.normal[3 * i + 1] + (double)o2 * A.normal[3 * i + 2];
-    const float viewCos = (float)(dot / (double)dist);
-    if (viewCos < C.viewing_cos_limit) break;
-    const float ratio = __fdiv_rn(mx, dist);
-    const float lg = (float)log((double)ratio);
-    int nScale = (int)ceilf(__fdiv_rn(lg, C.log_scale_factor));
-    if (nScale < 0) nScale = 0;
-    else if (nScale >= C.n_scale_levels) nScale = C.n_scale_levels - 1;
-    in = 1; pxr = __fsub_rn(ux, __fmul_rn(C.bf, invz)); dep = PcDist; lvl = nScale; vc = viewCos;
-  } while (0);
-  A.inView[i] = in; A.projX[i] = px; A.projY[i] = py; A.projXR[i] = pxr; A.depth[i] = dep; A.level[i] = lvl; A.viewCos[i] = vc;
+  const FrustumOut o = frustum_point(A.cam, A.P[3 * i], A.P[3 * i + 1], A.P[3 * i + 2], A.normal[3 * i], A.normal[3 * i + 1], A.normal[3 * i + 2],
+                                     A.maxDist[i], A.minDist[i]);
+  A.inView[i] = o.inView; A.projX[i] = o.projX; A.projY[i] = o.projY; A.projXR[i] = o.projXR; A.depth[i] = o.depth; A.level[i] = o.level;
+  A.viewCos[i] = o.viewCos;
 }
 
 inline size_t al16(size_t v) { return (v + 15) & ~(size_t)15; }

@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <vector>
 
+#include "frustum.cuh"
 #include "match_kernels.cuh"
 #include "orbx_internal.h"
 
@@ -428,6 +429,176 @@ int orbx_search_by_projection_mappoints_batch(orbx_matcher* m, orbx_extractor* e
     J.kpMp = kpMp + (size_t)f * capPerFrame; J.kpMpLen = counts[f]; J.nnratio = nnratio; J.nmatches = nmatches + f;
   }
   return run_window_jobs(m, jobs, RESOLVE_MAPPOINTS);
+}
+
+// ---- Tracking::SearchLocalPoints over a batch of frames, device-resident ---------------------------
+// The local map (positions, normals, distance ranges, descriptors) is uploaded once; per frame only its pose travels.
+// k_local_point_queries runs Frame::isInFrustum for every (frame, map point) pair and writes the window queries of
+// SearchByProjection straight into the arena the candidate / resolve kernels read -- no per-frame host staging, one
+// synchronisation per batch.
+}  // extern "C"
+
+struct orbx_local_map {
+  int device = 0, nmp = 0;
+  float* pos = nullptr; float* normal = nullptr; float* maxDist = nullptr; float* minDist = nullptr;
+  uint8_t* desc = nullptr; uint8_t* observed = nullptr;
+};
+
+namespace {
+struct LocalPointArgs {
+  const orbx_frustum* cams; const float* pos; const float* normal; const float* maxDist; const float* minDist;
+  int nmp, nlevels, kpStride, cap;
+  float th; int bFactor;
+  const float* scale;
+  GridFrame* frames; const QuerySet* sets; const int* counts; int* status;
+};
+
+// grid (ceil(nmp / 256), nframes): ORBmatcher.cc:52-73 (radius by viewing cosine, predicted level window) on top of isInFrustum
+__global__ void __launch_bounds__(256) k_local_point_queries(const __grid_constant__ LocalPointArgs A) {
+  __shared__ orbx_frustum cam;
+  const int f = blockIdx.y;
+  for (int i = threadIdx.x; i < (int)(sizeof(orbx_frustum) / 4); i += 256) reinterpret_cast<int*>(&cam)[i] = reinterpret_cast<const int*>(A.cams + f)[i];
+  __syncthreads();
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    const int n = A.counts[f];
+    if (n > A.cap || n > kMaxKpSmem) atomicExch(A.status, ORBX_ERR_CAPACITY);
+    A.frames[f].n = min(n, min(A.cap, kMaxKpSmem));
+  }
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= A.nmp) return;
+  const orbx::FrustumOut o = orbx::frustum_point(cam, A.pos[3 * i], A.pos[3 * i + 1], A.pos[3 * i + 2], A.normal[3 * i], A.normal[3 * i + 1],
+                                                 A.normal[3 * i + 2], A.maxDist[i], A.minDist[i]);
+  const QuerySet Q = A.sets[f];
+  const int lvl = o.level;
+  const bool ok = o.inView != 0 && lvl >= 0 && lvl < A.nlevels;
+  float r = (o.viewCos > 0.998) ? 2.5f : 4.0f;
+  if (A.bFactor) r = __fmul_rn(r, A.th);
+  const_cast<uint8_t*>(Q.valid)[i] = ok ? 1 : 0;
+  const_cast<float*>(Q.x)[i] = o.projX; const_cast<float*>(Q.y)[i] = o.projY;
+  const_cast<float*>(Q.r)[i] = ok ? __fmul_rn(r, A.scale[lvl]) : 0.f;
+  const_cast<int8_t*>(Q.minL)[i] = (int8_t)(lvl - 1); const_cast<int8_t*>(Q.maxL)[i] = (int8_t)lvl;
+}
+}  // namespace
+
+extern "C" {
+
+int orbx_local_map_create(orbx_matcher* m, int nmp, const float* world_pos, const float* normal, const float* max_dist,
+                          const float* min_dist, const uint8_t* desc, const uint8_t* observed, orbx_local_map** out) {
+  if (!m || !out || nmp < 1 || !world_pos || !normal || !max_dist || !min_dist || !desc) { set_error("local map: bad argument"); return ORBX_ERR_ARG; }
+  *out = nullptr;
+  std::lock_guard<std::recursive_mutex> setupLock(setup_mutex());
+  CK(cudaSetDevice(m->device));
+  orbx_local_map* L = new (std::nothrow) orbx_local_map();
+  if (!L) return ORBX_ERR_ARG;
+  L->device = m->device; L->nmp = nmp;
+  auto put = [&](void** d, const void* h, size_t bytes) -> cudaError_t {
+    cudaError_t e = cudaMalloc(d, bytes);
+    return e != cudaSuccess ? e : cudaMemcpy(*d, h, bytes, cudaMemcpyHostToDevice);
+  };
+  cudaError_t e = put((void**)&L->pos, world_pos, (size_t)nmp * 12);
+  if (e == cudaSuccess) e = put((void**)&L->normal, normal, (size_t)nmp * 12);
+  if (e == cudaSuccess) e = put((void**)&L->maxDist, max_dist, (size_t)nmp * 4);
+  if (e == cudaSuccess) e = put((void**)&L->minDist, min_dist, (size_t)nmp * 4);
+  if (e == cudaSuccess) e = put((void**)&L->desc, desc, (size_t)nmp * 32);
+  if (e == cudaSuccess && observed) e = put((void**)&L->observed, observed, (size_t)nmp);
+  if (e != cudaSuccess) {
+    set_error("local map upload: %s", cudaGetErrorString(e));
+    orbx_local_map_destroy(L);
+    return ORBX_ERR_CUDA;
+  }
+  *out = L;
+  return ORBX_OK;
+}
+
+void orbx_local_map_destroy(orbx_local_map* L) {
+  if (!L) return;
+  std::lock_guard<std::recursive_mutex> setupLock(setup_mutex());
+  cudaSetDevice(L->device);
+  cudaFree(L->pos); cudaFree(L->normal); cudaFree(L->maxDist); cudaFree(L->minDist); cudaFree(L->desc); cudaFree(L->observed);
+  delete L;
+}
+
+int orbx_search_local_points_batch(orbx_matcher* m, orbx_extractor* ex, int nframes, const orbx_frustum* frames, const orbx_local_map* map,
+                                   float th, float nnratio, int* kpMp, int capPerFrame, int* nmatches, void* stream) {
+  if (!m || !ex || !ex->haveGeom || nframes < 1 || !frames || !map || !kpMp || !nmatches || capPerFrame < 1) { set_error("search_local_points: bad argument"); return ORBX_ERR_ARG; }
+  if (map->device != m->device) { set_error("local map lives on another device"); return ORBX_ERR_ARG; }
+  Slot& s = ex->slot[ex->lastSlot];
+  if (nframes > s.lastFrames) { set_error("extractor holds %d frames", s.lastFrames); return ORBX_ERR_ARG; }
+  CK(cudaSetDevice(m->device));
+  const int nq = map->nmp, kpStride = ex->g.kpStride, nlevels = ex->p.nlevels;
+  const int nmax = std::min(kpStride, kMaxKpSmem);
+  // ---- arena: per-frame regions are laid out frame after frame so that the clears and the downloads are single calls
+  ArenaPlan plan;
+  const size_t szCell = ((kGridCells + 1) * sizeof(int) + 255) & ~(size_t)255, szItems = ((size_t)nmax * 4 + 255) & ~(size_t)255;
+  const size_t szQ1 = ((size_t)nq + 255) & ~(size_t)255, szQ4 = ((size_t)nq * 4 + 255) & ~(size_t)255;
+  const int entryCap = (int)std::min<long long>((long long)nq * nmax, std::max<long long>(1 << 16, (long long)nq * 256));
+  const size_t szEntries = (size_t)entryCap * 8;
+  const size_t oCell = plan.add(szCell * nframes), oItems = plan.add(szItems * nframes);
+  const size_t oValid = plan.add(szQ1 * nframes), oMinL = plan.add(szQ1 * nframes), oMaxL = plan.add(szQ1 * nframes);
+  const size_t oX = plan.add(szQ4 * nframes), oY = plan.add(szQ4 * nframes), oR = plan.add(szQ4 * nframes);
+  const size_t oQOff = plan.add(szQ4 * nframes), oQCnt = plan.add(szQ4 * nframes), oAssigned = plan.add(szQ4 * nframes);
+  const size_t oEntries = plan.add(szEntries * nframes), oCursor = plan.add((size_t)nframes * 4);
+  const size_t oKpMp = plan.add((size_t)nframes * kpStride * 4), oNm = plan.add((size_t)nframes * 4);
+  const size_t oBlk0 = plan.add(szItems * nframes), oBlk1 = plan.add(szItems * nframes), oChg = plan.add((size_t)nframes * 8);
+  const size_t oScale = plan.add((size_t)nlevels * 4), oCams = plan.add((size_t)nframes * sizeof(orbx_frustum));
+  const size_t oFrames = plan.add(nframes * sizeof(GridFrame)), oSets = plan.add(nframes * sizeof(QuerySet)), oArgs = plan.add(nframes * sizeof(ResolveArgs));
+  int rc = arena_ensure(m, plan.total);
+  if (rc != ORBX_OK) return rc;
+  cudaStream_t st = stream ? (cudaStream_t)stream : m->stream;
+  if (!stream) CK(cudaDeviceSynchronize());  // the extractor batch may be in flight on another stream
+  std::vector<GridFrame> G(nframes);
+  std::vector<QuerySet> Q(nframes);
+  std::vector<ResolveArgs> R(nframes);
+  for (int f = 0; f < nframes; f++) {
+    const orbx_frustum& C = frames[f];
+    if (!(C.max_x > C.min_x) || !(C.max_y > C.min_y)) { set_error("frame %d: empty image bounds", f); return ORBX_ERR_ARG; }
+    G[f].kps = s.kps + (size_t)f * kpStride; G[f].desc = s.desc + (size_t)f * kpStride * 32; G[f].uRight = nullptr; G[f].n = 0;  // n: device
+    G[f].minX = C.min_x; G[f].minY = C.min_y;
+    G[f].invW = (float)kGridCols / (C.max_x - C.min_x); G[f].invH = (float)kGridRows / (C.max_y - C.min_y);  // Frame.cc:160-161
+    G[f].cellStart = at<int>(m, oCell + f * szCell); G[f].cellItems = at<int>(m, oItems + f * szItems);
+    QuerySet& q = Q[f];
+    q = QuerySet{};
+    q.nq = nq;
+    q.valid = at<uint8_t>(m, oValid + f * szQ1); q.minL = at<int8_t>(m, oMinL + f * szQ1); q.maxL = at<int8_t>(m, oMaxL + f * szQ1);
+    q.x = at<float>(m, oX + f * szQ4); q.y = at<float>(m, oY + f * szQ4); q.r = at<float>(m, oR + f * szQ4);
+    q.xr = nullptr; q.desc = map->desc; q.xrCheck = 0; q.gate = 0; q.invSigma2 = nullptr;
+    q.qOff = at<int>(m, oQOff + f * szQ4); q.qCnt = at<int>(m, oQCnt + f * szQ4);
+    q.entries = at<unsigned long long>(m, oEntries + f * szEntries); q.entryCap = entryCap; q.entryCursor = at<int>(m, oCursor + (size_t)f * 4);
+    ResolveArgs& a = R[f];
+    a = ResolveArgs{};
+    a.observed = map->observed; a.angle = nullptr;
+    a.kpMp = at<int>(m, oKpMp + (size_t)f * kpStride * 4); a.assigned = at<int>(m, oAssigned + f * szQ4);
+    a.nmatches = at<int>(m, oNm + (size_t)f * 4);
+    a.blk[0] = at<int>(m, oBlk0 + f * szItems); a.blk[1] = at<int>(m, oBlk1 + f * szItems); a.chg = at<int>(m, oChg + (size_t)f * 8);
+    a.nnratio = nnratio; a.distTh = 100; a.anyMpBlocks = 0; a.checkOrientation = 0;
+  }
+  CK(cudaMemcpyAsync(m->arena + oFrames, G.data(), nframes * sizeof(GridFrame), cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(m->arena + oSets, Q.data(), nframes * sizeof(QuerySet), cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(m->arena + oArgs, R.data(), nframes * sizeof(ResolveArgs), cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(m->arena + oCams, frames, nframes * sizeof(orbx_frustum), cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(m->arena + oScale, ex->scale.data(), (size_t)nlevels * 4, cudaMemcpyHostToDevice, st));
+  CK(cudaMemsetAsync(m->arena + oCursor, 0, (size_t)nframes * 4, st));
+  CK(cudaMemsetAsync(m->arena + oKpMp, 0xff, (size_t)nframes * kpStride * 4, st));  // mvpMapPoints all empty (-1)
+  CK(cudaMemsetAsync(m->dStatus, 0, sizeof(int), st));
+  LocalPointArgs A{};
+  A.cams = at<orbx_frustum>(m, oCams); A.pos = map->pos; A.normal = map->normal; A.maxDist = map->maxDist; A.minDist = map->minDist;
+  A.nmp = nq; A.nlevels = nlevels; A.kpStride = kpStride; A.cap = std::min(capPerFrame, nmax);
+  A.th = th; A.bFactor = th != 1.0f; A.scale = at<float>(m, oScale);
+  A.frames = at<GridFrame>(m, oFrames); A.sets = at<QuerySet>(m, oSets); A.counts = s.counts; A.status = m->dStatus;
+  k_local_point_queries<<<dim3((nq + 255) / 256, nframes), 256, 0, st>>>(A);
+  k_build_grid<<<nframes, 256, 0, st>>>(A.frames);
+  k_window_candidates<<<dim3((nq + 7) / 8, nframes), 256, 0, st>>>(A.frames, A.sets, m->dStatus);
+  if (m->resolveSeq) k_resolve_mappoints<<<nframes, 32, 0, st>>>(A.frames, A.sets, at<ResolveArgs>(m, oArgs));
+  else k_resolve_par<<<dim3(kParCluster, nframes), kParThreads, 0, st>>>(A.frames, A.sets, at<ResolveArgs>(m, oArgs), 0);
+  CK(cudaGetLastError());
+  int status = 0;
+  CK(cudaMemcpyAsync(&status, m->dStatus, sizeof(int), cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpy2DAsync(kpMp, (size_t)capPerFrame * 4, m->arena + oKpMp, (size_t)kpStride * 4, (size_t)std::min(capPerFrame, kpStride) * 4, nframes,
+                       cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(nmatches, m->arena + oNm, (size_t)nframes * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  if (status != 0) { set_error(status == ORBX_ERR_CAPACITY ? "a frame's keypoints or candidate list exceed the capacity" : "search_local_points failed"); return status; }
+  return ORBX_OK;
 }
 
 int orbx_search_by_projection_window(orbx_matcher* m, const orbx_frame_view* F, int n, const uint8_t* valid, const float* u, const float* v,

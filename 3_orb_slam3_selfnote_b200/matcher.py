@@ -301,3 +301,44 @@ class ORBVocabulary:
         for nd in nodes:
             ind.extend(idx[nid[idx] == nd].tolist()); start.append(len(ind))
         return ids.astype(np.uint32), vals, (nodes.astype(np.uint32), np.array(start, np.int32), np.array(ind, np.uint32))
+
+
+class LocalMap:
+    """Device-resident local map for ORBmatcher.SearchLocalPointsBatch (Tracking::mvpLocalMapPoints as structure-of-arrays)."""
+
+    def __init__(self, matcher, world_pos, normal, max_dist, min_dist, desc, observed=None):
+        world_pos = np.ascontiguousarray(world_pos, np.float32).reshape(-1, 3)
+        normal = np.ascontiguousarray(normal, np.float32).reshape(-1, 3)
+        max_dist, min_dist, desc, observed = _f32(max_dist), _f32(min_dist), _u8(desc), _u8(observed)
+        self.n = len(world_pos)
+        self._l = C.c_void_p()
+        _check(lib().orbx_local_map_create(matcher._m, self.n, _p(world_pos), _p(normal), _p(max_dist), _p(min_dist), _p(desc),
+                                           _p(observed), C.byref(self._l)))
+
+    def close(self):
+        if getattr(self, "_l", None) and self._l.value:
+            lib().orbx_local_map_destroy(self._l)
+            self._l = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _search_local_points_batch(self, extractor, nframes, frustums, local_map, th=1.0, stream=None):
+    """Tracking::SearchLocalPoints for the frames of `extractor`'s last device batch; frustums = list of preproc.frustum(...)
+    -> (nmatches[nframes], kp_mp[nframes, cap])"""
+    from .preproc import _Frustum
+    arr = (_Frustum * nframes)(*frustums)
+    h, w = extractor._last_shape
+    cap = extractor.max_keypoints(w, h)
+    kp_mp = np.empty((nframes, cap), np.int32)
+    nm = np.zeros(nframes, np.int32)
+    _check(lib().orbx_search_local_points_batch(self._m, extractor._h, nframes, arr, local_map._l, C.c_float(th), C.c_float(self.mfNNratio),
+                                                _p(kp_mp), cap, _p(nm), C.c_void_p(stream or 0)))
+    return nm, kp_mp
+
+
+ORBmatcher.SearchLocalPointsBatch = _search_local_points_batch

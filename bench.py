@@ -227,6 +227,28 @@ def extra_configs(orbx, synth, torch, stream, local, steps):
     sec = timed(tum_step, max(2, steps // 2))
     out["tumvi512_extract_nfeat1500+SearchByProjection_5000mp_frames_per_s_per_gpu"] = n / sec
     out["tumvi512_matches_per_frame"] = float(np.mean(nm_holder["nm"]))
+    # the same shape through the device-resident path: the 5000-point local map stays in HBM, per frame only
+    # the pose goes in; isInFrustum + SearchByProjection run on the extractor's stream, kp_mp / nmatches come back once per batch
+    pre_mod = importlib.import_module("3_orb_slam3_selfnote_b200.preproc")
+    fx, fy, cx, cy = np.float32(190.978), np.float32(190.973), np.float32(254.93), np.float32(256.9)
+    zs = rng.uniform(1.0, 8.0, nmp)
+    P = np.stack([(px[0] - cx) / fx * zs, (py[0] - cy) / fy * zs, zs], 1).astype(np.float32)   # frame 0's map points, camera at the origin
+    dist = np.linalg.norm(P, axis=1)
+    scale = ex.GetScaleFactors()
+    maxd = (dist * scale[np.clip(lv[0], 0, 7)] * 1.1).astype(np.float32)
+    mind = (maxd / scale[7] * 0.8).astype(np.float32)
+    nrm = (P / dist[:, None]).astype(np.float32)
+    lm = orbx.LocalMap(mt, P, nrm, maxd, mind, md[0])
+    cams = [pre_mod.frustum(np.eye(3), np.zeros(3), fx, fy, cx, cy, (0, w, 0, h), 0.0, 1.2, 8) for _ in range(n)]
+
+    def tum_step_dev():
+        ex.extract_batch_device(dev.data_ptr(), n, w, h, w, w * h, (0, 0), sh)
+        nm_holder["nm_dev"] = mt.SearchLocalPointsBatch(ex, n, cams, lm, 1.0, sh)[0]
+
+    sec = timed(tum_step_dev, max(2, steps // 2))
+    out["tumvi512_extract_nfeat1500+SearchLocalPoints_5000mp_device_map_frames_per_s_per_gpu"] = n / sec
+    out["tumvi512_device_map_matches_per_frame"] = float(np.mean(nm_holder["nm_dev"]))
+    lm.close()
     ex.close(); mt.close()
     # all-pairs tile kernel: 16384 queries against 262144 train descriptors, running (best, second) keys
     nq, nt = 16384, 262144

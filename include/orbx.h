@@ -350,6 +350,21 @@ int orbx_is_in_frustum(orbx_preproc* p, const orbx_frustum* cam, int n, const fl
                        const float* min_dist, uint8_t* in_view, float* proj_x, float* proj_y, float* proj_xr, float* depth, int* level,
                        float* view_cos, int mem, void* stream);
 
+/* Tracking::SearchLocalPoints (src/Tracking.cc:3441-3525) over a batch of frames without host staging: the local map is
+ * uploaded once (orbx_local_map_create: MapPoint::GetWorldPos / GetNormal / GetMaxDistanceInvariance /
+ * GetMinDistanceInvariance / GetDescriptor, optional Observations() > 0 flags), then for the nframes frames whose keypoints
+ * `ex` holds on the device from its last orbx_extract_batch_device, frame f with pose / intrinsics frames[f]:
+ * isInFrustum(pMP, viewing_cos_limit) for every map point (Frame.cc:572-642) and SearchByProjection(F, vpMapPoints, th)
+ * (ORBmatcher.cc:44-142) with mvpMapPoints initially empty.  kp_mp[f * cap_per_frame + k] = index of the map point matched
+ * to keypoint k of frame f, or -1.  All kernels run on `stream` (pass the extractor's stream; NULL = the matcher's own
+ * stream after a device synchronisation); the call returns after the results have reached the host arrays. */
+typedef struct orbx_local_map orbx_local_map;
+int orbx_local_map_create(orbx_matcher* m, int nmp, const float* world_pos, const float* normal, const float* max_dist,
+                          const float* min_dist, const uint8_t* desc, const uint8_t* observed, orbx_local_map** out);
+void orbx_local_map_destroy(orbx_local_map* map);
+int orbx_search_local_points_batch(orbx_matcher* m, orbx_extractor* ex, int nframes, const orbx_frustum* frames, const orbx_local_map* map,
+                                   float th, float nnratio, int* kp_mp, int cap_per_frame, int* nmatches, void* stream);
+
 /* Page-locked host staging buffers for the *_host entry points (cudaHostAlloc).  Frames handed over in such a buffer upload at
  * the full link rate; memory pinned after the fact (cudaHostRegister of pageable pages, which is what e.g. torch's
  * pin_memory() produced on the test box) was measured at half of it (27 vs 55 GB/s host-to-device on PCIe 5 x16).  The

@@ -101,3 +101,69 @@ def test_frustum_feeds_search_by_projection(pre, orbx, oracle, synth):
     nm_g, kp_g = m.SearchByProjection(F, out["in_view"], out["proj_x"], out["proj_y"], out["level"], out["view_cos"], d, 1.0)
     assert nm_g == nm_o and np.array_equal(kp_g, kp_o) and nm_o > 400
     m.close()
+
+
+def _local_map_case(orbx, synth, pre, nframes, nmp, seed):
+    """frames on the device + a shared local map: the keypoints of frame 0 back-projected through frame 0's pose, padded with
+    random points; every frame sees the map from its own (slightly different) pose"""
+    import torch
+    W = H = 512
+    frames = synth.frames(W, H, seed, range(nframes), False)
+    dev = torch.from_numpy(frames).cuda()
+    gx = orbx.ORBextractor(1500, max_batch=nframes)
+    gx.extract_batch_device(dev.data_ptr(), nframes, W, H, W, W * H, (0, 0), 0)
+    torch.cuda.synchronize()
+    counts, _, kps, desc = gx.results_host(nframes)
+    rng = np.random.default_rng(seed)
+    fx, fy, cx, cy = np.float32(190.978), np.float32(190.973), np.float32(254.93), np.float32(256.9)  # TUM-VI cam0 (pinhole part)
+    R0, t0 = fc.pose(seed)
+    c0 = int(counts[0])
+    k0 = kps[0, :c0]
+    z = rng.uniform(1.0, 8.0, c0)
+    Pc = np.stack([(k0["x"] + 1.0 - cx) / fx * z, (k0["y"] - 1.0 - cy) / fy * z, z], 1)
+    P = ((Pc - t0) @ R0).astype(np.float32)
+    Ow0 = -(R0.T @ t0).astype(np.float32)
+    scale = gx.GetScaleFactors()
+    d0 = np.linalg.norm(P - Ow0, axis=1)
+    maxd = (d0 * scale[k0["octave"]] * 1.1).astype(np.float32)
+    npad = nmp - c0
+    Ppad = (((np.stack([rng.uniform(-3, 3, npad), rng.uniform(-3, 3, npad), rng.uniform(-1, 8, npad)], 1)) - t0) @ R0).astype(np.float32)
+    P = np.concatenate([P, Ppad]); maxd = np.concatenate([maxd, rng.uniform(2, 20, npad).astype(np.float32)])
+    mind = (maxd / scale[7] * 0.8).astype(np.float32)
+    nrm = (P - Ow0) / np.maximum(np.linalg.norm(P - Ow0, axis=1, keepdims=True), 1e-6) + rng.normal(size=(nmp, 3)) * 0.3
+    nrm = (nrm / np.linalg.norm(nrm, axis=1, keepdims=True)).astype(np.float32)
+    mdesc = np.concatenate([desc[0, :c0], rng.integers(0, 256, (npad, 32), dtype=np.uint8)])
+    observed = (rng.uniform(size=nmp) < 0.95).astype(np.uint8)
+    poses = []
+    for f in range(nframes):
+        dR, dt = fc.pose(1000 + f)
+        Rf = (np.eye(3) * (1 - 0.02 * (f > 0)) + 0.02 * (f > 0) * dR) @ R0   # not exactly orthonormal: irrelevant to the arithmetic
+        poses.append((Rf.astype(np.float32), (t0 + 0.01 * f * dt).astype(np.float32)))
+    cams = [pre.mod.frustum(Rf, tf, fx, fy, cx, cy, (0, W, 0, H), 0.0, 1.2, 8) for Rf, tf in poses]
+    return gx, (counts, kps, desc), (P, nrm, maxd, mind, mdesc, observed), poses, cams, (fx, fy, cx, cy, W, H)
+
+
+@pytest.mark.parametrize("nframes,nmp,th", [(6, 5000, 1.0), (3, 2500, 3.0)])
+def test_search_local_points_batch(pre, orbx, oracle, synth, nframes, nmp, th):
+    gx, (counts, kps, desc), (P, nrm, maxd, mind, mdesc, observed), poses, cams, (fx, fy, cx, cy, W, H) = \
+        _local_map_case(orbx, synth, pre, nframes, nmp, 31)
+    m = orbx.ORBmatcher(0.8)
+    lm = orbx.LocalMap(m, P, nrm, maxd, mind, mdesc, observed)
+    nm, kp_mp = m.SearchLocalPointsBatch(gx, nframes, cams, lm, th)
+    scale = gx.GetScaleFactors()
+    total = 0
+    for f in range(nframes):
+        Rf, tf = poses[f]
+        cam = oracle.FrustumCam()
+        cam.Rcw[:] = Rf.reshape(-1).tolist(); cam.tcw[:] = tf.tolist(); cam.Ow[:] = (-(Rf.T @ tf).astype(np.float32)).tolist()
+        cam.fx, cam.fy, cam.cx, cam.cy = fx, fy, cx, cy
+        cam.minX, cam.maxX, cam.minY, cam.maxY = 0, W, 0, H
+        cam.bf, cam.logScaleFactor, cam.viewingCosLimit, cam.nScaleLevels, cam.logMode = 0.0, float(np.log(np.float32(1.2))), 0.5, 8, 1
+        fr = oracle.is_in_frustum(cam, P, nrm, maxd, mind)
+        c = int(counts[f])
+        nm_o, kp_o = oracle.search_by_projection_mappoints(kps[f, :c], desc[f, :c], scale, W, H, fr["in_view"], fr["proj_x"], fr["proj_y"],
+                                                           fr["level"], fr["view_cos"], mdesc, th, 0.8, observed=observed)
+        assert nm[f] == nm_o and np.array_equal(kp_mp[f, :c], kp_o), f
+        total += nm_o
+    assert total > 300 * nframes // 2
+    lm.close(), m.close(), gx.close()
