@@ -1,6 +1,7 @@
 // C-ABI of the pre-processing step (include/orbx.h, "pre-processing" section): colour -> gray, remap, CLAHE.
 // Host orchestration only; the arithmetic is in preproc_kernels.cuh.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <new>
@@ -223,8 +224,10 @@ int orbx_remap(orbx_preproc* p, const orbx_remap_table* t, const uint8_t* src, i
   A.sw = t->sw; A.sh = t->sh; A.dw = t->dw; A.dh = t->dh; A.sstride = src_stride; A.dstride = dst_stride;
   A.sfs = src_frame_stride; A.dfs = dst_frame_stride;
   A.vecDst = aligned(S.dDst, dst_stride, dst_frame_stride, 4);
-  dim3 grid((t->dw + 1023) / 1024, t->dh, nframes);
-  k_remap<<<grid, 256, 0, S.st>>>(A);
+  A.vecSrc = aligned(S.dSrc, src_stride, src_frame_stride, 4);
+  static const bool tiled = getenv("ORBX_REMAP_TILE") != nullptr;   // A/B only: shared-memory staged source tiles (measured slower)
+  if (tiled) k_remap_tile<<<dim3((t->dw + ORBX_RT_W - 1) / ORBX_RT_W, (t->dh + ORBX_RT_H - 1) / ORBX_RT_H, nframes), 256, 0, S.st>>>(A);
+  else k_remap<<<dim3((t->dw + 1023) / 1024, t->dh, nframes), 256, 0, S.st>>>(A);
   return S.finish();
 }
 

@@ -269,6 +269,30 @@ def extra_configs(orbx, synth, torch, stream, local, steps):
     return out
 
 
+def _bind_to_gpu_numa_node(torch, local):
+    """Multi-rank runs: pin this rank (and the e2e worker threads it starts) to the CPUs of the NUMA node its GPU hangs off, so
+    the page-locked staging buffers are allocated next to the GPU's PCIe root.  Returns the cpulist used, or None."""
+    try:
+        p = torch.cuda.get_device_properties(local)
+        bus = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        with open("/sys/bus/pci/devices/%s/local_cpulist" % bus) as f:
+            cl = f.read().strip()
+        cpus = set()
+        for part in cl.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        cpus &= os.sched_getaffinity(0)
+        if len(cpus) < 2:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cl
+    except Exception:
+        return None
+
+
 STEREO_KERNELS = 4   # k_stereo_rowtable, k_stereo_hamming2, k_stereo_sad, k_stereo_median
 
 
@@ -283,6 +307,7 @@ def run_orbx(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
     torch.cuda.set_device(local)
+    affinity = _bind_to_gpu_numa_node(torch, local) if world > 1 else None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     B = args.batch
@@ -513,7 +538,8 @@ def run_orbx(args):
                            "stereo_matches_per_frame": matched,
                            "l2": "per-step working set (%.0f MB of images + pyramids + blurred levels per GPU) exceeds the 126 MB L2"
                                  % (2 * B * (W * H + 2 * LEVEL_PIXELS) / 1e6),
-                           "sharding": "stereo frames partitioned by rank, no collective on the data path"},
+                           "sharding": "stereo frames partitioned by rank, no collective on the data path",
+                           "cpu_affinity": affinity},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
                 "extra": extras}
         print(json.dumps(line), flush=True)
