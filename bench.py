@@ -128,6 +128,47 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def cv2_primitive_times(synth, nframes=6):
+    """the real OpenCV's (python cv2, one thread) time for the OpenCV primitives of one 752x480 stereo frame
+    -- resize chain, FAST on every level (whole level, not per cell: a lower bound), 7x7 GaussianBlur, BFMatcher 2-NN of
+    1200 x 1200 descriptors -- as a lower bound for those stages of the reference (the scalar oracle port is slower than
+    OpenCV's SIMD).  Reported only; quadtree, orientation, rBRIEF and the stereo search are not in it."""
+    try:
+        import cv2
+    except Exception:
+        return None
+    cv2.setNumThreads(1)
+    imgs = [synth.frame(W, H, 4242, i) for i in range(nframes)]
+    sizes = [(W, H)]
+    for _ in range(7):
+        sizes.append((int(round(sizes[-1][0] / 1.2)), int(round(sizes[-1][1] / 1.2))))   # close enough for a timing
+    fast = cv2.FastFeatureDetector_create(20, True)
+    t = {"resize_chain": 0.0, "fast_levels": 0.0, "blur_levels": 0.0}
+    for img in imgs:
+        t0 = time.perf_counter()
+        pyr = [img]
+        for (w_, h_) in sizes[1:]:
+            pyr.append(cv2.resize(pyr[-1], (w_, h_), interpolation=cv2.INTER_LINEAR))
+        t1 = time.perf_counter()
+        for lv in pyr:
+            fast.detect(lv, None)
+        t2 = time.perf_counter()
+        for lv in pyr:
+            cv2.GaussianBlur(lv, (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101)
+        t3 = time.perf_counter()
+        t["resize_chain"] += t1 - t0; t["fast_levels"] += t2 - t1; t["blur_levels"] += t3 - t2
+    rng = np.random.default_rng(0)
+    q = rng.integers(0, 256, (1200, 32), dtype=np.uint8); tr = rng.integers(0, 256, (1200, 32), dtype=np.uint8)
+    bf = cv2.BFMatcher(cv2.NORM_HAMMING)
+    t0 = time.perf_counter()
+    for _ in range(3):
+        bf.knnMatch(q, tr, k=2)
+    knn = (time.perf_counter() - t0) / 3
+    per_image = {k: v / nframes * 1e3 for k, v in t.items()}
+    return {"threads": 1, "cv2": cv2.__version__, "ms_per_image": per_image, "bf_knn2_1200x1200_ms": knn * 1e3,
+            "ms_per_stereo_frame_lower_bound": 2 * sum(per_image.values())}
+
+
 def cpu_stereo_sample(synth, nframes, threads, seed=12345):
     """reference CPU path (oracle port) on `nframes` stereo frames with `threads` host threads -> (frames/s, seconds)"""
     import oracle
@@ -529,6 +570,8 @@ def run_orbx(args):
         cpu = {"value": fpsN, "unit": "frames/s", "cores": cores, "kind": "port",
                "sample": "%d stereo frames of the workload, frame-parallel with 2 threads per frame, %d threads (%.1f s); one frame at a time "
                          "(2 threads): %.1f frames/s" % (ncpu, cores, secN, fps1), "two_thread_value": fps1}
+        if not args.skip_cpu:
+            cpu["cv2_primitives"] = cv2_primitive_times(synth)
         launches = (2 * exL.launches_per_batch() + STEREO_KERNELS) * args.steps * world
         line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": nwarm,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",

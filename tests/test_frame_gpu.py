@@ -167,3 +167,48 @@ def test_search_local_points_batch(pre, orbx, oracle, synth, nframes, nmp, th):
         total += nm_o
     assert total > 300 * nframes // 2
     lm.close(), m.close(), gx.close()
+
+
+def test_device_resident_forms_and_arguments(pre, orbx, oracle):
+    """ORBX_MEM_DEVICE: device pointers in / out on the caller's stream (in place for the keypoints), plus argument checking."""
+    import ctypes as C
+    import torch
+    lib = orbx.lib()
+    cam = fc.CAMERAS["euroc"]
+    fx, fy, cx, cy = [np.float32(v) for v in cam["K"]]
+    pts = fc.pixel_points(cam, 3000, seed=8)
+    kps = np.zeros(len(pts), orbx.KP_DTYPE)
+    kps["x"], kps["y"], kps["octave"] = pts[:, 0], pts[:, 1], 3
+    d_k = torch.from_numpy(kps.view(np.uint8).reshape(-1, 28).copy()).cuda()
+    D = np.zeros(5, np.float32); D[:4] = cam["D"]
+    st = torch.cuda.Stream()
+    vp = lambda t: C.c_void_p(t.data_ptr())
+    fl = lambda v: C.c_float(float(v))
+    assert lib.orbx_undistort_keypoints(pre._h, vp(d_k), len(kps), fl(fx), fl(fy), fl(cx), fl(cy), D.ctypes.data_as(C.c_void_p), vp(d_k), 1,
+                                        C.c_void_p(st.cuda_stream)) == 0
+    st.synchronize()
+    un = d_k.cpu().numpy().reshape(-1).view(orbx.KP_DTYPE)
+    ref = oracle.undistort_points(pts, fx, fy, cx, cy, D)
+    assert un["x"].tobytes() == ref[:, 0].tobytes() and un["y"].tobytes() == ref[:, 1].tobytes() and (un["octave"] == 3).all()
+    # frustum on device buffers
+    ocam, P, normal, maxd, mind = fc.frustum_case(oracle, 4000, seed=12)
+    g = pre.mod.frustum(np.array(ocam.Rcw[:]).reshape(3, 3), ocam.tcw[:], ocam.fx, ocam.fy, ocam.cx, ocam.cy,
+                        (ocam.minX, ocam.maxX, ocam.minY, ocam.maxY), ocam.bf, 1.2, 8, 0.5)
+    n = len(P)
+    dP, dN, dMx, dMn = [torch.from_numpy(a).cuda() for a in (P, normal, maxd, mind)]
+    dIn = torch.empty(n, dtype=torch.uint8, device="cuda")
+    dF = [torch.empty(n, dtype=torch.float32, device="cuda") for _ in range(5)]
+    dL = torch.empty(n, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    assert lib.orbx_is_in_frustum(pre._h, C.byref(g), n, vp(dP), vp(dN), vp(dMx), vp(dMn), vp(dIn), vp(dF[0]), vp(dF[1]), vp(dF[2]), vp(dF[3]),
+                                  vp(dL), vp(dF[4]), 1, C.c_void_p(st.cuda_stream)) == 0
+    st.synchronize()
+    ref = oracle.is_in_frustum(ocam, P, normal, maxd, mind)
+    assert np.array_equal(dIn.cpu().numpy(), ref["in_view"]) and np.array_equal(dL.cpu().numpy(), ref["level"])
+    for t, k in zip(dF, ("proj_x", "proj_y", "proj_xr", "depth", "view_cos")):
+        assert t.cpu().numpy().tobytes() == ref[k].tobytes(), k
+    # arguments
+    assert lib.orbx_is_in_frustum(pre._h, C.byref(g), 0, None, None, None, None, None, None, None, None, None, None, None, 0, None) == 0
+    assert lib.orbx_is_in_frustum(pre._h, C.byref(g), 5, None, None, None, None, None, None, None, None, None, None, None, 0, None) == orbx.ORBX_ERR_ARG
+    assert lib.orbx_undistort_keypoints(pre._h, None, 3, fl(fx), fl(fy), fl(cx), fl(cy), D.ctypes.data_as(C.c_void_p), None, 0, None) == orbx.ORBX_ERR_ARG
+    assert lib.orbx_undistort_keypoints(pre._h, vp(d_k), 3, fl(fx), fl(fy), fl(cx), fl(cy), D.ctypes.data_as(C.c_void_p), vp(d_k), 7, None) == orbx.ORBX_ERR_ARG
