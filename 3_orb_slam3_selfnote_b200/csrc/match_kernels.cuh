@@ -844,17 +844,34 @@ __global__ void __launch_bounds__(256) k_stereo_sad(const __grid_constant__ Geom
     py[k] = p / 11; px[k] = p - py[k] * 11;
     il[k] = (p < 121) ? (int)imL[(long long)(y0 + py[k]) * spL + xl0 + px[k]] - cL : 0;
   }
+  // The 11 shifted windows overlap in an 11 x 21 strip of the right image: stage it once per warp in shared memory (8 byte
+  // loads per lane, all in flight together) instead of 44 dependent one-byte global loads per lane.  Every exit above is
+  // warp-uniform (it depends on iL only), so a warp-level barrier is enough.
+  __shared__ uint8_t sR[8][11 * 24];
+  uint8_t* strip = sR[threadIdx.x >> 5];
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    const int p = lane + 32 * k;
+    if (p < 231) {
+      const int r = p / 21, c = p - r * 21;
+      strip[r * 24 + c] = imR[(long long)(y0 + r) * spR + xrBase - L + c];
+    }
+  }
+  __syncwarp();
+  int off[4];
+#pragma unroll
+  for (int k = 0; k < 4; k++) off[k] = py[k] * 24 + px[k];
   int bestDistS = INT_MAX, bestincR = 0;
   float vDists[11];
 #pragma unroll
   for (int incR = -5; incR <= 5; incR++) {
-    const int xr0 = xrBase + incR;
-    const int cR = imR[(long long)(y0 + w) * spR + xr0 + w];
+    const int sh = incR + L;                      // column of the window's left edge inside the strip
+    const int cR = strip[w * 24 + sh + w];
     int sum = 0;
 #pragma unroll
     for (int k = 0; k < 4; k++) {
       const int p = lane + 32 * k;
-      if (p < 121) sum += abs(il[k] - ((int)imR[(long long)(y0 + py[k]) * spR + xr0 + px[k]] - cR));
+      if (p < 121) sum += abs(il[k] - ((int)strip[off[k] + sh] - cR));
     }
 #pragma unroll
     for (int s = 16; s > 0; s >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, s);
