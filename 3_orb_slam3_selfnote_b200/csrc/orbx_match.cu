@@ -48,6 +48,10 @@ struct orbx_matcher {
   // right branch joined, input buffers free again (both extractions done), slot's downloads done
   cudaStream_t upStream = nullptr;
   cudaEvent_t evUpL[2] = {}, evUpR[2] = {}, evJoin[2] = {}, evInFree[2] = {}, evSlotDone[2] = {};
+  // pinned staging of run_window_jobs: host inputs are packed here and uploaded from page-locked memory (asynchronous, ~2 us per
+  // copy) instead of ~15 pageable cudaMemcpyAsync per job that each block the host; results come back the same way.  Grow-only,
+  // sized by the previous call's demand; a call that does not fit falls back to direct copies.
+  uint8_t* hPin = nullptr; size_t hPinCap = 0, hPinWant = 0;
   int* hStat = nullptr;    // pinned: device status words of every chunk of a call (2 per chunk)
   static constexpr int kStatChunks = 256;
 };
@@ -168,9 +172,34 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
   int rc = arena_ensure(m, plan.total);
   if (rc != ORBX_OK) return rc;
   cudaStream_t st = m->stream;
+  if (m->hPinWant > m->hPinCap) {   // the previous call outgrew the staging buffer (the stream is idle between calls)
+    std::lock_guard<std::recursive_mutex> setupLock(setup_mutex());
+    if (m->hPin) cudaFreeHost(m->hPin);
+    m->hPin = nullptr; m->hPinCap = 0;
+    const size_t want = m->hPinWant + m->hPinWant / 4;
+    if (cudaHostAlloc((void**)&m->hPin, want, cudaHostAllocDefault) == cudaSuccess) m->hPinCap = want;
+    else cudaGetLastError();
+  }
+  size_t pinCur = 0, pinNeed = 0;
+  auto pin = [&](size_t bytes) -> uint8_t* {   // 64-byte aligned slice of the staging buffer, or null when it is full
+    const size_t b = (bytes + 63) & ~(size_t)63;
+    pinNeed += b;
+    if (pinCur + b > m->hPinCap) return nullptr;
+    uint8_t* r = m->hPin + pinCur;
+    pinCur += b;
+    return r;
+  };
   auto up = [&](size_t o, const void* src, size_t bytes) -> cudaError_t {
     if (bytes == 0 || !src) return cudaSuccess;
+    if (uint8_t* h = pin(bytes)) { memcpy(h, src, bytes); src = h; }
     return cudaMemcpyAsync(m->arena + o, src, bytes, cudaMemcpyHostToDevice, st);
+  };
+  struct Pending { void* dst; const void* src; size_t bytes; };
+  std::vector<Pending> pending;   // results parked in the staging buffer, handed to the caller after the final synchronisation
+  auto down = [&](void* dst, size_t o, size_t bytes) -> cudaError_t {
+    if (bytes == 0 || !dst) return cudaSuccess;
+    if (uint8_t* h = pin(bytes)) { pending.push_back({dst, h, bytes}); dst = h; }
+    return cudaMemcpyAsync(dst, m->arena + o, bytes, cudaMemcpyDeviceToHost, st);
   };
   std::vector<GridFrame> frames(nj);
   std::vector<QuerySet> sets(nj);
@@ -235,10 +264,10 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
       A.nmatches = at<int>(m, o.nmatches); A.nnratio = J.nnratio; A.checkOrientation = J.checkOrientation;
     }
   }
-  CK(cudaMemcpyAsync(m->arena + oFrames, frames.data(), nj * sizeof(GridFrame), cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync(m->arena + oSets, sets.data(), nj * sizeof(QuerySet), cudaMemcpyHostToDevice, st));
-  if (kind == RESOLVE_INIT) CK(cudaMemcpyAsync(m->arena + oArgs, iargs.data(), nj * sizeof(InitArgs), cudaMemcpyHostToDevice, st));
-  else CK(cudaMemcpyAsync(m->arena + oArgs, rargs.data(), nj * sizeof(ResolveArgs), cudaMemcpyHostToDevice, st));
+  CK(up(oFrames, frames.data(), nj * sizeof(GridFrame)));
+  CK(up(oSets, sets.data(), nj * sizeof(QuerySet)));
+  if (kind == RESOLVE_INIT) CK(up(oArgs, iargs.data(), nj * sizeof(InitArgs)));
+  else CK(up(oArgs, rargs.data(), nj * sizeof(ResolveArgs)));
   CK(cudaMemsetAsync(m->dStatus, 0, sizeof(int), st));
   const GridFrame* dFrames = at<GridFrame>(m, oFrames);
   const QuerySet* dSets = at<QuerySet>(m, oSets);
@@ -261,15 +290,15 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
     WindowJob& J = jobs[j];
     const Off& o = off[j];
     if (kind == RESOLVE_MAPPOINTS || kind == RESOLVE_WINDOW) {
-      CK(cudaMemcpyAsync(J.kpMp, m->arena + o.kpMp, (size_t)std::min(frames[j].n, J.kpMpLen) * 4, cudaMemcpyDeviceToHost, st));
-      CK(cudaMemcpyAsync(J.nmatches, m->arena + o.nmatches, 4, cudaMemcpyDeviceToHost, st));
+      CK(down(J.kpMp, o.kpMp, (size_t)std::min(frames[j].n, J.kpMpLen) * 4));
+      CK(down(J.nmatches, o.nmatches, 4));
     } else if (kind == RESOLVE_INIT) {
-      CK(cudaMemcpyAsync(J.matches12, m->arena + o.m12, (size_t)J.q.nq * 4, cudaMemcpyDeviceToHost, st));
-      CK(cudaMemcpyAsync(J.prevMatched, m->arena + o.prevMatched, (size_t)J.q.nq * 8, cudaMemcpyDeviceToHost, st));
-      CK(cudaMemcpyAsync(J.nmatches, m->arena + o.nmatches, 4, cudaMemcpyDeviceToHost, st));
+      CK(down(J.matches12, o.m12, (size_t)J.q.nq * 4));
+      CK(down(J.prevMatched, o.prevMatched, (size_t)J.q.nq * 8));
+      CK(down(J.nmatches, o.nmatches, 4));
     } else if (kind == RESOLVE_BEST) {
-      CK(cudaMemcpyAsync(J.bestIdx, m->arena + o.assigned, (size_t)J.q.nq * 4, cudaMemcpyDeviceToHost, st));
-      CK(cudaMemcpyAsync(J.bestDist, m->arena + o.m12, (size_t)J.q.nq * 4, cudaMemcpyDeviceToHost, st));
+      CK(down(J.bestIdx, o.assigned, (size_t)J.q.nq * 4));
+      CK(down(J.bestDist, o.m12, (size_t)J.q.nq * 4));
     } else if (J.entriesOut) {
       int cnt = 0;
       CK(cudaMemcpyAsync(&cnt, m->arena + o.qCnt, 4, cudaMemcpyDeviceToHost, st));
@@ -279,6 +308,8 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
     }
   }
   CK(cudaStreamSynchronize(st));
+  for (const Pending& P : pending) memcpy(P.dst, P.src, P.bytes);
+  m->hPinWant = std::max(m->hPinWant, pinNeed);
   if (status != 0) { set_error("candidate list capacity exceeded"); return status; }
   return ORBX_OK;
 }
@@ -347,6 +378,7 @@ void orbx_matcher_destroy(orbx_matcher* m) {
     for (cudaEvent_t e : {m->evUpL[i], m->evUpR[i], m->evJoin[i], m->evInFree[i], m->evSlotDone[i]}) if (e) cudaEventDestroy(e);
   if (m->upStream) cudaStreamDestroy(m->upStream);
   if (m->hStat) cudaFreeHost(m->hStat);
+  if (m->hPin) cudaFreeHost(m->hPin);
   cudaStreamDestroy(m->stream);
   delete m;
 }
