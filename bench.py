@@ -291,6 +291,25 @@ def extra_configs(orbx, synth, torch, stream, local, steps):
     out["tumvi512_device_map_matches_per_frame"] = float(np.mean(nm_holder["nm_dev"]))
     lm.close()
     ex.close(); mt.close()
+    # pre-processing in front of the extractor, device-resident, 256 frames of 752x480 per call
+    pre = pre_mod.Preprocessor(device=local)
+    nb = 256
+    g8 = tiled(W, H, nb, 4, 5000)
+    col = torch.randint(0, 256, (nb, H, W, 3), dtype=torch.uint8, device="cuda")
+    dst = torch.empty_like(g8)
+    yy, xx = np.mgrid[0:H, 0:W].astype(np.float32)
+    r2 = ((xx - W / 2) ** 2 + (yy - H / 2) ** 2) / (0.6 * W) ** 2
+    kk = 1 - 0.28 * r2 + 0.07 * r2 * r2
+    tbl = pre.remap_table(((xx - W / 2) * kk * 1.08 + W / 2).astype(np.float32), ((yy - H / 2) * kk * 1.08 + H / 2).astype(np.float32), (W, H))
+    sec = timed(lambda: pre.cvt_gray_device(col.data_ptr(), nb, W, H, W * 3, H * W * 3, 3, False, dst.data_ptr(), W, H * W, sh), steps)
+    out["cvtColor_bgr2gray_752x480_frames_per_s_per_gpu"] = nb / sec
+    out["cvtColor_bgr2gray_GBps"] = nb * H * W * 4 / sec / 1e9
+    sec = timed(lambda: pre.remap_device(tbl, g8.data_ptr(), nb, W, H * W, dst.data_ptr(), W, H * W, sh), steps)
+    out["remap_rectify_752x480_frames_per_s_per_gpu"] = nb / sec
+    sec = timed(lambda: pre.clahe_device(g8.data_ptr(), nb, W, H, W, H * W, dst.data_ptr(), W, H * W, 3.0, (8, 8), sh), steps)
+    out["clahe_3.0_8x8_752x480_frames_per_s_per_gpu"] = nb / sec
+    tbl.close(); pre.close()
+    del col, g8, dst
     # all-pairs tile kernel: 16384 queries against 262144 train descriptors, running (best, second) keys
     nq, nt = 16384, 262144
     q = torch.randint(0, 256, (nq, 32), dtype=torch.uint8, device="cuda"); t = torch.randint(0, 256, (nt, 32), dtype=torch.uint8, device="cuda")
