@@ -52,11 +52,22 @@ struct orbx_matcher {
   // copy) instead of ~15 pageable cudaMemcpyAsync per job that each block the host; results come back the same way.  Grow-only,
   // sized by the previous call's demand; a call that does not fit falls back to direct copies.
   uint8_t* hPin = nullptr; size_t hPinCap = 0, hPinWant = 0;
+  uint8_t* dStage = nullptr;   // device twin of hPin: one copy each way per call, k_stage_copy moves the pieces to / from the arena
   int* hStat = nullptr;    // pinned: device status words of every chunk of a call (2 per chunk)
   static constexpr int kStatChunks = 256;
 };
 
 namespace {
+
+struct StageCopy { unsigned long long stageOff, arenaOff; unsigned bytes, pad; };   // bytes: multiple of 16
+
+// grid (pieces, 2): moves piece blockIdx.x between the staging buffer and the arena in 16-byte words
+__global__ void __launch_bounds__(256) k_stage_copy(uint8_t* stage, uint8_t* arena, const StageCopy* list, int toArena) {
+  const StageCopy c = list[blockIdx.x];
+  const uint4* src = reinterpret_cast<const uint4*>(toArena ? stage + c.stageOff : arena + c.arenaOff);
+  uint4* dst = reinterpret_cast<uint4*>(toArena ? arena + c.arenaOff : stage + c.stageOff);
+  for (unsigned i = blockIdx.y * 256 + threadIdx.x; i < (c.bytes >> 4); i += 256 * gridDim.y) dst[i] = src[i];
+}
 
 struct ArenaPlan {  // two-phase bump allocation: plan sizes, ensure capacity, then carve
   size_t total = 0;
@@ -177,8 +188,10 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
     if (m->hPin) cudaFreeHost(m->hPin);
     m->hPin = nullptr; m->hPinCap = 0;
     const size_t want = m->hPinWant + m->hPinWant / 4;
-    if (cudaHostAlloc((void**)&m->hPin, want, cudaHostAllocDefault) == cudaSuccess) m->hPinCap = want;
-    else cudaGetLastError();
+    if (m->dStage) cudaFree(m->dStage);
+    m->dStage = nullptr;
+    if (cudaHostAlloc((void**)&m->hPin, want, cudaHostAllocDefault) == cudaSuccess && cudaMalloc((void**)&m->dStage, want) == cudaSuccess) m->hPinCap = want;
+    else { cudaGetLastError(); if (m->hPin) cudaFreeHost(m->hPin); m->hPin = nullptr; }
   }
   size_t pinCur = 0, pinNeed = 0;
   auto pin = [&](size_t bytes) -> uint8_t* {   // 64-byte aligned slice of the staging buffer, or null when it is full
@@ -189,17 +202,66 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
     pinCur += b;
     return r;
   };
+  // Inputs are packed into the page-locked buffer and recorded; flush_up() sends the whole pack with ONE copy and lets
+  // k_stage_copy scatter the pieces to their arena offsets (every arena region is padded to 256 bytes, every slice to 64, so
+  // whole 16-byte words can be moved).  Results travel the other way in flush_down().  Pieces that do not fit the buffer
+  // (first call, or a call larger than any before) use direct copies.
+  std::vector<StageCopy> upList, downList;
   auto up = [&](size_t o, const void* src, size_t bytes) -> cudaError_t {
     if (bytes == 0 || !src) return cudaSuccess;
-    if (uint8_t* h = pin(bytes)) { memcpy(h, src, bytes); src = h; }
+    if (uint8_t* h = pin(bytes)) {
+      memcpy(h, src, bytes);
+      upList.push_back({(unsigned long long)(h - m->hPin), (unsigned long long)o, (unsigned)((bytes + 15) & ~(size_t)15), 0u});
+      return cudaSuccess;
+    }
     return cudaMemcpyAsync(m->arena + o, src, bytes, cudaMemcpyHostToDevice, st);
+  };
+  auto flush_up = [&]() -> cudaError_t {
+    if (upList.empty()) return cudaSuccess;
+    const size_t lb = upList.size() * sizeof(StageCopy);
+    uint8_t* hl = pin(lb);
+    if (!hl) {   // no room for the list itself: send the pieces one by one from the page-locked slices
+      for (const StageCopy& c : upList) {
+        cudaError_t e = cudaMemcpyAsync(m->arena + c.arenaOff, m->hPin + c.stageOff, c.bytes, cudaMemcpyHostToDevice, st);
+        if (e != cudaSuccess) return e;
+      }
+      return cudaSuccess;
+    }
+    memcpy(hl, upList.data(), lb);
+    cudaError_t e = cudaMemcpyAsync(m->dStage, m->hPin, pinCur, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return e;
+    k_stage_copy<<<dim3((unsigned)upList.size(), 2), 256, 0, st>>>(m->dStage, m->arena, reinterpret_cast<const StageCopy*>(m->dStage + (hl - m->hPin)), 1);
+    return cudaGetLastError();
   };
   struct Pending { void* dst; const void* src; size_t bytes; };
   std::vector<Pending> pending;   // results parked in the staging buffer, handed to the caller after the final synchronisation
   auto down = [&](void* dst, size_t o, size_t bytes) -> cudaError_t {
     if (bytes == 0 || !dst) return cudaSuccess;
-    if (uint8_t* h = pin(bytes)) { pending.push_back({dst, h, bytes}); dst = h; }
+    if (uint8_t* h = pin(bytes)) {
+      pending.push_back({dst, h, bytes});
+      downList.push_back({(unsigned long long)(h - m->hPin), (unsigned long long)o, (unsigned)((bytes + 15) & ~(size_t)15), 0u});
+      return cudaSuccess;
+    }
     return cudaMemcpyAsync(dst, m->arena + o, bytes, cudaMemcpyDeviceToHost, st);
+  };
+  auto flush_down = [&]() -> cudaError_t {
+    if (downList.empty()) return cudaSuccess;
+    const size_t first = downList.front().stageOff;
+    const size_t lb = downList.size() * sizeof(StageCopy);
+    uint8_t* hl = pin(lb);
+    if (!hl) {
+      for (const StageCopy& c : downList) {
+        cudaError_t e = cudaMemcpyAsync(m->hPin + c.stageOff, m->arena + c.arenaOff, c.bytes, cudaMemcpyDeviceToHost, st);
+        if (e != cudaSuccess) return e;
+      }
+      return cudaSuccess;
+    }
+    memcpy(hl, downList.data(), lb);
+    cudaError_t e = cudaMemcpyAsync(m->dStage + (hl - m->hPin), hl, lb, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return e;
+    k_stage_copy<<<dim3((unsigned)downList.size(), 2), 256, 0, st>>>(m->dStage, m->arena, reinterpret_cast<const StageCopy*>(m->dStage + (hl - m->hPin)), 0);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    return cudaMemcpyAsync(m->hPin + first, m->dStage + first, (size_t)(hl - m->hPin) - first, cudaMemcpyDeviceToHost, st);
   };
   std::vector<GridFrame> frames(nj);
   std::vector<QuerySet> sets(nj);
@@ -268,6 +330,7 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
   CK(up(oSets, sets.data(), nj * sizeof(QuerySet)));
   if (kind == RESOLVE_INIT) CK(up(oArgs, iargs.data(), nj * sizeof(InitArgs)));
   else CK(up(oArgs, rargs.data(), nj * sizeof(ResolveArgs)));
+  CK(flush_up());
   CK(cudaMemsetAsync(m->dStatus, 0, sizeof(int), st));
   const GridFrame* dFrames = at<GridFrame>(m, oFrames);
   const QuerySet* dSets = at<QuerySet>(m, oSets);
@@ -307,6 +370,7 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
       if (cnt) CK(cudaMemcpyAsync(J.entriesOut->data(), m->arena + o.entries, (size_t)cnt * 8, cudaMemcpyDeviceToHost, st));
     }
   }
+  CK(flush_down());
   CK(cudaStreamSynchronize(st));
   for (const Pending& P : pending) memcpy(P.dst, P.src, P.bytes);
   m->hPinWant = std::max(m->hPinWant, pinNeed);
@@ -379,6 +443,7 @@ void orbx_matcher_destroy(orbx_matcher* m) {
   if (m->upStream) cudaStreamDestroy(m->upStream);
   if (m->hStat) cudaFreeHost(m->hStat);
   if (m->hPin) cudaFreeHost(m->hPin);
+  if (m->dStage) cudaFree(m->dStage);
   cudaStreamDestroy(m->stream);
   delete m;
 }
