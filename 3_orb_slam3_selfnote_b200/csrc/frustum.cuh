@@ -25,8 +25,23 @@ __device__ __forceinline__ FrustumOut frustum_point(const orbx_frustum& C, float
   const float PcDist = (float)sqrt((double)Pc[0] * Pc[0] + (double)Pc[1] * Pc[1] + (double)Pc[2] * Pc[2]);
   const float invz = __fdiv_rn(1.0f, Pc[2]);
   if (Pc[2] < 0.0f) return o;
-  const float ux = __fadd_rn(__fdiv_rn(__fmul_rn(C.fx, Pc[0]), Pc[2]), C.cx);
-  const float uy = __fadd_rn(__fdiv_rn(__fmul_rn(C.fy, Pc[1]), Pc[2]), C.cy);
+  float ux, uy;
+  if (C.camera_model == ORBX_CAMERA_KB8) {
+    // KannalaBrandt8::project (KannalaBrandt8.cpp:29-45).  atan2f is evaluated as (float)atan2((double)..) (portable policy,
+    // DESIGN.md section 2); cos / sin resolve to the double overloads in the reference (no using-directive in that file), so
+    // the last line is double arithmetic rounded once to float, as written here.
+    const float x2y2 = __fadd_rn(__fmul_rn(Pc[0], Pc[0]), __fmul_rn(Pc[1], Pc[1]));
+    const float theta = (float)atan2((double)sqrtf(x2y2), (double)Pc[2]);
+    const float psi = (float)atan2((double)Pc[1], (double)Pc[0]);
+    const float t2 = __fmul_rn(theta, theta), t3 = __fmul_rn(theta, t2), t5 = __fmul_rn(t3, t2), t7 = __fmul_rn(t5, t2), t9 = __fmul_rn(t7, t2);
+    const float r = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(theta, __fmul_rn(C.kb[0], t3)), __fmul_rn(C.kb[1], t5)), __fmul_rn(C.kb[2], t7)),
+                              __fmul_rn(C.kb[3], t9));
+    ux = (float)__dadd_rn(__dmul_rn((double)__fmul_rn(C.fx, r), cos((double)psi)), (double)C.cx);
+    uy = (float)__dadd_rn(__dmul_rn((double)__fmul_rn(C.fy, r), sin((double)psi)), (double)C.cy);
+  } else {
+    ux = __fadd_rn(__fdiv_rn(__fmul_rn(C.fx, Pc[0]), Pc[2]), C.cx);
+    uy = __fadd_rn(__fdiv_rn(__fmul_rn(C.fy, Pc[1]), Pc[2]), C.cy);
+  }
   if (ux < C.min_x || ux > C.max_x) return o;
   if (uy < C.min_y || uy > C.max_y) return o;
   o.projX = ux; o.projY = uy;

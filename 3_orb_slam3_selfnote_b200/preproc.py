@@ -125,10 +125,10 @@ class _Frustum(C.Structure):
     _fields_ = [("Rcw", C.c_float * 9), ("tcw", C.c_float * 3), ("Ow", C.c_float * 3), ("fx", C.c_float), ("fy", C.c_float),
                 ("cx", C.c_float), ("cy", C.c_float), ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float),
                 ("max_y", C.c_float), ("bf", C.c_float), ("log_scale_factor", C.c_float), ("viewing_cos_limit", C.c_float),
-                ("n_scale_levels", C.c_int)]
+                ("n_scale_levels", C.c_int), ("camera_model", C.c_int), ("kb", C.c_float * 4)]
 
 
-def frustum(Rcw, tcw, fx, fy, cx, cy, bounds, bf, scale_factor, nlevels, viewing_cos_limit=0.5):
+def frustum(Rcw, tcw, fx, fy, cx, cy, bounds, bf, scale_factor, nlevels, viewing_cos_limit=0.5, kb=None):
     """The members of Frame that isInFrustum reads.  Ow = -Rcw^T tcw and mfLogScaleFactor = log(mfScaleFactor) are computed
     here in float32 like Frame::UpdatePoseMatrices (src/Frame.cc:561-566) and the constructor (:110)."""
     Rcw = np.asarray(Rcw, np.float32).reshape(3, 3)
@@ -142,6 +142,9 @@ def frustum(Rcw, tcw, fx, fy, cx, cy, bounds, bf, scale_factor, nlevels, viewing
     f.log_scale_factor = float(np.log(np.float32(scale_factor)))
     f.viewing_cos_limit = float(viewing_cos_limit)
     f.n_scale_levels = int(nlevels)
+    f.camera_model = 0 if kb is None else 1   # ORBX_CAMERA_PINHOLE / ORBX_CAMERA_KB8 (k1..k4 of KannalaBrandt8)
+    if kb is not None:
+        f.kb[:] = [float(k) for k in kb]
     return f
 
 

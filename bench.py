@@ -272,15 +272,24 @@ def extra_configs(orbx, synth, torch, stream, local, steps):
     # the pose goes in; isInFrustum + SearchByProjection run on the extractor's stream, kp_mp / nmatches come back once per batch
     pre_mod = importlib.import_module("3_orb_slam3_selfnote_b200.preproc")
     fx, fy, cx, cy = np.float32(190.978), np.float32(190.973), np.float32(254.93), np.float32(256.9)
+    kb = (0.003482389402, 0.000715034845, -0.002053236141, 0.000202936736)   # Examples/Monocular/TUM_512.yaml: KannalaBrandt8 k1..k4
     zs = rng.uniform(1.0, 8.0, nmp)
-    P = np.stack([(px[0] - cx) / fx * zs, (py[0] - cy) / fy * zs, zs], 1).astype(np.float32)   # frame 0's map points, camera at the origin
+    mx, my = (px[0].astype(np.float64) - cx) / fx, (py[0].astype(np.float64) - cy) / fy   # KannalaBrandt8::unproject by Newton steps
+    rr = np.maximum(np.hypot(mx, my), 1e-9)
+    th = rr.copy()
+    for _ in range(8):
+        t2 = th * th
+        f_ = th * (1 + t2 * (kb[0] + t2 * (kb[1] + t2 * (kb[2] + t2 * kb[3])))) - rr
+        df = 1 + t2 * (3 * kb[0] + t2 * (5 * kb[1] + t2 * (7 * kb[2] + t2 * 9 * kb[3])))
+        th = th - f_ / df
+    P = (np.stack([np.sin(th) * mx / rr, np.sin(th) * my / rr, np.cos(th)], 1) * zs[:, None]).astype(np.float32)   # frame 0's map points, camera at the origin
     dist = np.linalg.norm(P, axis=1)
     scale = ex.GetScaleFactors()
     maxd = (dist * scale[np.clip(lv[0], 0, 7)] * 1.1).astype(np.float32)
     mind = (maxd / scale[7] * 0.8).astype(np.float32)
     nrm = (P / dist[:, None]).astype(np.float32)
     lm = orbx.LocalMap(mt, P, nrm, maxd, mind, md[0])
-    cams = [pre_mod.frustum(np.eye(3), np.zeros(3), fx, fy, cx, cy, (0, w, 0, h), 0.0, 1.2, 8) for _ in range(n)]
+    cams = [pre_mod.frustum(np.eye(3), np.zeros(3), fx, fy, cx, cy, (0, w, 0, h), 0.0, 1.2, 8, kb=kb) for _ in range(n)]
 
     def tum_step_dev():
         ex.extract_batch_device(dev.data_ptr(), n, w, h, w, w * h, (0, 0), sh)
@@ -289,6 +298,18 @@ def extra_configs(orbx, synth, torch, stream, local, steps):
     sec = timed(tum_step_dev, max(2, steps // 2))
     out["tumvi512_extract_nfeat1500+SearchLocalPoints_5000mp_device_map_frames_per_s_per_gpu"] = n / sec
     out["tumvi512_device_map_matches_per_frame"] = float(np.mean(nm_holder["nm_dev"]))
+    # ... and with the CLAHE(3.0, 8x8) that mono_tum_vi.cc:109 applies to every frame in front of it
+    pre_t = pre_mod.Preprocessor(device=local)
+    dev_eq = torch.empty_like(dev)
+
+    def tum_step_clahe():
+        pre_t.clahe_device(dev.data_ptr(), n, w, h, w, w * h, dev_eq.data_ptr(), w, w * h, 3.0, (8, 8), sh)
+        ex.extract_batch_device(dev_eq.data_ptr(), n, w, h, w, w * h, (0, 0), sh)
+        nm_holder["nm_eq"] = mt.SearchLocalPointsBatch(ex, n, cams, lm, 1.0, sh)[0]
+
+    sec = timed(tum_step_clahe, max(2, steps // 2))
+    out["tumvi512_clahe+extract_nfeat1500+SearchLocalPoints_5000mp_frames_per_s_per_gpu"] = n / sec
+    pre_t.close()
     lm.close()
     ex.close(); mt.close()
     # pre-processing in front of the extractor, device-resident, 256 frames of 752x480 per call

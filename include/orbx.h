@@ -345,7 +345,12 @@ typedef struct orbx_frustum {
   float min_x, max_x, min_y, max_y;     /* mnMinX .. mnMaxY */
   float bf, log_scale_factor, viewing_cos_limit; /* mbf, mfLogScaleFactor, 0.5 at the call site */
   int n_scale_levels;                   /* mnScaleLevels */
+  int camera_model;                     /* ORBX_CAMERA_PINHOLE (Pinhole::project) or ORBX_CAMERA_KB8 (KannalaBrandt8::project,
+                                           src/CameraModels/KannalaBrandt8.cpp:29-45: TUM-VI fisheye, Frame.cc:597 through mpCamera) */
+  float kb[4];                          /* KannalaBrandt8 k1..k4 (mvParameters[4..7]); ignored for the pinhole model */
 } orbx_frustum;
+#define ORBX_CAMERA_PINHOLE 0
+#define ORBX_CAMERA_KB8 1
 int orbx_is_in_frustum(orbx_preproc* p, const orbx_frustum* cam, int n, const float* world_pos, const float* normal, const float* max_dist,
                        const float* min_dist, uint8_t* in_view, float* proj_x, float* proj_y, float* proj_xr, float* depth, int* level,
                        float* view_cos, int mem, void* stream);

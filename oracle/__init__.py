@@ -404,7 +404,7 @@ class FrustumCam(C.Structure):
     _fields_ = [("Rcw", C.c_float * 9), ("tcw", C.c_float * 3), ("Ow", C.c_float * 3), ("fx", C.c_float), ("fy", C.c_float),
                 ("cx", C.c_float), ("cy", C.c_float), ("minX", C.c_float), ("maxX", C.c_float), ("minY", C.c_float),
                 ("maxY", C.c_float), ("bf", C.c_float), ("logScaleFactor", C.c_float), ("viewingCosLimit", C.c_float),
-                ("nScaleLevels", C.c_int), ("logMode", C.c_int)]
+                ("nScaleLevels", C.c_int), ("logMode", C.c_int), ("cameraModel", C.c_int), ("kb", C.c_float * 4)]
 
 
 def undistort_points(pts, fx, fy, cx, cy, dist):

@@ -43,7 +43,9 @@ struct FrustumCam {
   float minX, maxX, minY, maxY;
   float bf, logScaleFactor, viewingCosLimit;
   int nScaleLevels;
-  int logMode;  // 0: logf (reference-literal, host libm); 1: (float)log((double)x) (portable, what the CUDA path implements)
+  int logMode;  // 0: logf / atan2f (reference-literal, host libm); 1: (float)log((double)x), (float)atan2((double)..) (portable, = CUDA path)
+  int cameraModel;  // 0 Pinhole::project, 1 KannalaBrandt8::project (KannalaBrandt8.cpp:29-45)
+  float kb[4];      // KB8 k1..k4
 };
 
 // Frame::isInFrustum, Nleft == -1 branch (Frame.cc:574-642).  Outputs per point: inView, mTrackProjX/Y/XR, mTrackDepth,
@@ -64,7 +66,19 @@ void oro_is_in_frustum(const FrustumCam* C, int n, const float* P /*n x 3*/, con
     const float PcZ = Pc[2];
     const float invz = 1.0f / PcZ;
     if (PcZ < 0.0f) continue;
-    const float ux = C->fx * Pc[0] / Pc[2] + C->cx, uy = C->fy * Pc[1] / Pc[2] + C->cy;
+    float ux, uy;
+    if (C->cameraModel == 1) {
+      const float x2y2 = Pc[0] * Pc[0] + Pc[1] * Pc[1];
+      const float theta = C->logMode == 0 ? atan2f(sqrtf(x2y2), Pc[2]) : (float)std::atan2((double)sqrtf(x2y2), (double)Pc[2]);
+      const float psi = C->logMode == 0 ? atan2f(Pc[1], Pc[0]) : (float)std::atan2((double)Pc[1], (double)Pc[0]);
+      const float theta2 = theta * theta, theta3 = theta * theta2, theta5 = theta3 * theta2, theta7 = theta5 * theta2, theta9 = theta7 * theta2;
+      const float r = theta + C->kb[0] * theta3 + C->kb[1] * theta5 + C->kb[2] * theta7 + C->kb[3] * theta9;
+      // cos(psi) / sin(psi): the double overloads (KannalaBrandt8.cpp has no using-directive) -> double product and sum
+      ux = (float)((double)(C->fx * r) * std::cos((double)psi) + (double)C->cx);
+      uy = (float)((double)(C->fy * r) * std::sin((double)psi) + (double)C->cy);
+    } else {
+      ux = C->fx * Pc[0] / Pc[2] + C->cx; uy = C->fy * Pc[1] / Pc[2] + C->cy;
+    }
     if (ux < C->minX || ux > C->maxX) continue;
     if (uy < C->minY || uy > C->maxY) continue;
     projX[i] = ux; projY[i] = uy;

@@ -30,7 +30,10 @@ def pose(seed):
     return R.astype(np.float32), t.astype(np.float32)
 
 
-def frustum_case(oracle, n, seed=0, log_mode=1):
+KB8_TUMVI = (0.003482389402, 0.000715034845, -0.002053236141, 0.000202936736)   # Examples/Monocular/TUM_512.yaml Camera.k1..k4
+
+
+def frustum_case(oracle, n, seed=0, log_mode=1, kb=None):
     """camera + n map points: in front / behind, inside / outside the image, in / out of the scale-invariance range, facing
     towards / away"""
     rng = np.random.default_rng(seed)
@@ -47,6 +50,9 @@ def frustum_case(oracle, n, seed=0, log_mode=1):
     cam.viewingCosLimit = 0.5
     cam.nScaleLevels = 8
     cam.logMode = log_mode
+    cam.cameraModel = 0 if kb is None else 1
+    if kb is not None:
+        cam.kb[:] = [float(k) for k in kb]
     # points in camera coordinates, then to the world
     z = rng.uniform(-2, 12, n)
     x = (rng.uniform(-0.3, 1.3, n) * 752 - cx) / fx * z

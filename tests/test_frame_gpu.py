@@ -48,16 +48,26 @@ def test_undistort_keypoints(pre, orbx, oracle, name):
     assert len(pre.UndistortKeyPoints(kps[:0], fx, fy, cx, cy, cam["D"])) == 0
 
 
-@pytest.mark.parametrize("n,seed", [(5000, 5), (1, 6), (70000, 7)])
-def test_is_in_frustum(pre, oracle, n, seed):
-    cam, P, normal, maxd, mind = fc.frustum_case(oracle, n, seed=seed, log_mode=oracle.LOG_PORTABLE)
+@pytest.mark.parametrize("n,seed,kb", [(5000, 5, None), (1, 6, None), (70000, 7, None), (20000, 8, fc.KB8_TUMVI)])
+def test_is_in_frustum(pre, oracle, n, seed, kb):
+    cam, P, normal, maxd, mind = fc.frustum_case(oracle, n, seed=seed, log_mode=oracle.LOG_PORTABLE, kb=kb)
     ref = oracle.is_in_frustum(cam, P, normal, maxd, mind)
     g = pre.mod.frustum(np.array(cam.Rcw[:]).reshape(3, 3), cam.tcw[:], cam.fx, cam.fy, cam.cx, cam.cy,
-                        (cam.minX, cam.maxX, cam.minY, cam.maxY), cam.bf, 1.2, cam.nScaleLevels, cam.viewingCosLimit)
+                        (cam.minX, cam.maxX, cam.minY, cam.maxY), cam.bf, 1.2, cam.nScaleLevels, cam.viewingCosLimit, kb=kb)
     assert np.array_equal(np.array(g.Ow[:], np.float32), np.array(cam.Ow[:], np.float32))
     out = pre.isInFrustum(g, P, normal, maxd, mind)
-    for k in KEYS:
-        assert np.array_equal(_bits(out[k]), _bits(ref[k])), k
+    if kb is None:
+        for k in KEYS:
+            assert np.array_equal(_bits(out[k]), _bits(ref[k])), k
+    else:
+        # KannalaBrandt8: atan2 / cos / sin come from two double-precision libraries (CUDA, glibc) that are each within 1-2 ulp
+        # of the exact value, so after the rounding to float a projection may differ in its last bit once in ~10^8 values.
+        # Tolerance: decisions and levels identical, at most 2 of the 2 x 20 000 projected coordinates off, by <= 1e-4 px.
+        assert np.array_equal(out["in_view"], ref["in_view"]) and np.array_equal(out["level"], ref["level"])
+        for k in ("proj_x", "proj_y", "proj_xr"):
+            assert (_bits(out[k]) != _bits(ref[k])).sum() <= 2 and np.abs(out[k] - ref[k]).max() <= 1e-4, k
+        for k in ("depth", "view_cos"):
+            assert np.array_equal(_bits(out[k]), _bits(ref[k])), k
     if n >= 5000:
         assert 0.1 < out["in_view"].mean() < 0.8 and len(np.unique(out["level"][out["in_view"] == 1])) >= 6
     # reference-literal logf on the host: same decisions and levels on this case

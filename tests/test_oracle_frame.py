@@ -30,7 +30,16 @@ def _frustum_numpy(cam, P, normal, maxd, mind, log_mode):
             out.append((0, -1, -1, 0, 0, -1, 0)); continue
         with np.errstate(all="ignore"):
             invz = f32(1) / Pc[2]
-            ux = f32(f32(f32(cam.fx) * Pc[0]) / Pc[2]) + f32(cam.cx); uy = f32(f32(f32(cam.fy) * Pc[1]) / Pc[2]) + f32(cam.cy)
+            if cam.cameraModel == 1:   # KannalaBrandt8::project, portable atan2 policy (log_mode 1)
+                th = f32(np.arctan2(np.float64(np.sqrt(f32(f32(Pc[0] * Pc[0]) + f32(Pc[1] * Pc[1])))), np.float64(Pc[2])))
+                psi = f32(np.arctan2(np.float64(Pc[1]), np.float64(Pc[0])))
+                t2 = f32(th * th); t3 = f32(th * t2); t5 = f32(t3 * t2); t7 = f32(t5 * t2); t9 = f32(t7 * t2)
+                k = [f32(v) for v in cam.kb[:]]
+                r = f32(f32(f32(f32(th + f32(k[0] * t3)) + f32(k[1] * t5)) + f32(k[2] * t7)) + f32(k[3] * t9))
+                ux = f32(np.float64(f32(f32(cam.fx) * r)) * np.cos(np.float64(psi)) + np.float64(f32(cam.cx)))
+                uy = f32(np.float64(f32(f32(cam.fy) * r)) * np.sin(np.float64(psi)) + np.float64(f32(cam.cy)))
+            else:
+                ux = f32(f32(f32(cam.fx) * Pc[0]) / Pc[2]) + f32(cam.cx); uy = f32(f32(f32(cam.fy) * Pc[1]) / Pc[2]) + f32(cam.cy)
         if not (ux >= f32(cam.minX) and ux <= f32(cam.maxX) and uy >= f32(cam.minY) and uy <= f32(cam.maxY)):
             if ux < f32(cam.minX) or ux > f32(cam.maxX) or uy < f32(cam.minY) or uy > f32(cam.maxY):
                 out.append((0, -1, -1, 0, 0, -1, 0)); continue
@@ -49,8 +58,9 @@ def _frustum_numpy(cam, P, normal, maxd, mind, log_mode):
     return out
 
 
-def test_is_in_frustum_matches_numpy_restatement(oracle):
-    cam, P, normal, maxd, mind = fc.frustum_case(oracle, 3000, seed=5)
+@pytest.mark.parametrize("kb", [None, fc.KB8_TUMVI])
+def test_is_in_frustum_matches_numpy_restatement(oracle, kb):
+    cam, P, normal, maxd, mind = fc.frustum_case(oracle, 3000, seed=5, kb=kb)
     o = oracle.is_in_frustum(cam, P, normal, maxd, mind)
     ref = _frustum_numpy(cam, P, normal, maxd, mind, cam.logMode)
     keys = ("in_view", "proj_x", "proj_y", "proj_xr", "depth", "level", "view_cos")
@@ -63,3 +73,5 @@ def test_is_in_frustum_matches_numpy_restatement(oracle):
     cam.logMode = oracle.LOG_LIBM_F32
     o2 = oracle.is_in_frustum(cam, P, normal, maxd, mind)
     assert np.array_equal(o2["in_view"], o["in_view"]) and (o2["level"] != o["level"]).sum() == 0
+    # ... and, for the fisheye model, move a projection by at most a few float ulps (libm atan2f against the rounded double atan2)
+    assert np.abs(o2["proj_x"] - o["proj_x"]).max() <= 2e-4 and np.abs(o2["proj_y"] - o["proj_y"]).max() <= 2e-4
