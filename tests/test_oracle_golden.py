@@ -1,4 +1,4 @@
-"""The oracle against its committed golden vectors (tests/golden/, made by tools/gen_golden.py) plus structural checks of
+"""The oracle against its committed golden vectors (tests/golden/, made by tests/golden/gen_golden.py) plus structural checks of
 the restated DistributeOctTree / operator() ordering.  The reference has no tests of its own for this path:
 these fixtures pin the oracle against regressions, the cv2 cross-checks (test_oracle_cv2.py) pin its primitives."""
 import glob

@@ -1,7 +1,8 @@
 #!/usr/bin/env python3
 """Host-call latency of ORBextractor::operator() on ONE frame (BASELINE.json configs[0]: 752x480, nFeatures 1000, EuRoC mono
-settings) -- the reference's per-frame use -- through orbx_extract (host image in, keypoints / descriptors out), next to the
-CPU oracle port on one thread.   python tools/extract_latency.py [reps=200]"""
+settings) -- the reference's per-frame use -- through orbx_extract (host image in, keypoints / descriptors out).  The CPU side
+of the comparison is bench.py's cpu_baseline (`two_thread_value`: one stereo frame at a time, one thread per image).
+    python tools/extract_latency.py [reps=200]"""
 import importlib
 import json
 import os
@@ -14,7 +15,6 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 orbx = importlib.import_module("3_orb_slam3_selfnote_b200")
 synth = importlib.import_module("3_orb_slam3_selfnote_b200.synth")
-import oracle  # noqa: E402  (reported baseline only)
 
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 200
 out = {}
@@ -30,13 +30,6 @@ for (w, h, nf, lap, name) in ((752, 480, 1000, (0, 1000), "euroc_mono_752x480_nf
         mono, k, d = gx(imgs[i % 8], None, lap)
         ts.append(time.perf_counter() - t0)
     ts = np.array(ts) * 1e3
-    ex = oracle.Extractor(nf, blur_taps=oracle.TAPS_OCV346, sincos_mode=oracle.SINCOS_PORTABLE)
-    tc = []
-    for i in range(10):
-        t0 = time.perf_counter()
-        ex(imgs[i % 8], lap)
-        tc.append(time.perf_counter() - t0)
-    out[name] = {"gpu_call_ms_median": float(np.median(ts)), "gpu_call_ms_p95": float(np.percentile(ts, 95)), "keypoints": int(len(k)),
-                 "cpu_oracle_1thread_ms_median": float(np.median(tc) * 1e3)}
+    out[name] = {"gpu_call_ms_median": float(np.median(ts)), "gpu_call_ms_p95": float(np.percentile(ts, 95)), "keypoints": int(len(k))}
     gx.close()
 print(json.dumps(out, indent=1))
