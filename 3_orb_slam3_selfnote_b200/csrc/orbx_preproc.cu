@@ -262,7 +262,10 @@ int orbx_clahe(orbx_preproc* p, const uint8_t* src, int nframes, int width, int 
     CK(cudaFuncSetAttribute(k_clahe_apply, cudaFuncAttributeMaxDynamicSharedMemorySize, 512 * 256));
     p->claheAttr = true;
   }
-  k_clahe_lut<<<dim3(tiles_x * tiles_y, nframes), 256, 0, S.st>>>(A);
+  static const bool lutV1 = getenv("ORBX_CLAHE_V1") != nullptr;   // A/B only: one CTA per tile
+  const int ntiles = tiles_x * tiles_y;
+  if (lutV1) k_clahe_lut<<<dim3(ntiles, nframes), 256, 0, S.st>>>(A);
+  else k_clahe_lut_w<<<(ntiles * nframes + 7) / 8, 256, 0, S.st>>>(A, ntiles, ntiles * nframes);
   const int wq = (width + 3) / 4, threads = wq >= 256 ? 256 : ((wq + 31) & ~31);
   k_clahe_apply<<<dim3((height + ORBX_CLAHE_ROWS - 1) / ORBX_CLAHE_ROWS, nframes), threads, nlut, S.st>>>(A);
   return S.finish();

@@ -223,6 +223,90 @@ __device__ __forceinline__ int reflect101_dev(int p, int len) {
   return p;
 }
 
+// Warp = one tile of one frame (8 tiles per CTA): a private 256-bin histogram per warp, no CTA barrier anywhere.  Rows are
+// taken four at a time so that four word loads per lane are in flight; then lane l owns bins 8l .. 8l+7 for the clip, the
+// redistribution, the running sum and the 8 LUT bytes it stores as one 64-bit word.
+__global__ void __launch_bounds__(256) k_clahe_lut_w(const __grid_constant__ ClaheArgs A, int ntiles /* tiles per frame */, int total /* x frames */) {
+  __shared__ int wh[8][256];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int job = blockIdx.x * 8 + warp;
+  if (job >= total) return;
+  const int frame = job / ntiles, tile = job - frame * ntiles, tx = tile % A.tilesX, ty = tile / A.tilesX;
+  const uint8_t* S = A.src + (long long)frame * A.sfs;
+  int* H = wh[warp];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) H[lane + 32 * j] = 0;
+  __syncwarp();
+  const bool inside = (tx + 1) * A.tw <= A.w && (ty + 1) * A.th <= A.h;
+  if (inside && A.vec) {
+    const int x0 = tx * A.tw, a0 = x0 & ~3, nw = (x0 + A.tw - a0 + 3) >> 2;
+    const uint8_t* base = S + (long long)(ty * A.th) * A.sstride + a0;
+    for (int w0 = 0; w0 < nw; w0 += 32) {
+      const int wi = w0 + lane, xb = a0 + wi * 4;
+      const bool on = wi < nw;
+      const bool whole = on && xb + 4 <= A.w;
+      unsigned lo = 0, hi = 0;   // byte range of this word inside [x0, x0 + tw)
+      if (on) { lo = (unsigned)max(x0 - xb, 0); hi = (unsigned)min(x0 + A.tw - xb, 4); }
+      for (int r = 0; r < A.th; r += 4) {
+        unsigned q[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          q[k] = 0;
+          if (on && r + k < A.th) {
+            const uint8_t* pw = base + (long long)(r + k) * A.sstride + wi * 4;
+            if (whole) q[k] = __ldg(reinterpret_cast<const unsigned*>(pw));
+            else for (unsigned b = lo; b < hi; ++b) q[k] |= (unsigned)__ldg(pw + b) << (8 * b);
+          }
+        }
+        // (electing one lane per bin with __match_any_sync before the atomic was measured at 0.93 ms per 256 frames against
+        // 0.26 ms for the plain shared-memory atomics below: match.any costs far more than the serialisation it removes)
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (on && r + k < A.th)
+            for (unsigned b = lo; b < hi; ++b) atomicAdd(&H[(q[k] >> (8 * b)) & 255u], 1);
+      }
+    }
+  } else {
+    const int npx = A.tw * A.th;
+    for (int i = lane; i < npx; i += 32) {
+      int yy = ty * A.th + i / A.tw, xx = tx * A.tw + i % A.tw;
+      if (!inside) { yy = reflect101_dev(yy, A.h); xx = reflect101_dev(xx, A.w); }
+      atomicAdd(&H[__ldg(S + (long long)yy * A.sstride + xx)], 1);
+    }
+  }
+  __syncwarp();
+  int hv[8], ex = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    hv[j] = H[lane * 8 + j];
+    if (A.clip > 0 && hv[j] > A.clip) { ex += hv[j] - A.clip; hv[j] = A.clip; }
+  }
+  if (A.clip > 0) {
+    for (int o = 16; o; o >>= 1) ex += __shfl_xor_sync(0xffffffffu, ex, o);
+    const int batch = ex >> 8, residual = ex - (batch << 8);
+    const int step = residual ? max(256 / residual, 1) : 1;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int i = lane * 8 + j;
+      hv[j] += batch;
+      if (residual != 0 && i % step == 0 && i / step < residual) hv[j]++;
+    }
+  }
+  int local = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { local += hv[j]; hv[j] = local; }
+  int incl = local;
+  for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+  const int before = incl - local;
+  unsigned w0 = 0, w1 = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int v = min(max(__float2int_rn(__fmul_rn((float)(before + hv[j]), A.lutScale)), 0), 255);
+    if (j < 4) w0 |= (unsigned)v << (8 * j); else w1 |= (unsigned)v << (8 * (j - 4));
+  }
+  *reinterpret_cast<uint2*>(A.lut + ((long long)frame * ntiles + tile) * 256 + lane * 8) = make_uint2(w0, w1);
+}
+
 // CTA = one tile of one frame: per-warp shared histograms, clip + redistribute, 256-wide inclusive scan, LUT.
 __global__ void __launch_bounds__(256) k_clahe_lut(const __grid_constant__ ClaheArgs A) {
   // one sub-histogram per warp.  (32 sub-histograms -- one per (warp, lane & 3), so that the correlated pixels of adjacent lanes
