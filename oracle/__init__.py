@@ -20,11 +20,34 @@ KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4
 assert KP_DTYPE.itemsize == 28
 
 
+def _host_tag():
+    """CPU model of this host: liborb_oracle.so is built -march=native, so a library built on another
+    machine (the build container's .so travels to the GPU box) is rebuilt here instead of being reused."""
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("model name") or line.startswith("flags"):
+                    if line.startswith("flags"):
+                        return model + "|" + str(hash(line) & 0xFFFFFFFF)
+                    model = line.split(":", 1)[1].strip()
+    except Exception:
+        pass
+    return "unknown"
+
+
 def build(force=False):
     srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.cc", "match_oracle.cc", "oracle_capi.cc", "preproc_oracle.cc", "frame_oracle.cc", "orb_oracle.h",
                                              "match_oracle.h", "Makefile")]
-    if force or not os.path.exists(_LIB) or any(os.path.getmtime(s) > os.path.getmtime(_LIB) for s in srcs):
-        subprocess.check_call(["make", "-C", _HERE, "-B", "liborb_oracle.so"], stdout=subprocess.DEVNULL)
+    tagfile = _LIB + ".host"
+    tag = _host_tag()
+    try:
+        built_for = open(tagfile).read()
+    except OSError:
+        built_for = ""
+    if force or not os.path.exists(_LIB) or built_for != tag or any(os.path.getmtime(s) > os.path.getmtime(_LIB) for s in srcs):
+        subprocess.check_call(["make", "-C", _HERE, "-B", "liborb_oracle.so", "ORACLE_MARCH=native"], stdout=subprocess.DEVNULL)
+        with open(tagfile, "w") as f:
+            f.write(tag)
     return _LIB
 
 

@@ -16,6 +16,7 @@
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
 // may load this library.  The product (liborbx.so) never links or calls it.
 #pragma once
+#include <cstddef>
 #include <cstdint>
 #include <vector>
 

@@ -31,3 +31,10 @@ def oracle():
     import oracle as o
     o.build()
     return o
+
+
+@pytest.fixture(scope="session")
+def oref():
+    """oracle/_ref: the reference's own ORBextractor.cc compiled unmodified (None when neither prebuilt nor buildable)."""
+    from oracle import ref
+    return ref if ref.available() else None

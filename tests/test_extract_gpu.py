@@ -38,7 +38,7 @@ def _assert_same(kg, dg, ko, do, what=""):
     (333, 251, 500, (100, 200), 0),   # odd sizes
     (752, 480, 5000, (0, 1000), 0),   # mono-initialisation extractor: 5 x nFeatures (Tracking.cc:844)
 ])
-def test_extract_matches_oracle(orbx, oracle, synth, w, h, nfeat, lap, taps):
+def test_extract_matches_oracle(orbx, oracle, oref, synth, w, h, nfeat, lap, taps):
     img = synth.frame(w, h, 100 + nfeat, 3)
     ex = oracle.Extractor(nfeat, blur_taps=taps, sincos_mode=oracle.SINCOS_PORTABLE)
     mono_o, ko, do = ex(img, lap)
@@ -46,6 +46,10 @@ def test_extract_matches_oracle(orbx, oracle, synth, w, h, nfeat, lap, taps):
     mono_g, kg, dg = gx(img, None, lap)
     assert mono_g == mono_o
     _assert_same(kg, dg, ko, do, "%dx%d" % (w, h))
+    if oref is not None:   # the reference's own ORBextractor.cc, compiled unmodified (oracle/_ref)
+        mono_r, kr, dr = oref.RefExtractor(nfeat, blur_taps=taps)(img, lap)
+        assert mono_g == mono_r
+        _assert_same(kg, dg, kr, dr, "%dx%d vs reference source" % (w, h))
     for l in range(8):
         assert np.array_equal(gx.pyramid_level(l), ex.level(l)), "pyramid level %d" % l
         assert np.array_equal(gx.debug_blurred_level(l), oracle.blur7(ex.level(l), taps)), "blurred level %d" % l
@@ -63,7 +67,7 @@ def test_extract_matches_oracle(orbx, oracle, synth, w, h, nfeat, lap, taps):
     (752, 480, 1000, 1.2, 8, 40, 12),     # other FAST thresholds (more cells take the minThFAST fallback)
     (752, 480, 300, 1.1, 12, 20, 7),      # many shallow levels
 ])
-def test_extract_other_geometries(orbx, oracle, synth, w, h, nfeat, scale, nlevels, ini, mn):
+def test_extract_other_geometries(orbx, oracle, oref, synth, w, h, nfeat, scale, nlevels, ini, mn):
     img = synth.frame(w, h, 300 + nfeat, 1)
     ex = oracle.Extractor(nfeat, scaleFactor=scale, nlevels=nlevels, iniThFAST=ini, minThFAST=mn, sincos_mode=oracle.SINCOS_PORTABLE)
     mono_o, ko, do = ex(img, (0, 0))
@@ -71,6 +75,13 @@ def test_extract_other_geometries(orbx, oracle, synth, w, h, nfeat, scale, nleve
     mono_g, kg, dg = gx(img, None, (0, 0))
     assert mono_g == mono_o
     _assert_same(kg, dg, ko, do, "%dx%d scale %.1f" % (w, h, scale))
+    if oref is not None:
+        rx = oref.RefExtractor(nfeat, scale, nlevels, ini, mn)
+        mono_r, kr, dr = rx(img, (0, 0))
+        assert mono_g == mono_r
+        _assert_same(kg, dg, kr, dr, "%dx%d scale %.1f vs reference source" % (w, h, scale))
+        for l in range(nlevels):
+            assert np.array_equal(gx.pyramid_level(l), rx.level(l)), "mvImagePyramid[%d] vs reference source" % l
     for l in range(nlevels):
         assert np.array_equal(gx.pyramid_level(l), ex.level(l)), "pyramid level %d" % l
     gx.close()
@@ -99,6 +110,7 @@ def test_golden_fixtures(orbx, synth):
     assert len(files) >= 5
     for fn in files:
         g = np.load(fn)
+        assert str(g["source"]) == "reference"   # fixtures hold the output of the reference's own compiled source
         w, h, nfeat, seed, fid, right, lap0, lap1 = [int(v) for v in g["spec"]]
         img = synth.frame(w, h, seed, fid, bool(right))
         assert zlib.crc32(img.tobytes()) == int(g["image_crc"])
@@ -157,7 +169,7 @@ def test_strided_input_and_reuse_across_sizes(orbx, oracle, synth):
     gx.close()
 
 
-def test_edge_cases(orbx, oracle):
+def test_edge_cases(orbx, oracle, oref):
     gx = orbx.ORBextractor(1000)
     # empty image -> -1 (src/ORBextractor.cc:1075-1076)
     mono, k, d = gx(np.empty((0, 0), np.uint8))
@@ -185,6 +197,10 @@ def test_edge_cases(orbx, oracle):
         mg, kg, dg = gx(img, None, (0, 0))
         assert mg == mo, name
         _assert_same(kg, dg, ko, do, name)
+        if oref is not None:
+            mr, kr, dr = oref.RefExtractor(1000)(img, (0, 0))
+            assert mg == mr
+            _assert_same(kg, dg, kr, dr, name + " vs reference source")
     gx.close()
 
 

@@ -1,6 +1,7 @@
-"""The oracle against its committed golden vectors (tests/golden/, made by tests/golden/gen_golden.py) plus structural checks of
-the restated DistributeOctTree / operator() ordering.  The reference has no tests of its own for this path:
-these fixtures pin the oracle against regressions, the cv2 cross-checks (test_oracle_cv2.py) pin its primitives."""
+"""The oracle against the committed golden vectors (tests/golden/, made by tests/golden/gen_golden.py from the REFERENCE'S OWN
+ORBextractor.cc compiled unmodified -- `source` == "reference") plus structural checks of the restated DistributeOctTree /
+operator() ordering.  The reference has no tests of its own for this path: these fixtures carry the
+reference's output to hosts where /root/reference does not exist; the cv2 cross-checks (test_oracle_cv2.py) pin the primitives."""
 import glob
 import os
 import zlib
@@ -16,6 +17,7 @@ def test_oracle_reproduces_golden(oracle, synth):
     for fn in files:
         g = np.load(fn)
         w, h, nfeat, seed, fid, right, lap0, lap1 = [int(v) for v in g["spec"]]
+        assert str(g["source"]) == "reference", "fixture was not generated from the reference source"
         img = synth.frame(w, h, seed, fid, bool(right))
         assert zlib.crc32(img.tobytes()) == int(g["image_crc"]), "synthetic generator changed"
         ex = oracle.Extractor(nfeat, blur_taps=oracle.TAPS_OCV346, sincos_mode=oracle.SINCOS_PORTABLE)
