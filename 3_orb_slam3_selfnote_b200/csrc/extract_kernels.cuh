@@ -3,13 +3,13 @@
 // u16x2 SIMD-in-register min/max (VIMNMX3.U16x2) for the FAST arcs, dp4a for the blur taps, warp shuffles for reductions.
 // No tensor cores: nothing here is a dense floating-point contraction.
 //
-// Reference stages (wangyunpeng139/3_ORB_SLAM3_SelfNote):
-//   k_pyr_resize   ORBextractor::ComputePyramid            src/ORBextractor.cc:1186-1219  (cv::resize INTER_LINEAR 8U)
-//   k_fast_nms     ComputeKeyPointsOctTree cell loop        src/ORBextractor.cc:787-854   (cv::FAST 9/16 + NMS per cell)
-//   k_quadtree     DistributeOctTree / DivideNode           src/ORBextractor.cc:479-761
-//   k_blur7        GaussianBlur(7x7, 2, REFLECT_101)        src/ORBextractor.cc:1132-1141
-//   k_assemble     operator() output ordering               src/ORBextractor.cc:1118,1164-1178
-//   k_orient_desc  IC_Angle + computeOrbDescriptor          src/ORBextractor.cc:75-145, 470-477, 1059-1066
+// Reference stages (wangyunpeng139/3_ORB_SLAM3_SelfNote) and the file that holds each kernel:
+//   k_pyr_resize3  ORBextractor::ComputePyramid            src/ORBextractor.cc:1186-1219  (cv::resize INTER_LINEAR 8U)   pyr_resize.cuh
+//   k_fast_nms3    ComputeKeyPointsOctTree cell loop        src/ORBextractor.cc:787-854   (cv::FAST 9/16 + NMS per cell)  fast_nms3.cuh
+//   k_quadtree     DistributeOctTree / DivideNode           src/ORBextractor.cc:479-761                                   this file
+//   k_blur7v       GaussianBlur(7x7, 2, REFLECT_101)        src/ORBextractor.cc:1132-1141                                 blur7.cuh
+//   k_assemble     operator() output ordering               src/ORBextractor.cc:1118,1164-1178                            this file
+//   k_orient_desc2 IC_Angle + computeOrbDescriptor          src/ORBextractor.cc:75-145, 470-477, 1059-1066                orient_desc.cuh
 #pragma once
 #include <cuda_runtime.h>
 #include <float.h>
@@ -18,213 +18,6 @@
 #include "geom.h"
 
 namespace orbx {
-
-// ---------------------------------------------------------------------------------------------------------------
-// Pyramid: level L from level L-1, OpenCV's fixed-point bilinear (Q11 weights).
-// Thread = 4 destination pixels (one 32-bit store); block 32x8 threads = 128x8 pixels; grid.z = frame.
-// ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_pyr_resize(const __grid_constant__ Geom g, const __grid_constant__ Batch b, int level) {
-  const LevelGeom& L = g.lv[level];
-  const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
-  const int y = blockIdx.y * 8 + threadIdx.y;
-  const int f = blockIdx.z;
-  if (x4 >= L.w || y >= L.h) return;
-  int sp;
-  const uint8_t* src = level_ptr(g, b, level - 1, f, sp);
-  const RsY ry = b.rsy[L.rsyOff + y];
-  const uint8_t* r0 = src + (long long)ry.s0 * sp;
-  const uint8_t* r1 = src + (long long)ry.s1 * sp;
-  uint32_t out = 0;
-#pragma unroll
-  for (int i = 0; i < 4; i++) {
-    const RsX rx = b.rsx[L.rsxOff + x4 + i];  // table is padded to a multiple of 4 entries
-    const int h0 = (int)__ldg(r0 + rx.s0) * rx.a0 + (int)__ldg(r0 + rx.s1) * rx.a1;
-    const int h1 = (int)__ldg(r1 + rx.s0) * rx.a0 + (int)__ldg(r1 + rx.s1) * rx.a1;
-    int v = ((((int)ry.b0 * (h0 >> 4)) >> 16) + (((int)ry.b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-    v = min(255, max(0, v));
-    out |= (uint32_t)v << (8 * i);
-  }
-  uint8_t* dst = b.pyr + (long long)f * b.pyrFrameStride + L.pyrOff + (long long)y * L.pitch + x4;
-  *reinterpret_cast<uint32_t*>(dst) = out;
-}
-
-// ---------------------------------------------------------------------------------------------------------------
-// FAST-9/16 score + per-cell 3x3 NMS.
-//   S(p) = max over the 16 arcs of 9 ring pixels of max(min(ring) - v, v - max(ring))  (SURVEY.md §9.3); a pixel is a
-//   cell keypoint at threshold t iff S > t and S is strictly greater than S of its 8 neighbours that lie in the same
-//   cell interior.  The ini/min threshold choice is per cell (src/ORBextractor.cc:825-828): this kernel emits every
-//   local maximum with S > minTh as a "pre-candidate" and raises cellFlags[cell] when one has S > iniTh; the quadtree
-//   kernel applies the per-cell choice when it loads its level.
-// CTA = one 62x30 output tile of one level of one frame.  Window 70x38 pixels is staged in shared memory twice as
-// u16 pairs -- copy A = (col 2j, 2j+1), copy B = (col 2j+1, 2j+2) -- so that every ring pixel of a horizontally adjacent
-// pixel PAIR is one aligned 32-bit LDS and all arc min/max run as 2-wide VIMNMX3.U16x2.
-// ---------------------------------------------------------------------------------------------------------------
-constexpr int kWinH = kTileH + 8;   // 38 window rows
-constexpr int kRawWords = 20;       // 80 raw bytes per row (70 + alignment slack)
-constexpr int kPairWords = 36;      // 72 columns per row as pairs
-
-template <int DX, int DY>
-__device__ __forceinline__ uint32_t ring_ld(const uint32_t* sA, const uint32_t* sB, int sr, int p) {
-  constexpr bool odd = (DX & 1) != 0;
-  const int row = sr + 3 + DY;
-  if (odd) return sA[row * kPairWords + p + (3 + DX) / 2];
-  return sB[row * kPairWords + p + 1 + DX / 2];
-}
-
-// (first version, kept for A/B comparison through ORBX_FAST_V1=1; the tuned kernel is k_fast_nms in fast_nms.cuh)
-__global__ void __launch_bounds__(256) k_fast_nms_v1(const __grid_constant__ Geom g, const __grid_constant__ Batch b) {
-  __shared__ uint32_t sRaw[kWinH * kRawWords];
-  __shared__ uint32_t sA[kWinH * kPairWords];
-  __shared__ uint32_t sB[kWinH * kPairWords];
-  __shared__ uint16_t sS[32 * 32];  // 64x32 scores as bytes
-
-  const int tid = threadIdx.x;
-  const int f = blockIdx.y;
-  int level = 0;
-  while (level + 1 < g.nlevels && (int)blockIdx.x >= g.lv[level + 1].tileBase) level++;
-  const LevelGeom& L = g.lv[level];
-  const int t = blockIdx.x - L.tileBase;
-  const int tx = t % L.tilesX, ty = t / L.tilesX;
-  const int ox = kEdge + kTileW * tx, oy = kEdge + kTileH * ty;  // first output pixel of the tile
-  const int wx0 = ox - 4, wy0 = oy - 4;                          // window origin
-  const int a = wx0 & 3, gx0 = wx0 - a;
-  int sp;
-  const uint8_t* src = level_ptr(g, b, level, f, sp);
-
-  // stage 1: aligned 32-bit global loads of the window rows
-  for (int i = tid; i < kWinH * kRawWords; i += 256) {
-    const int r = i / kRawWords, k = i - r * kRawWords;
-    const int gy = min(wy0 + r, L.h - 1);
-    const int gx = min(gx0 + 4 * k, sp - 4);
-    sRaw[i] = __ldg(reinterpret_cast<const uint32_t*>(src + (long long)gy * sp + gx));
-  }
-  __syncthreads();
-  // stage 2: expand to the two u16-pair copies
-  {
-    const uint8_t* rawb = reinterpret_cast<const uint8_t*>(sRaw);
-    for (int i = tid; i < kWinH * kPairWords; i += 256) {
-      const int r = i / kPairWords, j = i - r * kPairWords;
-      const int base = r * (kRawWords * 4) + 2 * j + a;
-      const uint32_t b0 = rawb[base], b1 = rawb[base + 1], b2 = rawb[base + 2];
-      sA[i] = b0 | (b1 << 16);
-      sB[i] = b1 | (b2 << 16);
-    }
-  }
-  __syncthreads();
-
-  const int warp = tid >> 5, p = tid & 31;
-  const uint32_t kBias = 0x01000100u;
-  const uint32_t thr2 = (uint32_t)g.minTh * 0x00010001u;
-  for (int sr = warp; sr < 32; sr += 8) {
-    const int y = oy - 1 + sr, x0 = ox - 1 + 2 * p;
-    const bool rowin = (y >= kEdge) && (y < L.h - kEdge);
-    const bool in0 = rowin && (x0 >= kEdge) && (x0 < L.w - kEdge);
-    const bool in1 = rowin && (x0 + 1 >= kEdge) && (x0 + 1 < L.w - kEdge);
-    const uint32_t v = sB[(sr + 3) * kPairWords + p + 1];
-    const uint32_t vb = v + kBias;
-    uint32_t S2 = 0;
-    // compass bound: every 9-arc holds one of (r0|r8) and one of (r4|r12)  =>  S <= Q
-    const uint32_t r0 = ring_ld<0, 3>(sA, sB, sr, p), r8 = ring_ld<0, -3>(sA, sB, sr, p);
-    const uint32_t r4 = ring_ld<3, 0>(sA, sB, sr, p), r12 = ring_ld<-3, 0>(sA, sB, sr, p);
-    {
-      const uint32_t hi = __vminu2(__vmaxu2(r0, r8), __vmaxu2(r4, r12));
-      const uint32_t lo = __vmaxu2(__vminu2(r0, r8), __vminu2(r4, r12));
-      const uint32_t q = __vmaxu2((hi + kBias) - v, vb - lo);             // biased by 256 per lane
-      const uint32_t pass = __vmaxu2(q, thr2 + kBias) ^ (thr2 + kBias);  // != 0 iff some lane has Q > minTh
-      const bool need = (pass != 0) && (in0 || in1);
-      if (__any_sync(ORBX_FULL, need)) {
-        const uint32_t r1 = ring_ld<1, 3>(sA, sB, sr, p), r2 = ring_ld<2, 2>(sA, sB, sr, p), r3 = ring_ld<3, 1>(sA, sB, sr, p);
-        const uint32_t r5 = ring_ld<3, -1>(sA, sB, sr, p), r6 = ring_ld<2, -2>(sA, sB, sr, p), r7 = ring_ld<1, -3>(sA, sB, sr, p);
-        const uint32_t r9 = ring_ld<-1, -3>(sA, sB, sr, p), r10 = ring_ld<-2, -2>(sA, sB, sr, p), r11 = ring_ld<-3, -1>(sA, sB, sr, p);
-        const uint32_t r13 = ring_ld<-3, 1>(sA, sB, sr, p), r14 = ring_ld<-2, 2>(sA, sB, sr, p), r15 = ring_ld<-1, 3>(sA, sB, sr, p);
-        const uint32_t r[16] = {r0, r1, r2, r3, r4, r5, r6, r7, r8, r9, r10, r11, r12, r13, r14, r15};
-        uint32_t n3[16], x3[16];
-#pragma unroll
-        for (int k = 0; k < 16; k++) {
-          n3[k] = __vimin3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
-          x3[k] = __vimax3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
-        }
-        uint32_t n9[16], x9[16];
-#pragma unroll
-        for (int k = 0; k < 16; k++) {
-          n9[k] = __vimin3_u16x2(n3[k], n3[(k + 3) & 15], n3[(k + 6) & 15]);
-          x9[k] = __vimax3_u16x2(x3[k], x3[(k + 3) & 15], x3[(k + 6) & 15]);
-        }
-        uint32_t mxn = __vimax3_u16x2(n9[0], n9[1], n9[2]), mnx = __vimin3_u16x2(x9[0], x9[1], x9[2]);
-#pragma unroll
-        for (int k = 3; k < 15; k += 2) {
-          mxn = __vimax3_u16x2(mxn, n9[k], n9[k + 1]);
-          mnx = __vimin3_u16x2(mnx, x9[k], x9[k + 1]);
-        }
-        mxn = __vmaxu2(mxn, n9[15]);
-        mnx = __vminu2(mnx, x9[15]);
-        // S + 256 per lane; clamp at 0
-        uint32_t s = __vmaxu2(__vmaxu2((mxn + kBias) - v, vb - mnx), kBias) - kBias;
-        uint32_t s0 = s & 0xffffu, s1 = s >> 16;
-        if (!in0 || s0 <= (uint32_t)g.minTh) s0 = 0;
-        if (!in1 || s1 <= (uint32_t)g.minTh) s1 = 0;
-        S2 = s0 | (s1 << 8);
-      }
-    }
-    sS[sr * 32 + p] = (uint16_t)S2;
-  }
-  __syncthreads();
-
-  // NMS inside the owning cell + emission
-  const uint8_t* S8 = reinterpret_cast<const uint8_t*>(sS);
-  PreCand* cand = b.cand + (long long)f * g.candSlab + L.candOff;
-  int* candCount = b.candCount + f * ORBX_MAX_LEVELS + level;
-  int* cellFlags = b.cellFlags + (long long)f * g.nCellsTotal + L.cellBase;
-  for (int sr = 1 + warp; sr <= kTileH; sr += 8) {
-    const uint32_t mine = sS[sr * 32 + p];
-    const int y = oy - 1 + sr;
-#pragma unroll
-    for (int half = 0; half < 2; half++) {
-      const int sc = 2 * p + half;
-      const int s = (mine >> (8 * half)) & 0xff;
-      bool keep = false;
-      int x = ox - 1 + sc, cell = 0;
-      if (s > 0 && sc >= 1 && sc <= kTileW) {
-        const uint32_t ci = b.info[L.colInfoOff + x], ri = b.info[L.rowInfoOff + y];
-        const bool fc = ci & 0x4000u, lc = ci & 0x8000u, fr = ri & 0x4000u, lr = ri & 0x8000u;
-        const uint8_t* c = S8 + sr * 64 + sc;
-        int m = 0;
-        if (!fr) {
-          if (!fc) m = max(m, (int)c[-65]);
-          m = max(m, (int)c[-64]);
-          if (!lc) m = max(m, (int)c[-63]);
-        }
-        if (!fc) m = max(m, (int)c[-1]);
-        if (!lc) m = max(m, (int)c[1]);
-        if (!lr) {
-          if (!fc) m = max(m, (int)c[63]);
-          m = max(m, (int)c[64]);
-          if (!lc) m = max(m, (int)c[65]);
-        }
-        keep = s > m;
-        cell = (int)(ri & 0x3fffu) * L.nCols + (int)(ci & 0x3fffu);
-      }
-      const uint32_t mask = __ballot_sync(ORBX_FULL, keep);
-      if (mask) {
-        int base = 0;
-        const int leader = __ffs(mask) - 1;
-        if (p == leader) base = atomicAdd(candCount, __popc(mask));
-        base = __shfl_sync(ORBX_FULL, base, leader);
-        if (keep) {
-          const int idx = base + __popc(mask & ((1u << p) - 1));
-          if (idx < L.candCap) {
-            PreCand pc;
-            pc.x = (uint16_t)x; pc.y = (uint16_t)y; pc.cell = (uint16_t)cell; pc.S = (uint8_t)s; pc.pad = 0;
-            cand[idx] = pc;
-          } else {
-            atomicExch(b.status, ORBX_ERR_CAPACITY);
-          }
-          if (s > g.iniTh) atomicOr(cellFlags + cell, 1);
-        }
-      }
-    }
-  }
-}
 
 // ---------------------------------------------------------------------------------------------------------------
 // Quadtree distribution: one CTA per (level, frame).  The reference's std::list algorithm is restated as data-parallel
@@ -540,88 +333,6 @@ __global__ void __launch_bounds__(256) k_quadtree(const __grid_constant__ Geom g
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// 7x7 Gaussian blur, OpenCV's 8-bit fixed-point path (Q8.8 horizontal into u16, Q16.16 vertical, +0x8000 >> 16),
-// BORDER_REFLECT_101 taken from the level itself.  CTA = 128x16 output tile; horizontal pass with
-// dp4a over byte quads from shared memory, vertical pass with 32-bit IMADs; 32-bit stores.
-// ---------------------------------------------------------------------------------------------------------------
-constexpr int kBlurW = 128, kBlurH = 16;
-constexpr int kBlurRawW = kBlurW + 8;  // bytes per staged row: x0-4 .. x0+131
-
-__device__ __forceinline__ int refl101(int i, int n) {
-  if (i < 0) i = -i;
-  if (i >= n) i = 2 * (n - 1) - i;
-  return max(0, min(n - 1, i));  // (only reached twice-reflected on degenerate tiny levels)
-}
-
-__global__ void __launch_bounds__(256) k_blur7(const __grid_constant__ Geom g, const __grid_constant__ Batch b) {
-  __shared__ uint32_t sRaw[(kBlurH + 6) * (kBlurRawW / 4)];
-  __shared__ uint32_t sHz[(kBlurH + 6) * (kBlurW / 2)];  // u16 pairs
-  const int tid = threadIdx.x, f = blockIdx.y;
-  int level = 0;
-  while (level + 1 < g.nlevels && (int)blockIdx.x >= g.lv[level + 1].blurTileBase) level++;
-  const LevelGeom& L = g.lv[level];
-  const int t = blockIdx.x - L.blurTileBase;
-  const int tx = t % L.blurTilesX, ty = t / L.blurTilesX;
-  const int x0 = tx * kBlurW, y0 = ty * kBlurH;
-  int sp;
-  const uint8_t* src = level_ptr(g, b, level, f, sp);
-  const bool interior = (x0 >= 4) && (x0 + kBlurW + 4 <= L.w) && ((sp & 3) == 0);
-  if (interior) {
-    for (int i = tid; i < (kBlurH + 6) * (kBlurRawW / 4); i += 256) {
-      const int r = i / (kBlurRawW / 4), k = i - r * (kBlurRawW / 4);
-      const int gy = refl101(y0 - 3 + r, L.h);
-      sRaw[i] = __ldg(reinterpret_cast<const uint32_t*>(src + (long long)gy * sp + x0 - 4 + 4 * k));
-    }
-  } else {
-    uint8_t* rawb = reinterpret_cast<uint8_t*>(sRaw);
-    for (int i = tid; i < (kBlurH + 6) * kBlurRawW; i += 256) {
-      const int r = i / kBlurRawW, c = i - r * kBlurRawW;
-      const int gy = refl101(y0 - 3 + r, L.h), gx = refl101(x0 - 4 + c, L.w);
-      rawb[i] = __ldg(src + (long long)gy * sp + gx);
-    }
-  }
-  __syncthreads();
-  const uint32_t tapLo = (uint32_t)g.taps[0] | ((uint32_t)g.taps[1] << 8) | ((uint32_t)g.taps[2] << 16) | ((uint32_t)g.taps[3] << 24);
-  const uint32_t tapHi = (uint32_t)g.taps[4] | ((uint32_t)g.taps[5] << 8) | ((uint32_t)g.taps[6] << 16);
-  // horizontal: task = 4 consecutive pixels of one staged row
-  for (int i = tid; i < (kBlurH + 6) * (kBlurW / 4); i += 256) {
-    const int r = i / (kBlurW / 4), q = i - r * (kBlurW / 4);
-    const uint32_t* row = sRaw + r * (kBlurRawW / 4) + q;   // bytes x-4 .. x+7 of pixel quad x = x0+4q
-    const uint32_t w0 = row[0], w1 = row[1], w2 = row[2];
-    uint32_t hz[4];
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-      // taps cover bytes (k+1 .. k+7) of the 12 staged bytes
-      const uint32_t lo = (k == 3) ? w1 : __funnelshift_r(w0, w1, 8 * (k + 1));
-      const uint32_t hi = (k == 3) ? w2 : __funnelshift_r(w1, w2, 8 * (k + 1));
-      uint32_t acc = __dp4a(lo, tapLo, 0u);
-      acc = __dp4a(hi, tapHi, acc);
-      hz[k] = min(acc, 65535u);
-    }
-    sHz[r * (kBlurW / 2) + 2 * q] = hz[0] | (hz[1] << 16);
-    sHz[r * (kBlurW / 2) + 2 * q + 1] = hz[2] | (hz[3] << 16);
-  }
-  __syncthreads();
-  uint8_t* dst = b.blur + (long long)f * b.blurFrameStride + L.blurOff;
-  for (int i = tid; i < kBlurH * (kBlurW / 4); i += 256) {
-    const int r = i / (kBlurW / 4), q = i - r * (kBlurW / 4);
-    const int x = x0 + 4 * q, y = y0 + r;
-    if (x >= L.w || y >= L.h) continue;
-    uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-#pragma unroll
-    for (int k = 0; k < 7; k++) {
-      const uint32_t p0 = sHz[(r + k) * (kBlurW / 2) + 2 * q], p1 = sHz[(r + k) * (kBlurW / 2) + 2 * q + 1];
-      const uint32_t tk = (uint32_t)g.taps[k];
-      a0 += tk * (p0 & 0xffffu); a1 += tk * (p0 >> 16);
-      a2 += tk * (p1 & 0xffffu); a3 += tk * (p1 >> 16);
-    }
-    const uint32_t o0 = min(255u, (a0 + 32768u) >> 16), o1 = min(255u, (a1 + 32768u) >> 16);
-    const uint32_t o2 = min(255u, (a2 + 32768u) >> 16), o3 = min(255u, (a3 + 32768u) >> 16);
-    *reinterpret_cast<uint32_t*>(dst + (long long)y * L.blurPitch + x) = o0 | (o1 << 8) | (o2 << 16) | (o3 << 24);
-  }
-}
-
-// ---------------------------------------------------------------------------------------------------------------
 // Output ordering of operator(): keypoints whose scaled x lies in [lap0, lap1] are written from the back, the others
 // from the front, level-major (src/ORBextractor.cc:1118, 1164-1178).  One CTA per frame computes every level
 // keypoint's final slot with two running exclusive scans.
@@ -686,77 +397,6 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
   if (x < 0) a = __fsub_rn(180.f, a);
   if (y < 0) a = __fsub_rn(360.f, a);
   return a;
-}
-
-__global__ void __launch_bounds__(256) k_orient_desc(const __grid_constant__ Geom g, const __grid_constant__ Batch b) {
-  const int f = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int slot = blockIdx.x * 8 + warp;
-  if (slot >= g.kpSlab) return;
-  int level = 0;
-  while (level + 1 < g.nlevels && slot >= g.lv[level + 1].kpOff) level++;
-  const LevelGeom& L = g.lv[level];
-  const int i = slot - L.kpOff;
-  if (i >= b.lkpCount[f * ORBX_MAX_LEVELS + level]) return;
-  const LevelKp kp = b.lkp[(long long)f * g.kpSlab + slot];
-  const int dest = b.lkpDest[(long long)f * g.kpSlab + slot];
-  int sp;
-  const uint8_t* img = level_ptr(g, b, level, f, sp);
-  // IC_Angle: m10 = sum u*I, m01 = sum v*I over the radius-15 disc
-  int m10 = 0, m01 = 0;
-  {
-    const int u = lane - kHalfPatch;
-    const int au = abs(u);
-    const uint8_t* c = img + (long long)kp.y * sp + kp.x + u;
-    if (lane < 31) {
-#pragma unroll 1
-      for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
-        if (au <= g.umax[abs(v)]) {
-          const int val = __ldg(c + (long long)v * sp);
-          m10 += u * val;
-          m01 += v * val;
-        }
-      }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      m10 += __shfl_xor_sync(ORBX_FULL, m10, o);
-      m01 += __shfl_xor_sync(ORBX_FULL, m01, o);
-    }
-  }
-  const float angle = fast_atan2_deg((float)m01, (float)m10);
-  // rBRIEF
-  const float factorPI = (float)(3.1415926535897932384626433832795 / 180.0);
-  const float ang = __fmul_rn(angle, factorPI);
-  const float ca = (float)cos((double)ang), sa = (float)sin((double)ang);
-  const uint8_t* bl = b.blur + (long long)f * b.blurFrameStride + L.blurOff + (long long)kp.y * L.blurPitch + kp.x;
-  const int bp = L.blurPitch;
-  const int4* pat4 = reinterpret_cast<const int4*>(b.pattern) + lane * 2;
-  const int4 pa = __ldg(pat4), pb = __ldg(pat4 + 1);
-  const int pw[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};
-  int val = 0;
-#pragma unroll
-  for (int j = 0; j < 8; j++) {
-    const float x0 = (float)(int8_t)(pw[j] & 0xff), y0 = (float)(int8_t)((pw[j] >> 8) & 0xff);
-    const float x1 = (float)(int8_t)((pw[j] >> 16) & 0xff), y1 = (float)(int8_t)((pw[j] >> 24) & 0xff);
-    const int rr0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sa), __fmul_rn(y0, ca)));
-    const int cc0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sa)));
-    const int rr1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sa), __fmul_rn(y1, ca)));
-    const int cc1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sa)));
-    const int t0 = __ldg(bl + rr0 * bp + cc0), t1 = __ldg(bl + rr1 * bp + cc1);
-    val |= (t0 < t1) << j;
-  }
-  b.desc[((long long)f * g.kpStride + dest) * 32 + lane] = (uint8_t)val;
-  if (lane == 0) {
-    orbx_keypoint o;
-    o.x = (level == 0) ? (float)kp.x : __fmul_rn((float)kp.x, L.scale);
-    o.y = (level == 0) ? (float)kp.y : __fmul_rn((float)kp.y, L.scale);
-    o.size = L.kpSize;
-    o.angle = angle;
-    o.response = (float)kp.resp;
-    o.octave = level;
-    o.class_id = -1;
-    b.kps[(long long)f * g.kpStride + dest] = o;
-  }
 }
 
 }  // namespace orbx

@@ -13,7 +13,11 @@ namespace orbx {
 struct FrustumOut { uint8_t inView; float projX, projY, projXR, depth, viewCos; int level; };
 
 __device__ __forceinline__ FrustumOut frustum_point(const orbx_frustum& C, float p0, float p1, float p2, float n0, float n1, float n2,
-                                                    float maxDist, float minDist) {
+                                                    float maxDistance, float minDistance) {
+  // maxDistance / minDistance are MapPoint::mfMaxDistance / mfMinDistance as stored.  The range gate uses
+  // GetMaxDistanceInvariance() = 1.2f * mfMaxDistance and GetMinDistanceInvariance() = 0.8f * mfMinDistance
+  // (MapPoint.cc:555-565, Frame.cc:609-615); PredictScale divides the RAW mfMaxDistance (MapPoint.cc:587-602).
+  const float maxDist = __fmul_rn(1.2f, maxDistance), minDist = __fmul_rn(0.8f, minDistance);
   FrustumOut o;
   o.inView = 0; o.projX = -1.f; o.projY = -1.f; o.projXR = 0.f; o.depth = 0.f; o.viewCos = 0.f; o.level = -1;
   float Pc[3];
@@ -51,7 +55,7 @@ __device__ __forceinline__ FrustumOut frustum_point(const orbx_frustum& C, float
   const double dot = (double)o0 * n0 + (double)o1 * n1 + (double)o2 * n2;
   const float viewCos = (float)(dot / (double)dist);
   if (viewCos < C.viewing_cos_limit) return o;
-  const float ratio = __fdiv_rn(maxDist, dist);
+  const float ratio = __fdiv_rn(maxDistance, dist);
   const float lg = (float)log((double)ratio);
   int nScale = (int)ceilf(__fdiv_rn(lg, C.log_scale_factor));
   if (nScale < 0) nScale = 0;

@@ -13,9 +13,6 @@ constexpr int kMinBorder = 16;    // EDGE_THRESHOLD-3, src/ORBextractor.cc:771
 constexpr int kHalfPatch = 15;    // HALF_PATCH_SIZE
 constexpr int kPatch = 31;        // PATCH_SIZE
 
-// FAST tile: 62x30 NMS outputs per CTA, S (corner score) on 64x32, pixel window 70x38 (see fast_nms.cuh)
-constexpr int kTileW = 62, kTileH = 30;
-
 struct LevelGeom {
   int w, h, pitch;            // un-blurred level (pitch: bytes per row inside the pyramid slab; level 0 uses the input pitch)
   int pyrOff;                 // byte offset of the level inside a frame's pyramid slab (levels >= 1)

@@ -8,9 +8,9 @@
 // Distances are 8 x (xor + popc) on 32-bit words, candidates of one query are spread over the lanes of a warp and reduced
 // with shuffles on packed (distance, traversal order, index) keys so that "first minimum wins" ties resolve exactly as the
 // reference's sequential loops do.  The searches whose result depends on earlier queries (keypoints
-// claimed by earlier map points) are split in two: a fully parallel candidate/distance pass, then one warp per frame
-// that replays the reference's order over the precomputed lists (k_resolve_mappoints / _window / _init, k_bow_resolve) or --
-// the default -- a parallel fixed-point iteration that reaches the same result (k_resolve_par, k_bow_resolve_par).
+// claimed by earlier map points) are split in two: a fully parallel candidate/distance pass, then a parallel fixed-point
+// iteration over the claims that reaches the sequential result (k_resolve_par, k_bow_resolve_par); SearchForInitialization,
+// whose claims are not monotone (matches can be stolen back), replays the reference's order with one warp (k_resolve_init).
 #pragma once
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
@@ -283,49 +283,7 @@ struct ResolveArgs {        // one per frame
   int checkOrientation;
 };
 
-// SearchByProjection(Frame&, vector<MapPoint*>&, ...), ORBmatcher.cc:44-142: one warp per frame replays the map points in order.
-__global__ void __launch_bounds__(32) k_resolve_mappoints(const GridFrame* frames, const QuerySet* sets, const ResolveArgs* args) {
-  __shared__ uint8_t blocked[kMaxKpSmem];
-  const GridFrame F = frames[blockIdx.x];
-  const QuerySet Q = sets[blockIdx.x];
-  const ResolveArgs A = args[blockIdx.x];
-  const int lane = threadIdx.x;
-  for (int k = lane; k < F.n; k += 32) {
-    const int s = A.kpMp[k];
-    blocked[k] = (s == -2) || (s >= 0 && (A.observed ? A.observed[s] != 0 : true));
-  }
-  __syncwarp();
-  int nmatches = 0;
-  for (int i = 0; i < Q.nq; i++) {
-    const int c = Q.qCnt[i];
-    if (c == 0) continue;
-    const unsigned long long* e = Q.entries + Q.qOff[i];
-    unsigned long long k1 = kKeyNone, k2 = kKeyNone;
-    for (int j = lane; j < c; j += 32) {
-      const unsigned long long k = e[j];
-      if (!blocked[key_idx(k)]) top2_insert(k, k1, k2);
-    }
-    top2_warp(k1, k2);
-    if (k1 == kKeyNone) continue;
-    const int bestDist = key_dist(k1), bestLevel = key_oct(k1), bestIdx = key_idx(k1);
-    const int bestDist2 = (k2 == kKeyNone) ? 256 : key_dist(k2), bestLevel2 = (k2 == kKeyNone) ? -1 : key_oct(k2);
-    if (bestDist <= 100) {  // TH_HIGH
-      const float lim = __fmul_rn(A.nnratio, (float)bestDist2);
-      if (bestLevel == bestLevel2 && (float)bestDist > lim) continue;
-      if (bestLevel != bestLevel2 || (float)bestDist <= lim) {
-        if (lane == 0) {
-          A.kpMp[bestIdx] = i;
-          blocked[bestIdx] = A.observed ? (A.observed[i] != 0) : 1;
-        }
-        nmatches++;
-        __syncwarp();
-      }
-    }
-  }
-  if (lane == 0) *A.nmatches = nmatches;
-}
-
-// The same search as a parallel fixed point (default path).  The reference's loop is sequential only through the claims: map
+// SearchByProjection(Frame&, vector<MapPoint*>&, ...), ORBmatcher.cc:44-142, as a parallel fixed point.  The reference's loop is sequential only through the claims: map
 // point i cannot take a keypoint that an earlier map point j < i with observations already took.  Let choice[i] be the keypoint
 // map point i ends up with; choice[i] is a function of {choice[j] : j < i} alone, so the sequential result is the unique fixed
 // point of  choice <- F(choice), and iterating F from "no claims" reaches it after at most (longest dependency chain) + 1
@@ -335,7 +293,7 @@ __global__ void __launch_bounds__(32) k_resolve_mappoints(const GridFrame* frame
 // kpMp[k] = the largest index that chose k (later map points overwrite earlier ones without observations, ORBmatcher.cc:89-91).
 constexpr int kParCluster = 8, kParThreads = 512;
 // mode 0: SearchByProjection(Frame&, vector<MapPoint*>&) (best / second with the level rule, TH_HIGH, ratio)
-// mode 1: the best-1 window searches (k_resolve_window's rule: distTh, anyMpBlocks, rotation histogram afterwards)
+// mode 1: the best-1 window searches (best-1 rule: distTh, anyMpBlocks, rotation histogram afterwards)
 __global__ void __cluster_dims__(kParCluster, 1, 1) __launch_bounds__(kParThreads)
 k_resolve_par(const GridFrame* frames, const QuerySet* sets, const ResolveArgs* args, int mode) {
   namespace cg = cooperative_groups;
@@ -440,66 +398,6 @@ k_resolve_par(const GridFrame* frames, const QuerySet* sets, const ResolveArgs* 
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
   if (lane == 0 && mine) atomicAdd(A.nmatches, mine);
-}
-
-// SearchByProjection(Frame&, const Frame&, ...) / (Frame&, KeyFrame*, ...): best-1 window search with the rotation histogram.
-__global__ void __launch_bounds__(32) k_resolve_window(const GridFrame* frames, const QuerySet* sets, const ResolveArgs* args) {
-  __shared__ uint8_t blocked[kMaxKpSmem];
-  __shared__ int hist[30];
-  const GridFrame F = frames[blockIdx.x];
-  const QuerySet Q = sets[blockIdx.x];
-  const ResolveArgs A = args[blockIdx.x];
-  const int lane = threadIdx.x;
-  for (int k = lane; k < F.n; k += 32) {
-    const int s = A.kpMp[k];
-    blocked[k] = A.anyMpBlocks ? (s != -1) : ((s == -2) || (s >= 0 && (A.observed ? A.observed[s] != 0 : true)));
-  }
-  if (lane < 30) hist[lane] = 0;
-  __syncwarp();
-  int nmatches = 0;
-  for (int i = 0; i < Q.nq; i++) {
-    const int c = Q.qCnt[i];
-    if (lane == 0) A.assigned[i] = -1;
-    if (c == 0) continue;
-    const unsigned long long* e = Q.entries + Q.qOff[i];
-    unsigned long long k1 = kKeyNone;
-    for (int j = lane; j < c; j += 32) {
-      const unsigned long long k = e[j];
-      if (!blocked[key_idx(k)]) k1 = min(k1, k);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) k1 = min(k1, __shfl_xor_sync(0xffffffffu, k1, o));
-    if (k1 == kKeyNone) continue;
-    const int bestDist = key_dist(k1), bestIdx = key_idx(k1);
-    if (bestDist <= A.distTh) {
-      if (lane == 0) {
-        A.kpMp[bestIdx] = i;
-        blocked[bestIdx] = A.anyMpBlocks ? 1 : (A.observed ? (A.observed[i] != 0) : 1);
-        int bin = 0;
-        if (A.checkOrientation) { bin = rot_bin(A.angle[i], F.kps[bestIdx].angle); hist[bin]++; }
-        A.assigned[i] = bestIdx | (bin << 24);
-      }
-      nmatches++;
-      __syncwarp();
-    }
-  }
-  __syncwarp();
-  if (A.checkOrientation) {
-    int i1, i2, i3;
-    three_maxima(hist, 30, i1, i2, i3);
-    int removed = 0;
-    for (int i = lane; i < Q.nq; i += 32) {
-      const int a = ((volatile int*)A.assigned)[i];
-      if (a >= 0) {
-        const int bin = a >> 24;
-        if (bin != i1 && bin != i2 && bin != i3) { A.kpMp[a & 0xffffff] = -1; removed++; }
-      }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) removed += __shfl_xor_sync(0xffffffffu, removed, o);
-    nmatches -= removed;
-  }
-  if (lane == 0) *A.nmatches = nmatches;
 }
 
 struct InitArgs {  // SearchForInitialization state, one per frame pair
@@ -658,54 +556,12 @@ struct StereoOut {   // [nframes][kpStride]
   float* uRight; float* depth; int* bestDist; int* bestIdx; int* sad;
 };
 
-// Hamming stage of Frame::ComputeStereoMatches (Frame.cc:911-984): one warp per left keypoint scans every right keypoint of
-// the pair; "iR is listed in row vL" (the reference's vRowIndices table) is evaluated as floor(yR - r) <= (int)vL <= ceil(yR + r).
-__global__ void __launch_bounds__(256) k_stereo_hamming(const __grid_constant__ Geom g, const __grid_constant__ Batch bL,
-                                                        const __grid_constant__ Batch bR, const __grid_constant__ ScaleTab tab,
-                                                        float maxD, StereoOut out) {
-  const int f = blockIdx.y, lane = threadIdx.x & 31;
-  const int iL = blockIdx.x * 8 + (threadIdx.x >> 5);
-  const int nL = bL.counts[f], nR = bR.counts[f];
-  if (iL >= nL) return;
-  const long long o = (long long)f * g.kpStride;
-  const orbx_keypoint kl = bL.kps[o + iL];
-  const int levelL = kl.octave;
-  const float vL = kl.y, uL = kl.x;
-  const int row = (int)vL;
-  const float minU = __fsub_rn(uL, maxD), maxU = uL;
-  uint32_t key = 100u << 16;  // TH_HIGH: only dist < 100 replaces it
-  if (!(maxU < 0)) {
-    uint32_t dl[8];
-    load_desc(bL.desc + (o + iL) * 32, dl);
-    for (int iR = lane; iR < nR; iR += 32) {
-      const orbx_keypoint kr = bR.kps[o + iR];
-      const float r = __fmul_rn(2.0f, tab.scale[kr.octave]);
-      const int maxr = (int)ceilf(__fadd_rn(kr.y, r)), minr = (int)floorf(__fsub_rn(kr.y, r));
-      if (row < minr || row > maxr) continue;
-      if (kr.octave < levelL - 1 || kr.octave > levelL + 1) continue;
-      if (kr.x >= minU && kr.x <= maxU) {
-        uint32_t dr[8];
-        load_desc(bR.desc + (o + iR) * 32, dr);
-        key = min(key, ((uint32_t)hamming8(dl, dr) << 16) | (uint32_t)iR);
-      }
-    }
-  }
-#pragma unroll
-  for (int s = 16; s > 0; s >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, s));
-  if (lane == 0) {
-    const int d = key >> 16;
-    out.bestDist[o + iL] = d;
-    out.bestIdx[o + iL] = d < 100 ? (int)(key & 0xffffu) : -1;
-    out.uRight[o + iL] = -1.0f; out.depth[o + iL] = -1.0f; out.sad[o + iL] = -1;
-  }
-}
-
 // ---- row table (Frame.cc:911-928) -------------------------------------------------------------------------------------------
 // The reference lists every right keypoint iR in the rows floor(y - r) .. ceil(y + r), r = 2 * scale[octave], and a left
 // keypoint only looks at the list of its own row.  k_stereo_rowtable builds that table per frame in CSR form (one CTA per
 // frame: shared-memory histogram over the image rows, exclusive scan, fill); an item carries everything the gates need
 // (index, octave, x) so k_stereo_hamming2 touches a right keypoint's record only for its 32-byte descriptor.  ~27 items per
-// row instead of a scan over all ~1200 right keypoints per left keypoint (k_stereo_hamming, kept for A/B: ORBX_STEREO_V1=1).
+// row instead of a scan over all ~1200 right keypoints per left keypoint.
 struct RowTable {
   int* rowStart;   // [nframes][rows + 1]
   uint2* items;    // [nframes][itemCap]   x = iR | octave << 16, y = float bits of kp.x
@@ -1001,35 +857,8 @@ __global__ void __launch_bounds__(256) k_bow_distances(const __grid_constant__ B
   }
 }
 
-// replay of the reference's order (node by node, then the node's list) with claiming of side-2 features: one warp
-__global__ void __launch_bounds__(32) k_bow_resolve(const __grid_constant__ BowArgs A) {
-  __shared__ uint8_t claimed[kMaxKpSmem];
-  const int lane = threadIdx.x;
-  for (int k = lane; k < A.s2.n; k += 32) claimed[k] = 0;
-  for (int k = lane; k < A.s1.n; k += 32) A.matches12[k] = -1;
-  __syncwarp();
-  for (int w = 0; w < A.nwork; w++) {
-    const BowWork W = A.work[w];
-    const int idx1 = (int)A.s1.indices[W.p1];
-    if ((unsigned)idx1 >= (unsigned)A.s1.n || (A.s1.elig && !A.s1.elig[idx1])) continue;
-    unsigned long long k1 = kKeyNone, k2 = kKeyNone;
-    const int c = W.b1 - W.b0;
-    for (int j = lane; j < c; j += 32) {
-      const unsigned long long k = A.entries[W.off + j];
-      if (k != kKeyNone && !claimed[(int)(k & 0xfffffu)]) top2_insert(k, k1, k2);
-    }
-    top2_warp(k1, k2);
-    if (k1 == kKeyNone) continue;
-    const int bestDist1 = (int)(k1 >> 40), bestIdx2 = (int)(k1 & 0xfffffu);
-    const int bestDist2 = (k2 == kKeyNone) ? 256 : (int)(k2 >> 40);
-    if (bestDist1 <= A.maxDist && (float)bestDist1 < __fmul_rn(A.nnratio, (float)bestDist2)) {
-      if (lane == 0) { A.matches12[idx1] = bestIdx2; claimed[bestIdx2] = 1; }
-      __syncwarp();
-    }
-  }
-}
-
-// The same replay as a parallel fixed point (see k_resolve_par): a side-2 feature claimed by work item w blocks every later
+// Replay of the reference's order (node by node, then the node's list) with claiming of side-2 features, as a parallel fixed
+// point (see k_resolve_par): a side-2 feature claimed by work item w blocks every later
 // work item; choice[w] depends only on the choices of earlier work items, so iterating from "nothing claimed" converges to
 // the sequential result.  Cluster of 8 CTAs per problem, warp = work item.
 __global__ void __cluster_dims__(kParCluster, 1, 1) __launch_bounds__(kParThreads) k_bow_resolve_par(const __grid_constant__ BowArgs A) {

@@ -13,7 +13,6 @@
 #include <vector>
 
 #include "extract_kernels.cuh"
-#include "fast_nms.cuh"
 #include "fast_nms3.cuh"
 #include "pyr_resize.cuh"
 #include "blur7.cuh"
@@ -52,11 +51,9 @@ static void free_geom(orbx_extractor* h) {
                     s.kps, s.desc, s.counts, s.mono};
     for (void* q : ptrs) if (q) cudaFree(q);
     if (s.hStatus) cudaFreeHost(s.hStatus);
-    cudaStream_t st = s.stream, sd = s.side;
-    cudaEvent_t ef = s.evFork, ej = s.evJoin;
-    if (sd) cudaStreamSynchronize(sd);
+    cudaStream_t st = s.stream;
     s = Slot();
-    s.stream = st; s.side = sd; s.evFork = ef; s.evJoin = ej;
+    s.stream = st;
   }
   if (h->dRsx) cudaFree(h->dRsx);
   if (h->dRsy) cudaFree(h->dRsy);
@@ -133,11 +130,11 @@ int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
     L.candOff = candOff; candOff += L.candCap;
     // FAST tiles over the region [19, w-19) x [19, h-19)
     const int rw = L.w - 2 * kEdge, rh = L.h - 2 * kEdge;
-    const int ftw = h->fastVer == 3 ? kF3TileW : kTileW, fth = h->fastVer == 3 ? kF3TileH : kTileH;
+    const int ftw = kF3TileW, fth = kF3TileH;
     L.tilesX = (rw > 0 && rh > 0 && L.nCols > 0) ? (rw + ftw - 1) / ftw : 0;
     L.tilesY = (rw > 0 && rh > 0 && L.nCols > 0) ? (rh + fth - 1) / fth : 0;
     L.tileBase = tileBase; tileBase += L.tilesX * L.tilesY;
-    const int btw = h->blurV1 ? kBlurW : kBvW, bth = h->blurV1 ? kBlurH : kBvH;
+    const int btw = kBvW, bth = kBvH;
     L.blurTilesX = (L.w + btw - 1) / btw; L.blurTilesY = (L.h + bth - 1) / bth;
     L.blurTileBase = blurTileBase; blurTileBase += L.blurTilesX * L.blurTilesY;
     // column / row cell info: cell index | first<<14 | last<<15
@@ -299,46 +296,24 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
   mark(1);
   for (int l = 1; l < g.nlevels; l++) {
     const LevelGeom& L = g.lv[l];
-    if (h->resizeVer == 1) {
-      dim3 grid((L.w + 127) / 128, (L.h + 7) / 8, nframes), block(32, 8);
-      k_pyr_resize<<<grid, block, 0, st>>>(gg, b, l);
-    } else if (h->resizeVer == 3 && h->rs3ok) {
+    if (h->rs3ok) {
       dim3 grid((L.w + kRs3TileW - 1) / kRs3TileW, (L.h + kRs3TileH - 1) / kRs3TileH, nframes);
       k_pyr_resize3<<<grid, 256, 0, st>>>(gg, b, l);
-    } else {
+    } else {   // scale factor > 2: a 4-column group spans more than 8 source bytes -> staged-window kernel
       dim3 grid((L.w + kRsTileW - 1) / kRsTileW, (L.h + kRsTileH - 1) / kRsTileH, nframes);
       k_pyr_resize2<<<grid, 256, h->rsSmem, st>>>(gg, b, l);
     }
   }
   mark(2);
-  // The blur needs only the pyramid: it runs on the slot's side stream beside FAST -> quadtree -> assemble, whose last two
-  // kernels are short dependent chains (one CTA per level / frame) that leave most SMs idle.  Profiling mode keeps one stream.
-  const bool fork = !prof && !h->noFork;
-  cudaStream_t sb = fork ? s.side : st;
-  if (fork) { CK(cudaEventRecord(s.evFork, st)); CK(cudaStreamWaitEvent(sb, s.evFork, 0)); }
-  if (fork) {
-    if (h->blurV1) k_blur7<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, sb>>>(gg, b);
-    else k_blur7v<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, sb>>>(gg, b);
-    CK(cudaEventRecord(s.evJoin, sb));
-  }
-  if (g.nTilesTotal > 0) {
-    if (h->fastVer == 1) k_fast_nms_v1<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
-    else if (h->fastVer == 2) k_fast_nms<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
-    else k_fast_nms3<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
-  }
+  if (g.nTilesTotal > 0) k_fast_nms3<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
   mark(3);
   k_quadtree<<<dim3(g.nlevels, nframes), 256, h->qtSmem, st>>>(gg, b, s.nCand);
   mark(4);
-  if (!fork) {
-    if (h->blurV1) k_blur7<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, st>>>(gg, b);
-    else k_blur7v<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, st>>>(gg, b);
-  }
+  k_blur7v<<<dim3(g.nBlurTilesTotal, nframes), 256, 0, st>>>(gg, b);
   mark(5);
   k_assemble<<<nframes, 256, 0, st>>>(gg, b);
-  if (fork) CK(cudaStreamWaitEvent(st, s.evJoin, 0));
   mark(6);
-  if (h->orientV1) k_orient_desc<<<dim3((g.kpSlab + 7) / 8, nframes), 256, 0, st>>>(gg, b);
-  else k_orient_desc2<<<dim3((g.kpSlab + 7) / 8, nframes), 256, 0, st>>>(gg, b);
+  k_orient_desc2<<<dim3((g.kpSlab + 7) / 8, nframes), 256, 0, st>>>(gg, b);
   mark(7);
   s.evValid = prof;
   CK(cudaGetLastError());
@@ -378,12 +353,6 @@ int orbx_create(const orbx_params* p, orbx_extractor** out) {
   CK(cudaSetDevice(p->device));
   orbx_extractor* h = new orbx_extractor();
   h->p = *p;
-  // A/B switches for the earlier versions of kernels
-  { const char* e = getenv("ORBX_FAST_V1"); if (e && e[0] == '1') h->fastVer = 1; }
-  { const char* e = getenv("ORBX_FAST_V2"); if (e && e[0] == '1') h->fastVer = 2; }
-  { const char* e = getenv("ORBX_RESIZE_V1"); if (e && e[0] == '1') h->resizeVer = 1; }
-  { const char* e = getenv("ORBX_RESIZE_V2"); if (e && e[0] == '1') h->resizeVer = 2; }
-  { const char* e = getenv("ORBX_BLUR_V1"); h->blurV1 = e && e[0] == '1'; }
   const int nl = p->nlevels;
   // ORBextractor::ORBextractor, src/ORBextractor.cc:408-468
   h->scaleFactorD = (double)p->scale_factor;  // `double scaleFactor` member initialised from the float argument
@@ -415,18 +384,14 @@ int orbx_create(const orbx_params* p, orbx_extractor** out) {
     }
   }
   for (Slot& s : h->slot)
-    if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess || cudaStreamCreateWithFlags(&s.side, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&s.evFork, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&s.evJoin, cudaEventDisableTiming) != cudaSuccess) {
+    if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) {
       delete h; set_error("stream creation failed"); return ORBX_ERR_CUDA;
     }
-  // measured: beside a concurrently running second extractor the fork gains nothing on the device path and costs 9 % end to end
-  { const char* e = getenv("ORBX_FORK"); h->noFork = !(e && e[0] == '1'); }
   float patF[1024];   // pair 8 * lane + j  ->  record j * 32 + lane (k_orient_desc2 reads [j][lane])
   for (int pr = 0; pr < 256; pr++)
     for (int k = 0; k < 4; k++) patF[((pr & 7) * 32 + (pr >> 3)) * 4 + k] = (float)kPatternHost[pr * 4 + k];
   for (int v = 0; v <= kHalfPatch; v++)
     if (h->umax[v] != od_umax(v)) { delete h; set_error("umax table differs from the compiled-in one"); return ORBX_ERR_UNSUPPORTED; }
-  { const char* e = getenv("ORBX_ORIENT_V1"); h->orientV1 = e && e[0] == '1'; }
   if (cudaMalloc(&h->dPattern, 1024 + sizeof(patF)) != cudaSuccess ||
       cudaMemcpy(h->dPattern, kPatternHost, 1024, cudaMemcpyHostToDevice) != cudaSuccess ||
       cudaMemcpy(h->dPattern + 1024, patF, sizeof(patF), cudaMemcpyHostToDevice) != cudaSuccess) {
@@ -441,9 +406,6 @@ void orbx_destroy(orbx_extractor* h) {
   free_geom(h);
   for (Slot& s : h->slot) {
     if (s.stream) cudaStreamDestroy(s.stream);
-    if (s.side) cudaStreamDestroy(s.side);
-    if (s.evFork) cudaEventDestroy(s.evFork);
-    if (s.evJoin) cudaEventDestroy(s.evJoin);
   }
   if (h->dPattern) cudaFree(h->dPattern);
   delete h;

@@ -26,8 +26,6 @@ std::recursive_mutex& setup_mutex();
 
 struct Slot {
   cudaStream_t stream = nullptr;
-  cudaStream_t side = nullptr;            // blur branch of a batch (runs beside FAST -> quadtree -> assemble)
-  cudaEvent_t evFork = nullptr, evJoin = nullptr;
   uint8_t* in = nullptr;  // staged level-0 frames for the host path [max_batch][h][inPitch]
   uint8_t* pyr = nullptr;
   uint8_t* blur = nullptr;
@@ -65,12 +63,8 @@ struct orbx_extractor {
   Slot slot[2];
   int lastSlot = 0;
   bool profile = false;
-  bool blurV1 = false, orientV1 = false;
-  int resizeVer = 3;     // ORBX_RESIZE_V1=1 / ORBX_RESIZE_V2=1: earlier resize kernels (A/B only)
-  bool rs3ok = true;     // k_pyr_resize3 applies to this geometry (scale factor <= 2)
-  bool noFork = true;    // ORBX_FORK=1: run the blur on the slot's side stream beside FAST -> quadtree -> assemble (A/B only)
+  bool rs3ok = true;     // k_pyr_resize3 applies to this geometry (scale factor <= 2); otherwise k_pyr_resize2
   size_t rsSmem = 0;
-  int fastVer = 3;      // ORBX_FAST_V1=1 / ORBX_FAST_V2=1: run an earlier FAST kernel instead of k_fast_nms3 (A/B only)
 };
 
 

@@ -29,7 +29,6 @@ struct orbx_matcher {
   // row table of the right keypoints (Frame.cc:911-928), two halves like the results
   int* sRowStart = nullptr; uint2* sRowItems = nullptr;
   size_t sRowStartCap = 0, sRowItemsCap = 0;
-  bool stereoV1 = false;   // ORBX_STEREO_V1=1: brute-force scan instead of the row table (A/B only)
   // CUDA graph of one chunk of orbx_stereo_frames_host (extract L + extract R + stereo kernels), one per slot: the call is
   // bound by the host's launch rate otherwise (~30 launches with 2 KB of parameters each per chunk)
   struct ChunkGraph {
@@ -42,8 +41,6 @@ struct orbx_matcher {
     }
   } chunkGraph[2][4];    // [slot][entry]: a call's chunks come in up to three sizes (ramped first, full, tail)
   int chunkGraphNext[2] = {0, 0};
-  bool noGraph = false;    // ORBX_NO_GRAPH=1
-  bool resolveSeq = false; // ORBX_RESOLVE_SEQ=1: one-warp sequential replay instead of the parallel fixed point (A/B only)
   // orbx_stereo_frames_host pipeline: one upload stream feeds both slots in issue order; per slot: images uploaded (left, right),
   // right branch joined, input buffers free again (both extractions done), slot's downloads done
   cudaStream_t upStream = nullptr;
@@ -337,11 +334,9 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
   k_build_grid<<<nj, 256, 0, st>>>(dFrames);
   if (maxQ > 0) k_window_candidates<<<dim3((maxQ + 7) / 8, nj), 256, 0, st>>>(dFrames, dSets, m->dStatus);
   if (kind == RESOLVE_MAPPOINTS) {
-    if (m->resolveSeq) k_resolve_mappoints<<<nj, 32, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs));
-    else k_resolve_par<<<dim3(kParCluster, nj), kParThreads, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs), 0);
+    k_resolve_par<<<dim3(kParCluster, nj), kParThreads, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs), 0);
   } else if (kind == RESOLVE_WINDOW) {
-    if (m->resolveSeq) k_resolve_window<<<nj, 32, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs));
-    else k_resolve_par<<<dim3(kParCluster, nj), kParThreads, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs), 1);
+    k_resolve_par<<<dim3(kParCluster, nj), kParThreads, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs), 1);
   }
   else if (kind == RESOLVE_INIT) k_resolve_init<<<nj, 32, 0, st>>>(dFrames, dSets, at<InitArgs>(m, oArgs));
   else if (kind == RESOLVE_BEST && maxQ > 0) k_resolve_best<<<dim3((maxQ + 7) / 8, nj), 256, 0, st>>>(dSets, at<ResolveArgs>(m, oArgs));
@@ -415,9 +410,6 @@ int orbx_matcher_create(int device, orbx_matcher** out) {
   CK(cudaSetDevice(device));
   orbx_matcher* m = new orbx_matcher();
   m->device = device;
-  { const char* e = getenv("ORBX_STEREO_V1"); m->stereoV1 = e && e[0] == '1'; }
-  { const char* e = getenv("ORBX_NO_GRAPH"); m->noGraph = e && e[0] == '1'; }
-  { const char* e = getenv("ORBX_RESOLVE_SEQ"); m->resolveSeq = e && e[0] == '1'; }
   bool evOk = true;
   for (int i = 0; i < 2; i++)
     for (cudaEvent_t* e : {&m->evUpL[i], &m->evUpR[i], &m->evJoin[i], &m->evInFree[i], &m->evSlotDone[i]})
@@ -685,8 +677,7 @@ int orbx_search_local_points_batch(orbx_matcher* m, orbx_extractor* ex, int nfra
   k_local_point_queries<<<dim3((nq + 255) / 256, nframes), 256, 0, st>>>(A);
   k_build_grid<<<nframes, 256, 0, st>>>(A.frames);
   k_window_candidates<<<dim3((nq + 7) / 8, nframes), 256, 0, st>>>(A.frames, A.sets, m->dStatus);
-  if (m->resolveSeq) k_resolve_mappoints<<<nframes, 32, 0, st>>>(A.frames, A.sets, at<ResolveArgs>(m, oArgs));
-  else k_resolve_par<<<dim3(kParCluster, nframes), kParThreads, 0, st>>>(A.frames, A.sets, at<ResolveArgs>(m, oArgs), 0);
+  k_resolve_par<<<dim3(kParCluster, nframes), kParThreads, 0, st>>>(A.frames, A.sets, at<ResolveArgs>(m, oArgs), 0);
   CK(cudaGetLastError());
   int status = 0;
   CK(cudaMemcpyAsync(&status, m->dStatus, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -779,7 +770,6 @@ int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches)
   if ((P.n1 > 0 && (!P.kps1 || !P.desc1)) || (P.n2 > 0 && (!P.kps2 || !P.desc2))) return ORBX_ERR_ARG;
   if (bow_check(P.fv1, P.n1) != ORBX_OK || bow_check(P.fv2, P.n2) != ORBX_OK) { set_error("bad feature vector (node ids must ascend)"); return ORBX_ERR_ARG; }
   if (P.n1 >= (1 << 20) || P.n2 >= (1 << 20)) { set_error("more than 2^20 features per keyframe is unsupported"); return ORBX_ERR_UNSUPPORTED; }
-  if (!P.triangulate && m->resolveSeq && P.n2 > kMaxKpSmem) { set_error("more than %d features per frame is unsupported by the resolve kernel", kMaxKpSmem); return ORBX_ERR_UNSUPPORTED; }
   *nmatches = 0;
   for (int i = 0; i < P.n1; i++) matches12[i] = -1;
   if (P.n1 == 0 || P.n2 == 0) return ORBX_OK;
@@ -845,8 +835,7 @@ int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches)
     k_bow_triangulate<<<(nw + 7) / 8, 256, 0, st>>>(A);
   } else {
     k_bow_distances<<<(nw + 7) / 8, 256, 0, st>>>(A);
-    if (m->resolveSeq) k_bow_resolve<<<1, 32, 0, st>>>(A);
-    else k_bow_resolve_par<<<kParCluster, kParThreads, 0, st>>>(A);
+    k_bow_resolve_par<<<kParCluster, kParThreads, 0, st>>>(A);
   }
   k_bow_rotfilter<<<1, 256, 0, st>>>(A);
   CK(cudaGetLastError());
@@ -1073,7 +1062,7 @@ static int stereo_prepare(orbx_matcher* m, orbx_extractor* exL, orbx_extractor* 
     m->sCap = 2 * half;
     m->sEpoch++;
   }
-  if (!m->stereoV1) {
+  {
     // a right keypoint is listed in at most 2 * ceil(r) + 2 rows, r = 2 * scale[octave]
     const int maxRows = 2 * (int)std::ceil(2.0f * exL->scale[g.nlevels - 1]) + 2;
     const size_t itemCap = (size_t)g.kpStride * maxRows, needStart = 2 * (size_t)nfCap * (g.height + 1), needItems = 2 * (size_t)nfCap * itemCap;
@@ -1116,9 +1105,7 @@ static int stereo_launch(orbx_matcher* m, orbx_extractor* exL, orbx_extractor* e
   const size_t o = (size_t)si * half;
   StereoOut out{m->sURight + o, m->sDepth + o, m->sBestDist + o, m->sBestIdx + o, m->sSad + o};
   dim3 grid((g.kpStride + 7) / 8, nf);
-  if (m->stereoV1) {
-    k_stereo_hamming<<<grid, 256, 0, st>>>(gg, sL.last, sR.last, tab, maxD, out);
-  } else {
+  {
     const int maxRows = 2 * (int)std::ceil(2.0f * exL->scale[g.nlevels - 1]) + 2;
     const size_t itemCap = (size_t)g.kpStride * maxRows;
     RowTable rt{m->sRowStart + (size_t)si * nfCap * (g.height + 1), m->sRowItems + (size_t)si * nfCap * itemCap, g.height, (int)itemCap};
@@ -1157,7 +1144,7 @@ int orbx_stereo_frames_host(orbx_matcher* m, orbx_extractor* exL, orbx_extractor
   const int ncopy = std::min(capPerFrame, g.kpStride);
   rc = stereo_prepare(m, exL, exR);
   if (rc != ORBX_OK) return rc;
-  const bool useGraph = !m->noGraph && !exL->profile && !exR->profile;
+  const bool useGraph = !exL->profile && !exR->profile;
   // ORBX_TRACE=1 (development): device timeline of the call, one line per chunk on stderr
   static const bool trace = [] { const char* e = getenv("ORBX_TRACE"); return e && e[0] == '1'; }();
   std::vector<cudaEvent_t> tev;

@@ -225,9 +225,7 @@ int orbx_remap(orbx_preproc* p, const orbx_remap_table* t, const uint8_t* src, i
   A.sfs = src_frame_stride; A.dfs = dst_frame_stride;
   A.vecDst = aligned(S.dDst, dst_stride, dst_frame_stride, 4);
   A.vecSrc = aligned(S.dSrc, src_stride, src_frame_stride, 4);
-  static const bool tiled = getenv("ORBX_REMAP_TILE") != nullptr;   // A/B only: shared-memory staged source tiles (measured slower)
-  if (tiled) k_remap_tile<<<dim3((t->dw + ORBX_RT_W - 1) / ORBX_RT_W, (t->dh + ORBX_RT_H - 1) / ORBX_RT_H, nframes), 256, 0, S.st>>>(A);
-  else k_remap<<<dim3((t->dw + 1023) / 1024, t->dh, nframes), 256, 0, S.st>>>(A);
+  k_remap<<<dim3((t->dw + 1023) / 1024, t->dh, nframes), 256, 0, S.st>>>(A);
   return S.finish();
 }
 
@@ -262,10 +260,8 @@ int orbx_clahe(orbx_preproc* p, const uint8_t* src, int nframes, int width, int 
     CK(cudaFuncSetAttribute(k_clahe_apply, cudaFuncAttributeMaxDynamicSharedMemorySize, 512 * 256));
     p->claheAttr = true;
   }
-  static const bool lutV1 = getenv("ORBX_CLAHE_V1") != nullptr;   // A/B only: one CTA per tile
   const int ntiles = tiles_x * tiles_y;
-  if (lutV1) k_clahe_lut<<<dim3(ntiles, nframes), 256, 0, S.st>>>(A);
-  else k_clahe_lut_w<<<(ntiles * nframes + 7) / 8, 256, 0, S.st>>>(A, ntiles, ntiles * nframes);
+  k_clahe_lut_w<<<(ntiles * nframes + 7) / 8, 256, 0, S.st>>>(A, ntiles, ntiles * nframes);
   const int wq = (width + 3) / 4, threads = wq >= 256 ? 256 : ((wq + 31) & ~31);
   k_clahe_apply<<<dim3((height + ORBX_CLAHE_ROWS - 1) / ORBX_CLAHE_ROWS, nframes), threads, nlut, S.st>>>(A);
   return S.finish();

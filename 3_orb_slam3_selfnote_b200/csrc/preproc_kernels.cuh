@@ -92,7 +92,8 @@ struct RemapArgs {
 // HBM (DRAM 7 %).  Variants measured on the B200 per 256 frames of 752x480 and dropped: 4 rows per thread with branch-free
 // clamped addresses 0.32 ms, 2 rows + warp-uniform interior fast path 0.27 ms, 1 row + fast path 0.25 ms, this one 0.19 ms:
 // deeper per-thread load queues only lengthen the LSU queue.  The step that would change the bound is a shared-memory
-// staged source tile per CTA -- built as k_remap_tile below and measured: slower still (0.31 ms).
+// staged source tile per CTA -- built in round 1 (k_remap_tile, see git history / profiles/README.md) and measured: slower still
+// (0.31 ms: table load -> box reduction -> staging -> taps are three dependent round trips separated by CTA barriers).
 __device__ __forceinline__ unsigned remap_px(const uint8_t* __restrict__ S, uint32_t t, const RemapArgs& A) {
   const int sx = (int)(t & 0xffffu) - 32, sy = (int)(t >> 16) - 32;
   const int ix = sx >> 5, iy = sy >> 5, fx = sx & 31, fy = sy & 31;
@@ -126,85 +127,6 @@ __global__ void __launch_bounds__(256) k_remap(const __grid_constant__ RemapArgs
     const int n = min(4, A.dw - x4);
     for (int i = 0; i < n; ++i) d[i] = (uint8_t)remap_px(S, tt[i], A);
   }
-}
-
-// Tiled variant: CTA = 128 x 8 destination pixels.  The table words give the bounding box of the tile's source footprint
-// (for a rectification map about 140 x 12 pixels); the box is staged once into shared memory with coalesced 32-bit loads --
-// zeros where it leaves the image, which is exactly BORDER_CONSTANT 0 -- and the 16 taps of a thread become shared-memory
-// byte loads.  Tiles whose box does not fit (arbitrary maps) fall back to the global gathers of remap_px.
-// MEASURED SLOWER than k_remap (0.31 vs 0.19 ms per 256 frames of 752x480): table load -> box reduction -> staging -> taps are
-// three dependent memory round trips separated by CTA barriers, against two for the direct gathers whose lines mostly hit
-// in L1 anyway (86 % hit rate).  Kept behind ORBX_REMAP_TILE=1 for A/B runs; parity-tested in both modes.
-#define ORBX_RT_W 128
-#define ORBX_RT_H 8
-#define ORBX_RT_SMEM 24576
-__global__ void __launch_bounds__(256) k_remap_tile(const __grid_constant__ RemapArgs A) {
-  __shared__ __align__(16) uint32_t sm32[ORBX_RT_SMEM / 4];
-  __shared__ int box[4];  // min x, max x, min y, max y of the top-left taps
-  const int lane = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int x4 = blockIdx.x * ORBX_RT_W + lane * 4, y = blockIdx.y * ORBX_RT_H + ty;
-  const bool live = x4 < A.dw && y < A.dh;
-  const int nlive = live ? min(4, A.dw - x4) : 0;
-  if (threadIdx.x == 0) { box[0] = INT_MAX; box[1] = INT_MIN; box[2] = INT_MAX; box[3] = INT_MIN; }
-  uint32_t t[4] = {0, 0, 0, 0};
-  if (live) {
-    const uint4 q = __ldg(reinterpret_cast<const uint4*>(A.table + (long long)y * A.tpitch + x4));
-    t[0] = q.x; t[1] = q.y; t[2] = q.z; t[3] = q.w;
-  }
-  int lox = INT_MAX, hix = INT_MIN, loy = INT_MAX, hiy = INT_MIN;
-#pragma unroll
-  for (int i = 0; i < 4; ++i)
-    if (i < nlive) {
-      const int ix = (int)((t[i] & 0xffffu) >> 5) - 1, iy = (int)(t[i] >> 21) - 1;
-      lox = min(lox, ix); hix = max(hix, ix); loy = min(loy, iy); hiy = max(hiy, iy);
-    }
-  lox = __reduce_min_sync(0xffffffffu, lox); hix = __reduce_max_sync(0xffffffffu, hix);
-  loy = __reduce_min_sync(0xffffffffu, loy); hiy = __reduce_max_sync(0xffffffffu, hiy);
-  __syncthreads();
-  if (lane == 0 && hix >= lox) { atomicMin(&box[0], lox); atomicMax(&box[1], hix); atomicMin(&box[2], loy); atomicMax(&box[3], hiy); }
-  __syncthreads();
-  const int bx0 = box[0] & ~3, by0 = box[2];
-  const int bw = (box[1] + 1 - bx0 + 4) & ~3, bh = box[3] + 1 - by0 + 1;  // bytes per staged row (multiple of 4), rows
-  const uint8_t* __restrict__ S = A.src + (long long)blockIdx.z * A.sfs;
-  uint8_t* d = A.dst + (long long)blockIdx.z * A.dfs + (long long)y * A.dstride + x4;
-  unsigned o[4];
-  if ((long long)bw * bh <= ORBX_RT_SMEM) {   // uniform over the CTA
-    const int bw4 = bw >> 2;
-    for (int idx = threadIdx.x; idx < bw4 * bh; idx += 256) {
-      const int r = idx / bw4, sx = bx0 + (idx - r * bw4) * 4, sy = by0 + r;
-      unsigned w = 0;
-      if ((unsigned)sy < (unsigned)A.sh) {
-        const uint8_t* row = S + (long long)sy * A.sstride;
-        if (A.vecSrc && sx >= 0 && sx + 4 <= A.sw) w = __ldg(reinterpret_cast<const unsigned*>(row + sx));
-        else {
-#pragma unroll
-          for (int b = 0; b < 4; ++b)
-            if ((unsigned)(sx + b) < (unsigned)A.sw) w |= (unsigned)__ldg(row + sx + b) << (8 * b);
-        }
-      }
-      sm32[idx] = w;
-    }
-    __syncthreads();
-    const uint8_t* sm = reinterpret_cast<const uint8_t*>(sm32);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      o[i] = 0;
-      if (i < nlive) {
-        const int ix = (int)((t[i] & 0xffffu) >> 5) - 1, iy = (int)(t[i] >> 21) - 1;
-        const uint8_t* a = sm + (iy - by0) * bw + (ix - bx0);
-        const unsigned fx = t[i] & 31u, fy = (t[i] >> 16) & 31u;
-        const unsigned top = a[0] * (32u - fx) + a[1] * fx, bot = a[bw] * (32u - fx) + a[bw + 1] * fx;
-        o[i] = (top * (32u - fy) + bot * fy + 512u) >> 10;
-      }
-    }
-  } else {
-#pragma unroll
-    for (int i = 0; i < 4; ++i) o[i] = i < nlive ? remap_px(S, t[i], A) : 0u;
-  }
-  if (!live) return;
-  if (A.vecDst && nlive == 4) *reinterpret_cast<unsigned*>(d) = o[0] | (o[1] << 8) | (o[2] << 16) | (o[3] << 24);
-  else
-    for (int i = 0; i < nlive; ++i) d[i] = (uint8_t)o[i];
 }
 
 // ---- CLAHE ---------------------------------------------------------------------------------------------------------------
@@ -305,73 +227,6 @@ __global__ void __launch_bounds__(256) k_clahe_lut_w(const __grid_constant__ Cla
     if (j < 4) w0 |= (unsigned)v << (8 * j); else w1 |= (unsigned)v << (8 * (j - 4));
   }
   *reinterpret_cast<uint2*>(A.lut + ((long long)frame * ntiles + tile) * 256 + lane * 8) = make_uint2(w0, w1);
-}
-
-// CTA = one tile of one frame: per-warp shared histograms, clip + redistribute, 256-wide inclusive scan, LUT.
-__global__ void __launch_bounds__(256) k_clahe_lut(const __grid_constant__ ClaheArgs A) {
-  // one sub-histogram per warp.  (32 sub-histograms -- one per (warp, lane & 3), so that the correlated pixels of adjacent lanes
-  // never share a counter -- removed the atomic serialisation but cost more in clearing and folding 32 KB than it saved: a
-  // tile is only ~22 pixels per thread.  Measured 0.27 -> 0.30 ms per 256 frames, reverted.)
-  __shared__ int wh[8][256];
-  __shared__ int wsum[8];
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int tile = blockIdx.x, tx = tile % A.tilesX, ty = tile / A.tilesX;
-  const uint8_t* S = A.src + (long long)blockIdx.y * A.sfs;
-  for (int i = tid; i < 8 * 256; i += 256) (&wh[0][0])[i] = 0;
-  __syncthreads();
-  const bool inside = (tx + 1) * A.tw <= A.w && (ty + 1) * A.th <= A.h;
-  if (inside && A.vec) {
-    // warp = tile row, lane = aligned 32-bit word of it (bytes outside [x0, x0 + tw) are skipped)
-    const int x0 = tx * A.tw, a0 = x0 & ~3, nw = (x0 + A.tw - a0 + 3) >> 2;
-    for (int r = warp; r < A.th; r += 8) {
-      const uint8_t* row = S + (long long)(ty * A.th + r) * A.sstride + a0;
-      for (int wi = lane; wi < nw; wi += 32) {
-        const int xb = a0 + wi * 4;
-        unsigned q;
-        if (xb + 4 <= A.w) q = __ldg(reinterpret_cast<const unsigned*>(row + wi * 4));
-        else { q = 0; for (int b = 0; b < A.w - xb; ++b) q |= (unsigned)__ldg(row + wi * 4 + b) << (8 * b); }
-#pragma unroll
-        for (int b = 0; b < 4; ++b)
-          if (xb + b >= x0 && xb + b < x0 + A.tw) atomicAdd(&wh[warp][(q >> (8 * b)) & 255u], 1);
-      }
-    }
-  } else {
-    const int total = A.tw * A.th;
-    for (int i = tid; i < total; i += 256) {
-      int yy = ty * A.th + i / A.tw, xx = tx * A.tw + i % A.tw;
-      if (!inside) { yy = reflect101_dev(yy, A.h); xx = reflect101_dev(xx, A.w); }
-      atomicAdd(&wh[warp][__ldg(S + (long long)yy * A.sstride + xx)], 1);
-    }
-  }
-  __syncthreads();
-  int hv = 0;
-#pragma unroll
-  for (int k = 0; k < 8; ++k) hv += wh[k][tid];
-  if (A.clip > 0) {
-    int ex = hv > A.clip ? hv - A.clip : 0;
-    hv = min(hv, A.clip);
-    for (int o = 16; o; o >>= 1) ex += __shfl_xor_sync(0xffffffffu, ex, o);
-    if (lane == 0) wsum[warp] = ex;
-    __syncthreads();
-    int clipped = 0;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) clipped += wsum[k];
-    __syncthreads();
-    const int batch = clipped >> 8;
-    int residual = clipped - (batch << 8);
-    hv += batch;
-    if (residual != 0) {
-      const int step = max(256 / residual, 1);
-      if (tid % step == 0 && tid / step < residual) hv++;
-    }
-  }
-  int s = hv;
-  for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, s, o); if (lane >= o) s += t; }
-  if (lane == 31) wsum[warp] = s;
-  __syncthreads();
-  for (int k = 0; k < warp; ++k) s += wsum[k];
-  int v = __float2int_rn(__fmul_rn((float)s, A.lutScale));
-  A.lut[((long long)blockIdx.y * A.tilesX * A.tilesY + tile) * 256 + tid] = (uint8_t)min(max(v, 0), 255);
 }
 
 struct ClaheCol { float xa, xa1; int i1, i2; };  // per-column constants of the blend (clahe.cpp's ind1_p / ind2_p / xa_p / xa1_p)

@@ -76,18 +76,20 @@ class FramePreproc {
   }
 
   // Frame::isInFrustum over a batch of map points (structure-of-arrays of the MapPoint getters the reference calls:
-  // GetWorldPos, GetNormal, GetMaxDistanceInvariance, GetMinDistanceInvariance).  Fills the MapPoint tracking fields.
+  // GetWorldPos, GetNormal) plus the RAW MapPoint::mfMaxDistance / mfMinDistance members -- not the *Invariance getters: the
+  // gate multiplies by 1.2f / 0.8f itself and PredictScale divides the raw mfMaxDistance (MapPoint.cc:555-602); the members
+  // are protected in the reference, INTEGRATION.md shows the two-line accessor.  Fills the MapPoint tracking fields.
   struct FrustumResult {
     std::vector<uint8_t> mbTrackInView;
     std::vector<float> mTrackProjX, mTrackProjY, mTrackProjXR, mTrackDepth, mTrackViewCos;
     std::vector<int> mnTrackScaleLevel;
   };
   int isInFrustum(const orbx_frustum& frame, const std::vector<float>& worldPos3, const std::vector<float>& normal3,
-                  const std::vector<float>& maxDist, const std::vector<float>& minDist, FrustumResult& r) {
-    const int n = (int)maxDist.size();
+                  const std::vector<float>& maxDistance, const std::vector<float>& minDistance, FrustumResult& r) {
+    const int n = (int)maxDistance.size();
     r.mbTrackInView.resize(n); r.mTrackProjX.resize(n); r.mTrackProjY.resize(n); r.mTrackProjXR.resize(n); r.mTrackDepth.resize(n);
     r.mTrackViewCos.resize(n); r.mnTrackScaleLevel.resize(n);
-    ck(orbx_is_in_frustum(h_, &frame, n, worldPos3.data(), normal3.data(), maxDist.data(), minDist.data(), r.mbTrackInView.data(),
+    ck(orbx_is_in_frustum(h_, &frame, n, worldPos3.data(), normal3.data(), maxDistance.data(), minDistance.data(), r.mbTrackInView.data(),
                           r.mTrackProjX.data(), r.mTrackProjY.data(), r.mTrackProjXR.data(), r.mTrackDepth.data(), r.mnTrackScaleLevel.data(),
                           r.mTrackViewCos.data(), ORBX_MEM_HOST, nullptr),
        "orbx_is_in_frustum");

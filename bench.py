@@ -285,7 +285,7 @@ def extra_configs(orbx, synth, torch, stream, local, steps):
     P = (np.stack([np.sin(th) * mx / rr, np.sin(th) * my / rr, np.cos(th)], 1) * zs[:, None]).astype(np.float32)   # frame 0's map points, camera at the origin
     dist = np.linalg.norm(P, axis=1)
     scale = ex.GetScaleFactors()
-    maxd = (dist * scale[np.clip(lv[0], 0, 7)] * 1.1).astype(np.float32)
+    maxd = (dist * scale[np.clip(lv[0], 0, 7)] * 0.95).astype(np.float32)
     mind = (maxd / scale[7] * 0.8).astype(np.float32)
     nrm = (P / dist[:, None]).astype(np.float32)
     lm = orbx.LocalMap(mt, P, nrm, maxd, mind, md[0])

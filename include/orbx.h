@@ -338,7 +338,10 @@ int orbx_undistort_keypoints(orbx_preproc* p, const orbx_keypoint* kps, int n, f
  * MapPoint fields the reference fills -- mbTrackInView, mTrackProjX, mTrackProjY, mTrackProjXR, mTrackDepth,
  * mnTrackScaleLevel, mTrackViewCos -- and are exactly the inputs of orbx_search_by_projection_mappoints
  * (Tracking::SearchLocalPoints, src/Tracking.cc:3490-3520).  Points that fail get in_view 0, level -1 and proj_x / proj_y -1
- * unless they passed the image-bounds test (:577-578, :604-605). */
+ * unless they passed the image-bounds test (:577-578, :604-605).
+ * max_distance / min_distance are MapPoint::mfMaxDistance / mfMinDistance AS STORED: the range gate applies the invariance
+ * factors itself (dist > 1.2f * mfMaxDistance or dist < 0.8f * mfMinDistance rejects, MapPoint.cc:555-565, Frame.cc:609-615),
+ * PredictScale divides the raw mfMaxDistance (MapPoint.cc:587-602).  Do NOT pass Get{Max,Min}DistanceInvariance(). */
 typedef struct orbx_frustum {
   float Rcw[9], tcw[3], Ow[3];          /* mRcw (row-major), mtcw, mOw */
   float fx, fy, cx, cy;                 /* Pinhole parameters */
@@ -351,21 +354,21 @@ typedef struct orbx_frustum {
 } orbx_frustum;
 #define ORBX_CAMERA_PINHOLE 0
 #define ORBX_CAMERA_KB8 1
-int orbx_is_in_frustum(orbx_preproc* p, const orbx_frustum* cam, int n, const float* world_pos, const float* normal, const float* max_dist,
-                       const float* min_dist, uint8_t* in_view, float* proj_x, float* proj_y, float* proj_xr, float* depth, int* level,
+int orbx_is_in_frustum(orbx_preproc* p, const orbx_frustum* cam, int n, const float* world_pos, const float* normal, const float* max_distance,
+                       const float* min_distance, uint8_t* in_view, float* proj_x, float* proj_y, float* proj_xr, float* depth, int* level,
                        float* view_cos, int mem, void* stream);
 
 /* Tracking::SearchLocalPoints (src/Tracking.cc:3441-3525) over a batch of frames without host staging: the local map is
- * uploaded once (orbx_local_map_create: MapPoint::GetWorldPos / GetNormal / GetMaxDistanceInvariance /
- * GetMinDistanceInvariance / GetDescriptor, optional Observations() > 0 flags), then for the nframes frames whose keypoints
+ * uploaded once (orbx_local_map_create: MapPoint::GetWorldPos / GetNormal / mfMaxDistance / mfMinDistance (raw, as for
+ * orbx_is_in_frustum) / GetDescriptor, optional Observations() > 0 flags), then for the nframes frames whose keypoints
  * `ex` holds on the device from its last orbx_extract_batch_device, frame f with pose / intrinsics frames[f]:
  * isInFrustum(pMP, viewing_cos_limit) for every map point (Frame.cc:572-642) and SearchByProjection(F, vpMapPoints, th)
  * (ORBmatcher.cc:44-142) with mvpMapPoints initially empty.  kp_mp[f * cap_per_frame + k] = index of the map point matched
  * to keypoint k of frame f, or -1.  All kernels run on `stream` (pass the extractor's stream; NULL = the matcher's own
  * stream after a device synchronisation); the call returns after the results have reached the host arrays. */
 typedef struct orbx_local_map orbx_local_map;
-int orbx_local_map_create(orbx_matcher* m, int nmp, const float* world_pos, const float* normal, const float* max_dist,
-                          const float* min_dist, const uint8_t* desc, const uint8_t* observed, orbx_local_map** out);
+int orbx_local_map_create(orbx_matcher* m, int nmp, const float* world_pos, const float* normal, const float* max_distance,
+                          const float* min_distance, const uint8_t* desc, const uint8_t* observed, orbx_local_map** out);
 void orbx_local_map_destroy(orbx_local_map* map);
 int orbx_search_local_points_batch(orbx_matcher* m, orbx_extractor* ex, int nframes, const orbx_frustum* frames, const orbx_local_map* map,
                                    float th, float nnratio, int* kp_mp, int cap_per_frame, int* nmatches, void* stream);

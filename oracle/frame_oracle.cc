@@ -51,8 +51,8 @@ struct FrustumCam {
 // Frame::isInFrustum, Nleft == -1 branch (Frame.cc:574-642).  Outputs per point: inView, mTrackProjX/Y/XR, mTrackDepth,
 // mnTrackScaleLevel, mTrackViewCos.  Points that fail keep the values the reference leaves behind: projX/projY = -1 unless the
 // image-bounds test passed (Frame.cc:577-578, 604-605); the other fields are written as 0 / -1 (the reference leaves them stale).
-void oro_is_in_frustum(const FrustumCam* C, int n, const float* P /*n x 3*/, const float* normal /*n x 3*/, const float* maxDist,
-                       const float* minDist, uint8_t* inView, float* projX, float* projY, float* projXR, float* depth, int* level,
+void oro_is_in_frustum(const FrustumCam* C, int n, const float* P /*n x 3*/, const float* normal /*n x 3*/, const float* maxDist /* mfMaxDistance */,
+                       const float* minDist /* mfMinDistance */, uint8_t* inView, float* projX, float* projY, float* projXR, float* depth, int* level,
                        float* viewCosOut) {
   for (int i = 0; i < n; ++i) {
     inView[i] = 0; projX[i] = -1; projY[i] = -1; projXR[i] = 0; depth[i] = 0; level[i] = -1; viewCosOut[i] = 0;
@@ -84,12 +84,13 @@ void oro_is_in_frustum(const FrustumCam* C, int n, const float* P /*n x 3*/, con
     projX[i] = ux; projY[i] = uy;
     const float PO[3] = {p[0] - C->Ow[0], p[1] - C->Ow[1], p[2] - C->Ow[2]};
     const float dist = (float)std::sqrt((double)PO[0] * PO[0] + (double)PO[1] * PO[1] + (double)PO[2] * PO[2]);
-    if (dist < minDist[i] || dist > maxDist[i]) continue;
+    // GetMinDistanceInvariance() = 0.8f * mfMinDistance, GetMaxDistanceInvariance() = 1.2f * mfMaxDistance (MapPoint.cc:555-565)
+    if (dist < 0.8f * minDist[i] || dist > 1.2f * maxDist[i]) continue;
     const float* Pn = normal + 3 * i;
     const double dot = (double)PO[0] * Pn[0] + (double)PO[1] * Pn[1] + (double)PO[2] * Pn[2];
     const float viewCos = (float)(dot / dist);
     if (viewCos < C->viewingCosLimit) continue;
-    const float ratio = maxDist[i] / dist;
+    const float ratio = maxDist[i] / dist;   // PredictScale: the RAW mfMaxDistance (MapPoint.cc:587-602)
     const float lg = C->logMode == 0 ? logf(ratio) : (float)std::log((double)ratio);
     int nScale = (int)std::ceil(lg / C->logScaleFactor);
     if (nScale < 0) nScale = 0;

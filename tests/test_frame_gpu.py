@@ -93,7 +93,7 @@ def test_frustum_feeds_search_by_projection(pre, orbx, oracle, synth):
     P = ((Pc - t) @ R).astype(np.float32)
     Ow = -(R.T @ t).astype(np.float32)
     dist = np.linalg.norm(P - Ow, axis=1)
-    maxd = (dist * scale[k["octave"]] * 1.1).astype(np.float32)   # so that PredictScale lands near the keypoint's octave
+    maxd = (dist * scale[k["octave"]] * 0.95).astype(np.float32)   # raw mfMaxDistance: PredictScale = ceil(octave - 0.28) = the octave
     mind = (maxd / scale[7] * 0.8).astype(np.float32)
     nrm = ((P - Ow) / dist[:, None]).astype(np.float32)
     cam = oracle.FrustumCam()
@@ -135,7 +135,7 @@ def _local_map_case(orbx, synth, pre, nframes, nmp, seed):
     Ow0 = -(R0.T @ t0).astype(np.float32)
     scale = gx.GetScaleFactors()
     d0 = np.linalg.norm(P - Ow0, axis=1)
-    maxd = (d0 * scale[k0["octave"]] * 1.1).astype(np.float32)
+    maxd = (d0 * scale[k0["octave"]] * 0.95).astype(np.float32)
     npad = nmp - c0
     Ppad = (((np.stack([rng.uniform(-3, 3, npad), rng.uniform(-3, 3, npad), rng.uniform(-1, 8, npad)], 1)) - t0) @ R0).astype(np.float32)
     P = np.concatenate([P, Ppad]); maxd = np.concatenate([maxd, rng.uniform(2, 20, npad).astype(np.float32)])

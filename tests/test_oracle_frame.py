@@ -45,12 +45,12 @@ def _frustum_numpy(cam, P, normal, maxd, mind, log_mode):
                 out.append((0, -1, -1, 0, 0, -1, 0)); continue
         PO = (p - Ow).astype(f32)
         dist = f32(np.sqrt(np.sum(PO.astype(np.float64) ** 2)))
-        if dist < mn or dist > mx:
+        if dist < f32(f32(0.8) * mn) or dist > f32(f32(1.2) * mx):   # Get{Min,Max}DistanceInvariance, MapPoint.cc:555-565
             out.append((0, ux, uy, 0, 0, -1, 0)); continue
         vc = f32(np.sum(PO.astype(np.float64) * nrm.astype(np.float64)) / np.float64(dist))
         if vc < f32(cam.viewingCosLimit):
             out.append((0, ux, uy, 0, 0, -1, 0)); continue
-        ratio = f32(mx / dist)
+        ratio = f32(mx / dist)   # PredictScale divides the raw mfMaxDistance, MapPoint.cc:587-602
         lg = f32(np.log(np.float64(ratio))) if log_mode else np.log(ratio)
         lvl = int(np.ceil(f32(lg / f32(cam.logScaleFactor))))
         lvl = 0 if lvl < 0 else min(lvl, cam.nScaleLevels - 1)
@@ -75,3 +75,24 @@ def test_is_in_frustum_matches_numpy_restatement(oracle, kb):
     assert np.array_equal(o2["in_view"], o["in_view"]) and (o2["level"] != o["level"]).sum() == 0
     # ... and, for the fisheye model, move a projection by at most a few float ulps (libm atan2f against the rounded double atan2)
     assert np.abs(o2["proj_x"] - o["proj_x"]).max() <= 2e-4 and np.abs(o2["proj_y"] - o["proj_y"]).max() <= 2e-4
+
+
+def test_predicted_level_uses_raw_max_distance(oracle):
+    """MapPoint::PredictScale (MapPoint.cc:587-602): level = ceil(log(mfMaxDistance / dist) / log(scaleFactor)) with the RAW
+    mfMaxDistance, while the range gate of Frame::isInFrustum (Frame.cc:609-615) uses 1.2f * mfMaxDistance / 0.8f * mfMinDistance.
+    Expected levels are built directly from that definition: a point seen at dist = mfMaxDistance / 1.2^(k - 0.5) is at level k."""
+    cam = fc.frustum_case(oracle, 1, seed=1)[0]
+    cam.Rcw[:] = [1, 0, 0, 0, 1, 0, 0, 0, 1]; cam.tcw[:] = [0, 0, 0]; cam.Ow[:] = [0, 0, 0]
+    dist = np.float32(4.0)
+    P = np.tile(np.array([[0, 0, dist]], np.float32), (12, 1))
+    normal = np.tile(np.array([[0, 0, 1]], np.float32), (12, 1))
+    k = np.arange(12)
+    maxd = (dist * np.float64(1.2) ** (k - 0.5)).astype(np.float32)       # k = 0: dist just above mfMaxDistance but inside 1.2 x
+    mind = np.full(12, 0.1, np.float32)
+    o = oracle.is_in_frustum(cam, P, normal, maxd, mind)
+    assert o["in_view"].all()                                            # dist <= 1.2 * mfMaxDistance even for k = 0
+    assert o["level"].tolist() == [0, 1, 2, 3, 4, 5, 6, 7, 7, 7, 7, 7]     # clamped to nScaleLevels - 1 = 7
+    # the gates: beyond 1.2 x mfMaxDistance / below 0.8 x mfMinDistance the point is rejected
+    o = oracle.is_in_frustum(cam, P[:4], normal[:4], np.array([dist / 1.19, dist / 1.21, 50, 50], np.float32),
+                             np.array([0.1, 0.1, dist / 0.81, dist / 0.79], np.float32))
+    assert o["in_view"].tolist() == [1, 0, 1, 0]

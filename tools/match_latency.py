@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """Host-call latency of the single-frame searches (the reference's per-frame use): SearchByProjection(F, 5000 map points),
-SearchByProjectionWindow (frame-to-frame), SearchByBoW.   python tools/match_latency.py   (ORBX_RESOLVE_SEQ=1 for the sequential kernels)"""
+SearchByProjectionWindow (frame-to-frame), SearchByBoW.   python tools/match_latency.py"""
 import importlib
 import os
 import sys
