@@ -2,41 +2,43 @@
 
 Every rank owns a contiguous shard of keyframes (`kf_per_rank` keyframes x `desc_per_kf` descriptors of 32 bytes, global row
 index = rank * rows_per_rank + local row).  For each of its own descriptors a rank wants the two nearest descriptors among
-ALL descriptors of all OTHER keyframes.  Shards travel by NCCL all-gather in `nchunks` pieces; while piece c+1 is in flight
-on NCCL's stream, the rank folds piece c (world x chunk_rows rows) into the running (best, second) keys of its own queries
-with `k_knn2` (orbx_knn2_chunk_device).  No reduction is needed afterwards: each rank owns its queries.
+ALL descriptors of all OTHER keyframes.
 
-torch.distributed is plumbing (the collective and the buffers); the distance work is the CUDA kernel behind the C-ABI.
-`fold` can be injected so that the chunk schedule / index bookkeeping is testable with the gloo backend on CPU (tests only);
-the default fold requires CUDA and raises otherwise -- there is no CPU fallback.
+The product path is the C-ABI call `orbx_allpairs_knn2` (csrc/orbx_allpairs.cu): raw ncclAllGather of the shards in `nchunks`
+pieces on a side stream while the 2-NN tile kernel folds the previous piece; CUDA tensors take that path and nothing else (no
+CPU fallback).  The same chunk schedule is written out below in torch.distributed terms with an injectable `fold`, so that
+the index bookkeeping (global rows, own-keyframe exclusion, ties across chunks and ranks) is testable with the gloo backend on
+CPU (tests/test_allpairs.py); that form never runs on a GPU.
 """
 import numpy as np
 
 KEY_NONE = np.uint64(0xFFFFFFFFFFFFFFFF)
 
 
-def _gpu_fold(matcher):
-    import torch
-
-    def fold(q, train, train_base, exclude, key0, key1, init):
-        if not q.is_cuda:
-            raise RuntimeError("allpairs: the default fold needs CUDA tensors (no CPU fallback)")
-        matcher.knn2_chunk_device(q.data_ptr(), q.shape[0], train.data_ptr(), train.shape[0], int(train_base), exclude.data_ptr(),
-                                  key0.data_ptr(), key1.data_ptr(), init, torch.cuda.current_stream().cuda_stream)
-    return fold
-
-
-def allpairs_knn2(desc, desc_per_kf, matcher=None, group=None, nchunks=4, fold=None):
+def allpairs_knn2(desc, desc_per_kf, matcher=None, group=None, nchunks=4, fold=None, comm=None, return_stats=False):
     """desc: torch.uint8 [rows_per_rank, 32] (this rank's shard; same shape on every rank).
-    Returns (idx[rows,2] int64 global row indices, dist[rows,2] int32), -1 where fewer than two neighbours exist."""
+    Returns (idx[rows,2] int64 global row indices, dist[rows,2] int32), -1 where fewer than two neighbours exist.
+    CUDA tensors: orbx_allpairs_knn2 through `matcher`; `comm` = a matcher.NcclComm to reuse (else one is made from `group`)."""
     import torch
+    import torch.distributed as dist
     if desc.is_cuda:
-        # run on an explicit stream: the C-ABI maps a NULL (legacy default) stream to the matcher's own stream, which would
-        # not be ordered with torch's work
-        cs = torch.cuda.Stream(device=desc.device)
-        cs.wait_stream(torch.cuda.current_stream(desc.device))
-        with torch.cuda.stream(cs):
-            return _allpairs_impl(desc, desc_per_kf, matcher, group, nchunks, fold)
+        if matcher is None:
+            raise RuntimeError("allpairs: CUDA tensors need an ORBmatcher (the sweep runs in liborbx.so)")
+        assert desc.dtype == torch.uint8 and desc.dim() == 2 and desc.shape[1] == 32 and desc.is_contiguous()
+        world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        own = None
+        if world > 1 and comm is None:
+            from .matcher import nccl_comm_from_torch
+            comm = own = nccl_comm_from_torch(desc.device.index, group)
+        torch.cuda.synchronize(desc.device)      # the library runs on its own streams
+        try:
+            idx, dst, stats = matcher.allpairs_knn2(desc.data_ptr(), desc.shape[0], desc_per_kf, nchunks, comm if world > 1 else None)
+        finally:
+            if own is not None:
+                own.close()
+        return (idx, dst, stats) if return_stats else (idx, dst)
+    if fold is None:
+        raise RuntimeError("allpairs: host tensors are accepted only with an injected fold (tests); there is no CPU fallback")
     return _allpairs_impl(desc, desc_per_kf, matcher, group, nchunks, fold)
 
 
@@ -47,7 +49,6 @@ def _allpairs_impl(desc, desc_per_kf, matcher, group, nchunks, fold):
     assert rows % desc_per_kf == 0 and desc.dtype == torch.uint8 and desc.shape[1] == 32
     world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
     rank = dist.get_rank(group) if world > 1 else 0
-    fold = fold or _gpu_fold(matcher)
     dev = desc.device
     # own-keyframe exclusion range per query, in global rows
     kf = torch.arange(rows, device=dev, dtype=torch.int64) // desc_per_kf

@@ -68,7 +68,9 @@ struct orbx_extractor {
 };
 
 
+struct orbx_matcher;
 namespace orbx {
+int matcher_device(const orbx_matcher* m);   // defined in orbx_match.cu
 // enqueue one extractor batch (defined in orbx_extract.cu)
 int extractor_run_batch(orbx_extractor* h, int slot, const uint8_t* dIn, int nframes, int pitch, long long frameStride, int lap0, int lap1,
                         cudaStream_t st);

@@ -54,6 +54,8 @@ struct orbx_matcher {
   static constexpr int kStatChunks = 256;
 };
 
+int orbx::matcher_device(const orbx_matcher* m) { return m->device; }
+
 namespace {
 
 struct StageCopy { unsigned long long stageOff, arenaOff; unsigned bytes, pad; };   // bytes: multiple of 16

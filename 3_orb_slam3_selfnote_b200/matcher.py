@@ -23,6 +23,43 @@ from . import KP_DTYPE, _check, _p, lib
 TH_HIGH, TH_LOW, HISTO_LENGTH = 100, 50, 30  # src/ORBmatcher.cc:36-38
 
 
+class AllpairsStats(C.Structure):   # orbx_allpairs_stats
+    _fields_ = [("world", C.c_int), ("rank", C.c_int), ("nchunks", C.c_int), ("pairs", C.c_double), ("total_ms", C.c_double),
+                ("fold_ms", C.c_double), ("gather_ms", C.c_double), ("gather_bytes", C.c_double), ("overlap_frac", C.c_double)]
+
+
+class NcclComm:
+    """An ncclComm_t created through the library's run-time NCCL binding (orbx_nccl_unique_id / orbx_nccl_comm_init).
+    `exchange(id_bytes_or_None) -> id_bytes` ships rank 0's 128-byte id to every rank (any channel: torch.distributed, MPI, a file)."""
+
+    def __init__(self, rank, world, device, exchange):
+        uid = (C.c_uint8 * 128)()
+        if rank == 0:
+            _check(lib().orbx_nccl_unique_id(uid))
+        got = exchange(bytes(uid) if rank == 0 else None)
+        uid = (C.c_uint8 * 128).from_buffer_copy(got)
+        self._c = C.c_void_p()
+        _check(lib().orbx_nccl_comm_init(uid, world, rank, device, C.byref(self._c)))
+        self.rank, self.world = rank, world
+
+    def close(self):
+        if self._c:
+            lib().orbx_nccl_comm_destroy(self._c)
+            self._c = C.c_void_p()
+
+
+def nccl_comm_from_torch(device, group=None):
+    """NcclComm over the ranks of an initialised torch.distributed group (torch only carries the 128-byte id)."""
+    import torch.distributed as dist
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+
+    def exchange(b):
+        box = [b]
+        dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        return box[0]
+    return NcclComm(rank, world, device, exchange)
+
+
 class _FrameViewC(C.Structure):
     _fields_ = [("n", C.c_int), ("keypoints", C.c_void_p), ("descriptors", C.c_void_p), ("u_right", C.c_void_p),
                 ("scale_factors", C.c_void_p), ("nlevels", C.c_int), ("min_x", C.c_float), ("min_y", C.c_float),
@@ -222,6 +259,16 @@ class ORBmatcher:
         _check(lib().orbx_knn2_chunk_device(self._m, C.c_void_p(d_q), nq, C.c_void_p(d_t), nt, C.c_longlong(train_base),
                                             C.c_void_p(d_exclude), C.c_void_p(d_key0), C.c_void_p(d_key1), int(init),
                                             C.c_void_p(stream)))
+
+    def allpairs_knn2(self, d_desc, rows, desc_per_kf, nchunks=4, comm=None):
+        """orbx_allpairs_knn2: the all-pairs keyframe sweep over this rank's `rows` device-resident descriptors (and, through the
+        NcclComm `comm`, every other rank's).  -> (idx[rows,2] int64 global rows, dist[rows,2] int32, stats dict)"""
+        idx = np.empty((rows, 2), np.int64)
+        dist = np.empty((rows, 2), np.int32)
+        st = AllpairsStats()
+        _check(lib().orbx_allpairs_knn2(self._m, C.c_void_p(comm._c.value if comm is not None else None), C.c_void_p(d_desc),
+                                        C.c_longlong(rows), int(desc_per_kf), int(nchunks), _p(idx), _p(dist), C.byref(st)))
+        return idx, dist, {f: getattr(st, f) for f, _ in AllpairsStats._fields_}
 
     def stereo_match_batch(self, exL, exR, mb, mbf, stream=0):
         """Frame::ComputeStereoMatches for every pair of the two extractors' last batches (asynchronous)"""

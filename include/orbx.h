@@ -270,6 +270,32 @@ int orbx_knn2(orbx_matcher* m, const uint8_t* query, int nq, const uint8_t* trai
 int orbx_knn2_chunk_device(orbx_matcher* m, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt, long long train_base,
                            const int* d_exclude, unsigned long long* d_key0, unsigned long long* d_key1, int init, void* stream);
 
+/* All-pairs keyframe-descriptor 2-NN sweep (BASELINE.json config 5; SURVEY.md 8-e, the one step of the path with an exchange).
+ * Every rank holds `rows` descriptors in HBM (rows / desc_per_kf keyframes; the same `rows` on every rank; global row =
+ * rank * rows + local row) and gets, for each of them, the two nearest descriptors among all descriptors of all OTHER
+ * keyframes of all ranks: idx[2*i+k] = global row, dist[2*i+k] = Hamming distance (k = 0 best, 1 second; -1 where fewer
+ * exist), ties to the lower global row exactly like cv::BFMatcher.  `nccl_comm` is an ncclComm_t spanning the ranks (NULL =
+ * single rank); the shards travel by ncclAllGather in `nchunks` pieces on a side stream while the previous piece is folded
+ * by the 2-NN tile kernel.  idx / dist are HOST arrays of 2 * rows; the call blocks until they are written.
+ * The communicator may come from the caller's own NCCL (same libnccl.so.2 in the process) or from the three helpers below,
+ * which bind NCCL at run time (liborbx.so has no link-time NCCL dependency): rank 0 calls orbx_nccl_unique_id, ships the 128
+ * bytes to the other ranks by any channel, every rank calls orbx_nccl_comm_init. */
+typedef struct orbx_allpairs_stats {
+  int world, rank, nchunks;
+  double pairs;         /* descriptor pairs this rank evaluated */
+  double total_ms;      /* device time of the sweep on this rank (first fold start to last fold end) */
+  double fold_ms;       /* sum over chunks of the 2-NN folds */
+  double gather_ms;     /* sum over chunks of the all-gathers (includes waiting for the slowest rank) */
+  double gather_bytes;  /* bytes this rank received */
+  double overlap_frac;  /* share of the all-gather time hidden behind folds */
+} orbx_allpairs_stats;
+int orbx_nccl_version(void);   /* e.g. 22809; 0 when libnccl.so.2 cannot be loaded */
+int orbx_nccl_unique_id(uint8_t id[128]);
+int orbx_nccl_comm_init(const uint8_t id[128], int nranks, int rank, int device, void** comm);
+int orbx_nccl_comm_destroy(void* comm);
+int orbx_allpairs_knn2(orbx_matcher* m, void* nccl_comm, const uint8_t* d_desc, long long rows, int desc_per_kf, int nchunks,
+                       long long* idx, int* dist, orbx_allpairs_stats* stats);
+
 /* Frame::ComputeStereoMatches, src/Frame.cc:901-1079, for every frame of the last batches of two extractor handles
  * (left / right image of each pair; same geometry and frame count; keypoints, descriptors and un-blurred pyramids are read
  * where they lie in HBM, exactly the members the reference reads at Frame.cc:908,998,1012).  mb / mbf as in Frame.

@@ -5,12 +5,8 @@
 // (DescriptorDistance, ComputeThreeMaxima; oracle/Makefile cuts them out of /root/reference/src/ORBmatcher.cc at
 // build time into oracle/_ref/).  Loaded by oracle/ref.py for tests/ and bench.py's CPU legs only.
 //
-// Node allocator: DistributeOctTree sorts (size, ExtractorNode*) pairs (ORBextractor.cc:680), i.e. ties between nodes
-// holding the same number of points are broken by heap ADDRESS, which under glibc malloc depends on the allocation
-// history of the process.  Every operator new issued while a reference call is running on this thread is
-// served from a monotone bump arena, so "later created = higher address": the declared, reproducible tie rule.
-#include <sys/mman.h>
-
+// Node allocator: every operator new issued while a reference call runs is served from a monotone bump arena (ref_alloc.cc),
+// so the (size, ExtractorNode*) tie of DistributeOctTree's sort is "later created = higher address" (SURVEY F5).
 #include <atomic>
 #include <chrono>
 #include <thread>
@@ -21,69 +17,9 @@
 #include <vector>
 
 #include "ORBextractor.h"
+#include "ref_alloc.h"
 
 namespace cvshim { extern thread_local int g_blur_taps; }
-
-namespace {
-const size_t kArenaBytes = (size_t)1 << 30;  // virtual; pages are committed on first touch only
-const int kMaxArenas = 256;
-struct Arena { char* base; std::atomic<int> busy; };
-Arena g_arenas[kMaxArenas];
-std::atomic<int> g_narenas{0};
-thread_local char* tl_cur = nullptr;
-thread_local char* tl_end = nullptr;
-thread_local bool tl_overflow = false;
-
-int arena_acquire() {
-  int n = g_narenas.load();
-  for (int i = 0; i < n; i++) {
-    int expected = 0;
-    if (g_arenas[i].busy.compare_exchange_strong(expected, 1)) return i;
-  }
-  int i = g_narenas.fetch_add(1);
-  if (i >= kMaxArenas) { g_narenas.fetch_sub(1); return -1; }
-  void* p = mmap(nullptr, kArenaBytes, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_NORESERVE, -1, 0);
-  if (p == MAP_FAILED) return -1;
-  g_arenas[i].base = (char*)p;
-  g_arenas[i].busy.store(1);
-  return i;
-}
-inline bool in_arena(void* p) {
-  int n = g_narenas.load(std::memory_order_relaxed);
-  for (int i = 0; i < n && i < kMaxArenas; i++) {
-    char* b = g_arenas[i].base;
-    if (b && (char*)p >= b && (char*)p < b + kArenaBytes) return true;
-  }
-  return false;
-}
-struct ArenaScope {
-  int id;
-  ArenaScope() : id(arena_acquire()) {
-    if (id >= 0) { tl_cur = g_arenas[id].base; tl_end = tl_cur + kArenaBytes; }
-    tl_overflow = false;
-  }
-  ~ArenaScope() {
-    tl_cur = tl_end = nullptr;
-    if (id >= 0) g_arenas[id].busy.store(0);
-  }
-};
-}  // namespace
-
-void* operator new(size_t n) {
-  if (tl_cur) {
-    size_t a = (n + 15) & ~(size_t)15;
-    if (tl_cur + a <= tl_end) { void* p = tl_cur; tl_cur += a; return p; }
-    tl_overflow = true;  // reported by the caller; the result of this call is not trusted
-  }
-  void* p = malloc(n ? n : 1);
-  if (!p) throw std::bad_alloc();
-  return p;
-}
-void* operator new[](size_t n) { return operator new(n); }
-void operator delete(void* p) noexcept { if (p && !in_arena(p)) free(p); }
-void operator delete[](void* p) noexcept { operator delete(p); }
-void operator delete(void* p, size_t) noexcept { operator delete(p); }
-void operator delete[](void* p, size_t) noexcept { operator delete(p); }
 
 namespace {
 // Read access to the protected tables (mnFeaturesPerLevel, umax) for the constructor parity test.
@@ -121,8 +57,8 @@ int ref_extract(void* h, const uint8_t* img, int w, int hgt, int stride, int lap
   cvshim::g_blur_taps = blur_taps;
   int mono, n;
   {
-    ArenaScope scope;
-    if (scope.id < 0) return -3;
+    refalloc::Scope scope;
+    if (!scope.ok()) return -3;
     {
       std::vector<cv::KeyPoint> kps;
       cv::Mat desc;
@@ -137,7 +73,7 @@ int ref_extract(void* h, const uint8_t* img, int w, int hgt, int stride, int lap
         for (int i = 0; i < n; i++) memcpy(desc_out + (size_t)i * 32, desc.ptr(i), 32);
       }
     }
-    if (tl_overflow) return -3;
+    if (refalloc::overflowed()) return -3;
   }
   if (mono < 0) return -1;
   if (n > cap) return -2;
@@ -195,7 +131,7 @@ double ref_time_extract(int nfeatures, float scaleFactor, int nlevels, int iniTh
       cvshim::g_blur_taps = blur_taps;
       Probe ex(nfeatures, scaleFactor, nlevels, iniTh, minTh);
       for (int f = t; f < nframes; f += nthreads) {
-        ArenaScope scope;
+        refalloc::Scope scope;
         std::vector<cv::KeyPoint> kps;
         cv::Mat desc;
         std::vector<int> lap{lap0, lap1};
