@@ -128,7 +128,103 @@ struct WindowJob {
   int* bestIdx = nullptr; int* bestDist = nullptr;
   // features_in_area
   std::vector<unsigned long long>* entriesOut = nullptr;
+  // projection prologue on the device (k_project_points): the queries are derived from 3-D points and a pose instead of q.x / q.y / ...
+  const orbx_projection* proj = nullptr; const orbx_projection_points* pts = nullptr; const orbx_projection_debug* dbg = nullptr;
 };
+
+// ---- projection prologue of the searches that start from map points and a pose ------------------------------------------------
+// One thread per point, the reference's float / double evaluation order spelled out (no contraction):
+//   x_c = R x_w + t        cv::gemm small-matrix path: ((a0*b0 + a1*b1) + a2*b2) in float, + t as one float add   (ORBmatcher.cc:2072)
+//   depth test / invz      per depth_mode / invz_mode (:2077, :1490-1493, :1850-1852)
+//   project                Pinhole::project / KannalaBrandt8::project (proj_mode 0) or fx * (x * invz) + cx (proj_mode 1, :1853-1858)
+//   bounds                 Frame float bounds (:2084-2087) or KeyFrame::IsInImage (:540, src/KeyFrame.cc:844-847)
+//   dist, range, normal    cv::norm / Mat::dot accumulate in double; 0.8f * mfMinDistance, 1.2f * mfMaxDistance (MapPoint.cc:555-565)
+//   level                  given octave (:2089) or MapPoint::PredictScale (MapPoint.cc:570-602); radius = th * mvScaleFactors[level]
+struct ProjectArgs {
+  orbx_projection P;
+  int n, nlevels;
+  const float* pos; const float* normal; const float* maxD; const float* minD; const int* octave; const uint8_t* validIn;
+  const float* scale;
+  uint8_t* valid; float* x; float* y; float* r; int8_t* minL; int8_t* maxL; float* xr; int* level;
+};
+
+__global__ void __launch_bounds__(256) k_project_points(const __grid_constant__ ProjectArgs A) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= A.n) return;
+  const orbx_projection& P = A.P;
+  A.valid[i] = 0; A.x[i] = -1.f; A.y[i] = -1.f; A.r[i] = 0.f; A.minL[i] = 0; A.maxL[i] = 0; A.level[i] = -1;
+  if (A.xr) A.xr[i] = 0.f;
+  if (A.validIn && !A.validIn[i]) return;
+  const float p0 = A.pos[3 * i], p1 = A.pos[3 * i + 1], p2 = A.pos[3 * i + 2];
+  float c[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k)
+    c[k] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(P.R[3 * k], p0), __fmul_rn(P.R[3 * k + 1], p1)), __fmul_rn(P.R[3 * k + 2], p2)), P.t[k]);
+  if (P.chain) {
+    float d[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      d[k] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(P.R2[3 * k], c[0]), __fmul_rn(P.R2[3 * k + 1], c[1])), __fmul_rn(P.R2[3 * k + 2], c[2])), P.t2[k]);
+    c[0] = d[0]; c[1] = d[1]; c[2] = d[2];
+  }
+  const float z = c[2];
+  const float invz = P.invz_mode == 0 ? (float)(1.0 / (double)z) : __fdiv_rn(1.0f, z);
+  if (P.depth_mode == 0) { if (invz < 0.f) return; }
+  else if (P.depth_mode == 1) { if (z < 0.0f) return; }
+  float u, v;
+  if (P.proj_mode == 1) {
+    u = __fadd_rn(__fmul_rn(P.fx, __fmul_rn(c[0], invz)), P.cx);
+    v = __fadd_rn(__fmul_rn(P.fy, __fmul_rn(c[1], invz)), P.cy);
+  } else if (P.camera_model == ORBX_CAMERA_KB8) {   // KannalaBrandt8.cpp:29-45, same policy as frustum_point (frustum.cuh)
+    const float x2y2 = __fadd_rn(__fmul_rn(c[0], c[0]), __fmul_rn(c[1], c[1]));
+    const float theta = (float)atan2((double)sqrtf(x2y2), (double)z);
+    const float psi = (float)atan2((double)c[1], (double)c[0]);
+    const float t2 = __fmul_rn(theta, theta), t3 = __fmul_rn(theta, t2), t5 = __fmul_rn(t3, t2), t7 = __fmul_rn(t5, t2), t9 = __fmul_rn(t7, t2);
+    const float rr = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(theta, __fmul_rn(P.kb[0], t3)), __fmul_rn(P.kb[1], t5)), __fmul_rn(P.kb[2], t7)), __fmul_rn(P.kb[3], t9));
+    u = (float)__dadd_rn(__dmul_rn((double)__fmul_rn(P.fx, rr), cos((double)psi)), (double)P.cx);
+    v = (float)__dadd_rn(__dmul_rn((double)__fmul_rn(P.fy, rr), sin((double)psi)), (double)P.cy);
+  } else {
+    u = __fadd_rn(__fdiv_rn(__fmul_rn(P.fx, c[0]), z), P.cx);
+    v = __fadd_rn(__fdiv_rn(__fmul_rn(P.fy, c[1]), z), P.cy);
+  }
+  A.x[i] = u; A.y[i] = v;
+  if (P.bounds_mode == 0) { if (u < P.min_x || u > P.max_x || v < P.min_y || v > P.max_y) return; }
+  else if (!(u >= P.min_x && u < P.max_x && v >= P.min_y && v < P.max_y)) return;
+  if (A.xr) A.xr[i] = __fsub_rn(u, __fmul_rn(P.bf, invz));
+  float dist = 0.f;
+  float o0 = 0.f, o1 = 0.f, o2 = 0.f;
+  if (P.range_mode || P.normal_check || P.level_mode == 1) {
+    if (P.dist_mode == 1) { o0 = c[0]; o1 = c[1]; o2 = c[2]; }
+    else { o0 = __fsub_rn(p0, P.Ow[0]); o1 = __fsub_rn(p1, P.Ow[1]); o2 = __fsub_rn(p2, P.Ow[2]); }
+    dist = (float)sqrt((double)o0 * o0 + (double)o1 * o1 + (double)o2 * o2);
+  }
+  if (P.range_mode) {
+    const float maxDistance = __fmul_rn(1.2f, A.maxD[i]), minDistance = __fmul_rn(0.8f, A.minD[i]);
+    if (dist < minDistance || dist > maxDistance) return;
+  }
+  if (P.normal_check) {
+    const double dot = (double)o0 * A.normal[3 * i] + (double)o1 * A.normal[3 * i + 1] + (double)o2 * A.normal[3 * i + 2];
+    if (dot < 0.5 * (double)dist) return;
+  }
+  int lvl;
+  if (P.level_mode == 1) {   // MapPoint::PredictScale
+    const float ratio = __fdiv_rn(A.maxD[i], dist);
+    const float lg = (float)log((double)ratio);
+    lvl = (int)ceilf(__fdiv_rn(lg, P.log_scale_factor));
+    if (lvl < 0) lvl = 0;
+    else if (lvl >= P.n_scale_levels) lvl = P.n_scale_levels - 1;
+  } else lvl = A.octave[i];
+  A.level[i] = lvl;
+  if (lvl < 0 || lvl >= A.nlevels || lvl > 126) return;
+  A.r[i] = __fmul_rn(P.th, A.scale[lvl]);
+  int8_t lo, hi;
+  if (P.window_mode == 1) { lo = (int8_t)lvl; hi = -1; }
+  else if (P.window_mode == 2) { lo = 0; hi = (int8_t)lvl; }
+  else if (P.window_mode == 3) { lo = (int8_t)(lvl - 1); hi = (int8_t)lvl; }
+  else { lo = (int8_t)(lvl - 1); hi = (int8_t)(lvl + 1); }
+  A.minL[i] = lo; A.maxL[i] = hi;
+  A.valid[i] = 1;
+}
 
 int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind kind) {
   const int nj = (int)jobs.size();
@@ -137,7 +233,8 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
   // ---- plan the arena
   ArenaPlan plan;
   struct Off { size_t kps, desc, uRight, cellStart, cellItems, valid, x, y, r, xr, minL, maxL, qdesc, qOff, qCnt, entries, cursor,
-               observed, angle, kpMp, assigned, nmatches, kps1, prevMatched, m12, m21, mdist, bins, sigma, blk0, blk1, chg; };
+               observed, angle, kpMp, assigned, nmatches, kps1, prevMatched, m12, m21, mdist, bins, sigma, blk0, blk1, chg,
+               pPos, pNormal, pMaxD, pMinD, pOct, pValid, pLevel, pScale; };
   std::vector<Off> off(nj);
   std::vector<int> entryCap(nj);
   for (int j = 0; j < nj; j++) {
@@ -152,7 +249,17 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
     o.cellItems = plan.add((size_t)std::max(n, 1) * sizeof(int));
     o.valid = plan.add(std::max(nq, 1));
     o.x = plan.add((size_t)std::max(nq, 1) * 4); o.y = plan.add((size_t)std::max(nq, 1) * 4); o.r = plan.add((size_t)std::max(nq, 1) * 4);
-    o.xr = (J.q.xrCheck || (J.q.gate && !J.q.xr.empty())) ? plan.add((size_t)std::max(nq, 1) * 4) : (size_t)-1;
+    o.xr = (J.q.xrCheck || (J.q.gate && !J.q.xr.empty()) || (J.proj && J.proj->want_xr)) ? plan.add((size_t)std::max(nq, 1) * 4) : (size_t)-1;
+    if (J.proj) {
+      o.pPos = plan.add((size_t)std::max(nq, 1) * 12);
+      o.pNormal = J.pts->normal ? plan.add((size_t)std::max(nq, 1) * 12) : (size_t)-1;
+      o.pMaxD = J.pts->max_distance ? plan.add((size_t)std::max(nq, 1) * 4) : (size_t)-1;
+      o.pMinD = J.pts->min_distance ? plan.add((size_t)std::max(nq, 1) * 4) : (size_t)-1;
+      o.pOct = J.pts->octave ? plan.add((size_t)std::max(nq, 1) * 4) : (size_t)-1;
+      o.pValid = J.pts->valid ? plan.add(std::max(nq, 1)) : (size_t)-1;
+      o.pLevel = plan.add((size_t)std::max(nq, 1) * 4);
+      o.pScale = plan.add((size_t)std::max(J.F->nlevels, 1) * 4);
+    }
     o.sigma = J.q.gate ? plan.add((size_t)std::max(J.q.nSigma, 1) * 4) : (size_t)-1;
     if (kind == RESOLVE_BEST) o.m12 = plan.add((size_t)std::max(nq, 1) * 4);
     o.minL = plan.add(std::max(nq, 1)); o.maxL = plan.add(std::max(nq, 1));
@@ -289,10 +396,20 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
     maxN = std::max(maxN, G.n);
     QuerySet& Q = sets[j];
     Q.nq = nq;
-    CK(up(o.valid, J.q.valid.data(), nq)); CK(up(o.x, J.q.x.data(), (size_t)nq * 4)); CK(up(o.y, J.q.y.data(), (size_t)nq * 4));
-    CK(up(o.r, J.q.r.data(), (size_t)nq * 4)); CK(up(o.minL, J.q.minL.data(), nq)); CK(up(o.maxL, J.q.maxL.data(), nq));
+    if (J.proj) {   // the queries are computed on the device from the points and the pose
+      CK(up(o.pPos, J.pts->world_pos, (size_t)nq * 12));
+      if (J.pts->normal) CK(up(o.pNormal, J.pts->normal, (size_t)nq * 12));
+      if (J.pts->max_distance) CK(up(o.pMaxD, J.pts->max_distance, (size_t)nq * 4));
+      if (J.pts->min_distance) CK(up(o.pMinD, J.pts->min_distance, (size_t)nq * 4));
+      if (J.pts->octave) CK(up(o.pOct, J.pts->octave, (size_t)nq * 4));
+      if (J.pts->valid) CK(up(o.pValid, J.pts->valid, nq));
+      CK(up(o.pScale, J.F->scale_factors, (size_t)J.F->nlevels * 4));
+    } else {
+      CK(up(o.valid, J.q.valid.data(), nq)); CK(up(o.x, J.q.x.data(), (size_t)nq * 4)); CK(up(o.y, J.q.y.data(), (size_t)nq * 4));
+      CK(up(o.r, J.q.r.data(), (size_t)nq * 4)); CK(up(o.minL, J.q.minL.data(), nq)); CK(up(o.maxL, J.q.maxL.data(), nq));
+      if (o.xr != (size_t)-1) CK(up(o.xr, J.q.xr.data(), (size_t)nq * 4));
+    }
     CK(up(o.qdesc, J.q.desc, (size_t)nq * 32));
-    if (o.xr != (size_t)-1) CK(up(o.xr, J.q.xr.data(), (size_t)nq * 4));
     if (J.q.gate) CK(up(o.sigma, J.q.invSigma2, (size_t)J.q.nSigma * 4));
     Q.valid = at<uint8_t>(m, o.valid); Q.x = at<float>(m, o.x); Q.y = at<float>(m, o.y); Q.r = at<float>(m, o.r);
     Q.minL = at<int8_t>(m, o.minL); Q.maxL = at<int8_t>(m, o.maxL); Q.desc = at<uint8_t>(m, o.qdesc);
@@ -333,6 +450,21 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
   CK(cudaMemsetAsync(m->dStatus, 0, sizeof(int), st));
   const GridFrame* dFrames = at<GridFrame>(m, oFrames);
   const QuerySet* dSets = at<QuerySet>(m, oSets);
+  for (int j = 0; j < nj; j++) {
+    const WindowJob& J = jobs[j];
+    if (!J.proj || J.q.nq == 0) continue;
+    const Off& o = off[j];
+    ProjectArgs A{};
+    A.P = *J.proj; A.n = J.q.nq; A.nlevels = J.F->nlevels;
+    A.pos = at<float>(m, o.pPos); A.normal = o.pNormal != (size_t)-1 ? at<float>(m, o.pNormal) : nullptr;
+    A.maxD = o.pMaxD != (size_t)-1 ? at<float>(m, o.pMaxD) : nullptr; A.minD = o.pMinD != (size_t)-1 ? at<float>(m, o.pMinD) : nullptr;
+    A.octave = o.pOct != (size_t)-1 ? at<int>(m, o.pOct) : nullptr; A.validIn = o.pValid != (size_t)-1 ? at<uint8_t>(m, o.pValid) : nullptr;
+    A.scale = at<float>(m, o.pScale);
+    A.valid = at<uint8_t>(m, o.valid); A.x = at<float>(m, o.x); A.y = at<float>(m, o.y); A.r = at<float>(m, o.r);
+    A.minL = at<int8_t>(m, o.minL); A.maxL = at<int8_t>(m, o.maxL); A.xr = o.xr != (size_t)-1 ? at<float>(m, o.xr) : nullptr;
+    A.level = at<int>(m, o.pLevel);
+    k_project_points<<<(A.n + 255) / 256, 256, 0, st>>>(A);
+  }
   k_build_grid<<<nj, 256, 0, st>>>(dFrames);
   if (maxQ > 0) k_window_candidates<<<dim3((maxQ + 7) / 8, nj), 256, 0, st>>>(dFrames, dSets, m->dStatus);
   if (kind == RESOLVE_MAPPOINTS) {
@@ -359,7 +491,14 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
     } else if (kind == RESOLVE_BEST) {
       CK(down(J.bestIdx, o.assigned, (size_t)J.q.nq * 4));
       CK(down(J.bestDist, o.m12, (size_t)J.q.nq * 4));
-    } else if (J.entriesOut) {
+    }
+    if (J.proj && J.dbg) {   // what the prologue produced (tests compare it with the oracle)
+      const int nq = J.q.nq;
+      CK(down(J.dbg->valid, o.valid, nq)); CK(down(J.dbg->u, o.x, (size_t)nq * 4)); CK(down(J.dbg->v, o.y, (size_t)nq * 4));
+      CK(down(J.dbg->radius, o.r, (size_t)nq * 4)); CK(down(J.dbg->level, o.pLevel, (size_t)nq * 4));
+      if (o.xr != (size_t)-1) CK(down(J.dbg->xr, o.xr, (size_t)nq * 4));
+    }
+    if (kind == RESOLVE_NONE && J.entriesOut) {
       int cnt = 0;
       CK(cudaMemcpyAsync(&cnt, m->arena + o.qCnt, 4, cudaMemcpyDeviceToHost, st));
       CK(cudaStreamSynchronize(st));
@@ -742,6 +881,59 @@ int orbx_search_window_best(orbx_matcher* m, const orbx_frame_view* F, int n, co
     if (l < 0 || l > 127) q.valid[i] = 0;
     q.minL[i] = (int8_t)(l - 1); q.maxL[i] = (int8_t)l;
   }
+  J.bestIdx = bestIdx; J.bestDist = bestDist;
+  return run_window_jobs(m, jobs, RESOLVE_BEST);
+}
+
+static int check_projection(const orbx_frame_view* F, const orbx_projection* P, const orbx_projection_points* pts) {
+  if (!P || !pts || pts->n < 0) return ORBX_ERR_ARG;
+  if (pts->n > 0 && (!pts->world_pos || !pts->desc)) { set_error("projection: world_pos / desc missing"); return ORBX_ERR_ARG; }
+  if (P->level_mode == 0 && pts->n > 0 && !pts->octave) { set_error("projection: level_mode 0 needs the source octaves"); return ORBX_ERR_ARG; }
+  if ((P->range_mode || P->level_mode == 1) && pts->n > 0 && (!pts->max_distance || !pts->min_distance)) {
+    set_error("projection: the distance range / PredictScale need mfMaxDistance and mfMinDistance"); return ORBX_ERR_ARG;
+  }
+  if (P->normal_check && pts->n > 0 && !pts->normal) { set_error("projection: the viewing-angle test needs the normals"); return ORBX_ERR_ARG; }
+  if (P->level_mode == 1 && (!(P->log_scale_factor > 0.f) || P->n_scale_levels < 1)) { set_error("projection: PredictScale needs log_scale_factor / n_scale_levels"); return ORBX_ERR_ARG; }
+  if (F->nlevels < 1 || !F->scale_factors) { set_error("projection: the frame view needs its scale factors"); return ORBX_ERR_ARG; }
+  if (P->camera_model != ORBX_CAMERA_PINHOLE && P->camera_model != ORBX_CAMERA_KB8) return ORBX_ERR_ARG;
+  return ORBX_OK;
+}
+
+int orbx_search_projected_window(orbx_matcher* m, const orbx_frame_view* F, const orbx_projection* P, const orbx_projection_points* pts,
+                                 const float* angle, const uint8_t* observed, int distTh, int anyMpBlocks, int checkOrientation, int* kpMp,
+                                 int* nmatches, const orbx_projection_debug* dbg) {
+  if (!m || !kpMp || !nmatches) return ORBX_ERR_ARG;
+  int rc = check_view(F, true);
+  if (rc != ORBX_OK) return rc;
+  if ((rc = check_projection(F, P, pts)) != ORBX_OK) return rc;
+  if (checkOrientation && pts->n > 0 && !angle) return ORBX_ERR_ARG;
+  std::vector<WindowJob> jobs(1);
+  WindowJob& J = jobs[0];
+  J.F = F; set_bounds(J, F);
+  J.proj = P; J.pts = pts; J.dbg = dbg;
+  J.q.nq = pts->n; J.q.desc = pts->desc;
+  J.q.xrCheck = P->want_xr != 0 && F->u_right != nullptr;
+  J.observed = observed; J.angle = angle; J.kpMp = kpMp; J.kpMpLen = F->n;
+  J.nnratio = 0.f; J.distTh = distTh; J.anyMpBlocks = anyMpBlocks; J.checkOrientation = checkOrientation;
+  J.nmatches = nmatches;
+  *nmatches = 0;
+  return run_window_jobs(m, jobs, RESOLVE_WINDOW);
+}
+
+int orbx_search_projected_best(orbx_matcher* m, const orbx_frame_view* F, const orbx_projection* P, const orbx_projection_points* pts, int gate,
+                               const float* invLevelSigma2, int* bestIdx, int* bestDist, const orbx_projection_debug* dbg) {
+  if (!m || !bestIdx || !bestDist) return ORBX_ERR_ARG;
+  int rc = check_view(F, false);
+  if (rc != ORBX_OK) return rc;
+  if ((rc = check_projection(F, P, pts)) != ORBX_OK) return rc;
+  if (gate && (!invLevelSigma2 || (F->u_right && !P->want_xr))) { set_error("chi-square gate needs inv_level_sigma2 (and want_xr for stereo keyframes)"); return ORBX_ERR_ARG; }
+  if (pts->n == 0) return ORBX_OK;
+  std::vector<WindowJob> jobs(1);
+  WindowJob& J = jobs[0];
+  J.F = F; set_bounds(J, F);
+  J.proj = P; J.pts = pts; J.dbg = dbg;
+  J.q.nq = pts->n; J.q.desc = pts->desc;
+  J.q.gate = gate != 0; J.q.invSigma2 = invLevelSigma2; J.q.nSigma = gate ? F->nlevels : 0;
   J.bestIdx = bestIdx; J.bestDist = bestDist;
   return run_window_jobs(m, jobs, RESOLVE_BEST);
 }

@@ -32,7 +32,7 @@ class FramePreproc {
 
   // cvtColor(src, gray, CV_{RGB|BGR}[A]2GRAY); bRGB = Tracking::mbRGB.  src and gray must not alias.
   void cvtColorToGray(const uint8_t* src, int cols, int rows, size_t step, int channels, bool bRGB, cvx::Mat& gray) {
-    gray.create(rows, cols, cvx::CV_8U);
+    gray.create(rows, cols, ORBX_MAT_8U);
     ck(orbx_cvt_gray(h_, src, 1, cols, rows, (int)step, 0, channels, bRGB ? 1 : 0, coeffs_, gray.data, (int)gray.step, 0, ORBX_MEM_HOST, nullptr),
        "orbx_cvt_gray");
   }
@@ -54,7 +54,7 @@ class FramePreproc {
   }
   // cv::remap(src, dst, M1, M2, cv::INTER_LINEAR)
   void remap(const cvx::Mat& src, cvx::Mat& dst, int mapId) {
-    dst.create(dims_[2 * mapId + 1], dims_[2 * mapId], cvx::CV_8U);
+    dst.create(dims_[2 * mapId + 1], dims_[2 * mapId], ORBX_MAT_8U);
     ck(orbx_remap(h_, tables_.at(mapId), src.data, 1, (int)src.step, 0, dst.data, (int)dst.step, 0, ORBX_MEM_HOST, nullptr), "orbx_remap");
   }
   // cv::createCLAHE(clipLimit, Size(tilesX, tilesY))->apply(im, im)

@@ -24,11 +24,11 @@ namespace ORB_SLAM3 {
 namespace orbx_shim {
 #ifdef ORBX_WITH_OPENCV
 inline cv::Mat as_mat(cv::InputArray a) { return a.getMat(); }
-inline cv::Mat create(cv::OutputArray a, int rows, int cols) { a.create(rows, cols, CV_8U); return a.getMat(); }
+inline cv::Mat create(cv::OutputArray a, int rows, int cols) { a.create(rows, cols, ORBX_MAT_8U); return a.getMat(); }
 inline void release(cv::OutputArray a) { a.release(); }
 #else
 inline cvx::Mat as_mat(cvx::InputArray a) { return a; }
-inline cvx::Mat& create(cvx::OutputArray a, int rows, int cols) { a.create(rows, cols, cvx::CV_8U); return a; }
+inline cvx::Mat& create(cvx::OutputArray a, int rows, int cols) { a.create(rows, cols, ORBX_MAT_8U); return a; }
 inline void release(cvx::OutputArray a) { a.release(); }
 #endif
 inline void check(int rc, const char* what) {
@@ -97,7 +97,7 @@ class ORBextractor {
     for (int l = 0; l < nlevels; l++) {
       int w = 0, hgt = 0;
       orbx_shim::check(orbx_pyramid_level(h_, 0, l, nullptr, 0, &w, &hgt), "orbx_pyramid_level");
-      mvImagePyramid[l].create(hgt, w, cvx::CV_8U);
+      mvImagePyramid[l].create(hgt, w, ORBX_MAT_8U);
       orbx_shim::check(orbx_pyramid_level(h_, 0, l, mvImagePyramid[l].ptr(0), (int)mvImagePyramid[l].step, &w, &hgt), "orbx_pyramid_level");
     }
     pyramidStale_ = false;

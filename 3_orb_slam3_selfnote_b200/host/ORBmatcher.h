@@ -3,14 +3,20 @@
 // the C-ABI of include/orbx.h.  The search methods are templates over the frame / map-point types and read exactly the
 // members the reference's bodies read (F.N, F.mvKeysUn, F.mDescriptors, F.mvuRight, F.mvScaleFactors, F.mnMinX.., F.Nleft,
 // F.mvpMapPoints, pMP->mbTrackInView, ...), so they bind to the reference's own Frame / MapPoint classes unchanged and to
-// the small mocks of tests/cpp/shim_test.cc alike.  Pose algebra / camera projection (the loop prologues of the
-// Frame-Frame and Frame-KeyFrame overloads) stay on the host: see SearchByProjectionProjected and INTEGRATION.md.
-// SearchByProjectionProjected with mode 3 is the search loop of both SearchByProjection(KeyFrame*, Scw, ...) overloads
-// (src/ORBmatcher.cc:489-720: anyMpBlocks = true, distTh = floor(TH_LOW*ratioHamming), kpMp = vpMatched as -1 / -2).
+// the small mocks of tests/cpp/shim_test.cc alike.
+// With ORBX_WITH_OPENCV (real OpenCV, i.e. the drop-in build) the overloads that start from poses and 3-D map points carry the
+// reference's exact parameter lists -- SearchByProjection(Frame&, const Frame&, th, bMono), (Frame&, KeyFrame*, set, th, ORBdist),
+// both (KeyFrame*, cv::Mat Scw, ...), Fuse x2, SearchBySim3, SearchForTriangulation(.., cv::Mat F12, ..): the 3x3 pose algebra in
+// front of each loop is the reference's own cv::Mat lines (a few per function), everything per point -- transform, projection,
+// bounds / range / viewing-angle tests, PredictScale, radius -- runs on the device (orbx_search_projected_window / _best).
+// The *Projected forms below them take already-projected points and work without OpenCV.
 #pragma once
 #include <climits>
+#include <cmath>
 #include <cstring>
+#include <set>
 #include <stdexcept>
+#include <tuple>
 #include <utility>
 #include <vector>
 
@@ -102,6 +108,234 @@ class ORBmatcher {
                      "orbx_search_by_projection_window");
     return nmatches;
   }
+
+#ifdef ORBX_WITH_OPENCV
+  // ---- reference signatures with the projection prologue on the device ------------------------------------------------------
+  // Project MapPoints tracked in last frame into the current frame and search matches (Tracking::TrackWithMotionModel),
+  // src/ORBmatcher.cc:2027-2289.  Monocular / rectified-stereo frames (Nleft == -1).
+  template <class FrameT>
+  int SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame, const float th, const bool bMono) {
+    if (CurrentFrame.Nleft != -1 || LastFrame.Nleft != -1) throw std::runtime_error("ORBmatcher::SearchByProjection(Frame, Frame): fisheye stereo (Nleft != -1) is not offloaded");
+    const cv::Mat Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3);   // :2038-2047, the reference's lines
+    const cv::Mat tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
+    const cv::Mat twc = -Rcw.t() * tcw;
+    const cv::Mat Rlw = LastFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+    const cv::Mat tlw = LastFrame.mTcw.rowRange(0, 3).col(3);
+    const cv::Mat tlc = Rlw * twc + tlw;
+    const bool bForward = tlc.at<float>(2) > CurrentFrame.mb && !bMono;
+    const bool bBackward = -tlc.at<float>(2) > CurrentFrame.mb && !bMono;
+    orbx_projection P = projection_of(Rcw, tcw, twc, CurrentFrame.mpCamera);
+    frame_bounds(CurrentFrame, P);
+    P.depth_mode = 0; P.invz_mode = 0; P.bf = CurrentFrame.mbf; P.want_xr = 1;
+    P.level_mode = 0; P.window_mode = bForward ? 1 : (bBackward ? 2 : 0); P.th = th;
+    const int n = LastFrame.N;
+    PointArrays A(n);
+    A.useOctave(); A.useAngle();
+    for (int i = 0; i < n; i++) {
+      auto* pMP = LastFrame.mvpMapPoints[i];
+      if (!pMP || LastFrame.mvbOutlier[i]) continue;
+      A.valid[i] = 1;
+      A.setPos(i, pMP->GetWorldPos()); A.setDesc(i, pMP->GetDescriptor());
+      A.octave[i] = LastFrame.mvKeys[i].octave;
+      A.angle[i] = LastFrame.mvKeysUn[i].angle;
+    }
+    return run_window(CurrentFrame, P, A, TH_HIGH, /*anyMpBlocks=*/false, mbCheckOrientation, [&](int k, int i) { CurrentFrame.mvpMapPoints[k] = LastFrame.mvpMapPoints[i]; });
+  }
+
+  // Project MapPoints seen in KeyFrame into the Frame and search matches (relocalisation), src/ORBmatcher.cc:2291-2413.
+  template <class FrameT, class KeyFrameT, class MapPointT>
+  int SearchByProjection(FrameT& CurrentFrame, KeyFrameT* pKF, const std::set<MapPointT*>& sAlreadyFound, const float th, const int ORBdist) {
+    if (CurrentFrame.Nleft != -1) throw std::runtime_error("ORBmatcher::SearchByProjection(Frame, KeyFrame): fisheye stereo (Nleft != -1) is not offloaded");
+    const cv::Mat Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3);   // :2295-2297
+    const cv::Mat tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
+    const cv::Mat Ow = -Rcw.t() * tcw;
+    orbx_projection P = projection_of(Rcw, tcw, Ow, CurrentFrame.mpCamera);
+    frame_bounds(CurrentFrame, P);
+    P.depth_mode = 2; P.range_mode = 1; P.level_mode = 1; P.window_mode = 0; P.th = th;
+    P.log_scale_factor = CurrentFrame.mfLogScaleFactor; P.n_scale_levels = CurrentFrame.mnScaleLevels;
+    const std::vector<MapPointT*> vpMPs = pKF->GetMapPointMatches();
+    const int n = (int)vpMPs.size();
+    PointArrays A(n);
+    A.useRange(); A.useAngle();
+    for (int i = 0; i < n; i++) {
+      MapPointT* pMP = vpMPs[i];
+      if (!pMP || pMP->isBad() || sAlreadyFound.count(pMP)) continue;
+      A.valid[i] = 1;
+      A.setPos(i, pMP->GetWorldPos()); A.setDesc(i, pMP->GetDescriptor());
+      A.setRange(i, pMP);
+      A.angle[i] = pKF->mvKeysUn[i].angle;
+    }
+    return run_window(CurrentFrame, P, A, ORBdist, /*anyMpBlocks=*/true, mbCheckOrientation, [&](int k, int i) { CurrentFrame.mvpMapPoints[k] = vpMPs[i]; });
+  }
+
+  // Project MapPoints using a Similarity Transformation and search matches (loop detection), src/ORBmatcher.cc:489-602.
+  template <class KeyFrameT, class MapPointT>
+  int SearchByProjection(KeyFrameT* pKF, cv::Mat Scw, const std::vector<MapPointT*>& vpPoints, std::vector<MapPointT*>& vpMatched, int th,
+                         float ratioHamming = 1.0) {
+    return search_scw(pKF, Scw, vpPoints, vpMatched, th, ratioHamming, [](int, int) {});
+  }
+  // ... with the keyframe of every point (place recognition), src/ORBmatcher.cc:604-720.
+  template <class KeyFrameT, class MapPointT>
+  int SearchByProjection(KeyFrameT* pKF, cv::Mat Scw, const std::vector<MapPointT*>& vpPoints, const std::vector<KeyFrameT*>& vpPointsKFs,
+                         std::vector<MapPointT*>& vpMatched, std::vector<KeyFrameT*>& vpMatchedKF, int th, float ratioHamming = 1.0) {
+    return search_scw(pKF, Scw, vpPoints, vpMatched, th, ratioHamming, [&](int k, int i) { vpMatchedKF[k] = vpPointsKFs[i]; });
+  }
+
+  // Project MapPoints into KeyFrame and search for duplicated MapPoints, src/ORBmatcher.cc:1425-1662 (bRight = false).
+  template <class KeyFrameT, class MapPointT>
+  int Fuse(KeyFrameT* pKF, const std::vector<MapPointT*>& vpMapPoints, const float th = 3.0, const bool bRight = false) {
+    if (bRight || pKF->NLeft != -1) throw std::runtime_error("ORBmatcher::Fuse: fisheye stereo (bRight / NLeft != -1) is not offloaded");
+    const cv::Mat Rcw = pKF->GetRotation(), tcw = pKF->GetTranslation(), Ow = pKF->GetCameraCenter();   // :1436-1438
+    orbx_projection P = projection_of(Rcw, tcw, Ow, pKF->mpCamera);
+    keyframe_bounds(pKF, P);
+    P.depth_mode = 1; P.invz_mode = 1; P.bf = pKF->mbf; P.want_xr = 1; P.range_mode = 1; P.normal_check = 1; P.level_mode = 1; P.window_mode = 3; P.th = th;
+    P.log_scale_factor = pKF->mfLogScaleFactor; P.n_scale_levels = pKF->mnScaleLevels;
+    const int n = (int)vpMapPoints.size();
+    PointArrays A(n);
+    A.useRange(); A.useNormal();
+    for (int i = 0; i < n; i++) {
+      MapPointT* pMP = vpMapPoints[i];
+      if (!pMP || pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+      A.valid[i] = 1;
+      A.setPos(i, pMP->GetWorldPos()); A.setDesc(i, pMP->GetDescriptor()); A.setRange(i, pMP); A.setNormal(i, pMP->GetNormal());
+    }
+    std::vector<int> bestIdx, bestDist;
+    run_best(*pKF, P, A, /*gate=*/true, pKF->mvInvLevelSigma2.data(), bestIdx, bestDist);
+    int nFused = 0;
+    for (int i = 0; i < n; i++) {   // the bookkeeping of :1626-1650 in the reference's order (it can change what later points see)
+      MapPointT* pMP = vpMapPoints[i];
+      if (!A.valid[i] || pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+      if (bestIdx[i] < 0 || bestDist[i] > TH_LOW) continue;
+      MapPointT* pMPinKF = pKF->GetMapPoint(bestIdx[i]);
+      if (pMPinKF) {
+        if (!pMPinKF->isBad()) {
+          if (pMPinKF->Observations() > pMP->Observations()) pMP->Replace(pMPinKF);
+          else pMPinKF->Replace(pMP);
+        }
+      } else {
+        pMP->AddObservation(pKF, bestIdx[i]);
+        pKF->AddMapPoint(pMP, bestIdx[i]);
+      }
+      nFused++;
+    }
+    return nFused;
+  }
+
+  // Project MapPoints into KeyFrame using a given Sim3 and search for duplicated MapPoints, src/ORBmatcher.cc:1664-1786.
+  template <class KeyFrameT, class MapPointT>
+  int Fuse(KeyFrameT* pKF, cv::Mat Scw, const std::vector<MapPointT*>& vpPoints, float th, std::vector<MapPointT*>& vpReplacePoint) {
+    cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);   // :1673-1677
+    const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
+    cv::Mat Rcw = sRcw / scw;
+    cv::Mat tcw = Scw.rowRange(0, 3).col(3) / scw;
+    cv::Mat Ow = -Rcw.t() * tcw;
+    orbx_projection P = projection_of(Rcw, tcw, Ow, pKF->mpCamera);
+    keyframe_bounds(pKF, P);
+    P.depth_mode = 1; P.range_mode = 1; P.normal_check = 1; P.level_mode = 1; P.window_mode = 3; P.th = th;
+    P.log_scale_factor = pKF->mfLogScaleFactor; P.n_scale_levels = pKF->mnScaleLevels;
+    const std::set<MapPointT*> spAlreadyFound = pKF->GetMapPoints();
+    const int n = (int)vpPoints.size();
+    PointArrays A(n);
+    A.useRange(); A.useNormal();
+    for (int i = 0; i < n; i++) {
+      MapPointT* pMP = vpPoints[i];
+      if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+      A.valid[i] = 1;
+      A.setPos(i, pMP->GetWorldPos()); A.setDesc(i, pMP->GetDescriptor()); A.setRange(i, pMP); A.setNormal(i, pMP->GetNormal());
+    }
+    std::vector<int> bestIdx, bestDist;
+    run_best(*pKF, P, A, /*gate=*/false, nullptr, bestIdx, bestDist);
+    int nFused = 0;
+    for (int i = 0; i < n; i++) {   // :1765-1782
+      MapPointT* pMP = vpPoints[i];
+      if (!A.valid[i] || bestIdx[i] < 0 || bestDist[i] > TH_LOW) continue;
+      MapPointT* pMPinKF = pKF->GetMapPoint(bestIdx[i]);
+      if (pMPinKF) {
+        if (!pMPinKF->isBad()) vpReplacePoint[i] = pMPinKF;
+      } else {
+        pMP->AddObservation(pKF, bestIdx[i]);
+        pKF->AddMapPoint(pMP, bestIdx[i]);
+      }
+      nFused++;
+    }
+    return nFused;
+  }
+
+  // Search matches between MapPoints seen in KF1 and KF2 transforming by a Sim3 [s12*R12|t12], src/ORBmatcher.cc:1788-2018.
+  template <class KeyFrameT, class MapPointT>
+  int SearchBySim3(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12, const float& s12, const cv::Mat& R12, const cv::Mat& t12,
+                   const float th) {
+    cv::Mat R1w = pKF1->GetRotation(), t1w = pKF1->GetTranslation();   // :1797-1807
+    cv::Mat R2w = pKF2->GetRotation(), t2w = pKF2->GetTranslation();
+    cv::Mat sR12 = s12 * R12;
+    cv::Mat sR21 = (1.0 / s12) * R12.t();
+    cv::Mat t21 = -sR21 * t12;
+    const std::vector<MapPointT*> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
+    const int N1 = (int)vpMapPoints1.size(), N2 = (int)vpMapPoints2.size();
+    std::vector<bool> vbAlreadyMatched1(N1, false), vbAlreadyMatched2(N2, false);
+    for (int i = 0; i < N1; i++) {
+      MapPointT* pMP = vpMatches12[i];
+      if (pMP) {
+        vbAlreadyMatched1[i] = true;
+        const int idx2 = std::get<0>(pMP->GetIndexInKeyFrame(pKF2));
+        if (idx2 >= 0 && idx2 < N2) vbAlreadyMatched2[idx2] = true;
+      }
+    }
+    auto pass = [&](KeyFrameT* from, KeyFrameT* into, const std::vector<MapPointT*>& pts, const std::vector<bool>& done, const cv::Mat& Ra, const cv::Mat& ta,
+                    const cv::Mat& Rb, const cv::Mat& tb, std::vector<int>& match) {
+      (void)from;
+      orbx_projection P = projection_of(Ra, ta, ta, into->mpCamera);
+      put3x3(Rb, P.R2); put3(tb, P.t2); P.chain = 1;
+      P.fx = into->fx; P.fy = into->fy; P.cx = into->cx; P.cy = into->cy; P.proj_mode = 1;   // :1792-1795 (pKF1's intrinsics; same camera)
+      keyframe_bounds(into, P);
+      P.depth_mode = 1; P.invz_mode = 0; P.range_mode = 1; P.dist_mode = 1; P.level_mode = 1; P.window_mode = 3; P.th = th;
+      P.log_scale_factor = into->mfLogScaleFactor; P.n_scale_levels = into->mnScaleLevels;
+      const int n = (int)pts.size();
+      PointArrays A(n);
+      A.useRange();
+      for (int i = 0; i < n; i++) {
+        MapPointT* pMP = pts[i];
+        if (!pMP || done[i] || pMP->isBad()) continue;
+        A.valid[i] = 1;
+        A.setPos(i, pMP->GetWorldPos()); A.setDesc(i, pMP->GetDescriptor()); A.setRange(i, pMP);
+      }
+      std::vector<int> bestIdx, bestDist;
+      run_best(*into, P, A, false, nullptr, bestIdx, bestDist);
+      match.assign(n, -1);
+      for (int i = 0; i < n; i++)
+        if (A.valid[i] && bestIdx[i] >= 0 && bestDist[i] <= TH_HIGH) match[i] = bestIdx[i];
+    };
+    std::vector<int> vnMatch1, vnMatch2;
+    pass(pKF1, pKF2, vpMapPoints1, vbAlreadyMatched1, R1w, t1w, sR21, t21, vnMatch1);   // :1838-1915
+    pass(pKF2, pKF1, vpMapPoints2, vbAlreadyMatched2, R2w, t2w, sR12, t12, vnMatch2);   // :1917-1996
+    int nFound = 0;   // :1998-2015
+    for (int i1 = 0; i1 < N1; i1++) {
+      const int idx2 = vnMatch1[i1];
+      if (idx2 >= 0) {
+        const int idx1 = vnMatch2[idx2];
+        if (idx1 == i1) { vpMatches12[i1] = vpMapPoints2[idx2]; nFound++; }
+      }
+    }
+    return nFound;
+  }
+
+  // Matching to triangulate new MapPoints with the reference's parameter list (cv::Mat F12), src/ORBmatcher.cc:981-1222: pinhole
+  // keyframes without a second camera.  F12 is the matrix LocalMapping::ComputeF12 formed (K1^-T [t12]x R12 K2^-1, the very
+  // expression Pinhole::epipolarConstrain re-evaluates per pair, Pinhole.cpp:145-148); the epipole is projected here (:988-994).
+  template <class KeyFrameT>
+  int SearchForTriangulation(KeyFrameT* pKF1, KeyFrameT* pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t> >& vMatchedPairs,
+                             const bool bOnlyStereo, const bool bCoarse = false) {
+    if (pKF1->mpCamera2 || pKF2->mpCamera2) throw std::runtime_error("ORBmatcher::SearchForTriangulation: fisheye stereo rigs are not offloaded");
+    cv::Mat Cw = pKF1->GetCameraCenter();
+    cv::Mat R2w = pKF2->GetRotation();
+    cv::Mat t2w = pKF2->GetTranslation();
+    cv::Mat C2 = R2w * Cw + t2w;
+    cv::Point2f ep = pKF2->mpCamera->project(C2);
+    float f[9];
+    put3x3(F12, f);
+    return SearchForTriangulation(pKF1, pKF2, f, ep, vMatchedPairs, bOnlyStereo, bCoarse);
+  }
+#endif  // ORBX_WITH_OPENCV
 
   // ---- SURVEY.md section 8(f) rank 1 ---------------------------------------------------------------------------------------
   // Search matches between MapPoints in a KeyFrame and ORB in a Frame, brute force constrained to ORB that belong to the same
@@ -233,6 +467,129 @@ class ORBmatcher {
   bool mbCheckOrientation;
 
  private:
+#ifdef ORBX_WITH_OPENCV
+  static void put3x3(const cv::Mat& R, float* o) { for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) o[3 * r + c] = R.at<float>(r, c); }
+  static void put3(const cv::Mat& t, float* o) { for (int i = 0; i < 3; i++) o[i] = t.at<float>(i); }
+  template <class CameraT>
+  static orbx_projection projection_of(const cv::Mat& R, const cv::Mat& t, const cv::Mat& Ow, CameraT* cam) {
+    orbx_projection P;
+    memset(&P, 0, sizeof P);
+    put3x3(R, P.R); put3(t, P.t); put3(Ow, P.Ow);
+    P.fx = cam->getParameter(0); P.fy = cam->getParameter(1); P.cx = cam->getParameter(2); P.cy = cam->getParameter(3);
+    P.camera_model = cam->GetType() == 1 ? ORBX_CAMERA_KB8 : ORBX_CAMERA_PINHOLE;   // GeometricCamera::CAM_FISHEYE
+    if (P.camera_model == ORBX_CAMERA_KB8) for (int i = 0; i < 4; i++) P.kb[i] = cam->getParameter(4 + i);
+    return P;
+  }
+  template <class FrameT> static void frame_bounds(const FrameT& F, orbx_projection& P) {
+    P.bounds_mode = 0; P.min_x = F.mnMinX; P.max_x = F.mnMaxX; P.min_y = F.mnMinY; P.max_y = F.mnMaxY;
+  }
+  template <class KeyFrameT> static void keyframe_bounds(const KeyFrameT* K, orbx_projection& P) {
+    P.bounds_mode = 1; P.min_x = (float)K->mnMinX; P.max_x = (float)K->mnMaxX; P.min_y = (float)K->mnMinY; P.max_y = (float)K->mnMaxY;
+  }
+  // structure-of-arrays image of the map points a search walks over
+  struct PointArrays {
+    int n;
+    std::vector<uint8_t> valid, desc;
+    std::vector<float> pos, normal, maxD, minD, angle;
+    std::vector<int> octave;
+    explicit PointArrays(int n_) : n(n_), valid(std::max(n_, 1), 0), desc((size_t)std::max(n_, 1) * 32, 0), pos((size_t)std::max(n_, 1) * 3, 0.f) {}
+    void useOctave() { octave.assign(std::max(n, 1), 0); }
+    void useAngle() { angle.assign(std::max(n, 1), 0.f); }
+    void useRange() { maxD.assign(std::max(n, 1), 0.f); minD.assign(std::max(n, 1), 0.f); }
+    void useNormal() { normal.assign((size_t)std::max(n, 1) * 3, 0.f); }
+    void setPos(int i, const cv::Mat& p) { for (int k = 0; k < 3; k++) pos[3 * (size_t)i + k] = p.at<float>(k); }
+    void setNormal(int i, const cv::Mat& p) { for (int k = 0; k < 3; k++) normal[3 * (size_t)i + k] = p.at<float>(k); }
+    void setDesc(int i, const cv::Mat& d) { memcpy(&desc[(size_t)i * 32], d.ptr(0), 32); }
+    // RAW mfMaxDistance / mfMinDistance recovered from the public getters (1.2f * max, 0.8f * min, MapPoint.cc:555-565): the
+    // device multiplies by the same constants again, so what must round-trip is x -> 1.2f*x -> /1.2f -> *1.2f.  A MapPoint class
+    // that exposes GetMaxDistance() / GetMinDistance() avoids the division.
+    template <class MapPointT> void setRange(int i, MapPointT* pMP) { raw_range(pMP, maxD[i], minD[i], 0); }
+    template <class MapPointT> static auto raw_range(MapPointT* p, float& mx, float& mn, int) -> decltype(p->GetMaxDistance(), void()) {
+      mx = p->GetMaxDistance(); mn = p->GetMinDistance();
+    }
+    template <class MapPointT> static void raw_range(MapPointT* p, float& mx, float& mn, long) {
+      mx = unscale(p->GetMaxDistanceInvariance(), 1.2f); mn = unscale(p->GetMinDistanceInvariance(), 0.8f);
+    }
+    static float unscale(float scaled, float k) {   // the float x with k * x == scaled (nearest candidate first)
+      float x = scaled / k;
+      if (k * x == scaled) return x;
+      const float lo = std::nextafter(x, -INFINITY), hi = std::nextafter(x, INFINITY);
+      if (k * lo == scaled) return lo;
+      if (k * hi == scaled) return hi;
+      return x;
+    }
+    orbx_projection_points c() const {
+      orbx_projection_points p;
+      p.n = n; p.world_pos = pos.data(); p.normal = normal.empty() ? nullptr : normal.data();
+      p.max_distance = maxD.empty() ? nullptr : maxD.data(); p.min_distance = minD.empty() ? nullptr : minD.data();
+      p.octave = octave.empty() ? nullptr : octave.data(); p.valid = valid.data(); p.desc = desc.data();
+      return p;
+    }
+  };
+  // window search with claiming: kpMp = the frame's current map points as -1 / -2 (blocking) / -3; assign(k, i) stores match i -> keypoint k
+  template <class FrameT, class Assign>
+  int run_window(FrameT& F, const orbx_projection& P, const PointArrays& A, int distTh, bool anyMpBlocks, bool checkOri, Assign assign) {
+    FrameViewHolder fv(F);
+    std::vector<int> kpMp(std::max(F.N, 1), -1);
+    for (int k = 0; k < F.N; k++) {
+      auto* p = F.mvpMapPoints[k];
+      kpMp[k] = !p ? -1 : ((anyMpBlocks || p->Observations() > 0) ? -2 : -3);
+    }
+    const orbx_projection_points pts = A.c();
+    int nmatches = 0;
+    orbx_shim::check(orbx_search_projected_window(m_, &fv.v, &P, &pts, A.angle.empty() ? nullptr : A.angle.data(), nullptr, distTh, anyMpBlocks ? 1 : 0,
+                                                  checkOri ? 1 : 0, kpMp.data(), &nmatches, nullptr),
+                     "orbx_search_projected_window");
+    for (int k = 0; k < F.N; k++)
+      if (kpMp[k] >= 0) assign(k, kpMp[k]);
+    return nmatches;
+  }
+  template <class KeyFrameT>
+  void run_best(KeyFrameT& K, const orbx_projection& P, const PointArrays& A, bool gate, const float* invSigma2, std::vector<int>& bestIdx,
+                std::vector<int>& bestDist) {
+    FrameViewHolder fv(K);
+    bestIdx.assign(std::max(A.n, 1), -1); bestDist.assign(std::max(A.n, 1), 256);
+    const orbx_projection_points pts = A.c();
+    orbx_shim::check(orbx_search_projected_best(m_, &fv.v, &P, &pts, gate ? 1 : 0, invSigma2, bestIdx.data(), bestDist.data(), nullptr),
+                     "orbx_search_projected_best");
+  }
+  template <class KeyFrameT, class MapPointT, class Extra>
+  int search_scw(KeyFrameT* pKF, cv::Mat Scw, const std::vector<MapPointT*>& vpPoints, std::vector<MapPointT*>& vpMatched, int th, float ratioHamming,
+                 Extra extra) {
+    cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);   // :499-503 / :614-618, the reference's lines
+    const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
+    cv::Mat Rcw = sRcw / scw;
+    cv::Mat tcw = Scw.rowRange(0, 3).col(3) / scw;
+    cv::Mat Ow = -Rcw.t() * tcw;
+    orbx_projection P = projection_of(Rcw, tcw, Ow, pKF->mpCamera);
+    keyframe_bounds(pKF, P);
+    P.depth_mode = 1; P.range_mode = 1; P.normal_check = 1; P.level_mode = 1; P.window_mode = 3; P.th = (float)th;
+    P.log_scale_factor = pKF->mfLogScaleFactor; P.n_scale_levels = pKF->mnScaleLevels;
+    std::set<MapPointT*> spAlreadyFound(vpMatched.begin(), vpMatched.end());
+    spAlreadyFound.erase(static_cast<MapPointT*>(nullptr));
+    const int n = (int)vpPoints.size();
+    PointArrays A(n);
+    A.useRange(); A.useNormal();
+    for (int i = 0; i < n; i++) {
+      MapPointT* pMP = vpPoints[i];
+      if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+      A.valid[i] = 1;
+      A.setPos(i, pMP->GetWorldPos()); A.setDesc(i, pMP->GetDescriptor()); A.setRange(i, pMP); A.setNormal(i, pMP->GetNormal());
+    }
+    FrameViewHolder fv(*pKF);
+    const int N = (int)vpMatched.size();
+    std::vector<int> kpMp(std::max(N, 1), -1);
+    for (int k = 0; k < N; k++) kpMp[k] = vpMatched[k] ? -2 : -1;   // `if(vpMatched[idx]) continue` (:578): every match blocks
+    const orbx_projection_points pts = A.c();
+    int nmatches = 0;
+    orbx_shim::check(orbx_search_projected_window(m_, &fv.v, &P, &pts, nullptr, nullptr, (int)std::floor(TH_LOW * ratioHamming), 1, 0, kpMp.data(),
+                                                  &nmatches, nullptr),
+                     "orbx_search_projected_window");
+    for (int k = 0; k < N; k++)
+      if (kpMp[k] >= 0) { vpMatched[k] = vpPoints[kpMp[k]]; extra(k, kpMp[k]); }
+    return nmatches;
+  }
+#endif
   // gathers the Frame members of include/orbx.h's orbx_frame_view (descriptors are copied only if the Mat is not dense)
   struct FrameViewHolder {
     orbx_frame_view v;

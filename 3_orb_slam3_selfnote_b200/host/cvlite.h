@@ -9,6 +9,9 @@
 #include <memory>
 #include <vector>
 
+// element type code of an 8-bit single-channel matrix (OpenCV's CV_8U is a macro, so it cannot be spelled cvx::CV_8U)
+#define ORBX_MAT_8U 0
+
 #ifdef ORBX_WITH_OPENCV
 #include <opencv2/core/core.hpp>
 namespace cvx = cv;
@@ -27,7 +30,6 @@ struct KeyPoint {
 };
 static_assert(sizeof(KeyPoint) == 28, "cv::KeyPoint layout");
 
-enum { CV_8U = 0, CV_8UC1 = 0 };
 
 // 8-bit single channel matrix with shared ownership (the subset of cv::Mat the frontend touches)
 class Mat {
@@ -36,7 +38,7 @@ class Mat {
   size_t step = 0;
   uint8_t* data = nullptr;
   Mat() {}
-  Mat(int r, int c, int /*type*/) { create(r, c, CV_8U); }
+  Mat(int r, int c, int /*type*/) { create(r, c, ORBX_MAT_8U); }
   Mat(int r, int c, int /*type*/, void* ext, size_t step_) : rows(r), cols(c), step(step_), data((uint8_t*)ext) {}
   void create(int r, int c, int /*type*/) {
     if (r == rows && c == cols && buf_) return;
@@ -46,7 +48,7 @@ class Mat {
   }
   void release() { buf_.reset(); data = nullptr; rows = cols = 0; step = 0; }
   bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
-  int type() const { return CV_8UC1; }
+  int type() const { return ORBX_MAT_8U; }
   uint8_t* ptr(int r = 0) { return data + (size_t)r * step; }
   const uint8_t* ptr(int r = 0) const { return data + (size_t)r * step; }
   template <class T> T* ptr(int r = 0) { return reinterpret_cast<T*>(data + (size_t)r * step); }

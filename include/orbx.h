@@ -255,6 +255,60 @@ void orbx_vocabulary_destroy(orbx_vocabulary* v);
 int orbx_vocabulary_transform(orbx_matcher* m, const orbx_vocabulary* v, const uint8_t* desc, int n, int levelsup, int* word_id,
                               int* node_id, double* weight);
 
+/* ---- searches that start from 3-D map points and a pose: the projection prologue runs on the device ---------------------------
+ * ORBmatcher's Frame-Frame, Frame-KeyFrame, KeyFrame-Sim3, Fuse and SearchBySim3 entry points first transform every map point
+ * into the target camera, project it, test bounds / distance range / viewing angle and pick a search radius and octave window
+ * (src/ORBmatcher.cc:2068-2118, :2305-2342, :518-560, :1486-1525, :1844-1866), then run the window search.  orbx_projection
+ * selects the reference's variant of each step; the 3x3 pose algebra in front of the loops (Rcw, tcw, Ow, the Sim3 pieces) is
+ * done by the caller exactly as the reference's cv::Mat lines do (host/ORBmatcher.h has them).  Evaluation order and rounding
+ * follow the reference's float / double code; KannalaBrandt8's atan2f / PredictScale's logf are (float) of the double function. */
+typedef struct orbx_projection {
+  float R[9], t[3];      /* x_c = R * x_w + t (row-major; cv::gemm's small-matrix float path) */
+  float R2[9], t2[3];    /* chain != 0: x_c <- R2 * x_c + t2 (SearchBySim3: sR21 / t21 after R1w / t1w, :1845-1846) */
+  int chain;
+  float Ow[3];           /* camera centre (dist_mode 0) */
+  float fx, fy, cx, cy;
+  int camera_model;      /* ORBX_CAMERA_PINHOLE / ORBX_CAMERA_KB8 */
+  float kb[4];
+  int proj_mode;         /* 0: mpCamera->project(x_c); 1: u = fx * (x * invz) + cx (SearchBySim3 :1853-1858) */
+  float min_x, max_x, min_y, max_y;
+  int bounds_mode;       /* 0: Frame: u < min_x || u > max_x rejects (:2084-2087); 1: KeyFrame::IsInImage: min <= u < max */
+  int depth_mode;        /* 0: reject invz < 0 (:2077); 1: reject z < 0 (:524, :1488, :1848); 2: no test (:2310-2312) */
+  int invz_mode;         /* 0: invz = (float)(1.0 / z) (:2075, :1852); 1: invz = 1 / z in float (Fuse :1493) */
+  float bf;
+  int want_xr;           /* xr = u - bf * invz (:2158, :1503): the mvuRight check of the window search / the Fuse gate */
+  int range_mode;        /* 1: dist outside [0.8f * mfMinDistance, 1.2f * mfMaxDistance] rejects */
+  int dist_mode;         /* 0: dist = |x_w - Ow|; 1: dist = |x_c| (SearchBySim3 :1862) */
+  int normal_check;      /* 1: (x_w - Ow) . normal < 0.5 * dist rejects (:553, :1538) */
+  int level_mode;        /* 0: level = octave[i] (:2089); 1: MapPoint::PredictScale(dist) */
+  int window_mode;       /* octave window: 0 [l-1, l+1]; 1 [l, any) (bForward); 2 [0, l] (bBackward); 3 [l-1, l] (KeyFrame loops) */
+  float th;              /* radius = th * scale_factors[level] */
+  float log_scale_factor;
+  int n_scale_levels;
+} orbx_projection;
+typedef struct orbx_projection_points {
+  int n;
+  const float* world_pos;      /* n x 3: MapPoint::GetWorldPos() */
+  const float* normal;         /* n x 3 (normal_check) or NULL */
+  const float* max_distance;   /* RAW mfMaxDistance / mfMinDistance (range_mode, level_mode 1) or NULL */
+  const float* min_distance;
+  const int* octave;           /* level_mode 0: the source keypoint's octave */
+  const uint8_t* valid;        /* the point takes part at all (exists, !isBad, not an outlier, not already found ...) or NULL = all */
+  const uint8_t* desc;         /* n x 32: MapPoint::GetDescriptor() */
+} orbx_projection_points;
+typedef struct orbx_projection_debug {   /* optional host outputs of the prologue, n entries each (any may be NULL) */
+  uint8_t* valid; float* u; float* v; float* radius; int* level; float* xr;
+} orbx_projection_debug;
+/* The window search with sequential claiming and the rotation histogram (orbx_search_by_projection_window) behind the prologue:
+ * SearchByProjection(Frame&, const Frame&, th, bMono), (Frame&, KeyFrame*, set, th, ORBdist) and both (KeyFrame*, Scw, ...). */
+int orbx_search_projected_window(orbx_matcher* m, const orbx_frame_view* F, const orbx_projection* proj, const orbx_projection_points* pts,
+                                 const float* angle, const uint8_t* observed, int dist_th, int any_mp_blocks, int check_orientation,
+                                 int* kp_mp, int* nmatches, const orbx_projection_debug* dbg);
+/* The independent best-keypoint search (orbx_search_window_best) behind the prologue: Fuse x2 (gate != 0 for the first
+ * overload's chi-square test) and both passes of SearchBySim3. */
+int orbx_search_projected_best(orbx_matcher* m, const orbx_frame_view* F, const orbx_projection* proj, const orbx_projection_points* pts,
+                               int gate, const float* inv_level_sigma2, int* best_idx, int* best_dist, const orbx_projection_debug* dbg);
+
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize), src/ORBmatcher.cc:722-837.
  * prev_matched: F1->n x 2 floats (in/out), matches12: F1->n ints (out). */
 int orbx_search_for_initialization(orbx_matcher* m, const orbx_frame_view* F1, const orbx_frame_view* F2, float* prev_matched,

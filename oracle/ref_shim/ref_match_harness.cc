@@ -14,19 +14,26 @@
 #include <memory>
 #include <thread>
 
+#ifdef ORBX_SHIM_TWIN
+// The twin build (oracle/_ref/libshim_match.so): the SAME caller code, data model and stand-in cv:: header, but the ORBmatcher is
+// the product's drop-in (host/ORBmatcher.h -> liborbx.so, CUDA) instead of the reference's class.  tests/ run both libraries on
+// the same worlds and compare every observable output, which exercises the reference-signature overloads end to end.
+#define ORBX_WITH_OPENCV 1
+#include "host/ORBmatcher.h"
+#else
 #include "ORBextractor.h"
 #include "ORBmatcher.h"
+#endif
 #include "ref_alloc.h"
 
 namespace cvshim { extern thread_local int g_blur_taps; }
 
 namespace ORB_SLAM3 {
 // ---- bodies cut from the reference (oracle/Makefile: frame_slice.inc <- src/Frame.cc, keyframe_slice.inc <- src/KeyFrame.cc,
-// mappoint_slice.inc <- src/MapPoint.cc, camera_slice.inc <- src/CameraModels/{Pinhole,KannalaBrandt8}.cpp)
+// mappoint_slice.inc <- src/MapPoint.cc; the camera bodies are compiled in ref_camera.cc)
 #include "frame_slice.inc"
 #include "keyframe_slice.inc"
 #include "mappoint_slice.inc"
-#include "camera_slice.inc"
 }  // namespace ORB_SLAM3
 
 using namespace ORB_SLAM3;
@@ -428,6 +435,7 @@ int rm_search_by_sim3(const RefView* KF1, const RefView* KF2, const RefPoints* P
   return nm;
 }
 
+#ifndef ORBX_SHIM_TWIN   // the stereo frame entry points time / pin the reference only
 // Whole stereo frame as Frame::Frame(stereo) does the data-parallel part (src/Frame.cc:89-187): both extractions with the
 // reference's ORBextractor (vLappingArea {0,0}) and Frame::ComputeStereoMatches (src/Frame.cc:901-1079).
 // Outputs: keypoints / descriptors of both images (cap records each), uRight / depth (cap floats).
@@ -531,5 +539,7 @@ double rm_time_stereo(int nfeatures, float scaleFactor, int nlevels, int iniTh, 
   if (matched) *matched = tot;
   return std::chrono::duration<double>(t1 - t0).count();
 }
+
+#endif  // ORBX_SHIM_TWIN
 
 }  // extern "C"

@@ -32,7 +32,9 @@
 
 #include <opencv2/core/core.hpp>
 
+#ifndef SLAM_WORLD_NO_USING_STD
 using namespace std;   // the reference's headers rely on it (include/ORBmatcher.h:75 names `pair` / `vector` unqualified)
+#endif
 
 namespace DBoW2 {
 typedef unsigned int NodeId;
@@ -62,12 +64,19 @@ class GeometricCamera {
     fprintf(stderr, "oracle/_ref: matchAndtriangulate needs cv::SVD (KannalaBrandt8.cpp:249-341), not available in the stand-in\n");
     abort();
   }
+  // include/CameraModels/GeometricCamera.h:81-88
+  float getParameter(const int i) { return mvParameters[i]; }
+  size_t size() { return mvParameters.size(); }
+  unsigned int GetType() { return mnType; }
+  const unsigned int CAM_PINHOLE = 0;
+  const unsigned int CAM_FISHEYE = 1;
   std::vector<float> mvParameters;
+  unsigned int mnType = 0;
 };
 
 class Pinhole : public GeometricCamera {
  public:
-  explicit Pinhole(const std::vector<float>& p) : GeometricCamera(p) {}
+  explicit Pinhole(const std::vector<float>& p) : GeometricCamera(p) { mnType = CAM_PINHOLE; }
   cv::Point2f project(const cv::Point3f& p3D);   // body: src/CameraModels/Pinhole.cpp:46-49 (slice)
   cv::Point2f project(const cv::Mat& m3D);       // body: src/CameraModels/Pinhole.cpp:52-56 (slice)
   // Pinhole.cpp:143-165 with the fundamental matrix supplied by the harness (see the header comment): the line test itself.
@@ -88,7 +97,7 @@ class Pinhole : public GeometricCamera {
 
 class KannalaBrandt8 : public GeometricCamera {
  public:
-  explicit KannalaBrandt8(const std::vector<float>& p) : GeometricCamera(p) {}
+  explicit KannalaBrandt8(const std::vector<float>& p) : GeometricCamera(p) { mnType = CAM_FISHEYE; }
   cv::Point2f project(const cv::Point3f& p3D);   // body: src/CameraModels/KannalaBrandt8.cpp:29-45 (slice)
   cv::Point2f project(const cv::Mat& m3D);       // body: src/CameraModels/KannalaBrandt8.cpp:47-51 (slice)
   bool epipolarConstrain(GeometricCamera*, const cv::KeyPoint&, const cv::KeyPoint&, const cv::Mat&, const cv::Mat&, const float, const float) {
@@ -116,7 +125,7 @@ class MapPoint {
   int PredictScale(const float& currentDist, KeyFrame* pKF);   // body: src/MapPoint.cc:570-585 (slice)
   int PredictScale(const float& currentDist, Frame* pF);       // body: src/MapPoint.cc:587-602 (slice)
   bool IsInKeyFrame(KeyFrame* pKF) { return mObservations.count(pKF) != 0; }
-  tuple<int, int> GetIndexInKeyFrame(KeyFrame* pKF) { return mObservations.count(pKF) ? mObservations[pKF] : tuple<int, int>(-1, -1); }
+  std::tuple<int, int> GetIndexInKeyFrame(KeyFrame* pKF) { return mObservations.count(pKF) ? mObservations[pKF] : std::tuple<int, int>(-1, -1); }
   void Replace(MapPoint* pMP) { if (events) events->push_back(WorldEvent{0, this, pMP, nullptr, -1}); }
   void AddObservation(KeyFrame* pKF, int idx) { if (events) events->push_back(WorldEvent{1, this, nullptr, pKF, idx}); }
 
@@ -126,7 +135,7 @@ class MapPoint {
   cv::Mat mWorldPos, mNormalVector, mDescriptor;
   float mfMinDistance, mfMaxDistance;
   std::mutex mMutexPos;   // the sliced bodies lock it
-  std::map<KeyFrame*, tuple<int, int> > mObservations;
+  std::map<KeyFrame*, std::tuple<int, int> > mObservations;
   // tracking fields written by Frame::isInFrustum
   bool mbTrackInView, mbTrackInViewR;
   float mTrackProjX, mTrackProjY, mTrackDepth, mTrackDepthR, mTrackProjXR, mTrackProjYR;
@@ -182,7 +191,7 @@ class Frame {
   void UpdatePoseMatrices();                                                         // src/Frame.cc:533-539 (slice)
   void AssignFeaturesToGrid();                                                       // src/Frame.cc:434-465 (slice)
   bool PosInGrid(const cv::KeyPoint& kp, int& posX, int& posY);                      // src/Frame.cc:815-825 (slice)
-  vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r, const int minLevel = -1, const int maxLevel = -1,
+  std::vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r, const int minLevel = -1, const int maxLevel = -1,
                                    const bool bRight = false) const;                 // src/Frame.cc:744-813 (slice)
   bool isInFrustum(MapPoint* pMP, float viewingCosLimit);                            // src/Frame.cc:572-661 (slice)
   bool isInFrustumChecks(MapPoint* pMP, float viewingCosLimit, bool bRight = false); // src/Frame.cc:1270-1343 (slice)

@@ -14,7 +14,29 @@ from . import KP_DTYPE
 from . import ref as _ref
 
 _LIB = os.path.join(_ref._DIR, "libref_match.so")
+_TWIN = os.path.join(_ref._DIR, "libshim_match.so")
 _lib = None
+_twin = None
+_use_twin = False
+
+
+class twin:
+    """`with refmatch.twin():` routes the calls of this module to oracle/_ref/libshim_match.so -- the same harness compiled
+    against the product's host/ORBmatcher.h (liborbx.so, CUDA) instead of the reference's ORBmatcher.cc.  GPU tests only."""
+
+    def __enter__(self):
+        global _use_twin
+        self.prev = _use_twin
+        _use_twin = True
+        return self
+
+    def __exit__(self, *a):
+        global _use_twin
+        _use_twin = self.prev
+
+
+def twin_available():
+    return os.path.exists(_TWIN)
 
 
 def available():
@@ -24,7 +46,13 @@ def available():
 
 
 def lib():
-    global _lib
+    global _lib, _twin
+    if _use_twin:
+        if _twin is None:
+            if not twin_available():
+                raise RuntimeError("oracle/_ref/libshim_match.so missing: run `make -C oracle twin` in the build container")
+            _twin = C.CDLL(_TWIN)
+        return _twin
     if _lib is None:
         if not available():
             raise RuntimeError("oracle/_ref/libref_match.so missing: run `make -C oracle ref` in the build container")
@@ -234,8 +262,8 @@ def fuse_scw(kf, Scw, pts, candidates, th):
 def search_by_sim3(kf1, kf2, pts, matches12, s12, R12, t12, th):
     m = np.ascontiguousarray(matches12, np.int32).copy()
     R12 = np.ascontiguousarray(R12, np.float32); t12 = np.ascontiguousarray(t12, np.float32)
-    nm = lib().rm_search_by_sim3(_r(kf1), _r(kf2), _r(pts), m.ctypes.data_as(C.c_void_p), C.c_float(s12), C.c_void_p(_p(R12)), C.c_void_p(_p(t12)),
-                                 C.c_float(th), )
+    nm = lib().rm_search_by_sim3(_r(kf1), _r(kf2), _r(pts), C.c_float(s12), C.c_void_p(_p(R12)), C.c_void_p(_p(t12)),
+                                 C.c_float(th), m.ctypes.data_as(C.c_void_p))
     return nm, m
 
 

@@ -27,7 +27,7 @@ int main(int argc, char** argv) {
   pre.cvtColorToGray(bgr.data(), W, H, (size_t)W * 3, 3, /*bRGB=*/false, gray);
   const int id = pre.addRectifyMap(mx.data(), my.data(), W, H, W, W, H);
   pre.remap(gray, rect, id);
-  cvx::Mat eq(H, W, cvx::CV_8U);
+  cvx::Mat eq(H, W, ORBX_MAT_8U);
   for (int y = 0; y < H; ++y) memcpy(eq.ptr(y), rect.ptr(y), W);
   pre.clahe(eq);
   // keypoints on a lattice, EuRoC cam0 intrinsics / distortion (Examples/Monocular/EuRoC.yaml)

@@ -1,0 +1,160 @@
+"""The reference-signature overloads of host/ORBmatcher.h (pose algebra on the host in the reference's own cv::Mat lines, per-point
+projection prologue + search on the device) against the reference's OWN src/ORBmatcher.cc: oracle/_ref/libref_match.so and its twin
+oracle/_ref/libshim_match.so are the same harness -- same caller code, same Frame / KeyFrame / MapPoint model, same stand-in cv::
+-- linked once with the reference's ORBmatcher and once with the drop-in.  Every observable output must be identical."""
+import numpy as np
+import pytest
+
+import world_cases as wc
+from oracle import refmatch as rm
+
+pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not (rm.available() and rm.twin_available()), reason="oracle/_ref twin libraries not built")]
+
+
+def both(fn, *a, **k):
+    ref = fn(*a, **k)
+    with rm.twin():
+        got = fn(*a, **k)
+    return ref, got
+
+
+def same(ref, got, what):
+    assert len(ref) == len(got)
+    for i, (r, g) in enumerate(zip(ref, got)):
+        if isinstance(r, np.ndarray):
+            assert r.shape == g.shape and (r == g).all(), "%s: output %d differs at %s" % (what, i, np.nonzero(r != g)[0][:8])
+        else:
+            assert r == g, "%s: output %d: reference %r, drop-in %r" % (what, i, r, g)
+
+
+@pytest.fixture(scope="module", params=["euroc", "kb8"])
+def scene(request):
+    cam = wc.EUROC if request.param == "euroc" else wc.KB8
+    W = wc.World(seed=5 if request.param == "euroc" else 6, n_pts=1800, cam=cam, n_dup=200)
+    Ra, ta = W.pose(seed=10)
+    Rb, tb = W.pose(seed=11)
+    A, B = W.observe(Ra, ta, seed=20), W.observe(Rb, tb, seed=21)
+    return dict(W=W, A=A, B=B, pts=W.points(rm), Ra=Ra, ta=ta, Rb=Rb, tb=tb, name=request.param)
+
+
+@pytest.mark.parametrize("mono,th,dt,ori", [(True, 7.0, None, True), (False, 15.0, None, True), (False, 7.0, (0, 0, 0.6), True),
+                                            (False, 7.0, (0, 0, -0.6), False), (True, 2.0, None, False)])
+def test_search_by_projection_frame_frame(scene, mono, th, dt, ori):
+    """src/ORBmatcher.cc:2027-2289: plain / forward / backward windows (|tlc.z| > mb), stereo ur check, rotation histogram"""
+    W, A, B = scene["W"], scene["A"], scene["B"]
+    if dt is not None:   # move the current camera along its optical axis so that bForward / bBackward trigger
+        B = W.observe(scene["Rb"], scene["tb"] - np.array(dt), seed=23)
+    pre = np.where(np.random.default_rng(4).random(len(B["kps"])) < 0.1, B["assoc"], -1).astype(np.int32)
+    for assoc in (np.full(len(B["kps"]), -1, np.int32), pre):
+        cur = W.view(rm, B, assoc=assoc)
+        last = W.view(rm, A, assoc=A["assoc"], outlier=A["outlier"])
+        ref, got = both(rm.search_by_projection_frame, cur, last, scene["pts"], th, mono, 0.9, ori)
+        same(ref, got, "SearchByProjection(Frame, Frame)")
+        assert ref[0] > 50
+
+
+@pytest.mark.parametrize("th,orb_dist,ori", [(10.0, 100, True), (3.0, 64, True), (10.0, 100, False)])
+def test_search_by_projection_frame_keyframe(scene, th, orb_dist, ori):
+    """src/ORBmatcher.cc:2291-2413 (relocalisation)"""
+    W, A, B = scene["W"], scene["A"], scene["B"]
+    found = (np.random.default_rng(7).random(W.n) < 0.15).astype(np.uint8)
+    pre = np.where(np.random.default_rng(8).random(len(B["kps"])) < 0.2, B["assoc"], -1).astype(np.int32)
+    cur = W.view(rm, B, assoc=pre)
+    kf = W.view(rm, A, assoc=A["assoc"])
+    ref, got = both(rm.search_by_projection_keyframe, cur, kf, scene["pts"], found, th, orb_dist, 0.9, ori)
+    same(ref, got, "SearchByProjection(Frame, KeyFrame)")
+    assert ref[0] > 50
+
+
+@pytest.mark.parametrize("th,ratio,with_kfs,s", [(4, 1.0, False, 1.07), (8, 0.9, True, 0.93), (3, 0.5, False, 1.0)])
+def test_search_by_projection_scw(scene, th, ratio, with_kfs, s):
+    """src/ORBmatcher.cc:489-602 and :604-720 (loop detection / place recognition)"""
+    W, B = scene["W"], scene["B"]
+    Scw = B["Tcw"].copy()
+    Scw[:3, :] *= np.float32(s)
+    kf = W.view(rm, B, assoc=B["assoc"])
+    matched = np.where(np.random.default_rng(1).random(len(B["kps"])) < 0.2, B["assoc"], -1).astype(np.int32)
+    ref, got = both(rm.search_by_projection_scw, kf, Scw, scene["pts"], th, ratio, matched, with_kfs)
+    same(ref, got, "SearchByProjection(KeyFrame, Scw)")
+    assert ref[0] > 20
+
+
+@pytest.mark.parametrize("th", [3.0, 6.5])
+def test_fuse(scene, th):
+    """src/ORBmatcher.cc:1425-1662 (bRight = false): AddObservation / AddMapPoint and both Replace directions"""
+    if scene["name"] == "kb8":
+        pytest.skip("Fuse's stereo branch needs bf > 0; the mono branch is covered by the euroc world's non-stereo keypoints")
+    W, B = scene["W"], scene["B"]
+    kf = W.view(rm, B, assoc=B["assoc"])   # the world's duplicated points arrive as candidates: Replace in both directions
+    cand = np.random.default_rng(3).permutation(W.n).astype(np.int32)
+    ref, got = both(rm.fuse, kf, scene["pts"], cand, th)
+    same(ref, got, "Fuse")
+    ev = ref[1]
+    assert (ev[:, 0] == 0).sum() > 10 and (ev[:, 0] == 1).sum() > 50
+
+
+def test_fuse_mono_keyframe(scene):
+    """the same on a keyframe without stereo measurements (mvuRight all -1) and a fisheye camera model"""
+    W, B = scene["W"], dict(scene["B"])
+    B["u_right"] = np.full(len(B["kps"]), -1.0, np.float32)
+    kf = W.view(rm, B, assoc=B["assoc"])
+    cand = np.arange(W.n, dtype=np.int32)
+    ref, got = both(rm.fuse, kf, scene["pts"], cand, 3.0)
+    same(ref, got, "Fuse (mono)")
+    assert ref[0] > 50
+
+
+@pytest.mark.parametrize("th,s", [(4.0, 1.05), (7.5, 0.97)])
+def test_fuse_scw(scene, th, s):
+    """src/ORBmatcher.cc:1664-1786 (loop closing)"""
+    W, B = scene["W"], scene["B"]
+    Scw = B["Tcw"].copy()
+    Scw[:3, :] *= np.float32(s)
+    kf = W.view(rm, B, assoc=B["assoc"])
+    cand = np.random.default_rng(9).permutation(W.n).astype(np.int32)
+    ref, got = both(rm.fuse_scw, kf, Scw, scene["pts"], cand, th)
+    same(ref, got, "Fuse(Scw)")
+    assert ref[0] > 50 and (ref[1] >= 0).sum() > 10
+
+
+@pytest.mark.parametrize("th,s12", [(7.5, 1.0), (10.0, 1.04)])
+def test_search_by_sim3(scene, th, s12):
+    """src/ORBmatcher.cc:1788-2018: both projection passes and the agreement check"""
+    if scene["name"] == "kb8":
+        pytest.skip("SearchBySim3 projects with fx, fy, cx, cy only (pinhole), src/ORBmatcher.cc:1792-1795")
+    W, A, B = scene["W"], scene["A"], scene["B"]
+    Ra, ta, Rb, tb = scene["Ra"], scene["ta"], scene["Rb"], scene["tb"]
+    R12 = Ra @ Rb.T
+    t12 = ta - R12 @ tb
+    kf1 = W.view(rm, A, assoc=A["assoc"])
+    kf2 = W.view(rm, B, assoc=B["assoc"])
+    # some pairs already matched: keypoints of KF1 whose point is also held by KF2
+    in2 = set(B["assoc"][B["assoc"] >= 0].tolist())
+    rng = np.random.default_rng(2)
+    m12 = np.array([a if (a >= 0 and a in in2 and rng.random() < 0.3) else -1 for a in A["assoc"]], np.int32)
+    ref, got = both(rm.search_by_sim3, kf1, kf2, scene["pts"], m12, s12, R12, t12 * s12, th)
+    same(ref, got, "SearchBySim3")
+    assert ref[0] > 20
+
+
+def test_search_for_triangulation_reference_signature(scene):
+    """src/ORBmatcher.cc:981-1222 through the cv::Mat F12 parameter list (epipole projected by the shim)"""
+    if scene["name"] == "kb8":
+        pytest.skip("pinhole keyframes")
+    import bowsynth
+    W, A, B = scene["W"], scene["A"], scene["B"]
+    Ra, ta, Rb, tb = scene["Ra"], scene["ta"], scene["Rb"], scene["tb"]
+    fx, fy, cx, cy = W.cam["K"]
+    K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]])
+    R12 = Ra @ Rb.T
+    t12 = ta - R12 @ tb
+    tx = np.array([[0, -t12[2], t12[1]], [t12[2], 0, -t12[0]], [-t12[1], t12[0], 0]])
+    F12 = (np.linalg.inv(K).T @ tx @ R12 @ np.linalg.inv(K)).astype(np.float32)
+    fva = bowsynth.feature_vector(A["desc"], 24, seed=1)
+    fvb = bowsynth.feature_vector(B["desc"], 24, seed=1)
+    kf1 = W.view(rm, A, assoc=A["assoc"], feat_vec=fva)
+    kf2 = W.view(rm, B, assoc=B["assoc"], feat_vec=fvb)
+    for only_stereo, coarse in ((False, False), (True, False), (False, True)):
+        ref, got = both(rm.search_for_triangulation, kf1, kf2, scene["pts"], F12, only_stereo, coarse)
+        same(ref, got, "SearchForTriangulation")
+    assert ref[0] > 10
