@@ -172,13 +172,14 @@ class ORBmatcher {
   template <class KeyFrameT, class MapPointT>
   int SearchByProjection(KeyFrameT* pKF, cv::Mat Scw, const std::vector<MapPointT*>& vpPoints, std::vector<MapPointT*>& vpMatched, int th,
                          float ratioHamming = 1.0) {
-    return search_scw(pKF, Scw, vpPoints, vpMatched, th, ratioHamming, [](int, int) {});
+    return search_scw(pKF, Scw, vpPoints, vpMatched, th, ratioHamming, /*cameraProject=*/true, [](int, int) {});
   }
   // ... with the keyframe of every point (place recognition), src/ORBmatcher.cc:604-720.
   template <class KeyFrameT, class MapPointT>
   int SearchByProjection(KeyFrameT* pKF, cv::Mat Scw, const std::vector<MapPointT*>& vpPoints, const std::vector<KeyFrameT*>& vpPointsKFs,
                          std::vector<MapPointT*>& vpMatched, std::vector<KeyFrameT*>& vpMatchedKF, int th, float ratioHamming = 1.0) {
-    return search_scw(pKF, Scw, vpPoints, vpMatched, th, ratioHamming, [&](int k, int i) { vpMatchedKF[k] = vpPointsKFs[i]; });
+    // this overload projects with fx*(x/z)+cx whatever the camera model is (:646-652)
+    return search_scw(pKF, Scw, vpPoints, vpMatched, th, ratioHamming, /*cameraProject=*/false, [&](int k, int i) { vpMatchedKF[k] = vpPointsKFs[i]; });
   }
 
   // Project MapPoints into KeyFrame and search for duplicated MapPoints, src/ORBmatcher.cc:1425-1662 (bRight = false).
@@ -540,8 +541,10 @@ class ORBmatcher {
     orbx_shim::check(orbx_search_projected_window(m_, &fv.v, &P, &pts, A.angle.empty() ? nullptr : A.angle.data(), nullptr, distTh, anyMpBlocks ? 1 : 0,
                                                   checkOri ? 1 : 0, kpMp.data(), &nmatches, nullptr),
                      "orbx_search_projected_window");
-    for (int k = 0; k < F.N; k++)
+    for (int k = 0; k < F.N; k++) {
       if (kpMp[k] >= 0) assign(k, kpMp[k]);
+      else if (kpMp[k] == -1 && F.mvpMapPoints[k]) F.mvpMapPoints[k] = nullptr;   // a non-blocking point was re-matched, then dropped by the
+    }                                                                             // rotation histogram (:2270-2281 writes NULL)
     return nmatches;
   }
   template <class KeyFrameT>
@@ -555,7 +558,7 @@ class ORBmatcher {
   }
   template <class KeyFrameT, class MapPointT, class Extra>
   int search_scw(KeyFrameT* pKF, cv::Mat Scw, const std::vector<MapPointT*>& vpPoints, std::vector<MapPointT*>& vpMatched, int th, float ratioHamming,
-                 Extra extra) {
+                 bool cameraProject, Extra extra) {
     cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);   // :499-503 / :614-618, the reference's lines
     const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
     cv::Mat Rcw = sRcw / scw;
@@ -565,6 +568,7 @@ class ORBmatcher {
     keyframe_bounds(pKF, P);
     P.depth_mode = 1; P.range_mode = 1; P.normal_check = 1; P.level_mode = 1; P.window_mode = 3; P.th = (float)th;
     P.log_scale_factor = pKF->mfLogScaleFactor; P.n_scale_levels = pKF->mnScaleLevels;
+    if (!cameraProject) { P.proj_mode = 1; P.invz_mode = 1; P.fx = pKF->fx; P.fy = pKF->fy; P.cx = pKF->cx; P.cy = pKF->cy; }
     std::set<MapPointT*> spAlreadyFound(vpMatched.begin(), vpMatched.end());
     spAlreadyFound.erase(static_cast<MapPointT*>(nullptr));
     const int n = (int)vpPoints.size();

@@ -182,7 +182,10 @@ int orbx_search_by_projection_mappoints_batch(orbx_matcher* m, orbx_extractor* e
  * reference's loop prologue): valid[i] = point exists, is not an outlier / not already found, invzc >= 0 and projects
  * inside the image bounds; u,v = projection; level = nLastOctave / predicted level; ur = uv.x - mbf*invzc (read only when
  * F->u_right != NULL, may be NULL); angle = source keypoint angle.  Rotation-consistency filtering (30-bin histogram, three
- * maxima, src/ORBmatcher.cc:2416-2458) is applied when check_orientation != 0. */
+ * maxima, src/ORBmatcher.cc:2416-2458) is applied when check_orientation != 0.
+ * kp_mp (in/out): in -1 none / -2 blocking map point / -3 non-blocking map point; out >= 0 = index of the matched source
+ * point, -1 = NULL (also for a -3 entry that was re-matched and then dropped by the rotation histogram: the reference writes
+ * NULL there, :2270-2281), -2 / -3 = untouched. */
 int orbx_search_by_projection_window(orbx_matcher* m, const orbx_frame_view* F, int n, const uint8_t* valid, const float* u,
                                      const float* v, const int* level, const float* ur, const float* angle,
                                      const uint8_t* src_desc, const uint8_t* observed, float th, int mode, int dist_th,

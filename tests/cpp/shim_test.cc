@@ -61,7 +61,7 @@ int main(int argc, char** argv) {
   if (argc < 6) return 2;
   const int W = atoi(argv[3]), H = atoi(argv[4]);
   std::vector<uint8_t> l = read_raw(argv[1], (size_t)W * H), r = read_raw(argv[2], (size_t)W * H);
-  cvx::Mat imL(H, W, ORBX_MAT_8U, l.data(), W), imR(H, W, cvx::CV_8UC1, r.data(), W), mask;
+  cvx::Mat imL(H, W, ORBX_MAT_8U, l.data(), W), imR(H, W, ORBX_MAT_8U, r.data(), W), mask;
   FILE* out = fopen(argv[5], "wb");
   try {
     // --- mono extraction, Frame::ExtractORB(0, im, 0, 1000) (src/Frame.cc:339)
