@@ -1327,7 +1327,8 @@ int orbx_stereo_frames_host(orbx_matcher* m, orbx_extractor* exL, orbx_extractor
                             int capPerFrame) {
   if (!m || !exL || !exR) return ORBX_ERR_ARG;
   if (!imagesL || !imagesR || width <= 0 || height <= 0 || nframes <= 0) return ORBX_EMPTY_IMAGE;
-  if (!kpsL || !descL || !countsL || !kpsR || !descR || !countsR || !uRight || !depth || capPerFrame <= 0 || stride < width) return ORBX_ERR_ARG;
+  if (!kpsL || !descL || !countsL || !countsR || !uRight || !depth || capPerFrame <= 0 || stride < width) return ORBX_ERR_ARG;
+  if ((kpsR == nullptr) != (descR == nullptr)) return ORBX_ERR_ARG;   // the right image's records are downloaded together or not at all
   int rc = extractor_build_geom(exL, width, height);
   if (rc != ORBX_OK) return rc;
   rc = extractor_build_geom(exR, width, height);
@@ -1449,8 +1450,10 @@ int orbx_stereo_frames_host(orbx_matcher* m, orbx_extractor* exL, orbx_extractor
     for (int e = 0; e < 2; e++) {
       Slot& s = ex[e]->slot[si];
       CK(cudaMemcpyAsync(cd[e] + f0, s.counts, nb * sizeof(int), cudaMemcpyDeviceToHost, st));
-      if ((rc = download(kd[e] + (size_t)f0 * capPerFrame, s.kps, sizeof(orbx_keypoint))) != ORBX_OK) return rc;
-      if ((rc = download(dd[e] + (size_t)f0 * capPerFrame * 32, s.desc, 32)) != ORBX_OK) return rc;
+      if (kd[e]) {
+        if ((rc = download(kd[e] + (size_t)f0 * capPerFrame, s.kps, sizeof(orbx_keypoint))) != ORBX_OK) return rc;
+        if ((rc = download(dd[e] + (size_t)f0 * capPerFrame * 32, s.desc, 32)) != ORBX_OK) return rc;
+      }
       CK(cudaMemcpyAsync(s.hStatus, s.status, sizeof(int), cudaMemcpyDeviceToHost, st));
       CK(cudaMemcpyAsync(m->hStat + 2 * (chunk % orbx_matcher::kStatChunks) + e, s.status, sizeof(int), cudaMemcpyDeviceToHost, st));
     }

@@ -276,17 +276,20 @@ class ORBmatcher:
         self._stereo_shape = exL._last_shape
         self._stereo_cap = exL.max_keypoints(exL._last_shape[1], exL._last_shape[0])
 
-    def stereo_frames_host(self, exL, exR, left, right, mb, mbf):
-        """whole stereo frames from host arrays (n,h,w): -> dict(countsL, kpsL, descL, countsR, kpsR, descR, uRight, depth)"""
+    def stereo_frames_host(self, exL, exR, left, right, mb, mbf, right_records=True):
+        """whole stereo frames from host arrays (n,h,w): -> dict(countsL, kpsL, descL, countsR, kpsR, descR, uRight, depth);
+        right_records=False leaves the right image's keypoints / descriptors on the device (kpsR = descR = None)"""
         left = np.ascontiguousarray(left, np.uint8); right = np.ascontiguousarray(right, np.uint8)
         n, h, w = left.shape
         cap = exL.max_keypoints(w, h)
         o = dict(countsL=np.empty(n, np.int32), kpsL=np.empty((n, cap), KP_DTYPE), descL=np.empty((n, cap, 32), np.uint8),
-                 countsR=np.empty(n, np.int32), kpsR=np.empty((n, cap), KP_DTYPE), descR=np.empty((n, cap, 32), np.uint8),
+                 countsR=np.empty(n, np.int32), kpsR=np.empty((n, cap), KP_DTYPE) if right_records else None,
+                 descR=np.empty((n, cap, 32), np.uint8) if right_records else None,
                  uRight=np.empty((n, cap), np.float32), depth=np.empty((n, cap), np.float32))
+        pr = (lambda a: _p(a)) if right_records else (lambda a: None)
         _check(lib().orbx_stereo_frames_host(self._m, exL._h, exR._h, _p(left), _p(right), n, w, h, w, C.c_size_t(w * h), C.c_float(mb),
-                                             C.c_float(mbf), _p(o["kpsL"]), _p(o["descL"]), _p(o["countsL"]), _p(o["kpsR"]),
-                                             _p(o["descR"]), _p(o["countsR"]), _p(o["uRight"]), _p(o["depth"]), cap))
+                                             C.c_float(mbf), _p(o["kpsL"]), _p(o["descL"]), _p(o["countsL"]), pr(o["kpsR"]),
+                                             pr(o["descR"]), _p(o["countsR"]), _p(o["uRight"]), _p(o["depth"]), cap))
         exL._last_shape = exR._last_shape = (h, w)
         return o
 

@@ -43,7 +43,7 @@ W, H, NFEAT = 752, 480, 1200
 LEVEL_PIXELS = 1117367            # sum over the 8 levels
 MBF, FX = np.float32(47.90639384423901), np.float32(435.2046959714599)   # Examples/Stereo/EuRoC.yaml:9,28
 MB = np.float32(MBF / FX)
-METRIC = "frames/s ORB extract+match @752x480/1k feats"
+METRIC = "frames/s ORB extract+match @752x480 (EuRoC-shaped stereo pairs, 1200 feats/image)"
 WORKLOAD = "euroc_stereo_752x480_nfeat1200_extractLR+ComputeStereoMatches"
 
 
@@ -169,14 +169,32 @@ def cv2_primitive_times(synth, nframes=6):
             "ms_per_stereo_frame_lower_bound": 2 * sum(per_image.values())}
 
 
+def static_config():
+    """the workload description, IDENTICAL in both arms (the driver compares the two `config` objects)"""
+    return {"workload": WORKLOAD, "images_per_frame": 2, "width": W, "height": H, "nfeatures": NFEAT, "levels": 8, "scale": 1.2, "fast": [20, 7],
+            "frame": "one rectified stereo pair: ORBextractor on both images + Frame::ComputeStereoMatches",
+            "l2": "inputs larger than L2: every launch reads a batch of images + pyramids + blurred levels far above the 126 MB L2",
+            "sharding": "stereo frames partitioned by rank, no collective on the data path"}
+
+
 def cpu_stereo_sample(synth, nframes, threads, seed=12345):
-    """reference CPU path (oracle port) on `nframes` stereo frames with `threads` host threads -> (frames/s, seconds)"""
+    """the reference's CPU path on `nframes` stereo frames with `threads` host threads -> (frames/s, seconds, matched, kind).
+    kind "reference": the reference's OWN src/ORBextractor.cc + Frame::ComputeStereoMatches compiled unmodified (oracle/_ref,
+    prebuilt where /root/reference exists); kind "port": the oracle restatement when that library is absent."""
     import oracle
-    oracle.build()
+    from oracle import refmatch
     left = synth.frames(W, H, seed, range(nframes), False)
     right = synth.frames(W, H, seed, range(nframes), True)
+    if refmatch.available():
+        sec, matched = refmatch.time_stereo(left, right, threads, NFEAT, float(MB), float(MBF))
+        return nframes / sec, sec, matched, "reference"
+    oracle.build()
     sec, matched = oracle.time_stereo(left, right, threads, NFEAT, float(MB), float(MBF))
-    return nframes / sec, sec, matched
+    return nframes / sec, sec, matched, "port"
+
+
+CPU_NOTE = ("oracle/_ref: the reference's unmodified ORBextractor.cc + ComputeStereoMatches built -O3 -march=x86-64-v3 against stand-in cv:: "
+            "primitives (scalar restatements of OpenCV's resize / FAST / GaussianBlur, slower than OpenCV's SIMD: see cv2_primitives for the floor)")
 
 
 def run_reference(args):
@@ -185,21 +203,21 @@ def run_reference(args):
     synth = importlib.import_module("3_orb_slam3_selfnote_b200.synth")
     cores = os.cpu_count() or 1
     per_step = max(cores // 2, min(2 * cores, 128))
-    for _ in range(args.warmup):
+    kind = "port"
+    for _ in range(min(args.warmup, 2)):
         cpu_stereo_sample(synth, max(2, cores // 2), cores)
     total_sec, total_frames = 0.0, 0
-    for s in range(args.steps):
-        _, sec, _ = cpu_stereo_sample(synth, per_step, cores, seed=1000 + s)
+    for s_ in range(args.steps):
+        _, sec, _, kind = cpu_stereo_sample(synth, per_step, cores, seed=1000 + s_)
         total_sec += sec
         total_frames += per_step
     fps = total_frames / total_sec
     sample = "%d stereo frames per step x %d steps; frame-parallel, 2 threads per frame (Frame.cc:120-121), %d threads" % (per_step, args.steps, cores)
     line = {"metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * total_sec / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "u8", "data": "synthetic", "impl": "reference",
-            "config": {"workload": WORKLOAD, "frames_per_step": per_step, "images_per_frame": 2, "width": W, "height": H, "nfeatures": NFEAT,
-                       "note": "CPU oracle port of the reference path (the reference needs OpenCV 3.4 C++: unbuildable in this image)"},
-            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+            "dtype": "u8", "data": "synthetic", "impl": "reference", "config": static_config(),
+            "run": {"frames_per_step": per_step, "note": CPU_NOTE if kind == "reference" else "oracle port (oracle/_ref not built)"},
+            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -375,6 +393,107 @@ def _bind_to_gpu_numa_node(torch, local):
 
 
 STEREO_KERNELS = 4   # k_stereo_rowtable, k_stereo_hamming2, k_stereo_sad, k_stereo_median
+NCU_ISSUE = NCU_SUMMARY   # the same capture: smsp__inst_executed.sum per launch
+
+
+def _popc_roof_pairs_per_s():
+    """issue roof of the 256-bit Hamming pair: 8 POPC per pair on a pipe that retires 16 POPC/clk/SM (tools/microbench/popc_rate.cu
+    measures 15.0 of them on this pool's B200s with the loop overhead of the probe, profiles/r02_popc_rate.txt): 16 x 148 SMs x SM clock / 8"""
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            mhz = float(json.load(f).get("sm_max_mhz", 1965.0))
+    except Exception:
+        mhz = 1965.0
+    measured = None
+    try:
+        for ln in open(os.path.join(ROOT, "profiles", "r02_popc_rate.txt")):
+            if ln.startswith("pair: 8 x"):
+                measured = float(ln.split()[-2])
+    except Exception:
+        pass
+    return 16 * 148 * mhz * 1e6 / 8, measured
+
+
+def _ncu_issue(stage, images_per_launch, kernel_ms, sm_mhz):
+    """issue-slot utilisation of the stage's kernel: warp instructions per launch (smsp__inst_executed.sum of the committed ncu capture,
+    scaled to this launch's image count) / (4 schedulers x 148 SMs x cycles of the LIVE kernel duration)"""
+    import csv
+    try:
+        rows = list(csv.reader(open(NCU_ISSUE)))
+        hdr = rows[0]
+        ii = hdr.index("smsp__inst_executed.sum")
+        ib = hdr.index("images_per_launch") if "images_per_launch" in hdr else None
+        name = NCU_NAME.get(stage)
+        for r in rows[2:]:
+            if name and r[0].startswith(name):
+                per = float(r[ib]) if ib is not None else 128.0
+                inst = float(r[ii]) * images_per_launch / per
+                cyc = kernel_ms * 1e-3 * sm_mhz * 1e6
+                return {"warp_inst_per_launch": inst, "frac": inst / (cyc * 4 * 148), "source": os.path.relpath(NCU_ISSUE, ROOT)}
+    except Exception:
+        pass
+    return None
+
+
+def allpairs_block(orbx, torch, dist, mt, rank, world, local, kf_total, desc_per_kf, nchunks):
+    """BASELINE.json configs[4], CI variant of SURVEY.md 8-d: all-pairs keyframe-descriptor 2-NN over kf_total keyframes x desc_per_kf
+    descriptors sharded over the ranks; orbx_allpairs_knn2 (ncclAllGather chunks on a side stream + k_knn2 folds).  Timed once after a
+    small warm-up sweep; device time = max over ranks of the library's own event timing (first fold start .. last fold end)."""
+    ap = importlib.import_module("3_orb_slam3_selfnote_b200.allpairs")
+    mmod = importlib.import_module("3_orb_slam3_selfnote_b200.matcher")
+    kf_rank = kf_total // world
+    rows = kf_rank * desc_per_kf
+    g = torch.Generator(device="cuda")
+    g.manual_seed(777 + rank)
+    desc = torch.randint(0, 256, (rows, 32), dtype=torch.uint8, device="cuda", generator=g)
+    comm = mmod.nccl_comm_from_torch(local) if world > 1 else None
+    try:
+        ap.allpairs_knn2(desc[: 40 * desc_per_kf].contiguous(), desc_per_kf, matcher=mt, nchunks=2, comm=comm)     # warm-up (NCCL channels, kernels)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        idx, dst, st = ap.allpairs_knn2(desc, desc_per_kf, matcher=mt, nchunks=nchunks, comm=comm, return_stats=True)
+        wall = time.perf_counter() - t0
+    finally:
+        if comm is not None:
+            comm.close()
+    vals = torch.tensor([st["total_ms"], st["fold_ms"], st["gather_ms"], wall * 1e3], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(vals, op=dist.ReduceOp.MAX)
+    total_ms, fold_ms, gather_ms, wall_ms = [float(x) for x in vals.tolist()]
+    # spot check (outside the timed region): 16 of this rank's rows against a brute-force scan of ALL rows on the device
+    if world > 1:
+        allrows = torch.empty((world * rows, 32), dtype=torch.uint8, device="cuda")
+        dist.all_gather_into_tensor(allrows, desc)
+    else:
+        allrows = desc
+    lut = torch.tensor([bin(i).count("1") for i in range(256)], dtype=torch.int32, device="cuda")
+    ar = torch.arange(world * rows, device="cuda", dtype=torch.int64)
+    rng = np.random.default_rng(5 + rank)
+    for r in rng.integers(0, rows, 16).tolist():
+        gr = rank * rows + r
+        d = torch.zeros(world * rows, dtype=torch.int32, device="cuda")
+        for c0 in range(0, 32, 8):
+            d += lut[(allrows[:, c0:c0 + 8] ^ allrows[gr, c0:c0 + 8]).long()].sum(1, dtype=torch.int32)
+        kf0 = (gr // desc_per_kf) * desc_per_kf
+        key = (d.long() << 32) | ar
+        key[kf0:kf0 + desc_per_kf] = 1 << 62
+        top = torch.topk(key, 2, largest=False).values.cpu().numpy()
+        want_idx, want_d = top & 0xFFFFFFFF, top >> 32
+        if not (np.array_equal(idx[r], want_idx) and np.array_equal(dst[r], want_d)):
+            raise AssertionError("allpairs: row %d of rank %d: got %s / %s, brute force %s / %s" % (r, rank, idx[r], dst[r], want_idx, want_d))
+    total_pairs = float(world) * rows * (world * rows - desc_per_kf)
+    roof, roof_probe = _popc_roof_pairs_per_s()
+    return {"workload": "allpairs_knn2_%dkf_x_%ddesc" % (kf_total, desc_per_kf), "keyframes": kf_total, "desc_per_kf": desc_per_kf,
+            "comm_nranks_seen": int(st["world"]), "nchunks": int(st["nchunks"]), "pairs": total_pairs, "device_s": total_ms / 1e3, "wall_s": wall_ms / 1e3,
+            "pairs_per_s": total_pairs / (total_ms / 1e3), "pairs_per_s_per_gpu": total_pairs / world / (total_ms / 1e3),
+            "popc_roof_pairs_per_s_per_gpu": roof, "popc_roof_kind": "16 POPC/clk/SM x 148 SMs x max SM clock / 8 POPC per pair",
+            "popc_probe_pairs_per_s_per_gpu": roof_probe, "frac_of_popc_roof": total_pairs / world / (total_ms / 1e3) / roof,
+            "fold_ms": fold_ms, "allgather_ms": gather_ms, "allgather_bytes_per_rank": float(st["gather_bytes"]), "overlap_frac": float(st["overlap_frac"]),
+            "allgather_gbs_per_rank": (float(st["gather_bytes"]) / (gather_ms / 1e3) / 1e9) if gather_ms > 0 else None,
+            "limiter": "popc issue (k_knn2 fold)" if fold_ms >= gather_ms else "NVLink all-gather",
+            "verified": "16 rows per rank equal a brute-force scan of all rows (index and distance, ties to the lower global row)"}
 
 
 def run_orbx(args):
@@ -391,12 +510,14 @@ def run_orbx(args):
     affinity = _bind_to_gpu_numa_node(torch, local) if world > 1 else None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    B = args.batch
-    distinct = min(B, 32)   # distinct synthetic pairs per rank, tiled to B (generation is host-side numpy)
+    B, S = args.batch, args.substeps          # frames per launch, launches per step: a step is S*B stereo frames per GPU
+    POOL = 2                                  # distinct device-resident sub-batches the launches cycle through
+    distinct = min(B, 32)                     # distinct synthetic pairs per sub-batch, tiled to B (generation is host-side numpy)
     reps = (B + distinct - 1) // distinct
-    hostL = np.concatenate([synth.frames(W, H, 1000 + rank, range(distinct), False)] * reps)[:B]
-    hostR = np.concatenate([synth.frames(W, H, 1000 + rank, range(distinct), True)] * reps)[:B]
-    devL, devR = torch.from_numpy(hostL).cuda(), torch.from_numpy(hostR).cuda()
+    hostL = [np.concatenate([synth.frames(W, H, 1000 + 17 * rank + 7919 * p, range(distinct), False)] * reps)[:B] for p in range(POOL)]
+    hostR = [np.concatenate([synth.frames(W, H, 1000 + 17 * rank + 7919 * p, range(distinct), True)] * reps)[:B] for p in range(POOL)]
+    devL = [torch.from_numpy(x).cuda() for x in hostL]
+    devR = [torch.from_numpy(x).cuda() for x in hostR]
     exL = orbx.ORBextractor(NFEAT, max_batch=B, device=local)
     exR = orbx.ORBextractor(NFEAT, max_batch=B, device=local)
     mt = orbx.ORBmatcher(device=local)
@@ -410,14 +531,18 @@ def run_orbx(args):
     shR = streamR.cuda_stream
     evFork, evJoin = torch.cuda.Event(), torch.cuda.Event()
 
-    def step():
+    def launch(p):
         evFork.record(stream)
         streamR.wait_event(evFork)
-        exR.extract_batch_device(devR.data_ptr(), B, W, H, W, W * H, (0, 0), shR)
+        exR.extract_batch_device(devR[p].data_ptr(), B, W, H, W, W * H, (0, 0), shR)
         evJoin.record(streamR)
-        exL.extract_batch_device(devL.data_ptr(), B, W, H, W, W * H, (0, 0), sh)
+        exL.extract_batch_device(devL[p].data_ptr(), B, W, H, W, W * H, (0, 0), sh)
         stream.wait_event(evJoin)
         mt.stereo_match_batch(exL, exR, MB, MBF, sh)
+
+    def step():
+        for k in range(S):
+            launch(k % POOL)
 
     nwarm = max(args.warmup, 3)
     for _ in range(nwarm):
@@ -442,20 +567,22 @@ def run_orbx(args):
         dist.barrier()
         ms = float(t.item())
     clocks = sampler.stop() if rank == 0 else None
+    launch(0)                     # results of sub-batch 0 (what the e2e call below processes), outside the timed region
+    torch.cuda.synchronize()
     countsL, _, _, _ = exL.results_host(B)   # also checks the device status word
     countsR, _, _, _ = exR.results_host(B)
     uR, depth, _, _ = mt.stereo_results(B)
     kp_per_image = float((countsL.mean() + countsR.mean()) / 2)
     matched = float((uR >= 0).sum() / B)
-    value = world * B * args.steps / (ms / 1e3)
+    value = world * B * S * args.steps / (ms / 1e3)
 
     # per-stage device times (profiling pass, outside the timed region)
     exL.set_profiling(True)
     acc, stereo_ms = None, 0.0
     s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     for _ in range(3):
-        exL.extract_batch_device(devL.data_ptr(), B, W, H, W, W * H, (0, 0), sh)
-        exR.extract_batch_device(devR.data_ptr(), B, W, H, W, W * H, (0, 0), sh)
+        exL.extract_batch_device(devL[0].data_ptr(), B, W, H, W, W * H, (0, 0), sh)
+        exR.extract_batch_device(devR[0].data_ptr(), B, W, H, W, W * H, (0, 0), sh)
         s0.record(stream)
         mt.stereo_match_batch(exL, exR, MB, MBF, sh)
         s1.record(stream)
@@ -464,7 +591,7 @@ def run_orbx(args):
         st = exL.stage_times()
         acc = list(st) if acc is None else [(n, a + t) for (n, a), (_, t) in zip(acc, st)]
     exL.set_profiling(False)
-    stages = [(n, t / 3) for n, t in acc]          # one image's extractor stages (the step runs them twice)
+    stages = [(n, t / 3) for n, t in acc]          # one image's extractor stages (a launch runs them twice)
     algo = {"k_pyr_resize(x levels-1)": (LEVEL_PIXELS - 210 * 134) + (LEVEL_PIXELS - W * H),  # read levels 0..6, write levels 1..7
             "k_fast_nms": LEVEL_PIXELS, "k_blur7": 2 * LEVEL_PIXELS, "k_quadtree": 0, "k_assemble": 0,
             "k_orient_desc": int(kp_per_image * 60), "memset": 0}
@@ -472,13 +599,19 @@ def run_orbx(args):
     peak, peak_kind = _peaks()
     dom_bytes = algo.get(dom_name, 0) * B
     achieved = dom_bytes / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0
-    step_ms = 2 * sum(t for _, t in stages) + stereo_ms
+    launch_ms = 2 * sum(t for _, t in stages) + stereo_ms
     abf = algo_bytes_per_stereo_frame(kp_per_image)
-    roof = {"bound": "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
-            "frac": achieved / peak, "traffic": _ncu_traffic(dom_name, B), "traffic_source": os.path.relpath(NCU_SUMMARY, ROOT), "kernel_ms_per_launch": dom_ms, "launches_per_step": 2,
-            "kernel_share_of_step": 2 * dom_ms / step_ms, "algorithmic_bytes_per_launch": dom_bytes,
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    issue = _ncu_issue(dom_name, B, dom_ms, sm_mhz)
+    hbm_frac = achieved / peak
+    roof = {"bound": "issue" if (issue and issue["frac"] > hbm_frac) else "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak,
+            "peak_kind": peak_kind, "unit": "GB/s", "frac": hbm_frac, "issue": issue,
+            "traffic": _ncu_traffic(dom_name, B), "traffic_source": os.path.relpath(NCU_SUMMARY, ROOT), "kernel_ms_per_launch": dom_ms,
+            "launches_per_step": 2 * S, "kernel_share_of_step": 2 * dom_ms / launch_ms, "algorithmic_bytes_per_launch": dom_bytes,
             "whole_path": {"achieved": value / world * abf / 1e9, "frac": value / world * abf / 1e9 / peak, "bytes_per_frame": abf},
-            "stage_ms_per_image_batch": {n: round(t, 4) for n, t in stages}, "stereo_match_ms": round(stereo_ms, 4)}
+            "stage_ms_per_image_batch": {n: round(t, 4) for n, t in stages}, "stereo_match_ms": round(stereo_ms, 4),
+            "note": "bound = the larger of the HBM fraction (algorithmic bytes / live duration / measured copy peak) and the issue-slot "
+                    "fraction (ncu warp instructions / live cycles / 592 schedulers); this path is integer ALU work, not a streaming copy"}
 
     # end to end through the host-buffer C-ABI call: pinned images in; keypoints, descriptors, uRight, depth out
     cap = exL.max_keypoints(W, H)
@@ -486,48 +619,54 @@ def run_orbx(args):
     # host buffers of the e2e call come from orbx_host_alloc (cudaHostAlloc): torch's pin_memory() buffers upload at half the link rate here
     hb = lambda shape, dt: orbx.HostBuffer(shape, dt)
     hinL, hinR = hb((B, H, W), np.uint8), hb((B, H, W), np.uint8)
-    hinL.array[...] = hostL
-    hinR.array[...] = hostR
+    hinL.array[...] = hostL[0]
+    hinR.array[...] = hostR[0]
     vp = lambda t: t.ptr
+    right_records = not args.e2e_no_right
 
     class Worker:
         """one host thread of the application: its own extractor / matcher handles (handles are independent, include/orbx.h) and its
-        own output buffers; issues the synchronous host-buffer call for the steps it is given"""
+        own output buffers; issues the synchronous host-buffer call for the sub-batches it is given"""
 
         def __init__(self):
             self.eL = orbx.ORBextractor(NFEAT, max_batch=nb, device=local)
             self.eR = orbx.ORBextractor(NFEAT, max_batch=nb, device=local)
             self.em = orbx.ORBmatcher(device=local)
-            self.okL, self.okR = hb((B, cap, 28), np.uint8), hb((B, cap, 28), np.uint8)
-            self.odL, self.odR = hb((B, cap, 32), np.uint8), hb((B, cap, 32), np.uint8)
+            self.okL, self.odL = hb((B, cap, 28), np.uint8), hb((B, cap, 32), np.uint8)
+            self.okR = hb((B, cap, 28), np.uint8) if right_records else None
+            self.odR = hb((B, cap, 32), np.uint8) if right_records else None
             self.ocL, self.ocR = hb((B,), np.int32), hb((B,), np.int32)
             self.ouR, self.odp = hb((B, cap), np.float32), hb((B, cap), np.float32)
 
-        def step(self):
+        def call(self):
             rc = orbx.lib().orbx_stereo_frames_host(self.em._m, self.eL._h, self.eR._h, vp(hinL), vp(hinR), B, W, H, W, C.c_size_t(W * H),
-                                                    C.c_float(MB), C.c_float(MBF), vp(self.okL), vp(self.odL), vp(self.ocL), vp(self.okR),
-                                                    vp(self.odR), vp(self.ocR), vp(self.ouR), vp(self.odp), cap)
+                                                    C.c_float(MB), C.c_float(MBF), vp(self.okL), vp(self.odL), vp(self.ocL),
+                                                    vp(self.okR) if right_records else None, vp(self.odR) if right_records else None,
+                                                    vp(self.ocR), vp(self.ouR), vp(self.odp), cap)
             if rc != 0:
                 raise RuntimeError("orbx_stereo_frames_host failed: %d %s" % (rc, orbx.lib().orbx_last_error()))
 
-    nworkers = max(1, args.e2e_workers)
+        def buffers(self):
+            return [o for o in (self.eL, self.eR, self.em, self.okL, self.okR, self.odL, self.odR, self.ocL, self.ocR, self.ouR, self.odp) if o is not None]
+
+    nworkers = args.e2e_workers if args.e2e_workers > 0 else (2 if world < 4 else 1)   # 8 ranks x 2 copy-issuing threads oversubscribe the host
     workers = [Worker() for _ in range(nworkers)]
 
-    def run_steps(nsteps):
-        """nsteps calls in total, dealt round-robin to the workers; every call is the blocking C-ABI call (ctypes drops the GIL)"""
+    def run_calls(ncalls):
+        """ncalls blocking C-ABI calls in total, dealt to the workers (ctypes drops the GIL)"""
         if nworkers == 1:
-            for _ in range(nsteps):
-                workers[0].step()
+            for _ in range(ncalls):
+                workers[0].call()
             return
         errs = []
 
         def loop(w, k):
             try:
                 for _ in range(k):
-                    w.step()
+                    w.call()
             except Exception as e:   # noqa: BLE001
                 errs.append(e)
-        ths = [threading.Thread(target=loop, args=(w, nsteps // nworkers + (1 if i < nsteps % nworkers else 0))) for i, w in enumerate(workers)]
+        ths = [threading.Thread(target=loop, args=(w, ncalls // nworkers + (1 if i < ncalls % nworkers else 0))) for i, w in enumerate(workers)]
         for t in ths:
             t.start()
         for t in ths:
@@ -535,99 +674,167 @@ def run_orbx(args):
         if errs:
             raise errs[0]
 
-    run_steps(3 * nworkers)
+    run_calls(3 * nworkers)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
-    run_steps(args.steps)
+    run_calls(args.steps * S)                # a step = S calls of B frames: the same S*B frames per step as the device-resident arm
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     if world > 1:
         t = torch.tensor([e2e_s], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
-    ocL, ouR = workers[0].ocL, workers[0].ouR
-    # host<->device link speed on this box (the e2e ceiling: h2d bytes per step / link rate), pinned buffers, device timer
+    # host<->device link speed on this box (the e2e ceiling: h2d bytes per step / link rate), pinned buffers, device timer; measured alone
+    # on rank 0's turn and with ALL ranks copying at once (the ceiling the multi-GPU e2e number lives under)
     probe_d = torch.empty(64 << 20, dtype=torch.uint8, device="cuda")
     probe_h = orbx.HostBuffer((64 << 20,), np.uint8)
     probe_h.array[...] = 1
     rt = C.CDLL("libcudart.so.12")
-    link = {}
-    for name, (dst, src, kind) in {"h2d": (C.c_void_p(probe_d.data_ptr()), probe_h.ptr, 1), "d2h": (probe_h.ptr, C.c_void_p(probe_d.data_ptr()), 2)}.items():
+
+    def probe(kind):
+        dst, src = (C.c_void_p(probe_d.data_ptr()), probe_h.ptr) if kind == 1 else (probe_h.ptr, C.c_void_p(probe_d.data_ptr()))
         p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         rt.cudaMemcpyAsync(dst, src, C.c_size_t(64 << 20), C.c_int(kind), C.c_void_p(sh))
         torch.cuda.synchronize()
         p0.record(stream)
-        for _ in range(4):
+        for _ in range(8):
             rt.cudaMemcpyAsync(dst, src, C.c_size_t(64 << 20), C.c_int(kind), C.c_void_p(sh))
         p1.record(stream)
         torch.cuda.synchronize()
-        link[name] = 4 * (64 << 20) / (p0.elapsed_time(p1) / 1e3) / 1e9
+        return 8 * (64 << 20) / (p0.elapsed_time(p1) / 1e3) / 1e9
+
+    link = {}
+    for r in range(world):              # one rank at a time
+        if world > 1:
+            dist.barrier()
+        if r == rank:
+            link = {"h2d": probe(1), "d2h": probe(2)}
+    link_conc = None
+    if world > 1:
+        dist.barrier()
+        hc = probe(1)
+        dist.barrier()
+        dc = probe(2)
+        t = torch.tensor([hc, dc, link["h2d"], link["d2h"]], device="cuda", dtype=torch.float64)
+        tsum = t.clone()
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        tmin = t.clone()
+        dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
+        link_conc = {"h2d_sum_gbs": float(tsum[0]), "d2h_sum_gbs": float(tsum[1]), "h2d_min_rank_gbs": float(tmin[0]),
+                     "h2d_alone_sum_gbs": float(tsum[2]), "d2h_alone_sum_gbs": float(tsum[3])}
     del probe_d
     probe_h.close()
-    for wi, w in enumerate(workers):   # every worker's last call must equal the device-resident results
-        okc, oku = np.array_equal(w.ocL.array, countsL), np.array_equal(w.ouR.array[:, :8], uR[:, :8])
+    for wi, w in enumerate(workers):   # every worker's last call must equal the device-resident results, all of them
+        okc = np.array_equal(w.ocL.array, countsL) and np.array_equal(w.ocR.array, countsR)
+        oku = all(w.ouR.array[f, :countsL[f]].tobytes() == uR[f, :countsL[f]].tobytes() and
+                  w.odp.array[f, :countsL[f]].tobytes() == depth[f, :countsL[f]].tobytes() for f in range(B))
         if not (okc and oku):
             badc = np.nonzero(w.ocL.array != countsL)[0]
-            badu = np.nonzero((w.ouR.array[:, :8] != uR[:, :8]).any(axis=1))[0]
-            raise AssertionError("e2e and device-resident paths disagree: worker %d counts differ at frames %s (%s vs %s), uRight at frames %s"
-                                 % (wi, badc[:8].tolist(), w.ocL.array[badc[:4]].tolist(), countsL[badc[:4]].tolist(), badu[:8].tolist()))
-    e2e = {"value": world * B * args.steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": 2 * B * W * H,
-           "d2h_bytes_per_step": int(B * (2 * cap * 60 + cap * 8 + 8)), "timer": "host wall clock around all calls",
-           "api": "orbx_stereo_frames_host (blocking call; %d host thread(s), each with its own handles, take the steps in turn)" % nworkers,
-           "host_threads": nworkers, "chunks_per_call": args.e2e_chunks,
+            raise AssertionError("e2e and device-resident paths disagree: worker %d, counts differ at frames %s, uRight/depth equal: %s"
+                                 % (wi, badc[:8].tolist(), oku))
+    h2d_call = 2 * B * W * H
+    d2h_call = int(B * ((2 if right_records else 1) * cap * 60 + cap * 8 + 8))
+    e2e = {"value": world * B * S * args.steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": S * h2d_call, "d2h_bytes_per_step": S * d2h_call,
+           "timer": "host wall clock around all calls", "timed_region_s": e2e_s,
+           "api": "orbx_stereo_frames_host (blocking call of %d frames; a step = %d calls; %d host thread(s), each with its own handles, "
+                  "take the calls in turn)" % (B, S, nworkers),
+           "host_threads": nworkers, "chunks_per_call": args.e2e_chunks, "right_image_records_downloaded": right_records,
+           "verified": "counts, uRight and depth of every frame of every worker's last call equal the device-resident results",
            "link_gbs_measured": {k: round(v, 2) for k, v in link.items()},
-           "link_bound_frames_per_s": world * B / (2 * B * W * H / (link["h2d"] * 1e9))}
+           "link_bound_frames_per_s": world * B / (h2d_call / (link["h2d"] * 1e9)),
+           "link_concurrent": link_conc,
+           "link_bound_frames_per_s_concurrent": (link_conc["h2d_sum_gbs"] * 1e9 / (2 * W * H)) if link_conc else None}
 
-    # informational: mono extraction only at the shape the north-star target is quoted on (752x480, nFeatures 1000)
+    # informational: mono extraction only at the shape the north-star target is quoted on (752x480, nFeatures 1000), device-resident and
+    # end to end through orbx_extract_batch_host
     gm = orbx.ORBextractor(1000, max_batch=B, device=local)
     for _ in range(3):
-        gm.extract_batch_device(devL.data_ptr(), B, W, H, W, W * H, (0, 0), sh)
+        gm.extract_batch_device(devL[0].data_ptr(), B, W, H, W, W * H, (0, 0), sh)
     m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     m0.record(stream)
-    for _ in range(args.steps):
-        gm.extract_batch_device(devL.data_ptr(), B, W, H, W, W * H, (0, 0), sh)
+    nmono = max(args.steps, 10) * 4
+    for k in range(nmono):
+        gm.extract_batch_device(devL[k % POOL].data_ptr(), B, W, H, W, W * H, (0, 0), sh)
     m1.record(stream)
     torch.cuda.synchronize()
-    mono_fps = B * args.steps / (m0.elapsed_time(m1) / 1e3)
+    mono_fps = B * nmono / (m0.elapsed_time(m1) / 1e3)
+    gm.extract_batch_device(devL[0].data_ptr(), B, W, H, W, W * H, (0, 0), sh)
+    torch.cuda.synchronize()
+    mcount, _, mk, _ = gm.results_host(B)
+    gme = orbx.ORBextractor(1000, max_batch=nb, device=local)
+    mcap = gme.max_keypoints(W, H)
+    mok, mod_, moc, mom = hb((B, mcap, 28), np.uint8), hb((B, mcap, 32), np.uint8), hb((B,), np.int32), hb((B,), np.int32)
 
-    extras = {"mono_extract_752x480_nfeat1000_frames_per_s_per_gpu": mono_fps}
+    def mono_call():
+        rc = orbx.lib().orbx_extract_batch_host(gme._h, vp(hinL), B, W, H, W, C.c_size_t(W * H), 0, 0, vp(mok), vp(mod_), mcap, vp(moc), vp(mom))
+        if rc != 0:
+            raise RuntimeError("orbx_extract_batch_host failed: %d %s" % (rc, orbx.lib().orbx_last_error()))
+
+    for _ in range(3):
+        mono_call()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(nmono):
+        mono_call()
+    mono_e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([mono_e2e_s], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        mono_e2e_s = float(t.item())
+    if not np.array_equal(moc.array, mcount):
+        raise AssertionError("mono e2e and device-resident keypoint counts disagree")
+    mono = {"workload": "euroc_mono_752x480_nfeat1000_extract (configs[0] shape, the north-star target's shape)",
+            "value": world * mono_fps if world == 1 else None, "frames_per_s_per_gpu": mono_fps, "unit": "frames/s",
+            "e2e": {"value": world * B * nmono / mono_e2e_s, "unit": "frames/s", "api": "orbx_extract_batch_host, one host thread per rank",
+                    "h2d_bytes_per_call": B * W * H, "d2h_bytes_per_call": int(B * (mcap * 60 + 8)), "timed_region_s": mono_e2e_s},
+            "keypoints_per_image": float(mcount.mean())}
+    for o in (gme, mok, mod_, moc, mom):
+        o.close()
+
+    allpairs = None
+    if not args.no_allpairs:
+        allpairs = allpairs_block(orbx, torch, dist, mt, rank, world, local, args.allpairs_kf, 1000, args.allpairs_chunks)
+
+    extras = {"mono_extract_752x480_nfeat1000_frames_per_s_per_gpu": mono_fps, "mono_1000": mono}
     if rank == 0 and not args.no_extras:
         extras.update(extra_configs(orbx, synth, torch, stream, local, max(3, min(args.steps, 10))))
     if rank == 0:
         cores = os.cpu_count() or 1
         ncpu = max(cores, min(2 * cores, 128))
-        fps1, _, _ = cpu_stereo_sample(synth, 4, 2)
+        fps1, _, _, kind = cpu_stereo_sample(synth, 4, 2)
         secN, passes = 0.0, 0
         while secN < (0.0 if args.skip_cpu else 10.0) and passes < 40:   # bounded sample: ~10 s of CPU work on all host threads
-            _, s_, _ = cpu_stereo_sample(synth, ncpu, cores, seed=2000 + passes)
+            _, s_, _, kind = cpu_stereo_sample(synth, ncpu, cores, seed=2000 + passes)
             secN += s_
             passes += 1
         ncpu *= passes
         fpsN = ncpu / secN if secN > 0 else 0.0
-        cpu = {"value": fpsN, "unit": "frames/s", "cores": cores, "kind": "port",
+        cpu = {"value": fpsN, "unit": "frames/s", "cores": cores, "kind": kind,
                "sample": "%d stereo frames of the workload, frame-parallel with 2 threads per frame, %d threads (%.1f s); one frame at a time "
-                         "(2 threads): %.1f frames/s" % (ncpu, cores, secN, fps1), "two_thread_value": fps1}
+                         "(2 threads): %.1f frames/s" % (ncpu, cores, secN, fps1), "two_thread_value": fps1,
+               "note": CPU_NOTE if kind == "reference" else "oracle port (oracle/_ref not built)"}
         if not args.skip_cpu:
-            cpu["cv2_primitives"] = cv2_primitive_times(synth)
-        launches = (2 * exL.launches_per_batch() + STEREO_KERNELS) * args.steps * world
+            cv = cv2_primitive_times(synth)
+            cpu["cv2_primitives"] = cv
+            if cv:   # what a SIMD OpenCV build could at best reach on this host if only those primitives cost anything
+                cpu["cv2_primitive_floor_frames_per_s_all_cores"] = cores / (cv["ms_per_stereo_frame_lower_bound"] / 1e3)
+        launches = (2 * exL.launches_per_batch() + STEREO_KERNELS) * S * args.steps * world
         line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": nwarm,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
-                "data": "synthetic",
-                "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "images_per_frame": 2, "images_per_s": 2 * value, "width": W,
-                           "height": H, "nfeatures": NFEAT, "levels": 8, "scale": 1.2, "fast": [20, 7], "keypoints_per_image": kp_per_image,
-                           "stereo_matches_per_frame": matched,
-                           "l2": "per-step working set (%.0f MB of images + pyramids + blurred levels per GPU) exceeds the 126 MB L2"
-                                 % (2 * B * (W * H + 2 * LEVEL_PIXELS) / 1e6),
-                           "sharding": "stereo frames partitioned by rank, no collective on the data path",
-                           "cpu_affinity": affinity},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
+                "data": "synthetic", "config": static_config(),
+                "run": {"frames_per_step_per_gpu": B * S, "frames_per_launch": B, "launches_per_step": S, "timed_region_s": ms / 1e3,
+                        "frames_timed_per_gpu": B * S * args.steps, "images_per_s": 2 * value, "keypoints_per_image": kp_per_image,
+                        "stereo_matches_per_frame": matched, "device_pool_subbatches": POOL,
+                        "working_set_mb_per_launch": 2 * B * (W * H + 2 * LEVEL_PIXELS) / 1e6, "cpu_affinity": affinity},
+                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu, "allpairs": allpairs,
                 "extra": extras}
         print(json.dumps(line), flush=True)
     for w in workers:
-        for o in (w.eL, w.eR, w.em, w.okL, w.okR, w.odL, w.odR, w.ocL, w.ocR, w.ouR, w.odp):
+        for o in w.buffers():
             o.close()
     for o in [exL, exR, mt, gm, hinL, hinR]:
         o.close()
@@ -641,9 +848,14 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="orbx", choices=["orbx", "reference"])
-    ap.add_argument("--batch", type=int, default=256, help="stereo frames per step per GPU")
+    ap.add_argument("--batch", type=int, default=256, help="stereo frames per launch per GPU")
+    ap.add_argument("--substeps", type=int, default=32, help="launches per step: a step is substeps*batch stereo frames per GPU")
     ap.add_argument("--e2e-chunks", type=int, default=4, help="chunks per orbx_stereo_frames_host call (copy/compute overlap)")
-    ap.add_argument("--e2e-workers", type=int, default=2, help="host threads issuing the blocking e2e call on their own handles")
+    ap.add_argument("--e2e-workers", type=int, default=0, help="host threads issuing the blocking e2e call on their own handles (0 = 2, or 1 from 4 ranks up)")
+    ap.add_argument("--e2e-no-right", action="store_true", help="leave the right image's keypoints/descriptors on the device (rectified stereo needs only uRight/depth)")
+    ap.add_argument("--allpairs-kf", type=int, default=2000, help="keyframes of the all-pairs sweep (x 1000 descriptors), sharded over the ranks")
+    ap.add_argument("--allpairs-chunks", type=int, default=8)
+    ap.add_argument("--no-allpairs", action="store_true", help="skip the all-pairs keyframe 2-NN sweep (configs[4])")
     ap.add_argument("--no-extras", action="store_true", help="skip the informational runs of BASELINE.json configs 2-4")
     ap.add_argument("--skip-cpu", action="store_true", help="development only: skip the cpu_baseline leg")
     args = ap.parse_args()

@@ -361,7 +361,10 @@ int orbx_stereo_match_batch(orbx_matcher* m, orbx_extractor* left, orbx_extracto
 int orbx_stereo_results_device(orbx_matcher* m, const float** d_u_right, const float** d_depth, int* stride);
 /* Whole stereo frames from HOST buffers (the data-parallel part of Frame::Frame(stereo), src/Frame.cc:89-187): for each of
  * `nframes` rectified pairs, both extractions (vLappingArea {0,0}, Frame.cc:120-121) and ComputeStereoMatches; uploads,
- * kernels and downloads are chunked by max_batch and double-buffered.  Outputs per frame f at index f*capacity_per_frame. */
+ * kernels and downloads are chunked by max_batch and double-buffered.  Outputs per frame f at index f*capacity_per_frame.
+ * keypoints_right and descriptors_right may both be NULL: the right image's records then stay on the device (counts_right is
+ * still written).  After ComputeStereoMatches a RECTIFIED stereo Frame only reads mvuRight / mvDepth of the right image
+ * (src/Frame.cc:141-187); mvKeysRight / mDescriptorsRight are consumed later only by fisheye rigs (Nleft != -1). */
 int orbx_stereo_frames_host(orbx_matcher* m, orbx_extractor* left, orbx_extractor* right, const uint8_t* images_left,
                             const uint8_t* images_right, int nframes, int width, int height, int stride, size_t frame_stride,
                             float mb, float mbf, orbx_keypoint* keypoints_left, uint8_t* descriptors_left, int* counts_left,

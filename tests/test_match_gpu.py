@@ -236,6 +236,53 @@ def test_stereo_frames_host_pipeline(orbx, oracle, synth):
         assert o["kpsL"][f, :cl].tobytes() == kl.tobytes() and o["kpsR"][f, :cr].tobytes() == kr.tobytes()
         assert np.array_equal(o["descL"][f, :cl], dl) and np.array_equal(o["descR"][f, :cr], dr)
         assert o["uRight"][f, :cl].tobytes() == uo.tobytes() and o["depth"][f, :cl].tobytes() == do.tobytes()
+    # the right image's records are optional (rectified stereo reads only mvuRight / mvDepth afterwards): same left outputs
+    o2 = m.stereo_frames_host(gl, gr, left, right, mb, mbf, right_records=False)
+    assert o2["kpsR"] is None and np.array_equal(o2["countsR"], o["countsR"]) and np.array_equal(o2["countsL"], o["countsL"])
+    for f in range(n):
+        cl = int(o["countsL"][f])
+        assert o2["kpsL"][f, :cl].tobytes() == o["kpsL"][f, :cl].tobytes() and o2["uRight"][f, :cl].tobytes() == o["uRight"][f, :cl].tobytes()
+        assert o2["depth"][f, :cl].tobytes() == o["depth"][f, :cl].tobytes()
+    gl.close(); gr.close(); m.close()
+
+
+def test_batch256_matches_oracle(orbx, oracle, synth):
+    """parity at the bench's own scale: ONE 256-frame extract_batch_device per image side + one stereo_match_batch launch; 8 sampled
+    frames against the oracle and, where built, against the reference's own source (oracle/_ref)"""
+    import torch
+    from oracle import refmatch
+    B = 256
+    distinct = 32
+    left = np.concatenate([synth.frames(W, H, 1000, range(distinct), False)] * (B // distinct))
+    right = np.concatenate([synth.frames(W, H, 1000, range(distinct), True)] * (B // distinct))
+    dl_, dr_ = torch.from_numpy(left).cuda(), torch.from_numpy(right).cuda()
+    gl = orbx.ORBextractor(1200, max_batch=B); gr = orbx.ORBextractor(1200, max_batch=B)
+    m = orbx.ORBmatcher()
+    mbf = np.float32(47.90639384423901); mb = np.float32(mbf / np.float32(435.2046959714599))
+    st = torch.cuda.current_stream().cuda_stream
+    gl.extract_batch_device(dl_.data_ptr(), B, W, H, W, W * H, (0, 0), st)
+    gr.extract_batch_device(dr_.data_ptr(), B, W, H, W, W * H, (0, 0), st)
+    m.stereo_match_batch(gl, gr, mb, mbf, st)
+    torch.cuda.synchronize()
+    cL, _, kL, dL = gl.results_host(B)
+    cR, _, kR, dR = gr.results_host(B)
+    uR, depth, _, _ = m.stereo_results(B)
+    exL = oracle.Extractor(1200, sincos_mode=oracle.SINCOS_PORTABLE); exR = oracle.Extractor(1200, sincos_mode=oracle.SINCOS_PORTABLE)
+    ref = refmatch.StereoFrames(1200) if refmatch.available() else None
+    for f in (0, 1, 31, 32, 100, 177, 254, 255):
+        _, kl, dl = exL(left[f], (0, 0)); _, kr, dr = exR(right[f], (0, 0))
+        uo, do, _, _ = oracle.stereo_matches(exL, exR, kl, dl, kr, dr, mb, mbf)
+        cl, cr = int(cL[f]), int(cR[f])
+        assert cl == len(kl) and cr == len(kr)
+        assert kL[f, :cl].tobytes() == kl.tobytes() and kR[f, :cr].tobytes() == kr.tobytes()
+        assert np.array_equal(dL[f, :cl], dl) and np.array_equal(dR[f, :cr], dr)
+        assert uR[f, :cl].tobytes() == uo.tobytes() and depth[f, :cl].tobytes() == do.tobytes()
+        if ref is not None and f in (0, 100, 255):
+            r = ref(left[f], right[f], float(mb), float(mbf))
+            assert r["kpsL"].tobytes() == kl.tobytes() and r["uRight"].tobytes() == uo.tobytes() and r["depth"].tobytes() == do.tobytes()
+    # frames that repeat an image must repeat its result (32 distinct pairs tiled 8 times)
+    for f in range(distinct, B):
+        assert cL[f] == cL[f % distinct] and uR[f, :cL[f]].tobytes() == uR[f % distinct, :cL[f]].tobytes()
     gl.close(); gr.close(); m.close()
 
 
