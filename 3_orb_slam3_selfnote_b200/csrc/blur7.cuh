@@ -31,25 +31,30 @@ __device__ __forceinline__ int bv_refl(int i, int n) {
   return max(0, min(n - 1, i));  // (twice-reflected only on degenerate tiny levels)
 }
 
-// one source row of the column pass: the lane's 4 pixels (columns gx .. gx+3, reflected at the level's left / right edge)
+// one source row of the column pass: the lane's 4 pixels (columns gx .. gx+3, reflected at the level's left / right edge).
+// pa = src + gx (inner lanes) or src + wb (edge lanes), pb = src + wb2; off = byte offset of the row
 template <bool EDGE>
-__device__ __forceinline__ uint32_t bv_load(const uint8_t* row, int gx, int wb, int wb2, uint32_t sel) {
-  if (!EDGE) return __ldg(reinterpret_cast<const uint32_t*>(row + gx));
+__device__ __forceinline__ uint32_t bv_load(const uint8_t* pa, const uint8_t* pb, unsigned long long off, uint32_t sel) {
+  if (!EDGE) return __ldg(reinterpret_cast<const uint32_t*>(pa + off));
   // reflected columns are 4 consecutive ones in reverse order: they lie in two adjacent aligned words, picked apart by PRMT
-  return __byte_perm(__ldg(reinterpret_cast<const uint32_t*>(row + wb)), __ldg(reinterpret_cast<const uint32_t*>(row + wb2)), sel);
+  return __byte_perm(__ldg(reinterpret_cast<const uint32_t*>(pa + off)), __ldg(reinterpret_cast<const uint32_t*>(pb + off)), sel);
 }
 
 template <bool EDGE>
 __device__ __forceinline__ void bv_column_pass(const Geom& g, const uint8_t* src, int sp, int h, int ys, int gx, int wb, int wb2, uint32_t sel,
                                                uint32_t* dst /* &sV[(warp * kBvR) * 64 + 2 * lane] */) {
   uint32_t w[kBvR + 6];
+  const uint8_t* pa = src + (EDGE ? wb : gx);
+  const uint8_t* pb = src + wb2;
+  asm volatile("" : "+l"(pa));   // whole per-thread pointers in registers: one IMAD.WIDE per row instead of re-adding the uniform base
+  if (EDGE) asm volatile("" : "+l"(pb));
+  const unsigned usp = (unsigned)sp;
   if (ys >= 3 && ys + kBvR + 2 < h) {   // warp-uniform: no row reflection needed
-    const uint8_t* row = src + (long long)(ys - 3) * sp;
 #pragma unroll
-    for (int i = 0; i < kBvR + 6; i++) { w[i] = bv_load<EDGE>(row, gx, wb, wb2, sel); row += sp; }
+    for (int i = 0; i < kBvR + 6; i++) w[i] = bv_load<EDGE>(pa, pb, (unsigned long long)(unsigned)(ys - 3 + i) * usp, sel);
   } else {
 #pragma unroll
-    for (int i = 0; i < kBvR + 6; i++) w[i] = bv_load<EDGE>(src + (long long)bv_refl(ys - 3 + i, h) * sp, gx, wb, wb2, sel);
+    for (int i = 0; i < kBvR + 6; i++) w[i] = bv_load<EDGE>(pa, pb, (unsigned long long)(unsigned)bv_refl(ys - 3 + i, h) * usp, sel);
   }
   const uint32_t t[7] = {(uint32_t)g.taps[0], (uint32_t)g.taps[1], (uint32_t)g.taps[2], (uint32_t)g.taps[3], (uint32_t)g.taps[4],
                          (uint32_t)g.taps[5], (uint32_t)g.taps[6]};
@@ -110,6 +115,8 @@ __global__ void __launch_bounds__(256) k_blur7v(const __grid_constant__ Geom g, 
       const uint32_t Tc = t0 | (t1 << 8) | (t2 << 16) | (t3 << 24);          // (t0, t1 | t2, t3)
       const uint32_t Td = t4 | (t5 << 8) | (t6 << 16);                       // (t4, t5 | t6,  0)
       uint8_t* dst = b.blur + (long long)f * b.blurFrameStride + L.blurOff + x;
+      asm volatile("" : "+l"(dst));   // keep the per-thread base whole in registers (else its uniform part is re-added per row)
+      const unsigned ubp = (unsigned)L.blurPitch;
 #pragma unroll
       for (int i = 0; i < kBvR; i++) {
         const int r = warp + 8 * i, y = y0 + r;
@@ -122,10 +129,10 @@ __global__ void __launch_bounds__(256) k_blur7v(const __grid_constant__ Geom g, 
         a1 = __dp2a_lo(w1, Tc, a1); a1 = __dp2a_hi(w2, Tc, a1); a1 = __dp2a_lo(w3, Td, a1); a1 = __dp2a_hi(w4, Td, a1);
         a2 = __dp2a_lo(w1, Ta, a2); a2 = __dp2a_hi(w2, Ta, a2); a2 = __dp2a_lo(w3, Tb, a2); a2 = __dp2a_hi(w4, Tb, a2);
         a3 = __dp2a_lo(w2, Tc, a3); a3 = __dp2a_hi(w3, Tc, a3); a3 = __dp2a_lo(w4, Td, a3); a3 = __dp2a_hi(w5, Td, a3);
-        // saturate_cast<uchar>: the OCV346 taps sum to 257, so a bright patch reaches 257.5 in Q16.16 (a >= 2^24)
-        a0 = min(a0, 0x00FFFFFFu); a1 = min(a1, 0x00FFFFFFu); a2 = min(a2, 0x00FFFFFFu); a3 = min(a3, 0x00FFFFFFu);
-        const uint32_t o01 = __byte_perm(a0, a1, 0x0062), o23 = __byte_perm(a2, a3, 0x0062);   // bits 16..23 of each sum
-        *reinterpret_cast<uint32_t*>(dst + (long long)y * L.blurPitch) = __byte_perm(o01, o23, 0x5410);
+        // saturate_cast<uchar>: the OCV346 taps sum to 257, so a bright patch reaches 257.5 in Q16.16 (a >> 16 <= 257): the
+        // upper halves of two sums are clamped together as a u16 pair
+        const uint32_t o01 = __vminu2(__byte_perm(a0, a1, 0x7632), 0x00ff00ffu), o23 = __vminu2(__byte_perm(a2, a3, 0x7632), 0x00ff00ffu);
+        *reinterpret_cast<uint32_t*>(dst + (unsigned long long)(unsigned)y * ubp) = __byte_perm(o01, o23, 0x6420);
       }
     }
   }

@@ -4,7 +4,7 @@
 // No tensor cores: nothing here is a dense floating-point contraction.
 //
 // Reference stages (wangyunpeng139/3_ORB_SLAM3_SelfNote) and the file that holds each kernel:
-//   k_pyr_resize3  ORBextractor::ComputePyramid            src/ORBextractor.cc:1186-1219  (cv::resize INTER_LINEAR 8U)   pyr_resize.cuh
+//   k_pyr_resize4  ORBextractor::ComputePyramid            src/ORBextractor.cc:1186-1219  (cv::resize INTER_LINEAR 8U)   pyr_resize.cuh
 //   k_fast_nms3    ComputeKeyPointsOctTree cell loop        src/ORBextractor.cc:787-854   (cv::FAST 9/16 + NMS per cell)  fast_nms3.cuh
 //   k_quadtree     DistributeOctTree / DivideNode           src/ORBextractor.cc:479-761                                   this file
 //   k_blur7v       GaussianBlur(7x7, 2, REFLECT_101)        src/ORBextractor.cc:1132-1141                                 blur7.cuh

@@ -190,7 +190,7 @@ int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
         e.b1 = (int16_t)std::min(32767, std::max(-32768, cv_round_f(fy * 2048.f)));
         rsy.push_back(e);
       }
-      // k_pyr_resize3 covers the taps of 4 adjacent destination columns with 8 source bytes
+      // k_pyr_resize4 covers the taps of 4 adjacent destination columns with 8 source bytes
       for (int x0 = 0; x0 < wpad; x0 += 4)
         if (rsx[L.rsxOff + x0 + 3].s1 - rsx[L.rsxOff + x0].s0 > 7 || (L.rsxOff & 1)) h->rs3ok = false;
       // staged source window of k_pyr_resize2: maxima over the level's tiles
@@ -242,7 +242,7 @@ int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
   const size_t B = (size_t)h->p.max_batch;
   for (Slot& s : h->slot) {
     CK(cudaMalloc(&s.in, B * h->inPitch * height));
-    CK(cudaMalloc(&s.pyr, B * h->pyrFrame));
+    CK(cudaMalloc(&s.pyr, B * h->pyrFrame + 64));   // + slack: k_pyr_resize4 reads up to 11 bytes past a row's last tap
     CK(cudaMalloc(&s.blur, B * h->blurFrame));
     CK(cudaMalloc(&s.cand, B * g.candSlab * sizeof(PreCand)));
     s.zeroBytes = (B * ORBX_MAX_LEVELS + B * g.nCellsTotal + 16) * sizeof(int);
@@ -297,8 +297,9 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
   for (int l = 1; l < g.nlevels; l++) {
     const LevelGeom& L = g.lv[l];
     if (h->rs3ok) {
-      dim3 grid((L.w + kRs3TileW - 1) / kRs3TileW, (L.h + kRs3TileH - 1) / kRs3TileH, nframes);
-      k_pyr_resize3<<<grid, 256, 0, st>>>(gg, b, l);
+      dim3 grid((L.w + kRs4TileW - 1) / kRs4TileW, (L.h + 8 * kRs4Rows - 1) / (8 * kRs4Rows), nframes);
+      if (l == 1) k_pyr_resize4<true><<<grid, 256, 0, st>>>(gg, b, l);     // source = the caller's image: no bytes may be read past its rows
+      else k_pyr_resize4<false><<<grid, 256, 0, st>>>(gg, b, l);
     } else {   // scale factor > 2: a 4-column group spans more than 8 source bytes -> staged-window kernel
       dim3 grid((L.w + kRsTileW - 1) / kRsTileW, (L.h + kRsTileH - 1) / kRsTileH, nframes);
       k_pyr_resize2<<<grid, 256, h->rsSmem, st>>>(gg, b, l);

@@ -63,7 +63,7 @@ struct orbx_extractor {
   Slot slot[2];
   int lastSlot = 0;
   bool profile = false;
-  bool rs3ok = true;     // k_pyr_resize3 applies to this geometry (scale factor <= 2); otherwise k_pyr_resize2
+  bool rs3ok = true;     // k_pyr_resize4 applies to this geometry (scale factor <= 2); otherwise k_pyr_resize2
   size_t rsSmem = 0;
 };
 

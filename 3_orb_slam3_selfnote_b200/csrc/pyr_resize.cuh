@@ -83,10 +83,9 @@ __global__ void __launch_bounds__(256) k_pyr_resize2(const __grid_constant__ Geo
 
 
 // ---------------------------------------------------------------------------------------------------------------------------
-// k_pyr_resize3 -- register-resident version (profiles/r01c: k_pyr_resize2 executed ~70 thread-instructions per destination
-// pixel, issue-bound at 82 %: partially filled staging loops, one shared-memory round trip for the horizontal pass, scalar
-// vertical arithmetic with clamps).
-//   thread = 4 destination columns (one 32-bit store) walking down a strip of kRs3Rows destination rows;
+// k_pyr_resize4 -- register-resident version (k_pyr_resize2 executed ~70 thread-instructions per destination pixel, issue-bound
+// at 82 %: partially filled staging loops, one shared-memory round trip for the horizontal pass, scalar vertical arithmetic).
+//   thread = 4 destination columns (one 32-bit store) walking down a strip of kRs4Rows destination rows;
 //   per source row: three aligned 32-bit loads cover the <= 8 source bytes the 4 columns touch (scale <= 2), two funnel shifts
 //   line them up at the first source column, and per column one PRMT picks its two taps and one IDP.2A computes
 //   S[sx]*a0 + S[sx+1]*a1 (the Q11 weights as a u16 pair); source rows are interpolated horizontally once and carried in
@@ -94,76 +93,107 @@ __global__ void __launch_bounds__(256) k_pyr_resize2(const __grid_constant__ Geo
 //   vertical: ((b0*(h0>>4))>>16) + ((b1*(h1>>4))>>16) as two IMAD.HI with the weights pre-shifted by 16, then (+2)>>2.
 //   No clamp: h>>4 <= 32655 and b0+b1 <= 2049 bound the result by 255.
 // Levels whose 4-column groups span more than 8 source bytes (scale factor > 2) use k_pyr_resize2.
-// Measured alternatives: strips of 8 / 16 rows (0.197 / 0.219 ms against 0.190 for 4), and loading every source row of a
-// strip before the first use (80 registers, 0.207 ms).
+// Its predecessor k_pyr_resize3 (round 1, 0.354 ms per 256 images of 752x480) spent 120 warp instructions per destination row
+// where the arithmetic needs ~55 (profiles/r01f source page: 27 % IMAD -- register moves of the carried rows and 64-bit address
+// arithmetic -- branches around the row-reuse tests, every load consumed right after issue).  This version (0.251 ms):
+//   * the two carried horizontal rows alternate roles statically (row j keeps h[s0] where row j-1 kept h[s1]): the common case
+//     "s0 advanced by one" computes ONE new source row and moves nothing; "advanced by two" computes both;
+//   * the raw words of the next destination row's lower source row are loaded one row ahead;
+//   * the row table of the strip is read with one 8-byte load per warp and broadcast by shuffles;
+//   * levels >= 2 read a source whose rows have slack behind them (pyramid slab), so the two trailing words need no clamp.
 // ---------------------------------------------------------------------------------------------------------------------------
-constexpr int kRs3Rows = 4;                    // destination rows per warp
-constexpr int kRs3TileW = 128, kRs3TileH = 8 * kRs3Rows;
+constexpr int kRs4TileW = 128;
+constexpr int kRs4Rows = 8;   // destination rows per warp (measured: 4 -> 0.284 ms, 8 -> 0.252, 12 -> 0.260, 16 -> 0.260)
 
-struct Rs3Col { uint32_t sel[4]; uint32_t wt[4]; int base; uint32_t sh; };
-
-__device__ __forceinline__ void rs3_hrow(const uint8_t* row, int sp, const Rs3Col& c, uint32_t (&h)[4]) {
-  const int o1 = min(c.base + 4, sp - 4), o2 = min(c.base + 8, sp - 4);   // words past the row end hold no tap (s1 <= w-1 < sp)
-  const uint32_t w0 = __ldg(reinterpret_cast<const uint32_t*>(row + c.base));
-  const uint32_t w1 = __ldg(reinterpret_cast<const uint32_t*>(row + o1));
-  const uint32_t w2 = __ldg(reinterpret_cast<const uint32_t*>(row + o2));
-  const uint32_t u0 = __funnelshift_r(w0, w1, c.sh), u1 = __funnelshift_r(w1, w2, c.sh);   // 8 bytes from the first source column on
-#pragma unroll
-  for (int k = 0; k < 4; k++) h[k] = __dp2a_lo(c.wt[k], __byte_perm(u0, u1, c.sel[k]), 0u) >> 4;
-}
-
-__global__ void __launch_bounds__(256) k_pyr_resize3(const __grid_constant__ Geom g, const __grid_constant__ Batch b, int level) {
+// one strip: 128 destination columns (x = first column of this lane's 4) x kRs4Rows destination rows from ys on.
+// kClamp: the source rows have no slack behind them (level 1 reads the caller's image).
+template <bool kClamp>
+__device__ __forceinline__ void rs4_strip(const Geom& g, const Batch& b, int level, int f, int x, int ys, int lane) {
   const LevelGeom& L = g.lv[level];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, f = blockIdx.z;
-  const int x = blockIdx.x * kRs3TileW + 4 * lane;
-  const int ys = blockIdx.y * kRs3TileH + warp * kRs3Rows;
   const int wpad = (L.w + 3) & ~3;   // the column table is padded to a multiple of 4
-  if (x >= wpad || ys >= L.h) return;
+  const bool active = x < wpad;      // lanes right of the level stay for the shuffles and skip loads / stores
   int sp;
   const uint8_t* src = level_ptr(g, b, level - 1, f, sp);
-  const RsY* ty = b.rsy + L.rsyOff;
-  Rs3Col c;
+  const int rows = min(kRs4Rows, L.h - ys);
+  // row table of the strip: lane j holds entry ys + j
+  uint2 myRow = make_uint2(0u, 0u);
+  if (lane < rows) myRow = __ldg(reinterpret_cast<const uint2*>(b.rsy + L.rsyOff + ys + lane));
+  uint32_t sel[4], wt[4], sh;
+  int off1 = 4, off2 = 8;
+  const uint8_t* srcx = src;
   {
-    const uint4* tx = reinterpret_cast<const uint4*>(b.rsx + L.rsxOff + x);   // 4 entries of 8 bytes
+    const uint4* tx = reinterpret_cast<const uint4*>(b.rsx + L.rsxOff + (active ? x : 0));   // 4 entries of 8 bytes
     const uint4 p0 = __ldg(tx), p1 = __ldg(tx + 1);
     const uint32_t e[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};   // (s0 | s1 << 16), (a0 | a1 << 16) per column
     const int sx0 = (int)(e[0] & 0xffffu);
-    c.base = sx0 & ~3; c.sh = (uint32_t)(sx0 & 3) * 8;
+    const int base = sx0 & ~3;
+    sh = (uint32_t)(sx0 & 3) * 8;
+    srcx = src + base;
+    if (kClamp) { off1 = min(base + 4, sp - 4) - base; off2 = min(base + 8, sp - 4) - base; }   // words past the row end hold no tap
 #pragma unroll
     for (int k = 0; k < 4; k++) {
       const int s0 = (int)(e[2 * k] & 0xffffu), s1 = (int)(e[2 * k] >> 16);
-      c.sel[k] = (uint32_t)min(s0 - sx0, 7) | ((uint32_t)min(s1 - sx0, 7) << 4);   // upper two bytes: don't care (byte 0)
-      c.wt[k] = e[2 * k + 1];
+      sel[k] = (uint32_t)min(s0 - sx0, 7) | ((uint32_t)min(s1 - sx0, 7) << 4);   // upper two bytes: don't care (byte 0)
+      wt[k] = e[2 * k + 1];
     }
   }
+  const unsigned usp = (unsigned)sp, upitch = (unsigned)L.pitch;
+  auto load3 = [&](int srow, uint32_t (&w)[3]) {
+    const uint8_t* p = srcx + (unsigned long long)(unsigned)srow * usp;   // one IMAD.WIDE.U32
+    w[0] = __ldg(reinterpret_cast<const uint32_t*>(p));
+    w[1] = __ldg(reinterpret_cast<const uint32_t*>(p + off1));
+    w[2] = __ldg(reinterpret_cast<const uint32_t*>(p + off2));
+  };
+  auto prmt = [](uint32_t a, uint32_t b2, uint32_t sl) { uint32_t r; asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b2), "r"(sl)); return r; };
+  auto hcalc = [&](const uint32_t (&w)[3], uint32_t (&h)[4]) {
+    const uint32_t u0 = __funnelshift_r(w[0], w[1], sh), u1 = __funnelshift_r(w[1], w[2], sh);   // 8 bytes from the first source column on
+#pragma unroll
+    for (int k = 0; k < 4; k++) h[k] = __dp2a_lo(wt[k], prmt(u0, u1, sel[k]), 0u) >> 4;
+  };
   uint8_t* dst = b.pyr + (long long)f * b.pyrFrameStride + L.pyrOff + x;
-  int r0 = -1, r1 = -1;
-  uint32_t hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0};
+  asm volatile("" : "+l"(dst));      // keep both per-thread base pointers whole in registers: otherwise the uniform part is re-added
+  asm volatile("" : "+l"(srcx));     // (IADD3 + IADD3.X) at every use
+  uint32_t hh[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
+  int held0 = -1;                    // source row whose h is in hh[j & 1] when row j starts (= s1 of row j-1)
+  uint32_t wn[3] = {0, 0, 0};        // raw words of the current row's s1, loaded one row ahead
+  uint32_t e0 = __shfl_sync(ORBX_FULL, myRow.x, 0);
+  if (active) load3((int)(e0 >> 16), wn);
 #pragma unroll
-  for (int j = 0; j < kRs3Rows; j++) {
-    const int y = ys + j;
-    if (y >= L.h) break;
-    const RsY e = ty[y];
-    const int s0 = e.s0, s1 = e.s1;
-    if (s0 != r0) {
-      if (s0 == r1) {
-#pragma unroll
-        for (int k = 0; k < 4; k++) hA[k] = hB[k];
-      } else rs3_hrow(src + (long long)s0 * sp, sp, c, hA);
-      r0 = s0;
+  for (int j = 0; j < kRs4Rows; j++) {
+    if (j >= rows) break;
+    const uint32_t eb = __shfl_sync(ORBX_FULL, myRow.y, j);
+    const int s0 = (int)(e0 & 0xffffu), s1 = (int)(e0 >> 16);
+    uint32_t eNext = 0;
+    const uint32_t wcur[3] = {wn[0], wn[1], wn[2]};
+    if (j + 1 < kRs4Rows) {
+      eNext = __shfl_sync(ORBX_FULL, myRow.x, j + 1);
+      if (j + 1 < rows && active) load3((int)(eNext >> 16), wn);
     }
-    if (s1 != r1) {
-      if (s1 == r0) {
+    if (active) {
+      uint32_t (&X)[4] = hh[j & 1];          // h[s0]: where the previous row kept h[s1]
+      uint32_t (&Y)[4] = hh[(j & 1) ^ 1];
+      hcalc(wcur, Y);
+      if (held0 != s0) { uint32_t w0[3]; load3(s0, w0); hcalc(w0, X); }   // first row of the strip, or s0 advanced by two
+      held0 = s1;
+      const uint32_t B0 = eb << 16, B1 = eb & 0xffff0000u;
+      uint32_t t[4];
 #pragma unroll
-        for (int k = 0; k < 4; k++) hB[k] = hA[k];
-      } else rs3_hrow(src + (long long)s1 * sp, sp, c, hB);
-      r1 = s1;
+      for (int k = 0; k < 4; k++) t[k] = __umulhi(B0, X[k]) + __umulhi(B1, Y[k]) + 2u;   // <= 1023
+      // (t >> 2) of two values per shift: t0 | t1 << 16 shifted right by 2 leaves t0 >> 2 in byte 0 and t1 >> 2 in byte 2
+      const uint32_t p01 = prmt(t[0], t[1], 0x5410u) >> 2, p23 = prmt(t[2], t[3], 0x5410u) >> 2;
+      *reinterpret_cast<uint32_t*>(dst + (unsigned long long)(unsigned)(ys + j) * upitch) = prmt(p01, p23, 0x6420u);
     }
-    const uint32_t B0 = (uint32_t)(uint16_t)e.b0 << 16, B1 = (uint32_t)(uint16_t)e.b1 << 16;
-    uint32_t v[4];
-#pragma unroll
-    for (int k = 0; k < 4; k++) v[k] = (__umulhi(B0, hA[k]) + __umulhi(B1, hB[k]) + 2u) >> 2;
-    *reinterpret_cast<uint32_t*>(dst + (long long)y * L.pitch) = v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24);
+    e0 = eNext;
   }
 }
+template <bool kClamp>
+__global__ void __launch_bounds__(256) k_pyr_resize4(const __grid_constant__ Geom g, const __grid_constant__ Batch b, int level) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int ys = (blockIdx.y * 8 + warp) * kRs4Rows;
+  if (ys >= g.lv[level].h) return;   // warp-uniform
+  rs4_strip<kClamp>(g, b, level, blockIdx.z, blockIdx.x * kRs4TileW + 4 * lane, ys, lane);
+}
+// Measured and dropped: one clustered launch for the small levels 4..7 of a frame (4 CTAs per frame, cluster barrier between the
+// levels, sources re-read through L2): 0.262 - 0.302 ms against 0.251 for one launch per level -- the separate launches overlap
+// their tails on the stream, the barrier-separated levels do not.
 }  // namespace orbx
