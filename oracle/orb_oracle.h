@@ -8,10 +8,13 @@
 // primitives are restated from their published algorithm and pinned against
 // the only executable OpenCV available (python cv2 4.13) in tests/test_oracle_cv2.py.
 //
-// PARITY STATUS: the reference ships no tests or golden vectors for this path and cannot
-// be compiled in this image (needs OpenCV 3.4 C++, Eigen, Pangolin) => "parity unpinned"
-// against the reference binary; pinned primitive-by-primitive against cv2 and by the
-// committed golden vectors in tests/golden/.
+// PARITY STATUS: pinned.  The reference ships no tests or golden vectors for this path, so the pin is the reference's own code:
+// oracle/Makefile (`make ref`) compiles the UNMODIFIED /root/reference/src/ORBextractor.cc and src/ORBmatcher.cc (plus the member
+// functions of Frame / KeyFrame / MapPoint / Pinhole / KannalaBrandt8 on the path, cut out of the reference's sources at build
+// time) against the stand-in cv:: header of oracle/ref_shim/ into oracle/_ref/*.so, and tests/test_oracle_ref.py /
+// tests/test_oracle_refmatch.py assert that this restatement equals it byte for byte (keypoints, descriptors, pyramid levels,
+// match indices, uRight / depth, frustum fields).  The OpenCV primitives underneath both are the restatements below, pinned
+// against python cv2 4.13 in tests/test_oracle_cv2.py; the committed golden vectors in tests/golden/ were generated from oracle/_ref.
 //
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
 // may load this library.  The product (liborbx.so) never links or calls it.

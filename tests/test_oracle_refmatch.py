@@ -1,0 +1,191 @@
+"""CPU: the oracle restatement of the ORBmatcher / Frame searches against the reference's OWN compiled source
+(oracle/_ref/libref_match.so = src/ORBmatcher.cc + the Frame / KeyFrame / MapPoint / camera member bodies, unmodified; see
+oracle/Makefile) on synthetic worlds.  For the searches that start from poses and 3-D points, the per-point prologue is the numpy
+restatement of tests/prologue_np.py (what k_project_points computes on the device) in front of the oracle's search loops."""
+import numpy as np
+import pytest
+
+import bowsynth
+import prologue_np as pro
+import world_cases as wc
+from oracle import refmatch as rm
+
+pytestmark = pytest.mark.skipif(not rm.available(), reason="oracle/_ref/libref_match.so not built (needs /root/reference)")
+
+
+@pytest.fixture(scope="module", params=["euroc", "kb8"])
+def scene(request):
+    cam = wc.EUROC if request.param == "euroc" else wc.KB8
+    W = wc.World(seed=15 if request.param == "euroc" else 16, n_pts=1500, cam=cam, n_dup=150)
+    Ra, ta = W.pose(seed=30)
+    Rb, tb = W.pose(seed=31)
+    A, B = W.observe(Ra, ta, seed=40), W.observe(Rb, tb, seed=41)
+    return dict(W=W, A=A, B=B, pts=W.points(rm), Ra=Ra, ta=ta, Rb=Rb, tb=tb, name=request.param)
+
+
+def _pose32(obs):
+    T = obs["Tcw"]
+    return T[:3, :3].copy(), T[:3, 3].copy()
+
+
+def _finish(kp_mp, src_to_mp, pre):
+    """oracle kp_mp (source index / -1 / untouched -2,-3) -> map-point index per keypoint as the reference leaves mvpMapPoints"""
+    return np.where(kp_mp >= 0, src_to_mp[np.clip(kp_mp, 0, None)], np.where(kp_mp == -1, -1, pre)).astype(np.int32)
+
+
+@pytest.mark.parametrize("mono,th,dz,ori", [(True, 7.0, 0.0, True), (False, 15.0, 0.0, True), (False, 7.0, 0.6, True), (False, 7.0, -0.6, False)])
+def test_search_by_projection_frame_frame(oracle, scene, mono, th, dz, ori):
+    W, A, B = scene["W"], scene["A"], scene["B"]
+    if dz:
+        B = W.observe(scene["Rb"], scene["tb"] - np.array([0, 0, dz]), seed=43)
+    cam = W.cam
+    pre = np.where(np.random.default_rng(4).random(len(B["kps"])) < 0.1, B["assoc"], -1).astype(np.int32)
+    cur = W.view(rm, B, assoc=pre)
+    last = W.view(rm, A, assoc=A["assoc"], outlier=A["outlier"])
+    nm_ref, kp_ref = rm.search_by_projection_frame(cur, last, scene["pts"], th, mono, 0.9, ori)
+    # restatement: src/ORBmatcher.cc:2038-2118 then the window search
+    Rcw, tcw = _pose32(B); Rlw, tlw = _pose32(A)
+    twc = pro.cam_center(Rcw, tcw)
+    tlc = pro.gemv_add(Rlw, twc[None], tlw)
+    mb = np.float32(cam.get("bf", 0.0) / cam["K"][0]) if cam.get("bf", 0.0) else np.float32(0)
+    mb = np.float32(np.float32(cam.get("bf", 0.0)) / np.float32(cam["K"][0]))
+    fwd = bool(tlc[2][0] > mb) and not mono
+    bwd = bool(-tlc[2][0] > mb) and not mono
+    mp = A["assoc"]
+    valid = (mp >= 0) & (A["outlier"] == 0)
+    P = W.P[np.clip(mp, 0, None)]
+    pj = pro.project(P, valid, Rcw, tcw, twc, cam["K"], W.bounds(), kb=cam.get("kb"), depth_mode=0, invz_double=True, bounds_mode=0,
+                     bf=cam.get("bf", 0.0), level_mode=0, octave=A["kps"]["octave"], scale_factors=cur.scale, th=th)
+    kp0 = np.where(pre < 0, -1, np.where(W.n_obs[np.clip(pre, 0, None)] > 0, -2, -3)).astype(np.int32)
+    nm, kp = oracle.search_by_projection_window(B["kps"], B["desc"], cur.scale, *cam["size"], pj["valid"], pj["u"], pj["v"], pj["level"],
+                                                A["kps"]["angle"], W.desc[np.clip(mp, 0, None)], th, mode=1 if fwd else (2 if bwd else 0),
+                                                dist_th=100, any_mp_blocks=False, check_orientation=ori, kp_mp=kp0,
+                                                uRight=B["u_right"] if cam.get("bf", 0.0) > 0 else None, ur=pj["ur"])
+    assert nm == nm_ref and nm > 50
+    assert np.array_equal(_finish(kp, mp, pre), kp_ref)
+
+
+@pytest.mark.parametrize("th,orb_dist,ori", [(10.0, 100, True), (3.0, 64, False)])
+def test_search_by_projection_frame_keyframe(oracle, scene, th, orb_dist, ori):
+    W, A, B = scene["W"], scene["A"], scene["B"]
+    cam = W.cam
+    found = (np.random.default_rng(7).random(W.n) < 0.15).astype(np.uint8)
+    pre = np.where(np.random.default_rng(8).random(len(B["kps"])) < 0.2, B["assoc"], -1).astype(np.int32)
+    cur = W.view(rm, B, assoc=pre)
+    kf = W.view(rm, A, assoc=A["assoc"])
+    nm_ref, kp_ref = rm.search_by_projection_keyframe(cur, kf, scene["pts"], found, th, orb_dist, 0.9, ori)
+    Rcw, tcw = _pose32(B)
+    Ow = pro.cam_center(Rcw, tcw)
+    mp = A["assoc"]
+    mpc = np.clip(mp, 0, None)
+    valid = (mp >= 0) & (W.bad[mpc] == 0) & (found[mpc] == 0)
+    pj = pro.project(W.P[mpc], valid, Rcw, tcw, Ow, cam["K"], W.bounds(), kb=cam.get("kb"), depth_mode=2, bounds_mode=0,
+                     max_d=W.max_dist[mpc], min_d=W.min_dist[mpc], level_mode=1, log_scale=np.log(np.float32(1.2)), scale_factors=cur.scale, th=th)
+    kp0 = np.where(pre < 0, -1, -2).astype(np.int32)
+    nm, kp = oracle.search_by_projection_window(B["kps"], B["desc"], cur.scale, *cam["size"], pj["valid"], pj["u"], pj["v"], pj["level"],
+                                                A["kps"]["angle"], W.desc[mpc], th, mode=0, dist_th=orb_dist, any_mp_blocks=True,
+                                                check_orientation=ori, kp_mp=kp0)
+    assert nm == nm_ref and nm > 50
+    assert np.array_equal(_finish(kp, mp, pre), kp_ref)
+
+
+def _scw(B, s):
+    Scw = B["Tcw"].copy()
+    Scw[:3, :] *= np.float32(s)
+    sR = Scw[:3, :3]
+    scw = np.float32(np.sqrt(np.float64(sR[0].astype(np.float64) @ sR[0].astype(np.float64))))   # sqrt(row.dot(row)): dot in double, sqrt(double) -> float
+    R = (sR / scw).astype(np.float32)
+    t = (Scw[:3, 3] / scw).astype(np.float32)
+    return Scw, R, t
+
+
+@pytest.mark.parametrize("th,ratio,with_kfs,s", [(4, 1.0, False, 1.07), (8, 0.9, True, 0.93)])
+def test_search_by_projection_scw(oracle, scene, th, ratio, with_kfs, s):
+    W, B = scene["W"], scene["B"]
+    cam = W.cam
+    Scw, R, t = _scw(B, s)
+    kf = W.view(rm, B, assoc=B["assoc"])
+    matched = np.where(np.random.default_rng(1).random(len(B["kps"])) < 0.2, B["assoc"], -1).astype(np.int32)
+    out = rm.search_by_projection_scw(kf, Scw, scene["pts"], th, ratio, matched, with_kfs)
+    nm_ref, m_ref = out[0], out[1]
+    Ow = pro.cam_center(R, t)
+    already = np.zeros(W.n, bool)
+    already[matched[matched >= 0]] = True
+    valid = (W.bad == 0) & ~already
+    w, h = cam["size"]
+    pj = pro.project(W.P, valid, R, t, Ow, cam["K"], (0, int(w), 0, int(h)), kb=None if with_kfs else cam.get("kb"), depth_mode=1,
+                     invz_double=False, bounds_mode=1, max_d=W.max_dist, min_d=W.min_dist, normal=W.normal, level_mode=1,
+                     log_scale=np.log(np.float32(1.2)), scale_factors=kf.scale, th=float(th), pinhole_formula=with_kfs)
+    kp0 = np.where(matched < 0, -1, -2).astype(np.int32)
+    nm, kp = oracle.search_by_projection_window(B["kps"], B["desc"], kf.scale, w, h, pj["valid"], pj["u"], pj["v"], pj["level"],
+                                                np.zeros(W.n, np.float32), W.desc, float(th), mode=3, dist_th=int(np.floor(50 * ratio)),
+                                                any_mp_blocks=True, check_orientation=False, kp_mp=kp0)
+    assert nm == nm_ref and nm > 20
+    assert np.array_equal(_finish(kp, np.arange(W.n, dtype=np.int32), matched), m_ref)
+    if with_kfs:
+        assert np.array_equal(out[2] >= 0, (m_ref >= 0) & (matched < 0))
+
+
+@pytest.mark.parametrize("th", [3.0, 6.5])
+def test_fuse(oracle, scene, th):
+    """src/ORBmatcher.cc:1425-1662: the gated best-match search + the Replace / AddObservation bookkeeping in candidate order"""
+    W, B = scene["W"], scene["B"]
+    cam = W.cam
+    kf = W.view(rm, B, assoc=B["assoc"])
+    cand = np.random.default_rng(3).permutation(W.n).astype(np.int32)
+    nf_ref, ev_ref = rm.fuse(kf, scene["pts"], cand, th)
+    R, t = _pose32(B)
+    Ow = pro.cam_center(R, t)
+    in_kf = np.zeros(W.n, bool)
+    in_kf[B["assoc"][B["assoc"] >= 0]] = True
+    valid = (W.bad[cand] == 0) & ~in_kf[cand]
+    w, h = cam["size"]
+    pj = pro.project(W.P[cand], valid, R, t, Ow, cam["K"], (0, int(w), 0, int(h)), kb=cam.get("kb"), depth_mode=1, invz_double=False,
+                     bounds_mode=1, bf=cam.get("bf", 0.0), max_d=W.max_dist[cand], min_d=W.min_dist[cand], normal=W.normal[cand], level_mode=1,
+                     log_scale=np.log(np.float32(1.2)), scale_factors=kf.scale, th=th)
+    _, _, _, inv_s2 = rm.scale_tables()
+    bi, bd = oracle.search_window_best(B["kps"], B["desc"], w, h, pj["valid"], pj["u"], pj["v"], pj["radius"], pj["level"], W.desc[cand],
+                                       gate=1, inv_level_sigma2=inv_s2, uRight=B["u_right"], ur=pj["ur"])
+    events, nfused = [], 0
+    holder = B["assoc"].copy()
+    for i, p in enumerate(cand):
+        if not pj["valid"][i] or bi[i] < 0 or bd[i] > 50:
+            continue
+        other = holder[bi[i]]
+        if other >= 0:
+            if not W.bad[other]:
+                events.append((0, p, other, -1) if W.n_obs[other] > W.n_obs[p] else (0, other, p, -1))
+        else:
+            events.append((1, p, -1, bi[i]))
+            holder[bi[i]] = p
+        nfused += 1
+    assert nfused == nf_ref and nfused > 50
+    assert np.array_equal(np.array(events, np.int32).reshape(-1, 4), ev_ref)
+
+
+def test_search_for_initialization_and_bow(oracle, scene):
+    """the searches without a projection prologue: SearchForInitialization (:722-837), both SearchByBoW (:273-475, :839-979)"""
+    W, A, B = scene["W"], scene["A"], scene["B"]
+    w, h = W.cam["size"]
+    v1, v2 = W.view(rm, A, with_pose=False), W.view(rm, B, with_pose=False)
+    lvl0 = A["kps"]["octave"] == 0
+    prev = np.stack([A["kps"]["x"], A["kps"]["y"]], 1).astype(np.float32)
+    nm_ref, m_ref, pm_ref = rm.search_for_initialization(v1, v2, prev, 60, 0.9, True)
+    nm, m12, pm = oracle.search_for_initialization(A["kps"], A["desc"], B["kps"], B["desc"], w, h, prev, 60, 0.9, True)
+    assert nm == nm_ref and np.array_equal(m12, m_ref) and np.array_equal(pm, pm_ref) and nm > 10 and lvl0.any()
+    fva = bowsynth.feature_vector(A["desc"], 24, seed=1)
+    fvb = bowsynth.feature_vector(B["desc"], 24, seed=1)
+    kfa = W.view(rm, A, assoc=A["assoc"], feat_vec=fva)
+    frb = W.view(rm, B, feat_vec=fvb)
+    nm_ref, out_ref = rm.search_by_bow_frame(kfa, frb, scene["pts"], 0.7, True)
+    elig = ((A["assoc"] >= 0) & (W.bad[np.clip(A["assoc"], 0, None)] == 0)).astype(np.uint8)
+    nm, m12 = oracle.search_by_bow(A["kps"], A["desc"], fva, elig, B["kps"], B["desc"], fvb, None, 50, 0.7, True)
+    got = np.full(len(B["kps"]), -1, np.int32)
+    got[m12[m12 >= 0]] = A["assoc"][np.nonzero(m12 >= 0)[0]]
+    assert nm == nm_ref and np.array_equal(got, out_ref) and nm > 20
+    kfb = W.view(rm, B, assoc=B["assoc"], feat_vec=fvb)
+    nm_ref, out_ref = rm.search_by_bow_keyframes(kfa, kfb, scene["pts"], 0.75, True)
+    elig2 = ((B["assoc"] >= 0) & (W.bad[np.clip(B["assoc"], 0, None)] == 0)).astype(np.uint8)
+    nm, m12 = oracle.search_by_bow(A["kps"], A["desc"], fva, elig, B["kps"], B["desc"], fvb, elig2, 50, 0.75, True)
+    got = np.where(m12 >= 0, B["assoc"][np.clip(m12, 0, None)], -1).astype(np.int32)
+    assert nm == nm_ref and np.array_equal(got, out_ref) and nm > 10
