@@ -21,7 +21,7 @@ JSON keys beyond the base contract:
                 OpenCV 3.4 C++ and cannot be compiled in this image) on the box's host cores, bounded sample
   extra         mono extraction-only throughput (752x480, nFeatures 1000: the shape the north-star target is quoted on) and
                 informational device-resident runs of the other BASELINE.json configs (HD shapes, TUM-VI shape with
-                SearchByProjection, the all-pairs 2-NN tile kernel against the popc roofline); --no-extras skips them
+                SearchByProjection, CLAHE / remap / cvtColor in front of the extractor); --no-extras skips them
   --impl reference  runs only the CPU arm, one bounded sample per step, same line with impl=reference
 """
 import argparse
@@ -349,22 +349,6 @@ def extra_configs(orbx, synth, torch, stream, local, steps):
     out["clahe_3.0_8x8_752x480_frames_per_s_per_gpu"] = nb / sec
     tbl.close(); pre.close()
     del col, g8, dst
-    # all-pairs tile kernel: 16384 queries against 262144 train descriptors, running (best, second) keys
-    nq, nt = 16384, 262144
-    q = torch.randint(0, 256, (nq, 32), dtype=torch.uint8, device="cuda"); t = torch.randint(0, 256, (nt, 32), dtype=torch.uint8, device="cuda")
-    k0 = torch.empty(nq, dtype=torch.int64, device="cuda"); k1 = torch.empty(nq, dtype=torch.int64, device="cuda")
-    mk = orbx.ORBmatcher(device=local)
-    sec = timed(lambda: mk.knn2_chunk_device(q.data_ptr(), nq, t.data_ptr(), nt, 0, 0, k0.data_ptr(), k1.data_ptr(), 1, sh), steps)
-    pairs = nq * nt / sec
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fjs:
-            smhz = float(json.load(fjs).get("sm_max_mhz", 1965.0))
-    except Exception:
-        smhz = 1965.0
-    popc_roof = 16 * 148 * smhz * 1e6 / 8      # 16 popc/clk/SM, 8 popc per 256-bit pair
-    out["allpairs_knn2_tile_pairs_per_s_per_gpu"] = pairs
-    out["allpairs_knn2_frac_of_popc_roofline"] = pairs / popc_roof
-    mk.close()
     return out
 
 
