@@ -21,9 +21,21 @@
 
 namespace orbx {
 
-constexpr int kTcM = 128, kTcN = 256;
+// CTA shape: kTcH accumulator halves of 128 queries each against train tiles of kTcN = 256 / kTcH descriptors.  L2 -> shared-memory
+// traffic is 256 B per train row per CTA pass, i.e. 2 / kTcH bytes per pair: with one half (128 queries x 256 train) the sweep ran
+// at 1.97e12 pairs/s = 3.9 TB/s of L2 reads, the L2's limit, so more queries share a tile.
+#ifndef ORBX_TC_H
+#define ORBX_TC_H 2
+#endif
+constexpr int kTcH = ORBX_TC_H;
+constexpr int kTcM = 128 * kTcH, kTcN = 256 / kTcH;
 constexpr int kTcTileBytes = kTcN * 256;          // one train tile image
-constexpr int kTcThreads = 192;
+#ifndef ORBX_TC_STAGES
+#define ORBX_TC_STAGES ((227 * 1024 - 128 * ORBX_TC_H * 256) / ((256 / ORBX_TC_H) * 256) > 6 ? 6 : (227 * 1024 - 128 * ORBX_TC_H * 256) / ((256 / ORBX_TC_H) * 256))
+#endif
+constexpr int kTcStages = ORBX_TC_STAGES;   // train-tile ring in shared memory (a bulk copy takes longer than one tile's MMAs: several must be in flight)
+constexpr int kTcEpiWarps = 4 * kTcH;
+constexpr int kTcThreads = 32 * (kTcEpiWarps + 2);
 
 __host__ __device__ inline size_t knn2_tc_workspace_bytes(long long nt) { return (size_t)((nt + kTcN - 1) / kTcN) * kTcTileBytes; }
 
@@ -104,9 +116,9 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 k_knn2_tc(const uint8_t* __restrict__ q, int nq, const uint8_t* __restrict__ texp, int nt, long long trainBase, const int2* __restrict__ exclude,
           unsigned long long* key0, unsigned long long* key1, int init) {
   extern __shared__ __align__(1024) uint8_t tc_smem[];
-  uint8_t* sA = tc_smem;                                   // 128 queries x 256 B, negated
-  uint8_t* sB = tc_smem + kTcM * 256;                      // 2 x (256 train x 256 B)
-  __shared__ __align__(8) uint64_t bFull[2], bEmpty[2], tFull[2], tEmpty[2];
+  uint8_t* sA = tc_smem;                                   // kTcM queries x 256 B, negated
+  uint8_t* sB = tc_smem + kTcM * 256;                      // kTcStages x (kTcN train x 256 B)
+  __shared__ __align__(8) uint64_t bFull[kTcStages], bEmpty[kTcStages], tFull[2], tEmpty[2];
   __shared__ uint32_t tmemBase;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int q0 = blockIdx.x * kTcM;
@@ -124,10 +136,11 @@ k_knn2_tc(const uint8_t* __restrict__ q, int nq, const uint8_t* __restrict__ tex
   }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the tensor core's async proxy
   if (tid == 0) {
-    for (int s = 0; s < 2; s++) { tc::mbar_init(&bFull[s], 1); tc::mbar_init(&bEmpty[s], 1); tc::mbar_init(&tFull[s], 1); tc::mbar_init(&tEmpty[s], 4); }
+    for (int s = 0; s < kTcStages; s++) { tc::mbar_init(&bFull[s], 1); tc::mbar_init(&bEmpty[s], 1); }
+    for (int s = 0; s < 2; s++) { tc::mbar_init(&tFull[s], 1); tc::mbar_init(&tEmpty[s], kTcEpiWarps); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 5) {
+  if (warp == kTcEpiWarps + 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(tc::smem_u32(&tmemBase)), "r"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
@@ -136,40 +149,44 @@ k_knn2_tc(const uint8_t* __restrict__ q, int nq, const uint8_t* __restrict__ tex
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tb = tmemBase;
 
-  if (warp == 4) {
+  if (warp == kTcEpiWarps) {
     // ---- producer: one 64 KB bulk copy per train tile into the 2-slot ring
     if (lane == 0) {
       for (int n = 0; n < ntiles; n++) {
-        const int s = n & 1, ph = (n >> 1) & 1;
+        const int s = n % kTcStages, ph = (n / kTcStages) & 1;
         tc::mbar_wait(&bEmpty[s], ph ^ 1);
         tc::mbar_expect_tx(&bFull[s], kTcTileBytes);
         tc::bulk_g2s(sB + (size_t)s * kTcTileBytes, texp + (size_t)n * kTcTileBytes, kTcTileBytes, &bFull[s]);
       }
     }
-  } else if (warp == 5) {
-    // ---- MMA issuer: D[128 x 256] (TMEM stage s) = A[128 x 256] * B[256 x 256]^T, K = 32 bytes per instruction
+  } else if (warp == kTcEpiWarps + 1) {
+    // ---- MMA issuer: per half h, D_h[128 x kTcN] (TMEM stage s) = A_h[128 x 256] * B[kTcN x 256]^T, K = 32 bytes per instruction
     if (lane == 0) {
       // instruction descriptor: D = S32 (2 << 4), A = B = signed 8 bit (1 << 7, 1 << 10), both K-major, N >> 3 at bit 17, M >> 4 at bit 24
-      const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kTcN >> 3) << 17) | ((uint32_t)(kTcM >> 4) << 24);
+      const uint32_t idesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kTcN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
       const uint32_t aBase = tc::smem_u32(sA), bBase = tc::smem_u32(sB);
       for (int n = 0; n < ntiles; n++) {
-        const int s = n & 1, ph = (n >> 1) & 1;
-        tc::mbar_wait(&bFull[s], ph);
+        const int s = n & 1, ph = (n >> 1) & 1;                          // accumulator stage
+        const int bs = n % kTcStages, bph = (n / kTcStages) & 1;         // ring slot of the train tile
+        tc::mbar_wait(&bFull[bs], bph);
         tc::mbar_wait(&tEmpty[s], ph ^ 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
-        for (int k = 0; k < 8; k++) {
-          const uint64_t da = tc::umma_desc(aBase + 2 * k * kTcM * 16, kTcM * 16, 128);
-          const uint64_t db = tc::umma_desc(bBase + s * kTcTileBytes + 2 * k * kTcN * 16, kTcN * 16, 128);
-          tc::umma_i8(tb + s * kTcN, da, db, idesc, k > 0);
+        for (int h = 0; h < kTcH; h++) {
+#pragma unroll
+          for (int k = 0; k < 8; k++) {
+            const uint64_t da = tc::umma_desc(aBase + (2 * k * kTcM + 128 * h) * 16, kTcM * 16, 128);
+            const uint64_t db = tc::umma_desc(bBase + bs * kTcTileBytes + 2 * k * kTcN * 16, kTcN * 16, 128);
+            tc::umma_i8(tb + s * 256 + h * kTcN, da, db, idesc, k > 0);
+          }
         }
-        tc::umma_commit(&bEmpty[s]);    // the tile's shared-memory slot may be refilled once these MMAs have read it
+        tc::umma_commit(&bEmpty[bs]);   // the tile's shared-memory slot may be refilled once these MMAs have read it
         tc::umma_commit(&tFull[s]);     // ... and the accumulator stage is complete
       }
     }
   } else {
     // ---- epilogue: thread = TMEM lane = query row
-    const int row = warp * 32 + lane, qi = q0 + row;
+    const int half = warp >> 2, row = half * 128 + (warp & 3) * 32 + lane, qi = q0 + row;
     const bool valid = qi < nq;
     unsigned long long g0 = 0xffffffffffffffffull, g1 = 0xffffffffffffffffull;
     if (valid && !init) { g0 = key0[qi]; g1 = key1[qi]; }
@@ -205,17 +222,17 @@ k_knn2_tc(const uint8_t* __restrict__ q, int nq, const uint8_t* __restrict__ tex
       const int s = n & 1, ph = (n >> 1) & 1;
       tc::mbar_wait(&tFull[s], ph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const uint32_t taddr = tb + ((uint32_t)(warp * 32) << 16) + (uint32_t)(s * kTcN);
+      const uint32_t taddr = tb + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(s * 256 + half * kTcN);
       const int colBase = n * kTcN;
       int va[32], vb[32];
       tc::tmem_ld32(taddr, va);
 #pragma unroll
-      for (int c = 0; c < 8; c += 2) {
+      for (int c = 0; c < kTcN / 32; c += 2) {
         tc::tmem_ld_wait(va);
         tc::tmem_ld32(taddr + 32 * (c + 1), vb);
         process(va, colBase + 32 * c);
         tc::tmem_ld_wait(vb);
-        if (c + 2 < 8) tc::tmem_ld32(taddr + 32 * (c + 2), va);
+        if (c + 2 < kTcN / 32) tc::tmem_ld32(taddr + 32 * (c + 2), va);
         else {   // every load of the stage has landed: hand the accumulator back before the last reduction
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
           __syncwarp();
@@ -232,7 +249,7 @@ k_knn2_tc(const uint8_t* __restrict__ q, int nq, const uint8_t* __restrict__ tex
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
-  if (warp == 5) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tb), "r"(512));
+  if (warp == kTcEpiWarps + 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tb), "r"(512));
 }
 
 // one fold: queries q[nq] against train t[nt] (nt <= 2^23), running keys in key0 / key1 (see k_knn2); workspace >= knn2_tc_workspace_bytes(nt)
@@ -240,13 +257,9 @@ inline cudaError_t knn2_tc_launch(const uint8_t* q, int nq, const uint8_t* t, in
                                   unsigned long long* key1, int init, void* workspace, cudaStream_t st) {
   if (nq <= 0 || nt <= 0) return cudaSuccess;
   if (nt > (1 << 23)) return cudaErrorInvalidValue;
-  constexpr int smemBytes = kTcM * 256 + 2 * kTcTileBytes;
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(k_knn2_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, smemBytes);
-    if (e != cudaSuccess) return e;
-    attr = true;
-  }
+  constexpr int smemBytes = kTcM * 256 + kTcStages * kTcTileBytes;
+  cudaError_t e = cudaFuncSetAttribute(k_knn2_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, smemBytes);   // per device: set on every call
+  if (e != cudaSuccess) return e;
   const long long ntiles = (nt + kTcN - 1) / kTcN;
   k_expand_i8<<<(unsigned)((ntiles * 16 * kTcN + 255) / 256), 256, 0, st>>>(t, nt, static_cast<uint8_t*>(workspace));
   k_knn2_tc<<<(nq + kTcM - 1) / kTcM, kTcThreads, smemBytes, st>>>(q, nq, static_cast<const uint8_t*>(workspace), nt, trainBase, exclude, key0, key1, init);

@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "frustum.cuh"
+#include "knn2_tc.cuh"
 #include "match_kernels.cuh"
 #include "orbx_internal.h"
 
@@ -21,6 +22,9 @@ struct orbx_matcher {
   uint8_t* arena = nullptr;
   size_t arenaCap = 0, arenaUsed = 0;
   int* dStatus = nullptr;
+  // all-pairs fold: int8 tile images of the current train chunk for k_knn2_tc (grown on demand), and which kernel folds
+  uint8_t* tcWs = nullptr; size_t tcWsBytes = 0;
+  int knn2Kernel = ORBX_KNN2_AUTO;
   // stereo results of the last orbx_stereo_match_batch
   float* sURight = nullptr; float* sDepth = nullptr; int* sBestDist = nullptr; int* sBestIdx = nullptr; int* sSad = nullptr;
   size_t sCap = 0, sHalf = 0;
@@ -568,7 +572,7 @@ void orbx_matcher_destroy(orbx_matcher* m) {
   if (!m) return;
   cudaSetDevice(m->device);
   cudaStreamSynchronize(m->stream);
-  void* ptrs[] = {m->arena, m->dStatus, m->sURight, m->sDepth, m->sBestDist, m->sBestIdx, m->sSad, m->sRowStart, m->sRowItems};
+  void* ptrs[] = {m->arena, m->tcWs, m->dStatus, m->sURight, m->sDepth, m->sBestDist, m->sBestIdx, m->sSad, m->sRowStart, m->sRowItems};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (auto& slot : m->chunkGraph) for (auto& cg : slot) cg.reset();
   for (int i = 0; i < 2; i++)
@@ -1198,6 +1202,12 @@ int orbx_search_for_initialization(orbx_matcher* m, const orbx_frame_view* F1, c
   return run_window_jobs(m, jobs, RESOLVE_INIT);
 }
 
+int orbx_matcher_set_knn2_kernel(orbx_matcher* m, int kind) {
+  if (!m || kind < ORBX_KNN2_AUTO || kind > ORBX_KNN2_TENSOR) return ORBX_ERR_ARG;
+  m->knn2Kernel = kind;
+  return ORBX_OK;
+}
+
 int orbx_knn2_chunk_device(orbx_matcher* m, const uint8_t* dQ, int nq, const uint8_t* dT, int nt, long long trainBase, const int* dExclude,
                            unsigned long long* dKey0, unsigned long long* dKey1, int init, void* stream) {
   if (!m || nq < 0 || nt < 0 || !dKey0 || !dKey1) return ORBX_ERR_ARG;
@@ -1205,6 +1215,20 @@ int orbx_knn2_chunk_device(orbx_matcher* m, const uint8_t* dQ, int nq, const uin
   if (nt > (1 << 23)) { set_error("train chunk larger than 2^23 rows"); return ORBX_ERR_ARG; }
   CK(cudaSetDevice(m->device));
   cudaStream_t st = stream ? (cudaStream_t)stream : m->stream;
+  // k_knn2_tc pays one expansion pass over the train chunk and a per-CTA prologue: it wins from ~1e8 pairs on; below that (and for
+  // nt = 0, where only the init matters) the POPC kernel folds.  Both write identical keys.
+  const bool tensor = nt > 0 && (m->knn2Kernel == ORBX_KNN2_TENSOR || (m->knn2Kernel == ORBX_KNN2_AUTO && (long long)nq * nt >= (1ll << 26)));
+  if (tensor) {
+    const size_t need = knn2_tc_workspace_bytes(nt);
+    if (need > m->tcWsBytes) {   // cudaFree waits for every kernel still reading the old buffer
+      if (m->tcWs) CK(cudaFree(m->tcWs));
+      m->tcWs = nullptr; m->tcWsBytes = 0;
+      CK(cudaMalloc((void**)&m->tcWs, need));
+      m->tcWsBytes = need;
+    }
+    CK(knn2_tc_launch(dQ, nq, dT, nt, trainBase, reinterpret_cast<const int2*>(dExclude), dKey0, dKey1, init, m->tcWs, st));
+    return ORBX_OK;
+  }
   k_knn2<<<(nq + 127) / 128, 128, 0, st>>>(dQ, nq, dT, nt, trainBase, reinterpret_cast<const int2*>(dExclude), dKey0, dKey1, init);
   CK(cudaGetLastError());
   return ORBX_OK;

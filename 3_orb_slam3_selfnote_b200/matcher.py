@@ -255,6 +255,12 @@ class ORBmatcher:
         _check(lib().orbx_knn2(self._m, _p(q), len(q), _p(t), len(t), _p(idx), _p(dist), _p(good)))
         return idx, dist, good
 
+    KNN2_AUTO, KNN2_POPC, KNN2_TENSOR = 0, 1, 2
+
+    def set_knn2_kernel(self, kind):
+        """orbx_matcher_set_knn2_kernel: which kernel folds the 2-NN chunks (0 auto by size, 1 POPC, 2 tcgen05); same results"""
+        _check(lib().orbx_matcher_set_knn2_kernel(self._m, int(kind)))
+
     def knn2_chunk_device(self, d_q, nq, d_t, nt, train_base, d_exclude, d_key0, d_key1, init, stream=0):
         _check(lib().orbx_knn2_chunk_device(self._m, C.c_void_p(d_q), nq, C.c_void_p(d_t), nt, C.c_longlong(train_base),
                                             C.c_void_p(d_exclude), C.c_void_p(d_key0), C.c_void_p(d_key1), int(init),

@@ -323,7 +323,15 @@ int orbx_search_for_initialization(orbx_matcher* m, const orbx_frame_view* F1, c
 int orbx_knn2(orbx_matcher* m, const uint8_t* query, int nq, const uint8_t* train, int nt, int* idx, int* dist, uint8_t* good);
 /* Device building block of the all-pairs keyframe sweep: folds one train chunk (global index of its first row =
  * train_base) into the running best / second-best keys (dist << 32 | global index; init != 0 resets them).  d_exclude
- * (optional, nq x int2) = global train range to skip per query (its own keyframe).  Asynchronous on `stream`. */
+ * (optional, nq x int2) = global train range to skip per query (its own keyframe).  Asynchronous on `stream`.
+ * Two kernels fold, with identical results: the POPC kernel (thread = query) and, from 2^26 pairs per call on, the
+ * tensor-core kernel (tcgen05 kind::i8 on the descriptors expanded to +-1 bytes; csrc/knn2_tc.cuh), which keeps the
+ * expanded image of the current train chunk in a matcher-owned workspace: calls of ONE matcher on different streams must
+ * be ordered by the caller.  orbx_matcher_set_knn2_kernel pins the choice (parity tests, A/B timing). */
+#define ORBX_KNN2_AUTO 0
+#define ORBX_KNN2_POPC 1
+#define ORBX_KNN2_TENSOR 2
+int orbx_matcher_set_knn2_kernel(orbx_matcher* m, int kind);
 int orbx_knn2_chunk_device(orbx_matcher* m, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt, long long train_base,
                            const int* d_exclude, unsigned long long* d_key0, unsigned long long* d_key1, int init, void* stream);
 

@@ -121,3 +121,75 @@ def test_allpairs_nccl_two_gpus(tmp_path):
     idx, dst = _run_ranks(tmp_path, "nccl", world, desc_all, desc_per_kf)
     ridx, rdst = brute_force(desc_all, desc_per_kf)
     assert np.array_equal(idx, ridx) and np.array_equal(dst, rdst)
+
+
+def _fold(m, q, chunks, ex, base, kind):
+    """fold the train chunks one call each (init on the first) with the given kernel -> (key0, key1) as numpy uint64"""
+    import torch
+    m.set_knn2_kernel(kind)
+    nq = q.shape[0]
+    k0 = torch.empty(nq, dtype=torch.int64, device="cuda"); k1 = torch.empty_like(k0)
+    off = 0
+    for i, t in enumerate(chunks):
+        m.knn2_chunk_device(q.data_ptr(), nq, t.data_ptr(), t.shape[0], base + off, ex.data_ptr() if ex is not None else 0, k0.data_ptr(),
+                            k1.data_ptr(), init=(i == 0), stream=torch.cuda.current_stream().cuda_stream)
+        off += t.shape[0]
+    torch.cuda.synchronize()
+    m.set_knn2_kernel(m.KNN2_AUTO)
+    return k0.cpu().numpy().view(np.uint64), k1.cpu().numpy().view(np.uint64)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nq,sizes,ties", [(1, (1,), True), (77, (5, 1, 300), True), (256, (128, 128), False), (1000, (129, 2047, 640), True),
+                                            (5000, (20000, 12345), False)])
+def test_knn2_tc_matches_popc_kernel(orbx, nq, sizes, ties):
+    """k_knn2_tc (tcgen05 kind::i8) writes the keys k_knn2 writes: ragged tiles, chunks smaller than a tile, ties across chunks,
+    exact duplicates, own-keyframe exclusion ranges"""
+    import torch
+    rng = np.random.default_rng(nq)
+    nt = sum(sizes)
+    q = rng.integers(0, 256, (nq, 32), dtype=np.uint8); t = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+    if ties:
+        t[:, 5:] = t[0, 5:]; q[:, 5:] = t[0, 5:]
+    t[nt - 1] = q[0]; t[nt // 2] = q[nq // 2]
+    base = 7_000_000
+    ex = np.stack([base + (np.arange(nq) // 50) * 50 % max(nt, 1), base + (np.arange(nq) // 50) * 50 % max(nt, 1) + 50], 1).astype(np.int32)
+    dq = torch.from_numpy(q).cuda(); dex = torch.from_numpy(ex).cuda()
+    chunks = [torch.from_numpy(c.copy()).cuda() for c in np.split(t, np.cumsum(sizes)[:-1])]
+    m = orbx.ORBmatcher()
+    for e in (dex, None):
+        p0, p1 = _fold(m, dq, chunks, e, base, m.KNN2_POPC)
+        g0, g1 = _fold(m, dq, chunks, e, base, m.KNN2_TENSOR)
+        assert np.array_equal(p0, g0) and np.array_equal(p1, g1)
+    if nq * nt <= 4_000_000:   # and both equal the brute force
+        d = np.unpackbits(q[:, None, :] ^ t[None, :, :], axis=2).sum(axis=2).astype(np.uint64)
+        key = (d << np.uint64(32)) | (np.uint64(base) + np.arange(nt, dtype=np.uint64))[None, :]
+        key.sort(axis=1)
+        assert np.array_equal(g0, key[:, 0])
+        if nt > 1:
+            assert np.array_equal(g1, key[:, 1])
+    m.close()
+
+
+@pytest.mark.gpu
+def test_allpairs_single_gpu_tensor_path(orbx):
+    """the sweep at a size where the tensor-core fold is picked by itself (>= 2^26 pairs per chunk), against sampled brute force"""
+    import torch
+    ap = importlib.import_module(PKG + ".allpairs")
+    desc_per_kf, nkf = 500, 80
+    rng = np.random.default_rng(9)
+    desc = rng.integers(0, 256, (nkf * desc_per_kf, 32), dtype=np.uint8)
+    desc[:, 8:] = desc[0, 8:]
+    desc[123] = desc[30123]
+    m = orbx.ORBmatcher()
+    idx, dst = ap.allpairs_knn2(torch.from_numpy(desc).cuda(), desc_per_kf, matcher=m, nchunks=2)
+    m.set_knn2_kernel(m.KNN2_POPC)
+    idx_p, dst_p = ap.allpairs_knn2(torch.from_numpy(desc).cuda(), desc_per_kf, matcher=m, nchunks=2)
+    assert np.array_equal(idx, idx_p) and np.array_equal(dst, dst_p)
+    rows = rng.choice(len(desc), 64, replace=False)
+    d = np.unpackbits(desc[rows][:, None, :] ^ desc[None, :, :], axis=2).sum(axis=2).astype(np.int64)
+    key = (d << 32) | np.arange(len(desc))[None, :]
+    key[(rows // desc_per_kf)[:, None] == (np.arange(len(desc)) // desc_per_kf)[None, :]] = np.iinfo(np.int64).max
+    key.sort(axis=1)
+    assert np.array_equal(idx[rows], key[:, :2] & 0xFFFFFFFF) and np.array_equal(dst[rows], (key[:, :2] >> 32).astype(np.int32))
+    m.close()

@@ -40,8 +40,11 @@ int main(int argc, char** argv) {
   srand(11);
   for (auto& x : q) x = rand() & 255;
   for (auto& x : t) x = rand() & 255;
-  for (size_t i = 0; i < t.size(); i++) if ((i & 31) >= 6) t[i] = t[i & 31];           // few distinct distances: many ties
-  for (size_t i = 0; i < q.size(); i++) if ((i & 31) >= 6) q[i] = t[i & 31];
+  const bool ties = !(argc > 3 && atoi(argv[3]) == 1);   // default: few distinct distances (many ties); 1 = fully random descriptors
+  if (ties) {
+    for (size_t i = 0; i < t.size(); i++) if ((i & 31) >= 6) t[i] = t[i & 31];
+    for (size_t i = 0; i < q.size(); i++) if ((i & 31) >= 6) q[i] = t[i & 31];
+  }
   for (int i = 0; i < 32; i++) { t[(size_t)12345 % nt * 32 + i] = q[7 * 32 + i]; t[(size_t)(nt - 1) * 32 + i] = q[9 * 32 + i]; }   // exact duplicates, one in the ragged last tile
   std::vector<int2> ex(nq);
   for (int i = 0; i < nq; i++) { const int kf = i / 1000; ex[i] = make_int2((int)base + kf * 1000, (int)base + kf * 1000 + 1000); }   // "own keyframe" ranges
