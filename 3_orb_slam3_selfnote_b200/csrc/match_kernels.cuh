@@ -281,6 +281,7 @@ struct ResolveArgs {        // one per frame
   int distTh;
   int anyMpBlocks;
   int checkOrientation;
+  const int* partner;       // k_resolve_fisheye: stereo partner of each keypoint in the other image (-1 none), or null
 };
 
 // SearchByProjection(Frame&, vector<MapPoint*>&, ...), ORBmatcher.cc:44-142, as a parallel fixed point.  The reference's loop is sequential only through the claims: map
@@ -478,6 +479,84 @@ __global__ void __launch_bounds__(32) k_resolve_init(const GridFrame* frames, co
     if (m >= 0) { A.prevMatched[2 * i] = F2.kps[m].x; A.prevMatched[2 * i + 1] = F2.kps[m].y; }
   }
   if (lane == 0) *A.nmatches = nmatches;
+}
+
+// ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, ...) on a fisheye-STEREO frame (F.Nleft != -1), ORBmatcher.cc:44-211:
+// per map point a left-camera pass over the left grid and a right-camera pass over mGridRight, both claiming F.mvpMapPoints.
+// A match also hands the map point to the keypoint's stereo partner in the other image (mvLeftToRightMatch /
+// mvRightToLeftMatch, :131-135 and :196-200) WITHOUT asking who held it, so a blocking holder can be replaced by a
+// non-blocking one and the claims are not monotone: the reference's order is replayed by one warp (lanes = window candidates),
+// the per-keypoint "held by a map point with observations" bit lives in shared memory.  frames / sets / args [0] = left image,
+// [1] = right image; both query sets have one entry per map point.  The left pass's `continue` on a failed ratio test (:121-122)
+// skips the map point's right pass, as in the reference.
+__global__ void __launch_bounds__(32) k_resolve_fisheye(const GridFrame* frames, const QuerySet* sets, const ResolveArgs* args) {
+  extern __shared__ uint8_t sBlocked[];   // [nL + nR]
+  const GridFrame FL = frames[0], FR = frames[1];
+  const QuerySet QL = sets[0], QR = sets[1];
+  const ResolveArgs AL = args[0], AR = args[1];
+  const int lane = threadIdx.x, nL = FL.n, nR = FR.n;
+  auto obs = [&](int i) { return AL.observed ? AL.observed[i] != 0 : true; };
+  for (int k = lane; k < nL + nR; k += 32) {
+    const int s = k < nL ? AL.kpMp[k] : AR.kpMp[k - nL];
+    sBlocked[k] = (s == -2) || (s >= 0 && obs(s));
+  }
+  __syncwarp();
+  int nmatches = 0;
+  for (int i = 0; i < QL.nq; i++) {
+    const uint8_t ob = obs(i) ? 1 : 0;
+    bool skipRight = false;
+    if (QL.valid[i] && QL.qCnt[i] > 0) {
+      const unsigned long long* e = QL.entries + QL.qOff[i];
+      const int c = QL.qCnt[i];
+      unsigned long long k1 = kKeyNone, k2 = kKeyNone;
+      for (int j = lane; j < c; j += 32) {
+        const unsigned long long k = e[j];
+        if (!sBlocked[key_idx(k)]) top2_insert(k, k1, k2);
+      }
+      top2_warp(k1, k2);
+      if (k1 != kKeyNone && key_dist(k1) <= 100) {   // TH_HIGH
+        const int bestDist = key_dist(k1), bestLevel = key_oct(k1);
+        const int bestDist2 = (k2 == kKeyNone) ? 256 : key_dist(k2), bestLevel2 = (k2 == kKeyNone) ? -1 : key_oct(k2);
+        if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(AL.nnratio, (float)bestDist2)) skipRight = true;
+        else {
+          const int best = key_idx(k1);
+          const int p = AL.partner ? AL.partner[best] : -1;
+          if (lane == 0) {
+            AL.kpMp[best] = i; sBlocked[best] = ob;
+            if (p != -1) { AR.kpMp[p] = i; sBlocked[nL + p] = ob; }
+          }
+          nmatches += (p != -1) ? 2 : 1;
+          __syncwarp();
+        }
+      }
+    }
+    if (skipRight) continue;
+    if (QR.valid[i] && QR.qCnt[i] > 0) {
+      const unsigned long long* e = QR.entries + QR.qOff[i];
+      const int c = QR.qCnt[i];
+      unsigned long long k1 = kKeyNone, k2 = kKeyNone;
+      for (int j = lane; j < c; j += 32) {
+        const unsigned long long k = e[j];
+        if (!sBlocked[nL + key_idx(k)]) top2_insert(k, k1, k2);
+      }
+      top2_warp(k1, k2);
+      if (k1 != kKeyNone && key_dist(k1) <= 100) {
+        const int bestDist = key_dist(k1), bestLevel = key_oct(k1);
+        const int bestDist2 = (k2 == kKeyNone) ? 256 : key_dist(k2), bestLevel2 = (k2 == kKeyNone) ? -1 : key_oct(k2);
+        if (!(bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(AL.nnratio, (float)bestDist2))) {
+          const int best = key_idx(k1);
+          const int p = AR.partner ? AR.partner[best] : -1;
+          if (lane == 0) {
+            if (p != -1) { AL.kpMp[p] = i; sBlocked[p] = ob; }
+            AR.kpMp[best] = i; sBlocked[nL + best] = ob;
+          }
+          nmatches += (p != -1) ? 2 : 1;
+          __syncwarp();
+        }
+      }
+    }
+  }
+  if (lane == 0) { *AL.nmatches = nmatches; *AR.nmatches = nmatches; }
 }
 
 // ---- brute-force 2-NN ----------------------------------------------------------------------------------------------------
@@ -827,6 +906,9 @@ struct BowArgs {
   int* nmatches;
   int maxDist; float nnratio; int checkOrientation;
   int* blk[2]; int* chg; int* choice;   // parallel resolve scratch: [n2] x 2, [2], [nwork]
+  // fisheye-stereo frame on side 2 (F.Nleft != -1, ORBmatcher.cc:338-431): features >= nLeft2 belong to the right image and are
+  // matched separately (best only, no ratio test); nLeft2 < 0 otherwise
+  int nLeft2; int* matches12R; int* choiceR;
   // triangulation gates (ORBmatcher.cc:1087-1146, Pinhole.cpp:150-164)
   float F12[9]; float epx, epy; const float* scaleFactors2; const float* levelSigma2; int coarse;
 };
@@ -867,9 +949,10 @@ __global__ void __cluster_dims__(kParCluster, 1, 1) __launch_bounds__(kParThread
   const int lane = threadIdx.x & 31;
   const int gthread = blockIdx.x * kParThreads + threadIdx.x, nthreads = kParCluster * kParThreads;
   const int gwarp = gthread >> 5, nwarps = nthreads >> 5;
+  const bool fish = A.nLeft2 >= 0;
   for (int k = gthread; k < A.s2.n; k += nthreads) { A.blk[0][k] = INT_MAX; A.blk[1][k] = INT_MAX; }
-  for (int k = gthread; k < A.s1.n; k += nthreads) A.matches12[k] = -1;
-  for (int w = gthread; w < A.nwork; w += nthreads) A.choice[w] = -1;
+  for (int k = gthread; k < A.s1.n; k += nthreads) { A.matches12[k] = -1; if (fish) A.matches12R[k] = -1; }
+  for (int w = gthread; w < A.nwork; w += nthreads) { A.choice[w] = -1; if (fish) A.choiceR[w] = -1; }
   if (gthread < 2) A.chg[gthread] = 0;
   cluster.sync();
   for (int it = 0; it <= A.nwork; it++) {
@@ -879,24 +962,39 @@ __global__ void __cluster_dims__(kParCluster, 1, 1) __launch_bounds__(kParThread
     for (int w = gwarp; w < A.nwork; w += nwarps) {
       const BowWork W = A.work[w];
       const int idx1 = (int)A.s1.indices[W.p1];
-      int choice = -1;
+      int choice = -1, choiceR = -1;
       if ((unsigned)idx1 < (unsigned)A.s1.n && (!A.s1.elig || A.s1.elig[idx1])) {
-        unsigned long long k1 = kKeyNone, k2 = kKeyNone;
+        unsigned long long k1 = kKeyNone, k2 = kKeyNone, r1 = kKeyNone;
         const int c = W.b1 - W.b0;
         for (int j = lane; j < c; j += 32) {
           const unsigned long long k = A.entries[W.off + j];
-          if (k != kKeyNone && !(__ldcg(cur + (int)(k & 0xfffffu)) < w)) top2_insert(k, k1, k2);
+          if (k != kKeyNone && !(__ldcg(cur + (int)(k & 0xfffffu)) < w)) {
+            if (fish && (int)(k & 0xfffffu) >= A.nLeft2) r1 = min(r1, k);
+            else top2_insert(k, k1, k2);
+          }
         }
         top2_warp(k1, k2);
+        if (fish) {
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) r1 = min(r1, __shfl_xor_sync(0xffffffffu, r1, o));
+        }
         if (k1 != kKeyNone) {
           const int bestDist1 = (int)(k1 >> 40);
           const int bestDist2 = (k2 == kKeyNone) ? 256 : (int)(k2 >> 40);
-          if (bestDist1 <= A.maxDist && (float)bestDist1 < __fmul_rn(A.nnratio, (float)bestDist2)) choice = (int)(k1 & 0xfffffu);
+          if (bestDist1 <= A.maxDist) {
+            if ((float)bestDist1 < __fmul_rn(A.nnratio, (float)bestDist2)) choice = (int)(k1 & 0xfffffu);
+            // ORBmatcher.cc:400-403: inside `bestDist1 <= TH_LOW`, whatever the left ratio test said; "|| true" voids the right ratio test
+            if (fish && r1 != kKeyNone && (int)(r1 >> 40) <= A.maxDist) choiceR = (int)(r1 & 0xfffffu);
+          }
         }
       }
       if (lane == 0) {
         if (choice != A.choice[w]) { A.choice[w] = choice; changed = true; }
         if (choice >= 0) atomicMin(nxt + choice, w);
+        if (fish) {
+          if (choiceR != A.choiceR[w]) { A.choiceR[w] = choiceR; changed = true; }
+          if (choiceR >= 0) atomicMin(nxt + choiceR, w);
+        }
       }
     }
     if (changed) atomicExch(A.chg + (it & 1), 1);
@@ -908,8 +1006,10 @@ __global__ void __cluster_dims__(kParCluster, 1, 1) __launch_bounds__(kParThread
     if (!any) break;
   }
   for (int w = gthread; w < A.nwork; w += nthreads) {
+    const int idx1 = (int)A.s1.indices[A.work[w].p1];   // a feature sits in one node: one work item per idx1
     const int ch = __ldcg(A.choice + w);
-    if (ch >= 0) A.matches12[(int)A.s1.indices[A.work[w].p1]] = ch;   // a feature sits in one node: one work item per idx1
+    if (ch >= 0) A.matches12[idx1] = ch;
+    if (fish) { const int chR = __ldcg(A.choiceR + w); if (chR >= 0) A.matches12R[idx1] = chR; }
   }
 }
 
@@ -968,24 +1068,31 @@ __global__ void __launch_bounds__(256) k_bow_rotfilter(const __grid_constant__ B
   if (tid < 30) hist[tid] = 0;
   if (tid == 0) total = 0;
   __syncthreads();
+  const int nsets = A.nLeft2 >= 0 ? 2 : 1;   // fisheye-stereo frame: the right-image matches vote and are filtered too (:405-424)
   int mine = 0;
   if (A.checkOrientation) {
-    for (int i = tid; i < A.s1.n; i += 256) {
-      const int m = A.matches12[i];
-      if (m >= 0) atomicAdd(&hist[rot_bin(A.s1.kps[i].angle, A.s2.kps[m].angle)], 1);
+    for (int s = 0; s < nsets; s++) {
+      const int* mm = s ? A.matches12R : A.matches12;
+      for (int i = tid; i < A.s1.n; i += 256) {
+        const int m = mm[i];
+        if (m >= 0) atomicAdd(&hist[rot_bin(A.s1.kps[i].angle, A.s2.kps[m].angle)], 1);
+      }
     }
     __syncthreads();
     if (tid == 0) { int i1, i2, i3; three_maxima(hist, 30, i1, i2, i3); keep[0] = i1; keep[1] = i2; keep[2] = i3; }
     __syncthreads();
   }
-  for (int i = tid; i < A.s1.n; i += 256) {
-    const int m = A.matches12[i];
-    if (m < 0) continue;
-    if (A.checkOrientation) {
-      const int bin = rot_bin(A.s1.kps[i].angle, A.s2.kps[m].angle);
-      if (bin != keep[0] && bin != keep[1] && bin != keep[2]) { A.matches12[i] = -1; continue; }
+  for (int s = 0; s < nsets; s++) {
+    int* mm = s ? A.matches12R : A.matches12;
+    for (int i = tid; i < A.s1.n; i += 256) {
+      const int m = mm[i];
+      if (m < 0) continue;
+      if (A.checkOrientation) {
+        const int bin = rot_bin(A.s1.kps[i].angle, A.s2.kps[m].angle);
+        if (bin != keep[0] && bin != keep[1] && bin != keep[2]) { mm[i] = -1; continue; }
+      }
+      mine++;
     }
-    mine++;
   }
   atomicAdd(&total, mine);
   __syncthreads();

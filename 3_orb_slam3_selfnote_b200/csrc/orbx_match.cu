@@ -113,7 +113,7 @@ struct HostQueries {
   bool gate = false; const float* invSigma2 = nullptr; int nSigma = 0;   // Fuse chi-square gate (xr = projected right coordinate)
 };
 
-enum ResolveKind { RESOLVE_NONE, RESOLVE_MAPPOINTS, RESOLVE_WINDOW, RESOLVE_INIT, RESOLVE_BEST };
+enum ResolveKind { RESOLVE_NONE, RESOLVE_MAPPOINTS, RESOLVE_WINDOW, RESOLVE_INIT, RESOLVE_BEST, RESOLVE_FISHEYE };
 
 struct WindowJob {
   // frame (host, or device when devKps != null)
@@ -125,6 +125,7 @@ struct WindowJob {
   const uint8_t* observed = nullptr; const float* angle = nullptr;
   int* kpMp = nullptr; int kpMpLen = 0;  // host in/out
   float nnratio = 0; int distTh = 100; int anyMpBlocks = 0; int checkOrientation = 0;
+  const int* partner = nullptr;   // RESOLVE_FISHEYE: mvLeftToRightMatch (left job) / mvRightToLeftMatch (right job)
   // init search
   const orbx_frame_view* F1 = nullptr; float* prevMatched = nullptr; int* matches12 = nullptr;
   int* nmatches = nullptr;
@@ -237,7 +238,7 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
   // ---- plan the arena
   ArenaPlan plan;
   struct Off { size_t kps, desc, uRight, cellStart, cellItems, valid, x, y, r, xr, minL, maxL, qdesc, qOff, qCnt, entries, cursor,
-               observed, angle, kpMp, assigned, nmatches, kps1, prevMatched, m12, m21, mdist, bins, sigma, blk0, blk1, chg,
+               observed, angle, kpMp, assigned, nmatches, kps1, prevMatched, m12, m21, mdist, bins, sigma, blk0, blk1, chg, partner,
                pPos, pNormal, pMaxD, pMinD, pOct, pValid, pLevel, pScale; };
   std::vector<Off> off(nj);
   std::vector<int> entryCap(nj);
@@ -279,6 +280,7 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
     o.assigned = plan.add((size_t)std::max(nq, 1) * 4);
     o.nmatches = plan.add(4);
     o.blk0 = plan.add((size_t)std::max(n, 32) * 4); o.blk1 = plan.add((size_t)std::max(n, 32) * 4); o.chg = plan.add(8);
+    o.partner = J.partner ? plan.add((size_t)std::max(n, 1) * 4) : (size_t)-1;
     if (kind == RESOLVE_INIT) {
       o.kps1 = plan.add((size_t)std::max(nq, 1) * sizeof(orbx_keypoint));
       o.prevMatched = plan.add((size_t)std::max(nq, 1) * 8);
@@ -423,8 +425,10 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
     Q.entries = at<unsigned long long>(m, o.entries); Q.entryCap = entryCap[j]; Q.entryCursor = at<int>(m, o.cursor);
     CK(cudaMemsetAsync(m->arena + o.cursor, 0, 4, st));
     maxQ = std::max(maxQ, nq);
-    if (kind == RESOLVE_MAPPOINTS || kind == RESOLVE_WINDOW) {
+    if (kind == RESOLVE_MAPPOINTS || kind == RESOLVE_WINDOW || kind == RESOLVE_FISHEYE) {
       ResolveArgs& A = rargs[j];
+      if (J.partner) CK(up(o.partner, J.partner, (size_t)G.n * 4));
+      A.partner = J.partner ? at<int>(m, o.partner) : nullptr;
       if (J.observed) CK(up(o.observed, J.observed, nq));
       if (J.angle) CK(up(o.angle, J.angle, (size_t)nq * 4));
       CK(up(o.kpMp, J.kpMp, (size_t)G.n * 4));
@@ -476,6 +480,7 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
   } else if (kind == RESOLVE_WINDOW) {
     k_resolve_par<<<dim3(kParCluster, nj), kParThreads, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs), 1);
   }
+  else if (kind == RESOLVE_FISHEYE) k_resolve_fisheye<<<1, 32, (size_t)(frames[0].n + frames[1].n), st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs));
   else if (kind == RESOLVE_INIT) k_resolve_init<<<nj, 32, 0, st>>>(dFrames, dSets, at<InitArgs>(m, oArgs));
   else if (kind == RESOLVE_BEST && maxQ > 0) k_resolve_best<<<dim3((maxQ + 7) / 8, nj), 256, 0, st>>>(dSets, at<ResolveArgs>(m, oArgs));
   CK(cudaGetLastError());
@@ -485,7 +490,7 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
   for (int j = 0; j < nj; j++) {
     WindowJob& J = jobs[j];
     const Off& o = off[j];
-    if (kind == RESOLVE_MAPPOINTS || kind == RESOLVE_WINDOW) {
+    if (kind == RESOLVE_MAPPOINTS || kind == RESOLVE_WINDOW || kind == RESOLVE_FISHEYE) {
       CK(down(J.kpMp, o.kpMp, (size_t)std::min(frames[j].n, J.kpMpLen) * 4));
       CK(down(J.nmatches, o.nmatches, 4));
     } else if (kind == RESOLVE_INIT) {
@@ -637,6 +642,39 @@ int orbx_search_by_projection_mappoints(orbx_matcher* m, const orbx_frame_view* 
   prep_mappoint_queries(J.q, nmp, inView, projX, projY, level, viewCos, mpDesc, projXR, th, F->scale_factors, F->nlevels, F->u_right != nullptr);
   J.observed = observed; J.kpMp = kpMp; J.kpMpLen = F->n; J.nnratio = nnratio; J.nmatches = nmatches;
   return run_window_jobs(m, jobs, RESOLVE_MAPPOINTS);
+}
+
+int orbx_search_by_projection_mappoints_stereo(orbx_matcher* m, const orbx_frame_view* left, const orbx_frame_view* right, int nmp,
+                                               const orbx_mappoint_track* trackLeft, const orbx_mappoint_track* trackRight, const uint8_t* mpDesc,
+                                               const uint8_t* observed, const int* leftToRight, const int* rightToLeft, float th, float nnratio,
+                                               int* kpMp, int* nmatches) {
+  if (!m || nmp < 0 || !kpMp || !nmatches || !trackLeft || !trackRight || !left || !right) return ORBX_ERR_ARG;
+  for (const orbx_mappoint_track* t : {trackLeft, trackRight})
+    if (nmp > 0 && (!t->in_view || !t->proj_x || !t->proj_y || !t->level || !t->view_cos)) return ORBX_ERR_ARG;
+  if (nmp > 0 && !mpDesc) return ORBX_ERR_ARG;
+  if ((left->n > 0 && !leftToRight) || (right->n > 0 && !rightToLeft)) return ORBX_ERR_ARG;
+  int rc = check_view(left, true);
+  if (rc != ORBX_OK) return rc;
+  if ((rc = check_view(right, true)) != ORBX_OK) return rc;
+  if (left->n + right->n > 2 * kMaxKpSmem) { set_error("more than %d keypoints in the two images", 2 * kMaxKpSmem); return ORBX_ERR_CAPACITY; }
+  for (int k = 0; k < left->n; k++)
+    if (leftToRight[k] < -1 || leftToRight[k] >= right->n) { set_error("leftToRight[%d] out of range", k); return ORBX_ERR_ARG; }
+  for (int k = 0; k < right->n; k++)
+    if (rightToLeft[k] < -1 || rightToLeft[k] >= left->n) { set_error("rightToLeft[%d] out of range", k); return ORBX_ERR_ARG; }
+  std::vector<WindowJob> jobs(2);
+  const orbx_frame_view* views[2] = {left, right};
+  const orbx_mappoint_track* tracks[2] = {trackLeft, trackRight};
+  for (int s = 0; s < 2; s++) {
+    WindowJob& J = jobs[s];
+    J.F = views[s]; set_bounds(J, views[s]);
+    // the left window is scaled by th (ORBmatcher.cc:70-71), the right one is not (:147-150); no mvuRight check on such frames (:92)
+    prep_mappoint_queries(J.q, nmp, tracks[s]->in_view, tracks[s]->proj_x, tracks[s]->proj_y, tracks[s]->level, tracks[s]->view_cos, mpDesc, nullptr,
+                          s == 0 ? th : 1.0f, views[s]->scale_factors, views[s]->nlevels, false);
+    J.observed = observed; J.nnratio = nnratio; J.nmatches = s == 0 ? nmatches : nullptr;
+    J.kpMp = kpMp + (s == 0 ? 0 : left->n); J.kpMpLen = views[s]->n;
+    J.partner = s == 0 ? leftToRight : rightToLeft;
+  }
+  return run_window_jobs(m, jobs, RESOLVE_FISHEYE);
 }
 
 int orbx_search_by_projection_mappoints_batch(orbx_matcher* m, orbx_extractor* ex, int nframes, int nmp, const uint8_t* inView,
@@ -961,6 +999,7 @@ struct BowProblem {
   const orbx_keypoint* kps2; const uint8_t* desc2; const orbx_featvec* fv2; const uint8_t* elig2; const uint8_t* stereo2;
   int maxDist; float nnratio; int checkOrientation;
   bool triangulate; const float* F12; float epx, epy; const float* scaleFactors2; const float* levelSigma2; int nlevels; int coarse;
+  int nLeft2 = -1; int* matches12R = nullptr;   // side 2 is a fisheye-stereo frame: features >= nLeft2 are the right image's
 };
 
 int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches) {
@@ -968,8 +1007,10 @@ int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches)
   if ((P.n1 > 0 && (!P.kps1 || !P.desc1)) || (P.n2 > 0 && (!P.kps2 || !P.desc2))) return ORBX_ERR_ARG;
   if (bow_check(P.fv1, P.n1) != ORBX_OK || bow_check(P.fv2, P.n2) != ORBX_OK) { set_error("bad feature vector (node ids must ascend)"); return ORBX_ERR_ARG; }
   if (P.n1 >= (1 << 20) || P.n2 >= (1 << 20)) { set_error("more than 2^20 features per keyframe is unsupported"); return ORBX_ERR_UNSUPPORTED; }
+  const bool fish = P.nLeft2 >= 0;
+  if (fish && (!P.matches12R || P.nLeft2 > P.n2 || P.triangulate)) return ORBX_ERR_ARG;
   *nmatches = 0;
-  for (int i = 0; i < P.n1; i++) matches12[i] = -1;
+  for (int i = 0; i < P.n1; i++) { matches12[i] = -1; if (fish) P.matches12R[i] = -1; }
   if (P.n1 == 0 || P.n2 == 0) return ORBX_OK;
   CK(cudaSetDevice(m->device));
   std::vector<BowWork> work;
@@ -1004,6 +1045,7 @@ int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches)
   const size_t oM = plan.add((size_t)P.n1 * 4), oN = plan.add(4);
   const size_t oB0 = plan.add((size_t)P.n2 * 4), oB1 = plan.add((size_t)P.n2 * 4), oChg = plan.add(8), oCh = plan.add((size_t)nw * 4);
   const size_t oSF = P.triangulate ? plan.add((size_t)P.nlevels * 4) : (size_t)-1, oLS = P.triangulate ? plan.add((size_t)P.nlevels * 4) : (size_t)-1;
+  const size_t oMR = fish ? plan.add((size_t)P.n1 * 4) : (size_t)-1, oChR = fish ? plan.add((size_t)nw * 4) : (size_t)-1;
   int rc = arena_ensure(m, plan.total);
   if (rc != ORBX_OK) return rc;
   cudaStream_t st = m->stream;
@@ -1026,6 +1068,7 @@ int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches)
   A.matches12 = at<int>(m, oM); A.nmatches = at<int>(m, oN);
   A.maxDist = P.maxDist; A.nnratio = P.nnratio; A.checkOrientation = P.checkOrientation;
   A.blk[0] = at<int>(m, oB0); A.blk[1] = at<int>(m, oB1); A.chg = at<int>(m, oChg); A.choice = at<int>(m, oCh);
+  A.nLeft2 = P.nLeft2; A.matches12R = fish ? at<int>(m, oMR) : nullptr; A.choiceR = fish ? at<int>(m, oChR) : nullptr;
   if (P.triangulate) {
     memcpy(A.F12, P.F12, sizeof(A.F12));
     A.epx = P.epx; A.epy = P.epy; A.scaleFactors2 = at<float>(m, oSF); A.levelSigma2 = at<float>(m, oLS); A.coarse = P.coarse;
@@ -1038,6 +1081,7 @@ int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches)
   k_bow_rotfilter<<<1, 256, 0, st>>>(A);
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(matches12, m->arena + oM, (size_t)P.n1 * 4, cudaMemcpyDeviceToHost, st));
+  if (fish) CK(cudaMemcpyAsync(P.matches12R, m->arena + oMR, (size_t)P.n1 * 4, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(nmatches, m->arena + oN, 4, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   return ORBX_OK;
@@ -1052,6 +1096,18 @@ int orbx_search_by_bow(orbx_matcher* m, int n1, const orbx_keypoint* kps1, const
   P.n2 = n2; P.kps2 = kps2; P.desc2 = desc2; P.fv2 = fv2; P.elig2 = elig2;
   P.maxDist = maxDist; P.nnratio = nnratio; P.checkOrientation = checkOrientation; P.triangulate = false;
   return run_bow(m, P, matches12, nmatches);
+}
+
+int orbx_search_by_bow_stereo(orbx_matcher* m, int n1, const orbx_keypoint* kps1, const uint8_t* desc1, const orbx_featvec* fv1,
+                              const uint8_t* elig1, int n2, int nLeft2, const orbx_keypoint* kps2, const uint8_t* desc2, const orbx_featvec* fv2,
+                              int maxDist, float nnratio, int checkOrientation, int* matches12Left, int* matches12Right, int* nmatches) {
+  if (nLeft2 < 0 || nLeft2 > n2 || !matches12Right) return ORBX_ERR_ARG;
+  BowProblem P{};
+  P.n1 = n1; P.kps1 = kps1; P.desc1 = desc1; P.fv1 = fv1; P.elig1 = elig1;
+  P.n2 = n2; P.kps2 = kps2; P.desc2 = desc2; P.fv2 = fv2; P.elig2 = nullptr;
+  P.maxDist = maxDist; P.nnratio = nnratio; P.checkOrientation = checkOrientation; P.triangulate = false;
+  P.nLeft2 = nLeft2; P.matches12R = matches12Right;
+  return run_bow(m, P, matches12Left, nmatches);
 }
 
 int orbx_search_for_triangulation(orbx_matcher* m, int n1, const orbx_keypoint* kps1, const uint8_t* desc1, const orbx_featvec* fv1,

@@ -98,6 +98,34 @@ class FramePreproc {
     return visible;
   }
 
+  // The right camera of a fisheye-stereo frame as Frame::isInFrustumChecks(pMP, limit, bRight = true) sets it up
+  // (src/Frame.cc:1274-1281): mR = Rrl * mRcw, mt = Rrl * mtcw + trl, twc = mRwc * tlr + mOw, projection through mpCamera2.
+  // Float products in the order of cv::gemm's small-matrix path (((a0*b0 + a1*b1) + a2*b2), then + c), so the composed pose has the
+  // bits the reference's cv::Mat lines produce.  Trl / Tlr are the frame's 3x4 row-major mTrl / mTlr; cam2 = fx fy cx cy of
+  // mpCamera2 (kb2 = its k1..k4 for KannalaBrandt8, null for a pinhole).  Frame::isInFrustum on such a frame (:643-660) is
+  // isInFrustum(left) for mbTrackInView + mTrackProjX/Y, mnTrackScaleLevel, mTrackViewCos, mTrackDepth and isInFrustum(right)
+  // for mbTrackInViewR + mTrackProjXR (= its mTrackProjX), mTrackProjYR, mnTrackScaleLevelR, mTrackViewCosR, mTrackDepthR;
+  // fields of points that fail keep their previous values in the reference (the result arrays hold -1 there).
+  static orbx_frustum RightCameraFrustum(const orbx_frustum& left, const float* Trl, const float* Tlr, const float* cam2, const float* kb2) {
+    orbx_frustum g = left;
+    auto dot3 = [](float a0, float b0, float a1, float b1, float a2, float b2) {
+      volatile float s = a0 * b0; volatile float p = a1 * b1; s = s + p; p = a2 * b2; s = s + p; return (float)s; };
+    for (int i = 0; i < 3; i++) {
+      for (int j = 0; j < 3; j++)
+        g.Rcw[3 * i + j] = dot3(Trl[4 * i], left.Rcw[j], Trl[4 * i + 1], left.Rcw[3 + j], Trl[4 * i + 2], left.Rcw[6 + j]);
+      volatile float t = dot3(Trl[4 * i], left.tcw[0], Trl[4 * i + 1], left.tcw[1], Trl[4 * i + 2], left.tcw[2]);
+      t = t + Trl[4 * i + 3];
+      g.tcw[i] = t;
+      volatile float o = dot3(left.Rcw[i], Tlr[3], left.Rcw[3 + i], Tlr[7], left.Rcw[6 + i], Tlr[11]);   // mRwc = mRcw^T
+      o = o + left.Ow[i];
+      g.Ow[i] = o;
+    }
+    g.fx = cam2[0]; g.fy = cam2[1]; g.cx = cam2[2]; g.cy = cam2[3];
+    g.camera_model = kb2 ? ORBX_CAMERA_KB8 : ORBX_CAMERA_PINHOLE;
+    for (int k = 0; k < 4; k++) g.kb[k] = kb2 ? kb2[k] : 0.f;
+    return g;
+  }
+
   orbx_preproc* handle() { return h_; }
 
  private:

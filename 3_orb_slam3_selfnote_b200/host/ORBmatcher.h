@@ -42,12 +42,12 @@ class ORBmatcher {
   // Computes the Hamming distance between two ORB descriptors (src/ORBmatcher.cc:2463-2483)
   static int DescriptorDistance(const cvx::Mat& a, const cvx::Mat& b) { return orbx_hamming(a.ptr(0), b.ptr(0)); }
 
-  // Search matches between Frame keypoints and projected MapPoints (local-map tracking), src/ORBmatcher.cc:44-142.
-  // Monocular / rectified-stereo frames (F.Nleft == -1); the fisheye-stereo right-camera pass (:144-211) is not offloaded.
+  // Search matches between Frame keypoints and projected MapPoints (local-map tracking), src/ORBmatcher.cc:44-211: monocular /
+  // rectified-stereo frames (F.Nleft == -1, :63-141) and fisheye-stereo frames (both camera passes, :63-211).
   template <class FrameT, class MapPointT>
   int SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, const float th = 3, const bool bFarPoints = false,
                          const float thFarPoints = 50.0f) {
-    if (F.Nleft != -1) throw std::runtime_error("ORBmatcher::SearchByProjection: fisheye stereo (Nleft != -1) is not offloaded");
+    if (F.Nleft != -1) return SearchByProjectionTwoCameras(F, vpMapPoints, th, bFarPoints, thFarPoints);
     const int nmp = (int)vpMapPoints.size();
     std::vector<uint8_t> inView(nmp), observed(nmp), desc((size_t)nmp * 32);
     std::vector<float> px(nmp), py(nmp), vc(nmp), pxr(nmp);
@@ -73,6 +73,49 @@ class ORBmatcher {
     orbx_shim::check(orbx_search_by_projection_mappoints(m_, &fv.v, nmp, inView.data(), px.data(), py.data(), lvl.data(), vc.data(), desc.data(),
                                                          observed.data(), pxr.data(), th, mfNNratio, kpMp.data(), &nmatches),
                      "orbx_search_by_projection_mappoints");
+    for (int k = 0; k < F.N; k++)
+      if (kpMp[k] >= 0) F.mvpMapPoints[k] = vpMapPoints[kpMp[k]];
+    return nmatches;
+  }
+
+  // The fisheye-stereo form of the search above (F.Nleft != -1): left pass over mvKeys / the left grid, right pass over mvKeysRight /
+  // mGridRight, stereo partners through mvLeftToRightMatch / mvRightToLeftMatch (orbx_search_by_projection_mappoints_stereo).
+  template <class FrameT, class MapPointT>
+  int SearchByProjectionTwoCameras(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, const float th, const bool bFarPoints,
+                                   const float thFarPoints) {
+    const int nmp = (int)vpMapPoints.size(), nl = F.Nleft, nr = F.N - F.Nleft;
+    std::vector<uint8_t> inL(nmp), inR(nmp), observed(nmp), desc((size_t)nmp * 32);
+    std::vector<float> pxL(nmp), pyL(nmp), vcL(nmp), pxR(nmp), pyR(nmp), vcR(nmp);
+    std::vector<int> lvL(nmp), lvR(nmp);
+    for (int i = 0; i < nmp; i++) {  // the gating of src/ORBmatcher.cc:52-62
+      MapPointT* pMP = vpMapPoints[i];
+      bool ok = pMP->mbTrackInView || pMP->mbTrackInViewR;
+      if (ok && bFarPoints && pMP->mTrackDepth > thFarPoints) ok = false;
+      if (ok && pMP->isBad()) ok = false;
+      if (!ok) continue;
+      inL[i] = pMP->mbTrackInView; inR[i] = pMP->mbTrackInViewR;
+      pxL[i] = pMP->mTrackProjX; pyL[i] = pMP->mTrackProjY; lvL[i] = pMP->mnTrackScaleLevel; vcL[i] = pMP->mTrackViewCos;
+      pxR[i] = pMP->mTrackProjXR; pyR[i] = pMP->mTrackProjYR; lvR[i] = pMP->mnTrackScaleLevelR; vcR[i] = pMP->mTrackViewCosR;
+      observed[i] = pMP->Observations() > 0;
+      const cvx::Mat d = pMP->GetDescriptor();
+      memcpy(&desc[(size_t)i * 32], d.ptr(0), 32);
+    }
+    DescHolder dd(F.mDescriptors, F.N);
+    orbx_frame_view L, R;
+    L.n = nl; L.keypoints = reinterpret_cast<const orbx_keypoint*>(F.mvKeys.data()); L.descriptors = dd.p; L.u_right = nullptr;
+    L.scale_factors = F.mvScaleFactors.data(); L.nlevels = (int)F.mvScaleFactors.size();
+    L.min_x = F.mnMinX; L.min_y = F.mnMinY; L.max_x = F.mnMaxX; L.max_y = F.mnMaxY;
+    R = L;
+    R.n = nr; R.keypoints = reinterpret_cast<const orbx_keypoint*>(F.mvKeysRight.data()); R.descriptors = dd.p + (size_t)nl * 32;
+    const orbx_mappoint_track tL = {inL.data(), pxL.data(), pyL.data(), lvL.data(), vcL.data()};
+    const orbx_mappoint_track tR = {inR.data(), pxR.data(), pyR.data(), lvR.data(), vcR.data()};
+    std::vector<int> kpMp(F.N);
+    for (int k = 0; k < F.N; k++) kpMp[k] = !F.mvpMapPoints[k] ? -1 : (F.mvpMapPoints[k]->Observations() > 0 ? -2 : -3);
+    int nmatches = 0;
+    orbx_shim::check(orbx_search_by_projection_mappoints_stereo(m_, &L, &R, nmp, &tL, &tR, desc.data(), observed.data(),
+                                                                F.mvLeftToRightMatch.data(), F.mvRightToLeftMatch.data(), th, mfNNratio,
+                                                                kpMp.data(), &nmatches),
+                     "orbx_search_by_projection_mappoints_stereo");
     for (int k = 0; k < F.N; k++)
       if (kpMp[k] >= 0) F.mvpMapPoints[k] = vpMapPoints[kpMp[k]];
     return nmatches;
@@ -340,10 +383,10 @@ class ORBmatcher {
 
   // ---- SURVEY.md section 8(f) rank 1 ---------------------------------------------------------------------------------------
   // Search matches between MapPoints in a KeyFrame and ORB in a Frame, brute force constrained to ORB that belong to the same
-  // vocabulary node (relocalisation / reference-keyframe tracking), src/ORBmatcher.cc:273-475.  Nleft == -1 frames.
+  // vocabulary node (relocalisation / reference-keyframe tracking), src/ORBmatcher.cc:273-475, incl. fisheye-stereo frames
+  // (F.Nleft != -1, :338-431: a keyframe feature may take one left-image and one right-image feature of the frame).
   template <class KeyFrameT, class FrameT, class MapPointT>
   int SearchByBoW(KeyFrameT* pKF, FrameT& F, std::vector<MapPointT*>& vpMapPointMatches) {
-    if (F.Nleft != -1) throw std::runtime_error("ORBmatcher::SearchByBoW: fisheye stereo (Nleft != -1) is not offloaded");
     const std::vector<MapPointT*> vpMapPointsKF = pKF->GetMapPointMatches();
     vpMapPointMatches.assign(F.N, static_cast<MapPointT*>(nullptr));
     const int n1 = (int)vpMapPointsKF.size();
@@ -353,6 +396,30 @@ class ORBmatcher {
     DescHolder d1(pKF->mDescriptors, n1), d2(F.mDescriptors, F.N);
     std::vector<int> m12(std::max(n1, 1), -1);
     int nmatches = 0;
+    if (F.Nleft != -1) {
+      // keypoints whose angles feed the rotation histogram (:381-389, :409-416): mvKeys then mvKeysRight on both sides when the
+      // keyframe has a second camera, else the keyframe's mvKeysUn
+      std::vector<orbx_keypoint> k1, k2;
+      const orbx_keypoint* kp1 = reinterpret_cast<const orbx_keypoint*>(pKF->mvKeysUn.data());
+      if (pKF->mpCamera2) {
+        k1.resize(std::max(n1, 1));
+        for (int i = 0; i < n1; i++)
+          memcpy(&k1[i], i >= pKF->NLeft ? (const void*)&pKF->mvKeysRight[i - pKF->NLeft] : (const void*)&pKF->mvKeys[i], sizeof(orbx_keypoint));
+        kp1 = k1.data();
+      }
+      k2.resize(std::max(F.N, 1));
+      for (int i = 0; i < F.N; i++)
+        memcpy(&k2[i], i >= F.Nleft ? (const void*)&F.mvKeysRight[i - F.Nleft] : (const void*)&F.mvKeys[i], sizeof(orbx_keypoint));
+      std::vector<int> m12R(std::max(n1, 1), -1);
+      orbx_shim::check(orbx_search_by_bow_stereo(m_, n1, kp1, d1.p, &fv1.v, elig1.data(), F.N, F.Nleft, k2.data(), d2.p, &fv2.v, TH_LOW, mfNNratio,
+                                                 mbCheckOrientation ? 1 : 0, m12.data(), m12R.data(), &nmatches),
+                       "orbx_search_by_bow_stereo");
+      for (int i = 0; i < n1; i++) {
+        if (m12[i] >= 0) vpMapPointMatches[m12[i]] = vpMapPointsKF[i];
+        if (m12R[i] >= 0) vpMapPointMatches[m12R[i]] = vpMapPointsKF[i];
+      }
+      return nmatches;
+    }
     orbx_shim::check(orbx_search_by_bow(m_, n1, reinterpret_cast<const orbx_keypoint*>(pKF->mvKeysUn.data()), d1.p, &fv1.v, elig1.data(), F.N,
                                         reinterpret_cast<const orbx_keypoint*>(F.mvKeys.data()), d2.p, &fv2.v, nullptr, TH_LOW, mfNNratio,
                                         mbCheckOrientation ? 1 : 0, m12.data(), &nmatches),

@@ -128,12 +128,23 @@ class _Frustum(C.Structure):
                 ("n_scale_levels", C.c_int), ("camera_model", C.c_int), ("kb", C.c_float * 4)]
 
 
-def frustum(Rcw, tcw, fx, fy, cx, cy, bounds, bf, scale_factor, nlevels, viewing_cos_limit=0.5, kb=None):
-    """The members of Frame that isInFrustum reads.  Ow = -Rcw^T tcw and mfLogScaleFactor = log(mfScaleFactor) are computed
-    here in float32 like Frame::UpdatePoseMatrices (src/Frame.cc:561-566) and the constructor (:110)."""
+def _mm3(A, B):
+    """3x3 (or 3x3 * 3x1) float32 product in the order of OpenCV's small-matrix gemm: ((a0*b0 + a1*b1) + a2*b2), every step rounded to float"""
+    A = np.asarray(A, np.float32); B = np.asarray(B, np.float32).reshape(3, -1)
+    out = np.empty((3, B.shape[1]), np.float32)
+    for i in range(3):
+        for j in range(B.shape[1]):
+            out[i, j] = np.float32(np.float32(np.float32(A[i, 0] * B[0, j]) + np.float32(A[i, 1] * B[1, j])) + np.float32(A[i, 2] * B[2, j]))
+    return out
+
+
+def frustum(Rcw, tcw, fx, fy, cx, cy, bounds, bf, scale_factor, nlevels, viewing_cos_limit=0.5, kb=None, Ow=None):
+    """The members of Frame that isInFrustum reads.  mfLogScaleFactor = log(mfScaleFactor) in float32 (Frame.cc:110).  Ow: the
+    frame's mOw; when omitted it is formed as Frame::UpdatePoseMatrices does (src/Frame.cc:561-566, mOw = -mRcw.t()*mtcw: OpenCV
+    materialises the transpose for the unary minus, then runs one small-matrix gemm with alpha = -1)."""
     Rcw = np.asarray(Rcw, np.float32).reshape(3, 3)
     tcw = np.asarray(tcw, np.float32).reshape(3)
-    Ow = -(Rcw.T @ tcw).astype(np.float32)
+    Ow = (-_mm3(np.ascontiguousarray(Rcw.T), tcw).reshape(3)).astype(np.float32) if Ow is None else np.asarray(Ow, np.float32).reshape(3)
     f = _Frustum()
     f.Rcw[:] = Rcw.reshape(-1).tolist(); f.tcw[:] = tcw.tolist(); f.Ow[:] = Ow.tolist()
     f.fx, f.fy, f.cx, f.cy = float(fx), float(fy), float(cx), float(cy)
@@ -146,6 +157,27 @@ def frustum(Rcw, tcw, fx, fy, cx, cy, bounds, bf, scale_factor, nlevels, viewing
     if kb is not None:
         f.kb[:] = [float(k) for k in kb]
     return f
+
+
+def frustum_right_camera(left, Tlr, fx, fy, cx, cy, kb=None):
+    """The right camera of a fisheye-stereo frame as Frame::isInFrustumChecks(pMP, limit, bRight = true) sets it up
+    (src/Frame.cc:1274-1281): mR = Rrl * mRcw, mt = Rrl * mtcw + trl, twc = mRwc * tlr + mOw, projected through mpCamera2
+    (fx .. kb).  Tlr = mTlr (3x4, left <- right); Trl is derived as the constructor does (Frame.cc:1192-1195:
+    Rrl = Rlr^T, trl = Rrl * (-1 * tlr)).  `left` is the frustum() of the left camera; same bounds, scale and limits."""
+    Tlr = np.asarray(Tlr, np.float32).reshape(3, 4)
+    Rlr, tlr = Tlr[:, :3], Tlr[:, 3]
+    Rrl = np.ascontiguousarray(Rlr.T)
+    trl = _mm3(Rrl, (np.float32(-1) * tlr).astype(np.float32)).reshape(3)
+    Rcw = np.array(left.Rcw[:], np.float32).reshape(3, 3); tcw = np.array(left.tcw[:], np.float32); Ow = np.array(left.Ow[:], np.float32)
+    g = _Frustum.from_buffer_copy(left)
+    g.Rcw[:] = _mm3(Rrl, Rcw).reshape(-1).tolist()
+    g.tcw[:] = (_mm3(Rrl, tcw).reshape(3) + trl).astype(np.float32).tolist()
+    g.Ow[:] = (_mm3(np.ascontiguousarray(Rcw.T), tlr).reshape(3) + Ow).astype(np.float32).tolist()
+    g.fx, g.fy, g.cx, g.cy = float(fx), float(fy), float(cx), float(cy)
+    g.camera_model = 0 if kb is None else 1
+    if kb is not None:
+        g.kb[:] = [float(k) for k in kb]
+    return g
 
 
 def _undistort(self, kps, fx, fy, cx, cy, dist):

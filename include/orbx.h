@@ -173,6 +173,23 @@ int orbx_search_by_projection_mappoints_batch(orbx_matcher* m, orbx_extractor* e
                                               const uint8_t* mp_desc, const uint8_t* observed, float th, float nnratio,
                                               int* kp_mp, int capacity_per_frame, int* nmatches);
 
+/* The same entry point on a fisheye-STEREO frame (F.Nleft != -1; Examples/Stereo/TUM_512.yaml-shaped rigs), src/ORBmatcher.cc:44-211:
+ * per map point the left-camera pass (:63-141) over the left image's keypoints / grid, then the right-camera pass (:144-211)
+ * over mvKeysRight / mGridRight; both claim F.mvpMapPoints, and a match also hands the map point to the keypoint's stereo
+ * partner in the other image (mvLeftToRightMatch / mvRightToLeftMatch, :131-135, :196-200).  `left` = mvKeys + descriptor rows
+ * [0, Nleft), `right` = mvKeysRight + rows [Nleft, N) (same bounds; u_right = NULL).  track_left = mbTrackInView, mTrackProjX/Y,
+ * mnTrackScaleLevel, mTrackViewCos; track_right = mbTrackInViewR, mTrackProjXR/YR, mnTrackScaleLevelR (-1: no right pass),
+ * mTrackViewCosR, as Frame::isInFrustumChecks wrote them (src/Frame.cc:1270-1343); in_view already carries the gates of :52-62
+ * for both.  th scales the left window only (:70-71 vs :147-150).  kp_mp: [left->n + right->n], in/out, coded as above;
+ * *nmatches counts partner assignments too, as the reference does. */
+typedef struct orbx_mappoint_track {
+  const uint8_t* in_view; const float* proj_x; const float* proj_y; const int* level; const float* view_cos;
+} orbx_mappoint_track;
+int orbx_search_by_projection_mappoints_stereo(orbx_matcher* m, const orbx_frame_view* left, const orbx_frame_view* right, int nmp,
+                                               const orbx_mappoint_track* track_left, const orbx_mappoint_track* track_right,
+                                               const uint8_t* mp_desc, const uint8_t* observed, const int* left_to_right,
+                                               const int* right_to_left, float th, float nnratio, int* kp_mp, int* nmatches);
+
 /* Window best-match search shared by ORBmatcher::SearchByProjection(Frame& Cur, const Frame& Last, th, bMono)
  * (src/ORBmatcher.cc:2027-2289; mode 0 = levels [l-1,l+1], 1 = forward [l,inf), 2 = backward [0,l]; dist_th = TH_HIGH),
  * both SearchByProjection(KeyFrame*, Scw, vpPoints, [vpPointsKFs,] vpMatched, ...) overloads (:489-602, :604-720; mode 3 =
@@ -221,6 +238,16 @@ typedef struct orbx_featvec {
 int orbx_search_by_bow(orbx_matcher* m, int n1, const orbx_keypoint* kps1, const uint8_t* desc1, const orbx_featvec* fv1,
                        const uint8_t* elig1, int n2, const orbx_keypoint* kps2, const uint8_t* desc2, const orbx_featvec* fv2,
                        const uint8_t* elig2, int max_dist, float nnratio, int check_orientation, int* matches12, int* nmatches);
+
+/* SearchByBoW(KeyFrame*, Frame&, ...) when the frame is a fisheye-stereo one (F.Nleft != -1), src/ORBmatcher.cc:338-431: side 2
+ * holds N = Nleft + Nright features (keypoints mvKeys then mvKeysRight, descriptors as stacked in mDescriptors); within a node the
+ * left-image candidates go through the best / second-best ratio test, the right-image ones keep their best only (the reference
+ * voids that ratio test with "|| true") and only when the left best is within max_dist (:400 sits inside :373).  Both claim.
+ * matches12_left[i] / matches12_right[i] = side-2 feature index (right ones >= n_left2) or -1, after the rotation filter. */
+int orbx_search_by_bow_stereo(orbx_matcher* m, int n1, const orbx_keypoint* kps1, const uint8_t* desc1, const orbx_featvec* fv1,
+                              const uint8_t* elig1, int n2, int n_left2, const orbx_keypoint* kps2, const uint8_t* desc2,
+                              const orbx_featvec* fv2, int max_dist, float nnratio, int check_orientation, int* matches12_left,
+                              int* matches12_right, int* nmatches);
 
 /* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo, bCoarse), src/ORBmatcher.cc:981-1222, for
  * pinhole keyframes without a second camera.  elig1[i] = !pKF1->GetMapPoint(i) && (!bOnlyStereo || stereo1[i]), elig2

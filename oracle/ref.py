@@ -36,6 +36,15 @@ def build(force=False):
     return True
 
 
+def build_twin():
+    """libshim_match.so: the reference-side harness linked against the product's host/ORBmatcher.h + liborbx.so (tests/test_refsig_gpu.py).
+    Needs the product library built first; returns False when /root/reference is absent."""
+    if not can_build():
+        return False
+    subprocess.check_call(["make", "-C", _HERE, "REF=" + REFERENCE_ROOT, "twin"], stdout=subprocess.DEVNULL)
+    return True
+
+
 def available(variant="strict"):
     if not os.path.exists(_LIBS[variant]) and can_build():
         build()

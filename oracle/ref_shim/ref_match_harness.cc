@@ -62,6 +62,8 @@ struct RefView {
   const int* mapPointIdx;       // mvpMapPoints as indices into the map-point arrays (-1 = none), N entries, or null
   const uint8_t* outlier;       // mvbOutlier or null
   int fvNodes; const uint32_t* fvIds; const int* fvStart; const uint32_t* fvIdx;   // mFeatVec as CSR (ids ascending) or fvNodes = 0
+  const int* leftToRight;       // mvLeftToRightMatch (Nleft entries) or null = all -1   (fisheye stereo, Frame.cc:1228-1262)
+  const int* rightToLeft;       // mvRightToLeftMatch (Nright entries) or null = all -1
 };
 
 struct RefPoints {
@@ -151,6 +153,11 @@ struct World {
       cv::Mat trl = Rrl * (-1 * F.mTlr.col(3));
       F.mTrl = cv::Mat(3, 4, CV_32F);
       for (int y = 0; y < 3; y++) { for (int x = 0; x < 3; x++) F.mTrl.at<float>(y, x) = Rrl.at<float>(y, x); F.mTrl.at<float>(y, 3) = trl.at<float>(y); }
+    }
+    if (V.Nleft != -1) {
+      F.mvLeftToRightMatch.assign(V.Nleft, -1); F.mvRightToLeftMatch.assign(V.N - V.Nleft, -1);
+      if (V.leftToRight) F.mvLeftToRightMatch.assign(V.leftToRight, V.leftToRight + V.Nleft);
+      if (V.rightToLeft) F.mvRightToLeftMatch.assign(V.rightToLeft, V.rightToLeft + (V.N - V.Nleft));
     }
     F.mvpMapPoints.assign(V.N, nullptr);
     if (V.mapPointIdx) for (int i = 0; i < V.N; i++) F.mvpMapPoints[i] = mp(V.mapPointIdx[i]);
@@ -266,6 +273,30 @@ int rm_search_by_projection_mappoints(const RefView* V, const RefPoints* P, int 
       m.mbTrackInView = inView[i] != 0; m.mTrackProjX = projX[i]; m.mTrackProjY = projY[i]; m.mTrackProjXR = projXR ? projXR[i] : 0.f;
       m.mnTrackScaleLevel = level[i]; m.mTrackViewCos = viewCos[i]; m.mTrackDepth = trackDepth ? trackDepth[i] : 0.f;
     }
+    vp.push_back(&m);
+  }
+  ORBmatcher matcher(nnratio, true);
+  const int nm = matcher.SearchByProjection(F, vp, th, bFarPoints != 0, thFarPoints);
+  export_matches(F.mvpMapPoints, W, kpMp);
+  return nm;
+}
+
+// The same call on a fisheye-stereo frame (V->Nleft != -1) with the tracking fields of BOTH cameras given (the fields
+// Frame::isInFrustumChecks writes, src/Frame.cc:1324-1339): L / R = in_view, proj_x, proj_y, level, view_cos per map point.
+int rm_search_by_projection_mappoints_stereo(const RefView* V, const RefPoints* P, const uint8_t* inL, const float* pxL, const float* pyL,
+                                             const int* lvL, const float* vcL, const uint8_t* inR, const float* pxR, const float* pyR,
+                                             const int* lvR, const float* vcR, const float* trackDepth, float th, float nnratio, int bFarPoints,
+                                             float thFarPoints, int* kpMp) {
+  World W; Frame F;
+  W.points(P);
+  RefView v2 = *V; v2.mapPointIdx = kpMp;
+  W.fill_common(v2, F);
+  std::vector<MapPoint*> vp;
+  for (int i = 0; i < P->n; i++) {
+    MapPoint& m = W.mps[i];
+    m.mbTrackInView = inL[i] != 0; m.mTrackProjX = pxL[i]; m.mTrackProjY = pyL[i]; m.mnTrackScaleLevel = lvL[i]; m.mTrackViewCos = vcL[i];
+    m.mbTrackInViewR = inR[i] != 0; m.mTrackProjXR = pxR[i]; m.mTrackProjYR = pyR[i]; m.mnTrackScaleLevelR = lvR[i]; m.mTrackViewCosR = vcR[i];
+    m.mTrackDepth = trackDepth ? trackDepth[i] : 0.f;
     vp.push_back(&m);
   }
   ORBmatcher matcher(nnratio, true);

@@ -72,7 +72,7 @@ class _View(C.Structure):
                 ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("bf", C.c_float), ("b", C.c_float),
                 ("camModel", C.c_int), ("kb", C.c_float * 4), ("cam2Model", C.c_int), ("cam2", C.c_float * 8), ("Tcw", C.c_void_p),
                 ("Tlr", C.c_void_p), ("mapPointIdx", C.c_void_p), ("outlier", C.c_void_p), ("fvNodes", C.c_int), ("fvIds", C.c_void_p),
-                ("fvStart", C.c_void_p), ("fvIdx", C.c_void_p)]
+                ("fvStart", C.c_void_p), ("fvIdx", C.c_void_p), ("leftToRight", C.c_void_p), ("rightToLeft", C.c_void_p)]
 
 
 class _Points(C.Structure):
@@ -99,7 +99,8 @@ class View:
     """Members of a Frame or KeyFrame.  kps = mvKeys (= mvKeysUn unless kps_un is given); bounds = (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
 
     def __init__(self, kps, desc, bounds, K=(1.0, 1.0, 0.0, 0.0), bf=0.0, b=0.0, u_right=None, kps_un=None, scale_factor=1.2, nlevels=8,
-                 Tcw=None, map_point_idx=None, outlier=None, feat_vec=None, kb=None, kps_right=None, n_left=-1, cam2=None, Tlr=None):
+                 Tcw=None, map_point_idx=None, outlier=None, feat_vec=None, kb=None, kps_right=None, n_left=-1, cam2=None, Tlr=None,
+                 left_to_right=None, right_to_left=None):
         self.keep = []
         k = lambda a, dt: None if a is None else self._hold(np.ascontiguousarray(a, dt))
         v = _View()
@@ -128,6 +129,7 @@ class View:
             v.cam2[:] = [float(x) for x in cam2[1:9]]
         v.Tcw = _p(k(Tcw, np.float32)); v.Tlr = _p(k(Tlr, np.float32))
         v.mapPointIdx = _p(k(map_point_idx, np.int32)); v.outlier = _p(k(outlier, np.uint8))
+        v.leftToRight = _p(k(left_to_right, np.int32)); v.rightToLeft = _p(k(right_to_left, np.int32))
         if feat_vec is not None:
             ids, start, idx = feat_vec
             v.fvNodes = len(ids)
@@ -184,6 +186,19 @@ def search_by_projection_mappoints(view, pts, th, nnratio, fields=None, viewing_
          g("view_cos", np.float32), g("depth", np.float32)]
     nm = lib().rm_search_by_projection_mappoints(_r(view), _r(pts), int(fields is None), C.c_float(viewing_cos_limit), *[C.c_void_p(_p(x)) for x in a],
                                                  C.c_float(th), C.c_float(nnratio), int(far_points), C.c_float(th_far), C.c_void_p(_p(kp_mp)))
+    return nm, kp_mp
+
+
+def search_by_projection_mappoints_stereo(view, pts, th, nnratio, left, right, kp_mp=None, depth=None, far_points=False, th_far=50.0):
+    """Fisheye-stereo frame (view.Nleft != -1): left / right = dict(in_view, proj_x, proj_y, level, view_cos) of the two cameras."""
+    kp_mp = np.full(view.N, -1, np.int32) if kp_mp is None else np.ascontiguousarray(kp_mp, np.int32).copy()
+    a = []
+    for f in (left, right):
+        a += [np.ascontiguousarray(f["in_view"], np.uint8), np.ascontiguousarray(f["proj_x"], np.float32), np.ascontiguousarray(f["proj_y"], np.float32),
+              np.ascontiguousarray(f["level"], np.int32), np.ascontiguousarray(f["view_cos"], np.float32)]
+    a.append(None if depth is None else np.ascontiguousarray(depth, np.float32))
+    nm = lib().rm_search_by_projection_mappoints_stereo(_r(view), _r(pts), *[C.c_void_p(_p(x)) for x in a], C.c_float(th), C.c_float(nnratio),
+                                                        int(far_points), C.c_float(th_far), C.c_void_p(_p(kp_mp)))
     return nm, kp_mp
 
 

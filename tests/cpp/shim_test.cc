@@ -13,9 +13,9 @@
 using namespace ORB_SLAM3;
 
 struct MockMapPoint {
-  bool mbTrackInView = true;
-  float mTrackDepth = 1.f, mTrackProjX = 0, mTrackProjY = 0, mTrackProjXR = 0, mTrackViewCos = 1.f;
-  int mnTrackScaleLevel = 0;
+  bool mbTrackInView = true, mbTrackInViewR = false;
+  float mTrackDepth = 1.f, mTrackProjX = 0, mTrackProjY = 0, mTrackProjXR = 0, mTrackProjYR = 0, mTrackViewCos = 1.f, mTrackViewCosR = 1.f;
+  int mnTrackScaleLevel = 0, mnTrackScaleLevelR = -1;
   cvx::Mat desc;
   int id = 0;
   bool isBad() const { return false; }
@@ -25,7 +25,8 @@ struct MockMapPoint {
 
 struct MockFrame {
   int N = 0, Nleft = -1;
-  std::vector<cvx::KeyPoint> mvKeys, mvKeysUn;
+  std::vector<cvx::KeyPoint> mvKeys, mvKeysUn, mvKeysRight;
+  std::vector<int> mvLeftToRightMatch, mvRightToLeftMatch;
   cvx::Mat mDescriptors;
   std::vector<float> mvuRight, mvDepth, mvScaleFactors;
   float mnMinX = 0, mnMinY = 0, mnMaxX = 0, mnMaxY = 0, mb = 0, mbf = 0;
@@ -35,7 +36,8 @@ struct MockFrame {
 // the members of KeyFrame the bag-of-words searches read (include/KeyFrame.h)
 struct MockKeyFrame {
   int N = 0, NLeft = -1;
-  std::vector<cvx::KeyPoint> mvKeysUn;
+  void* mpCamera2 = nullptr;
+  std::vector<cvx::KeyPoint> mvKeys, mvKeysUn, mvKeysRight;
   cvx::Mat mDescriptors;
   std::vector<float> mvuRight, mvScaleFactors, mvLevelSigma2, mvInvLevelSigma2;
   float mnMinX = 0, mnMinY = 0, mnMaxX = 0, mnMaxY = 0;

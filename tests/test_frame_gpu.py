@@ -53,7 +53,7 @@ def test_is_in_frustum(pre, oracle, n, seed, kb):
     cam, P, normal, maxd, mind = fc.frustum_case(oracle, n, seed=seed, log_mode=oracle.LOG_PORTABLE, kb=kb)
     ref = oracle.is_in_frustum(cam, P, normal, maxd, mind)
     g = pre.mod.frustum(np.array(cam.Rcw[:]).reshape(3, 3), cam.tcw[:], cam.fx, cam.fy, cam.cx, cam.cy,
-                        (cam.minX, cam.maxX, cam.minY, cam.maxY), cam.bf, 1.2, cam.nScaleLevels, cam.viewingCosLimit, kb=kb)
+                        (cam.minX, cam.maxX, cam.minY, cam.maxY), cam.bf, 1.2, cam.nScaleLevels, cam.viewingCosLimit, kb=kb, Ow=cam.Ow[:])
     assert np.array_equal(np.array(g.Ow[:], np.float32), np.array(cam.Ow[:], np.float32))
     out = pre.isInFrustum(g, P, normal, maxd, mind)
     if kb is None:
@@ -104,7 +104,7 @@ def test_frustum_feeds_search_by_projection(pre, orbx, oracle, synth):
     ref = oracle.is_in_frustum(cam, P, nrm, maxd, mind)
     nm_o, kp_o = oracle.search_by_projection_mappoints(k, d, scale, W, H, ref["in_view"], ref["proj_x"], ref["proj_y"], ref["level"],
                                                        ref["view_cos"], d, 1.0, 0.8)
-    g = pre.mod.frustum(R, t, fx, fy, cx, cy, (0, W, 0, H), 47.9, 1.2, 8)
+    g = pre.mod.frustum(R, t, fx, fy, cx, cy, (0, W, 0, H), 47.9, 1.2, 8, Ow=Ow)
     out = pre.isInFrustum(g, P, nrm, maxd, mind)
     F = orbx.FrameView(k, d, scale, W, H)
     m = orbx.ORBmatcher(0.8)
@@ -165,7 +165,7 @@ def test_search_local_points_batch(pre, orbx, oracle, synth, nframes, nmp, th):
     for f in range(nframes):
         Rf, tf = poses[f]
         cam = oracle.FrustumCam()
-        cam.Rcw[:] = Rf.reshape(-1).tolist(); cam.tcw[:] = tf.tolist(); cam.Ow[:] = (-(Rf.T @ tf).astype(np.float32)).tolist()
+        cam.Rcw[:] = Rf.reshape(-1).tolist(); cam.tcw[:] = tf.tolist(); cam.Ow[:] = cams[f].Ow[:]   # the frame's mOw as frustum() forms it (Frame.cc:565)
         cam.fx, cam.fy, cam.cx, cam.cy = fx, fy, cx, cy
         cam.minX, cam.maxX, cam.minY, cam.maxY = 0, W, 0, H
         cam.bf, cam.logScaleFactor, cam.viewingCosLimit, cam.nScaleLevels, cam.logMode = 0.0, float(np.log(np.float32(1.2))), 0.5, 8, 1
@@ -203,7 +203,7 @@ def test_device_resident_forms_and_arguments(pre, orbx, oracle):
     # frustum on device buffers
     ocam, P, normal, maxd, mind = fc.frustum_case(oracle, 4000, seed=12)
     g = pre.mod.frustum(np.array(ocam.Rcw[:]).reshape(3, 3), ocam.tcw[:], ocam.fx, ocam.fy, ocam.cx, ocam.cy,
-                        (ocam.minX, ocam.maxX, ocam.minY, ocam.maxY), ocam.bf, 1.2, 8, 0.5)
+                        (ocam.minX, ocam.maxX, ocam.minY, ocam.maxY), ocam.bf, 1.2, 8, 0.5, Ow=ocam.Ow[:])
     n = len(P)
     dP, dN, dMx, dMn = [torch.from_numpy(a).cuda() for a in (P, normal, maxd, mind)]
     dIn = torch.empty(n, dtype=torch.uint8, device="cuda")

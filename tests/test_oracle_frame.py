@@ -96,3 +96,26 @@ def test_predicted_level_uses_raw_max_distance(oracle):
     o = oracle.is_in_frustum(cam, P[:4], normal[:4], np.array([dist / 1.19, dist / 1.21, 50, 50], np.float32),
                              np.array([0.1, 0.1, dist / 0.81, dist / 0.79], np.float32))
     assert o["in_view"].tolist() == [1, 0, 1, 0]
+
+
+def test_right_camera_pose_composition_matches_cv2_gemm():
+    """frustum_right_camera (src/Frame.cc:1274-1281 + :1192-1195) composes the right camera's pose with the float op order of cv::gemm's
+    small-matrix path: checked bit for bit against cv2.gemm, the arithmetic behind the reference's cv::Mat expressions."""
+    import importlib
+    cv2 = pytest.importorskip("cv2")
+    pp = importlib.import_module("3_orb_slam3_selfnote_b200.preproc")
+    rng = np.random.default_rng(3)
+    for _ in range(200):
+        R, _ = np.linalg.qr(rng.normal(size=(3, 3)))
+        Rcw = R.astype(np.float32); tcw = rng.normal(size=3).astype(np.float32)
+        Q, _ = np.linalg.qr(np.eye(3) + rng.normal(size=(3, 3)) * 0.01)
+        Tlr = np.concatenate([Q.astype(np.float32), rng.normal(size=(3, 1)).astype(np.float32) * 0.1], 1)
+        left = pp.frustum(Rcw, tcw, 190.0, 190.0, 255.0, 257.0, (0, 512, 0, 512), 0.0, 1.2, 8, 0.5, kb=(0.003, 0.0007, -0.002, 0.0002))
+        g = pp.frustum_right_camera(left, Tlr, 191.0, 191.5, 254.0, 256.0, kb=(0.003, 0.0007, -0.002, 0.0002))
+        Rrl = np.ascontiguousarray(Tlr[:, :3].T)
+        trl = cv2.gemm(Rrl, (np.float32(-1) * Tlr[:, 3:4]).astype(np.float32), 1, None, 0)
+        Ow = np.array(left.Ow[:], np.float32).reshape(3, 1)
+        assert np.array_equal(np.array(g.Rcw[:], np.float32).reshape(3, 3), cv2.gemm(Rrl, Rcw, 1, None, 0))
+        assert np.array_equal(np.array(g.tcw[:], np.float32).reshape(3, 1), cv2.gemm(Rrl, tcw.reshape(3, 1), 1, trl, 1))
+        assert np.array_equal(np.array(g.Ow[:], np.float32).reshape(3, 1), cv2.gemm(np.ascontiguousarray(Rcw.T), Tlr[:, 3:4].copy(), 1, Ow, 1))
+        assert (g.fx, g.camera_model) == (191.0, 1)

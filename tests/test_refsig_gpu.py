@@ -158,3 +158,116 @@ def test_search_for_triangulation_reference_signature(scene):
         ref, got = both(rm.search_for_triangulation, kf1, kf2, scene["pts"], F12, only_stereo, coarse)
         same(ref, got, "SearchForTriangulation")
     assert ref[0] > 10
+
+
+# ---- fisheye-stereo frames (F.Nleft != -1; Examples/Stereo/TUM_512.yaml-shaped rigs) ------------------------------------------
+@pytest.fixture(scope="module")
+def rig():
+    W = wc.World(seed=8, n_pts=2200, cam=wc.KB8, n_dup=300)
+    R, t = W.pose(seed=12)
+    obs = W.observe_two_cameras(R, t, seed=30)
+    return dict(W=W, obs=obs, pts=W.points(rm))
+
+
+def _tracks(view, pts):
+    """the MapPoint tracking fields of both cameras as the reference's Frame::isInFrustum writes them (src/Frame.cc:643-660, 1270-1343)"""
+    t = rm.is_in_frustum(view, pts, 0.5, right=True)
+    left = dict(in_view=t["in_view"], proj_x=t["proj_x"], proj_y=t["proj_y"], level=t["level"], view_cos=t["view_cos"])
+    right = dict(in_view=t["in_view_r"], proj_x=t["proj_xr_r"], proj_y=t["proj_y_r"], level=t["level_r"], view_cos=t["view_cos_r"])
+    return left, right, t["depth"]
+
+
+@pytest.mark.parametrize("th,pre_share,far", [(1.0, 0.0, False), (3.0, 0.15, False), (5.0, 0.4, True)])
+def test_search_by_projection_two_cameras(rig, th, pre_share, far):
+    """src/ORBmatcher.cc:44-211 on a fisheye-stereo frame: left pass, right pass, stereo-partner hand-over, claims across both"""
+    W, obs = rig["W"], rig["obs"]
+    n = len(obs["assoc"])
+    pre = np.where(np.random.default_rng(5).random(n) < pre_share, obs["assoc"], -1).astype(np.int32)
+    view = W.view_two_cameras(rm, obs, assoc=pre)
+    left, right, depth = _tracks(view, rig["pts"])
+    assert left["in_view"].sum() > 300 and right["in_view"].sum() > 300
+    ref, got = both(rm.search_by_projection_mappoints_stereo, view, rig["pts"], th, 0.8, left, right, pre, depth, far, 6.0)
+    same(ref, got, "SearchByProjection(Frame, MapPoints) two cameras")
+    nl = obs["n_left"]
+    new = (ref[1] >= 0) & (ref[1] != pre)
+    assert new[:nl].sum() > 100 and new[nl:].sum() > 100
+    # the integrated path (isInFrustum inside the harness, then the search)
+    ref2, got2 = both(rm.search_by_projection_mappoints, view, rig["pts"], th, 0.8, None, 0.5, pre)
+    same(ref2, got2, "SearchLocalPoints core, two cameras")
+
+
+def test_search_by_projection_two_cameras_crowded(rig):
+    """many map points per keypoint and map points without observations: claims get replaced through the partner hand-over"""
+    W, obs = rig["W"], rig["obs"]
+    rng = np.random.default_rng(17)
+    view = W.view_two_cameras(rm, obs)
+    left, right, depth = _tracks(view, rig["pts"])
+    # three copies of every map point (jittered projections, shuffled), a third of them without observations
+    rep = 3
+    order = rng.permutation(W.n * rep)
+    t3 = lambda a: np.tile(a, (rep,) + (1,) * (a.ndim - 1))[order]
+    n_obs = (rng.random(W.n * rep) < 0.66).astype(np.int32)
+    P = rm.Points(t3(W.P), t3(W.desc), t3(W.normal), t3(W.min_dist), t3(W.max_dist), n_obs, t3(W.bad))
+
+    def widen(f):
+        g = {k: t3(v) for k, v in f.items()}
+        g["proj_x"] = (g["proj_x"] + rng.normal(size=W.n * rep) * 1.5).astype(np.float32)
+        g["proj_y"] = (g["proj_y"] + rng.normal(size=W.n * rep) * 1.5).astype(np.float32)
+        return g
+    L, R = widen(left), widen(right)
+    ref, got = both(rm.search_by_projection_mappoints_stereo, view, P, 4.0, 0.9, L, R)
+    same(ref, got, "SearchByProjection two cameras, crowded")
+    assert ref[0] > 400
+
+
+@pytest.mark.parametrize("kf_two_cameras,ori", [(False, True), (True, True), (True, False)])
+def test_search_by_bow_two_cameras(rig, kf_two_cameras, ori):
+    """src/ORBmatcher.cc:338-431: the frame is a fisheye-stereo one; a keyframe feature may take a left and a right feature"""
+    import bowsynth
+    W, obs = rig["W"], rig["obs"]
+    fvF = bowsynth.feature_vector(obs["desc"], 40, seed=3)
+    frame = W.view_two_cameras(rm, obs, feat_vec=fvF)
+    R2, t2 = W.pose(seed=13)
+    if kf_two_cameras:
+        ko = W.observe_two_cameras(R2, t2, seed=40)
+        kf = W.view_two_cameras(rm, ko, assoc=ko["assoc"], feat_vec=bowsynth.feature_vector(ko["desc"], 40, seed=3))
+    else:
+        ko = W.observe(R2, t2, seed=41)
+        kf = W.view(rm, ko, assoc=ko["assoc"], feat_vec=bowsynth.feature_vector(ko["desc"], 40, seed=3))
+    ref, got = both(rm.search_by_bow_frame, kf, frame, rig["pts"], 0.7, ori)
+    same(ref, got, "SearchByBoW(KeyFrame, Frame) two cameras")
+    nl = obs["n_left"]
+    assert (ref[1][:nl] >= 0).sum() > 50 and (ref[1][nl:] >= 0).sum() > 50
+
+
+def test_is_in_frustum_checks_two_cameras(rig):
+    """Frame::isInFrustum on a fisheye-stereo frame (src/Frame.cc:643-660 -> isInFrustumChecks :1270-1343, both cameras): the device
+    kernel with the right camera's pose composed as :1274-1281 against the reference's compiled Frame.cc.  Fields are compared where the
+    reference wrote them (points in view).  Tolerance: the compiled reference calls libm's float atan2f / logf, the
+    kernel evaluates (float)atan2((double)..) / (float)log((double)..): decisions and predicted levels identical, projections within
+    2e-4 px; depth and viewing cosine (no transcendental involved) bit-equal."""
+    import importlib
+    pkg = importlib.import_module("3_orb_slam3_selfnote_b200")
+    pre_mod = importlib.import_module("3_orb_slam3_selfnote_b200.preproc")
+    W, obs = rig["W"], rig["obs"]
+    view = W.view_two_cameras(rm, obs)
+    t = rm.is_in_frustum(view, rig["pts"], 0.5, right=True)
+    cam = W.cam
+    fx, fy, cx, cy = cam["K"]
+    Tcw = obs["Tcw"]
+    left = pre_mod.frustum(Tcw[:3, :3], Tcw[:3, 3], fx, fy, cx, cy, W.bounds(), 0.0, W.scale, W.nlevels, 0.5, kb=cam["kb"])
+    right = pre_mod.frustum_right_camera(left, obs["Tlr"], fx, fy, cx, cy, kb=cam["kb"])
+    pre = pre_mod.Preprocessor()
+    try:
+        for g, sfx, px_key in ((left, "", "proj_x"), (right, "_r", "proj_xr_r")):
+            out = pre.isInFrustum(g, W.P, W.normal, W.max_dist, W.min_dist)
+            inv = t["in_view" + sfx] != 0
+            assert np.array_equal(out["in_view"] != 0, inv) and inv.sum() > 300
+            assert np.array_equal(out["level"][inv], t["level" + sfx][inv])
+            for ours, ref in ((out["proj_x"], t[px_key]), (out["proj_y"], t["proj_y" + sfx])):
+                d = np.abs(ours[inv] - ref[inv])
+                assert d.max() <= 2e-4
+            assert np.array_equal(out["depth"][inv].view(np.uint32), t["depth" + sfx][inv].view(np.uint32)), "depth" + sfx
+            assert np.array_equal(out["view_cos"][inv].view(np.uint32), t["view_cos" + sfx][inv].view(np.uint32)), "view_cos" + sfx
+    finally:
+        pre.close()

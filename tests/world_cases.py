@@ -141,6 +141,34 @@ class World:
         outlier = ((rng.random(n) < 0.05) & (assoc >= 0)).astype(np.uint8)
         return dict(kps=kps, desc=desc, u_right=ur, mp_idx=mp, assoc=assoc, outlier=outlier, Tcw=T_of(R, t), R=R, t=t)
 
+    def observe_two_cameras(self, R, t, seed=3, paired=0.7, baseline=0.11, **kw):
+        """A fisheye-STEREO frame (Frame.cc:1080-1262, Nleft != -1): the left camera at (R, t), the right one at Trl * Tcw with a
+        small relative rotation; the two keypoint sets stacked as the reference stacks them (mvKeys, mvKeysRight, descriptors
+        vconcat), and mvLeftToRightMatch / mvRightToLeftMatch linking keypoints that show the same map point (a `paired` share)."""
+        rng = np.random.default_rng(seed + 77)
+        Rrl = rodrigues(rng.normal(size=3) * 0.01)
+        trl = np.array([-baseline, 0.002, -0.001])
+        L = self.observe(R, t, seed=seed, **kw)
+        Rg = self.observe(Rrl @ R, Rrl @ t + trl, seed=seed + 1, **kw)
+        nl, nr = len(L["kps"]), len(Rg["kps"])
+        l2r, r2l = np.full(nl, -1, np.int32), np.full(nr, -1, np.int32)
+        where_r = {int(m): j for j, m in enumerate(Rg["mp_idx"]) if m >= 0}
+        for i, mpi in enumerate(L["mp_idx"]):
+            j = where_r.get(int(mpi), -1)
+            if mpi >= 0 and j >= 0 and rng.random() < paired:
+                l2r[i] = j; r2l[j] = i
+        Tlr = np.zeros((3, 4), np.float32)           # left <- right (Frame.cc:1186-1195 derives Trl from it)
+        Tlr[:, :3] = Rrl.T; Tlr[:, 3] = -(Rrl.T @ trl)
+        return dict(kps=L["kps"], kps_right=Rg["kps"], desc=np.vstack([L["desc"], Rg["desc"]]), n_left=nl, l2r=l2r, r2l=r2l, Tlr=Tlr,
+                    Tcw=L["Tcw"], mp_idx=np.concatenate([L["mp_idx"], Rg["mp_idx"]]), assoc=np.concatenate([L["assoc"], Rg["assoc"]]))
+
+    def view_two_cameras(self, rm, obs, assoc=None, feat_vec=None):
+        cam = self.cam
+        cam2 = (1 if "kb" in cam else 0,) + tuple(cam["K"]) + tuple(cam.get("kb", (0, 0, 0, 0)))
+        return rm.View(obs["kps"], obs["desc"], self.bounds(), K=cam["K"], scale_factor=self.scale, nlevels=self.nlevels, Tcw=obs["Tcw"],
+                       map_point_idx=assoc, kb=cam.get("kb"), kps_right=obs["kps_right"], n_left=obs["n_left"], cam2=cam2, Tlr=obs["Tlr"],
+                       left_to_right=obs["l2r"], right_to_left=obs["r2l"], feat_vec=feat_vec)
+
     def bounds(self):
         w, h = self.cam["size"]
         return (0.0, float(w), 0.0, float(h))
