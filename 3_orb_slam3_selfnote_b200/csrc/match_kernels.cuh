@@ -282,6 +282,8 @@ struct ResolveArgs {        // one per frame
   int anyMpBlocks;
   int checkOrientation;
   const int* partner;       // k_resolve_fisheye: stereo partner of each keypoint in the other image (-1 none), or null
+  const uint8_t* gateValid; // k_resolve_par: query i is searched only if the sibling job's query i was valid and had candidates
+  const int* gateCnt;       //   (right-camera pass of SearchByProjection(Frame, Frame), ORBmatcher.cc:2077-2124 `continue`s); or null
 };
 
 // SearchByProjection(Frame&, vector<MapPoint*>&, ...), ORBmatcher.cc:44-142, as a parallel fixed point.  The reference's loop is sequential only through the claims: map
@@ -322,7 +324,7 @@ k_resolve_par(const GridFrame* frames, const QuerySet* sets, const ResolveArgs* 
     int* nxt = A.blk[(it & 1) ^ 1];
     bool changed = false;
     for (int i = gwarp; i < Q.nq; i += nwarps) {
-      const int c = Q.qCnt[i];
+      const int c = (A.gateValid && (!A.gateValid[i] || A.gateCnt[i] == 0)) ? 0 : Q.qCnt[i];
       int choice = -1;
       if (c > 0) {
         const unsigned long long* e = Q.entries + Q.qOff[i];
@@ -399,6 +401,45 @@ k_resolve_par(const GridFrame* frames, const QuerySet* sets, const ResolveArgs* 
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
   if (lane == 0 && mine) atomicAdd(A.nmatches, mine);
+}
+
+// SearchByProjection(Frame& Cur, const Frame& Last, ...) on a fisheye-stereo current frame (ORBmatcher.cc:2027-2289): the left and the
+// right image are resolved as two k_resolve_par problems (claims never cross the images), but the rotation histogram is ONE
+// (:2176-2186 and :2240-2252 push into the same rotHist): this kernel runs after both, bins every match of both images, keeps
+// the three maxima and clears the rest (:2264-2283).  *args[0].nmatches receives the total.
+__global__ void __launch_bounds__(256) k_rotfilter_pair(const GridFrame* frames, const QuerySet* sets, const ResolveArgs* args, int checkOrientation) {
+  __shared__ int hist[30];
+  __shared__ int keep[3];
+  __shared__ int removedAll;
+  const int tid = threadIdx.x;
+  if (tid < 30) hist[tid] = 0;
+  if (tid == 0) removedAll = 0;
+  __syncthreads();
+  if (checkOrientation) {
+    for (int j = 0; j < 2; j++) {
+      const ResolveArgs A = args[j];
+      for (int i = tid; i < sets[j].nq; i += 256) {
+        const int ch = A.assigned[i];
+        if (ch >= 0) atomicAdd(&hist[rot_bin(A.angle[i], frames[j].kps[ch].angle)], 1);
+      }
+    }
+    __syncthreads();
+    if (tid == 0) { int i1, i2, i3; three_maxima(hist, 30, i1, i2, i3); keep[0] = i1; keep[1] = i2; keep[2] = i3; }
+    __syncthreads();
+    int removed = 0;
+    for (int j = 0; j < 2; j++) {
+      const ResolveArgs A = args[j];
+      for (int i = tid; i < sets[j].nq; i += 256) {
+        const int ch = A.assigned[i];
+        if (ch < 0) continue;
+        const int bin = rot_bin(A.angle[i], frames[j].kps[ch].angle);
+        if (bin != keep[0] && bin != keep[1] && bin != keep[2]) { A.kpMp[ch] = -1; removed++; }
+      }
+    }
+    atomicAdd(&removedAll, removed);
+    __syncthreads();
+  }
+  if (tid == 0) *args[0].nmatches = *args[0].nmatches + *args[1].nmatches - removedAll;
 }
 
 struct InitArgs {  // SearchForInitialization state, one per frame pair

@@ -113,7 +113,7 @@ struct HostQueries {
   bool gate = false; const float* invSigma2 = nullptr; int nSigma = 0;   // Fuse chi-square gate (xr = projected right coordinate)
 };
 
-enum ResolveKind { RESOLVE_NONE, RESOLVE_MAPPOINTS, RESOLVE_WINDOW, RESOLVE_INIT, RESOLVE_BEST, RESOLVE_FISHEYE };
+enum ResolveKind { RESOLVE_NONE, RESOLVE_MAPPOINTS, RESOLVE_WINDOW, RESOLVE_INIT, RESOLVE_BEST, RESOLVE_FISHEYE, RESOLVE_WINDOW_PAIR };
 
 struct WindowJob {
   // frame (host, or device when devKps != null)
@@ -126,6 +126,7 @@ struct WindowJob {
   int* kpMp = nullptr; int kpMpLen = 0;  // host in/out
   float nnratio = 0; int distTh = 100; int anyMpBlocks = 0; int checkOrientation = 0;
   const int* partner = nullptr;   // RESOLVE_FISHEYE: mvLeftToRightMatch (left job) / mvRightToLeftMatch (right job)
+  int gateJob = -1;               // RESOLVE_WINDOW_PAIR: this job's query i runs only if job gateJob's query i was valid with candidates
   // init search
   const orbx_frame_view* F1 = nullptr; float* prevMatched = nullptr; int* matches12 = nullptr;
   int* nmatches = nullptr;
@@ -194,7 +195,7 @@ __global__ void __launch_bounds__(256) k_project_points(const __grid_constant__ 
   }
   A.x[i] = u; A.y[i] = v;
   if (P.bounds_mode == 0) { if (u < P.min_x || u > P.max_x || v < P.min_y || v > P.max_y) return; }
-  else if (!(u >= P.min_x && u < P.max_x && v >= P.min_y && v < P.max_y)) return;
+  else if (P.bounds_mode == 1) { if (!(u >= P.min_x && u < P.max_x && v >= P.min_y && v < P.max_y)) return; }
   if (A.xr) A.xr[i] = __fsub_rn(u, __fmul_rn(P.bf, invz));
   float dist = 0.f;
   float o0 = 0.f, o1 = 0.f, o2 = 0.f;
@@ -425,8 +426,10 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
     Q.entries = at<unsigned long long>(m, o.entries); Q.entryCap = entryCap[j]; Q.entryCursor = at<int>(m, o.cursor);
     CK(cudaMemsetAsync(m->arena + o.cursor, 0, 4, st));
     maxQ = std::max(maxQ, nq);
-    if (kind == RESOLVE_MAPPOINTS || kind == RESOLVE_WINDOW || kind == RESOLVE_FISHEYE) {
+    if (kind == RESOLVE_MAPPOINTS || kind == RESOLVE_WINDOW || kind == RESOLVE_FISHEYE || kind == RESOLVE_WINDOW_PAIR) {
       ResolveArgs& A = rargs[j];
+      A.gateValid = J.gateJob >= 0 ? at<uint8_t>(m, off[J.gateJob].valid) : nullptr;
+      A.gateCnt = J.gateJob >= 0 ? at<int>(m, off[J.gateJob].qCnt) : nullptr;
       if (J.partner) CK(up(o.partner, J.partner, (size_t)G.n * 4));
       A.partner = J.partner ? at<int>(m, o.partner) : nullptr;
       if (J.observed) CK(up(o.observed, J.observed, nq));
@@ -435,7 +438,8 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
       A.observed = J.observed ? at<uint8_t>(m, o.observed) : nullptr;
       A.angle = J.angle ? at<float>(m, o.angle) : nullptr;
       A.kpMp = at<int>(m, o.kpMp); A.assigned = at<int>(m, o.assigned); A.nmatches = at<int>(m, o.nmatches);
-      A.nnratio = J.nnratio; A.distTh = J.distTh; A.anyMpBlocks = J.anyMpBlocks; A.checkOrientation = J.checkOrientation;
+      A.nnratio = J.nnratio; A.distTh = J.distTh; A.anyMpBlocks = J.anyMpBlocks;
+      A.checkOrientation = kind == RESOLVE_WINDOW_PAIR ? 0 : J.checkOrientation;   // pair: one histogram over both images, k_rotfilter_pair
       A.blk[0] = at<int>(m, o.blk0); A.blk[1] = at<int>(m, o.blk1); A.chg = at<int>(m, o.chg);
     } else if (kind == RESOLVE_BEST) {
       ResolveArgs& A = rargs[j];
@@ -480,6 +484,10 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
   } else if (kind == RESOLVE_WINDOW) {
     k_resolve_par<<<dim3(kParCluster, nj), kParThreads, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs), 1);
   }
+  else if (kind == RESOLVE_WINDOW_PAIR) {   // both images with the rotation filter deferred, then the shared histogram
+    k_resolve_par<<<dim3(kParCluster, nj), kParThreads, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs), 1);
+    k_rotfilter_pair<<<1, 256, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs), jobs[0].checkOrientation);
+  }
   else if (kind == RESOLVE_FISHEYE) k_resolve_fisheye<<<1, 32, (size_t)(frames[0].n + frames[1].n), st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs));
   else if (kind == RESOLVE_INIT) k_resolve_init<<<nj, 32, 0, st>>>(dFrames, dSets, at<InitArgs>(m, oArgs));
   else if (kind == RESOLVE_BEST && maxQ > 0) k_resolve_best<<<dim3((maxQ + 7) / 8, nj), 256, 0, st>>>(dSets, at<ResolveArgs>(m, oArgs));
@@ -490,7 +498,7 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
   for (int j = 0; j < nj; j++) {
     WindowJob& J = jobs[j];
     const Off& o = off[j];
-    if (kind == RESOLVE_MAPPOINTS || kind == RESOLVE_WINDOW || kind == RESOLVE_FISHEYE) {
+    if (kind == RESOLVE_MAPPOINTS || kind == RESOLVE_WINDOW || kind == RESOLVE_FISHEYE || kind == RESOLVE_WINDOW_PAIR) {
       CK(down(J.kpMp, o.kpMp, (size_t)std::min(frames[j].n, J.kpMpLen) * 4));
       CK(down(J.nmatches, o.nmatches, 4));
     } else if (kind == RESOLVE_INIT) {
@@ -960,6 +968,34 @@ int orbx_search_projected_window(orbx_matcher* m, const orbx_frame_view* F, cons
   J.nmatches = nmatches;
   *nmatches = 0;
   return run_window_jobs(m, jobs, RESOLVE_WINDOW);
+}
+
+int orbx_search_projected_window_stereo(orbx_matcher* m, const orbx_frame_view* left, const orbx_frame_view* right, const orbx_projection* projLeft,
+                                        const orbx_projection* projRight, const orbx_projection_points* pts, const float* angle,
+                                        const uint8_t* observed, int distTh, int checkOrientation, int* kpMp, int* nmatches) {
+  if (!m || !kpMp || !nmatches || !left || !right) return ORBX_ERR_ARG;
+  const orbx_frame_view* views[2] = {left, right};
+  const orbx_projection* projs[2] = {projLeft, projRight};
+  for (int s = 0; s < 2; s++) {
+    int rc = check_view(views[s], true);
+    if (rc != ORBX_OK) return rc;
+    if ((rc = check_projection(views[s], projs[s], pts)) != ORBX_OK) return rc;
+  }
+  if (checkOrientation && pts->n > 0 && !angle) return ORBX_ERR_ARG;
+  std::vector<WindowJob> jobs(2);
+  for (int s = 0; s < 2; s++) {
+    WindowJob& J = jobs[s];
+    J.F = views[s]; set_bounds(J, views[s]);
+    J.proj = projs[s]; J.pts = pts;
+    J.q.nq = pts->n; J.q.desc = pts->desc;
+    J.observed = observed; J.angle = angle;
+    J.kpMp = kpMp + (s == 0 ? 0 : left->n); J.kpMpLen = views[s]->n;
+    J.distTh = distTh; J.anyMpBlocks = 0; J.checkOrientation = checkOrientation;
+    J.nmatches = s == 0 ? nmatches : nullptr;
+    J.gateJob = s == 0 ? -1 : 0;
+  }
+  *nmatches = 0;
+  return run_window_jobs(m, jobs, RESOLVE_WINDOW_PAIR);
 }
 
 int orbx_search_projected_best(orbx_matcher* m, const orbx_frame_view* F, const orbx_projection* P, const orbx_projection_points* pts, int gate,

@@ -155,10 +155,9 @@ class ORBmatcher {
 #ifdef ORBX_WITH_OPENCV
   // ---- reference signatures with the projection prologue on the device ------------------------------------------------------
   // Project MapPoints tracked in last frame into the current frame and search matches (Tracking::TrackWithMotionModel),
-  // src/ORBmatcher.cc:2027-2289.  Monocular / rectified-stereo frames (Nleft == -1).
+  // src/ORBmatcher.cc:2027-2289, incl. fisheye-stereo frames (Nleft != -1: the right-image pass of :2188-2255).
   template <class FrameT>
   int SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame, const float th, const bool bMono) {
-    if (CurrentFrame.Nleft != -1 || LastFrame.Nleft != -1) throw std::runtime_error("ORBmatcher::SearchByProjection(Frame, Frame): fisheye stereo (Nleft != -1) is not offloaded");
     const cv::Mat Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3);   // :2038-2047, the reference's lines
     const cv::Mat tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
     const cv::Mat twc = -Rcw.t() * tcw;
@@ -173,22 +172,53 @@ class ORBmatcher {
     P.level_mode = 0; P.window_mode = bForward ? 1 : (bBackward ? 2 : 0); P.th = th;
     const int n = LastFrame.N;
     PointArrays A(n);
-    A.useOctave(); A.useAngle();
+    A.useOctave(); A.useAngle(); A.useObserved();
     for (int i = 0; i < n; i++) {
       auto* pMP = LastFrame.mvpMapPoints[i];
       if (!pMP || LastFrame.mvbOutlier[i]) continue;
       A.valid[i] = 1;
       A.setPos(i, pMP->GetWorldPos()); A.setDesc(i, pMP->GetDescriptor());
-      A.octave[i] = LastFrame.mvKeys[i].octave;
-      A.angle[i] = LastFrame.mvKeysUn[i].angle;
+      A.observed[i] = pMP->Observations() > 0;   // a keypoint given to a point without observations can be taken again (:2134-2136)
+      const bool lastLeft = LastFrame.Nleft == -1 || i < LastFrame.Nleft;                          // :2100-2101, :2169-2171
+      A.octave[i] = lastLeft ? LastFrame.mvKeys[i].octave : LastFrame.mvKeysRight[i - LastFrame.Nleft].octave;
+      A.angle[i] = LastFrame.Nleft == -1 ? LastFrame.mvKeysUn[i].angle : (lastLeft ? LastFrame.mvKeys[i].angle : LastFrame.mvKeysRight[i - LastFrame.Nleft].angle);
     }
-    return run_window(CurrentFrame, P, A, TH_HIGH, /*anyMpBlocks=*/false, mbCheckOrientation, [&](int k, int i) { CurrentFrame.mvpMapPoints[k] = LastFrame.mvpMapPoints[i]; });
+    if (CurrentFrame.Nleft == -1)
+      return run_window(CurrentFrame, P, A, TH_HIGH, /*anyMpBlocks=*/false, mbCheckOrientation, [&](int k, int i) { CurrentFrame.mvpMapPoints[k] = LastFrame.mvpMapPoints[i]; });
+    // fisheye-stereo current frame: left image = mvKeys, right image = mvKeysRight, searched with x3Dr = Rrl * x3Dc + trl (:2189-2192)
+    const int nl = CurrentFrame.Nleft, nr = CurrentFrame.N - nl;
+    DescHolder dd(CurrentFrame.mDescriptors, CurrentFrame.N);
+    orbx_frame_view L, R;
+    L.n = nl; L.keypoints = reinterpret_cast<const orbx_keypoint*>(CurrentFrame.mvKeys.data()); L.descriptors = dd.p; L.u_right = nullptr;
+    L.scale_factors = CurrentFrame.mvScaleFactors.data(); L.nlevels = (int)CurrentFrame.mvScaleFactors.size();
+    L.min_x = CurrentFrame.mnMinX; L.min_y = CurrentFrame.mnMinY; L.max_x = CurrentFrame.mnMaxX; L.max_y = CurrentFrame.mnMaxY;
+    R = L;
+    R.n = nr; R.keypoints = reinterpret_cast<const orbx_keypoint*>(CurrentFrame.mvKeysRight.data()); R.descriptors = dd.p + (size_t)nl * 32;
+    P.want_xr = 0;
+    orbx_projection PR = P;
+    PR.chain = 1; PR.depth_mode = 2; PR.bounds_mode = 2;
+    put3x3(CurrentFrame.mTrl.colRange(0, 3).rowRange(0, 3), PR.R2); put3(CurrentFrame.mTrl.col(3), PR.t2);
+    std::vector<int> kpMp(std::max(CurrentFrame.N, 1), -1);
+    for (int k = 0; k < CurrentFrame.N; k++) {
+      auto* p = CurrentFrame.mvpMapPoints[k];
+      kpMp[k] = !p ? -1 : (p->Observations() > 0 ? -2 : -3);
+    }
+    const orbx_projection_points pts = A.c();
+    int nmatches = 0;
+    orbx_shim::check(orbx_search_projected_window_stereo(m_, &L, &R, &P, &PR, &pts, A.angle.data(), A.observed.data(), TH_HIGH, mbCheckOrientation ? 1 : 0, kpMp.data(),
+                                                         &nmatches),
+                     "orbx_search_projected_window_stereo");
+    for (int k = 0; k < CurrentFrame.N; k++) {
+      if (kpMp[k] >= 0) CurrentFrame.mvpMapPoints[k] = LastFrame.mvpMapPoints[kpMp[k]];
+      else if (kpMp[k] == -1 && CurrentFrame.mvpMapPoints[k]) CurrentFrame.mvpMapPoints[k] = nullptr;
+    }
+    return nmatches;
   }
 
   // Project MapPoints seen in KeyFrame into the Frame and search matches (relocalisation), src/ORBmatcher.cc:2291-2413.
   template <class FrameT, class KeyFrameT, class MapPointT>
   int SearchByProjection(FrameT& CurrentFrame, KeyFrameT* pKF, const std::set<MapPointT*>& sAlreadyFound, const float th, const int ORBdist) {
-    if (CurrentFrame.Nleft != -1) throw std::runtime_error("ORBmatcher::SearchByProjection(Frame, KeyFrame): fisheye stereo (Nleft != -1) is not offloaded");
+    // (on a fisheye-stereo frame the reference searches the left image only here: GetFeaturesInArea without bRight, :2342; mvKeysUn = mvKeys)
     const cv::Mat Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3);   // :2295-2297
     const cv::Mat tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
     const cv::Mat Ow = -Rcw.t() * tcw;
@@ -225,12 +255,14 @@ class ORBmatcher {
     return search_scw(pKF, Scw, vpPoints, vpMatched, th, ratioHamming, /*cameraProject=*/false, [&](int k, int i) { vpMatchedKF[k] = vpPointsKFs[i]; });
   }
 
-  // Project MapPoints into KeyFrame and search for duplicated MapPoints, src/ORBmatcher.cc:1425-1662 (bRight = false).
+  // Project MapPoints into KeyFrame and search for duplicated MapPoints, src/ORBmatcher.cc:1425-1662, incl. the right camera of a
+  // fisheye-stereo keyframe (bRight: right pose, mpCamera2, mvKeysRight / mGridRight, descriptor rows and indices offset by NLeft).
   template <class KeyFrameT, class MapPointT>
   int Fuse(KeyFrameT* pKF, const std::vector<MapPointT*>& vpMapPoints, const float th = 3.0, const bool bRight = false) {
-    if (bRight || pKF->NLeft != -1) throw std::runtime_error("ORBmatcher::Fuse: fisheye stereo (bRight / NLeft != -1) is not offloaded");
-    const cv::Mat Rcw = pKF->GetRotation(), tcw = pKF->GetTranslation(), Ow = pKF->GetCameraCenter();   // :1436-1438
-    orbx_projection P = projection_of(Rcw, tcw, Ow, pKF->mpCamera);
+    const cv::Mat Rcw = bRight ? pKF->GetRightRotation() : pKF->GetRotation();   // :1431-1443
+    const cv::Mat tcw = bRight ? pKF->GetRightTranslation() : pKF->GetTranslation();
+    const cv::Mat Ow = bRight ? pKF->GetRightCameraCenter() : pKF->GetCameraCenter();
+    orbx_projection P = projection_of(Rcw, tcw, Ow, bRight ? pKF->mpCamera2 : pKF->mpCamera);
     keyframe_bounds(pKF, P);
     P.depth_mode = 1; P.invz_mode = 1; P.bf = pKF->mbf; P.want_xr = 1; P.range_mode = 1; P.normal_check = 1; P.level_mode = 1; P.window_mode = 3; P.th = th;
     P.log_scale_factor = pKF->mfLogScaleFactor; P.n_scale_levels = pKF->mnScaleLevels;
@@ -244,7 +276,22 @@ class ORBmatcher {
       A.setPos(i, pMP->GetWorldPos()); A.setDesc(i, pMP->GetDescriptor()); A.setRange(i, pMP); A.setNormal(i, pMP->GetNormal());
     }
     std::vector<int> bestIdx, bestDist;
-    run_best(*pKF, P, A, /*gate=*/true, pKF->mvInvLevelSigma2.data(), bestIdx, bestDist);
+    if (pKF->NLeft == -1) run_best(*pKF, P, A, /*gate=*/true, pKF->mvInvLevelSigma2.data(), bestIdx, bestDist);
+    else {   // :1563-1565: mvKeys or mvKeysRight; mvuRight is read with the image-local index (:1574), rows / results carry + NLeft (:1602, :1610)
+      const int off = bRight ? pKF->NLeft : 0;
+      const std::vector<cv::KeyPoint>& keys = bRight ? pKF->mvKeysRight : pKF->mvKeys;
+      DescHolder dd(pKF->mDescriptors, pKF->N);
+      orbx_frame_view v;
+      v.n = (int)keys.size(); v.keypoints = reinterpret_cast<const orbx_keypoint*>(keys.data()); v.descriptors = dd.p + (size_t)off * 32;
+      v.u_right = pKF->mvuRight.size() >= keys.size() && v.n > 0 ? pKF->mvuRight.data() : nullptr;
+      v.scale_factors = pKF->mvScaleFactors.data(); v.nlevels = (int)pKF->mvScaleFactors.size();
+      v.min_x = pKF->mnMinX; v.min_y = pKF->mnMinY; v.max_x = pKF->mnMaxX; v.max_y = pKF->mnMaxY;
+      bestIdx.assign(std::max(A.n, 1), -1); bestDist.assign(std::max(A.n, 1), 256);
+      const orbx_projection_points pts = A.c();
+      orbx_shim::check(orbx_search_projected_best(m_, &v, &P, &pts, 1, pKF->mvInvLevelSigma2.data(), bestIdx.data(), bestDist.data(), nullptr),
+                       "orbx_search_projected_best");
+      for (int i = 0; i < n; i++) if (bestIdx[i] >= 0) bestIdx[i] += off;
+    }
     int nFused = 0;
     for (int i = 0; i < n; i++) {   // the bookkeeping of :1626-1650 in the reference's order (it can change what later points see)
       MapPointT* pMP = vpMapPoints[i];
@@ -557,12 +604,13 @@ class ORBmatcher {
   // structure-of-arrays image of the map points a search walks over
   struct PointArrays {
     int n;
-    std::vector<uint8_t> valid, desc;
+    std::vector<uint8_t> valid, desc, observed;   // observed: Observations() > 0 of the point (it blocks the keypoint it takes); empty = all
     std::vector<float> pos, normal, maxD, minD, angle;
     std::vector<int> octave;
     explicit PointArrays(int n_) : n(n_), valid(std::max(n_, 1), 0), desc((size_t)std::max(n_, 1) * 32, 0), pos((size_t)std::max(n_, 1) * 3, 0.f) {}
     void useOctave() { octave.assign(std::max(n, 1), 0); }
     void useAngle() { angle.assign(std::max(n, 1), 0.f); }
+    void useObserved() { observed.assign(std::max(n, 1), 1); }
     void useRange() { maxD.assign(std::max(n, 1), 0.f); minD.assign(std::max(n, 1), 0.f); }
     void useNormal() { normal.assign((size_t)std::max(n, 1) * 3, 0.f); }
     void setPos(int i, const cv::Mat& p) { for (int k = 0; k < 3; k++) pos[3 * (size_t)i + k] = p.at<float>(k); }
@@ -605,7 +653,8 @@ class ORBmatcher {
     }
     const orbx_projection_points pts = A.c();
     int nmatches = 0;
-    orbx_shim::check(orbx_search_projected_window(m_, &fv.v, &P, &pts, A.angle.empty() ? nullptr : A.angle.data(), nullptr, distTh, anyMpBlocks ? 1 : 0,
+    orbx_shim::check(orbx_search_projected_window(m_, &fv.v, &P, &pts, A.angle.empty() ? nullptr : A.angle.data(),
+                                                  A.observed.empty() ? nullptr : A.observed.data(), distTh, anyMpBlocks ? 1 : 0,
                                                   checkOri ? 1 : 0, kpMp.data(), &nmatches, nullptr),
                      "orbx_search_projected_window");
     for (int k = 0; k < F.N; k++) {

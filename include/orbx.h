@@ -302,7 +302,8 @@ typedef struct orbx_projection {
   float kb[4];
   int proj_mode;         /* 0: mpCamera->project(x_c); 1: u = fx * (x * invz) + cx (SearchBySim3 :1853-1858) */
   float min_x, max_x, min_y, max_y;
-  int bounds_mode;       /* 0: Frame: u < min_x || u > max_x rejects (:2084-2087); 1: KeyFrame::IsInImage: min <= u < max */
+  int bounds_mode;       /* 0: Frame: u < min_x || u > max_x rejects (:2084-2087); 1: KeyFrame::IsInImage: min <= u < max;
+                            2: no test (right-camera pass of the Frame-Frame search, :2189-2192) */
   int depth_mode;        /* 0: reject invz < 0 (:2077); 1: reject z < 0 (:524, :1488, :1848); 2: no test (:2310-2312) */
   int invz_mode;         /* 0: invz = (float)(1.0 / z) (:2075, :1852); 1: invz = 1 / z in float (Fuse :1493) */
   float bf;
@@ -334,6 +335,16 @@ typedef struct orbx_projection_debug {   /* optional host outputs of the prologu
 int orbx_search_projected_window(orbx_matcher* m, const orbx_frame_view* F, const orbx_projection* proj, const orbx_projection_points* pts,
                                  const float* angle, const uint8_t* observed, int dist_th, int any_mp_blocks, int check_orientation,
                                  int* kp_mp, int* nmatches, const orbx_projection_debug* dbg);
+/* SearchByProjection(Frame& Cur, const Frame& Last, th, bMono) when Cur is a fisheye-stereo frame (Nleft != -1), :2027-2289: per point
+ * of the last frame the left-image search (proj_left, claims among left keypoints) and, only if that one got past its `continue`s
+ * (projection valid, window not empty: :2077-2124), the right-image search (:2188-2255) of x3Dr = Rrl * x3Dc + trl -- proj_right =
+ * proj_left with chain = 1, R2 / t2 = mTrl, depth_mode 2, bounds_mode 2 and, as the reference has it, the LEFT camera's model --
+ * over mvKeysRight / mGridRight with its own claims.  Both feed ONE rotation histogram.  kp_mp: [left->n + right->n], coded as for
+ * orbx_search_projected_window; any_mp_blocks = 0. */
+int orbx_search_projected_window_stereo(orbx_matcher* m, const orbx_frame_view* left, const orbx_frame_view* right,
+                                        const orbx_projection* proj_left, const orbx_projection* proj_right,
+                                        const orbx_projection_points* pts, const float* angle, const uint8_t* observed, int dist_th,
+                                        int check_orientation, int* kp_mp, int* nmatches);
 /* The independent best-keypoint search (orbx_search_window_best) behind the prologue: Fuse x2 (gate != 0 for the first
  * overload's chi-square test) and both passes of SearchBySim3. */
 int orbx_search_projected_best(orbx_matcher* m, const orbx_frame_view* F, const orbx_projection* proj, const orbx_projection_points* pts,

@@ -53,6 +53,19 @@ def test_search_by_projection_frame_frame(scene, mono, th, dt, ori):
         assert ref[0] > 50
 
 
+def test_search_by_projection_frame_frame_shared_points(scene):
+    """every map point is held by two keypoints of the last frame: the second query lands on the keypoint the first one took, and takes it
+    again when the point has no observations (:2134-2136) -- the count differs from the blocking case even where the final holders agree"""
+    W, A, B = scene["W"], scene["A"], scene["B"]
+    A2 = {k: np.concatenate([A[k], A[k]]) for k in ("kps", "desc", "u_right", "assoc", "outlier")}
+    A2["Tcw"] = A["Tcw"]
+    cur = W.view(rm, B, assoc=np.full(len(B["kps"]), -1, np.int32))
+    last = W.view(rm, A2, assoc=A2["assoc"], outlier=A2["outlier"])
+    ref, got = both(rm.search_by_projection_frame, cur, last, scene["pts"], 7.0, True, 0.9, True)
+    same(ref, got, "SearchByProjection(Frame, Frame), shared points")
+    assert ref[0] > (ref[1] >= 0).sum() + 20   # re-taken keypoints were counted twice
+
+
 @pytest.mark.parametrize("th,orb_dist,ori", [(10.0, 100, True), (3.0, 64, True), (10.0, 100, False)])
 def test_search_by_projection_frame_keyframe(scene, th, orb_dist, ori):
     """src/ORBmatcher.cc:2291-2413 (relocalisation)"""
@@ -271,3 +284,53 @@ def test_is_in_frustum_checks_two_cameras(rig):
             assert np.array_equal(out["view_cos"][inv].view(np.uint32), t["view_cos" + sfx][inv].view(np.uint32)), "view_cos" + sfx
     finally:
         pre.close()
+
+
+@pytest.mark.parametrize("mono,th,dz,ori", [(False, 7.0, 0.0, True), (False, 10.0, 0.6, True), (False, 7.0, -0.6, False), (True, 15.0, 0.0, True)])
+def test_search_by_projection_frame_frame_two_cameras(rig, mono, th, dz, ori):
+    """src/ORBmatcher.cc:2027-2289 with a fisheye-stereo current frame: the right-image pass (:2188-2255) is skipped where the left one hit
+    a `continue`, claims stay inside each image, one rotation histogram over both; the last frame is a two-camera frame too (octaves
+    and angles of its right keypoints, :2100-2101, :2169-2171)"""
+    W = rig["W"]
+    Ra, ta = W.pose(seed=14)
+    Rb, tb = W.pose(seed=15)
+    last = W.observe_two_cameras(Ra, ta, seed=50)
+    cur = W.observe_two_cameras(Rb, tb - np.array([0, 0, dz]), seed=52)
+    n = len(cur["assoc"])
+    pre = np.where(np.random.default_rng(6).random(n) < 0.1, cur["assoc"], -1).astype(np.int32)
+    for assoc in (np.full(n, -1, np.int32), pre):
+        vc = W.view_two_cameras(rm, cur, assoc=assoc)
+        vl = W.view_two_cameras(rm, last, assoc=last["assoc"])
+        ref, got = both(rm.search_by_projection_frame, vc, vl, rig["pts"], th, mono, 0.9, ori)
+        same(ref, got, "SearchByProjection(Frame, Frame) two cameras")
+        nl = cur["n_left"]
+        new = (ref[1] >= 0) & (ref[1] != assoc)
+        assert new[:nl].sum() > 50 and new[nl:].sum() > 50
+
+
+def test_search_by_projection_frame_keyframe_two_cameras(rig):
+    """src/ORBmatcher.cc:2291-2413 on a fisheye-stereo frame: the reference searches its left image only"""
+    W, obs = rig["W"], rig["obs"]
+    R2, t2 = W.pose(seed=16)
+    ko = W.observe(R2, t2, seed=60)
+    n = len(obs["assoc"])
+    pre = np.where(np.random.default_rng(8).random(n) < 0.2, obs["assoc"], -1).astype(np.int32)
+    cur = W.view_two_cameras(rm, obs, assoc=pre)
+    kf = W.view(rm, ko, assoc=ko["assoc"])
+    found = (np.random.default_rng(7).random(W.n) < 0.15).astype(np.uint8)
+    ref, got = both(rm.search_by_projection_keyframe, cur, kf, rig["pts"], found, 10.0, 100, 0.9, True)
+    same(ref, got, "SearchByProjection(Frame, KeyFrame) two cameras")
+    assert ref[0] > 50 and (ref[1][obs["n_left"]:] != pre[obs["n_left"]:]).sum() == 0
+
+
+@pytest.mark.parametrize("right,th", [(False, 3.0), (True, 3.0), (True, 6.5)])
+def test_fuse_two_cameras(rig, right, th):
+    """src/ORBmatcher.cc:1425-1662 on a fisheye-stereo keyframe: bRight selects the right pose, mpCamera2, mvKeysRight / mGridRight and
+    offsets descriptor rows and indices by NLeft"""
+    W, obs = rig["W"], rig["obs"]
+    kf = W.view_two_cameras(rm, obs, assoc=obs["assoc"])
+    cand = np.random.default_rng(3).permutation(W.n).astype(np.int32)
+    ref, got = both(rm.fuse, kf, rig["pts"], cand, th, right)
+    same(ref, got, "Fuse two cameras")
+    ev = ref[1]
+    assert ref[0] > 50 and (ev[:, 0] == 1).sum() > 30
