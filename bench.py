@@ -469,14 +469,32 @@ def allpairs_block(orbx, torch, dist, mt, rank, world, local, kf_total, desc_per
             raise AssertionError("allpairs: row %d of rank %d: got %s / %s, brute force %s / %s" % (r, rank, idx[r], dst[r], want_idx, want_d))
     total_pairs = float(world) * rows * (world * rows - desc_per_kf)
     roof, roof_probe = _popc_roof_pairs_per_s()
+    pps_gpu = total_pairs / world / (total_ms / 1e3)
+    # Which kernel folded: chunks of >= 2^26 pairs go to k_knn2_tc (tcgen05 kind::i8 on +-1 expanded bits: 256 int8 MACs = 512 integer
+    # operations per pair), smaller ones to the POPC kernel (orbx_knn2_chunk_device).  Tensor roof: dense int8 is twice the dense bf16 rate
+    # on this part (4.5 vs 2.25 POP/s nominal), so 2 x the cuBLAS bf16 throughput measured on this pool (MEASURED_PEAKS.json) is the yardstick.
+    chunk_pairs = float(rows) * (rows / max(int(st["nchunks"]), 1))
+    tensor = chunk_pairs >= float(1 << 26)
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            bf16_tf = float(json.load(f).get("bf16_tflops", 0.0)) or None
+    except Exception:
+        bf16_tf = None
+    i8_peak = 2.0 * bf16_tf if bf16_tf else 4500.0
+    tops = pps_gpu * 512.0 / 1e12
+    fold_name = "tensor pipe (k_knn2_tc fold)" if tensor else "popc issue (k_knn2 fold)"
     return {"workload": "allpairs_knn2_%dkf_x_%ddesc" % (kf_total, desc_per_kf), "keyframes": kf_total, "desc_per_kf": desc_per_kf,
             "comm_nranks_seen": int(st["world"]), "nchunks": int(st["nchunks"]), "pairs": total_pairs, "device_s": total_ms / 1e3, "wall_s": wall_ms / 1e3,
-            "pairs_per_s": total_pairs / (total_ms / 1e3), "pairs_per_s_per_gpu": total_pairs / world / (total_ms / 1e3),
-            "popc_roof_pairs_per_s_per_gpu": roof, "popc_roof_kind": "16 POPC/clk/SM x 148 SMs x max SM clock / 8 POPC per pair",
-            "popc_probe_pairs_per_s_per_gpu": roof_probe, "frac_of_popc_roof": total_pairs / world / (total_ms / 1e3) / roof,
+            "pairs_per_s": total_pairs / (total_ms / 1e3), "pairs_per_s_per_gpu": pps_gpu,
+            "fold_kernel": "k_knn2_tc (tcgen05.mma kind::i8, TMEM accumulators, bulk-copy operand ring)" if tensor else "k_knn2 (xor + popc)",
+            "roofline": {"bound": "tensor", "achieved": tops, "peak": i8_peak, "unit": "TOP/s (int8)", "frac": tops / i8_peak,
+                         "ops_per_pair": 512, "peak_kind": ("2 x measured dense bf16 (MEASURED_PEAKS.json)" if bf16_tf else "nominal dense int8"),
+                         "frac_of_nominal_4500": tops / 4500.0, "ncu": "profiles/r02_knn2_tc.md (tensor pipe active, SASS excerpt)"} if tensor else None,
+            "popc_roof_pairs_per_s_per_gpu": roof, "popc_roof_kind": "16 POPC/clk/SM x 148 SMs x max SM clock / 8 POPC per pair (what the xor+popc kernel is bound by)",
+            "popc_probe_pairs_per_s_per_gpu": roof_probe, "x_popc_roof": pps_gpu / roof,
             "fold_ms": fold_ms, "allgather_ms": gather_ms, "allgather_bytes_per_rank": float(st["gather_bytes"]), "overlap_frac": float(st["overlap_frac"]),
             "allgather_gbs_per_rank": (float(st["gather_bytes"]) / (gather_ms / 1e3) / 1e9) if gather_ms > 0 else None,
-            "limiter": "popc issue (k_knn2 fold)" if fold_ms >= gather_ms else "NVLink all-gather",
+            "limiter": fold_name if fold_ms >= gather_ms else "NVLink all-gather",
             "verified": "16 rows per rank equal a brute-force scan of all rows (index and distance, ties to the lower global row)"}
 
 
