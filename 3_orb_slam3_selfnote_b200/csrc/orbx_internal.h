@@ -65,6 +65,14 @@ struct orbx_extractor {
   bool profile = false;
   bool rs3ok = true;     // k_pyr_resize4 applies to this geometry (scale factor <= 2); otherwise k_pyr_resize2
   size_t rsSmem = 0;
+  // latency path of the host entry points (one small chunk, e.g. the reference's per-frame operator() call): page-locked staging
+  // for the frames and the results, and ONE CUDA graph holding upload + kernels + downloads
+  struct LatencyPath {
+    uint8_t* hIn = nullptr; size_t inBytes = 0;
+    uint8_t* hOut = nullptr; size_t outBytes = 0;
+    cudaGraphExec_t exec = nullptr;
+    int nb = 0, lap0 = 0, lap1 = 0; unsigned long long epoch = 0;
+  } lat;
 };
 
 

@@ -1464,6 +1464,11 @@ int orbx_stereo_frames_host(orbx_matcher* m, orbx_extractor* exL, orbx_extractor
   // Chunk schedule: the call's latency is upload(first chunk, left) + kernels + download(last chunk), and a chunk's kernel time
   // has a fixed part (~0.1 ms of short dependent kernels), so the first chunk is a quarter of the others.
   const int first = (nframes > B / 4 && B >= 8) ? B / 4 : B;
+  // on every return below (errors included) nothing may still be copying into the caller's buffers or hold the slot events open
+  struct Drain {
+    orbx_matcher* m; orbx_extractor* a; orbx_extractor* b;
+    ~Drain() { for (int k = 0; k < 2; k++) { cudaStreamSynchronize(a->slot[k].stream); cudaStreamSynchronize(b->slot[k].stream); } cudaStreamSynchronize(m->upStream); }
+  } drain{m, exL, exR};
   int chunk = 0;
   for (int f0 = 0; f0 < nframes; chunk++) {
     const int nb = std::min(chunk == 0 ? first : B, nframes - f0), si = chunk & 1;

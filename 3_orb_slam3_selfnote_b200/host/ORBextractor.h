@@ -8,8 +8,11 @@
 // layout-compatible stand-ins of cvlite.h are used (this image has no C++ OpenCV).
 //
 // Differences from the reference, all outside the observable contract of the path:
-//   * mvImagePyramid holds tight copies of the levels (no 19-px replicated frame around them; nothing reads it).  They are
-//     downloaded lazily by SyncPyramid() -- the GPU stereo matcher (host/ORBmatcher.h) reads the levels in HBM instead.
+//   * mvImagePyramid holds tight copies of the levels (no 19-px replicated frame around them; nothing reads it).  It is a live
+//     member: the levels are downloaded on first access after a call (operator[] / begin() / the vector conversion sync by
+//     themselves), so Frame::ComputeStereoMatches' `mpORBextractorLeft->mvImagePyramid[kpL.octave].rowRange(..)` (src/Frame.cc:
+//     908, 998, 1012) reads current pixels without any change at the call site; a caller that never touches the member never pays
+//     the copy -- the GPU stereo matcher (host/ORBmatcher.h) reads the levels in HBM instead.
 //   * the blur taps default to OpenCV 3.4.6's (ORBX_TAPS_OCV346); pass ORBX_TAPS_OCV4 to match an OpenCV >= 3.4.9 build.
 #pragma once
 #include <stdexcept>
@@ -51,7 +54,7 @@ class ORBextractor {
     orbx_get_scale_tables(h_, mvScaleFactor.data(), mvInvScaleFactor.data(), mvLevelSigma2.data(), mvInvLevelSigma2.data());
     mnFeaturesPerLevel.resize(nlevels);
     orbx_get_features_per_level(h_, mnFeaturesPerLevel.data());
-    mvImagePyramid.resize(nlevels);
+    mvImagePyramid.attach(this, nlevels);
   }
   ~ORBextractor() { orbx_destroy(h_); }
   ORBextractor(const ORBextractor&) = delete;
@@ -90,17 +93,36 @@ class ORBextractor {
   std::vector<float> inline GetScaleSigmaSquares() { return mvLevelSigma2; }
   std::vector<float> inline GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
 
-  // Host copies of the un-blurred levels of the last call (the reference's public member, ORBextractor.h:84).
-  std::vector<cvx::Mat> mvImagePyramid;
-  void SyncPyramid() {
+  // Host copies of the un-blurred levels of the last call (the reference's public member std::vector<cv::Mat> mvImagePyramid,
+  // ORBextractor.h:84), fetched from the device on first access after a call.
+  class Pyramid {
+   public:
+    typedef std::vector<cvx::Mat>::iterator iterator;
+    cvx::Mat& operator[](size_t l) { sync(); return levels_[l]; }
+    cvx::Mat& at(size_t l) { sync(); return levels_.at(l); }
+    size_t size() const { return levels_.size(); }
+    bool empty() const { return levels_.empty(); }
+    iterator begin() { sync(); return levels_.begin(); }
+    iterator end() { sync(); return levels_.end(); }
+    operator std::vector<cvx::Mat>&() { sync(); return levels_; }
+   private:
+    friend class ORBextractor;
+    void attach(ORBextractor* o, int n) { owner_ = o; levels_.resize(n); }
+    void sync() { owner_->SyncPyramid(); }
+    ORBextractor* owner_ = nullptr;
+    std::vector<cvx::Mat> levels_;
+  };
+  Pyramid mvImagePyramid;
+  void SyncPyramid() {   // explicit form of what the accessors above do
     if (!pyramidStale_) return;
+    pyramidStale_ = false;
     for (int l = 0; l < nlevels; l++) {
       int w = 0, hgt = 0;
       orbx_shim::check(orbx_pyramid_level(h_, 0, l, nullptr, 0, &w, &hgt), "orbx_pyramid_level");
-      mvImagePyramid[l].create(hgt, w, ORBX_MAT_8U);
-      orbx_shim::check(orbx_pyramid_level(h_, 0, l, mvImagePyramid[l].ptr(0), (int)mvImagePyramid[l].step, &w, &hgt), "orbx_pyramid_level");
+      cvx::Mat& m = mvImagePyramid.levels_[l];
+      m.create(hgt, w, ORBX_MAT_8U);
+      orbx_shim::check(orbx_pyramid_level(h_, 0, l, m.ptr(0), (int)m.step, &w, &hgt), "orbx_pyramid_level");
     }
-    pyramidStale_ = false;
   }
 
   orbx_extractor* handle() { return h_; }  // for host/ORBmatcher.h (device-resident stereo matching)

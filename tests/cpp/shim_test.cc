@@ -77,8 +77,10 @@ int main(int argc, char** argv) {
     fwrite(keys.data(), 28, n, out);
     for (int i = 0; i < n; i++) fwrite(desc.ptr(i), 1, 32, out);
     if (mono(cvx::Mat(), mask, keys, desc, lap) != -1) { fprintf(stderr, "empty image must return -1\n"); return 3; }
-    mono.SyncPyramid();
-    if (mono.mvImagePyramid.size() != 8 || mono.mvImagePyramid[1].cols != 627) { fprintf(stderr, "pyramid\n"); return 3; }
+    // the public member is live: reading a level right after operator() fetches it (src/Frame.cc:908,998,1012 do exactly this)
+    if (mono.mvImagePyramid.size() != 8 || mono.mvImagePyramid[1].cols != 627 || mono.mvImagePyramid[0].rows != H) { fprintf(stderr, "pyramid\n"); return 3; }
+    { const cvx::Mat& l0 = mono.mvImagePyramid[0];
+      for (int y = 0; y < H; y += 37) if (memcmp(l0.ptr(y), l.data() + (size_t)y * W, W) != 0) { fprintf(stderr, "pyramid level 0 pixels\n"); return 3; } }
     if (mono.GetLevels() != 8 || mono.GetScaleFactors().size() != 8) return 3;
 
     // --- stereo frame (src/Frame.cc:120-141)
