@@ -120,31 +120,39 @@ __global__ void __launch_bounds__(256, 5) k_fast_nms3(const __grid_constant__ Ge
   }
 
   // ---- 1. compass bound for every pair: every 9-arc holds one of (r0|r8) and one of (r4|r12)  =>  S <= Q
+  // The 8 rows of a warp (sr = warp + 8k; dealt round-robin: 8 consecutive rows per warp would avoid some bank conflicts of the
+  // gathers in steps 2 and 3 but measured 8 % slower -- busy rows cluster, the warps of a CTA finish unevenly) sit at constant
+  // offsets from the first one, so the loop is fully unrolled over two base pointers (every LDS carries an immediate offset) and the
+  // "row inside the region / column needed" tests are one precomputed bit per (lane, row) -- profiles/r02 showed 40 instructions per
+  // row here, 14 of them addressing and loop control.
   const uint32_t kBias = 0x01000100u;
   const uint32_t thrB = (uint32_t)g.minTh * 0x00010001u + kBias;
   uint16_t* const myList = sList[warp];
   int cnt = 0;   // warp-uniform
   {
-    const bool colNeeded = (ox - 1 + 2 * p) < maxX;
+    // rows below the region are never read as neighbours of a kept pixel; columns right of it neither
+    const int rowsIn = maxY - (oy - 1) - warp;                       // row k is inside  <=>  8k < rowsIn
+    const uint32_t rowMask = rowsIn <= 0 ? 0u : (rowsIn >= 57 ? 0xffu : ((1u << ((rowsIn + 7) >> 3)) - 1u));
+    const uint32_t need = ((ox - 1 + 2 * p) < maxX) ? rowMask : 0u;
     const uint32_t lt = (1u << p) - 1;
-    // rows are dealt to the warps round-robin: 8 consecutive rows per warp would avoid some bank conflicts of the gathers in
-    // steps 2 and 3, but was measured 8 % slower (busy rows cluster, the warps of a CTA finish unevenly)
-#pragma unroll 4
-    for (int sr = warp; sr < kF3SH; sr += 8) {
-      S[sr * kF3SPitch + p] = 0;
-      if (kF3SPitch > 32 && p == 0) S[sr * kF3SPitch + 32] = 0;
-      if (oy - 1 + sr >= maxY) continue;   // warp-uniform: rows below the region are never read as neighbours of a kept pixel
-      const int idx = (sr + 3) * kF3Pitch + p;
-      const int eI = eBase + idx, oI = oBase + idx;
-      const uint32_t v = f3ring<0, 0>(sW, eI, oI);
-      const uint32_t r0 = f3ring<0, 3>(sW, eI, oI), r8 = f3ring<0, -3>(sW, eI, oI);
-      const uint32_t r4 = f3ring<3, 0>(sW, eI, oI), r12 = f3ring<-3, 0>(sW, eI, oI);
+    const uint32_t* const pe = sW + eBase + (warp + 3) * kF3Pitch + p;
+    const uint32_t* const po = sW + oBase + (warp + 3) * kF3Pitch + p;
+    uint32_t* const Srow = S + warp * kF3SPitch + p;
+    uint32_t entry = (uint32_t)(warp * 32 + p);
+#pragma unroll
+    for (int k = 0; k < kF3SH / 8; k++) {
+      const int ro = 8 * k * kF3Pitch;
+      Srow[8 * k * kF3SPitch] = 0;
+      if (kF3SPitch > 32 && p == 0) Srow[8 * k * kF3SPitch + 32] = 0;
+      const uint32_t v = pe[ro];
+      const uint32_t r0 = pe[ro + 3 * kF3Pitch], r8 = pe[ro - 3 * kF3Pitch];
+      const uint32_t r4 = po[ro + 2], r12 = po[ro - 1];               // dx = +3 / -3 live in the other pair copy at (dx + 1) / 2
       const uint32_t hi = __vminu2(__vmaxu2(r0, r8), __vmaxu2(r4, r12));
       const uint32_t lo = __vmaxu2(__vminu2(r0, r8), __vminu2(r4, r12));
       const uint32_t q = __vmaxu2((hi + kBias) - v, (v + kBias) - lo);  // Q + 256 per half
-      const bool pass = colNeeded && (__vmaxu2(q, thrB) != thrB);
+      const bool pass = ((need >> k) & 1u) && (__vmaxu2(q, thrB) != thrB);
       const uint32_t m = __ballot_sync(ORBX_FULL, pass);
-      if (pass) myList[cnt + __popc(m & lt)] = (uint16_t)(sr * 32 + p);
+      if (pass) myList[cnt + __popc(m & lt)] = (uint16_t)(entry + 256 * k);
       cnt += __popc(m);
     }
   }
