@@ -220,7 +220,7 @@ def run_reference(args):
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 def extra_configs(orbx, synth, torch, stream, local, steps):
@@ -834,7 +834,7 @@ def run_orbx(args):
                         "working_set_mb_per_launch": 2 * B * (W * H + 2 * LEVEL_PIXELS) / 1e6, "cpu_affinity": affinity},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu, "allpairs": allpairs,
                 "extra": extras}
-        print(json.dumps(line), flush=True)
+        _emit(line)
     for w in workers:
         for o in w.buffers():
             o.close()
@@ -867,5 +867,16 @@ def main():
         run_orbx(args)
 
 
+def _emit(line):
+    """the ONE JSON line goes to the process's original stdout"""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+# Native libraries write to file descriptor 1 behind Python's back (NCCL prints its version banner there when the raw communicator of
+# the all-pairs sweep is created): the contract is ONE JSON line on stdout, so everything else is routed to stderr at fd level.
+_REAL_STDOUT = 1
 if __name__ == "__main__":
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     main()
