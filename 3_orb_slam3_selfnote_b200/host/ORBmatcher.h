@@ -416,7 +416,10 @@ class ORBmatcher {
   template <class KeyFrameT>
   int SearchForTriangulation(KeyFrameT* pKF1, KeyFrameT* pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t> >& vMatchedPairs,
                              const bool bOnlyStereo, const bool bCoarse = false) {
-    if (pKF1->mpCamera2 || pKF2->mpCamera2) throw std::runtime_error("ORBmatcher::SearchForTriangulation: fisheye stereo rigs are not offloaded");
+    // the gate is pCamera1->epipolarConstrain (:1146): Pinhole's epipolar-line distance runs on the device; KannalaBrandt8's triangulates the
+    // pair through cv::SVD (KannalaBrandt8.cpp:244-247, 340-399), which cannot be pinned without OpenCV -- refuse rather than approximate
+    if (pKF1->mpCamera2 || pKF2->mpCamera2 || pKF1->mpCamera->GetType() == 1 || pKF2->mpCamera->GetType() == 1)
+      throw std::runtime_error("ORBmatcher::SearchForTriangulation: KannalaBrandt8::epipolarConstrain (cv::SVD triangulation) is not offloaded");
     cv::Mat Cw = pKF1->GetCameraCenter();
     cv::Mat R2w = pKF2->GetRotation();
     cv::Mat t2w = pKF2->GetTranslation();

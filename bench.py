@@ -707,6 +707,26 @@ def run_orbx(args):
         torch.cuda.synchronize()
         return 8 * (64 << 20) / (p0.elapsed_time(p1) / 1e3) / 1e9
 
+    def probe_bidir(down_share):
+        """uploads and downloads at once, in the byte ratio of the workload (the e2e pipeline keeps both directions busy): GB/s of uploads"""
+        s2 = torch.cuda.Stream()
+        up_b, dn_b = 64 << 20, max(1 << 20, int((64 << 20) * down_share) & ~4095)
+        hd = orbx.HostBuffer((dn_b,), np.uint8)
+        dd = torch.empty(dn_b, dtype=torch.uint8, device="cuda")
+        p0, p1, p2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        p0.record(stream)
+        s2.wait_event(p0)
+        for _ in range(8):
+            rt.cudaMemcpyAsync(C.c_void_p(probe_d.data_ptr()), probe_h.ptr, C.c_size_t(up_b), C.c_int(1), C.c_void_p(sh))
+            rt.cudaMemcpyAsync(hd.ptr, C.c_void_p(dd.data_ptr()), C.c_size_t(dn_b), C.c_int(2), C.c_void_p(s2.cuda_stream))
+        p1.record(stream)
+        p2.record(s2)
+        torch.cuda.synchronize()
+        ms = max(p0.elapsed_time(p1), p0.elapsed_time(p2))
+        hd.close()
+        return 8 * up_b / (ms / 1e3) / 1e9
+
     link = {}
     for r in range(world):              # one rank at a time
         if world > 1:
@@ -719,13 +739,17 @@ def run_orbx(args):
         hc = probe(1)
         dist.barrier()
         dc = probe(2)
-        t = torch.tensor([hc, dc, link["h2d"], link["d2h"]], device="cuda", dtype=torch.float64)
+        dist.barrier()
+        bd = probe_bidir((((2 if right_records else 1) * cap * 60 + cap * 8 + 8)) / float(2 * W * H))
+        t = torch.tensor([hc, dc, link["h2d"], link["d2h"], bd], device="cuda", dtype=torch.float64)
         tsum = t.clone()
         dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
         tmin = t.clone()
         dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
         link_conc = {"h2d_sum_gbs": float(tsum[0]), "d2h_sum_gbs": float(tsum[1]), "h2d_min_rank_gbs": float(tmin[0]),
-                     "h2d_alone_sum_gbs": float(tsum[2]), "d2h_alone_sum_gbs": float(tsum[3])}
+                     "h2d_alone_sum_gbs": float(tsum[2]), "d2h_alone_sum_gbs": float(tsum[3]),
+                     "h2d_sum_gbs_with_downloads": float(tsum[4]),
+                     "note": "all ranks copying at once; *_with_downloads = uploads while every rank also downloads in the workload's byte ratio"}
     del probe_d
     probe_h.close()
     for wi, w in enumerate(workers):   # every worker's last call must equal the device-resident results, all of them
@@ -747,7 +771,7 @@ def run_orbx(args):
            "link_gbs_measured": {k: round(v, 2) for k, v in link.items()},
            "link_bound_frames_per_s": world * B / (h2d_call / (link["h2d"] * 1e9)),
            "link_concurrent": link_conc,
-           "link_bound_frames_per_s_concurrent": (link_conc["h2d_sum_gbs"] * 1e9 / (2 * W * H)) if link_conc else None}
+           "link_bound_frames_per_s_concurrent": (link_conc["h2d_sum_gbs_with_downloads"] * 1e9 / (2 * W * H)) if link_conc else None}
 
     # informational: mono extraction only at the shape the north-star target is quoted on (752x480, nFeatures 1000), device-resident and
     # end to end through orbx_extract_batch_host
