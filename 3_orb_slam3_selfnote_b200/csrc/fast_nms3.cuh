@@ -22,6 +22,7 @@
 #pragma once
 #include "dev_common.cuh"
 #include "geom.h"
+#include "orbx_internal.h"
 
 namespace orbx {
 
@@ -33,6 +34,18 @@ constexpr int kF3RowsPerWarp = (kF3WinH + 7) / 8;
 constexpr int kF3Copy = kF3WinH * kF3Pitch;   // words per pair copy
 constexpr int kF3SPitch = 32, kF3SSlack = 34; // score rows: 32 pair words (33 = one pad word: fewer conflicts in step 3, measured 3 % slower); slack before / after the tile
 constexpr int kF3OutCap = 1024;               // kept pixels per tile: 3x3 local maxima, at most one per 2x2 block (961)
+constexpr int kF3RawW = 96;                   // bytes per raw window row fetched by the TMA path: the box must start on a 16-byte boundary of the
+                                              // row (measured: any other inner coordinate raises "illegal instruction", tools/microbench/
+                                              // tma_window.cu), so up to 12 bytes of lead-in + 19 words + the byte lane 18 borrows
+constexpr int kF3RawBytes = kF3WinH * kF3RawW;
+
+// One tensor map per pyramid level over (x, y, frame) of the un-blurred level, encoded on the host (orbx_extract.cu): the TMA path
+// of step 0 fetches a tile's 96 x 70 byte window with ONE cp.async.bulk.tensor instruction issued by one thread while the CTA
+// sets up its cell tables -- no per-lane address arithmetic, row / column clamps or shuffles, and rows / columns outside the
+// level arrive as zeros (they are never read for a pixel that can be kept).
+// (struct FastMaps { alignas(64) unsigned char m[kFastMapLevels][128]; } lives in orbx_internal.h: CUtensorMap = 128 opaque bytes)
+
+__device__ __forceinline__ uint32_t f3smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // ring pixel pair (DX, DY) of the pair whose centre word is at eIdx (even dx) / oIdx (odd dx); both are word indices into sW
 template <int DX, int DY>
@@ -42,15 +55,22 @@ __device__ __forceinline__ uint32_t f3ring(const uint32_t* sW, int eIdx, int oId
   return sW[eIdx + DY * kF3Pitch + DX / 2];
 }
 
-__global__ void __launch_bounds__(256, 5) k_fast_nms3(const __grid_constant__ Geom g, const __grid_constant__ Batch b) {
+template <bool kTma>
+__global__ void __launch_bounds__(256, 5) k_fast_nms3(const __grid_constant__ Geom g, const __grid_constant__ Batch b, const __grid_constant__ FastMaps tm) {
   // pair copy A = (col 2j, 2j+1) at [0, kF3Copy), copy B = (col 2j+1, 2j+2) at [kF3Copy, 2 kF3Copy), columns relative to the
   // aligned window origin; after step 2 the same memory holds the kept pixels of the tile
   __shared__ __align__(16) uint32_t sW[2 * kF3Copy];
-  __shared__ uint32_t sS[kF3SH * kF3SPitch + 2 * kF3SSlack];  // 64x64 scores as u16 pairs (+1 pad word per row), slack words each side
+  // 64x64 scores as u16 pairs (+1 pad word per row), slack words each side.  The TMA path lands the raw window here first (it is dead once
+  // the pair copies are built, and the scores are not written before that): the kernel keeps its 34.5 KB, so five CTAs still leave room
+  // for the other extractor's kernels on the SM (a separate 6.7 KB raw buffer cost 2.4 % of the two-stream step, measured)
+  __shared__ __align__(128) uint32_t sS[kF3SH * kF3SPitch + 2 * kF3SSlack];
+  static_assert(sizeof(uint32_t) * (kF3SH * kF3SPitch + 2 * kF3SSlack) >= kF3RawBytes, "the raw window must fit the score array");
   __shared__ uint16_t sList[8][kF3SH * 32 / 8];               // per warp: surviving pairs of its rows, sr * 32 + p
   __shared__ uint16_t sCol[kF3SW], sRow[kF3SH];               // cell info of the tile's columns / rows
   __shared__ uint32_t sMask[3][32];                           // per pair column: left / right neighbour masks, valid halves
   __shared__ int sNOut, sBase;
+  uint8_t* const sRaw = reinterpret_cast<uint8_t*>(sS);         // TMA path: the raw window (see sS)
+  __shared__ __align__(8) unsigned long long sBar;
 
   const int tid = threadIdx.x, warp = tid >> 5, p = tid & 31;
   const int f = blockIdx.y;
@@ -65,9 +85,17 @@ __global__ void __launch_bounds__(256, 5) k_fast_nms3(const __grid_constant__ Ge
   const uint8_t* src = level_ptr(g, b, level, f, sp);
   uint32_t* const S = sS + kF3SSlack;   // score pair (sr, q) at S[sr * kF3SPitch + q]
 
+  if (kTma && tid == 0) {
+    const uint32_t bar = f3smem(&sBar);
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(kF3RawBytes) : "memory");
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 :: "r"(f3smem(sRaw)), "l"(reinterpret_cast<unsigned long long>(&tm.m[level & (kFastMapLevels - 1)][0])), "r"(gx0 & ~15), "r"(wy0), "r"(f), "r"(bar) : "memory");
+  }
   if (tid == 0) sNOut = 0;
   // slack and pad words are read as (masked) neighbours: they must stay <= 255 per half or the packed compare borrows
-  if (tid < kF3SSlack) { sS[tid] = 0; sS[kF3SSlack + kF3SH * kF3SPitch + tid] = 0; }
+  if (!kTma && tid < kF3SSlack) { sS[tid] = 0; sS[kF3SSlack + kF3SH * kF3SPitch + tid] = 0; }   // (TMA path: after the raw window is consumed)
   if (tid < kF3SW) {
     const int x = ox - 1 + tid;
     sCol[tid] = (x >= kEdge && x < maxX) ? b.info[L.colInfoOff + x] : (uint16_t)0;
@@ -76,8 +104,30 @@ __global__ void __launch_bounds__(256, 5) k_fast_nms3(const __grid_constant__ Ge
     sRow[tid - kF3SW] = (y >= kEdge && y < maxY) ? b.info[L.rowInfoOff + y] : (uint16_t)0;
   }
 
-  // ---- 0. stage the window as two u16-pair copies (all loads first)
-  {
+  // ---- 0. stage the window as two u16-pair copies
+  if (kTma) {
+    __syncthreads();   // the barrier object is initialised (and the cell tables above are written) before anybody polls it
+    {
+      const uint32_t bar = f3smem(&sBar);
+      uint32_t done = 0;
+      while (!done)
+        asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], 0;\n\tselp.u32 %0, 1, 0, P1;\n\t}" : "=r"(done) : "r"(bar) : "memory");
+    }
+    const uint32_t* raw = reinterpret_cast<const uint32_t*>(sRaw) + ((gx0 >> 2) & 3) + p;   // skip the lead-in words of the 16-byte aligned box
+#pragma unroll
+    for (int k = 0; k < kF3RowsPerWarp; k++) {
+      const int r = warp + 8 * k;
+      if (r < kF3WinH && p < 19) {
+        const uint32_t u = raw[r * (kF3RawW / 4)];
+        const uint32_t un = raw[r * (kF3RawW / 4) + 1] & 0xffu;   // first byte of the next word
+        uint2 va, vb;
+        va.x = __byte_perm(u, 0u, 0x4140); va.y = __byte_perm(u, 0u, 0x4342);
+        vb.x = __byte_perm(u, 0u, 0x4241); vb.y = __byte_perm(u, un, 0x5453);
+        *reinterpret_cast<uint2*>(&sW[r * kF3Pitch + 2 * p]) = va;
+        *reinterpret_cast<uint2*>(&sW[kF3Copy + r * kF3Pitch + 2 * p]) = vb;
+      }
+    }
+  } else {   // levels whose base / pitch is not 16-byte aligned (odd image widths): per-lane loads, all of a warp in flight before the first use
     const int gx = min(gx0 + 4 * p, sp - 4);
     const uint8_t* colp = src + gx;
     uint32_t w[kF3RowsPerWarp];
@@ -108,6 +158,7 @@ __global__ void __launch_bounds__(256, 5) k_fast_nms3(const __grid_constant__ Ge
   const int eBase = (a & 1) ? (3 + a) / 2 : kF3Copy + 1 + a / 2;
   const int oBase = (a & 1) ? kF3Copy + (a + 1) / 2 : a / 2 + 1;
   __syncthreads();
+  if (kTma && tid < kF3SSlack) { sS[tid] = 0; sS[kF3SSlack + kF3SH * kF3SPitch + tid] = 0; }   // read first in step 3, two barriers from here
   if (tid < 32) {
     // the left neighbour of a first-column pixel and the right neighbour of a last-column pixel belong to another cell;
     // halves outside the tile's 62 output columns or outside the region are never kept

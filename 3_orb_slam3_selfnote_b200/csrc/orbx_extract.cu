@@ -1,6 +1,7 @@
 // Host side of the extractor: handle, geometry/tables, workspaces, stream orchestration, and the extern "C" entry points
 // declared in include/orbx.h.  All pixel / keypoint arithmetic happens in the kernels of extract_kernels.cuh; this file
 // only sizes buffers, fills the small lookup tables and enqueues launches.  There is no CPU fallback.
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdio.h>
@@ -269,6 +270,37 @@ int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
 }
 
 // Enqueue one device batch on `st` using the workspaces of slot `si`.
+namespace {
+// Tensor maps of the FAST kernel's TMA staging (fast_nms3.cuh): one per level over (x, y, frame) of the un-blurred level, u8, box
+// 96 x 70 x 1, no swizzle, zero fill outside.  cuTensorMapEncodeTiled comes from the driver through the runtime (no -lcuda).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) { cudaGetLastError(); p = nullptr; }
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+// false when the level cannot be described (base or strides not 16-byte aligned, or no driver entry point): the caller then launches the per-lane path
+bool encode_level_map(void* out, const uint8_t* base, int w, int h, int pitch, long long frameStride, int nframes) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn || ((uintptr_t)base & 15) || (pitch & 15) || (frameStride & 15) || w < 1 || h < 1 || nframes < 1) return false;
+  static_assert(sizeof(CUtensorMap) == 128, "CUtensorMap size");
+  const cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)nframes};
+  const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)(nframes > 1 ? frameStride : (long long)pitch * h)};
+  const cuuint32_t box[3] = {(cuuint32_t)orbx::kF3RawW, (cuuint32_t)orbx::kF3WinH, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  CUtensorMap m;
+  if (fn(&m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+         CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return false;
+  memcpy(out, &m, sizeof m);
+  return true;
+}
+}  // namespace
+
 int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int nframes, int pitch, long long frameStride, int lap0, int lap1,
                      cudaStream_t st) {
   Slot& s = h->slot[si];
@@ -306,7 +338,19 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
     }
   }
   mark(2);
-  if (g.nTilesTotal > 0) k_fast_nms3<<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b);
+  if (g.nTilesTotal > 0) {
+    // TMA staging when every level can be described by a tensor map (16-byte aligned base / pitch / frame stride: always for the staged
+    // host path and the usual image widths); the maps of the slab levels are encoded once per slot and geometry, level 0 per call
+    if (s.mapsEpoch != h->geomEpoch + 1) {
+      s.mapsOk = g.nlevels <= kFastMapLevels;
+      for (int l = 1; l < g.nlevels && s.mapsOk; l++)
+        s.mapsOk = encode_level_map(s.maps.m[l], s.pyr + g.lv[l].pyrOff, g.lv[l].w, g.lv[l].h, g.lv[l].pitch, h->pyrFrame, h->p.max_batch);
+      s.mapsEpoch = h->geomEpoch + 1;
+    }
+    const bool tma = s.mapsOk && encode_level_map(s.maps.m[0], dIn, g.lv[0].w, g.lv[0].h, pitch, frameStride, nframes);
+    if (tma) k_fast_nms3<true><<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b, s.maps);
+    else k_fast_nms3<false><<<dim3(g.nTilesTotal, nframes), 256, 0, st>>>(gg, b, s.maps);
+  }
   mark(3);
   k_quadtree<<<dim3(g.nlevels, nframes), 256, h->qtSmem, st>>>(gg, b, s.nCand);
   mark(4);

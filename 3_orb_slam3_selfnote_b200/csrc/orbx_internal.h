@@ -8,6 +8,10 @@
 
 #include "geom.h"
 
+// tensor maps of the FAST kernel (fast_nms3.cuh), passed as a kernel parameter: 8 levels (the reference's setting) keep the parameter block
+// below the classic 4 KB; extractors with more levels use the per-lane staging path
+namespace orbx { constexpr int kFastMapLevels = 8; struct FastMaps { alignas(64) unsigned char m[kFastMapLevels][128]; }; }
+
 namespace orbx {
 void set_error(const char* fmt, ...);
 // Process-wide lock around the rare host-side set-up sections of every handle (allocation / free, function attributes,
@@ -41,6 +45,8 @@ struct Slot {
   int lastFrames = 0;
   cudaEvent_t ev[8] = {};  // stage boundaries (profiling mode only)
   bool evValid = false;
+  FastMaps maps{};         // TMA descriptors of the un-blurred levels (levels >= 1 valid while mapsEpoch == geomEpoch + 1)
+  unsigned long long mapsEpoch = 0; bool mapsOk = false;
 };
 
 }  // namespace orbx
