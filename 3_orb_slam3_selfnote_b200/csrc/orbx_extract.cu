@@ -285,13 +285,13 @@ EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 // false when the level cannot be described (base or strides not 16-byte aligned, or no driver entry point): the caller then launches the per-lane path
-bool encode_level_map(void* out, const uint8_t* base, int w, int h, int pitch, long long frameStride, int nframes) {
+bool encode_level_map(void* out, const uint8_t* base, int w, int h, int pitch, long long frameStride, int nframes, int boxW = orbx::kF3RawW, int boxH = orbx::kF3WinH) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn || ((uintptr_t)base & 15) || (pitch & 15) || (frameStride & 15) || w < 1 || h < 1 || nframes < 1) return false;
   static_assert(sizeof(CUtensorMap) == 128, "CUtensorMap size");
   const cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)nframes};
   const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)(nframes > 1 ? frameStride : (long long)pitch * h)};
-  const cuuint32_t box[3] = {(cuuint32_t)orbx::kF3RawW, (cuuint32_t)orbx::kF3WinH, 1};
+  const cuuint32_t box[3] = {(cuuint32_t)boxW, (cuuint32_t)boxH, 1};
   const cuuint32_t estr[3] = {1, 1, 1};
   CUtensorMap m;
   if (fn(&m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<uint8_t*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
@@ -345,6 +345,12 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
       s.mapsOk = g.nlevels <= kFastMapLevels;
       for (int l = 1; l < g.nlevels && s.mapsOk; l++)
         s.mapsOk = encode_level_map(s.maps.m[l], s.pyr + g.lv[l].pyrOff, g.lv[l].w, g.lv[l].h, g.lv[l].pitch, h->pyrFrame, h->p.max_batch);
+      s.omapsOk = s.mapsOk;
+      for (int l = 0; l < g.nlevels && s.omapsOk; l++) {
+        s.omapsOk = encode_level_map(s.omaps.blur[l], s.blur + g.lv[l].blurOff, g.lv[l].w, g.lv[l].h, g.lv[l].blurPitch, h->blurFrame, h->p.max_batch, kOdBoxW, kOdRows);
+        if (l > 0 && s.omapsOk)
+          s.omapsOk = encode_level_map(s.omaps.raw[l], s.pyr + g.lv[l].pyrOff, g.lv[l].w, g.lv[l].h, g.lv[l].pitch, h->pyrFrame, h->p.max_batch, kOmBoxW, kPatch);
+      }
       s.mapsEpoch = h->geomEpoch + 1;
     }
     const bool tma = s.mapsOk && encode_level_map(s.maps.m[0], dIn, g.lv[0].w, g.lv[0].h, pitch, frameStride, nframes);
@@ -358,7 +364,9 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
   mark(5);
   k_assemble<<<nframes, 256, 0, st>>>(gg, b);
   mark(6);
-  k_orient_desc2<<<dim3((g.kpSlab + 7) / 8, nframes), 256, 0, st>>>(gg, b);
+  if (g.nTilesTotal > 0 && s.omapsOk && encode_level_map(s.omaps.raw[0], dIn, g.lv[0].w, g.lv[0].h, pitch, frameStride, nframes, kOmBoxW, kPatch))
+    k_orient_desc2<true><<<dim3((g.kpSlab + 7) / 8, nframes), 256, 0, st>>>(gg, b, s.omaps);
+  else k_orient_desc2<false><<<dim3((g.kpSlab + 7) / 8, nframes), 256, 0, st>>>(gg, b, s.omaps);
   mark(7);
   s.evValid = prof;
   CK(cudaGetLastError());

@@ -10,7 +10,11 @@
 
 // tensor maps of the FAST kernel (fast_nms3.cuh), passed as a kernel parameter: 8 levels (the reference's setting) keep the parameter block
 // below the classic 4 KB; extractors with more levels use the per-lane staging path
-namespace orbx { constexpr int kFastMapLevels = 8; struct FastMaps { alignas(64) unsigned char m[kFastMapLevels][128]; }; }
+namespace orbx {
+constexpr int kFastMapLevels = 8;
+struct FastMaps { alignas(64) unsigned char m[kFastMapLevels][128]; };
+struct OrientMaps { alignas(64) unsigned char raw[kFastMapLevels][128]; alignas(64) unsigned char blur[kFastMapLevels][128]; };   // k_orient_desc2's patch boxes
+}
 
 namespace orbx {
 void set_error(const char* fmt, ...);
@@ -47,6 +51,7 @@ struct Slot {
   bool evValid = false;
   FastMaps maps{};         // TMA descriptors of the un-blurred levels (levels >= 1 valid while mapsEpoch == geomEpoch + 1)
   unsigned long long mapsEpoch = 0; bool mapsOk = false;
+  OrientMaps omaps{}; bool omapsOk = false;
 };
 
 }  // namespace orbx

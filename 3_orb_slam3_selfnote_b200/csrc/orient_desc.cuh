@@ -15,6 +15,7 @@
 #include "dev_common.cuh"
 #include "extract_kernels.cuh"
 #include "geom.h"
+#include "orbx_internal.h"
 
 namespace orbx {
 
@@ -48,9 +49,19 @@ __device__ __forceinline__ void od_stage(const uint8_t* rowPtr0, int pitch, uint
     if (lane < 3 * WORDS && 3 * k + r3 < ROWS) dst[3 * WORDS * k + lane] = wv[k];
 }
 
-__global__ void __launch_bounds__(256) k_orient_desc2(const __grid_constant__ Geom g, const __grid_constant__ Batch b) {
-  __shared__ uint32_t sPatch[8][kOdRows * kOdWords];   // blurred 37x37 patch (rBRIEF samples)
-  __shared__ uint32_t sRaw[8][kPatch * kOmWords];       // un-blurred 31x31 patch (moments)
+// TMA staging (kTma): lane 0 of the warp fetches both patches with one cp.async.bulk.tensor.3d each -- boxes of 48 x 31 (raw) and 64 x 37
+// (blurred) bytes starting on the 16-byte boundary at or before the patch's first column (the inner coordinate of a tensor copy must be a
+// multiple of 16 bytes) -- onto a per-warp mbarrier; the 24 + 24 load / store instructions of od_stage and their L1 wavefronts disappear
+// (the kernel is L1 / shared-memory bound).  Maps: OrientMaps, encoded on the host like FastMaps.
+constexpr int kOmBoxW = 48, kOdBoxW = 64;
+constexpr int kOmBoxBytes = (kOmBoxW * kPatch + 127) & ~127, kOdBoxBytes = (kOdBoxW * kOdRows + 127) & ~127;
+
+template <bool kTma>
+__global__ void __launch_bounds__(256) k_orient_desc2(const __grid_constant__ Geom g, const __grid_constant__ Batch b, const __grid_constant__ OrientMaps tm) {
+  constexpr int kRawPitch = kTma ? kOmBoxW : kOmWords * 4, kBlurPitch = kTma ? kOdBoxW : kOdWords * 4;   // bytes per staged row
+  __shared__ __align__(128) uint8_t sPatchB[8][kTma ? kOdBoxBytes : kOdRows * kOdWords * 4];   // blurred 37x37 patch (rBRIEF samples)
+  __shared__ __align__(128) uint8_t sRawB[8][kTma ? kOmBoxBytes : kPatch * kOmWords * 4];       // un-blurred 31x31 patch (moments)
+  __shared__ __align__(8) unsigned long long sBar[8];
   const int f = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int slot = blockIdx.x * 8 + warp;
   if (slot >= g.kpSlab) return;
@@ -61,27 +72,51 @@ __global__ void __launch_bounds__(256) k_orient_desc2(const __grid_constant__ Ge
   if (i >= b.lkpCount[f * ORBX_MAX_LEVELS + level]) return;
   const LevelKp kp = b.lkp[(long long)f * g.kpSlab + slot];
   const int dest = b.lkpDest[(long long)f * g.kpSlab + slot];
-  int sp;
-  const uint8_t* img = level_ptr(g, b, level, f, sp);
-  // both patches start at the aligned word holding their first column (level pitches and the input pitch are multiples of 4)
-  const int bp = L.blurPitch;
-  const int px0 = kp.x - kOdR, pa = px0 & 3;
-  const int mx0 = kp.x - kHalfPatch, ma = mx0 & 3;
-  od_stage<kPatch, kOmWords>(img + (long long)(kp.y - kHalfPatch) * sp + (mx0 - ma), sp, sRaw[warp], lane);
-  od_stage<kOdRows, kOdWords>(b.blur + (long long)f * b.blurFrameStride + L.blurOff + (long long)(kp.y - kOdR) * bp + (px0 - pa), bp,
-                              sPatch[warp], lane);
+  const int px0 = kp.x - kOdR, mx0 = kp.x - kHalfPatch;
+  int pa, ma;   // offset of the patch's first column inside the staged row
+  if (kTma) {
+    pa = px0 & 15; ma = mx0 & 15;
+    if (lane == 0) {
+      const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sBar[warp]);
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar));
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(kOmBoxW * kPatch + kOdBoxW * kOdRows) : "memory");
+      asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                   :: "r"((uint32_t)__cvta_generic_to_shared(sRawB[warp])), "l"(reinterpret_cast<unsigned long long>(&tm.raw[level & (kFastMapLevels - 1)][0])),
+                      "r"(mx0 - ma), "r"(kp.y - kHalfPatch), "r"(f), "r"(bar) : "memory");
+      asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                   :: "r"((uint32_t)__cvta_generic_to_shared(sPatchB[warp])), "l"(reinterpret_cast<unsigned long long>(&tm.blur[level & (kFastMapLevels - 1)][0])),
+                      "r"(px0 - pa), "r"(kp.y - kOdR), "r"(f), "r"(bar) : "memory");
+    }
+    __syncwarp();   // the barrier is initialised before the other lanes poll it
+    {
+      const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sBar[warp]);
+      uint32_t done = 0;
+      while (!done)
+        asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], 0;\n\tselp.u32 %0, 1, 0, P1;\n\t}" : "=r"(done) : "r"(bar) : "memory");
+    }
+  } else {
+    int sp;
+    const uint8_t* img = level_ptr(g, b, level, f, sp);
+    // both patches start at the aligned word holding their first column (level pitches and the input pitch are multiples of 4)
+    const int bp = L.blurPitch;
+    pa = px0 & 3; ma = mx0 & 3;
+    od_stage<kPatch, kOmWords>(img + (long long)(kp.y - kHalfPatch) * sp + (mx0 - ma), sp, reinterpret_cast<uint32_t*>(sRawB[warp]), lane);
+    od_stage<kOdRows, kOdWords>(b.blur + (long long)f * b.blurFrameStride + L.blurOff + (long long)(kp.y - kOdR) * bp + (px0 - pa), bp,
+                                reinterpret_cast<uint32_t*>(sPatchB[warp]), lane);
+  }
   __syncwarp();
   // IC_Angle: m10 = sum u*I, m01 = sum v*I over the radius-15 disc; lane = column u + 15 (lane 31 idles)
   int m10 = 0, m01 = 0;
   {
     const int u = lane - kHalfPatch;
     const int au = abs(u);
-    const uint8_t* c = reinterpret_cast<const uint8_t*>(sRaw[warp]) + ma + min(lane, kPatch - 1);
+    const uint8_t* c = sRawB[warp] + ma + min(lane, kPatch - 1);
     int rowSum = 0;
 #pragma unroll
     for (int r = 0; r < kPatch; r++) {
       const int v = r - kHalfPatch;
-      const int raw = c[r * (kOmWords * 4)];                              // always in the staged patch: select, don't branch
+      const int raw = c[r * kRawPitch];                                   // always in the staged patch: select, don't branch
       const int val = (au <= od_umax(v < 0 ? -v : v)) ? raw : 0;
       rowSum += val;
       m01 += v * val;
@@ -98,7 +133,7 @@ __global__ void __launch_bounds__(256) k_orient_desc2(const __grid_constant__ Ge
   const float factorPI = (float)(3.1415926535897932384626433832795 / 180.0);
   const float ang = __fmul_rn(angle, factorPI);
   const float ca = (float)cos((double)ang), sa = (float)sin((double)ang);
-  const uint8_t* bl = reinterpret_cast<const uint8_t*>(sPatch[warp]) + kOdR * (kOdWords * 4) + kOdR + pa;   // patch centre
+  const uint8_t* bl = sPatchB[warp] + kOdR * kBlurPitch + kOdR + pa;   // patch centre
   const float4* pat = b.patternF + lane;   // transposed: record j of lane l (pair 8l + j) at [j * 32 + l]
   int bits = 0;
 #pragma unroll
@@ -108,7 +143,7 @@ __global__ void __launch_bounds__(256) k_orient_desc2(const __grid_constant__ Ge
     const int cc0 = __float2int_rn(__fsub_rn(__fmul_rn(q.x, ca), __fmul_rn(q.y, sa)));
     const int rr1 = __float2int_rn(__fadd_rn(__fmul_rn(q.z, sa), __fmul_rn(q.w, ca)));
     const int cc1 = __float2int_rn(__fsub_rn(__fmul_rn(q.z, ca), __fmul_rn(q.w, sa)));
-    const int t0 = bl[rr0 * (kOdWords * 4) + cc0], t1 = bl[rr1 * (kOdWords * 4) + cc1];
+    const int t0 = bl[rr0 * kBlurPitch + cc0], t1 = bl[rr1 * kBlurPitch + cc1];
     bits |= (t0 < t1) << j;
   }
   b.desc[((long long)f * g.kpStride + dest) * 32 + lane] = (uint8_t)bits;
