@@ -178,10 +178,11 @@ class ORBextractor:
         self._last_shape = (h, w)
         return counts, mono, kps, desc
 
-    def extract_batch_device(self, d_ptr, n, w, h, pitch, frame_stride, vLappingArea=(0, 0), stream=0):
-        """frames resident in HBM (raw device pointer); results stay on the device (see results_device)."""
-        _check(lib().orbx_extract_batch_device(self._h, C.c_void_p(d_ptr), n, w, h, pitch, C.c_size_t(frame_stride),
-                                               int(vLappingArea[0]), int(vLappingArea[1]), C.c_void_p(stream)))
+    def extract_batch_device(self, d_ptr, n, w, h, pitch, frame_stride, vLappingArea=(0, 0), stream=0, slot=0):
+        """frames resident in HBM (raw device pointer); results stay on the device (see results_device).  slot: which of the handle's
+        two workspace sets the batch uses (alternate them to overlap the readers of batch i with the extraction of batch i+1)."""
+        _check(lib().orbx_extract_batch_device_slot(self._h, int(slot), C.c_void_p(d_ptr), n, w, h, pitch, C.c_size_t(frame_stride),
+                                                    int(vLappingArea[0]), int(vLappingArea[1]), C.c_void_p(stream)))
         self._last_shape = (h, w)
 
     def results_device(self):

@@ -53,8 +53,10 @@ static void free_geom(orbx_extractor* h) {
     for (void* q : ptrs) if (q) cudaFree(q);
     if (s.hStatus) cudaFreeHost(s.hStatus);
     cudaStream_t st = s.stream;
+    cudaEvent_t eb = s.evBatch;
+    for (cudaEvent_t e : s.ev) if (e) cudaEventDestroy(e);
     s = Slot();
-    s.stream = st;
+    s.stream = st; s.evBatch = eb;
   }
   if (h->dRsx) cudaFree(h->dRsx);
   if (h->dRsy) cudaFree(h->dRsy);
@@ -370,6 +372,16 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
   mark(7);
   s.evValid = prof;
   CK(cudaGetLastError());
+  {
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    s.evBatchValid = false;
+    s.lastStream = st;
+    if (cudaStreamIsCapturing(st, &cap) == cudaSuccess && cap == cudaStreamCaptureStatusNone) {
+      if (!s.evBatch) CK(cudaEventCreateWithFlags(&s.evBatch, cudaEventDisableTiming));
+      CK(cudaEventRecord(s.evBatch, st));
+      s.evBatchValid = true;
+    }
+  }
   return ORBX_OK;
 }
 
@@ -459,6 +471,7 @@ void orbx_destroy(orbx_extractor* h) {
   free_geom(h);
   for (Slot& s : h->slot) {
     if (s.stream) cudaStreamDestroy(s.stream);
+    if (s.evBatch) cudaEventDestroy(s.evBatch);
   }
   if (h->dPattern) cudaFree(h->dPattern);
   if (h->lat.exec) cudaGraphExecDestroy(h->lat.exec);
@@ -514,7 +527,12 @@ int orbx_launches_per_batch(const orbx_extractor* h) {
 
 int orbx_extract_batch_device(orbx_extractor* h, const uint8_t* dImages, int nframes, int width, int height, int pitch,
                               size_t frameStride, int lap0, int lap1, void* stream) {
-  if (!h) return ORBX_ERR_ARG;
+  return orbx_extract_batch_device_slot(h, 0, dImages, nframes, width, height, pitch, frameStride, lap0, lap1, stream);
+}
+
+int orbx_extract_batch_device_slot(orbx_extractor* h, int slot, const uint8_t* dImages, int nframes, int width, int height, int pitch,
+                                   size_t frameStride, int lap0, int lap1, void* stream) {
+  if (!h || slot < 0 || slot > 1) return ORBX_ERR_ARG;
   if (!dImages || width <= 0 || height <= 0 || nframes <= 0) return ORBX_EMPTY_IMAGE;
   if (nframes > h->p.max_batch) { set_error("nframes %d > max_batch %d", nframes, h->p.max_batch); return ORBX_ERR_ARG; }
   if (pitch < width || (pitch & 3) || ((uintptr_t)dImages & 3) || (frameStride & 3)) {
@@ -523,8 +541,8 @@ int orbx_extract_batch_device(orbx_extractor* h, const uint8_t* dImages, int nfr
   }
   int rc = extractor_build_geom(h, width, height);
   if (rc != ORBX_OK) return rc;
-  cudaStream_t st = stream ? (cudaStream_t)stream : h->slot[0].stream;
-  return extractor_run_batch(h, 0, dImages, nframes, pitch, (long long)frameStride, lap0, lap1, st);
+  cudaStream_t st = stream ? (cudaStream_t)stream : h->slot[slot].stream;
+  return extractor_run_batch(h, slot, dImages, nframes, pitch, (long long)frameStride, lap0, lap1, st);
 }
 
 int orbx_batch_results_device(orbx_extractor* h, const orbx_keypoint** kps, const uint8_t** desc, const int** counts, const int** mono,

@@ -52,6 +52,9 @@ struct Slot {
   FastMaps maps{};         // TMA descriptors of the un-blurred levels (levels >= 1 valid while mapsEpoch == geomEpoch + 1)
   unsigned long long mapsEpoch = 0; bool mapsOk = false;
   OrientMaps omaps{}; bool omapsOk = false;
+  // completion of the last batch enqueued in this slot outside a graph capture: consumers on another stream (orbx_stereo_match_batch)
+  // wait for it, so a NULL / different stream there cannot race the extraction
+  cudaEvent_t evBatch = nullptr; cudaStream_t lastStream = nullptr; bool evBatchValid = false;
 };
 
 }  // namespace orbx

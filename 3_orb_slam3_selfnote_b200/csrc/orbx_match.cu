@@ -1432,7 +1432,12 @@ int orbx_stereo_match_batch(orbx_matcher* m, orbx_extractor* exL, orbx_extractor
   if (!m || !exL || !exR || !exL->haveGeom || !exR->haveGeom) return ORBX_ERR_ARG;
   if (exL->lastSlot != exR->lastSlot) { set_error("left / right extractors last ran in different slots"); return ORBX_ERR_ARG; }
   CK(cudaSetDevice(m->device));
-  return stereo_launch(m, exL, exR, exL->lastSlot, mb, mbf, stream ? (cudaStream_t)stream : m->stream);
+  cudaStream_t st = stream ? (cudaStream_t)stream : m->stream;
+  for (orbx_extractor* e : {exL, exR}) {   // the batches may have been enqueued on other streams (or the handles' own): wait for them on the device
+    Slot& s = e->slot[e->lastSlot];
+    if (s.evBatchValid && s.lastStream != st) CK(cudaStreamWaitEvent(st, s.evBatch, 0));
+  }
+  return stereo_launch(m, exL, exR, exL->lastSlot, mb, mbf, st);
 }
 
 // Whole stereo frames from host buffers: per chunk H2D(left,right) -> both extractions -> stereo matching -> D2H, double-buffered

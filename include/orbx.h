@@ -91,6 +91,13 @@ int orbx_extract_batch_host(orbx_extractor* h, const uint8_t* images, int nframe
  * `stream` (a cudaStream_t; NULL = the handle's own stream) and NOT synchronised: the caller owns ordering. */
 int orbx_extract_batch_device(orbx_extractor* h, const uint8_t* d_images, int nframes, int width, int height, int pitch,
                               size_t frame_stride, int lap0, int lap1, void* stream);
+/* The same with the workspace slot named (0 or 1; orbx_extract_batch_device = slot 0).  A handle owns two complete sets of pyramid /
+ * candidate / result buffers -- the host pipelines alternate them -- and consecutive device batches issued into alternating slots share
+ * nothing, so whatever still reads batch i (orbx_stereo_match_batch on another stream, a download of its results) overlaps the extraction
+ * of batch i+1.  The caller orders the reuse of a slot: batch i+2 after the readers of batch i (an event wait).  "Last batch" in the calls
+ * below means the batch of the slot used last. */
+int orbx_extract_batch_device_slot(orbx_extractor* h, int slot, const uint8_t* d_images, int nframes, int width, int height, int pitch,
+                                   size_t frame_stride, int lap0, int lap1, void* stream);
 /* Device views of the last batch: keypoints [nframes][kp_stride] (28 B), descriptors [nframes][kp_stride][32],
  * counts [nframes], mono_index [nframes], status word (0 = ok, else ORBX_ERR_CAPACITY raised by a kernel). */
 int orbx_batch_results_device(orbx_extractor* h, const orbx_keypoint** d_keypoints, const uint8_t** d_descriptors,
@@ -402,7 +409,8 @@ int orbx_allpairs_knn2(orbx_matcher* m, void* nccl_comm, const uint8_t* d_desc, 
 /* Frame::ComputeStereoMatches, src/Frame.cc:901-1079, for every frame of the last batches of two extractor handles
  * (left / right image of each pair; same geometry and frame count; keypoints, descriptors and un-blurred pyramids are read
  * where they lie in HBM, exactly the members the reference reads at Frame.cc:908,998,1012).  mb / mbf as in Frame.
- * Asynchronous on `stream` (NULL = the matcher's stream).  Results: per left keypoint mvuRight / mvDepth (-1 = no match). */
+ * Asynchronous on `stream` (NULL = the matcher's stream); the call makes that stream wait on the device for the two extraction
+ * batches wherever they were enqueued.  Results: per left keypoint mvuRight / mvDepth (-1 = no match). */
 int orbx_stereo_match_batch(orbx_matcher* m, orbx_extractor* left, orbx_extractor* right, float mb, float mbf, void* stream);
 int orbx_stereo_results_device(orbx_matcher* m, const float** d_u_right, const float** d_depth, int* stride);
 /* Whole stereo frames from HOST buffers (the data-parallel part of Frame::Frame(stereo), src/Frame.cc:89-187): for each of

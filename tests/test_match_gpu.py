@@ -286,6 +286,64 @@ def test_batch256_matches_oracle(orbx, oracle, synth):
     gl.close(); gr.close(); m.close()
 
 
+def test_device_batches_pipelined_over_two_slots(orbx, synth):
+    """orbx_extract_batch_device_slot: launches alternate the handles' two workspace slots, the stereo matcher runs on its own stream while
+    the next launch is extracted (bench.py's device-resident loop).  Every launch's results must equal the serial single-slot run."""
+    import torch
+    B, NL = 24, 5
+    left = [np.stack([synth.frame(W, H, 300 + k, i % 5, False) for i in range(B)]) for k in range(NL)]
+    right = [np.stack([synth.frame(W, H, 300 + k, i % 5, True) for i in range(B)]) for k in range(NL)]
+    dL = [torch.from_numpy(a).cuda() for a in left]; dR = [torch.from_numpy(a).cuda() for a in right]
+    mbf = np.float32(47.90639384423901); mb = np.float32(mbf / np.float32(435.2046959714599))
+    gl = orbx.ORBextractor(1200, max_batch=B); gr = orbx.ORBextractor(1200, max_batch=B); m = orbx.ORBmatcher()
+    st = torch.cuda.Stream().cuda_stream
+    serial = []
+    for k in range(NL):
+        gl.extract_batch_device(dL[k].data_ptr(), B, W, H, W, W * H, (0, 0), st)
+        gr.extract_batch_device(dR[k].data_ptr(), B, W, H, W, W * H, (0, 0), st)
+        m.stereo_match_batch(gl, gr, mb, mbf, st)
+        torch.cuda.synchronize()
+        serial.append((gl.results_host(B), gr.results_host(B), m.stereo_results(B)))
+    sA, sB, sS = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()
+    evL, evR, evDone = [torch.cuda.Event() for _ in range(2)], [torch.cuda.Event() for _ in range(2)], [torch.cuda.Event() for _ in range(2)]
+    got = []
+    for k in range(NL):
+        slot = k & 1
+        sA.wait_event(evDone[slot]); sB.wait_event(evDone[slot])
+        gl.extract_batch_device(dL[k].data_ptr(), B, W, H, W, W * H, (0, 0), sA.cuda_stream, slot=slot)
+        evL[slot].record(sA)
+        gr.extract_batch_device(dR[k].data_ptr(), B, W, H, W, W * H, (0, 0), sB.cuda_stream, slot=slot)
+        evR[slot].record(sB)
+        sS.wait_event(evL[slot]); sS.wait_event(evR[slot])
+        m.stereo_match_batch(gl, gr, mb, mbf, sS.cuda_stream)
+        evDone[slot].record(sS)
+    torch.cuda.synchronize()
+    # results are read from the slot used last: run the pipeline again stopping after launch `stop`, for every stop
+    for stop in range(NL):
+        for k in range(stop + 1):
+            slot = k & 1
+            sA.wait_event(evDone[slot]); sB.wait_event(evDone[slot])
+            gl.extract_batch_device(dL[k].data_ptr(), B, W, H, W, W * H, (0, 0), sA.cuda_stream, slot=slot)
+            evL[slot].record(sA)
+            gr.extract_batch_device(dR[k].data_ptr(), B, W, H, W, W * H, (0, 0), sB.cuda_stream, slot=slot)
+            evR[slot].record(sB)
+            sS.wait_event(evL[slot]); sS.wait_event(evR[slot])
+            m.stereo_match_batch(gl, gr, mb, mbf, sS.cuda_stream)
+            evDone[slot].record(sS)
+        torch.cuda.synchronize()
+        got.append((gl.results_host(B), gr.results_host(B), m.stereo_results(B)))
+    for k in range(NL):
+        (cl, ml, kl, dl), (cr, mr, kr, dr), (ur, dp, _, _) = serial[k]
+        (cl2, ml2, kl2, dl2), (cr2, mr2, kr2, dr2), (ur2, dp2, _, _) = got[k]
+        assert np.array_equal(cl, cl2) and np.array_equal(cr, cr2) and cl.min() > 300
+        for f in range(B):
+            n, nr = int(cl[f]), int(cr[f])
+            assert kl[f, :n].tobytes() == kl2[f, :n].tobytes() and np.array_equal(dl[f, :n], dl2[f, :n]), (k, f)
+            assert kr[f, :nr].tobytes() == kr2[f, :nr].tobytes() and np.array_equal(dr[f, :nr], dr2[f, :nr]), (k, f)
+            assert ur[f, :n].tobytes() == ur2[f, :n].tobytes() and dp[f, :n].tobytes() == dp2[f, :n].tobytes(), (k, f)
+    gl.close(); gr.close(); m.close()
+
+
 def test_host_buffers_and_chunked_pipeline(orbx, oracle, synth):
     """orbx_host_alloc staging buffers + orbx_stereo_frames_host over several ramped / tail chunks (graph cache hit on the
     second call) against the per-frame oracle."""
