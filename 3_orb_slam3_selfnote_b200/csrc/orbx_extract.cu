@@ -88,6 +88,7 @@ int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
   for (int i = 0; i < 16; i++) g.umax[i] = h->umax[i];
 
   std::vector<RsX> rsx; std::vector<RsY> rsy; std::vector<uint16_t> info;
+  int rsBoxW = 0, rsBoxH = 0;
   int pyrOff = 0, blurOff = 0, cellBase = 0, candOff = 0, kpOff = 0, tileBase = 0, blurTileBase = 0, maxNodeCap = 0;
   h->inPitch = round_up(width, 4);  // dense when width % 4 == 0: host frames then upload as one linear copy
   for (int l = 0; l < nl; l++) {
@@ -208,8 +209,21 @@ int orbx::extractor_build_geom(orbx_extractor* h, int width, int height) {
         const int yl = std::min(y0 + kRsTileH, L.h) - 1;
         g.rsWinRows = std::max(g.rsWinRows, ty[yl].s1 - ty[y0].s0 + 1);
       }
+      // source window of k_pyr_resize4t's 128 x 64 destination tiles: from the 16-byte boundary at or before the first tap of the tile to
+      // the last of the three words its last 4-column group loads; rows from the first row's s0 to the last row's s1
+      for (int x0 = 0; x0 < L.w; x0 += kRs4TileW) {
+        const int xg = ((std::min(x0 + kRs4TileW, wpad) - 1) & ~3);
+        rsBoxW = std::max(rsBoxW, ((tx[xg].s0 & ~3) + 12) - (tx[x0].s0 & ~15));
+      }
+      for (int y0 = 0; y0 < L.h; y0 += 8 * kRs4Rows) {
+        const int yl = std::min(y0 + 8 * kRs4Rows, L.h) - 1;
+        rsBoxH = std::max(rsBoxH, ty[yl].s1 - ty[y0].s0 + 1);
+      }
     }
   }
+  rsBoxW = round_up(std::max(rsBoxW, 16), 16);
+  h->rsBoxW = (rsBoxW <= 256 && rsBoxH <= 256 && rsBoxH >= 1) ? rsBoxW : 0;
+  h->rsBoxH = h->rsBoxW ? rsBoxH : 0;
   g.rsWinWords = round_up(std::max(g.rsWinWords, 4), 4);
   g.rsWinRows = std::max(g.rsWinRows, 1);
   h->rsSmem = (size_t)g.rsWinRows * (g.rsWinWords + kRsTileW) * 4;
@@ -328,9 +342,23 @@ int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int
   mark(0);
   CK(cudaMemsetAsync(s.zero, 0, s.zeroBytes, st));
   mark(1);
+  // TMA-fed strips when every source level has a tensor map with the window box (encoded once per slot and geometry, level 0 per call)
+  bool rsTma = false;
+  if (h->rs3ok && h->rsBoxW > 0 && g.nlevels > 1 && g.nlevels <= kFastMapLevels) {
+    if (s.rmapsEpoch != h->geomEpoch + 1) {
+      s.rmapsOk = true;
+      for (int l = 1; l + 1 < g.nlevels && s.rmapsOk; l++)
+        s.rmapsOk = encode_level_map(s.rmaps.m[l], s.pyr + g.lv[l].pyrOff, g.lv[l].w, g.lv[l].h, g.lv[l].pitch, h->pyrFrame, h->p.max_batch, h->rsBoxW, h->rsBoxH);
+      s.rmapsEpoch = h->geomEpoch + 1;
+    }
+    rsTma = s.rmapsOk && encode_level_map(s.rmaps.m[0], dIn, g.lv[0].w, g.lv[0].h, pitch, frameStride, nframes, h->rsBoxW, h->rsBoxH);
+  }
   for (int l = 1; l < g.nlevels; l++) {
     const LevelGeom& L = g.lv[l];
-    if (h->rs3ok) {
+    if (rsTma) {
+      dim3 grid((L.w + kRs4TileW - 1) / kRs4TileW, (L.h + 8 * kRs4Rows - 1) / (8 * kRs4Rows), nframes);
+      k_pyr_resize4t<<<grid, 256, (size_t)h->rsBoxW * h->rsBoxH, st>>>(gg, b, s.rmaps, l, h->rsBoxW, h->rsBoxH);
+    } else if (h->rs3ok) {
       dim3 grid((L.w + kRs4TileW - 1) / kRs4TileW, (L.h + 8 * kRs4Rows - 1) / (8 * kRs4Rows), nframes);
       if (l == 1) k_pyr_resize4<true><<<grid, 256, 0, st>>>(gg, b, l);     // source = the caller's image: no bytes may be read past its rows
       else k_pyr_resize4<false><<<grid, 256, 0, st>>>(gg, b, l);

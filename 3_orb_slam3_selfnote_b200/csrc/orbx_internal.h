@@ -52,6 +52,7 @@ struct Slot {
   FastMaps maps{};         // TMA descriptors of the un-blurred levels (levels >= 1 valid while mapsEpoch == geomEpoch + 1)
   unsigned long long mapsEpoch = 0; bool mapsOk = false;
   OrientMaps omaps{}; bool omapsOk = false;
+  FastMaps rmaps{}; bool rmapsOk = false; unsigned long long rmapsEpoch = 0;   // k_pyr_resize4t: source windows of the levels 0 .. nlevels-2
   // completion of the last batch enqueued in this slot outside a graph capture: consumers on another stream (orbx_stereo_match_batch)
   // wait for it, so a NULL / different stream there cannot race the extraction
   cudaEvent_t evBatch = nullptr; cudaStream_t lastStream = nullptr; bool evBatchValid = false;
@@ -77,6 +78,7 @@ struct orbx_extractor {
   Slot slot[2];
   int lastSlot = 0;
   bool profile = false;
+  int rsBoxW = 0, rsBoxH = 0;   // k_pyr_resize4t: source window of a 128 x 64 destination tile (0 = does not fit a TMA box)
   bool rs3ok = true;     // k_pyr_resize4 applies to this geometry (scale factor <= 2); otherwise k_pyr_resize2
   size_t rsSmem = 0;
   // latency path of the host entry points (one small chunk, e.g. the reference's per-frame operator() call): page-locked staging

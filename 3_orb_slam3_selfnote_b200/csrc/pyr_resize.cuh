@@ -12,6 +12,7 @@
 #pragma once
 #include "dev_common.cuh"
 #include "geom.h"
+#include "orbx_internal.h"
 
 namespace orbx {
 
@@ -107,29 +108,33 @@ constexpr int kRs4Rows = 8;   // destination rows per warp (measured: 4 -> 0.284
 
 // one strip: 128 destination columns (x = first column of this lane's 4) x kRs4Rows destination rows from ys on.
 // kClamp: the source rows have no slack behind them (level 1 reads the caller's image).
-template <bool kClamp>
-__device__ __forceinline__ void rs4_strip(const Geom& g, const Batch& b, int level, int f, int x, int ys, int lane) {
+// kSmem: the CTA's source window was fetched into shared memory by one TMA copy (k_pyr_resize4t): win = its first byte, (winX, winY) = the
+// source coordinates of that byte, winPitch = bytes per window row; xIdle = a column of this CTA that lanes right of the level may read.
+template <bool kClamp, bool kSmem = false>
+__device__ __forceinline__ void rs4_strip(const Geom& g, const Batch& b, int level, int f, int x, int ys, int lane, const uint8_t* win = nullptr,
+                                          int winX = 0, int winY = 0, int winPitch = 0, int xIdle = 0) {
   const LevelGeom& L = g.lv[level];
   const int wpad = (L.w + 3) & ~3;   // the column table is padded to a multiple of 4
   const bool active = x < wpad;      // lanes right of the level stay for the shuffles and skip loads / stores
   int sp;
   const uint8_t* src = level_ptr(g, b, level - 1, f, sp);
+  if (kSmem) { src = win - ((long long)winY * winPitch + winX); sp = winPitch; }   // source (sx, sy) at src + sy * sp + sx, inside the window
   const int rows = min(kRs4Rows, L.h - ys);
-  // row table of the strip: lane j holds entry ys + j
+  // row table of the strip: lane j holds entry ys + j (kSmem: lanes past the end repeat the last row, whose source rows are in the window)
   uint2 myRow = make_uint2(0u, 0u);
-  if (lane < rows) myRow = __ldg(reinterpret_cast<const uint2*>(b.rsy + L.rsyOff + ys + lane));
+  if (lane < rows || kSmem) myRow = __ldg(reinterpret_cast<const uint2*>(b.rsy + L.rsyOff + ys + min(lane, rows - 1)));
   uint32_t sel[4], wt[4], sh;
   int off1 = 4, off2 = 8;
   const uint8_t* srcx = src;
   {
-    const uint4* tx = reinterpret_cast<const uint4*>(b.rsx + L.rsxOff + (active ? x : 0));   // 4 entries of 8 bytes (lanes right of the level: column 0)
+    const uint4* tx = reinterpret_cast<const uint4*>(b.rsx + L.rsxOff + (active ? x : xIdle));   // 4 entries of 8 bytes (lanes right of the level: column 0 / a column of the window)
     const uint4 p0 = __ldg(tx), p1 = __ldg(tx + 1);
     const uint32_t e[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};   // (s0 | s1 << 16), (a0 | a1 << 16) per column
     const int sx0 = (int)(e[0] & 0xffffu);
     const int base = sx0 & ~3;
     sh = (uint32_t)(sx0 & 3) * 8;
     srcx = src + base;
-    if (kClamp) { off1 = min(base + 4, sp - 4) - base; off2 = min(base + 8, sp - 4) - base; }   // words past the row end hold no tap
+    if (kClamp && !kSmem) { off1 = min(base + 4, sp - 4) - base; off2 = min(base + 8, sp - 4) - base; }   // words past the row end hold no tap
 #pragma unroll
     for (int k = 0; k < 4; k++) {
       const int s0 = (int)(e[2 * k] & 0xffffu), s1 = (int)(e[2 * k] >> 16);
@@ -139,10 +144,17 @@ __device__ __forceinline__ void rs4_strip(const Geom& g, const Batch& b, int lev
   }
   const unsigned usp = (unsigned)sp, upitch = (unsigned)L.pitch;
   auto load3 = [&](int srow, uint32_t (&w)[3]) {
-    const uint8_t* p = srcx + (unsigned long long)(unsigned)srow * usp;   // one IMAD.WIDE.U32
-    w[0] = __ldg(reinterpret_cast<const uint32_t*>(p));
-    w[1] = __ldg(reinterpret_cast<const uint32_t*>(p + off1));
-    w[2] = __ldg(reinterpret_cast<const uint32_t*>(p + off2));
+    if (kSmem) {
+      const uint8_t* p = srcx + srow * (int)usp;
+      w[0] = *reinterpret_cast<const uint32_t*>(p);
+      w[1] = *reinterpret_cast<const uint32_t*>(p + 4);
+      w[2] = *reinterpret_cast<const uint32_t*>(p + 8);
+    } else {
+      const uint8_t* p = srcx + (unsigned long long)(unsigned)srow * usp;   // one IMAD.WIDE.U32
+      w[0] = __ldg(reinterpret_cast<const uint32_t*>(p));
+      w[1] = __ldg(reinterpret_cast<const uint32_t*>(p + off1));
+      w[2] = __ldg(reinterpret_cast<const uint32_t*>(p + off2));
+    }
   };
   auto prmt = [](uint32_t a, uint32_t b2, uint32_t sl) { uint32_t r; asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b2), "r"(sl)); return r; };
   auto hcalc = [&](const uint32_t (&w)[3], uint32_t (&h)[4]) {
@@ -152,7 +164,7 @@ __device__ __forceinline__ void rs4_strip(const Geom& g, const Batch& b, int lev
   };
   uint8_t* dst = b.pyr + (long long)f * b.pyrFrameStride + L.pyrOff + x;
   asm volatile("" : "+l"(dst));      // keep both per-thread base pointers whole in registers: otherwise the uniform part is re-added
-  asm volatile("" : "+l"(srcx));     // (IADD3 + IADD3.X) at every use
+  if (!kSmem) asm volatile("" : "+l"(srcx));     // (IADD3 + IADD3.X) at every use
   uint32_t hh[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
   int held0 = -1;                    // source row whose h is in hh[j & 1] when row j starts (= s1 of row j-1)
   // raw words of row j's s1 are loaded one row ahead (two rows ahead: 48 registers, 0.256 ms against 0.242), unconditionally: lanes right of the level read from column 0 and rows past
@@ -194,6 +206,41 @@ __global__ void __launch_bounds__(256) k_pyr_resize4(const __grid_constant__ Geo
   const int ys = (blockIdx.y * 8 + warp) * kRs4Rows;
   if (ys >= g.lv[level].h) return;   // warp-uniform
   rs4_strip<kClamp>(g, b, level, blockIdx.z, blockIdx.x * kRs4TileW + 4 * lane, ys, lane);
+}
+// k_pyr_resize4t -- the same strips fed from shared memory: the CTA's source window (128 x 64 destination pixels -> boxW x boxH source
+// bytes, e.g. 192 x 80 at scale 1.2; the sizes are maxima over all tiles of all levels, computed on the host from the tables) arrives by ONE
+// cp.async.bulk.tensor.3d issued by thread 0 (tensor map of level - 1 over x, y, frame; box start = the tile's first source column rounded
+// down to 16 bytes, its first source row; zeros outside the level) and is waited for on an mbarrier.  The three word loads per source row
+// become LDS with ~20x less latency than the L2 / HBM loads the register-resident kernel hides with one-row-ahead prefetching.
+__global__ void __launch_bounds__(256) k_pyr_resize4t(const __grid_constant__ Geom g, const __grid_constant__ Batch b, const __grid_constant__ FastMaps tm,
+                                                      int level, int boxW, int boxH) {
+  extern __shared__ __align__(128) uint8_t rs_win[];
+  __shared__ __align__(8) unsigned long long sBar;
+  __shared__ int sOrg[2];
+  const LevelGeom& L = g.lv[level];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int x0 = blockIdx.x * kRs4TileW, y0 = blockIdx.y * 8 * kRs4Rows, f = blockIdx.z;
+  if (threadIdx.x == 0) {
+    const int gx = (int)b.rsx[L.rsxOff + x0].s0 & ~15, wy = (int)b.rsy[L.rsyOff + y0].s0;
+    sOrg[0] = gx; sOrg[1] = wy;
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sBar);
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(boxW * boxH) : "memory");
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 :: "r"((uint32_t)__cvta_generic_to_shared(rs_win)), "l"(reinterpret_cast<unsigned long long>(&tm.m[(level - 1) & (kFastMapLevels - 1)][0])),
+                    "r"(gx), "r"(wy), "r"(f), "r"(bar) : "memory");
+  }
+  __syncthreads();
+  {
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sBar);
+    uint32_t done = 0;
+    while (!done)
+      asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], 0;\n\tselp.u32 %0, 1, 0, P1;\n\t}" : "=r"(done) : "r"(bar) : "memory");
+  }
+  const int ys = y0 + warp * kRs4Rows;
+  if (ys >= L.h) return;   // warp-uniform
+  rs4_strip<false, true>(g, b, level, f, x0 + 4 * lane, ys, lane, rs_win, sOrg[0], sOrg[1], boxW, x0);
 }
 // Measured and dropped: one clustered launch for the small levels 4..7 of a frame (4 CTAs per frame, cluster barrier between the
 // levels, sources re-read through L2): 0.262 - 0.302 ms against 0.251 for one launch per level -- the separate launches overlap
