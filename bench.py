@@ -61,8 +61,14 @@ def _peaks():
         return 6650.0, "fallback"
 
 
-NCU_SUMMARY = os.path.join(ROOT, "profiles", "r02_ncu_full_summary.csv")   # tools/ncu_summary.py of one --set full capture (128 images per launch)
+NCU_SUMMARY = os.path.join(ROOT, "profiles", "r02i_ncu_full_summary.csv")   # tools/ncu_summary.py of one --set full capture (128 images per launch)
 NCU_NAME = {"k_fast_nms": "k_fast_nms3", "k_blur7": "k_blur7v", "k_orient_desc": "k_orient_desc2", "k_quadtree": "k_quadtree"}
+
+
+def _kernel_is(ncu_name, name):
+    """ncu prints templated kernels as `void name<args>(...)`, plain ones as `name(...)`"""
+    base = ncu_name.split("(")[0].replace("void ", "").split("<")[0].strip()
+    return base == name
 
 
 def _ncu_traffic(stage, images_per_launch):
@@ -76,7 +82,7 @@ def _ncu_traffic(stage, images_per_launch):
         mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
         name = NCU_NAME.get(stage)
         for r in rows[2:]:
-            if name and r[0].startswith(name + "("):
+            if name and _kernel_is(r[0], name):
                 return (float(r[ir]) * mult[units[ir]] + float(r[iw]) * mult[units[iw]]) * images_per_launch / 128.0
     except Exception:
         pass
@@ -409,7 +415,7 @@ def _ncu_issue(stage, images_per_launch, kernel_ms, sm_mhz):
         ib = hdr.index("images_per_launch") if "images_per_launch" in hdr else None
         name = NCU_NAME.get(stage)
         for r in rows[2:]:
-            if name and r[0].startswith(name):
+            if name and _kernel_is(r[0], name):
                 per = float(r[ib]) if ib is not None else 128.0
                 inst = float(r[ii]) * images_per_launch / per
                 cyc = kernel_ms * 1e-3 * sm_mhz * 1e6
