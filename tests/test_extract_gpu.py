@@ -147,6 +147,18 @@ def test_batch_host_and_device_paths_agree_with_single_frame(orbx, oracle, synth
         m, k, d = ref[f]
         assert counts2[f] == len(k) and mono2[f] == m
         _assert_same(kps2[f, :len(k)], desc2[f, :len(k)], k, d, "device batch frame %d" % f)
+    # the same frames with a row pitch that is NOT a multiple of 16 bytes: level 0 cannot be described by a tensor map, so FAST,
+    # orientation / rBRIEF and the resize take their per-lane staging paths instead of the TMA ones -- results must not change
+    pitch = w + 4
+    tp = torch.zeros((n, h, pitch), dtype=torch.uint8, device="cuda")
+    tp[:, :, :w] = t
+    gd.extract_batch_device(tp.data_ptr(), n, w, h, pitch, pitch * h, (0, 0), st.cuda_stream)
+    st.synchronize()
+    counts3, mono3, kps3, desc3 = gd.results_host(n)
+    assert np.array_equal(counts3, counts2) and np.array_equal(mono3, mono2)
+    for f in range(n):
+        c = int(counts2[f])
+        assert kps3[f, :c].tobytes() == kps2[f, :c].tobytes() and np.array_equal(desc3[f, :c], desc2[f, :c]), "pitch %d frame %d" % (pitch, f)
     gx.close(); gd.close()
 
 
