@@ -600,6 +600,100 @@ __global__ void __launch_bounds__(32) k_resolve_fisheye(const GridFrame* frames,
   if (lane == 0) { *AL.nmatches = nmatches; *AR.nmatches = nmatches; }
 }
 
+// The same search as a parallel fixed point, for the common case in which every map point that takes part has observations (then a
+// keypoint, once written -- directly or through the partner hand-over -- stays blocked for every later query, and the claims are
+// monotone again).  Queries are ordered as the reference walks them: q = 2 i (left pass of map point i), q = 2 i + 1 (its right pass);
+// blk[side][k] = smallest q that writes keypoint k of that image (its own choice or the stereo partner of its choice); k is blocked
+// for q iff blk < q; the right pass of i is skipped when its left pass failed the ratio test (a per-point flag of the same iteration
+// scheme).  choice[q] depends only on {choice[q'], skip : q' < q}, so iterating from "nothing written" reaches the sequential result.
+// One cluster of 8 CTAs, warp = query.  The host picks this kernel when no participating point has observed == 0.
+__global__ void __cluster_dims__(kParCluster, 1, 1) __launch_bounds__(kParThreads)
+k_resolve_fisheye_par(const GridFrame* frames, const QuerySet* sets, const ResolveArgs* args) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  const GridFrame F[2] = {frames[0], frames[1]};
+  const QuerySet Q[2] = {sets[0], sets[1]};
+  const ResolveArgs A[2] = {args[0], args[1]};
+  const int lane = threadIdx.x & 31;
+  const int gthread = blockIdx.x * kParThreads + threadIdx.x, nthreads = kParCluster * kParThreads;
+  const int gwarp = gthread >> 5, nwarps = nthreads >> 5;
+  const int nmp = Q[0].nq;
+  int* const skip = A[1].bestDist;   // per map point: its left pass failed the ratio test (right pass skipped); scratch [nmp]
+  auto pre = [&](int s, int k) { const int v = A[s].kpMp[k]; return (v == -2 || v >= 0) ? -1 : INT_MAX; };   // (every index written earlier is an observed point)
+  for (int s = 0; s < 2; s++)
+    for (int k = gthread; k < F[s].n; k += nthreads) { A[s].blk[0][k] = pre(s, k); A[s].blk[1][k] = pre(s, k); }
+  for (int i = gthread; i < nmp; i += nthreads) { A[0].assigned[i] = -1; A[1].assigned[i] = -1; skip[i] = 0; }
+  if (gthread < 2) A[0].chg[gthread] = 0;
+  cluster.sync();
+  for (int it = 0; it <= 2 * nmp; it++) {
+    const int cb = it & 1;
+    bool changed = false;
+    for (int q = gwarp; q < 2 * nmp; q += nwarps) {
+      const int s = q & 1, i = q >> 1;
+      int c = Q[s].valid[i] ? Q[s].qCnt[i] : 0;
+      if (s == 1 && __ldcg(skip + i)) c = 0;
+      int choice = -1, sk = 0;
+      if (c > 0) {
+        const unsigned long long* e = Q[s].entries + Q[s].qOff[i];
+        const int* cur = A[s].blk[cb];
+        unsigned long long k1 = kKeyNone, k2 = kKeyNone;
+        for (int j = lane; j < c; j += 32) {
+          const unsigned long long k = e[j];
+          if (!(__ldcg(cur + key_idx(k)) < q)) top2_insert(k, k1, k2);
+        }
+        top2_warp(k1, k2);
+        if (k1 != kKeyNone && key_dist(k1) <= 100) {   // TH_HIGH
+          const int bestDist = key_dist(k1), bestLevel = key_oct(k1);
+          const int bestDist2 = (k2 == kKeyNone) ? 256 : key_dist(k2), bestLevel2 = (k2 == kKeyNone) ? -1 : key_oct(k2);
+          if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(A[0].nnratio, (float)bestDist2)) sk = 1;
+          else choice = key_idx(k1);
+        }
+      }
+      if (lane == 0) {
+        if (choice != A[s].assigned[i]) { A[s].assigned[i] = choice; changed = true; }
+        if (s == 0 && sk != skip[i]) { skip[i] = sk; changed = true; }
+        if (choice >= 0) {
+          atomicMin(A[s].blk[cb ^ 1] + choice, q);
+          const int p = A[s].partner ? A[s].partner[choice] : -1;
+          if (p != -1) atomicMin(A[s ^ 1].blk[cb ^ 1] + p, q);
+        }
+      }
+    }
+    if (changed) atomicExch(A[0].chg + cb, 1);
+    cluster.sync();
+    const int any = __ldcg(A[0].chg + cb);
+    for (int s = 0; s < 2; s++)
+      for (int k = gthread; k < F[s].n; k += nthreads) A[s].blk[cb][k] = pre(s, k);
+    if (gthread == 0) A[0].chg[cb ^ 1] = 0;
+    cluster.sync();
+    if (!any) break;
+  }
+  // fixed point reached: the holder of a keypoint is its LAST writer (the hand-over overwrites), :131-135, :196-203
+  for (int s = 0; s < 2; s++)
+    for (int k = gthread; k < F[s].n; k += nthreads) A[s].blk[0][k] = -1;
+  if (gthread == 0) { *A[0].nmatches = 0; *A[1].nmatches = 0; }
+  cluster.sync();
+  int mine = 0;
+  for (int q = gthread; q < 2 * nmp; q += nthreads) {
+    const int s = q & 1, i = q >> 1;
+    const int ch = __ldcg(A[s].assigned + i);
+    if (ch < 0) continue;
+    atomicMax(A[s].blk[0] + ch, q);
+    mine++;
+    const int p = A[s].partner ? A[s].partner[ch] : -1;
+    if (p != -1) { atomicMax(A[s ^ 1].blk[0] + p, q); mine++; }
+  }
+  cluster.sync();
+  for (int s = 0; s < 2; s++)
+    for (int k = gthread; k < F[s].n; k += nthreads) {
+      const int w = __ldcg(A[s].blk[0] + k);
+      if (w >= 0) A[s].kpMp[k] = w >> 1;
+    }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+  if (lane == 0 && mine) { atomicAdd(A[0].nmatches, mine); }
+}
+
 // ---- brute-force 2-NN ----------------------------------------------------------------------------------------------------
 // thread = one query (descriptor in 8 registers); train descriptors stream through shared memory in tiles of 128 and are
 // read as broadcast LDS.128; best/second inside one launch are packed 32-bit keys (dist << 23 | local train index) so the

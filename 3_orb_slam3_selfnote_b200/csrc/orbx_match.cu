@@ -267,7 +267,7 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
       o.pScale = plan.add((size_t)std::max(J.F->nlevels, 1) * 4);
     }
     o.sigma = J.q.gate ? plan.add((size_t)std::max(J.q.nSigma, 1) * 4) : (size_t)-1;
-    if (kind == RESOLVE_BEST) o.m12 = plan.add((size_t)std::max(nq, 1) * 4);
+    if (kind == RESOLVE_BEST || kind == RESOLVE_FISHEYE) o.m12 = plan.add((size_t)std::max(nq, 1) * 4);
     o.minL = plan.add(std::max(nq, 1)); o.maxL = plan.add(std::max(nq, 1));
     o.qdesc = plan.add((size_t)std::max(nq, 1) * 32);
     o.qOff = plan.add((size_t)std::max(nq, 1) * 4); o.qCnt = plan.add((size_t)std::max(nq, 1) * 4);
@@ -441,6 +441,7 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
       A.nnratio = J.nnratio; A.distTh = J.distTh; A.anyMpBlocks = J.anyMpBlocks;
       A.checkOrientation = kind == RESOLVE_WINDOW_PAIR ? 0 : J.checkOrientation;   // pair: one histogram over both images, k_rotfilter_pair
       A.blk[0] = at<int>(m, o.blk0); A.blk[1] = at<int>(m, o.blk1); A.chg = at<int>(m, o.chg);
+      if (kind == RESOLVE_FISHEYE) A.bestDist = at<int>(m, o.m12);   // k_resolve_fisheye_par: per-point scratch
     } else if (kind == RESOLVE_BEST) {
       ResolveArgs& A = rargs[j];
       A = ResolveArgs{};
@@ -488,7 +489,17 @@ int run_window_jobs(orbx_matcher* m, std::vector<WindowJob>& jobs, ResolveKind k
     k_resolve_par<<<dim3(kParCluster, nj), kParThreads, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs), 1);
     k_rotfilter_pair<<<1, 256, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs), jobs[0].checkOrientation);
   }
-  else if (kind == RESOLVE_FISHEYE) k_resolve_fisheye<<<1, 32, (size_t)(frames[0].n + frames[1].n), st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs));
+  else if (kind == RESOLVE_FISHEYE) {
+    // claims are monotone when every participating map point has observations (the normal case: local-map points) -> cluster fixed point;
+    // otherwise the partner hand-over can replace a blocking holder by a non-blocking one -> one-warp replay of the reference's order
+    bool allObserved = true;
+    const uint8_t* ob = jobs[0].observed;
+    if (ob)
+      for (int i = 0; i < jobs[0].q.nq && allObserved; i++)
+        if ((jobs[0].q.valid[i] || jobs[1].q.valid[i]) && !ob[i]) allObserved = false;
+    if (allObserved) k_resolve_fisheye_par<<<dim3(kParCluster, 1), kParThreads, 0, st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs));
+    else k_resolve_fisheye<<<1, 32, (size_t)(frames[0].n + frames[1].n), st>>>(dFrames, dSets, at<ResolveArgs>(m, oArgs));
+  }
   else if (kind == RESOLVE_INIT) k_resolve_init<<<nj, 32, 0, st>>>(dFrames, dSets, at<InitArgs>(m, oArgs));
   else if (kind == RESOLVE_BEST && maxQ > 0) k_resolve_best<<<dim3((maxQ + 7) / 8, nj), 256, 0, st>>>(dSets, at<ResolveArgs>(m, oArgs));
   CK(cudaGetLastError());

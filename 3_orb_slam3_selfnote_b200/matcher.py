@@ -70,6 +70,10 @@ class _FeatVecC(C.Structure):
     _fields_ = [("nnodes", C.c_int), ("node_ids", C.c_void_p), ("node_start", C.c_void_p), ("indices", C.c_void_p)]
 
 
+class _TrackC(C.Structure):
+    _fields_ = [("in_view", C.c_void_p), ("proj_x", C.c_void_p), ("proj_y", C.c_void_p), ("level", C.c_void_p), ("view_cos", C.c_void_p)]
+
+
 class FrameView:
     """N, mvKeysUn, mDescriptors, mvuRight, mvScaleFactors, mnMinX.. of a Frame (include/Frame.h)."""
 
@@ -254,6 +258,27 @@ class ORBmatcher:
         good = np.empty(len(q), np.uint8)
         _check(lib().orbx_knn2(self._m, _p(q), len(q), _p(t), len(t), _p(idx), _p(dist), _p(good)))
         return idx, dist, good
+
+    def SearchByProjectionTwoCameras(self, left, right, track_left, track_right, mp_desc, left_to_right, right_to_left, th, observed=None, kp_mp=None):
+        """orbx_search_by_projection_mappoints_stereo: SearchByProjection(Frame, MapPoints) on a fisheye-stereo frame (ORBmatcher.cc:44-211).
+        left / right: FrameView of mvKeys / mvKeysRight; track_*: dict(in_view, proj_x, proj_y, level, view_cos) -> (nmatches, kp_mp[nl+nr])"""
+        keep = []
+
+        def track(t):
+            a = [_u8(t["in_view"]), _f32(t["proj_x"]), _f32(t["proj_y"]), _i32(t["level"]), _f32(t["view_cos"])]
+            keep.append(a)
+            return _TrackC(*[x.ctypes.data for x in a])
+        tl, tr = track(track_left), track(track_right)
+        nmp = len(keep[0][0])
+        d = _u8(mp_desc).reshape(-1, 32)
+        ob = _u8(observed)
+        l2r, r2l = _i32(left_to_right), _i32(right_to_left)
+        kp = np.full(left.N + right.N, -1, np.int32) if kp_mp is None else _i32(kp_mp).copy()
+        nm = C.c_int(0)
+        _check(lib().orbx_search_by_projection_mappoints_stereo(self._m, C.byref(left.c), C.byref(right.c), nmp, C.byref(tl), C.byref(tr), _p(d),
+                                                                _p(ob), _p(l2r), _p(r2l), C.c_float(th), C.c_float(self.mfNNratio), _p(kp),
+                                                                C.byref(nm)))
+        return nm.value, kp
 
     KNN2_AUTO, KNN2_POPC, KNN2_TENSOR = 0, 1, 2
 

@@ -209,6 +209,39 @@ def test_search_by_projection_two_cameras(rig, th, pre_share, far):
     same(ref2, got2, "SearchLocalPoints core, two cameras")
 
 
+@pytest.mark.parametrize("th,pre_share,rep", [(3.0, 0.0, 1), (5.0, 0.2, 1), (4.0, 0.1, 3)])
+def test_search_by_projection_two_cameras_all_observed(rig, th, pre_share, rep):
+    """every map point has observations (what Tracking::SearchLocalPoints hands over): the drop-in resolves both camera passes as a
+    parallel fixed point (k_resolve_fisheye_par) instead of the one-warp replay; rep = 3 crowds every keypoint with three candidates"""
+    W, obs = rig["W"], rig["obs"]
+    rng = np.random.default_rng(23)
+    n = len(obs["assoc"])
+    view0 = W.view_two_cameras(rm, obs)
+    left, right, depth = _tracks(view0, rig["pts"])
+    order = rng.permutation(W.n * rep)
+    t3 = lambda a: np.tile(a, (rep,) + (1,) * (a.ndim - 1))[order]
+    n_obs = rng.integers(1, 6, W.n * rep).astype(np.int32)
+    P = rm.Points(t3(W.P), t3(W.desc), t3(W.normal), t3(W.min_dist), t3(W.max_dist), n_obs, t3(W.bad))
+
+    def widen(f):
+        g = {k: t3(v) for k, v in f.items()}
+        if rep > 1:
+            g["proj_x"] = (g["proj_x"] + rng.normal(size=W.n * rep) * 1.5).astype(np.float32)
+            g["proj_y"] = (g["proj_y"] + rng.normal(size=W.n * rep) * 1.5).astype(np.float32)
+        return g
+    L, R = widen(left), widen(right)
+    # pre-existing associations must point at observed points of P: map an original index to one of its copies
+    where = np.full(W.n, -1, np.int64)
+    where[order % W.n] = np.arange(W.n * rep)
+    pre = np.where((rng.random(n) < pre_share) & (obs["assoc"] >= 0), where[np.maximum(obs["assoc"], 0)], -1).astype(np.int32)
+    view = W.view_two_cameras(rm, obs, assoc=pre)
+    ref, got = both(rm.search_by_projection_mappoints_stereo, view, P, th, 0.8, L, R, pre)
+    same(ref, got, "SearchByProjection two cameras, all observed")
+    nl = obs["n_left"]
+    new = (ref[1] >= 0) & (ref[1] != pre)
+    assert new[:nl].sum() > 100 and new[nl:].sum() > 100
+
+
 def test_search_by_projection_two_cameras_crowded(rig):
     """many map points per keypoint and map points without observations: claims get replaced through the partner hand-over"""
     W, obs = rig["W"], rig["obs"]
