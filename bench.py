@@ -881,7 +881,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="orbx", choices=["orbx", "reference"])
     ap.add_argument("--batch", type=int, default=256, help="stereo frames per launch per GPU")
-    ap.add_argument("--substeps", type=int, default=32, help="launches per step: a step is substeps*batch stereo frames per GPU")
+    ap.add_argument("--substeps", type=int, default=40, help="launches per step: a step is substeps*batch stereo frames per GPU")
     ap.add_argument("--e2e-chunks", type=int, default=4, help="chunks per orbx_stereo_frames_host call (copy/compute overlap)")
     ap.add_argument("--e2e-workers", type=int, default=0, help="host threads issuing the blocking e2e call on their own handles (0 = 2, or 1 from 4 ranks up)")
     ap.add_argument("--e2e-no-right", action="store_true", help="leave the right image's keypoints/descriptors on the device (rectified stereo needs only uRight/depth)")
