@@ -502,6 +502,9 @@ void orbx_destroy(orbx_extractor* h) {
     if (s.evBatch) cudaEventDestroy(s.evBatch);
   }
   if (h->dPattern) cudaFree(h->dPattern);
+  if (h->upStream) cudaStreamDestroy(h->upStream);
+  for (int k = 0; k < 2; k++) { if (h->evUp[k]) cudaEventDestroy(h->evUp[k]); if (h->evInFree[k]) cudaEventDestroy(h->evInFree[k]); }
+  if (h->hRing) cudaFreeHost(h->hRing);
   if (h->lat.exec) cudaGraphExecDestroy(h->lat.exec);
   if (h->lat.hIn) cudaFreeHost(h->lat.hIn);
   if (h->lat.hOut) cudaFreeHost(h->lat.hOut);
@@ -673,44 +676,61 @@ int orbx_extract_batch_host(orbx_extractor* h, const uint8_t* images, int nframe
     }
     return ORBX_OK;
   }
-  // pipelined path (many frames): on every return below, nothing may still be writing into the caller's buffers
-  struct Drain { orbx_extractor* h; ~Drain() { for (Slot& s : h->slot) cudaStreamSynchronize(s.stream); } } drain{h};
+  // pipelined path (many frames).  Uploads run back to back on their own stream; a slot's kernels wait for their upload on the device and
+  // release the slot's input buffer with an event when they are done with it (level 0 is read until the descriptor stage); downloads follow
+  // the kernels on the slot stream; the host only waits at the end (or when the status ring wraps).
+  if (!h->upStream) {
+    std::lock_guard<std::recursive_mutex> setupLock(setup_mutex());
+    CK(cudaSetDevice(h->p.device));
+    CK(cudaStreamCreateWithFlags(&h->upStream, cudaStreamNonBlocking));
+    for (int k = 0; k < 2; k++) {
+      CK(cudaEventCreateWithFlags(&h->evUp[k], cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&h->evInFree[k], cudaEventDisableTiming));
+    }
+    CK(cudaHostAlloc((void**)&h->hRing, orbx_extractor::kRing * sizeof(int), cudaHostAllocDefault));
+  }
+  // on every return below, nothing may still be writing into the caller's buffers
+  struct Drain { orbx_extractor* h; ~Drain() { cudaStreamSynchronize(h->upStream); for (Slot& s : h->slot) cudaStreamSynchronize(s.stream); } } drain{h};
+  auto check_ring = [&](int used) -> int {
+    for (Slot& s : h->slot) CK(cudaStreamSynchronize(s.stream));
+    for (int k = 0; k < used; k++)
+      if (h->hRing[k] != 0) { set_error("device reported status %d (capacity)", h->hRing[k]); return h->hRing[k]; }
+    return ORBX_OK;
+  };
   int chunk = 0;
   for (int f0 = 0; f0 < nframes; f0 += B, chunk++) {
     const int nb = std::min(B, nframes - f0);
     const int si = chunk & 1;
     Slot& s = h->slot[si];
-    cudaStream_t st = s.stream;
-    // (the slot's previous chunk was enqueued on the same stream, so its D2H copies finish before these buffers are reused)
+    cudaStream_t st = s.stream, up = h->upStream;
+    CK(cudaStreamWaitEvent(up, h->evInFree[si], 0));   // the slot's previous kernels no longer read its input buffer
     const uint8_t* src = images + (size_t)f0 * frameStride;
     if (frameStride == (size_t)stride * height && stride == h->inPitch) {
-      CK(cudaMemcpyAsync(s.in, src, (size_t)stride * height * nb, cudaMemcpyHostToDevice, st));
+      CK(cudaMemcpyAsync(s.in, src, (size_t)stride * height * nb, cudaMemcpyHostToDevice, up));
     } else if (frameStride == (size_t)stride * height) {
-      CK(cudaMemcpy2DAsync(s.in, h->inPitch, src, stride, width, (size_t)height * nb, cudaMemcpyHostToDevice, st));
+      CK(cudaMemcpy2DAsync(s.in, h->inPitch, src, stride, width, (size_t)height * nb, cudaMemcpyHostToDevice, up));
     } else {
       for (int f = 0; f < nb; f++)
         CK(cudaMemcpy2DAsync(s.in + (size_t)f * h->inPitch * height, h->inPitch, src + (size_t)f * frameStride, stride, width, height,
-                             cudaMemcpyHostToDevice, st));
+                             cudaMemcpyHostToDevice, up));
     }
+    CK(cudaEventRecord(h->evUp[si], up));
+    CK(cudaStreamWaitEvent(st, h->evUp[si], 0));
+    // (the slot's previous chunk was enqueued on the same stream, so its D2H copies finish before the result buffers are rewritten)
     rc = extractor_run_batch(h, si, s.in, nb, h->inPitch, (long long)h->inPitch * height, lap0, lap1, st);
     if (rc != ORBX_OK) return rc;
+    CK(cudaEventRecord(h->evInFree[si], st));
     CK(cudaMemcpyAsync(counts + f0, s.counts, nb * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(mono + f0, s.mono, nb * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpy2DAsync(kps + (size_t)f0 * capPerFrame, (size_t)capPerFrame * sizeof(orbx_keypoint), s.kps,
                          (size_t)g.kpStride * sizeof(orbx_keypoint), (size_t)ncopy * sizeof(orbx_keypoint), nb, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpy2DAsync(desc + (size_t)f0 * capPerFrame * 32, (size_t)capPerFrame * 32, s.desc, (size_t)g.kpStride * 32, (size_t)ncopy * 32, nb,
                          cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(h->hRing + chunk % orbx_extractor::kRing, s.status, sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(s.hStatus, s.status, sizeof(int), cudaMemcpyDeviceToHost, st));
-    if (chunk >= 1) {  // keep at most two chunks in flight: wait for the other slot before queueing a third
-      Slot& o = h->slot[si ^ 1];
-      CK(cudaStreamSynchronize(o.stream));
-      if (*o.hStatus != 0) { set_error("device reported status %d (capacity)", *o.hStatus); return *o.hStatus; }
-    }
+    if ((chunk + 1) % orbx_extractor::kRing == 0 && (rc = check_ring(orbx_extractor::kRing)) != ORBX_OK) return rc;
   }
-  for (Slot& s : h->slot) {
-    CK(cudaStreamSynchronize(s.stream));
-    if (s.hStatus && s.lastFrames > 0 && *s.hStatus != 0) { set_error("device reported status %d (capacity)", *s.hStatus); return *s.hStatus; }
-  }
+  if ((rc = check_ring(chunk % orbx_extractor::kRing)) != ORBX_OK) return rc;
   for (int f = 0; f < nframes; f++)
     if (counts[f] > capPerFrame) { set_error("frame %d has %d keypoints, capacity %d", f, counts[f], capPerFrame); return ORBX_ERR_CAPACITY; }
   return ORBX_OK;

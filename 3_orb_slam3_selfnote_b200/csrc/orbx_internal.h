@@ -89,6 +89,10 @@ struct orbx_extractor {
     cudaGraphExec_t exec = nullptr;
     int nb = 0, lap0 = 0, lap1 = 0; unsigned long long epoch = 0;
   } lat;
+  // pipelined host path (many chunks per call): uploads run back to back on their own stream, a slot's kernels wait for its upload on
+  // the device, its input buffer is released by an event after the kernels; chunk status words land in a page-locked ring
+  cudaStream_t upStream = nullptr; cudaEvent_t evUp[2] = {nullptr, nullptr}, evInFree[2] = {nullptr, nullptr};
+  int* hRing = nullptr; static constexpr int kRing = 32;
 };
 
 
