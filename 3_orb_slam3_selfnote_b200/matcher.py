@@ -219,6 +219,19 @@ class ORBmatcher:
                                         int(self.mbCheckOrientation), _p(m12), C.byref(nm)))
         return nm.value, m12[:len(kps1)]
 
+    def SearchByBoWTwoCameras(self, kps1, desc1, fv1, elig1, kps2, desc2, fv2, n_left2, max_dist=TH_LOW):
+        """orbx_search_by_bow_stereo: SearchByBoW(KeyFrame, Frame) with a fisheye-stereo frame on side 2 (ORBmatcher.cc:338-431)
+        -> (nmatches, matches12_left, matches12_right)"""
+        kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+        desc1, desc2, elig1 = _u8(desc1), _u8(desc2), _u8(elig1)
+        c1, keep1 = self._fv(fv1); c2, keep2 = self._fv(fv2)
+        mL = np.full(max(len(kps1), 1), -1, np.int32); mR = np.full(max(len(kps1), 1), -1, np.int32)
+        nm = C.c_int(0)
+        _check(lib().orbx_search_by_bow_stereo(self._m, len(kps1), _p(kps1), _p(desc1), C.byref(c1), _p(elig1), len(kps2), int(n_left2), _p(kps2),
+                                               _p(desc2), C.byref(c2), int(max_dist), C.c_float(self.mfNNratio), int(self.mbCheckOrientation),
+                                               _p(mL), _p(mR), C.byref(nm)))
+        return nm.value, mL[:len(kps1)], mR[:len(kps1)]
+
     def SearchForTriangulation(self, kps1, desc1, fv1, elig1, stereo1, kps2, desc2, fv2, elig2, stereo2, F12, ep, scale_factors2,
                                level_sigma2_2, coarse=False):
         kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)

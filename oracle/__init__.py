@@ -243,6 +243,28 @@ def search_by_projection_mappoints(kps, desc, scale_factors, w, h, in_view, proj
     return nm, kp_mp
 
 
+def search_by_projection_mappoints_stereo(kps_l, desc_l, kps_r, desc_r, scale_factors, w, h, left, right, mp_desc, l2r, r2l, th, nnratio,
+                                          observed=None, kp_mp=None):
+    """ORBmatcher::SearchByProjection(Frame, MapPoints) on a fisheye-stereo frame (ORBmatcher.cc:44-211); left / right =
+    dict(in_view, proj_x, proj_y, level, view_cos) of the two cameras -> (nmatches, kp_mp[nL + nR])"""
+    kps_l = np.ascontiguousarray(kps_l, KP_DTYPE); kps_r = np.ascontiguousarray(kps_r, KP_DTYPE)
+    desc_l = _u8(desc_l); desc_r = _u8(desc_r)
+    nl, nr = kps_l.shape[0], kps_r.shape[0]
+    kp_mp = np.full(nl + nr, -1, np.int32) if kp_mp is None else np.ascontiguousarray(kp_mp, np.int32).copy()
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    u8 = lambda a: None if a is None else np.ascontiguousarray(a, np.uint8)
+    i32 = lambda a: np.ascontiguousarray(a, np.int32)
+    sf = f32(scale_factors)
+    t = []
+    for f in (left, right):
+        t += [u8(f["in_view"]), f32(f["proj_x"]), f32(f["proj_y"]), i32(f["level"]), f32(f["view_cos"])]
+    mp_desc = _u8(mp_desc); observed = u8(observed); l2r = i32(l2r); r2l = i32(r2l)
+    nm = lib().oro_search_by_projection_mappoints_stereo(nl, _p(kps_l), _p(desc_l), nr, _p(kps_r), _p(desc_r), _p(sf), _p(_bounds(w, h)),
+                                                         t[0].shape[0], *[_p(x) for x in t], _p(mp_desc), _p(observed), _p(l2r), _p(r2l),
+                                                         C.c_float(th), C.c_float(nnratio), _p(kp_mp))
+    return nm, kp_mp
+
+
 def search_by_projection_window(kps, desc, scale_factors, w, h, valid, u, v, lvl, angle, srcDesc, th, mode=0, dist_th=100,
                                 any_mp_blocks=False, check_orientation=True, kp_mp=None, observed=None, uRight=None, ur=None):
     kps = np.ascontiguousarray(kps, KP_DTYPE)
@@ -287,6 +309,19 @@ def search_by_bow(kps1, desc1, fv1, elig1, kps2, desc2, fv2, elig2, max_dist, nn
                                  _p(kps2), _p(desc2), i2.shape[0], _p(i2), _p(s2), _p(x2), _p(elig2), int(max_dist),
                                  C.c_float(nnratio), int(check_orientation), _p(m12))
     return nm, m12[:kps1.shape[0]]
+
+
+def search_by_bow_stereo(kps1, desc1, fv1, elig1, kps2, desc2, fv2, n_left2, max_dist, nnratio, check_orientation=True):
+    """SearchByBoW(KeyFrame, Frame) with a fisheye-stereo frame on side 2 (ORBmatcher.cc:338-431) -> (nmatches, matches12_left, matches12_right)"""
+    kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+    desc1, desc2 = _u8(desc1), _u8(desc2)
+    i1, s1, x1 = _fv(fv1); i2, s2, x2 = _fv(fv2)
+    elig1 = _u8(elig1)
+    mL = np.empty(max(kps1.shape[0], 1), np.int32); mR = np.empty(max(kps1.shape[0], 1), np.int32)
+    nm = lib().oro_search_by_bow_stereo(kps1.shape[0], _p(kps1), _p(desc1), i1.shape[0], _p(i1), _p(s1), _p(x1), _p(elig1), kps2.shape[0],
+                                        int(n_left2), _p(kps2), _p(desc2), i2.shape[0], _p(i2), _p(s2), _p(x2), int(max_dist),
+                                        C.c_float(nnratio), int(check_orientation), _p(mL), _p(mR))
+    return nm, mL[:kps1.shape[0]], mR[:kps1.shape[0]]
 
 
 def search_for_triangulation(kps1, desc1, fv1, elig1, stereo1, kps2, desc2, fv2, elig2, stereo2, F12, ep, scale_factors2,

@@ -111,6 +111,69 @@ int search_by_projection_mappoints(FrameView& F, int nMP, const uint8_t* in_view
   return nmatches;
 }
 
+// ORBmatcher.cc:44-211 on a fisheye-stereo frame (F.Nleft != -1): FL = mvKeys / descriptor rows [0, Nleft) / the left grid, FR =
+// mvKeysRight / rows [Nleft, N) / mGridRight; kp_mp = F.mvpMapPoints as indices ([nL + nR], coded as above).  Per map point the
+// left-camera pass (:63-141; its failed ratio test `continue`s past the right pass, :121-122), then the right-camera pass (:144-211: no
+// th factor on the radius, skipped when mnTrackScaleLevelR == -1).  A match also hands the point to the keypoint's stereo partner
+// (mvLeftToRightMatch / mvRightToLeftMatch) and counts it (:131-135, :196-200).
+int search_by_projection_mappoints_stereo(FrameView& FL, FrameView& FR, int nMP, const uint8_t* inL, const float* pxL, const float* pyL,
+                                          const int* lvL, const float* vcL, const uint8_t* inR, const float* pxR, const float* pyR,
+                                          const int* lvR, const float* vcR, const uint8_t* mpDesc, const uint8_t* observed,
+                                          const int* l2r, const int* r2l, float th, float nnratio, int* kp_mp) {
+  int nmatches = 0;
+  const bool bFactor = th != 1.0;
+  const int Nleft = FL.N;
+  for (int iMP = 0; iMP < nMP; iMP++) {
+    if (!inL[iMP] && !inR[iMP]) continue;
+    const uint8_t* MPdescriptor = mpDesc + 32 * (size_t)iMP;
+    if (inL[iMP]) {
+      const int nPredictedLevel = lvL[iMP];
+      float r = (vcL[iMP] > 0.998) ? 2.5f : 4.0f;
+      if (bFactor) r *= th;
+      const std::vector<int> vIndices = FL.getFeaturesInArea(pxL[iMP], pyL[iMP], r * FL.scaleFactors[nPredictedLevel], nPredictedLevel - 1, nPredictedLevel);
+      if (!vIndices.empty()) {
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int idx : vIndices) {
+          if (blocks(kp_mp[idx], observed)) continue;
+          const int dist = hamming256(MPdescriptor, FL.desc + 32 * (size_t)idx);
+          if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = FL.kps[idx].octave; bestIdx = idx; }
+          else if (dist < bestDist2) { bestLevel2 = FL.kps[idx].octave; bestDist2 = dist; }
+        }
+        if (bestDist <= TH_HIGH) {
+          if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+          if (bestLevel != bestLevel2 || bestDist <= nnratio * bestDist2) {
+            kp_mp[bestIdx] = iMP;
+            if (l2r[bestIdx] != -1) { kp_mp[l2r[bestIdx] + Nleft] = iMP; nmatches++; }
+            nmatches++;
+          }
+        }
+      }
+    }
+    if (inR[iMP]) {
+      const int nPredictedLevel = lvR[iMP];
+      if (nPredictedLevel != -1) {
+        const float r = (vcR[iMP] > 0.998) ? 2.5f : 4.0f;
+        const std::vector<int> vIndices = FR.getFeaturesInArea(pxR[iMP], pyR[iMP], r * FR.scaleFactors[nPredictedLevel], nPredictedLevel - 1, nPredictedLevel);
+        if (vIndices.empty()) continue;
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int idx : vIndices) {
+          if (blocks(kp_mp[idx + Nleft], observed)) continue;
+          const int dist = hamming256(MPdescriptor, FR.desc + 32 * (size_t)idx);
+          if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = FR.kps[idx].octave; bestIdx = idx; }
+          else if (dist < bestDist2) { bestLevel2 = FR.kps[idx].octave; bestDist2 = dist; }
+        }
+        if (bestDist <= TH_HIGH) {
+          if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+          if (r2l[bestIdx] != -1) { kp_mp[r2l[bestIdx]] = iMP; nmatches++; }
+          kp_mp[bestIdx + Nleft] = iMP;
+          nmatches++;
+        }
+      }
+    }
+  }
+  return nmatches;
+}
+
 // ORBmatcher.cc:2027-2289 (Frame/Frame), :2291-2413 (Frame/KeyFrame) and :489-720 (KeyFrame/Scw, mode 3), search part.
 int search_by_projection_window(FrameView& F, int n, const uint8_t* valid, const float* u, const float* v, const int* lvl,
                                 const float* ur, const float* angle, const uint8_t* srcDesc, const uint8_t* observed, float th,
@@ -388,6 +451,56 @@ int search_by_bow(int n1, const KeyPoint* kps1, const uint8_t* desc1, const Feat
     for (int i = 0; i < HISTO_LENGTH; i++)
       if (i != ind1 && i != ind2 && i != ind3)
         for (int j : rotHist[i]) { matches12[j] = -1; nmatches--; }
+  }
+  return nmatches;
+}
+
+// ORBmatcher.cc:273-475 when the frame is a fisheye-stereo one (F.Nleft != -1, :338-431): side 2 holds N = nLeft2 + Nright features; within
+// a node the left-image candidates go through best / second-best, the right-image ones keep their best; the right match is taken inside
+// `bestDist1 <= TH_LOW` whatever the left ratio test said, and its own ratio test is voided by "|| true" (:400-403).  Both claim.
+int search_by_bow_stereo(int n1, const KeyPoint* kps1, const uint8_t* desc1, const FeatVec& fv1, const uint8_t* elig1, int n2, int nLeft2,
+                         const KeyPoint* kps2, const uint8_t* desc2, const FeatVec& fv2, int maxDist, float nnratio, bool check_orientation,
+                         int* matches12L, int* matches12R) {
+  for (int i = 0; i < n1; i++) { matches12L[i] = -1; matches12R[i] = -1; }
+  std::vector<uint8_t> claimed2(n2, 0);
+  std::vector<std::pair<int, int> > rotHist[HISTO_LENGTH];   // (idx1, 0 = left match / 1 = right match)
+  int nmatches = 0;
+  for_common_nodes(fv1, fv2, [&](int a, int b) {
+    for (int p1 = fv1.nodeStart[a]; p1 < fv1.nodeStart[a + 1]; p1++) {
+      const int idx1 = (int)fv1.indices[p1];
+      if (idx1 >= n1 || !elig1[idx1]) continue;
+      const uint8_t* d1 = desc1 + 32 * (size_t)idx1;
+      int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256, bestDist1R = 256, bestIdxFR = -1, bestDist2R = 256;
+      for (int p2 = fv2.nodeStart[b]; p2 < fv2.nodeStart[b + 1]; p2++) {
+        const int idx2 = (int)fv2.indices[p2];
+        if (idx2 >= n2 || claimed2[idx2]) continue;
+        const int dist = hamming256(d1, desc2 + 32 * (size_t)idx2);
+        if (idx2 < nLeft2 && dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = idx2; }
+        else if (idx2 < nLeft2 && dist < bestDist2) bestDist2 = dist;
+        if (idx2 >= nLeft2 && dist < bestDist1R) { bestDist2R = bestDist1R; bestDist1R = dist; bestIdxFR = idx2; }
+        else if (idx2 >= nLeft2 && dist < bestDist2R) bestDist2R = dist;
+      }
+      if (bestDist1 <= maxDist) {
+        if ((float)bestDist1 < nnratio * (float)bestDist2) {
+          matches12L[idx1] = bestIdxF; claimed2[bestIdxF] = 1;
+          if (check_orientation) rotHist[rot_bin_of(kps1[idx1].angle, kps2[bestIdxF].angle)].push_back(std::make_pair(idx1, 0));
+          nmatches++;
+        }
+        if (bestDist1R <= maxDist) {
+          matches12R[idx1] = bestIdxFR; claimed2[bestIdxFR] = 1;
+          if (check_orientation) rotHist[rot_bin_of(kps1[idx1].angle, kps2[bestIdxFR].angle)].push_back(std::make_pair(idx1, 1));
+          nmatches++;
+        }
+      }
+    }
+  });
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1, hs[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; i++) hs[i] = (int)rotHist[i].size();
+    compute_three_maxima(hs, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++)
+      if (i != ind1 && i != ind2 && i != ind3)
+        for (const auto& j : rotHist[i]) { (j.second ? matches12R : matches12L)[j.first] = -1; nmatches--; }
   }
   return nmatches;
 }

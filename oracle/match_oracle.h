@@ -53,6 +53,10 @@ void compute_three_maxima(const int* hist_sizes, int L, int& ind1, int& ind2, in
 // projXR (mTrackProjXR; used only when F.uRight != null).  kp_mp[] is F.mvpMapPoints as indices: -1 empty,
 // -2 = pre-existing map point with observations (blocks), -3 = pre-existing map point without observations (does not block).
 // Returns nmatches.
+int search_by_projection_mappoints_stereo(FrameView& FL, FrameView& FR, int nMP, const uint8_t* inL, const float* pxL, const float* pyL,
+                                          const int* lvL, const float* vcL, const uint8_t* inR, const float* pxR, const float* pyR,
+                                          const int* lvR, const float* vcR, const uint8_t* mpDesc, const uint8_t* observed,
+                                          const int* l2r, const int* r2l, float th, float nnratio, int* kp_mp);
 int search_by_projection_mappoints(FrameView& F, int nMP, const uint8_t* in_view, const float* projX, const float* projY,
                                    const int* level, const float* viewCos, const uint8_t* mpDesc, const uint8_t* observed,
                                    const float* projXR, float th, float nnratio, int* kp_mp);
@@ -95,6 +99,9 @@ struct FeatVec {
 // feature is skipped by later side-1 features.  Accept when best <= maxDist and (float)best < nnratio * (float)second.
 // maxDist = TH_LOW for KF-Frame (":<=TH_LOW"), TH_LOW - 1 for KF-KF ("<TH_LOW").  matches12[i] = j or -1; returns nmatches
 // after the rotation filter (angle1 - angle2 histogram).
+int search_by_bow_stereo(int n1, const KeyPoint* kps1, const uint8_t* desc1, const FeatVec& fv1, const uint8_t* elig1, int n2, int nLeft2,
+                         const KeyPoint* kps2, const uint8_t* desc2, const FeatVec& fv2, int maxDist, float nnratio, bool check_orientation,
+                         int* matches12L, int* matches12R);
 int search_by_bow(int n1, const KeyPoint* kps1, const uint8_t* desc1, const FeatVec& fv1, const uint8_t* elig1, int n2,
                   const KeyPoint* kps2, const uint8_t* desc2, const FeatVec& fv2, const uint8_t* elig2, int maxDist, float nnratio,
                   bool check_orientation, int* matches12);

@@ -133,6 +133,16 @@ int oro_search_by_projection_mappoints(int N, const KeyPoint* kps, const uint8_t
   fill_view(F, N, kps, desc, uRight, scaleFactors, bounds4);
   return search_by_projection_mappoints(F, nMP, in_view, projX, projY, level, viewCos, mpDesc, observed, projXR, th, nnratio, kp_mp);
 }
+int oro_search_by_projection_mappoints_stereo(int nL, const KeyPoint* kpsL, const uint8_t* descL, int nR, const KeyPoint* kpsR, const uint8_t* descR,
+                                              const float* scaleFactors, const float* bounds4, int nMP, const uint8_t* inL, const float* pxL,
+                                              const float* pyL, const int* lvL, const float* vcL, const uint8_t* inR, const float* pxR,
+                                              const float* pyR, const int* lvR, const float* vcR, const uint8_t* mpDesc, const uint8_t* observed,
+                                              const int* l2r, const int* r2l, float th, float nnratio, int* kp_mp) {
+  FrameView FL, FR;
+  fill_view(FL, nL, kpsL, descL, nullptr, scaleFactors, bounds4);
+  fill_view(FR, nR, kpsR, descR, nullptr, scaleFactors, bounds4);
+  return search_by_projection_mappoints_stereo(FL, FR, nMP, inL, pxL, pyL, lvL, vcL, inR, pxR, pyR, lvR, vcR, mpDesc, observed, l2r, r2l, th, nnratio, kp_mp);
+}
 int oro_search_by_projection_window(int N, const KeyPoint* kps, const uint8_t* desc, const float* uRight, const float* scaleFactors,
                                     const float* bounds4, int n, const uint8_t* valid, const float* u, const float* v, const int* lvl,
                                     const float* ur, const float* angle, const uint8_t* srcDesc, const uint8_t* observed, float th,
@@ -170,6 +180,13 @@ int oro_search_by_bow(int n1, const KeyPoint* kps1, const uint8_t* desc1, int nn
                       int check_orientation, int* matches12) {
   return search_by_bow(n1, kps1, desc1, fv_of(nn1, ids1, start1, ind1), elig1, n2, kps2, desc2, fv_of(nn2, ids2, start2, ind2), elig2,
                        maxDist, nnratio, check_orientation != 0, matches12);
+}
+int oro_search_by_bow_stereo(int n1, const KeyPoint* kps1, const uint8_t* desc1, int nn1, const uint32_t* ids1, const int* start1,
+                             const uint32_t* ind1, const uint8_t* elig1, int n2, int nLeft2, const KeyPoint* kps2, const uint8_t* desc2, int nn2,
+                             const uint32_t* ids2, const int* start2, const uint32_t* ind2, int maxDist, float nnratio, int check_orientation,
+                             int* matches12L, int* matches12R) {
+  return search_by_bow_stereo(n1, kps1, desc1, fv_of(nn1, ids1, start1, ind1), elig1, n2, nLeft2, kps2, desc2, fv_of(nn2, ids2, start2, ind2),
+                              maxDist, nnratio, check_orientation != 0, matches12L, matches12R);
 }
 int oro_search_for_triangulation(int n1, const KeyPoint* kps1, const uint8_t* desc1, int nn1, const uint32_t* ids1, const int* start1,
                                  const uint32_t* ind1, const uint8_t* elig1, const uint8_t* stereo1, int n2, const KeyPoint* kps2,

@@ -218,3 +218,70 @@ def test_parallel_resolve_on_long_claim_chains(orbx, oracle, synth, frames):
     got = m.SearchByBoW(k1, d1, fv1, np.ones(n, np.uint8), k, d, fv2, None, 50)
     assert got[0] == ref[0] and np.array_equal(got[1], ref[1]) and ref[0] > 100
     m.close()
+
+
+@pytest.mark.parametrize("th,all_observed,pre_share", [(1.0, True, 0.0), (4.0, True, 0.2), (3.0, False, 0.2), (5.0, False, 0.0)])
+def test_search_by_projection_two_cameras_vs_oracle(orbx, oracle, th, all_observed, pre_share):
+    """orbx_search_by_projection_mappoints_stereo through the C-ABI against the CPU restatement (ORBmatcher.cc:44-211 on a fisheye-stereo
+    frame; the restatement is pinned to the reference's compiled source in test_oracle_refmatch.py): every map point observed -> the cluster
+    fixed point k_resolve_fisheye_par, otherwise the one-warp replay k_resolve_fisheye.  Tracking fields are synthetic here (no _ref needed):
+    projections of the keypoints' own map points plus jitter, so windows overlap and claims collide."""
+    import world_cases as wc
+    W = wc.World(seed=21, n_pts=1800, cam=wc.KB8, n_dup=0)
+    rng = np.random.default_rng(31)
+    n_obs = np.maximum(W.n_obs, 1) if all_observed else W.n_obs
+    R, t = W.pose(seed=4)
+    obs = W.observe_two_cameras(R, t, seed=9)
+    nl = obs["n_left"]
+    kl, kr = obs["kps"], obs["kps_right"]
+    w, h = W.cam["size"]
+    sf = np.float32(1.2) ** np.arange(8, dtype=np.float32)
+
+    def track(kps, mp):
+        inv = np.zeros(W.n, np.uint8); px = np.zeros(W.n, np.float32); py = np.zeros(W.n, np.float32)
+        lv = np.full(W.n, -1, np.int32); vc = np.full(W.n, 0.9, np.float32)
+        sel = mp >= 0
+        idx = mp[sel]
+        inv[idx] = 1
+        px[idx] = kps["x"][sel] + rng.normal(size=sel.sum()).astype(np.float32) * 2.0
+        py[idx] = kps["y"][sel] + rng.normal(size=sel.sum()).astype(np.float32) * 2.0
+        lv[idx] = np.clip(kps["octave"][sel] + rng.integers(0, 2, sel.sum()), 0, 7)
+        vc[idx] = np.where(rng.random(sel.sum()) < 0.5, 0.999, 0.9).astype(np.float32)
+        return dict(in_view=inv, proj_x=px, proj_y=py, level=lv, view_cos=vc)
+    left, right = track(kl, obs["mp_idx"][:nl]), track(kr, obs["mp_idx"][nl:])
+    right["level"][rng.random(W.n) < 0.05] = -1          # mnTrackScaleLevelR == -1: no right pass (:146)
+    pre = np.where((rng.random(len(obs["assoc"])) < pre_share) & (obs["assoc"] >= 0), obs["assoc"], -1)
+    code = np.where(pre < 0, -1, np.where(n_obs[np.maximum(pre, 0)] > 0, -2, -3)).astype(np.int32)
+    observed = (n_obs > 0).astype(np.uint8)
+    nm_o, kp_o = oracle.search_by_projection_mappoints_stereo(kl, obs["desc"][:nl], kr, obs["desc"][nl:], sf, w, h, left, right, W.desc,
+                                                              obs["l2r"], obs["r2l"], th, 0.8, observed=observed, kp_mp=code)
+    m = orbx.ORBmatcher(0.8)
+    FL, FR = orbx.FrameView(kl, obs["desc"][:nl], sf, w, h), orbx.FrameView(kr, obs["desc"][nl:], sf, w, h)
+    nm_g, kp_g = m.SearchByProjectionTwoCameras(FL, FR, left, right, W.desc, obs["l2r"], obs["r2l"], th, observed=observed, kp_mp=code)
+    m.close()
+    assert nm_g == nm_o and nm_o > 600
+    assert np.array_equal(kp_g, kp_o)
+    assert (kp_o[:nl] >= 0).sum() > 200 and (kp_o[nl:] >= 0).sum() > 200
+
+
+@pytest.mark.parametrize("ori,ratio", [(True, 0.7), (False, 0.7), (True, 0.9)])
+def test_search_by_bow_two_cameras_vs_oracle(orbx, oracle, ori, ratio):
+    """orbx_search_by_bow_stereo through the C-ABI against the CPU restatement of ORBmatcher.cc:338-431 (pinned to the reference's compiled
+    source in test_oracle_refmatch.py): left / right matching of a keyframe feature inside the cluster fixed point, shared rotation filter"""
+    import world_cases as wc
+    W = wc.World(seed=33, n_pts=1800, cam=wc.KB8, n_dup=0)
+    R, t = W.pose(seed=5)
+    obs = W.observe_two_cameras(R, t, seed=12)
+    R2, t2 = W.pose(seed=6)
+    ko = W.observe(R2, t2, seed=14)
+    fvF = feature_vector(obs["desc"], 24, seed=2)
+    fvK = feature_vector(ko["desc"], 24, seed=2)
+    kps2 = np.concatenate([obs["kps"], obs["kps_right"]])
+    elig = ((ko["assoc"] >= 0) & (W.bad[np.maximum(ko["assoc"], 0)] == 0)).astype(np.uint8)
+    nm_o, mL_o, mR_o = oracle.search_by_bow_stereo(ko["kps"], ko["desc"], fvK, elig, kps2, obs["desc"], fvF, obs["n_left"], 50, ratio, ori)
+    m = orbx.ORBmatcher(ratio, ori)
+    nm_g, mL_g, mR_g = m.SearchByBoWTwoCameras(ko["kps"], ko["desc"], fvK, elig, kps2, obs["desc"], fvF, obs["n_left"])
+    m.close()
+    assert nm_g == nm_o and nm_o > 300
+    assert np.array_equal(mL_g, mL_o) and np.array_equal(mR_g, mR_o)
+    assert (mL_o >= 0).sum() > 100 and (mR_o >= 0).sum() > 100 and (mR_o[mR_o >= 0] >= obs["n_left"]).all()

@@ -189,3 +189,61 @@ def test_search_for_initialization_and_bow(oracle, scene):
     nm, m12 = oracle.search_by_bow(A["kps"], A["desc"], fva, elig, B["kps"], B["desc"], fvb, elig2, 50, 0.75, True)
     got = np.where(m12 >= 0, B["assoc"][np.clip(m12, 0, None)], -1).astype(np.int32)
     assert nm == nm_ref and np.array_equal(got, out_ref) and nm > 10
+
+
+@pytest.mark.parametrize("th,all_observed", [(1.0, False), (3.0, False), (4.0, True)])
+def test_search_by_projection_two_cameras_restatement(th, all_observed):
+    """oracle.search_by_projection_mappoints_stereo (ORBmatcher.cc:44-211 on a fisheye-stereo frame) == the reference's compiled ORBmatcher.cc,
+    with the tracking fields of both cameras written by the reference's own Frame::isInFrustum (src/Frame.cc:643-660, 1270-1343)"""
+    import oracle
+    W = wc.World(seed=8, n_pts=1600, cam=wc.KB8, n_dup=200)
+    if all_observed:
+        W.n_obs[:] = np.maximum(W.n_obs, 1)
+    R, t = W.pose(seed=12)
+    obs = W.observe_two_cameras(R, t, seed=30)
+    n = len(obs["assoc"])
+    pre = np.where(np.random.default_rng(5).random(n) < 0.2, obs["assoc"], -1).astype(np.int32)
+    view = W.view_two_cameras(rm, obs, assoc=pre)
+    pts = W.points(rm)
+    tr = rm.is_in_frustum(view, pts, 0.5, right=True)
+    left = dict(in_view=tr["in_view"], proj_x=tr["proj_x"], proj_y=tr["proj_y"], level=tr["level"], view_cos=tr["view_cos"])
+    right = dict(in_view=tr["in_view_r"], proj_x=tr["proj_xr_r"], proj_y=tr["proj_y_r"], level=tr["level_r"], view_cos=tr["view_cos_r"])
+    nm_r, kp_r = rm.search_by_projection_mappoints_stereo(view, pts, th, 0.8, left, right, pre)
+    # the restatement takes mvpMapPoints coded -1 / -2 (holder with observations) / -3 (holder without) and the gates of :52-62 folded into in_view
+    bad = W.bad != 0
+    gate = lambda f: dict(f, in_view=(np.asarray(f["in_view"]) != 0) & ~bad)
+    code = np.where(pre < 0, -1, np.where(W.n_obs[np.maximum(pre, 0)] > 0, -2, -3)).astype(np.int32)
+    nl = obs["n_left"]
+    w, h = W.cam["size"]
+    nm_o, kp_o = oracle.search_by_projection_mappoints_stereo(obs["kps"], obs["desc"][:nl], obs["kps_right"], obs["desc"][nl:], view.scale, w, h,
+                                                              gate(left), gate(right), W.desc, obs["l2r"], obs["r2l"], th, 0.8,
+                                                              observed=(W.n_obs > 0).astype(np.uint8), kp_mp=code)
+    assert nm_o == nm_r and nm_r > 500
+    got = np.where(kp_o >= 0, kp_o, np.where(code == -1, -1, pre))   # untouched holders keep their map point
+    assert np.array_equal(got, kp_r)
+
+
+@pytest.mark.parametrize("ori", [True, False])
+def test_search_by_bow_two_cameras_restatement(ori):
+    """oracle.search_by_bow_stereo (ORBmatcher.cc:338-431) == the reference's compiled SearchByBoW(KeyFrame, Frame) on a fisheye-stereo frame"""
+    import oracle
+    W = wc.World(seed=8, n_pts=1600, cam=wc.KB8, n_dup=0)
+    R, t = W.pose(seed=12)
+    obs = W.observe_two_cameras(R, t, seed=30)
+    fvF = bowsynth.feature_vector(obs["desc"], 40, seed=3)
+    frame = W.view_two_cameras(rm, obs, feat_vec=fvF)
+    R2, t2 = W.pose(seed=13)
+    ko = W.observe(R2, t2, seed=41)
+    fvK = bowsynth.feature_vector(ko["desc"], 40, seed=3)
+    kf = W.view(rm, ko, assoc=ko["assoc"], feat_vec=fvK)
+    nm_r, out_r = rm.search_by_bow_frame(kf, frame, W.points(rm), 0.7, ori)
+    elig = (ko["assoc"] >= 0) & (W.bad[np.maximum(ko["assoc"], 0)] == 0)
+    kps2 = np.concatenate([obs["kps"], obs["kps_right"]])
+    nm_o, mL, mR = oracle.search_by_bow_stereo(ko["kps"], ko["desc"], fvK, elig.astype(np.uint8), kps2, obs["desc"], fvF, obs["n_left"], 50, 0.7, ori)
+    got = np.full(len(kps2), -1, np.int32)
+    for m in (mL, mR):
+        sel = m >= 0
+        got[m[sel]] = ko["assoc"][sel]
+    assert nm_o == nm_r and nm_r > 300
+    assert np.array_equal(got, out_r)
+    assert (mL >= 0).sum() > 100 and (mR >= 0).sum() > 100
