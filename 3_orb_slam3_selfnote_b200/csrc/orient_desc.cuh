@@ -132,7 +132,11 @@ __global__ void __launch_bounds__(256) k_orient_desc2(const __grid_constant__ Ge
   // rBRIEF
   const float factorPI = (float)(3.1415926535897932384626433832795 / 180.0);
   const float ang = __fmul_rn(angle, factorPI);
-  const float ca = (float)cos((double)ang), sa = (float)sin((double)ang);
+  // (float)cos((double)ang), (float)sin((double)ang) with one shared argument reduction: sincos() gives the same two floats for EVERY float in
+  // [0, 6.3] (all 1 086 953 883 of them compared on the B200, tools/microbench/sincos_check.cu), and ang = angle * pi/180 lies in [0, 2 pi)
+  double sd, cd;
+  sincos((double)ang, &sd, &cd);
+  const float ca = (float)cd, sa = (float)sd;
   const uint8_t* bl = sPatchB[warp] + kOdR * kBlurPitch + kOdR + pa;   // patch centre
   const float4* pat = b.patternF + lane;   // transposed: record j of lane l (pair 8l + j) at [j * 32 + l]
   int bits = 0;
