@@ -845,6 +845,8 @@ __global__ void __launch_bounds__(256) k_stereo_hamming2(const __grid_constant__
   if (iL >= nL) return;
   const long long o = (long long)f * g.kpStride;
   const orbx_keypoint kl = bL.kps[o + iL];
+  uint32_t dl[8];
+  load_desc(bL.desc + (o + iL) * 32, dl);   // independent of the row table: in flight while the row bounds and items arrive
   const int levelL = kl.octave;
   const float vL = kl.y, uL = kl.x;
   const int row = (int)vL;
@@ -854,8 +856,6 @@ __global__ void __launch_bounds__(256) k_stereo_hamming2(const __grid_constant__
     const int* rowStart = rt.rowStart + (long long)f * (rt.rows + 1);
     const int beg = rowStart[row], end = rowStart[row + 1];
     const uint2* items = rt.items + (long long)f * rt.itemCap;
-    uint32_t dl[8];
-    load_desc(bL.desc + (o + iL) * 32, dl);
     for (int j = beg + lane; j < end; j += 32) {
       const uint2 it = items[j];
       const int oct = (int)(it.x >> 16), iR = (int)(it.x & 0xffffu);
