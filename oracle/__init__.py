@@ -341,6 +341,74 @@ def search_for_triangulation(kps1, desc1, fv1, elig1, stereo1, kps2, desc2, fv2,
     return nm, m12[:kps1.shape[0]]
 
 
+LIBM_F32, LIBM_PORTABLE = 0, 1
+
+
+def kb8_pair(R12, t12, cam1, cam2):
+    """One (camera of KF1, camera of KF2) geometry record of the KannalaBrandt8 gate: R12[9] t12[3] cam1[8] cam2[8] (cam = fx fy cx cy k1..k4)"""
+    return np.concatenate([np.asarray(R12, np.float32).reshape(9), np.asarray(t12, np.float32).reshape(3),
+                           np.asarray(cam1, np.float32).reshape(8), np.asarray(cam2, np.float32).reshape(8)])
+
+
+def search_for_triangulation_kb8(kps1, desc1, fv1, elig1, stereo1, n_left1, kps2, desc2, fv2, elig2, stereo2, n_left2, pairs, ep,
+                                 scale_factors2, level_sigma2_1, level_sigma2_2, coarse=False, check_orientation=True,
+                                 libm_mode=LIBM_PORTABLE):
+    """ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:981-1222) on KannalaBrandt8 keyframes: pairs = [kb8_pair(..)] (n_left = -1) or
+    the four records ll, lr, rl, rr of a fisheye-stereo rig (kps = mvKeys followed by mvKeysRight)."""
+    kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+    desc1, desc2 = _u8(desc1), _u8(desc2)
+    i1, s1, x1 = _fv(fv1); i2, s2, x2 = _fv(fv2)
+    u8 = lambda a: None if a is None else np.ascontiguousarray(a, np.uint8)
+    elig1, elig2, stereo1, stereo2 = u8(elig1), u8(elig2), u8(stereo1), u8(stereo2)
+    G = np.ascontiguousarray(np.stack(pairs), np.float32)
+    assert G.shape == ((4 if n_left1 != -1 else 1), 28) and (n_left1 == -1) == (n_left2 == -1)
+    sf = np.ascontiguousarray(scale_factors2, np.float32)
+    l1 = np.ascontiguousarray(level_sigma2_1, np.float32); l2 = np.ascontiguousarray(level_sigma2_2, np.float32)
+    m12 = np.empty(max(kps1.shape[0], 1), np.int32)
+    nm = lib().oro_search_for_triangulation_kb8(kps1.shape[0], _p(kps1), _p(desc1), i1.shape[0], _p(i1), _p(s1), _p(x1), _p(elig1),
+                                                _p(stereo1), int(n_left1), kps2.shape[0], _p(kps2), _p(desc2), i2.shape[0], _p(i2),
+                                                _p(s2), _p(x2), _p(elig2), _p(stereo2), int(n_left2), _p(G), C.c_float(ep[0]),
+                                                C.c_float(ep[1]), _p(sf), _p(l1), _p(l2), int(coarse), int(check_orientation),
+                                                int(libm_mode), _p(m12))
+    return nm, m12[:kps1.shape[0]]
+
+
+def kb8_triangulate_matches(pair, xy1, xy2, sigma1, sigma2, libm_mode=LIBM_PORTABLE):
+    """KannalaBrandt8::TriangulateMatches (KannalaBrandt8.cpp:343-418) for n independent keypoint pairs: (z1 or -1, point) per pair"""
+    pair = np.ascontiguousarray(pair, np.float32).reshape(28)
+    xy1 = np.ascontiguousarray(xy1, np.float32).reshape(-1, 2); xy2 = np.ascontiguousarray(xy2, np.float32).reshape(-1, 2)
+    n = xy1.shape[0]
+    sigma1 = np.ascontiguousarray(np.broadcast_to(np.asarray(sigma1, np.float32), (n,)))
+    sigma2 = np.ascontiguousarray(np.broadcast_to(np.asarray(sigma2, np.float32), (n,)))
+    z1 = np.empty(n, np.float32); p3d = np.empty((n, 3), np.float32)
+    lib().oro_kb8_triangulate_matches(_p(pair), n, _p(xy1), _p(xy2), _p(sigma1), _p(sigma2), int(libm_mode), _p(z1), _p(p3d))
+    return z1, p3d
+
+
+def kb8_unproject(cam, xy, libm_mode=LIBM_PORTABLE):
+    cam = np.ascontiguousarray(cam, np.float32).reshape(8)
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    rays = np.empty((xy.shape[0], 3), np.float32)
+    lib().oro_kb8_unproject(_p(cam), xy.shape[0], _p(xy), int(libm_mode), _p(rays))
+    return rays
+
+
+def kb8_project(cam, X, libm_mode=LIBM_PORTABLE):
+    cam = np.ascontiguousarray(cam, np.float32).reshape(8)
+    X = np.ascontiguousarray(X, np.float32).reshape(-1, 3)
+    uv = np.empty((X.shape[0], 2), np.float32)
+    lib().oro_kb8_project(_p(cam), X.shape[0], _p(X), int(libm_mode), _p(uv))
+    return uv
+
+
+def jacobi_svd4(A):
+    """cv::SVD::compute on 4x4 float32 matrices (n x 4 x 4): (w n x 4, vt n x 4 x 4)"""
+    A = np.ascontiguousarray(A, np.float32).reshape(-1, 4, 4)
+    w = np.empty((A.shape[0], 4), np.float32); vt = np.empty((A.shape[0], 4, 4), np.float32)
+    lib().oro_jacobi_svd4(_p(A), A.shape[0], _p(w), _p(vt))
+    return w, vt
+
+
 def search_window_best(kps, desc, w, h, valid, u, v, radius, level, qdesc, gate=0, inv_level_sigma2=None, uRight=None, ur=None):
     kps = np.ascontiguousarray(kps, KP_DTYPE); desc = _u8(desc)
     f32 = lambda a: None if a is None else np.ascontiguousarray(a, np.float32)

@@ -565,6 +565,217 @@ int search_for_triangulation(int n1, const KeyPoint* kps1, const uint8_t* desc1,
   return nmatches;
 }
 
+// ---- KannalaBrandt8::epipolarConstrain -------------------------------------------------------------------------------------------
+// Every cv::Mat expression of KannalaBrandt8.cpp:343-444 is written out with the rounding OpenCV gives it (oracle/ref_shim/cv_prims.cc
+// holds the same rules behind the stand-in cv:: header the reference's own file is compiled against; tests/test_oracle_cvmat.py pins
+// them to cv2): small gemm = float products summed left to right; Mat::dot / cv::norm = double; s*row - row = one rounding
+// (addWeighted); Mat / s = multiply by (float)(1.0 / s); cv::SVD = JacobiSVDImpl_<float>.
+void kb8_unproject(const float* cam, float u, float v, int libmMode, float* ray) {
+  const float pwx = (u - cam[2]) / cam[0], pwy = (v - cam[3]) / cam[1];
+  float scale = 1.f;
+  float theta_d = sqrtf(pwx * pwx + pwy * pwy);
+  theta_d = fminf(fmaxf((float)(-M_PI / 2.f), theta_d), (float)(M_PI / 2.f));
+  if (theta_d > 1e-8) {
+    float theta = theta_d;
+    for (int j = 0; j < 10; j++) {
+      const float theta2 = theta * theta, theta4 = theta2 * theta2, theta6 = theta4 * theta2, theta8 = theta4 * theta4;
+      const float k0_theta2 = cam[4] * theta2, k1_theta4 = cam[5] * theta4;
+      const float k2_theta6 = cam[6] * theta6, k3_theta8 = cam[7] * theta8;
+      const float theta_fix = (theta * (1 + k0_theta2 + k1_theta4 + k2_theta6 + k3_theta8) - theta_d) /
+                              (1 + 3 * k0_theta2 + 5 * k1_theta4 + 7 * k2_theta6 + 9 * k3_theta8);
+      theta = theta - theta_fix;
+      if (fabsf(theta_fix) < 1e-6f) break;   // KannalaBrandt8::precision (include/CameraModels/KannalaBrandt8.h:47-52)
+    }
+    const float tn = libmMode == LIBM_F32 ? tanf(theta) : (float)std::tan((double)theta);
+    scale = tn / theta_d;
+  }
+  ray[0] = pwx * scale; ray[1] = pwy * scale; ray[2] = 1.f;
+}
+
+void kb8_project(const float* cam, const float* X, int libmMode, float* u, float* v) {
+  const float x2y2 = X[0] * X[0] + X[1] * X[1];
+  const float theta = libmMode == LIBM_F32 ? atan2f(sqrtf(x2y2), X[2]) : (float)std::atan2((double)sqrtf(x2y2), (double)X[2]);
+  const float psi = libmMode == LIBM_F32 ? atan2f(X[1], X[0]) : (float)std::atan2((double)X[1], (double)X[0]);
+  const float theta2 = theta * theta, theta3 = theta * theta2, theta5 = theta3 * theta2, theta7 = theta5 * theta2, theta9 = theta7 * theta2;
+  const float r = theta + cam[4] * theta3 + cam[5] * theta5 + cam[6] * theta7 + cam[7] * theta9;
+  *u = (float)((double)(cam[0] * r) * std::cos((double)psi) + (double)cam[2]);   // ::cos(double), see oracle/ref_shim/ref_camera.cc
+  *v = (float)((double)(cam[1] * r) * std::sin((double)psi) + (double)cam[3]);
+}
+
+void jacobi_svd4(const float* A, float* w, float* vt) {
+  const int n = 4;
+  float At[4][4], Vt[4][4];
+  double W[4];
+  for (int i = 0; i < n; i++) {
+    double sd = 0;
+    for (int k = 0; k < n; k++) {
+      const float t = A[k * 4 + i];   // At = A^T: row i of At is column i of A
+      At[i][k] = t; Vt[i][k] = i == k ? 1.f : 0.f;
+      sd += (double)t * t;
+    }
+    W[i] = sd;
+  }
+  const float eps = 2 * 1.1920929e-07f;   // FLT_EPSILON * 2
+  for (int iter = 0; iter < 30; iter++) {   // max_iter = max(m, 30)
+    bool changed = false;
+    for (int i = 0; i < n - 1; i++)
+      for (int j = i + 1; j < n; j++) {
+        float *Ai = At[i], *Aj = At[j];
+        double a = W[i], p = 0, b = W[j];
+        for (int k = 0; k < n; k++) p += (double)Ai[k] * Aj[k];
+        if (std::fabs(p) <= eps * std::sqrt(a * b)) continue;
+        p *= 2;
+        const double beta = a - b, gamma = hypot(p, beta);
+        float c, s;
+        if (beta < 0) {
+          const double delta = (gamma - beta) * 0.5;
+          s = (float)std::sqrt(delta / gamma);
+          c = (float)(p / (gamma * s * 2));
+        } else {
+          c = (float)std::sqrt((gamma + beta) / (gamma * 2));
+          s = (float)(p / (gamma * c * 2));
+        }
+        a = b = 0;
+        for (int k = 0; k < n; k++) {
+          const float t0 = c * Ai[k] + s * Aj[k];
+          const float t1 = -s * Ai[k] + c * Aj[k];
+          Ai[k] = t0; Aj[k] = t1;
+          a += (double)t0 * t0; b += (double)t1 * t1;
+        }
+        W[i] = a; W[j] = b;
+        changed = true;
+        float *Vi = Vt[i], *Vj = Vt[j];
+        for (int k = 0; k < n; k++) {
+          const float t0 = c * Vi[k] + s * Vj[k];
+          const float t1 = -s * Vi[k] + c * Vj[k];
+          Vi[k] = t0; Vj[k] = t1;
+        }
+      }
+    if (!changed) break;
+  }
+  for (int i = 0; i < n; i++) {
+    double sd = 0;
+    for (int k = 0; k < n; k++) sd += (double)At[i][k] * At[i][k];
+    W[i] = std::sqrt(sd);
+  }
+  for (int i = 0; i < n - 1; i++) {   // selection sort, descending; rows of Vt follow
+    int j = i;
+    for (int k = i + 1; k < n; k++)
+      if (W[j] < W[k]) j = k;
+    if (i != j) {
+      std::swap(W[i], W[j]);
+      for (int k = 0; k < n; k++) std::swap(Vt[i][k], Vt[j][k]);
+    }
+  }
+  for (int i = 0; i < n; i++) {
+    w[i] = (float)W[i];
+    for (int k = 0; k < n; k++) vt[i * 4 + k] = Vt[i][k];
+  }
+}
+
+float kb8_triangulate_matches(const Kb8Pair& G, float x1, float y1, float x2, float y2, float sigmaLevel, float unc, int libmMode,
+                              float* p3D) {
+  float r1[3], r2[3], r21[3];
+  kb8_unproject(G.cam1, x1, y1, libmMode, r1);
+  kb8_unproject(G.cam2, x2, y2, libmMode, r2);
+  const float* R = G.R12;
+  for (int i = 0; i < 3; i++) r21[i] = R[3 * i] * r2[0] + R[3 * i + 1] * r2[1] + R[3 * i + 2] * r2[2];   // R12 * r2
+  double dot = 0, n1 = 0, n2 = 0;
+  for (int i = 0; i < 3; i++) { dot += (double)r1[i] * (double)r21[i]; n1 += (double)r1[i] * r1[i]; n2 += (double)r21[i] * r21[i]; }
+  const float cosParallaxRays = (float)(dot / (std::sqrt(n1) * std::sqrt(n2)));
+  if (cosParallaxRays > 0.9998) return -1;
+  // Tcw1 = [I | 0], Tcw2 = [R21 | t21] with R21 = R12^T, t21 = -R21 * t12 (gemm with alpha = -1)
+  float T1[3][4] = {{1, 0, 0, 0}, {0, 1, 0, 0}, {0, 0, 1, 0}}, T2[3][4];
+  for (int i = 0; i < 3; i++) {
+    for (int k = 0; k < 3; k++) T2[i][k] = R[3 * k + i];
+    const float t = R[i] * G.t12[0] + R[3 + i] * G.t12[1] + R[6 + i] * G.t12[2];
+    T2[i][3] = (float)((double)t * -1.0);
+  }
+  // A.row(i) = p.x * Tcw.row(2) - Tcw.row(0|1): addWeighted(row2, p, row01, -1), one rounding per element
+  float A[16];
+  const float ps[4] = {r1[0], r1[1], r2[0], r2[1]};
+  for (int i = 0; i < 4; i++) {
+    const float(*T)[4] = i < 2 ? T1 : T2;
+    for (int k = 0; k < 4; k++) A[4 * i + k] = (float)((double)T[2][k] * (double)ps[i] + (double)T[i & 1][k] * -1.0);
+  }
+  float w[4], vt[16];
+  jacobi_svd4(A, w, vt);
+  const float inv = (float)(1.0 / (double)vt[15]);   // x3D.rowRange(0,3) / x3D.at<float>(3)
+  const float x3D[3] = {vt[12] * inv, vt[13] * inv, vt[14] * inv};
+  const float z1 = x3D[2];
+  if (z1 <= 0) return -1;
+  const float z2 = (float)(((double)T2[2][0] * x3D[0] + (double)T2[2][1] * x3D[1] + (double)T2[2][2] * x3D[2]) + (double)T2[2][3]);
+  if (z2 <= 0) return -1;
+  float u, v;
+  kb8_project(G.cam1, x3D, libmMode, &u, &v);
+  const float errX1 = u - x1, errY1 = v - y1;
+  if ((errX1 * errX1 + errY1 * errY1) > 5.991 * sigmaLevel) return -1;
+  float x3D2[3];
+  for (int i = 0; i < 3; i++) {   // R21 * x3D + t21: small gemm with C
+    const float t = T2[i][0] * x3D[0] + T2[i][1] * x3D[1] + T2[i][2] * x3D[2];
+    x3D2[i] = (float)((double)t + (double)T2[i][3]);
+  }
+  kb8_project(G.cam2, x3D2, libmMode, &u, &v);
+  const float errX2 = u - x2, errY2 = v - y2;
+  if ((errX2 * errX2 + errY2 * errY2) > 5.991 * unc) return -1;
+  if (p3D) { p3D[0] = x3D[0]; p3D[1] = x3D[1]; p3D[2] = x3D[2]; }
+  return z1;
+}
+
+// ORBmatcher.cc:981-1222 with KannalaBrandt8 cameras (one per keyframe, or the two of a fisheye-stereo rig).
+int search_for_triangulation_kb8(int n1, const KeyPoint* kps1, const uint8_t* desc1, const FeatVec& fv1, const uint8_t* elig1,
+                                 const uint8_t* stereo1, int nLeft1, int n2, const KeyPoint* kps2, const uint8_t* desc2,
+                                 const FeatVec& fv2, const uint8_t* elig2, const uint8_t* stereo2, int nLeft2, const Kb8Pair* G,
+                                 float epx, float epy, const float* scaleFactors2, const float* levelSigma2_1,
+                                 const float* levelSigma2_2, bool coarse, bool check_orientation, int libmMode, int* matches12) {
+  for (int i = 0; i < n1; i++) matches12[i] = -1;
+  std::vector<int> rotHist[HISTO_LENGTH];
+  int nmatches = 0;
+  const bool twoCameras = nLeft1 != -1;   // pKF1->mpCamera2 (and pKF2->mpCamera2) set
+  for_common_nodes(fv1, fv2, [&](int a, int b) {
+    for (int p1 = fv1.nodeStart[a]; p1 < fv1.nodeStart[a + 1]; p1++) {
+      const int idx1 = (int)fv1.indices[p1];
+      if (!elig1[idx1]) continue;
+      const bool bStereo1 = !twoCameras && stereo1 && stereo1[idx1];
+      const KeyPoint& kp1 = kps1[idx1];
+      const bool bRight1 = twoCameras && idx1 >= nLeft1;
+      const uint8_t* d1 = desc1 + 32 * (size_t)idx1;
+      int bestDist = TH_LOW, bestIdx2 = -1;
+      for (int p2 = fv2.nodeStart[b]; p2 < fv2.nodeStart[b + 1]; p2++) {
+        const int idx2 = (int)fv2.indices[p2];
+        if (!elig2[idx2]) continue;
+        const bool bStereo2 = nLeft2 == -1 && stereo2 && stereo2[idx2];
+        const int dist = hamming256(d1, desc2 + 32 * (size_t)idx2);
+        if (dist > TH_LOW || dist > bestDist) continue;
+        const KeyPoint& kp2 = kps2[idx2];
+        const bool bRight2 = nLeft2 != -1 && idx2 >= nLeft2;
+        if (!bStereo1 && !bStereo2 && !twoCameras) {
+          const float distex = epx - kp2.x, distey = epy - kp2.y;
+          if (distex * distex + distey * distey < 100 * scaleFactors2[kp2.octave]) continue;
+        }
+        const Kb8Pair& g = twoCameras ? G[2 * (int)bRight1 + (int)bRight2] : G[0];
+        const bool ok = kb8_triangulate_matches(g, kp1.x, kp1.y, kp2.x, kp2.y, levelSigma2_1[kp1.octave], levelSigma2_2[kp2.octave],
+                                                libmMode, nullptr) > 0.0001f;
+        if (ok || coarse) { bestIdx2 = idx2; bestDist = dist; }
+      }
+      if (bestIdx2 >= 0) {
+        matches12[idx1] = bestIdx2;
+        nmatches++;
+        if (check_orientation) rotHist[rot_bin_of(kp1.angle, kps2[bestIdx2].angle)].push_back(idx1);
+      }
+    }
+  });
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1, hs[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; i++) hs[i] = (int)rotHist[i].size();
+    compute_three_maxima(hs, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++)
+      if (i != ind1 && i != ind2 && i != ind3)
+        for (int j : rotHist[i]) { matches12[j] = -1; nmatches--; }
+  }
+  return nmatches;
+}
+
 // ORBmatcher.cc:1524-1590 (Fuse), :1728-1756 (Fuse/Scw), :1866-1895 and :1946-1975 (SearchBySim3).
 void search_window_best(const FrameView& F, int n, const uint8_t* valid, const float* u, const float* v, const float* radius,
                         const int* level, const float* ur, const uint8_t* desc, int gate, const float* invLevelSigma2,

@@ -118,6 +118,34 @@ int search_for_triangulation(int n1, const KeyPoint* kps1, const uint8_t* desc1,
                              const float* scaleFactors2, const float* levelSigma2_2, bool coarse, bool check_orientation,
                              int* matches12);
 
+// ---- KannalaBrandt8 cameras: the gate of SearchForTriangulation is a two-view triangulation (KannalaBrandt8.cpp:244-247) ----------
+// Relative geometry of one (camera of KF1, camera of KF2) combination: R12 / t12 as ORBmatcher.cc:1000-1019 forms them,
+// cam = fx fy cx cy k1 k2 k3 k4.
+struct Kb8Pair { float R12[9]; float t12[3]; float cam1[8]; float cam2[8]; };
+// libm policy (same switch as frame_oracle.cc): 0 = tanf / atan2f of the host libm (what the reference's binary calls);
+// 1 = (float)tan((double)x), (float)atan2((double)..) -- portable, the arithmetic of the CUDA path.
+enum { LIBM_F32 = 0, LIBM_PORTABLE = 1 };
+// KannalaBrandt8::unproject (KannalaBrandt8.cpp:112-137): Newton iterations on the distortion polynomial, ray = (x, y, 1).
+void kb8_unproject(const float* cam, float u, float v, int libmMode, float* ray);
+// KannalaBrandt8::project (KannalaBrandt8.cpp:29-45).
+void kb8_project(const float* cam, const float* X, int libmMode, float* u, float* v);
+// cv::SVD::compute(A, w, u, vt, MODIFY_A | FULL_UV) of a 4x4 CV_32F matrix (row-major), w and vt only: OpenCV's one-sided Jacobi
+// (modules/core/src/lapack.cpp, JacobiSVDImpl_<float>), which is what cv::SVD runs for a matrix this small in every build.
+void jacobi_svd4(const float* A, float* w, float* vt);
+// KannalaBrandt8::TriangulateMatches (KannalaBrandt8.cpp:343-418) + Triangulate (:430-444): z1 of the triangulated point in camera 1, or
+// -1.  p3D (3 floats, may be null) receives the point when it is accepted.  epipolarConstrain is `> 0.0001f` on the result.
+float kb8_triangulate_matches(const Kb8Pair& G, float x1, float y1, float x2, float y2, float sigmaLevel, float unc, int libmMode,
+                              float* p3D);
+// SearchForTriangulation for KannalaBrandt8 keyframes (ORBmatcher.cc:981-1222).  One camera per keyframe: nLeft1 = nLeft2 = -1, G[0]
+// is the pair, the epipole gate (:1093-1101) applies.  Fisheye-stereo keyframes (mpCamera2 set, NLeft != -1): kps = mvKeys followed
+// by mvKeysRight, G[2 * bRight1 + bRight2] = (ll, lr, rl, rr), no feature counts as stereo and the epipole gate is off (:1093).
+// levelSigma2_1 / _2 = mvLevelSigma2 of pKF1 / pKF2 (sigmaLevel and unc of the gate).
+int search_for_triangulation_kb8(int n1, const KeyPoint* kps1, const uint8_t* desc1, const FeatVec& fv1, const uint8_t* elig1,
+                                 const uint8_t* stereo1, int nLeft1, int n2, const KeyPoint* kps2, const uint8_t* desc2,
+                                 const FeatVec& fv2, const uint8_t* elig2, const uint8_t* stereo2, int nLeft2, const Kb8Pair* G,
+                                 float epx, float epy, const float* scaleFactors2, const float* levelSigma2_1,
+                                 const float* levelSigma2_2, bool coarse, bool check_orientation, int libmMode, int* matches12);
+
 // The per-point search loop shared by Fuse (both overloads), SearchBySim3 and (without blocking) SearchByProjection(KF,Scw):
 // KeyFrame::GetFeaturesInArea(u, v, radius) -> octave in [level-1, level] -> optional Fuse chi-square gate
 // (gate != 0: uses F.uRight / ur / invLevelSigma2; 7.8 with a right coordinate, 5.99 without) -> strict argmin Hamming.

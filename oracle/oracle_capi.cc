@@ -198,6 +198,37 @@ int oro_search_for_triangulation(int n1, const KeyPoint* kps1, const uint8_t* de
                                   fv_of(nn2, ids2, start2, ind2), elig2, stereo2, F12, epx, epy, scaleFactors2, levelSigma2_2,
                                   coarse != 0, check_orientation != 0, matches12);
 }
+// KannalaBrandt8 gate of SearchForTriangulation.  pairs: npairs x 28 floats (R12[9] t12[3] cam1[8] cam2[8]), npairs = 1 (one camera per
+// keyframe, nLeft = -1) or 4 (ll, lr, rl, rr of a fisheye-stereo rig).
+int oro_search_for_triangulation_kb8(int n1, const KeyPoint* kps1, const uint8_t* desc1, int nn1, const uint32_t* ids1, const int* start1,
+                                     const uint32_t* ind1, const uint8_t* elig1, const uint8_t* stereo1, int nLeft1, int n2,
+                                     const KeyPoint* kps2, const uint8_t* desc2, int nn2, const uint32_t* ids2, const int* start2,
+                                     const uint32_t* ind2, const uint8_t* elig2, const uint8_t* stereo2, int nLeft2, const float* pairs,
+                                     float epx, float epy, const float* scaleFactors2, const float* levelSigma2_1,
+                                     const float* levelSigma2_2, int coarse, int check_orientation, int libmMode, int* matches12) {
+  static_assert(sizeof(Kb8Pair) == 28 * sizeof(float), "Kb8Pair layout");
+  return search_for_triangulation_kb8(n1, kps1, desc1, fv_of(nn1, ids1, start1, ind1), elig1, stereo1, nLeft1, n2, kps2, desc2,
+                                      fv_of(nn2, ids2, start2, ind2), elig2, stereo2, nLeft2, (const Kb8Pair*)pairs, epx, epy,
+                                      scaleFactors2, levelSigma2_1, levelSigma2_2, coarse != 0, check_orientation != 0, libmMode, matches12);
+}
+// n independent pairs through KannalaBrandt8::TriangulateMatches: xy1 / xy2 n x 2, sigma1 / sigma2 n; z1 (or -1) and the point per pair.
+void oro_kb8_triangulate_matches(const float* pair, int n, const float* xy1, const float* xy2, const float* sigma1, const float* sigma2,
+                                 int libmMode, float* z1, float* p3D) {
+  for (int i = 0; i < n; i++) {
+    p3D[3 * i] = p3D[3 * i + 1] = p3D[3 * i + 2] = 0.f;
+    z1[i] = kb8_triangulate_matches(*(const Kb8Pair*)pair, xy1[2 * i], xy1[2 * i + 1], xy2[2 * i], xy2[2 * i + 1], sigma1[i], sigma2[i], libmMode,
+                                    p3D + 3 * i);
+  }
+}
+void oro_kb8_unproject(const float* cam, int n, const float* xy, int libmMode, float* rays) {
+  for (int i = 0; i < n; i++) kb8_unproject(cam, xy[2 * i], xy[2 * i + 1], libmMode, rays + 3 * i);
+}
+void oro_kb8_project(const float* cam, int n, const float* X, int libmMode, float* uv) {
+  for (int i = 0; i < n; i++) kb8_project(cam, X + 3 * i, libmMode, uv + 2 * i, uv + 2 * i + 1);
+}
+void oro_jacobi_svd4(const float* A, int n, float* w, float* vt) {
+  for (int i = 0; i < n; i++) jacobi_svd4(A + 16 * i, w + 4 * i, vt + 16 * i);
+}
 void oro_search_window_best(int N, const KeyPoint* kps, const uint8_t* desc, const float* uRight, const float* bounds4, int n,
                             const uint8_t* valid, const float* u, const float* v, const float* radius, const int* level,
                             const float* ur, const uint8_t* qdesc, int gate, const float* invLevelSigma2, int* bestIdx, int* bestDist) {

@@ -4,7 +4,9 @@
 // against python cv2 4.13 (resize on every level, FAST on full frames and ROI cells incl. order and response,
 // GaussianBlur with the OCV4 taps, fastAtan2).
 #include <algorithm>
+#include <cfloat>
 #include <cmath>
+#include <cstring>
 #include <vector>
 
 #include "../orb_oracle.h"
@@ -177,9 +179,12 @@ void cvshim_add_weighted(const Mat& a, double alpha, const Mat& b, double beta, 
         if (!hasB) o = (alpha == 1) ? av : (alpha == -1 ? -av : av * fa);
         else {
           const float bv = b.at<float>(y, x);
-          if (alpha == 1) o = beta == 1 ? av + bv : (beta == -1 ? av - bv : bv * fb + av);
-          else if (beta == 1) o = alpha == -1 ? bv - av : av * fa + bv;
-          else o = av * fa + bv * fb;
+          // cv::scaleAdd / cv::addWeighted on CV_32F as cv2 4.13 evaluates them on an FMA-capable host: the scaled sum is rounded
+          // to float ONCE (tests/test_oracle_cvmat.py: equal to the double expression on every sample, to the two-rounding float
+          // expression on a third of them)
+          if (alpha == 1) o = beta == 1 ? av + bv : (beta == -1 ? av - bv : (float)((double)bv * (double)fb + (double)av));
+          else if (beta == 1) o = alpha == -1 ? bv - av : (float)((double)av * (double)fa + (double)bv);
+          else o = (float)((double)av * alpha + (double)bv * beta);
         }
         r.at<float>(y, x) = o;
       } else {
@@ -291,6 +296,101 @@ double norm(InputArray a_, InputArray b_, int normType) {
       s += normType == NORM_L1 ? std::fabs(v) : v * v;
     }
   return normType == NORM_L1 ? s : std::sqrt(s);
+}
+
+
+void hconcat(InputArray a_, InputArray b_, OutputArray dst) {
+  Mat a = a_.getMat(), b = b_.getMat();
+  assert(a.rows == b.rows && a.type() == b.type());
+  Mat r(a.rows, a.cols + b.cols, a.type());
+  for (int y = 0; y < a.rows; y++) {
+    memcpy(r.ptr(y), a.ptr(y), (size_t)a.cols * a.elemSize());
+    memcpy(r.ptr(y) + (size_t)a.cols * a.elemSize(), b.ptr(y), (size_t)b.cols * b.elemSize());
+  }
+  dst.create(r.rows, r.cols, r.type());
+  Mat d = dst.getMat();
+  r.copyTo(d);
+}
+
+// JacobiSVDImpl_<float> (modules/core/src/lapack.cpp) for a square n x n CV_32F matrix, n <= 8: At = src^T (rows = columns of src),
+// Hestenes rotations until no pair is rotated (at most max(n, 30) sweeps), W accumulated in double, c / s rounded to float, rotated
+// elements float(c*x) + float(s*y); singular values sorted descending with the rows of Vt following.  u is not produced (the
+// reference reads vt only, KannalaBrandt8.cpp:441-442).  Pinned to cv2.SVDecomp in tests/test_oracle_cvmat.py.
+void SVD::compute(InputArray src_, OutputArray w_, OutputArray u_, OutputArray vt_, int) {
+  Mat src = src_.getMat();
+  assert(src.type() == CV_32F && src.rows == src.cols && src.rows <= 8);
+  const int n = src.rows, m = n;
+  float At[8][8], Vt[8][8];
+  double W[8];
+  for (int i = 0; i < n; i++)
+    for (int k = 0; k < m; k++) { At[i][k] = src.at<float>(k, i); Vt[i][k] = i == k ? 1.f : 0.f; }
+  for (int i = 0; i < n; i++) {
+    double sd = 0;
+    for (int k = 0; k < m; k++) { const float t = At[i][k]; sd += (double)t * t; }
+    W[i] = sd;
+  }
+  const float eps = FLT_EPSILON * 2;
+  const int max_iter = std::max(m, 30);
+  for (int iter = 0; iter < max_iter; iter++) {
+    bool changed = false;
+    for (int i = 0; i < n - 1; i++)
+      for (int j = i + 1; j < n; j++) {
+        float *Ai = At[i], *Aj = At[j];
+        double a = W[i], p = 0, b = W[j];
+        for (int k = 0; k < m; k++) p += (double)Ai[k] * Aj[k];
+        if (std::abs(p) <= eps * std::sqrt((double)a * b)) continue;
+        p *= 2;
+        const double beta = a - b, gamma = hypot((double)p, beta);
+        float c, s;
+        if (beta < 0) {
+          const double delta = (gamma - beta) * 0.5;
+          s = (float)std::sqrt(delta / gamma);
+          c = (float)(p / (gamma * s * 2));
+        } else {
+          c = (float)std::sqrt((gamma + beta) / (gamma * 2));
+          s = (float)(p / (gamma * c * 2));
+        }
+        a = b = 0;
+        for (int k = 0; k < m; k++) {
+          const float t0 = c * Ai[k] + s * Aj[k];
+          const float t1 = -s * Ai[k] + c * Aj[k];
+          Ai[k] = t0; Aj[k] = t1;
+          a += (double)t0 * t0; b += (double)t1 * t1;
+        }
+        W[i] = a; W[j] = b;
+        changed = true;
+        float *Vi = Vt[i], *Vj = Vt[j];
+        for (int k = 0; k < n; k++) {
+          const float t0 = c * Vi[k] + s * Vj[k];
+          const float t1 = -s * Vi[k] + c * Vj[k];
+          Vi[k] = t0; Vj[k] = t1;
+        }
+      }
+    if (!changed) break;
+  }
+  for (int i = 0; i < n; i++) {
+    double sd = 0;
+    for (int k = 0; k < m; k++) { const float t = At[i][k]; sd += (double)t * t; }
+    W[i] = std::sqrt(sd);
+  }
+  for (int i = 0; i < n - 1; i++) {
+    int j = i;
+    for (int k = i + 1; k < n; k++)
+      if (W[j] < W[k]) j = k;
+    if (i != j) {
+      std::swap(W[i], W[j]);
+      for (int k = 0; k < m; k++) std::swap(At[i][k], At[j][k]);
+      for (int k = 0; k < n; k++) std::swap(Vt[i][k], Vt[j][k]);
+    }
+  }
+  w_.create(n, 1, CV_32F);
+  vt_.create(n, n, CV_32F);
+  Mat w = w_.getMat(), vt = vt_.getMat();
+  for (int i = 0; i < n; i++) {
+    w.at<float>(i, 0) = (float)W[i];
+    for (int k = 0; k < n; k++) vt.at<float>(i, k) = Vt[i][k];
+  }
+  (void)u_;
 }
 
 }  // namespace cv

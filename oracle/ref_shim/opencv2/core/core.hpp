@@ -290,7 +290,16 @@ class MatExpr {
   int flags;            // GEMM_1_T = 1, GEMM_2_T = 2, GEMM_3_T = 4
 };
 inline Mat::Mat(const MatExpr& e) : Mat() { *this = e.eval(); }
-inline Mat& Mat::operator=(const MatExpr& e) { Mat m = e.eval(); return *this = m; }
+// Mat = MatExpr: OpenCV lets the expression write into the destination (MatOp::assign -> dst.create(), a no-op when shape and type
+// already match), which is what makes `A.row(0) = s*B.row(2) - B.row(0)` (KannalaBrandt8.cpp:434-437) fill the row of A.
+inline Mat& Mat::operator=(const MatExpr& e) {
+  Mat m = e.eval();
+  if (data && m.data != data && rows == m.rows && cols == m.cols && type_ == m.type()) {
+    for (int y = 0; y < rows; y++) memmove(ptr(y), m.ptr(y), (size_t)cols * elemSize());
+    return *this;
+  }
+  return *this = m;
+}
 
 enum { GEMM_1_T = 1, GEMM_2_T = 2, GEMM_3_T = 4, DECOMP_LU = 0 };
 enum { NORM_INF = 1, NORM_L1 = 2, NORM_L2 = 4, NORM_HAMMING = 6 };
@@ -302,6 +311,13 @@ void cvshim_add_scalar(const Mat& a, double alpha, double s, Mat& d);           
 void cvshim_transpose(const Mat& a, Mat& d);
 void cvshim_invert(const Mat& a, Mat& d);                                                                    // cv::invert, DECOMP_LU
 double norm(InputArray a, int normType = NORM_L2);
+void hconcat(InputArray a, InputArray b, OutputArray dst);   // cv::hconcat of two matrices with equal rows and type
+// cv::SVD::compute on a square CV_32F matrix: OpenCV's own one-sided Jacobi (modules/core/src/lapack.cpp JacobiSVDImpl_<float>);
+// matrices this small never reach LAPACK even in a LAPACK build (hal_internal.cpp: HAL_SVD_SMALL_MATRIX_THRESH).  w and vt only.
+struct SVD {
+  enum { MODIFY_A = 1, NO_UV = 2, FULL_UV = 4 };
+  static void compute(InputArray src, OutputArray w, OutputArray u, OutputArray vt, int flags = 0);
+};
 double norm(InputArray a, InputArray b, int normType = NORM_L2);
 
 inline MatExpr cvshim_scaled(const Mat& m, double alpha) { MatExpr e; e.op = MatExpr::ADDEX; e.a = m; e.alpha = alpha; e.beta = 0; return e; }

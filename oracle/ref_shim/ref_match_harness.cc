@@ -397,8 +397,57 @@ int rm_search_by_bow_keyframes(const RefView* KF1, const RefView* KF2, const Ref
   return nm;
 }
 
-// ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo, bCoarse), src/ORBmatcher.cc:981-1222 (pinhole
-// cameras; the epipolar test uses the F12 given here, see slam_world.h).  pairs: up to cap (i1, i2) pairs; returns nmatches.
+// ---- the stand-in cv:: arithmetic, exposed so that tests/test_oracle_cvmat.py can hold it against python cv2 -------------------
+void rm_cv_svd(const float* A, int n, float* w, float* vt) {   // cv::SVD::compute(A, w, u, vt, MODIFY_A | FULL_UV) of an n x n matrix
+  cv::Mat a = mat_from(A, n, n), W, U, Vt;
+  cv::SVD::compute(a, W, U, Vt, cv::SVD::MODIFY_A | cv::SVD::FULL_UV);
+  for (int i = 0; i < n; i++) { w[i] = W.at<float>(i); for (int k = 0; k < n; k++) vt[i * n + k] = Vt.at<float>(i, k); }
+}
+void rm_cv_scaled_sub_row(const float* a, float s, const float* b, int cols, float* out) {   // M.row(0) = s*A - B written into a row view
+  cv::Mat A = mat_from(a, 1, cols), B = mat_from(b, 1, cols), M = cv::Mat::zeros(2, cols, CV_32F);
+  M.row(0) = s * A - B;
+  for (int k = 0; k < cols; k++) out[k] = M.at<float>(0, k);
+}
+void rm_cv_div_scalar(const float* a, int n, float s, float* out) {   // Mat / s
+  cv::Mat A = mat_from(a, n, 1);
+  cv::Mat r = A / s;
+  for (int k = 0; k < n; k++) out[k] = r.at<float>(k);
+}
+void rm_cv_gemm(const float* a, int ar, int ac, const float* b, int br, int bc, double alpha, const float* c, double beta, int flags, float* out) {
+  cv::Mat A = mat_from(a, ar, ac), B = mat_from(b, br, bc), Cm, D;
+  const int M = (flags & cv::GEMM_1_T) ? ac : ar, N = (flags & cv::GEMM_2_T) ? br : bc;
+  if (c) Cm = mat_from(c, (flags & cv::GEMM_3_T) ? N : M, (flags & cv::GEMM_3_T) ? M : N);
+  cv::cvshim_gemm(A, B, alpha, Cm, beta, D, flags);
+  for (int i = 0; i < M; i++) for (int k = 0; k < N; k++) out[i * N + k] = D.at<float>(i, k);
+}
+double rm_cv_dot(const float* a, const float* b, int n) { return mat_from(a, n, 1).dot(mat_from(b, n, 1)); }
+double rm_cv_norm(const float* a, int n) { return cv::norm(mat_from(a, n, 1)); }
+
+// KannalaBrandt8::unproject (KannalaBrandt8.cpp:112-137) and ::TriangulateMatches (:343-418), the reference's bodies: cam = fx fy cx cy
+// k1..k4, n independent keypoint pairs; z1 (or -1) and the accepted point per pair.
+void rm_kb8_unproject(const float* cam, int n, const float* xy, float* rays) {
+  KannalaBrandt8 K(std::vector<float>(cam, cam + 8));
+  for (int i = 0; i < n; i++) {
+    const cv::Point3f r = K.unproject(cv::Point2f(xy[2 * i], xy[2 * i + 1]));
+    rays[3 * i] = r.x; rays[3 * i + 1] = r.y; rays[3 * i + 2] = r.z;
+  }
+}
+void rm_kb8_triangulate_matches(const float* cam1, const float* cam2, const float* R12, const float* t12, int n, const float* xy1,
+                                const float* xy2, const float* sigma1, const float* sigma2, float* z1, float* p3D) {
+  KannalaBrandt8 K1(std::vector<float>(cam1, cam1 + 8)), K2(std::vector<float>(cam2, cam2 + 8));
+  const cv::Mat R = mat_from(R12, 3, 3), t = mat_from(t12, 3, 1);
+  for (int i = 0; i < n; i++) {
+    cv::KeyPoint kp1, kp2;
+    kp1.pt = cv::Point2f(xy1[2 * i], xy1[2 * i + 1]); kp2.pt = cv::Point2f(xy2[2 * i], xy2[2 * i + 1]);
+    cv::Mat X;
+    z1[i] = K1.TriangulateMatches(&K2, kp1, kp2, R, t, sigma1[i], sigma2[i], X);
+    for (int k = 0; k < 3; k++) p3D[3 * i + k] = X.empty() ? 0.f : X.at<float>(k);
+  }
+}
+
+// ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo, bCoarse), src/ORBmatcher.cc:981-1222.  Pinhole
+// cameras: the epipolar test uses the F12 given here (see slam_world.h); KannalaBrandt8 cameras (one per keyframe or a fisheye-stereo
+// rig) run the reference's own triangulation gate and ignore F12.  pairs: up to cap (i1, i2) pairs; returns nmatches.
 int rm_search_for_triangulation(const RefView* KF1, const RefView* KF2, const RefPoints* P, const float* F12, int bOnlyStereo, int bCoarse, float nnratio,
                                 int checkOri, int* pairs, int cap) {
   World W; Owned O;

@@ -11,7 +11,7 @@
 // bodies out of the reference's .cc files at build time (oracle/_ref/*_slice.inc) and ref_match_harness.cc includes them.
 // What IS written here: plain accessors (GetRotation ...), MapPoint / KeyFrame bookkeeping reduced to an event log, and the
 // two camera entry points that would need cv::solve / cv::SVD (Pinhole::epipolarConstrain takes the caller's F12 instead of
-// rebuilding it from R12 / t12; KannalaBrandt8::epipolarConstrain / matchAndtriangulate are not available).
+// rebuilding it from R12 / t12; matchAndtriangulate, which nothing calls, is not available).
 #pragma once
 #define FRAME_H
 #define KEYFRAME_H
@@ -58,6 +58,10 @@ class GeometricCamera {
   virtual ~GeometricCamera() {}
   virtual cv::Point2f project(const cv::Point3f& p3D) = 0;
   virtual cv::Point2f project(const cv::Mat& m3D) = 0;
+  virtual cv::Mat unprojectMat(const cv::Point2f&) {
+    fprintf(stderr, "oracle/_ref: unprojectMat is only needed for KannalaBrandt8 cameras\n");
+    abort();
+  }
   virtual bool epipolarConstrain(GeometricCamera* otherCamera, const cv::KeyPoint& kp1, const cv::KeyPoint& kp2, const cv::Mat& R12,
                                  const cv::Mat& t12, const float sigmaLevel, const float unc) = 0;
   virtual bool matchAndtriangulate(const cv::KeyPoint&, const cv::KeyPoint&, GeometricCamera*, cv::Mat&, cv::Mat&, const float, const float, cv::Mat&) {
@@ -100,10 +104,18 @@ class KannalaBrandt8 : public GeometricCamera {
   explicit KannalaBrandt8(const std::vector<float>& p) : GeometricCamera(p) { mnType = CAM_FISHEYE; }
   cv::Point2f project(const cv::Point3f& p3D);   // body: src/CameraModels/KannalaBrandt8.cpp:29-45 (slice)
   cv::Point2f project(const cv::Mat& m3D);       // body: src/CameraModels/KannalaBrandt8.cpp:47-51 (slice)
-  bool epipolarConstrain(GeometricCamera*, const cv::KeyPoint&, const cv::KeyPoint&, const cv::Mat&, const cv::Mat&, const float, const float) {
-    fprintf(stderr, "oracle/_ref: KannalaBrandt8::epipolarConstrain needs cv::SVD (KannalaBrandt8.cpp:343-429), not available in the stand-in\n");
-    abort();
-  }
+  // bodies: src/CameraModels/KannalaBrandt8.cpp:103-137 (unprojectMat / unproject), :244-247 (epipolarConstrain), :343-418
+  // (TriangulateMatches), :430-444 (Triangulate), cut by oracle/Makefile into camera_slice.inc; cv::SVD::compute behind Triangulate is
+  // OpenCV's one-sided Jacobi restated in cv_prims.cc and pinned to cv2.SVDecomp (tests/test_oracle_cvmat.py)
+  cv::Mat unprojectMat(const cv::Point2f& p2D);
+  cv::Point3f unproject(const cv::Point2f& p2D);
+  bool epipolarConstrain(GeometricCamera* pCamera2, const cv::KeyPoint& kp1, const cv::KeyPoint& kp2, const cv::Mat& R12, const cv::Mat& t12,
+                         const float sigmaLevel, const float unc);
+  float TriangulateMatches(GeometricCamera* pCamera2, const cv::KeyPoint& kp1, const cv::KeyPoint& kp2, const cv::Mat& R12, const cv::Mat& t12,
+                           const float sigmaLevel, const float unc, cv::Mat& p3D);
+ private:
+  const float precision = 1e-6;   // include/CameraModels/KannalaBrandt8.h:47-52
+  void Triangulate(const cv::Point2f& p1, const cv::Point2f& p2, const cv::Mat& Tcw1, const cv::Mat& Tcw2, cv::Mat& x3D);
 };
 
 // One entry per MapPoint / KeyFrame mutation ORBmatcher.cc performs (Fuse): kind 0 = pMP->Replace(pOther), 1 = AddObservation +

@@ -255,6 +255,69 @@ def search_for_triangulation(kf1, kf2, pts, F12, only_stereo=False, coarse=False
     return nm, pairs[:nm].copy()
 
 
+def kb8_unproject(cam, xy):
+    """KannalaBrandt8::unproject, the reference's body (libm tanf)"""
+    cam = np.ascontiguousarray(cam, np.float32).reshape(8); xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    rays = np.empty((xy.shape[0], 3), np.float32)
+    lib().rm_kb8_unproject(C.c_void_p(_p(cam)), xy.shape[0], C.c_void_p(_p(xy)), C.c_void_p(_p(rays)))
+    return rays
+
+
+def kb8_triangulate_matches(cam1, cam2, R12, t12, xy1, xy2, sigma1, sigma2):
+    """KannalaBrandt8::TriangulateMatches, the reference's body over the stand-in cv:: (z1 or -1, accepted point) per keypoint pair"""
+    f = lambda a, shape: np.ascontiguousarray(a, np.float32).reshape(shape)
+    cam1, cam2, R12, t12, xy1, xy2 = f(cam1, 8), f(cam2, 8), f(R12, 9), f(t12, 3), f(xy1, (-1, 2)), f(xy2, (-1, 2))
+    n = xy1.shape[0]
+    sigma1 = np.ascontiguousarray(np.broadcast_to(np.asarray(sigma1, np.float32), (n,)))
+    sigma2 = np.ascontiguousarray(np.broadcast_to(np.asarray(sigma2, np.float32), (n,)))
+    z1 = np.empty(n, np.float32); p3d = np.empty((n, 3), np.float32)
+    lib().rm_kb8_triangulate_matches(*[C.c_void_p(_p(a)) for a in (cam1, cam2, R12, t12)], n, *[C.c_void_p(_p(a)) for a in (xy1, xy2, sigma1, sigma2, z1, p3d)])
+    return z1, p3d
+
+
+def cv_svd(A):
+    A = np.ascontiguousarray(A, np.float32); n = A.shape[0]
+    w = np.empty(n, np.float32); vt = np.empty((n, n), np.float32)
+    lib().rm_cv_svd(C.c_void_p(_p(A)), n, C.c_void_p(_p(w)), C.c_void_p(_p(vt)))
+    return w, vt
+
+
+def cv_scaled_sub_row(a, s, b):
+    a = np.ascontiguousarray(a, np.float32).ravel(); b = np.ascontiguousarray(b, np.float32).ravel()
+    out = np.empty(a.size, np.float32)
+    lib().rm_cv_scaled_sub_row(C.c_void_p(_p(a)), C.c_float(s), C.c_void_p(_p(b)), a.size, C.c_void_p(_p(out)))
+    return out
+
+
+def cv_div_scalar(a, s):
+    a = np.ascontiguousarray(a, np.float32).ravel()
+    out = np.empty(a.size, np.float32)
+    lib().rm_cv_div_scalar(C.c_void_p(_p(a)), a.size, C.c_float(s), C.c_void_p(_p(out)))
+    return out
+
+
+def cv_gemm(a, b, alpha=1.0, c=None, beta=0.0, flags=0):
+    a = np.ascontiguousarray(a, np.float32); b = np.ascontiguousarray(b, np.float32)
+    M = a.shape[1] if flags & 1 else a.shape[0]; N = b.shape[0] if flags & 2 else b.shape[1]
+    cc = None if c is None else np.ascontiguousarray(c, np.float32)
+    out = np.empty((M, N), np.float32)
+    lib().rm_cv_gemm(C.c_void_p(_p(a)), a.shape[0], a.shape[1], C.c_void_p(_p(b)), b.shape[0], b.shape[1], C.c_double(alpha),
+                     C.c_void_p(_p(cc)) if cc is not None else None, C.c_double(beta), int(flags), C.c_void_p(_p(out)))
+    return out
+
+
+def cv_dot(a, b):
+    a = np.ascontiguousarray(a, np.float32).ravel(); b = np.ascontiguousarray(b, np.float32).ravel()
+    fn = lib().rm_cv_dot; fn.restype = C.c_double
+    return fn(C.c_void_p(_p(a)), C.c_void_p(_p(b)), a.size)
+
+
+def cv_norm(a):
+    a = np.ascontiguousarray(a, np.float32).ravel()
+    fn = lib().rm_cv_norm; fn.restype = C.c_double
+    return fn(C.c_void_p(_p(a)), a.size)
+
+
 def fuse(kf, pts, candidates, th=3.0, right=False):
     cand = np.ascontiguousarray(candidates, np.int32)
     ev = np.empty((2 * len(cand) + 4, 4), np.int32)

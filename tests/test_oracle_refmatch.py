@@ -247,3 +247,112 @@ def test_search_by_bow_two_cameras_restatement(ori):
     assert nm_o == nm_r and nm_r > 300
     assert np.array_equal(got, out_r)
     assert (mL >= 0).sum() > 100 and (mR >= 0).sum() > 100
+
+
+# ---- KannalaBrandt8::epipolarConstrain, the gate of SearchForTriangulation on fisheye keyframes -------------------------------------
+def _kb8_cam():
+    return np.array(list(wc.KB8["K"]) + list(wc.KB8["kb"]), np.float32)
+
+
+def test_kb8_unproject_restatement():
+    """oracle.kb8_unproject in the host-libm mode == the reference's compiled KannalaBrandt8::unproject (KannalaBrandt8.cpp:112-137), bit
+    for bit; the portable mode ((float)tan((double)theta), the CUDA arithmetic) moves ~3 % of the rays, by at most 4 ulp of a coordinate"""
+    import oracle
+    rng = np.random.default_rng(2)
+    xy = np.concatenate([rng.uniform(0, 512, (20000, 2)), [[wc.KB8["K"][2], wc.KB8["K"][3]]]]).astype(np.float32)   # incl. the principal point
+    ref = rm.kb8_unproject(_kb8_cam(), xy)
+    lit = oracle.kb8_unproject(_kb8_cam(), xy, oracle.LIBM_F32)
+    assert np.array_equal(lit.view(np.uint32), ref.view(np.uint32))
+    por = oracle.kb8_unproject(_kb8_cam(), xy, oracle.LIBM_PORTABLE)
+    d = np.abs(por.view(np.int32).astype(np.int64) - ref.view(np.int32))
+    assert d.max() <= 4 and (d > 0).any(1).mean() < 0.05    # glibc's tanf is within an ulp of tan, not always the nearest float
+
+
+def _pair_candidates(W, A, B, n_rand, seed):
+    """keypoint pairs for the triangulation gate: the true correspondences of two observations plus random pairs"""
+    ia = {int(m): i for i, m in enumerate(A["mp_idx"]) if m >= 0}
+    tr = [(ia[int(m)], j) for j, m in enumerate(B["mp_idx"]) if m >= 0 and int(m) in ia]
+    rng = np.random.default_rng(seed)
+    rd = list(zip(rng.integers(0, len(A["kps"]), n_rand), rng.integers(0, len(B["kps"]), n_rand)))
+    p = np.array(tr + rd)
+    return p[:, 0], p[:, 1], len(tr)
+
+
+@pytest.mark.parametrize("seed,dt", [(16, 0.25), (17, 0.6), (18, 0.05)])
+def test_kb8_triangulate_matches_restatement(seed, dt):
+    """oracle.kb8_triangulate_matches == the reference's compiled KannalaBrandt8::TriangulateMatches / Triangulate (KannalaBrandt8.cpp:343-444)
+    over the stand-in cv:: (gemm, dot, norm, hconcat, row assignment, cv::SVD -- each pinned to cv2 in test_oracle_cvmat.py): the returned
+    depth and the accepted point, bit for bit, on true correspondences (accepted, rejected by parallax or by reprojection) and random pairs"""
+    import oracle
+    from tri_cases import triangulation_geometry_kb8
+    W = wc.World(seed=seed, n_pts=1500, cam=wc.KB8, n_dup=0)
+    Ra, ta = W.pose(seed=30, dt=dt)
+    Rb, tb = W.pose(seed=31, dt=dt)
+    A, B = W.observe(Ra, ta, seed=40), W.observe(Rb, tb, seed=41)
+    pairs, _ = triangulation_geometry_kb8(oracle, A["Tcw"], B["Tcw"], _kb8_cam(), gemm=rm.cv_gemm, libm_mode=oracle.LIBM_F32)
+    G = pairs[0]
+    i1, i2, ntrue = _pair_candidates(W, A, B, 1500, seed)
+    xy1 = np.stack([A["kps"]["x"][i1], A["kps"]["y"][i1]], 1); xy2 = np.stack([B["kps"]["x"][i2], B["kps"]["y"][i2]], 1)
+    _, _, s2, _ = rm.scale_tables(1.2, 8)
+    sg1, sg2 = s2[A["kps"]["octave"][i1]], s2[B["kps"]["octave"][i2]]
+    z_r, p_r = rm.kb8_triangulate_matches(_kb8_cam(), _kb8_cam(), G[:9], G[9:12], xy1, xy2, sg1, sg2)
+    z_o, p_o = oracle.kb8_triangulate_matches(G, xy1, xy2, sg1, sg2, oracle.LIBM_F32)
+    assert np.array_equal(z_o.view(np.uint32), z_r.view(np.uint32))
+    assert np.array_equal(p_o.view(np.uint32), p_r.view(np.uint32))
+    acc = z_r > 0.0001
+    assert acc[:ntrue].mean() > (0.5 if dt >= 0.25 else 0.0) and acc[ntrue:].mean() < 0.2 and (~acc[:ntrue]).sum() > 5
+    # portable libm policy: the same decisions on this sample (a flip needs a value within an ulp of a threshold)
+    z_p, _ = oracle.kb8_triangulate_matches(G, xy1, xy2, sg1, sg2, oracle.LIBM_PORTABLE)
+    assert np.array_equal(z_p > 0.0001, acc)
+
+
+def _free(assoc, keep, seed):
+    return np.where(np.random.default_rng(seed).random(len(assoc)) < keep, assoc, -1).astype(np.int32)
+
+
+@pytest.mark.parametrize("only_stereo,coarse,ori", [(False, False, True), (False, True, True), (False, False, False), (True, False, True)])
+def test_search_for_triangulation_kb8_restatement(only_stereo, coarse, ori):
+    """oracle.search_for_triangulation_kb8 == the reference's compiled SearchForTriangulation (ORBmatcher.cc:981-1222) on monocular-fisheye
+    keyframes: the gate is KannalaBrandt8::epipolarConstrain, R12 / t12 / the epipole are the reference's own cv::Mat lines"""
+    import oracle
+    from tri_cases import triangulation_geometry_kb8
+    W = wc.World(seed=16, n_pts=1500, cam=wc.KB8, n_dup=0)
+    Ra, ta = W.pose(seed=30); Rb, tb = W.pose(seed=31)
+    A, B = W.observe(Ra, ta, seed=40), W.observe(Rb, tb, seed=41)
+    fva, fvb = bowsynth.feature_vector(A["desc"], 24, seed=1), bowsynth.feature_vector(B["desc"], 24, seed=1)
+    aa, bb = _free(A["assoc"], 0.25, 1), _free(B["assoc"], 0.25, 2)
+    kf1, kf2 = W.view(rm, A, assoc=aa, feat_vec=fva), W.view(rm, B, assoc=bb, feat_vec=fvb)
+    nm_r, pr = rm.search_for_triangulation(kf1, kf2, W.points(rm), np.eye(3, dtype=np.float32), only_stereo, coarse, 0.6, ori)
+    pairs, ep = triangulation_geometry_kb8(oracle, A["Tcw"], B["Tcw"], _kb8_cam(), gemm=rm.cv_gemm, libm_mode=oracle.LIBM_F32)
+    s1, s2 = (A["u_right"] >= 0), (B["u_right"] >= 0)
+    e1 = ((aa < 0) & (~np.bool_(only_stereo) | s1)).astype(np.uint8); e2 = ((bb < 0) & (~np.bool_(only_stereo) | s2)).astype(np.uint8)
+    nm_o, m12 = oracle.search_for_triangulation_kb8(A["kps"], A["desc"], fva, e1, s1, -1, B["kps"], B["desc"], fvb, e2, s2, -1, pairs, ep,
+                                                    kf2.scale, kf1.scale ** 2, kf2.scale ** 2, coarse, ori, oracle.LIBM_F32)
+    got = np.stack([np.nonzero(m12 >= 0)[0], m12[m12 >= 0]], 1)
+    assert nm_o == nm_r and np.array_equal(got, pr)
+    assert nm_r > (100 if not only_stereo else -1)
+
+
+@pytest.mark.parametrize("coarse,ori", [(False, True), (True, False)])
+def test_search_for_triangulation_two_cameras_restatement(coarse, ori):
+    """the same on fisheye-stereo keyframes (mpCamera2 set, ORBmatcher.cc:1005-1019, 1103-1140): the pair (left|right, left|right) selects
+    Rll..Rrr / tll..trr and the two cameras; the epipole gate is off"""
+    import oracle
+    from tri_cases import triangulation_geometry_kb8
+    W = wc.World(seed=8, n_pts=1600, cam=wc.KB8, n_dup=0)
+    Ra, ta = W.pose(seed=12); Rb, tb = W.pose(seed=13)
+    A, B = W.observe_two_cameras(Ra, ta, seed=30), W.observe_two_cameras(Rb, tb, seed=50)
+    fva, fvb = bowsynth.feature_vector(A["desc"], 30, seed=1), bowsynth.feature_vector(B["desc"], 30, seed=1)
+    aa, bb = _free(A["assoc"], 0.25, 1), _free(B["assoc"], 0.25, 2)
+    kf1, kf2 = W.view_two_cameras(rm, A, assoc=aa, feat_vec=fva), W.view_two_cameras(rm, B, assoc=bb, feat_vec=fvb)
+    nm_r, pr = rm.search_for_triangulation(kf1, kf2, W.points(rm), np.eye(3, dtype=np.float32), False, coarse, 0.6, ori)
+    pairs, ep = triangulation_geometry_kb8(oracle, A["Tcw"], B["Tcw"], _kb8_cam(), Tlr=A["Tlr"], Tlr2=B["Tlr"], gemm=rm.cv_gemm,
+                                           libm_mode=oracle.LIBM_F32)
+    k1, k2 = np.concatenate([A["kps"], A["kps_right"]]), np.concatenate([B["kps"], B["kps_right"]])
+    nm_o, m12 = oracle.search_for_triangulation_kb8(k1, A["desc"], fva, (aa < 0).astype(np.uint8), None, A["n_left"], k2, B["desc"], fvb,
+                                                    (bb < 0).astype(np.uint8), None, B["n_left"], pairs, ep, kf2.scale, kf1.scale ** 2,
+                                                    kf2.scale ** 2, coarse, ori, oracle.LIBM_F32)
+    got = np.stack([np.nonzero(m12 >= 0)[0], m12[m12 >= 0]], 1)
+    assert nm_o == nm_r and np.array_equal(got, pr) and nm_r > 150
+    right1, right2 = got[:, 0] >= A["n_left"], got[:, 1] >= B["n_left"]
+    assert all(((right1 == a) & (right2 == b)).sum() > 5 for a in (False, True) for b in (False, True))   # ll, lr, rl, rr all occur
