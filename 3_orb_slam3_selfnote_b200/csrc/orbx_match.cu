@@ -13,6 +13,7 @@
 #include "knn2_tc.cuh"
 #include "match_kernels.cuh"
 #include "orbx_internal.h"
+#include "kb8_triangulate.cuh"   // after match_kernels.cuh: uses BowArgs, load_desc, hamming8, bow_key
 
 using namespace orbx;
 
@@ -1047,6 +1048,8 @@ struct BowProblem {
   int maxDist; float nnratio; int checkOrientation;
   bool triangulate; const float* F12; float epx, epy; const float* scaleFactors2; const float* levelSigma2; int nlevels; int coarse;
   int nLeft2 = -1; int* matches12R = nullptr;   // side 2 is a fisheye-stereo frame: features >= nLeft2 are the right image's
+  // KannalaBrandt8 gate of SearchForTriangulation (kb8 != null): pair records, left counts of both keyframes, pKF1's sigma table
+  const orbx_kb8_pair* kb8 = nullptr; int triLeft1 = -1, triLeft2 = -1; const float* levelSigma1 = nullptr;
 };
 
 int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches) {
@@ -1093,6 +1096,7 @@ int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches)
   const size_t oB0 = plan.add((size_t)P.n2 * 4), oB1 = plan.add((size_t)P.n2 * 4), oChg = plan.add(8), oCh = plan.add((size_t)nw * 4);
   const size_t oSF = P.triangulate ? plan.add((size_t)P.nlevels * 4) : (size_t)-1, oLS = P.triangulate ? plan.add((size_t)P.nlevels * 4) : (size_t)-1;
   const size_t oMR = fish ? plan.add((size_t)P.n1 * 4) : (size_t)-1, oChR = fish ? plan.add((size_t)nw * 4) : (size_t)-1;
+  const size_t oLS1 = P.kb8 ? plan.add((size_t)P.nlevels * 4) : (size_t)-1;
   int rc = arena_ensure(m, plan.total);
   if (rc != ORBX_OK) return rc;
   cudaStream_t st = m->stream;
@@ -1105,6 +1109,7 @@ int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches)
   CK(up(oE1, P.elig1, P.n1)); CK(up(oE2, P.elig2, P.n2)); CK(up(oS1, P.stereo1, P.n1)); CK(up(oS2, P.stereo2, P.n2));
   CK(up(oW, work.data(), (size_t)nw * sizeof(BowWork)));
   CK(up(oSF, P.scaleFactors2, (size_t)P.nlevels * 4)); CK(up(oLS, P.levelSigma2, (size_t)P.nlevels * 4));
+  CK(up(oLS1, P.levelSigma1, (size_t)P.nlevels * 4));
   BowArgs A{};
   A.s1 = BowSide{at<orbx_keypoint>(m, oK1), at<uint8_t>(m, oD1), P.n1, at<unsigned>(m, oI1), P.elig1 ? at<uint8_t>(m, oE1) : nullptr,
                  P.stereo1 ? at<uint8_t>(m, oS1) : nullptr};
@@ -1117,10 +1122,18 @@ int run_bow(orbx_matcher* m, const BowProblem& P, int* matches12, int* nmatches)
   A.blk[0] = at<int>(m, oB0); A.blk[1] = at<int>(m, oB1); A.chg = at<int>(m, oChg); A.choice = at<int>(m, oCh);
   A.nLeft2 = P.nLeft2; A.matches12R = fish ? at<int>(m, oMR) : nullptr; A.choiceR = fish ? at<int>(m, oChR) : nullptr;
   if (P.triangulate) {
-    memcpy(A.F12, P.F12, sizeof(A.F12));
+    if (P.F12) memcpy(A.F12, P.F12, sizeof(A.F12));
     A.epx = P.epx; A.epy = P.epy; A.scaleFactors2 = at<float>(m, oSF); A.levelSigma2 = at<float>(m, oLS); A.coarse = P.coarse;
     CK(cudaMemsetAsync(m->arena + oM, 0xff, (size_t)P.n1 * 4, st));
-    k_bow_triangulate<<<(nw + 7) / 8, 256, 0, st>>>(A);
+    if (P.kb8) {
+      Kb8TriArgs T{};
+      static_assert(sizeof(Kb8PairDev) == sizeof(orbx_kb8_pair), "orbx_kb8_pair layout");
+      memcpy(T.pair, P.kb8, sizeof(orbx_kb8_pair) * (P.triLeft1 != -1 ? 4 : 1));
+      T.nLeft1 = P.triLeft1; T.nLeft2 = P.triLeft2; T.levelSigma1 = at<float>(m, oLS1);
+      k_bow_triangulate_kb8<<<(nw + 7) / 8, 256, 0, st>>>(A, T);
+    } else {
+      k_bow_triangulate<<<(nw + 7) / 8, 256, 0, st>>>(A);
+    }
   } else {
     k_bow_distances<<<(nw + 7) / 8, 256, 0, st>>>(A);
     k_bow_resolve_par<<<kParCluster, kParThreads, 0, st>>>(A);
@@ -1171,6 +1184,55 @@ int orbx_search_for_triangulation(orbx_matcher* m, int n1, const orbx_keypoint* 
   P.checkOrientation = checkOrientation; P.triangulate = true;
   P.F12 = F12; P.epx = epx; P.epy = epy; P.scaleFactors2 = scaleFactors2; P.levelSigma2 = levelSigma2_2; P.nlevels = nlevels; P.coarse = coarse;
   return run_bow(m, P, matches12, nmatches);
+}
+
+int orbx_search_for_triangulation_kb8(orbx_matcher* m, int n1, const orbx_keypoint* kps1, const uint8_t* desc1, const orbx_featvec* fv1,
+                                      const uint8_t* elig1, const uint8_t* stereo1, int nLeft1, int n2, const orbx_keypoint* kps2,
+                                      const uint8_t* desc2, const orbx_featvec* fv2, const uint8_t* elig2, const uint8_t* stereo2,
+                                      int nLeft2, const orbx_kb8_pair* pairs, int npairs, float epx, float epy,
+                                      const float* scaleFactors2, const float* levelSigma2_1, const float* levelSigma2_2, int nlevels,
+                                      int coarse, int checkOrientation, int* matches12, int* nmatches) {
+  if (!pairs || !scaleFactors2 || !levelSigma2_1 || !levelSigma2_2 || nlevels < 1 || !elig1 || !elig2) return ORBX_ERR_ARG;
+  const bool two = nLeft1 != -1;
+  if ((nLeft2 != -1) != two || npairs != (two ? 4 : 1)) { set_error("both keyframes carry a second camera (4 pair records) or neither does (1)"); return ORBX_ERR_ARG; }
+  if (two && (nLeft1 < 0 || nLeft1 > n1 || nLeft2 < 0 || nLeft2 > n2)) return ORBX_ERR_ARG;
+  for (int i = 0; i < n1 && kps1; i++)
+    if (kps1[i].octave < 0 || kps1[i].octave >= nlevels) { set_error("keypoint octave outside the level tables"); return ORBX_ERR_ARG; }
+  for (int i = 0; i < n2 && kps2; i++)
+    if (kps2[i].octave < 0 || kps2[i].octave >= nlevels) { set_error("keypoint octave outside the level tables"); return ORBX_ERR_ARG; }
+  BowProblem P{};
+  P.n1 = n1; P.kps1 = kps1; P.desc1 = desc1; P.fv1 = fv1; P.elig1 = elig1; P.stereo1 = two ? nullptr : stereo1;
+  P.n2 = n2; P.kps2 = kps2; P.desc2 = desc2; P.fv2 = fv2; P.elig2 = elig2; P.stereo2 = two ? nullptr : stereo2;
+  P.checkOrientation = checkOrientation; P.triangulate = true;
+  P.F12 = nullptr; P.epx = epx; P.epy = epy; P.scaleFactors2 = scaleFactors2; P.levelSigma2 = levelSigma2_2; P.nlevels = nlevels; P.coarse = coarse;
+  P.kb8 = pairs; P.triLeft1 = nLeft1; P.triLeft2 = nLeft2; P.levelSigma1 = levelSigma2_1;
+  return run_bow(m, P, matches12, nmatches);
+}
+
+int orbx_kb8_triangulate_matches(orbx_matcher* m, const orbx_kb8_pair* pair, int n, const float* xy1, const float* xy2, const float* sigma1,
+                                 const float* sigma2, float* z1, float* p3D) {
+  if (!m || !pair || n < 0 || (n > 0 && (!xy1 || !xy2 || !sigma1 || !sigma2 || !z1 || !p3D))) return ORBX_ERR_ARG;
+  if (n == 0) return ORBX_OK;
+  CK(cudaSetDevice(m->device));
+  ArenaPlan plan;
+  const size_t oA = plan.add((size_t)n * 8), oB = plan.add((size_t)n * 8), oS1 = plan.add((size_t)n * 4), oS2 = plan.add((size_t)n * 4);
+  const size_t oZ = plan.add((size_t)n * 4), oP = plan.add((size_t)n * 12);
+  int rc = arena_ensure(m, plan.total);
+  if (rc != ORBX_OK) return rc;
+  cudaStream_t st = m->stream;
+  CK(cudaMemcpyAsync(m->arena + oA, xy1, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(m->arena + oB, xy2, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(m->arena + oS1, sigma1, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(m->arena + oS2, sigma2, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+  Kb8PairDev G;
+  memcpy(&G, pair, sizeof(G));
+  k_kb8_triangulate_pairs<<<(n + 127) / 128, 128, 0, st>>>(G, n, at<float>(m, oA), at<float>(m, oB), at<float>(m, oS1), at<float>(m, oS2),
+                                                          at<float>(m, oZ), at<float>(m, oP));
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(z1, m->arena + oZ, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(p3D, m->arena + oP, (size_t)n * 12, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return ORBX_OK;
 }
 
 int orbx_distinctive_descriptors(orbx_matcher* m, const uint8_t* desc, const int* start, int npoints, int* bestIdx, int* bestMedian) {

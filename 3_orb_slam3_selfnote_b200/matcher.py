@@ -246,6 +246,36 @@ class ORBmatcher:
                                                    int(self.mbCheckOrientation), _p(m12), C.byref(nm)))
         return nm.value, m12[:len(kps1)]
 
+    def SearchForTriangulationKB8(self, kps1, desc1, fv1, elig1, stereo1, n_left1, kps2, desc2, fv2, elig2, stereo2, n_left2, pairs, ep,
+                                  scale_factors2, level_sigma2_1, level_sigma2_2, coarse=False):
+        """SearchForTriangulation on KannalaBrandt8 keyframes (src/ORBmatcher.cc:981-1222 with the gate of KannalaBrandt8.cpp:244-247):
+        pairs = one 28-float record R12[9] t12[3] cam1[8] cam2[8] (n_left = -1) or the four records ll, lr, rl, rr of a fisheye-stereo
+        rig (kps / desc = left features followed by right ones)."""
+        kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+        desc1, desc2, elig1, elig2 = _u8(desc1), _u8(desc2), _u8(elig1), _u8(elig2)
+        stereo1 = None if stereo1 is None else _u8(stereo1); stereo2 = None if stereo2 is None else _u8(stereo2)
+        c1, keep1 = self._fv(fv1); c2, keep2 = self._fv(fv2)
+        G = np.ascontiguousarray(np.stack([_f32(p).reshape(28) for p in pairs]))
+        sf = _f32(scale_factors2); l1 = _f32(level_sigma2_1); l2 = _f32(level_sigma2_2)
+        m12 = np.full(max(len(kps1), 1), -1, np.int32)
+        nm = C.c_int(0)
+        _check(lib().orbx_search_for_triangulation_kb8(self._m, len(kps1), _p(kps1), _p(desc1), C.byref(c1), _p(elig1), _p(stereo1),
+                                                       int(n_left1), len(kps2), _p(kps2), _p(desc2), C.byref(c2), _p(elig2), _p(stereo2),
+                                                       int(n_left2), _p(G), len(G), C.c_float(ep[0]), C.c_float(ep[1]), _p(sf), _p(l1),
+                                                       _p(l2), len(sf), int(coarse), int(self.mbCheckOrientation), _p(m12), C.byref(nm)))
+        return nm.value, m12[:len(kps1)]
+
+    def TriangulateMatchesKB8(self, pair, xy1, xy2, sigma1, sigma2):
+        """KannalaBrandt8::TriangulateMatches (KannalaBrandt8.cpp:343-418) for n keypoint pairs -> (z1 or -1, accepted point) per pair"""
+        G = _f32(pair).reshape(28)
+        xy1 = _f32(xy1).reshape(-1, 2); xy2 = _f32(xy2).reshape(-1, 2)
+        n = len(xy1)
+        s1 = np.ascontiguousarray(np.broadcast_to(np.asarray(sigma1, np.float32), (n,)))
+        s2 = np.ascontiguousarray(np.broadcast_to(np.asarray(sigma2, np.float32), (n,)))
+        z1 = np.empty(max(n, 1), np.float32); p3d = np.empty((max(n, 1), 3), np.float32)
+        _check(lib().orbx_kb8_triangulate_matches(self._m, _p(G), n, _p(xy1), _p(xy2), _p(s1), _p(s2), _p(z1), _p(p3d)))
+        return z1[:n], p3d[:n]
+
     def DistinctiveDescriptors(self, desc, start):
         """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:350) for a batch of map points: descriptors of point p
         are rows start[p]:start[p+1].  -> (best_idx[npoints] relative to start[p], best_median[npoints])"""

@@ -268,6 +268,31 @@ int orbx_search_for_triangulation(orbx_matcher* m, int n1, const orbx_keypoint* 
                                   const float* level_sigma2_2, int nlevels, int coarse, int check_orientation, int* matches12,
                                   int* nmatches);
 
+/* The same entry point for KannalaBrandt8 keyframes, where the gate of src/ORBmatcher.cc:1146 is
+ * KannalaBrandt8::epipolarConstrain (src/CameraModels/KannalaBrandt8.cpp:244-247): the candidate pair is triangulated
+ * (TriangulateMatches :343-418: unproject both keypoints, parallax test, the 4x4 homogeneous system solved by cv::SVD -- OpenCV's
+ * one-sided Jacobi, restated on the device --, both depths positive, both reprojection errors within 5.991 sigma^2).
+ * One record per (camera of pKF1, camera of pKF2) combination: R12 / t12 row-major as src/ORBmatcher.cc:1000-1019 forms them,
+ * cam = fx fy cx cy k1 k2 k3 k4. */
+typedef struct orbx_kb8_pair { float R12[9]; float t12[3]; float cam1[8]; float cam2[8]; } orbx_kb8_pair;
+/* n_left1 = n_left2 = -1: one camera per keyframe (TUM-VI monocular), npairs = 1, kps = mvKeysUn, the epipole gate of
+ * :1093-1101 applies.  Fisheye-stereo keyframes (mpCamera2 set, pKF->NLeft != -1): kps / desc = the left features followed by
+ * the right ones (mvKeys then mvKeysRight), npairs = 4 in the order ll, lr, rl, rr (index 2 * bRight1 + bRight2, :1103-1140), no
+ * feature counts as stereo and the epipole gate is off.  level_sigma2_1 / _2 = mvLevelSigma2 of pKF1 / pKF2. */
+int orbx_search_for_triangulation_kb8(orbx_matcher* m, int n1, const orbx_keypoint* kps1, const uint8_t* desc1, const orbx_featvec* fv1,
+                                      const uint8_t* elig1, const uint8_t* stereo1, int n_left1, int n2, const orbx_keypoint* kps2,
+                                      const uint8_t* desc2, const orbx_featvec* fv2, const uint8_t* elig2, const uint8_t* stereo2,
+                                      int n_left2, const orbx_kb8_pair* pairs, int npairs, float epx, float epy,
+                                      const float* scale_factors2, const float* level_sigma2_1, const float* level_sigma2_2,
+                                      int nlevels, int coarse, int check_orientation, int* matches12, int* nmatches);
+
+/* KannalaBrandt8::TriangulateMatches (src/CameraModels/KannalaBrandt8.cpp:343-418) for n independent keypoint pairs: what
+ * Frame::ComputeStereoFishEyeMatches does with every left-right match that survived orbx_knn_ratio_match (src/Frame.cc:1255-1262, pair =
+ * {mRlr, mtlr, left camera, right camera}, sigma1 / sigma2 = mvLevelSigma2 of the two keypoints' octaves).  xy1 / xy2: n x 2 pixel
+ * coordinates.  z1[i] = depth in camera 1 or -1 (the reference accepts z1 > 0.0001f); p3D[3i..] = the point when accepted, else 0. */
+int orbx_kb8_triangulate_matches(orbx_matcher* m, const orbx_kb8_pair* pair, int n, const float* xy1, const float* xy2,
+                                 const float* sigma1, const float* sigma2, float* z1, float* p3D);
+
 /* ---- pure Hamming workloads on descriptors next to the path ---------------------------------- */
 
 /* MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:350-436, for a batch of map points (LocalMapping calls it per

@@ -285,3 +285,102 @@ def test_search_by_bow_two_cameras_vs_oracle(orbx, oracle, ori, ratio):
     assert nm_g == nm_o and nm_o > 300
     assert np.array_equal(mL_g, mL_o) and np.array_equal(mR_g, mR_o)
     assert (mL_o >= 0).sum() > 100 and (mR_o >= 0).sum() > 100 and (mR_o[mR_o >= 0] >= obs["n_left"]).all()
+
+
+# ---- KannalaBrandt8::epipolarConstrain on the device (the gate of SearchForTriangulation on fisheye keyframes) -----------------------
+def _kb8_cam():
+    import world_cases as wc
+    return np.array(list(wc.KB8["K"]) + list(wc.KB8["kb"]), np.float32)
+
+
+def _kb8_world(seed, dt=0.25, two=False):
+    import world_cases as wc
+    Wd = wc.World(seed=seed, n_pts=1600, cam=wc.KB8, n_dup=0)
+    Ra, ta = Wd.pose(seed=30, dt=dt); Rb, tb = Wd.pose(seed=31, dt=dt)
+    if two:
+        return Wd, Wd.observe_two_cameras(Ra, ta, seed=30), Wd.observe_two_cameras(Rb, tb, seed=50)
+    return Wd, Wd.observe(Ra, ta, seed=40), Wd.observe(Rb, tb, seed=41)
+
+
+@pytest.mark.parametrize("seed,dt", [(16, 0.25), (17, 0.6), (18, 0.05)])
+def test_kb8_triangulate_matches_vs_oracle(orbx, oracle, seed, dt):
+    """orbx_kb8_triangulate_matches (k_kb8_triangulate_pairs: unproject, parallax, the 4x4 system through the Jacobi SVD, depths, both
+    reprojections) against the CPU restatement in its portable libm mode -- itself equal, in host-libm mode, to the reference's compiled
+    KannalaBrandt8::TriangulateMatches (tests/test_oracle_refmatch.py).  Depth and point bit for bit; CUDA's and glibc's double tan /
+    atan2 / cos / sin / hypot may differ in the last place, which after the rounding to float is allowed to show in a handful of values."""
+    from tri_cases import triangulation_geometry_kb8
+    Wd, A, B = _kb8_world(seed, dt)
+    pairs, _ = triangulation_geometry_kb8(oracle, A["Tcw"], B["Tcw"], _kb8_cam())
+    ia = {int(mp): i for i, mp in enumerate(A["mp_idx"]) if mp >= 0}
+    tr = [(ia[int(mp)], j) for j, mp in enumerate(B["mp_idx"]) if mp >= 0 and int(mp) in ia]
+    rng = np.random.default_rng(seed)
+    rd = list(zip(rng.integers(0, len(A["kps"]), 3000), rng.integers(0, len(B["kps"]), 3000)))
+    p = np.array(tr + rd)
+    xy1 = np.stack([A["kps"]["x"][p[:, 0]], A["kps"]["y"][p[:, 0]]], 1); xy2 = np.stack([B["kps"]["x"][p[:, 1]], B["kps"]["y"][p[:, 1]]], 1)
+    s2 = (np.float32(1.2) ** np.arange(8, dtype=np.float32)) ** 2
+    sg1, sg2 = s2[A["kps"]["octave"][p[:, 0]]], s2[B["kps"]["octave"][p[:, 1]]]
+    z_o, p_o = oracle.kb8_triangulate_matches(pairs[0], xy1, xy2, sg1, sg2, oracle.LIBM_PORTABLE)
+    m = orbx.ORBmatcher(0.6)
+    z_g, p_g = m.TriangulateMatchesKB8(pairs[0], xy1, xy2, sg1, sg2)
+    m.close()
+    assert np.array_equal(z_g > 0.0001, z_o > 0.0001)
+    assert (z_g.view(np.uint32) != z_o.view(np.uint32)).sum() <= 3 and (p_g.view(np.uint32) != p_o.view(np.uint32)).sum() <= 9
+    acc = z_o > 0.0001
+    assert acc[:len(tr)].sum() > (100 if dt >= 0.25 else 0) and (~acc[:len(tr)]).sum() > 5 and acc[len(tr):].mean() < 0.2
+
+
+@pytest.mark.parametrize("only_stereo,coarse,ori", [(False, False, True), (False, True, True), (False, False, False), (True, False, True)])
+def test_search_for_triangulation_kb8_vs_oracle(orbx, oracle, only_stereo, coarse, ori):
+    """orbx_search_for_triangulation_kb8 (k_bow_triangulate_kb8) on monocular-fisheye keyframes against the CPU restatement, which
+    tests/test_oracle_refmatch.py pins to the reference's compiled SearchForTriangulation: same pairs, same count"""
+    from tri_cases import triangulation_geometry_kb8
+    Wd, A, B = _kb8_world(16)
+    fva, fvb = feature_vector(A["desc"], 24, 1), feature_vector(B["desc"], 24, 1)
+    rng = np.random.default_rng(1)
+    aa = np.where(rng.random(len(A["assoc"])) < 0.25, A["assoc"], -1); bb = np.where(rng.random(len(B["assoc"])) < 0.25, B["assoc"], -1)
+    pairs, ep = triangulation_geometry_kb8(oracle, A["Tcw"], B["Tcw"], _kb8_cam())
+    sf = np.float32(1.2) ** np.arange(8, dtype=np.float32)
+    s1, s2 = (A["u_right"] >= 0).astype(np.uint8), (B["u_right"] >= 0).astype(np.uint8)
+    if only_stereo:     # the reference's flag on a camera without stereo measurements: nothing is eligible
+        e1 = ((aa < 0) & (s1 > 0)).astype(np.uint8); e2 = ((bb < 0) & (s2 > 0)).astype(np.uint8)
+    else:
+        e1 = (aa < 0).astype(np.uint8); e2 = (bb < 0).astype(np.uint8)
+    ref_n, ref = oracle.search_for_triangulation_kb8(A["kps"], A["desc"], fva, e1, s1, -1, B["kps"], B["desc"], fvb, e2, s2, -1, pairs, ep,
+                                                     sf, sf * sf, sf * sf, coarse, ori, oracle.LIBM_PORTABLE)
+    m = orbx.ORBmatcher(0.6, ori)
+    n, got = m.SearchForTriangulationKB8(A["kps"], A["desc"], fva, e1, s1, -1, B["kps"], B["desc"], fvb, e2, s2, -1, pairs, ep, sf, sf * sf,
+                                         sf * sf, coarse)
+    m.close()
+    assert n == ref_n and np.array_equal(got, ref)
+    assert ref_n > (100 if not only_stereo else -1)
+
+
+@pytest.mark.parametrize("coarse,ori", [(False, True), (False, False), (True, True)])
+def test_search_for_triangulation_two_cameras_vs_oracle(orbx, oracle, coarse, ori):
+    """the same on fisheye-stereo keyframes: features of both cameras in one list, the pair (left|right, left|right) selects one of four
+    relative poses (src/ORBmatcher.cc:1103-1140), no epipole gate"""
+    from tri_cases import triangulation_geometry_kb8
+    Wd, A, B = _kb8_world(8, two=True)
+    fva, fvb = feature_vector(A["desc"], 30, 1), feature_vector(B["desc"], 30, 1)
+    rng = np.random.default_rng(2)
+    aa = np.where(rng.random(len(A["assoc"])) < 0.25, A["assoc"], -1); bb = np.where(rng.random(len(B["assoc"])) < 0.25, B["assoc"], -1)
+    pairs, ep = triangulation_geometry_kb8(oracle, A["Tcw"], B["Tcw"], _kb8_cam(), Tlr=A["Tlr"], Tlr2=B["Tlr"])
+    k1, k2 = np.concatenate([A["kps"], A["kps_right"]]), np.concatenate([B["kps"], B["kps_right"]])
+    sf = np.float32(1.2) ** np.arange(8, dtype=np.float32)
+    e1, e2 = (aa < 0).astype(np.uint8), (bb < 0).astype(np.uint8)
+    ref_n, ref = oracle.search_for_triangulation_kb8(k1, A["desc"], fva, e1, None, A["n_left"], k2, B["desc"], fvb, e2, None, B["n_left"], pairs,
+                                                     ep, sf, sf * sf, sf * sf, coarse, ori, oracle.LIBM_PORTABLE)
+    m = orbx.ORBmatcher(0.6, ori)
+    n, got = m.SearchForTriangulationKB8(k1, A["desc"], fva, e1, None, A["n_left"], k2, B["desc"], fvb, e2, None, B["n_left"], pairs, ep, sf,
+                                         sf * sf, sf * sf, coarse)
+    assert n == ref_n and np.array_equal(got, ref) and ref_n > 150
+    r1, r2 = np.nonzero(got >= 0)[0] >= A["n_left"], got[got >= 0] >= B["n_left"]
+    assert all(((r1 == a) & (r2 == b)).sum() > 5 for a in (False, True) for b in (False, True))
+    # argument checks: a rig on one side only, a wrong record count
+    import ctypes
+    with pytest.raises(Exception):
+        m.SearchForTriangulationKB8(k1, A["desc"], fva, e1, None, A["n_left"], k2, B["desc"], fvb, e2, None, -1, pairs, ep, sf, sf * sf, sf * sf)
+    with pytest.raises(Exception):
+        m.SearchForTriangulationKB8(k1, A["desc"], fva, e1, None, A["n_left"], k2, B["desc"], fvb, e2, None, B["n_left"], pairs[:1], ep, sf,
+                                    sf * sf, sf * sf)
+    m.close()
