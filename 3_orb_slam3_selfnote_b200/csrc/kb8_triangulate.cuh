@@ -1,8 +1,8 @@
 // KannalaBrandt8::epipolarConstrain on the device: the gate of ORBmatcher::SearchForTriangulation on fisheye keyframes
 // (src/ORBmatcher.cc:1146 -> src/CameraModels/KannalaBrandt8.cpp:244-247 -> TriangulateMatches :343-418 -> Triangulate :430-444).
 //
-// Every cv::Mat expression of those lines is written out with the rounding OpenCV gives it (the same rules as oracle/match_oracle.cc,
-// which tests/ hold bit for bit against the reference's own compiled file and against cv2): a small cv::gemm is float products summed
+// Every cv::Mat expression of those lines is written out with the rounding OpenCV gives it (the rules tests/ hold bit for bit
+// against the reference's own compiled file and against cv2): a small cv::gemm is float products summed
 // left to right, Mat::dot / cv::norm accumulate in double, `s * row - row` is one rounding (addWeighted), `Mat / s` multiplies by
 // (float)(1.0 / s), and cv::SVD::compute of a 4x4 is OpenCV's one-sided Jacobi (modules/core/src/lapack.cpp JacobiSVDImpl_<float>:
 // matrices this small never reach LAPACK).  libm calls follow the portable policy of DESIGN.md section 2: tanf / atan2f are the double
@@ -13,7 +13,7 @@
 namespace orbx {
 
 // One (camera of KF1, camera of KF2) combination: R12 / t12 as ORBmatcher.cc:1000-1019 forms them, cam = fx fy cx cy k1..k4.
-// Layout = orbx.h's orbx_kb8_pair = oracle/match_oracle.h's Kb8Pair.
+// Layout = orbx.h's orbx_kb8_pair.
 struct Kb8PairDev { float R12[9]; float t12[3]; float cam1[8]; float cam2[8]; };
 
 // KannalaBrandt8::unproject (KannalaBrandt8.cpp:112-137): Newton on theta + k1 theta^3 + .. = theta_d, ray = (x, y, 1).

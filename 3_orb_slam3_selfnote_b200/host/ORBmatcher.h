@@ -411,23 +411,83 @@ class ORBmatcher {
   }
 
   // Matching to triangulate new MapPoints with the reference's parameter list (cv::Mat F12), src/ORBmatcher.cc:981-1222: pinhole
-  // keyframes without a second camera.  F12 is the matrix LocalMapping::ComputeF12 formed (K1^-T [t12]x R12 K2^-1, the very
+  // keyframes without a second camera, KannalaBrandt8 keyframes with one camera (TUM-VI monocular) or two (fisheye stereo).  For
+  // pinhole keyframes F12 is the matrix LocalMapping::ComputeF12 formed (K1^-T [t12]x R12 K2^-1, the very
   // expression Pinhole::epipolarConstrain re-evaluates per pair, Pinhole.cpp:145-148); the epipole is projected here (:988-994).
   template <class KeyFrameT>
   int SearchForTriangulation(KeyFrameT* pKF1, KeyFrameT* pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t> >& vMatchedPairs,
                              const bool bOnlyStereo, const bool bCoarse = false) {
-    // the gate is pCamera1->epipolarConstrain (:1146): Pinhole's epipolar-line distance runs on the device; KannalaBrandt8's triangulates the
-    // pair through cv::SVD (KannalaBrandt8.cpp:244-247, 340-399), which cannot be pinned without OpenCV -- refuse rather than approximate
-    if (pKF1->mpCamera2 || pKF2->mpCamera2 || pKF1->mpCamera->GetType() == 1 || pKF2->mpCamera->GetType() == 1)
-      throw std::runtime_error("ORBmatcher::SearchForTriangulation: KannalaBrandt8::epipolarConstrain (cv::SVD triangulation) is not offloaded");
+    // the gate is pCamera1->epipolarConstrain (:1146): Pinhole's epipolar-line distance and KannalaBrandt8's two-view triangulation
+    // (KannalaBrandt8.cpp:244-247, 343-444; the cv::SVD of the 4x4 system is OpenCV's Jacobi, restated in csrc/kb8_triangulate.cuh)
+    // both run on the device.  The 3x3 pose algebra in front of the loop is the reference's own lines (:988-1019).
     cv::Mat Cw = pKF1->GetCameraCenter();
     cv::Mat R2w = pKF2->GetRotation();
     cv::Mat t2w = pKF2->GetTranslation();
     cv::Mat C2 = R2w * Cw + t2w;
     cv::Point2f ep = pKF2->mpCamera->project(C2);
-    float f[9];
-    put3x3(F12, f);
-    return SearchForTriangulation(pKF1, pKF2, f, ep, vMatchedPairs, bOnlyStereo, bCoarse);
+    const bool fisheye1 = pKF1->mpCamera->GetType() == 1, fisheye2 = pKF2->mpCamera->GetType() == 1;   // GeometricCamera::CAM_FISHEYE
+    if (!fisheye1 && !fisheye2 && !pKF1->mpCamera2 && !pKF2->mpCamera2) {
+      float f[9];
+      put3x3(F12, f);
+      return SearchForTriangulation(pKF1, pKF2, f, ep, vMatchedPairs, bOnlyStereo, bCoarse);
+    }
+    if (!fisheye1 || !fisheye2 || (pKF1->mpCamera2 != nullptr) != (pKF2->mpCamera2 != nullptr) ||
+        (pKF1->mpCamera2 && (pKF1->mpCamera2->GetType() != 1 || pKF2->mpCamera2->GetType() != 1)))
+      throw std::runtime_error("ORBmatcher::SearchForTriangulation: keyframes must share a camera model (Pinhole without a second camera, or "
+                               "KannalaBrandt8 with or without one on both sides)");
+    cv::Mat R1w = pKF1->GetRotation();
+    cv::Mat t1w = pKF1->GetTranslation();
+    orbx_kb8_pair G[4];
+    memset(G, 0, sizeof G);
+    auto cam8 = [](decltype(pKF1->mpCamera) c, float* o) { for (int i = 0; i < 8; i++) o[i] = c->getParameter(i); };
+    const bool two = pKF1->mpCamera2 != nullptr;
+    if (!two) {
+      cv::Mat R12 = R1w * R2w.t();
+      cv::Mat t12 = -R1w * R2w.t() * t2w + t1w;
+      put3x3(R12, G[0].R12); put3(t12, G[0].t12); cam8(pKF1->mpCamera, G[0].cam1); cam8(pKF2->mpCamera, G[0].cam2);
+    } else {
+      cv::Mat Rll = pKF1->GetRotation() * pKF2->GetRotation().t();
+      cv::Mat Rlr = pKF1->GetRotation() * pKF2->GetRightRotation().t();
+      cv::Mat Rrl = pKF1->GetRightRotation() * pKF2->GetRotation().t();
+      cv::Mat Rrr = pKF1->GetRightRotation() * pKF2->GetRightRotation().t();
+      cv::Mat tll = pKF1->GetRotation() * (-pKF2->GetRotation().t() * pKF2->GetTranslation()) + pKF1->GetTranslation();
+      cv::Mat tlr = pKF1->GetRotation() * (-pKF2->GetRightRotation().t() * pKF2->GetRightTranslation()) + pKF1->GetTranslation();
+      cv::Mat trl = pKF1->GetRightRotation() * (-pKF2->GetRotation().t() * pKF2->GetTranslation()) + pKF1->GetRightTranslation();
+      cv::Mat trr = pKF1->GetRightRotation() * (-pKF2->GetRightRotation().t() * pKF2->GetRightTranslation()) + pKF1->GetRightTranslation();
+      put3x3(Rll, G[0].R12); put3(tll, G[0].t12); cam8(pKF1->mpCamera, G[0].cam1); cam8(pKF2->mpCamera, G[0].cam2);
+      put3x3(Rlr, G[1].R12); put3(tlr, G[1].t12); cam8(pKF1->mpCamera, G[1].cam1); cam8(pKF2->mpCamera2, G[1].cam2);
+      put3x3(Rrl, G[2].R12); put3(trl, G[2].t12); cam8(pKF1->mpCamera2, G[2].cam1); cam8(pKF2->mpCamera, G[2].cam2);
+      put3x3(Rrr, G[3].R12); put3(trr, G[3].t12); cam8(pKF1->mpCamera2, G[3].cam1); cam8(pKF2->mpCamera2, G[3].cam2);
+    }
+    const int n1 = pKF1->N, n2 = pKF2->N;
+    // kp = NLeft == -1 ? mvKeysUn[i] : i < NLeft ? mvKeys[i] : mvKeysRight[i - NLeft] (:1062-1064, 1102-1104): one list per keyframe
+    std::vector<cv::KeyPoint> k1, k2;
+    auto keys = [](KeyFrameT* K, std::vector<cv::KeyPoint>& out) {
+      if (K->NLeft == -1) { out = K->mvKeysUn; return; }
+      out.assign(K->mvKeys.begin(), K->mvKeys.begin() + K->NLeft);
+      out.insert(out.end(), K->mvKeysRight.begin(), K->mvKeysRight.end());
+    };
+    keys(pKF1, k1); keys(pKF2, k2);
+    if ((int)k1.size() != n1 || (int)k2.size() != n2) throw std::runtime_error("ORBmatcher::SearchForTriangulation: N != NLeft + NRight");
+    std::vector<uint8_t> e1(std::max(n1, 1)), e2(std::max(n2, 1)), s1(std::max(n1, 1)), s2(std::max(n2, 1));
+    for (int i = 0; i < n1; i++) { s1[i] = !two && pKF1->mvuRight[i] >= 0; e1[i] = !pKF1->GetMapPoint(i) && (!bOnlyStereo || s1[i]); }
+    for (int i = 0; i < n2; i++) { s2[i] = !two && pKF2->mvuRight[i] >= 0; e2[i] = !pKF2->GetMapPoint(i) && (!bOnlyStereo || s2[i]); }
+    FeatVecHolder fv1(pKF1->mFeatVec), fv2(pKF2->mFeatVec);
+    DescHolder d1(pKF1->mDescriptors, n1), d2(pKF2->mDescriptors, n2);
+    std::vector<int> m12(std::max(n1, 1), -1);
+    int nmatches = 0;
+    orbx_shim::check(orbx_search_for_triangulation_kb8(m_, n1, reinterpret_cast<const orbx_keypoint*>(k1.data()), d1.p, &fv1.v, e1.data(), s1.data(),
+                                                       two ? pKF1->NLeft : -1, n2, reinterpret_cast<const orbx_keypoint*>(k2.data()), d2.p, &fv2.v,
+                                                       e2.data(), s2.data(), two ? pKF2->NLeft : -1, G, two ? 4 : 1, ep.x, ep.y,
+                                                       pKF2->mvScaleFactors.data(), pKF1->mvLevelSigma2.data(), pKF2->mvLevelSigma2.data(),
+                                                       (int)pKF2->mvScaleFactors.size(), bCoarse ? 1 : 0, mbCheckOrientation ? 1 : 0, m12.data(),
+                                                       &nmatches),
+                     "orbx_search_for_triangulation_kb8");
+    vMatchedPairs.clear();
+    vMatchedPairs.reserve(nmatches);
+    for (int i = 0; i < n1; i++)
+      if (m12[i] >= 0) vMatchedPairs.push_back(std::make_pair((size_t)i, (size_t)m12[i]));
+    return nmatches;
   }
 #endif  // ORBX_WITH_OPENCV
 

@@ -151,9 +151,10 @@ def test_search_by_sim3(scene, th, s12):
 
 
 def test_search_for_triangulation_reference_signature(scene):
-    """src/ORBmatcher.cc:981-1222 through the cv::Mat F12 parameter list (epipole projected by the shim)"""
-    if scene["name"] == "kb8":
-        pytest.skip("pinhole keyframes")
+    """src/ORBmatcher.cc:981-1222 through the cv::Mat F12 parameter list (epipole projected by the shim).  Pinhole keyframes: the epipolar
+    line test with the caller's F12; KannalaBrandt8 keyframes: the reference's own KannalaBrandt8::epipolarConstrain (two-view
+    triangulation through cv::SVD, compiled in oracle/_ref) against k_bow_triangulate_kb8 -- the reference's binary calls the host's tanf /
+    atan2f, the device rounds the double functions, and the matched pairs are the same."""
     import bowsynth
     W, A, B = scene["W"], scene["A"], scene["B"]
     Ra, ta, Rb, tb = scene["Ra"], scene["ta"], scene["Rb"], scene["tb"]
@@ -165,12 +166,33 @@ def test_search_for_triangulation_reference_signature(scene):
     F12 = (np.linalg.inv(K).T @ tx @ R12 @ np.linalg.inv(K)).astype(np.float32)
     fva = bowsynth.feature_vector(A["desc"], 24, seed=1)
     fvb = bowsynth.feature_vector(B["desc"], 24, seed=1)
-    kf1 = W.view(rm, A, assoc=A["assoc"], feat_vec=fva)
-    kf2 = W.view(rm, B, assoc=B["assoc"], feat_vec=fvb)
-    for only_stereo, coarse in ((False, False), (True, False), (False, True)):
-        ref, got = both(rm.search_for_triangulation, kf1, kf2, scene["pts"], F12, only_stereo, coarse)
-        same(ref, got, "SearchForTriangulation")
-    assert ref[0] > 10
+    free = lambda a, seed: np.where(np.random.default_rng(seed).random(len(a)) < 0.3, a, -1).astype(np.int32)
+    for a1, a2, floor in ((A["assoc"], B["assoc"], 10), (free(A["assoc"], 1), free(B["assoc"], 2), 100)):
+        kf1 = W.view(rm, A, assoc=a1, feat_vec=fva)
+        kf2 = W.view(rm, B, assoc=a2, feat_vec=fvb)
+        for only_stereo, coarse in ((False, False), (True, False), (False, True)):
+            ref, got = both(rm.search_for_triangulation, kf1, kf2, scene["pts"], F12, only_stereo, coarse)
+            same(ref, got, "SearchForTriangulation")
+        assert ref[0] > floor
+
+
+@pytest.mark.parametrize("coarse,ori", [(False, True), (True, False)])
+def test_search_for_triangulation_two_cameras(coarse, ori):
+    """src/ORBmatcher.cc:1005-1019, 1103-1140 on fisheye-stereo keyframes: Rll..Rrr / tll..trr from the shim's own cv::Mat lines, features of
+    both cameras in one list, the KannalaBrandt8 gate with the camera pair the two features belong to"""
+    import bowsynth
+    W = wc.World(seed=8, n_pts=1600, cam=wc.KB8, n_dup=0)
+    Ra, ta = W.pose(seed=12); Rb, tb = W.pose(seed=13)
+    A, B = W.observe_two_cameras(Ra, ta, seed=30), W.observe_two_cameras(Rb, tb, seed=50)
+    fva, fvb = bowsynth.feature_vector(A["desc"], 30, seed=1), bowsynth.feature_vector(B["desc"], 30, seed=1)
+    free = lambda a, seed: np.where(np.random.default_rng(seed).random(len(a)) < 0.25, a, -1).astype(np.int32)
+    kf1 = W.view_two_cameras(rm, A, assoc=free(A["assoc"], 1), feat_vec=fva)
+    kf2 = W.view_two_cameras(rm, B, assoc=free(B["assoc"], 2), feat_vec=fvb)
+    ref, got = both(rm.search_for_triangulation, kf1, kf2, W.points(rm), np.eye(3, dtype=np.float32), False, coarse, 0.6, ori)
+    same(ref, got, "SearchForTriangulation (two cameras)")
+    assert ref[0] > 150
+    r1, r2 = ref[1][:, 0] >= A["n_left"], ref[1][:, 1] >= B["n_left"]
+    assert all(((r1 == a) & (r2 == b)).sum() > 5 for a in (False, True) for b in (False, True))
 
 
 # ---- fisheye-stereo frames (F.Nleft != -1; Examples/Stereo/TUM_512.yaml-shaped rigs) ------------------------------------------
