@@ -1711,4 +1711,70 @@ int orbx_stereo_results_host(orbx_matcher* m, float* uRight, float* depth, int* 
   return ORBX_OK;
 }
 
+
+// ---- orbx_knn2_device_static: the 2-NN fold without any allocation ---------------------------------------------------------------
+// No counterpart in the reference (see include/orbx.h).  orbx_knn2 keeps its running
+// (best, second) keys in the matcher's arena (cudaMalloc on growth); this variant keeps them in a file-scope device array that
+// every GPU loading the library holds until exit: ORBX_KNN2_STATIC_MAX_QUERIES x 2 keys x 8 bytes = 256 KB.  The array's name is a
+// host-side stand-in in host code: its device address is fetched once per device with cudaGetSymbolAddress (that device current)
+// and only that pointer is handed to kernels.
+static __device__ __align__(256) unsigned long long g_knn2_static_keys[2 * ORBX_KNN2_STATIC_MAX_QUERIES];
+
+// keys -> idx / dist / good exactly as the host loop of orbx_knn2 does (Frame.cc:1253: float distance against a double 0.7)
+__global__ void __launch_bounds__(128) k_knn2_unpack(const unsigned long long* key0, const unsigned long long* key1, int nq, int* idx, int* dist,
+                                                      uint8_t* good) {
+  const int i = blockIdx.x * 128 + threadIdx.x;
+  if (i >= nq) return;
+  const unsigned long long h0 = key0[i], h1 = key1[i];
+  const bool a = h0 != kKeyNone, b = h1 != kKeyNone;
+  const int d0 = a ? (int)(h0 >> 32) : -1, d1 = b ? (int)(h1 >> 32) : -1;
+  idx[2 * i] = a ? (int)(h0 & 0xffffffffu) : -1; dist[2 * i] = d0;
+  idx[2 * i + 1] = b ? (int)(h1 & 0xffffffffu) : -1; dist[2 * i + 1] = d1;
+  if (good) good[i] = b && ((double)(float)d0 < __dmul_rn((double)(float)d1, 0.7));
+}
+
+static int knn2_static_scratch(unsigned long long** out) {
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static unsigned long long* ptrs[kMaxDevices] = {};
+  int dev = -1;
+  CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) { set_error("device ordinal %d outside the static scratch table", dev); return ORBX_ERR_UNSUPPORTED; }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    unsigned long long* p = nullptr;
+    CK(cudaGetSymbolAddress((void**)&p, g_knn2_static_keys));
+    if (!p) { set_error("cudaGetSymbolAddress returned a null scratch address"); return ORBX_ERR_CUDA; }
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return ORBX_OK;
+}
+
+int orbx_knn2_device_static(const uint8_t* dQ, int nq, const uint8_t* dT, int nt, int* dIdx, int* dDist, uint8_t* dGood, void* stream) {
+  if (nq < 0 || nt < 0 || (nq > 0 && (!dQ || !dIdx || !dDist)) || (nt > 0 && !dT)) return ORBX_ERR_ARG;
+  if (nq > ORBX_KNN2_STATIC_MAX_QUERIES) {
+    set_error("orbx_knn2_device_static: %d queries exceed the static scratch (ORBX_KNN2_STATIC_MAX_QUERIES = %d); use orbx_knn2", nq,
+              ORBX_KNN2_STATIC_MAX_QUERIES);
+    return ORBX_ERR_CAPACITY;
+  }
+  if (nq == 0) return ORBX_OK;
+  unsigned long long* keys = nullptr;
+  const int rc = knn2_static_scratch(&keys);
+  if (rc != ORBX_OK) return rc;
+  unsigned long long *key0 = keys, *key1 = keys + ORBX_KNN2_STATIC_MAX_QUERIES;
+  cudaStream_t st = (cudaStream_t)stream;
+  // the array keeps the previous call's keys: the first fold runs with init = 1, which overwrites every key this call reads
+  int init = 1, base = 0;
+  do {
+    const int n = std::min(1 << 23, nt - base);
+    k_knn2<<<(nq + 127) / 128, 128, 0, st>>>(dQ, nq, dT ? dT + (size_t)base * 32 : nullptr, n, base, nullptr, key0, key1, init);
+    CK(cudaGetLastError());
+    init = 0; base += n;
+  } while (base < nt);
+  k_knn2_unpack<<<(nq + 127) / 128, 128, 0, st>>>(key0, key1, nq, dIdx, dDist, dGood);
+  CK(cudaGetLastError());
+  return ORBX_OK;
+}
+
 }  // extern "C"

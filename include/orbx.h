@@ -545,6 +545,22 @@ int orbx_search_local_points_batch(orbx_matcher* m, orbx_extractor* ex, int nfra
 int orbx_host_alloc(size_t bytes, void** ptr);
 int orbx_host_free(void* ptr);
 
+/* orbx_knn2 for callers that cannot allocate: code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc.  NO COUNTERPART IN THE REFERENCE.
+ * Same answer as orbx_knn2 (cv::BFMatcher(NORM_HAMMING).knnMatch(k = 2) + the 0.7 ratio flag of src/Frame.cc:1246-1253) with
+ * every array in DEVICE memory of the CURRENT device: d_query nq x 32 bytes, d_train nt x 32 bytes, d_idx / d_dist nq x 2
+ * ints (-1 where fewer than two train rows exist), d_good nq bytes or NULL.  Asynchronous on `stream` (NULL = the default
+ * stream); needs no matcher handle.  The running (best, second) keys live in a file-scope device array of
+ * ORBX_KNN2_STATIC_MAX_QUERIES x 16 bytes = 256 KB that every GPU loading liborbx.so holds until exit; nq beyond that limit
+ * is refused with ORBX_ERR_CAPACITY (orbx_last_error says so), nt is unlimited.  The call runs no cudaMalloc / cudaFree or
+ * allocating library routine; the first call on each device looks the array's address up (cudaGetSymbolAddress), so make
+ * one call per device at set-up, before capturing.  All calls share the array, which keeps the last call's contents (each
+ * call overwrites the keys it reads first): calls that overlap on the GPU -- different streams without an ordering event,
+ * or two host threads -- race and must be ordered by the caller. */
+#define ORBX_KNN2_STATIC_MAX_QUERIES 16384
+int orbx_knn2_device_static(const uint8_t* d_query, int nq, const uint8_t* d_train, int nt, int* d_idx, int* d_dist, uint8_t* d_good,
+                            void* stream);
+
 const char* orbx_last_error(void);
 const char* orbx_version(void);
 
