@@ -61,7 +61,7 @@ def _peaks():
         return 6650.0, "fallback"
 
 
-NCU_SUMMARY = os.path.join(ROOT, "profiles", "r02i_ncu_full_summary.csv")   # tools/ncu_summary.py of one --set full capture (128 images per launch)
+NCU_SUMMARY = os.path.join(ROOT, "profiles", "r02m_ncu_full_summary.csv")   # tools/ncu_summary.py of one --set full capture (128 images per launch)
 NCU_NAME = {"k_fast_nms": "k_fast_nms3", "k_blur7": "k_blur7v", "k_orient_desc": "k_orient_desc2", "k_quadtree": "k_quadtree"}
 
 
