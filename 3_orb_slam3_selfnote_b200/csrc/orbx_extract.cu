@@ -319,6 +319,9 @@ bool encode_level_map(void* out, const uint8_t* base, int w, int h, int pitch, l
 
 int orbx::extractor_run_batch(orbx_extractor* h, int si, const uint8_t* dIn, int nframes, int pitch, long long frameStride, int lap0, int lap1,
                      cudaStream_t st) {
+  // the calling host thread may never have selected this handle's device (a worker thread of a rank that owns GPU 1 starts on GPU 0:
+  // launches into the handle's streams then fail with "invalid resource handle")
+  CK(cudaSetDevice(h->p.device));
   Slot& s = h->slot[si];
   const Geom& g = h->g;
   Geom gg = g;
@@ -614,6 +617,7 @@ int orbx_extract_batch_host(orbx_extractor* h, const uint8_t* images, int nframe
   if (!h) return ORBX_ERR_ARG;
   if (!images || width <= 0 || height <= 0 || nframes <= 0) return ORBX_EMPTY_IMAGE;
   if (!kps || !desc || !counts || !mono || capPerFrame <= 0 || stride < width) return ORBX_ERR_ARG;
+  CK(cudaSetDevice(h->p.device));   // every call: the steady state below creates nothing, but its copies / events / launches need the handle's device current
   int rc = extractor_build_geom(h, width, height);
   if (rc != ORBX_OK) return rc;
   const Geom& g = h->g;

@@ -258,3 +258,36 @@ def test_full_size_batch_properties(orbx, synth):
             assert (kl["x"] >= 19 * scale[l] - 1e-3).all() and (kl["x"] <= (lw - 20) * scale[l] + 1e-3).all()
             assert (kl["y"] >= 19 * scale[l] - 1e-3).all() and (kl["y"] <= (lh - 20) * scale[l] + 1e-3).all()
     g1.close(); g2.close()
+
+
+def test_second_device_from_worker_threads(orbx, synth):
+    """Handles that live on GPU 1, driven from host threads that never selected a device (they start on GPU 0): the pipelined host call,
+    the single-frame latency path and a device batch must select the handle's device themselves and answer as GPU 0 does.
+    (bench.py's two-thread e2e loop at N > 1 failed with "invalid resource handle" before extractor_run_batch did so.)"""
+    import threading
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
+    n = 16   # > 4 MB of input: the pipelined path
+    imgs = synth.frames(752, 480, 77, range(n), False)
+    ref = orbx.ORBextractor(1000, max_batch=8, device=0).extract_batch(imgs)
+    ex = orbx.ORBextractor(1000, max_batch=8, device=1)
+    out, errs = {}, []
+
+    def work(key, fn):
+        try:
+            out[key] = fn()
+        except Exception as e:   # noqa: BLE001
+            errs.append(e)
+
+    for key, fn in (("first", lambda: ex.extract_batch(imgs)), ("steady", lambda: ex.extract_batch(imgs)),
+                    ("latency", lambda: ex.extract_batch(imgs[:1]))):
+        t = threading.Thread(target=work, args=(key, fn))
+        t.start(); t.join()
+    assert not errs, errs
+    for key in ("first", "steady"):
+        for a, b in zip(ref, out[key]):
+            assert np.array_equal(a, b), key
+    c = int(ref[0][0])
+    assert int(out["latency"][0][0]) == c
+    assert np.array_equal(out["latency"][2][0, :c], ref[2][0, :c]) and np.array_equal(out["latency"][3][0, :c], ref[3][0, :c])
