@@ -71,3 +71,18 @@ def test_product_never_references_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cc", ".cpp")):
                 src = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "import oracle" not in src and "liborb_oracle" not in src and "oracle/" not in src, f
+
+
+def test_static_knn2_rejects_oversize_and_bad_arguments_before_touching_the_device(orbx):
+    """orbx_knn2_device_static (the allocation-free entry point): the size limit and the pointer checks come before any CUDA call"""
+    lib = orbx.lib()
+    hdr = open(os.path.join(ROOT, "include", "orbx.h")).read()
+    maxq = int(re.search(r"#define\s+ORBX_KNN2_STATIC_MAX_QUERIES\s+(\d+)", hdr).group(1))
+    assert maxq == 16384
+    dummy = C.c_void_p(0x1000)   # never dereferenced: every call below is refused first
+    rc = lib.orbx_knn2_device_static(dummy, maxq + 1, dummy, 10, dummy, dummy, None, None)
+    assert rc == orbx.ORBX_ERR_CAPACITY and b"ORBX_KNN2_STATIC_MAX_QUERIES" in lib.orbx_last_error()
+    assert lib.orbx_knn2_device_static(None, 5, dummy, 10, dummy, dummy, None, None) == orbx.ORBX_ERR_ARG
+    assert lib.orbx_knn2_device_static(dummy, 5, None, 10, dummy, dummy, None, None) == orbx.ORBX_ERR_ARG
+    assert lib.orbx_knn2_device_static(dummy, -1, dummy, 10, dummy, dummy, None, None) == orbx.ORBX_ERR_ARG
+    assert lib.orbx_knn2_device_static(None, 0, None, 0, None, None, None, None) == orbx.ORBX_OK
