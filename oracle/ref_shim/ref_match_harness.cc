@@ -398,6 +398,32 @@ int rm_search_by_bow_keyframes(const RefView* KF1, const RefView* KF2, const Ref
 }
 
 // ---- the stand-in cv:: arithmetic, exposed so that tests/test_oracle_cvmat.py can hold it against python cv2 -------------------
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:350-436) for npoints map points.  The observations of point p are the
+// keyframes start[p] .. start[p+1]-1; kind[k] = 0: keyframe k sees the point with its left feature only (one descriptor row), 1: the
+// keyframe is bad (one row, skipped by the reference), 2: left and right feature (two consecutive rows).  Rows are consumed in that
+// order from desc.  The keyframes of a point live in one array, so the reference's map<KeyFrame*, ..> (ordered by ADDRESS) iterates
+// them in index order.  out: the chosen mDescriptor (32 bytes per point), has[p] = 0 where the reference leaves mDescriptor empty.
+void rm_distinctive(const uint8_t* desc, const int* start, const uint8_t* kind, int npoints, uint8_t* out, int* has) {
+  size_t row = 0;
+  for (int p = 0; p < npoints; p++) {
+    const int n = start[p + 1] - start[p];
+    std::vector<KeyFrame> kfs(n);
+    MapPoint mp;
+    for (int k = 0; k < n; k++) {
+      const int kd = kind[start[p] + k];
+      const int rows = kd == 2 ? 2 : 1;
+      kfs[k].mbBad = kd == 1;
+      kfs[k].mDescriptors = cv::Mat(rows, 32, CV_8U);
+      for (int r = 0; r < rows; r++) memcpy(kfs[k].mDescriptors.ptr(r), desc + (row + r) * 32, 32);
+      row += rows;
+      mp.mObservations[&kfs[k]] = std::tuple<int, int>(0, kd == 2 ? 1 : -1);
+    }
+    mp.ComputeDistinctiveDescriptors();
+    has[p] = mp.mDescriptor.empty() ? 0 : 1;
+    if (has[p]) memcpy(out + (size_t)p * 32, mp.mDescriptor.ptr(0), 32);
+  }
+}
+
 void rm_cv_svd(const float* A, int n, float* w, float* vt) {   // cv::SVD::compute(A, w, u, vt, MODIFY_A | FULL_UV) of an n x n matrix
   cv::Mat a = mat_from(A, n, n), W, U, Vt;
   cv::SVD::compute(a, W, U, Vt, cv::SVD::MODIFY_A | cv::SVD::FULL_UV);

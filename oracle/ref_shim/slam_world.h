@@ -136,6 +136,7 @@ class MapPoint {
   float GetMaxDistanceInvariance();   // body: src/MapPoint.cc:561-565 (slice)
   int PredictScale(const float& currentDist, KeyFrame* pKF);   // body: src/MapPoint.cc:570-585 (slice)
   int PredictScale(const float& currentDist, Frame* pF);       // body: src/MapPoint.cc:587-602 (slice)
+  void ComputeDistinctiveDescriptors();                        // body: src/MapPoint.cc:350-436 (slice)
   bool IsInKeyFrame(KeyFrame* pKF) { return mObservations.count(pKF) != 0; }
   std::tuple<int, int> GetIndexInKeyFrame(KeyFrame* pKF) { return mObservations.count(pKF) ? mObservations[pKF] : std::tuple<int, int>(-1, -1); }
   void Replace(MapPoint* pMP) { if (events) events->push_back(WorldEvent{0, this, pMP, nullptr, -1}); }
@@ -146,7 +147,7 @@ class MapPoint {
   int nObs;
   cv::Mat mWorldPos, mNormalVector, mDescriptor;
   float mfMinDistance, mfMaxDistance;
-  std::mutex mMutexPos;   // the sliced bodies lock it
+  std::mutex mMutexPos, mMutexFeatures;   // the sliced bodies lock them
   std::map<KeyFrame*, std::tuple<int, int> > mObservations;
   // tracking fields written by Frame::isInFrustum
   bool mbTrackInView, mbTrackInViewR;
@@ -175,8 +176,10 @@ class KeyFrame {
   void AddMapPoint(MapPoint* pMP, const size_t& idx) { mvpMapPoints[idx] = pMP; }
   std::vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r, const bool bRight = false) const;   // src/KeyFrame.cc:798-842 (slice)
   bool IsInImage(const float& x, const float& y) const;                                                                      // src/KeyFrame.cc:844-847 (slice)
+  bool isBad() { return mbBad; }
 
   long unsigned int mnId;
+  bool mbBad = false;
   int N, NLeft, NRight;
   float fx, fy, cx, cy, invfx, invfy, mbf, mb;
   std::vector<cv::KeyPoint> mvKeys, mvKeysUn, mvKeysRight;

@@ -382,3 +382,19 @@ def time_stereo(left, right, nthreads, nfeatures, mb, mbf, blur_taps=0):
     s = lib().rm_time_stereo(nfeatures, C.c_float(1.2), 8, 20, 7, blur_taps, C.c_void_p(_p(left)), C.c_void_p(_p(right)), n, w, h, C.c_float(mb),
                              C.c_float(mbf), nthreads, C.byref(matched))
     return float(s), int(matched.value)
+
+
+def distinctive(desc, start, kind=None):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:350-436), the reference's own body, for a batch of map points:
+    start = keyframe ranges per point, kind[k] = 0 left feature only / 1 bad keyframe / 2 left + right feature (two rows);
+    desc rows in that order -> (mDescriptor[npoints, 32], has[npoints])"""
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    start = np.ascontiguousarray(start, np.int32)
+    npoints = len(start) - 1
+    kind = np.zeros(int(start[-1]), np.uint8) if kind is None else np.ascontiguousarray(kind, np.uint8)
+    assert len(desc) == int(np.where(kind == 2, 2, 1).sum())
+    out = np.zeros((npoints, 32), np.uint8)
+    has = np.zeros(npoints, np.int32)
+    lib().rm_distinctive(desc.ctypes.data_as(C.c_void_p), start.ctypes.data_as(C.c_void_p), kind.ctypes.data_as(C.c_void_p), npoints,
+                         out.ctypes.data_as(C.c_void_p), has.ctypes.data_as(C.c_void_p))
+    return out, has

@@ -356,3 +356,42 @@ def test_search_for_triangulation_two_cameras_restatement(coarse, ori):
     assert nm_o == nm_r and np.array_equal(got, pr) and nm_r > 150
     right1, right2 = got[:, 0] >= A["n_left"], got[:, 1] >= B["n_left"]
     assert all(((right1 == a) & (right2 == b)).sum() > 5 for a in (False, True) for b in (False, True))   # ll, lr, rl, rr all occur
+
+
+def test_distinctive_descriptors_restatement(oracle):
+    """MapPoint::ComputeDistinctiveDescriptors: the restatement (oracle.distinctive_descriptors, what k_distinctive is held against)
+    equals the reference's own body (src/MapPoint.cc:350-436, cut out at build time) -- chosen descriptor per map point, incl. points
+    without observations, observations in bad keyframes (skipped), keyframes that see the point with both cameras (two rows),
+    clusters of identical descriptors (ties go to the first row in the reference's map order) and small descriptors (low distances)."""
+    rng = np.random.default_rng(12)
+    counts = np.concatenate([[0, 1, 2, 3, 8, 33, 64, 5, 1, 2], rng.integers(1, 40, 60)]).astype(np.int32)
+    start = np.concatenate([[0], np.cumsum(counts)]).astype(np.int32)
+    nkf = int(start[-1])
+    kind = rng.choice(np.array([0, 0, 0, 1, 2], np.uint8), nkf)
+    kind[start[8]:start[9]] = 1            # a point all of whose keyframes are bad: mDescriptor stays empty
+    kind[start[9]:start[10]] = [1, 2]
+    rows = np.where(kind == 2, 2, 1)
+    row0 = np.concatenate([[0], np.cumsum(rows)])
+    desc = rng.integers(0, 256, (int(row0[-1]), 32), dtype=np.uint8)
+    for p in range(12, 40, 3):             # families of near-duplicates and exact duplicates: equal medians
+        a, b = int(row0[start[p]]), int(row0[start[p + 1]])
+        desc[a:b] = desc[a]
+        if b - a > 3:
+            desc[a + 1, 0] ^= 1
+            desc[b - 1, 5] ^= 3
+    ref_desc, has = rm.distinctive(desc, start, kind)
+    # what a caller of the product gathers: the rows of the keyframes that are not bad, in map order
+    keep_rows, pstart = [], [0]
+    for p in range(len(counts)):
+        for k in range(start[p], start[p + 1]):
+            if kind[k] != 1:
+                keep_rows += list(range(int(row0[k]), int(row0[k + 1])))
+        pstart.append(len(keep_rows))
+    d2 = desc[keep_rows] if keep_rows else np.zeros((0, 32), np.uint8)
+    bi, bm = oracle.distinctive_descriptors(d2, np.asarray(pstart, np.int32))
+    for p in range(len(counts)):
+        n = pstart[p + 1] - pstart[p]
+        assert bool(has[p]) == (n > 0), p
+        if n:
+            assert 0 <= bi[p] < n
+            assert np.array_equal(ref_desc[p], d2[pstart[p] + bi[p]]), p
