@@ -395,3 +395,54 @@ def test_distinctive_descriptors_restatement(oracle):
         if n:
             assert 0 <= bi[p] < n
             assert np.array_equal(ref_desc[p], d2[pstart[p] + bi[p]]), p
+
+
+def _sorted_children(voc):
+    """the same tree with every node's children stored in ascending id order (what a text vocabulary file can express)"""
+    v = dict(voc)
+    ci = voc["child_ids"].copy()
+    cs = voc["child_start"]
+    for p in range(len(cs) - 1):
+        ci[cs[p]:cs[p + 1]] = np.sort(ci[cs[p]:cs[p + 1]])
+    v["child_ids"] = ci
+    return v
+
+
+@pytest.mark.parametrize("k,L,levelsup", [(10, 3, 1), (10, 3, 4), (6, 4, 2), (9, 2, 0), (3, 5, 4)])
+def test_vocabulary_transform_restatement(oracle, tmp_path, k, L, levelsup):
+    """Frame::ComputeBoW (src/Frame.cc:828-835): the restatement (oracle.vocab_transform + vocab_fold, what k_vocab_transform and the
+    host fold are held against) equals the reference's own vendored DBoW2 -- the vocabulary loaded by loadFromTextFile as ORB-SLAM3
+    loads ORBvoc.txt, TemplatedVocabulary::transform with its strict-'<' child choice, TF-IDF accumulation in feature order, the L1
+    normalisation over ascending word ids and the FeatureVector at `levelsup` levels above the leaves (nodes, feature lists, order);
+    doubles compared bit for bit.  Queries include exact node descriptors (distance 0) and descriptors equidistant from two
+    children (ties -> the first child); a few words carry weight 0 (stopped words: no BowVector / FeatureVector entry)."""
+    from oracle import refbow
+    if not refbow.available():
+        pytest.skip("oracle/_ref/libref_bow.so not built (needs /root/reference)")
+    voc = _sorted_children(bowsynth.vocabulary(k, L, 7 * k + L, ragged=False))
+    path = str(tmp_path / "voc.txt")
+    refbow.write_text_vocabulary(path, voc, k)
+    rv = refbow.Vocabulary(path)
+    try:
+        leaves = np.flatnonzero(voc["node_word_id"] >= 0)
+        assert rv.words() == len(leaves)
+        rng = np.random.default_rng(100 + k + L)
+        desc = np.concatenate([rng.integers(0, 256, (300, 32), dtype=np.uint8), voc["node_desc"][rng.choice(leaves, 40)],
+                               voc["node_desc"][1:1 + min(20, len(voc["node_desc"]) - 1)]])
+        # ties: a query exactly between two sibling descriptors (flip half of the differing bits of the first one)
+        cs, ci = voc["child_start"], voc["child_ids"]
+        a, b = voc["node_desc"][ci[cs[0]]], voc["node_desc"][ci[cs[0] + 1]]
+        diff = np.flatnonzero(np.unpackbits(a ^ b))
+        t = np.unpackbits(a).copy(); t[diff[: len(diff) // 2]] ^= 1
+        desc = np.concatenate([desc, np.packbits(t)[None, :]])
+        w, nid, wt = oracle.vocab_transform(voc, desc, levelsup)
+        assert np.array_equal(rv.transform_words(desc), w.astype(np.uint32))
+        ids, vals, (fn, fs, fx) = oracle.vocab_fold(w, nid, wt)
+        rids, rvals, (rfn, rfs, rfx) = rv.transform(desc, levelsup)
+        assert np.array_equal(ids, rids) and np.array_equal(vals.view(np.uint64), rvals.view(np.uint64))
+        assert np.array_equal(fn, rfn) and np.array_equal(fs, rfs) and np.array_equal(fx, rfx)
+        # empty input: empty containers
+        e = rv.transform(np.zeros((0, 32), np.uint8), levelsup)
+        assert len(e[0]) == 0 and len(e[2][0]) == 0
+    finally:
+        rv.close()
