@@ -91,3 +91,63 @@ def test_vocabulary_rejects_malformed_trees(orbx):
     bad = dict(voc); bad["L"] = 1                                                                            # deeper than L
     with pytest.raises(Exception):
         orbx.ORBVocabulary(bad)
+
+
+@pytest.mark.parametrize("k,L,levelsup", [(10, 4, 4), (10, 3, 2), (5, 5, 1)])
+def test_vocabulary_transform_vs_reference_dbow2(orbx, oracle, synth, tmp_path, k, L, levelsup):
+    """Frame::ComputeBoW on the GPU against the reference's OWN vendored DBoW2 (oracle/_ref/libref_bow.so: Thirdparty/DBoW2 compiled
+    unmodified; the vocabulary goes through loadFromTextFile as ORBvoc.txt does): BowVector ids and doubles, FeatureVector nodes and
+    feature lists, bit for bit.  levelsup = 4 is what Frame.cc:833 passes."""
+    from oracle import refbow
+    if not refbow.available():
+        pytest.skip("oracle/_ref/libref_bow.so not prebuilt (needs /root/reference at build time)")
+    voc = vocabulary(k, L, 11, False)
+    ci, cs = voc["child_ids"].copy(), voc["child_start"]
+    for p in range(len(cs) - 1):          # a text vocabulary lists children in id order
+        ci[cs[p]:cs[p + 1]] = np.sort(ci[cs[p]:cs[p + 1]])
+    voc["child_ids"] = ci
+    path = str(tmp_path / "voc.txt")
+    refbow.write_text_vocabulary(path, voc, k)
+    rv = refbow.Vocabulary(path)
+    ex = oracle.Extractor(1500, sincos_mode=oracle.SINCOS_PORTABLE)
+    _, kps, desc = ex(synth.frame(W, H, 31, 3, False), (0, 0))
+    rng = np.random.default_rng(2)
+    desc = np.concatenate([desc, voc["node_desc"][rng.integers(1, len(voc["node_desc"]), 200)], synth.random_descriptors(300, 4)])
+    m = orbx.ORBmatcher()
+    V = orbx.ORBVocabulary(voc)
+    try:
+        bi, bv, fv = V.transform(m, desc, levelsup)
+        rbi, rbv, rfv = rv.transform(desc, levelsup)
+        assert np.array_equal(bi, rbi) and bv.tobytes() == rbv.tobytes() and len(bi) > 50
+        assert all(np.array_equal(a, b) for a, b in zip(fv, rfv))
+        w, _, _ = V.transform_features(m, desc, levelsup)
+        assert np.array_equal(w.astype(np.uint32), rv.transform_words(desc))
+    finally:
+        V.close(); m.close(); rv.close()
+
+
+def test_distinctive_descriptors_vs_reference_body(orbx):
+    """k_distinctive against the reference's OWN MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:350-436, cut out of the
+    reference's file into oracle/_ref/libref_match.so): the descriptor the reference stores in mDescriptor is the row the GPU picks,
+    for clustered observations, tie families (duplicated rows) and single observations."""
+    from oracle import refmatch
+    if not refmatch.available():
+        pytest.skip("oracle/_ref/libref_match.so not prebuilt (needs /root/reference at build time)")
+    rng = np.random.default_rng(77)
+    desc, start = _observations(rng, 400, 40)
+    for p in range(0, 400, 7):            # tie families
+        a, b = int(start[p]), int(start[p + 1])
+        desc[a:b] = desc[a]
+        if b - a > 2:
+            desc[b - 1, 3] ^= 5
+    ref_desc, has = refmatch.distinctive(desc, start)
+    m = orbx.ORBmatcher()
+    try:
+        bi, bm = m.DistinctiveDescriptors(desc, start)
+        for p in range(400):
+            n = int(start[p + 1] - start[p])
+            assert bool(has[p]) == (n > 0)
+            if n:
+                assert np.array_equal(desc[start[p] + bi[p]], ref_desc[p]), p
+    finally:
+        m.close()
