@@ -13,7 +13,8 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "liborbx.so")
 SOURCES = ["orbx_extract.cu", "orbx_match.cu", "orbx_preproc.cu", "orbx_frame.cu", "orbx_allpairs.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--fmad=false",
-              "-Xcompiler", "-fPIC,-O2,-ffp-contract=off,-Wall,-Wno-unused-function", "-shared", "-cudart", "static", "-ldl"]
+              "-Xcompiler", "-fPIC,-O2,-ffp-contract=off,-Wall,-Wno-unused-function", "-shared", "-cudart", "static", "-ldl",
+              "-Xlinker", "--version-script=" + os.path.join(CSRC, "orbx.map")]   # only orbx_* is exported
 
 
 def _stale():

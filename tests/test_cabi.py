@@ -86,3 +86,12 @@ def test_static_knn2_rejects_oversize_and_bad_arguments_before_touching_the_devi
     assert lib.orbx_knn2_device_static(dummy, 5, None, 10, dummy, dummy, None, None) == orbx.ORBX_ERR_ARG
     assert lib.orbx_knn2_device_static(dummy, -1, dummy, 10, dummy, dummy, None, None) == orbx.ORBX_ERR_ARG
     assert lib.orbx_knn2_device_static(None, 0, None, 0, None, None, None, None) == orbx.ORBX_OK
+
+
+def test_library_exports_nothing_but_the_c_abi(orbx):
+    """liborbx.so's dynamic symbol table = the orbx_* entry points (csrc/orbx.map): no kernel stubs, C++ helpers or CUDA runtime leak out"""
+    import subprocess
+    out = subprocess.run(["nm", "-D", "--defined-only", orbx.LIB_PATH], capture_output=True, text=True, check=True).stdout
+    names = [l.split()[-1] for l in out.splitlines() if l.strip()]
+    assert names and all(n.startswith("orbx_") for n in names), [n for n in names if not n.startswith("orbx_")][:5]
+    assert set(_declared_symbols()) <= set(names)
