@@ -147,3 +147,31 @@ def test_literal_fma_build_difference_is_reported(synth):
         diff += int((ds != dl).any(axis=1).sum())
     print("descriptor rows differing between the FMA-contracted and the strict build: %d of %d" % (diff, rows))
     assert diff <= max(2, rows // 500)
+
+
+def test_random_geometries_equal_reference_source(oracle, synth):
+    """Seeded random image sizes, feature counts, scale factors, level counts, FAST thresholds and lapping areas (a 120-case run of the
+    same generator found no difference): restatement == the reference's compiled ORBextractor.cc, keypoints, descriptors, all levels.
+    Cases where a level's bordered region is more than twice as tall as wide are skipped: the reference divides by zero there
+    (nIni = round(width / height) = 0, ORBextractor.cc:541-543; the product answers ORBX_ERR_UNSUPPORTED)."""
+    rng = np.random.default_rng(2024)
+    ran = 0
+    for t in range(16):
+        w, h = int(rng.integers(80, 900)), int(rng.integers(80, 700))
+        if w < 0.55 * h:
+            w = int(0.6 * h)
+        nfeat = int(rng.integers(50, 2500)); scale = float(np.float32(rng.uniform(1.05, 1.6)))
+        nlev = int(rng.integers(2, 11)); ini = int(rng.integers(8, 40)); mn = int(rng.integers(2, ini + 1))
+        lap = (0, 0) if t % 3 else (int(rng.integers(0, w // 2)), int(rng.integers(w // 2, w)))
+        if min(w, h) / scale ** (nlev - 1) < 60:
+            nlev = max(2, int(np.log(min(w, h) / 60) / np.log(scale)))
+        if any(round((round(w / scale ** l) - 32) / max(1, round(h / scale ** l) - 32)) < 1 for l in range(nlev)):
+            continue
+        img = synth.frame(w, h, 500 + t, t)
+        rx = oref.RefExtractor(nfeat, scale, nlev, ini, mn)
+        ex = oracle.Extractor(nfeat, scale, nlev, ini, mn, sincos_mode=oracle.SINCOS_LIBM_F32)
+        _same(rx(img, lap), ex(img, lap), "case %d: %dx%d nfeat %d scale %.3f levels %d fast %d/%d lap %s" % (t, w, h, nfeat, scale, nlev, ini, mn, lap))
+        for l in range(nlev):
+            assert np.array_equal(rx.level(l), ex.level(l))
+        ran += 1
+    assert ran >= 12
