@@ -291,3 +291,30 @@ def test_second_device_from_worker_threads(orbx, synth):
     c = int(ref[0][0])
     assert int(out["latency"][0][0]) == c
     assert np.array_equal(out["latency"][2][0, :c], ref[2][0, :c]) and np.array_equal(out["latency"][3][0, :c], ref[3][0, :c])
+
+
+def test_random_geometries(orbx, oracle, synth):
+    """Seeded random image sizes, feature counts, scale factors, level counts, FAST thresholds and lapping areas (the generator of
+    tests/test_oracle_ref.py::test_random_geometries_equal_reference_source, where the oracle is held against the reference's compiled
+    ORBextractor.cc): keypoint records and descriptors byte-equal.  Same loop as tools/random_geometry_check.py."""
+    rng = np.random.default_rng(2024)
+    ran = 0
+    for t in range(14):
+        w, h = int(rng.integers(80, 900)), int(rng.integers(80, 700))
+        if w < 0.55 * h:
+            w = int(0.6 * h)
+        nfeat = int(rng.integers(50, 2500)); scale = float(np.float32(rng.uniform(1.05, 1.6)))
+        nlev = int(rng.integers(2, 11)); ini = int(rng.integers(8, 40)); mn = int(rng.integers(2, ini + 1))
+        lap = (0, 0) if t % 3 else (int(rng.integers(0, w // 2)), int(rng.integers(w // 2, w)))
+        if min(w, h) / scale ** (nlev - 1) < 60:
+            nlev = max(2, int(np.log(min(w, h) / 60) / np.log(scale)))
+        if any(round((round(w / scale ** l) - 32) / max(1, round(h / scale ** l) - 32)) < 1 for l in range(nlev)):
+            continue   # the reference divides by zero (nIni = 0); the product answers ORBX_ERR_UNSUPPORTED
+        img = synth.frame(w, h, 500 + t, t)
+        mo, ko, do = oracle.Extractor(nfeat, scale, nlev, ini, mn, sincos_mode=oracle.SINCOS_PORTABLE)(img, lap)
+        mg, kg, dg = orbx.ORBextractor(nfeat, scale, nlev, ini, mn)(img, None, lap)
+        what = "case %d: %dx%d nfeat %d scale %.4f levels %d fast %d/%d lap %s" % (t, w, h, nfeat, scale, nlev, ini, mn, lap)
+        assert mg == mo and len(kg) == len(ko), what
+        assert kg.tobytes() == ko.tobytes() and np.array_equal(dg, do), what
+        ran += 1
+    assert ran >= 10
