@@ -60,6 +60,7 @@ def test_search_by_projection_frame_frame(oracle, scene, mono, th, dz, ori):
     nm, kp = oracle.search_by_projection_window(B["kps"], B["desc"], cur.scale, *cam["size"], pj["valid"], pj["u"], pj["v"], pj["level"],
                                                 A["kps"]["angle"], W.desc[np.clip(mp, 0, None)], th, mode=1 if fwd else (2 if bwd else 0),
                                                 dist_th=100, any_mp_blocks=False, check_orientation=ori, kp_mp=kp0,
+                                                observed=W.n_obs[np.clip(mp, 0, None)] > 0,   # :2134-2136: a point without observations does not hold its keypoint
                                                 uRight=B["u_right"] if cam.get("bf", 0.0) > 0 else None, ur=pj["ur"])
     assert nm == nm_ref and nm > 50
     assert np.array_equal(_finish(kp, mp, pre), kp_ref)
