@@ -447,3 +447,26 @@ def test_vocabulary_transform_restatement(oracle, tmp_path, k, L, levelsup):
         assert len(e[0]) == 0 and len(e[2][0]) == 0
     finally:
         rv.close()
+
+
+@pytest.mark.parametrize("w,h,nfeat,fx,bf", [(752, 480, 1200, 435.2046959714599, 47.90639384423901), (512, 512, 1500, 190.97847715128717, 21.0),
+                                             (1241, 376, 2000, 718.856, 386.1448)])
+def test_compute_stereo_matches_restatement(oracle, w, h, nfeat, fx, bf):
+    """Frame::ComputeStereoMatches (src/Frame.cc:901-1079, cut out of the reference's Frame.cc) behind two reference extractors ==
+    oracle.stereo_matches behind two oracle extractors on seeded rectified pairs (EuRoC, a square rig, KITTI): left keypoints, mvuRight
+    and mvDepth byte for byte, on the CPU (the GPU test test_batch256_matches_oracle holds the kernels against both)."""
+    import importlib
+    synth = importlib.import_module("3_orb_slam3_selfnote_b200.synth")
+    mbf = np.float32(bf); mb = np.float32(mbf / np.float32(fx))
+    ref = rm.StereoFrames(nfeat)
+    exL = oracle.Extractor(nfeat, sincos_mode=oracle.SINCOS_LIBM_F32); exR = oracle.Extractor(nfeat, sincos_mode=oracle.SINCOS_LIBM_F32)
+    matched = 0
+    for f in (0, 3, 7, 12):
+        left, right = synth.frame(w, h, 2000 + w, f, False), synth.frame(w, h, 2000 + w, f, True)
+        r = ref(left, right, float(mb), float(mbf))
+        _, kl, dl = exL(left, (0, 0)); _, kr, dr = exR(right, (0, 0))
+        uo, do, _, _ = oracle.stereo_matches(exL, exR, kl, dl, kr, dr, mb, mbf)
+        assert r["kpsL"].tobytes() == kl.tobytes(), f
+        assert r["uRight"].tobytes() == uo.tobytes() and r["depth"].tobytes() == do.tobytes(), f
+        matched += int((uo >= 0).sum())
+    assert matched > 200
