@@ -10,14 +10,16 @@ f32 = np.float32
 
 
 def cam_center(R, t):
-    """-R^T t as cv::Mat evaluates `-Rcw.t()*tcw`: one gemm with the transposed flag (double accumulation), scaled by -1, to float"""
-    R = R.astype(np.float64); t = t.astype(np.float64)
+    """-R^T t as cv::Mat evaluates `-Rcw.t()*tcw` (ORBmatcher.cc:2038, Frame.cc:538): the unary minus MATERIALISES the transpose
+    (MatOp::subtract(Scalar, expr) assigns the expression to a Mat and scales it by -1), so the product is a plain 3x3 * 3x1 gemm with
+    alpha = -1 on the small-matrix path: float products summed left to right in float, then (float)(s * alpha).  (A gemm with the
+    GEMM_1_T flag would accumulate in double; cv2.gemm shows both, and the reference's compiled Frame::UpdatePoseMatrices gives the float
+    one -- tests/test_oracle_refmatch.py::test_is_in_frustum_and_grid_restatement depends on it to the last bit.)"""
+    R = R.astype(np.float32); t = t.astype(np.float32).reshape(-1)
     out = np.empty(3, np.float32)
     for i in range(3):
-        s = 0.0
-        for k in range(3):
-            s += R[k, i] * t[k]
-        out[i] = f32(-s)
+        s = f32(f32(f32(R[0, i] * t[0]) + f32(R[1, i] * t[1])) + f32(R[2, i] * t[2]))
+        out[i] = f32(np.float64(s) * -1.0)
     return out
 
 

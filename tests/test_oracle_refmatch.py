@@ -470,3 +470,47 @@ def test_compute_stereo_matches_restatement(oracle, w, h, nfeat, fx, bf):
         assert r["uRight"].tobytes() == uo.tobytes() and r["depth"].tobytes() == do.tobytes(), f
         matched += int((uo >= 0).sum())
     assert matched > 200
+
+
+@pytest.mark.parametrize("kb", [None, "tumvi"])
+def test_is_in_frustum_and_grid_restatement(oracle, kb):
+    """Frame::isInFrustum (src/Frame.cc:572-642 + MapPoint::PredictScale + Pinhole / KannalaBrandt8 project, all cut from the reference's
+    files) == oracle.is_in_frustum in its literal-libm mode, field by field, on 3 000 map points in front of / behind / beside the
+    camera, in and out of the scale-invariance range, facing towards and away; and Frame::GetFeaturesInArea (src/Frame.cc:744-813 over the
+    grid of AssignFeaturesToGrid) == oracle.features_in_area, indices in the reference's order, on random windows and level ranges."""
+    import frame_cases as fc
+    kbv = None if kb is None else fc.KB8_TUMVI
+    cam, P, normal, maxd, mind = fc.frustum_case(oracle, 3000, seed=5, log_mode=0, kb=kbv)
+    cam.logScaleFactor = float(np.log(np.float32(1.2)))
+    Tcw = np.eye(4, dtype=np.float32)
+    Tcw[:3, :3] = np.array(cam.Rcw[:], np.float32).reshape(3, 3); Tcw[:3, 3] = np.array(cam.tcw[:], np.float32)
+    # the camera centre as Frame::UpdatePoseMatrices forms it (mOw = -mRcw.t() * mtcw, a float gemm), not numpy's product
+    cam.Ow[:] = [float(x) for x in np.asarray(pro.cam_center(Tcw[:3, :3].copy(), Tcw[:3, 3].copy())).reshape(-1)]
+    rng = np.random.default_rng(9)
+    n = 1500
+    kps = np.zeros(n, oracle.KP_DTYPE)
+    kps["x"] = rng.uniform(0, 752, n).astype(np.float32); kps["y"] = rng.uniform(0, 480, n).astype(np.float32)
+    kps["octave"] = rng.integers(0, 8, n); kps["size"] = 31; kps["angle"] = rng.uniform(0, 360, n).astype(np.float32)
+    desc = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    view = rm.View(kps, desc, (cam.minX, cam.maxX, cam.minY, cam.maxY), K=(cam.fx, cam.fy, cam.cx, cam.cy), bf=cam.bf, b=cam.bf / cam.fx,
+                   u_right=np.full(n, -1, np.float32), Tcw=Tcw, kb=kbv)
+    pts = rm.Points(P, rng.integers(0, 256, (len(P), 32), dtype=np.uint8), normal, mind, maxd, np.ones(len(P), np.int32), np.zeros(len(P), np.uint8))
+    r = rm.is_in_frustum(view, pts, 0.5)
+    o = oracle.is_in_frustum(cam, P, normal, maxd, mind)
+    assert np.array_equal(r["in_view"], o["in_view"]) and 300 < int(o["in_view"].sum()) < 2700
+    iv = o["in_view"] != 0
+    for k in ("proj_x", "proj_y", "proj_xr", "depth", "view_cos"):
+        assert r[k][iv].tobytes() == o[k][iv].tobytes(), k
+    assert np.array_equal(r["level"][iv], o["level"][iv])
+    if kb is None:
+        # the grid over the image bounds (0, w, 0, h) that oracle.features_in_area assumes
+        gview = rm.View(kps, desc, (0.0, 752.0, 0.0, 480.0), K=(cam.fx, cam.fy, cam.cx, cam.cy), u_right=np.full(n, -1, np.float32))
+        hits = 0
+        for _ in range(200):
+            x, y, rad = float(rng.uniform(-20, 780)), float(rng.uniform(-20, 500)), float(rng.uniform(1, 90))
+            lo = int(rng.integers(-1, 6)); hi = int(rng.integers(lo, 8)) if lo >= 0 and rng.random() < 0.7 else -1
+            a = rm.features_in_area(gview, x, y, rad, lo, hi)
+            b = oracle.features_in_area(kps, 752, 480, x, y, rad, lo, hi)
+            assert np.array_equal(a, b), (x, y, rad, lo, hi)
+            hits += len(a)
+        assert hits > 500
