@@ -133,3 +133,18 @@ def test_hamming_matches_numpy(oracle):
         assert oracle.hamming(a[i], b[i]) == int(np.unpackbits(a[i] ^ b[i]).sum())
     assert oracle.hamming(a[0], a[0]) == 0
     assert oracle.hamming(np.zeros(32, np.uint8), np.full(32, 255, np.uint8)) == 256
+
+
+def test_primitives_on_random_sizes(oracle, synth):
+    """cv::resize / cv::GaussianBlur / cv::FAST restatements against live cv2 on seeded random image sizes (40-1400 x 40-900, synthetic
+    scenes and noise), resize ratios 1.05-2.6 and FAST thresholds 2-59; a 150-case run of the same generator found no difference."""
+    rng = np.random.default_rng(77)
+    for t in range(24):
+        w, h = int(rng.integers(40, 1400)), int(rng.integers(40, 900))
+        img = synth.frame(w, h, 900 + t, t) if t % 2 else rng.integers(0, 256, (h, w), dtype=np.uint8)
+        s = float(rng.uniform(1.05, 2.6))
+        dw, dh = max(8, int(round(w / s))), max(8, int(round(h / s)))
+        assert np.array_equal(oracle.resize(img, dw, dh), cv2.resize(img, (dw, dh), interpolation=cv2.INTER_LINEAR)), (w, h, dw, dh)
+        assert np.array_equal(oracle.blur7(img, oracle.TAPS_OCV4), cv2.GaussianBlur(img, (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101)), (w, h)
+        th = int(rng.integers(2, 60))
+        assert _cv_fast(img, th) == [tuple(r) for r in oracle.fast(img, th).tolist()], (w, h, th)
