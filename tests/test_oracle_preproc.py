@@ -59,3 +59,27 @@ def test_oracle_matches_live_cv2_on_random_inputs(oracle):
         assert np.array_equal(cv2.remap(g, mx, my, cv2.INTER_LINEAR), oracle.remap_linear(g, mx, my))
         for clip, tiles in [(3.0, (8, 8)), (1.0, (2, 7)), (0.0, (8, 8))]:
             assert np.array_equal(cv2.createCLAHE(clip, tiles).apply(g), oracle.clahe(g, clip, tiles))
+
+
+def test_preproc_on_random_sizes(oracle):
+    """cvtColor (BGR / RGBA), remap (INTER_LINEAR, a random distortion field incl. samples outside the image) and CLAHE (random clip
+    limits and tile grids, incl. sizes that need padding) against live cv2 on seeded random image sizes; an 80-case run found no
+    difference."""
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(55)
+    for t in range(12):
+        w, h = int(rng.integers(16, 1000)), int(rng.integers(16, 700))
+        col = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+        if t % 3 == 0:
+            col = cv2.GaussianBlur(col, (9, 9), 3)
+        assert np.array_equal(cv2.cvtColor(col, cv2.COLOR_RGBA2GRAY), oracle.cvt_gray(col, True)), (w, h)
+        c3 = np.ascontiguousarray(col[:, :, :3])
+        g = cv2.cvtColor(c3, cv2.COLOR_BGR2GRAY)
+        assert np.array_equal(g, oracle.cvt_gray(c3, False)), (w, h)
+        xx, yy = np.meshgrid(np.arange(w, dtype=np.float32), np.arange(h, dtype=np.float32))
+        mx = (xx * np.float32(rng.uniform(0.9, 1.1)) + np.float32(rng.uniform(-8, 8)) + np.float32(3) * np.sin(yy / 17).astype(np.float32)).astype(np.float32)
+        my = (yy * np.float32(rng.uniform(0.9, 1.1)) + np.float32(rng.uniform(-8, 8)) + np.float32(2) * np.cos(xx / 23).astype(np.float32)).astype(np.float32)
+        assert np.array_equal(cv2.remap(g, mx, my, cv2.INTER_LINEAR), oracle.remap_linear(g, mx, my)), (w, h)
+        clip = float(rng.choice([1.0, 2.0, 3.0, 4.5, 40.0])); tiles = (int(rng.integers(1, 12)), int(rng.integers(1, 12)))
+        if w >= tiles[0] and h >= tiles[1]:
+            assert np.array_equal(cv2.createCLAHE(clip, tiles).apply(g), oracle.clahe(g, clip, tiles)), (w, h, clip, tiles)
